@@ -32,6 +32,9 @@ dup_bytes(const void *src, size_t n)
     return p;
 }
 
+static const char EMPTY[1] = { 0 };
+#define NZ(p) ((p) != NULL ? (p) : EMPTY)
+
 static int
 load_tables(const orc_input_t *in, tsk_table_collection_t *tables)
 {
@@ -55,8 +58,8 @@ load_tables(const orc_input_t *in, tsk_table_collection_t *tables)
     }
     if (in->num_sites > 0) {
         ret = tsk_site_table_set_columns(&tables->sites, in->num_sites, in->site_position,
-            in->site_ancestral_state, (const tsk_size_t *) in->site_ancestral_state_offset,
-            in->site_metadata, (const tsk_size_t *) in->site_metadata_offset);
+            NZ(in->site_ancestral_state), (const tsk_size_t *) in->site_ancestral_state_offset,
+            NZ(in->site_metadata), (const tsk_size_t *) in->site_metadata_offset);
         if (ret != 0) {
             return msp_set_tsk_error(ret);
         }
@@ -64,8 +67,8 @@ load_tables(const orc_input_t *in, tsk_table_collection_t *tables)
     if (in->num_mutations > 0) {
         ret = tsk_mutation_table_set_columns(&tables->mutations, in->num_mutations,
             in->mutation_site, in->mutation_node, NULL, in->mutation_time,
-            in->mutation_derived_state,
-            (const tsk_size_t *) in->mutation_derived_state_offset, in->mutation_metadata,
+            NZ(in->mutation_derived_state),
+            (const tsk_size_t *) in->mutation_derived_state_offset, NZ(in->mutation_metadata),
             (const tsk_size_t *) in->mutation_metadata_offset);
         if (ret != 0) {
             return msp_set_tsk_error(ret);
