@@ -1,0 +1,192 @@
+/* msprime_b200 -- C ABI of the B200-native mutation overlay.
+ *
+ * This is the drop-in boundary for ONE path of msprime: the C call behind
+ * msprime.sim_mutations.  Everything is extern "C", plain pointers and sizes, no
+ * torch or CUDA types.  Each entry point names the reference interface it
+ * replaces (paths relative to the msprime source tree):
+ *
+ *   mspb_sim_mutations      <- msprime_sim_mutations, msprime/_msprimemodule.c:3047-3120
+ *                              (= mutgen_alloc + mutgen_set_rate_map +
+ *                              mutgen_set_time_interval + mutgen_generate,
+ *                              lib/mutgen.c:742-821,1304-1350)
+ *   mspb_ctx_load_tables    <- LightweightTableCollection.fromdict, the table hand-off
+ *                              in msprime/mutations.py:1686-1687
+ *   mspb_generate           <- mutgen_generate, lib/mutgen.c:1304
+ *   mspb_fetch              <- LightweightTableCollection.asdict, msprime/mutations.py:1699
+ *   mspb_strerror           <- msp_strerror, lib/util.c:344-359
+ *
+ * Status codes follow lib/util.h:48-136 (MSP_ERR_*); tskit integrity errors are
+ * folded in with bit 13 flipped exactly as msp_set_tsk_error does (lib/util.c:337).
+ * Codes <= -1000 are specific to this implementation (CUDA failures, replay limits).
+ *
+ * Table columns use the tskit layout (tskit_lwt_interface.h): float64 positions and
+ * times, int32 ids, ragged columns as a byte array plus an offset array of
+ * num_rows + 1 entries.  Offsets are uint64 here (tsk_size_t, tskit core.h:111).
+ */
+#ifndef MSPRIME_B200_H
+#define MSPRIME_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MSPB_VERSION "0.1.0"
+
+/* msprime numbering (lib/util.h) */
+#define MSPB_ERR_GENERIC (-1)
+#define MSPB_ERR_NO_MEMORY (-2)
+#define MSPB_ERR_BAD_PARAM_VALUE (-4)
+#define MSPB_ERR_DUPLICATE_SITE_POSITION (-21)
+#define MSPB_ERR_BAD_RATE_VALUE (-43)
+#define MSPB_ERR_INCOMPATIBLE_MUTATION_MAP_LENGTH (-44)
+#define MSPB_ERR_INSUFFICIENT_INTERVALS (-45)
+#define MSPB_ERR_INTERVAL_MAP_START_NON_ZERO (-46)
+#define MSPB_ERR_NONFINITE_INTERVAL_POSITION (-47)
+#define MSPB_ERR_INTERVAL_POSITIONS_UNSORTED (-48)
+#define MSPB_ERR_UNKNOWN_ALLELE (-51)
+#define MSPB_ERR_INSUFFICIENT_ALLELES (-52)
+#define MSPB_ERR_BAD_ROOT_PROBABILITIES (-53)
+#define MSPB_ERR_BAD_TRANSITION_MATRIX (-54)
+#define MSPB_ERR_UNKNOWN_TIME_NOT_SUPPORTED (-69)
+/* implementation specific */
+#define MSPB_ERR_CUDA (-1000)
+#define MSPB_ERR_NO_DEVICE (-1001)
+#define MSPB_ERR_TABLES_NOT_LOADED (-1002)
+#define MSPB_ERR_REPLAY_STREAM_EXHAUSTED (-1003)
+#define MSPB_ERR_REPLAY_REDRAW (-1004) /* stream would need a redraw (x >= hi or collision) */
+#define MSPB_ERR_TOO_MANY_ROWS (-1005) /* more than 2^31 - 1 sites or mutations */
+#define MSPB_ERR_UNSORTED_MUTATIONS (-1006) /* kept mutations not grouped by site */
+#define MSPB_ERR_NOT_GENERATED (-1007)
+
+enum { MSPB_MODEL_MATRIX = 0, MSPB_MODEL_INFINITE_ALLELES = 1 };
+
+/* Input tables (host memory, borrowed for the duration of the call). */
+typedef struct {
+    double sequence_length;
+    uint64_t num_nodes;
+    const double *node_time;
+    uint64_t num_edges;
+    const double *edge_left;
+    const double *edge_right;
+    const int32_t *edge_parent;
+    const int32_t *edge_child;
+    /* existing sites / mutations; read only when keep != 0 */
+    uint64_t num_sites;
+    const double *site_position;
+    const char *site_ancestral_state;
+    const uint64_t *site_ancestral_state_offset;
+    const char *site_metadata;
+    const uint64_t *site_metadata_offset;
+    uint64_t num_mutations;
+    const int32_t *mutation_site;
+    const int32_t *mutation_node;
+    const double *mutation_time; /* NULL = all unknown */
+    const char *mutation_derived_state;
+    const uint64_t *mutation_derived_state_offset;
+    const char *mutation_metadata;
+    const uint64_t *mutation_metadata_offset;
+} mspb_tables_t;
+
+/* Call parameters: rate map, model, flags, window, random source, genome slice. */
+typedef struct {
+    /* rate map: map_size intervals, map_size + 1 positions (lib/rate_map.c:45) */
+    uint64_t map_size;
+    const double *map_position;
+    const double *map_rate;
+    /* model (lib/msprime.h:440-470) */
+    int32_t model_kind;
+    uint64_t num_alleles;
+    const char *alleles;
+    const uint64_t *allele_offset; /* num_alleles + 1 */
+    const double *root_distribution; /* num_alleles */
+    const double *transition_matrix; /* num_alleles^2, row major */
+    uint64_t start_allele; /* infinite alleles: next_allele on entry */
+    /* flags and window (MSP_DISCRETE_SITES / MSP_KEEP_SITES, lib/msprime.h:66-68) */
+    int32_t discrete_genome;
+    int32_t keep;
+    double start_time;
+    double end_time;
+    /* random source: the native stream is Philox4x32-10 keyed by seed; a non-NULL
+     * replay_stream switches to the replay harness, where uniforms are consumed
+     * from the array in the reference's order (single slice only). */
+    uint64_t seed;
+    const double *replay_stream;
+    uint64_t replay_len;
+    /* genome slice [slice_left, slice_right) owned by this call; 0,0 = whole genome.
+     * The native stream is keyed by (edge, ordinal), so the union of the slices'
+     * outputs is identical to the single-slice output. */
+    double slice_left;
+    double slice_right;
+} mspb_params_t;
+
+/* Row and byte counts of the result of the last mspb_generate. */
+typedef struct {
+    uint64_t num_sites;
+    uint64_t num_mutations;
+    uint64_t num_new_mutations;
+    uint64_t ancestral_state_bytes;
+    uint64_t site_metadata_bytes;
+    uint64_t derived_state_bytes;
+    uint64_t mutation_metadata_bytes;
+    uint64_t next_allele; /* infinite alleles: counter after the call */
+    uint64_t draws; /* replay: uniforms consumed */
+    uint64_t num_new_sites;
+    double device_ms; /* CUDA-event time of the generate step */
+} mspb_counts_t;
+
+/* Output columns; caller-allocated to the sizes in mspb_counts_t (offset arrays
+ * are num_rows + 1 long).  Host pointers for mspb_fetch; mspb_device_columns
+ * fills the same struct with device pointers owned by the context. */
+typedef struct {
+    double *site_position;
+    char *site_ancestral_state;
+    uint64_t *site_ancestral_state_offset;
+    char *site_metadata;
+    uint64_t *site_metadata_offset;
+    int32_t *mutation_site;
+    int32_t *mutation_node;
+    int32_t *mutation_parent;
+    double *mutation_time;
+    char *mutation_derived_state;
+    uint64_t *mutation_derived_state_offset;
+    char *mutation_metadata;
+    uint64_t *mutation_metadata_offset;
+} mspb_columns_t;
+
+typedef struct mspb_ctx mspb_ctx_t;
+
+/* Context on CUDA device `device`; fails with MSPB_ERR_NO_DEVICE when there is no
+ * usable GPU (there is no CPU fallback). */
+int mspb_ctx_create(int device, mspb_ctx_t **ctx);
+void mspb_ctx_destroy(mspb_ctx_t *ctx);
+/* Validates (tskit check_integrity(0) subset, lib/mutgen.c:1316), uploads the tables
+ * and builds the child-sorted edge index.  Reusable across mspb_generate calls. */
+int mspb_ctx_load_tables(mspb_ctx_t *ctx, const mspb_tables_t *tables);
+/* Runs the overlay on the device; the result stays resident until the next call. */
+int mspb_generate(mspb_ctx_t *ctx, const mspb_params_t *params, mspb_counts_t *counts);
+/* Copies the resident result to host buffers. */
+int mspb_fetch(mspb_ctx_t *ctx, const mspb_columns_t *host_columns);
+/* Device pointers of the resident result (valid until the next mspb_generate). */
+int mspb_device_columns(mspb_ctx_t *ctx, mspb_columns_t *device_columns);
+/* Number of kernels this library launched since the context was created. */
+uint64_t mspb_kernel_launches(const mspb_ctx_t *ctx);
+/* Per-phase device milliseconds of the last mspb_generate (n <= MSPB_NUM_PHASES). */
+#define MSPB_NUM_PHASES 8
+int mspb_phase_ms(const mspb_ctx_t *ctx, float *ms, int n);
+const char *mspb_phase_name(int phase);
+
+/* One-shot form with the semantics of _msprime.sim_mutations: host tables in,
+ * malloc'd host columns out (release with mspb_columns_free). */
+int mspb_sim_mutations(int device, const mspb_tables_t *tables, const mspb_params_t *params,
+    mspb_counts_t *counts, mspb_columns_t *out);
+void mspb_columns_free(mspb_columns_t *cols);
+
+const char *mspb_strerror(int err);
+const char *mspb_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

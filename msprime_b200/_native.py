@@ -1,0 +1,297 @@
+"""ctypes binding of the C ABI in ``include/msprime_b200.h`` (``_mspb.so``).
+
+This is the thin extension layer the reference has in ``msprime/_msprimemodule.c``:
+it turns numpy columns into plain pointers, calls the CUDA library and maps status
+codes to the reference's exception classes (``_msprimemodule.c:80-96``):
+``LibraryError`` for MSP_ERR_* / tskit codes, ``InputError`` for rate-map input
+errors.  There is no CPU fallback: if the extension is missing or no GPU is usable
+the call fails loudly.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import tables as _tables
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+SO_PATH = os.path.join(HERE, "_mspb.so")
+
+MODEL_MATRIX = 0
+MODEL_INFINITE_ALLELES = 1
+NUM_PHASES = 8
+
+ERR_NO_DEVICE = -1001
+_RATE_MAP_ERRORS = {-43, -44, -45, -46, -47, -48}
+
+
+class LibraryError(Exception):
+    """Error raised by the native library (mirrors ``_msprime.LibraryError``)."""
+
+    def __init__(self, message, status=None):
+        super().__init__(message)
+        self.status = status
+
+
+class InputError(Exception):
+    """Bad user input detected by the native library (mirrors ``_msprime.InputError``)."""
+
+    def __init__(self, message, status=None):
+        super().__init__(message)
+        self.status = status
+
+
+class _Tables(C.Structure):
+    _fields_ = [
+        ("sequence_length", C.c_double),
+        ("num_nodes", C.c_uint64), ("node_time", C.c_void_p),
+        ("num_edges", C.c_uint64), ("edge_left", C.c_void_p), ("edge_right", C.c_void_p),
+        ("edge_parent", C.c_void_p), ("edge_child", C.c_void_p),
+        ("num_sites", C.c_uint64), ("site_position", C.c_void_p),
+        ("site_ancestral_state", C.c_void_p), ("site_ancestral_state_offset", C.c_void_p),
+        ("site_metadata", C.c_void_p), ("site_metadata_offset", C.c_void_p),
+        ("num_mutations", C.c_uint64), ("mutation_site", C.c_void_p), ("mutation_node", C.c_void_p),
+        ("mutation_time", C.c_void_p),
+        ("mutation_derived_state", C.c_void_p), ("mutation_derived_state_offset", C.c_void_p),
+        ("mutation_metadata", C.c_void_p), ("mutation_metadata_offset", C.c_void_p),
+    ]
+
+
+class _Params(C.Structure):
+    _fields_ = [
+        ("map_size", C.c_uint64), ("map_position", C.c_void_p), ("map_rate", C.c_void_p),
+        ("model_kind", C.c_int32), ("num_alleles", C.c_uint64), ("alleles", C.c_void_p),
+        ("allele_offset", C.c_void_p), ("root_distribution", C.c_void_p),
+        ("transition_matrix", C.c_void_p), ("start_allele", C.c_uint64),
+        ("discrete_genome", C.c_int32), ("keep", C.c_int32),
+        ("start_time", C.c_double), ("end_time", C.c_double),
+        ("seed", C.c_uint64), ("replay_stream", C.c_void_p), ("replay_len", C.c_uint64),
+        ("slice_left", C.c_double), ("slice_right", C.c_double),
+    ]
+
+
+class _Counts(C.Structure):
+    _fields_ = [
+        ("num_sites", C.c_uint64), ("num_mutations", C.c_uint64), ("num_new_mutations", C.c_uint64),
+        ("ancestral_state_bytes", C.c_uint64), ("site_metadata_bytes", C.c_uint64),
+        ("derived_state_bytes", C.c_uint64), ("mutation_metadata_bytes", C.c_uint64),
+        ("next_allele", C.c_uint64), ("draws", C.c_uint64), ("num_new_sites", C.c_uint64),
+        ("device_ms", C.c_double),
+    ]
+
+
+_COLUMNS = [
+    ("site_position", np.float64), ("site_ancestral_state", np.uint8),
+    ("site_ancestral_state_offset", np.uint64), ("site_metadata", np.uint8),
+    ("site_metadata_offset", np.uint64), ("mutation_site", np.int32), ("mutation_node", np.int32),
+    ("mutation_parent", np.int32), ("mutation_time", np.float64), ("mutation_derived_state", np.uint8),
+    ("mutation_derived_state_offset", np.uint64), ("mutation_metadata", np.uint8),
+    ("mutation_metadata_offset", np.uint64),
+]
+
+
+class _Columns(C.Structure):
+    _fields_ = [(name, C.c_void_p) for name, _ in _COLUMNS]
+
+
+EXPORTED_SYMBOLS = [
+    "mspb_ctx_create", "mspb_ctx_destroy", "mspb_ctx_load_tables", "mspb_generate", "mspb_fetch",
+    "mspb_device_columns", "mspb_kernel_launches", "mspb_phase_ms", "mspb_phase_name",
+    "mspb_sim_mutations", "mspb_columns_free", "mspb_strerror", "mspb_version",
+]
+
+_lib = None
+
+
+def lib():
+    """Loads ``_mspb.so``; raises RuntimeError (never falls back) when it is not built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(SO_PATH):
+            raise RuntimeError(
+                f"msprime_b200: CUDA extension {SO_PATH} is not built "
+                "(run `python -m msprime_b200.build`); there is no CPU fallback")
+        L = C.CDLL(SO_PATH)
+        L.mspb_ctx_create.argtypes = [C.c_int, C.POINTER(C.c_void_p)]
+        L.mspb_ctx_destroy.argtypes = [C.c_void_p]
+        L.mspb_ctx_destroy.restype = None
+        L.mspb_ctx_load_tables.argtypes = [C.c_void_p, C.POINTER(_Tables)]
+        L.mspb_generate.argtypes = [C.c_void_p, C.POINTER(_Params), C.POINTER(_Counts)]
+        L.mspb_fetch.argtypes = [C.c_void_p, C.POINTER(_Columns)]
+        L.mspb_device_columns.argtypes = [C.c_void_p, C.POINTER(_Columns)]
+        L.mspb_kernel_launches.argtypes = [C.c_void_p]
+        L.mspb_kernel_launches.restype = C.c_uint64
+        L.mspb_phase_ms.argtypes = [C.c_void_p, C.POINTER(C.c_float), C.c_int]
+        L.mspb_phase_name.argtypes = [C.c_int]
+        L.mspb_phase_name.restype = C.c_char_p
+        L.mspb_strerror.argtypes = [C.c_int]
+        L.mspb_strerror.restype = C.c_char_p
+        L.mspb_version.restype = C.c_char_p
+        _lib = L
+    return _lib
+
+
+def strerror(status: int) -> str:
+    return lib().mspb_strerror(int(status)).decode()
+
+
+def check(status: int):
+    if status == 0:
+        return
+    msg = strerror(status)
+    if status in _RATE_MAP_ERRORS:
+        raise InputError(f"Input error in mutation rate map: {msg}", status)
+    raise LibraryError(msg, status)
+
+
+def _c(a, dtype):
+    return np.ascontiguousarray(np.asarray(a, dtype=dtype))
+
+
+def _p(a):
+    return a.ctypes.data
+
+
+class Params:
+    """Keeps the numpy arrays behind a ``mspb_params_t`` alive."""
+
+    def __init__(self, *, map_position, map_rate, model, discrete_genome, keep, start_time, end_time,
+                 seed=0, replay_stream=None, slice_left=0.0, slice_right=0.0):
+        self._hold = []
+        p = _Params()
+        pos, rate = _c(map_position, np.float64), _c(map_rate, np.float64)
+        if pos.ndim != 1 or rate.ndim != 1 or len(pos) != len(rate) + 1:
+            # _msprimemodule.c:155-204 (parse_rate_map)
+            raise ValueError("The position array must be one larger than the rate array")
+        self._hold += [pos, rate]
+        p.map_size, p.map_position, p.map_rate = len(rate), _p(pos), _p(rate)
+        p.model_kind = model["kind"]
+        if model["kind"] == MODEL_MATRIX:
+            data, off = _tables.encode_ragged(model["alleles"])
+            root = _c(model["root_distribution"], np.float64)
+            mat = _c(model["transition_matrix"], np.float64)
+            self._hold += [data, off, root, mat]
+            p.num_alleles = len(model["alleles"])
+            p.alleles, p.allele_offset = _p(data), _p(off)
+            p.root_distribution, p.transition_matrix = _p(root), _p(mat)
+        else:
+            p.start_allele = int(model["start_allele"]) & 0xFFFFFFFFFFFFFFFF
+        p.discrete_genome, p.keep = int(bool(discrete_genome)), int(bool(keep))
+        p.start_time, p.end_time = float(start_time), float(end_time)
+        p.seed = int(seed) & 0xFFFFFFFFFFFFFFFF
+        if replay_stream is not None:
+            st = _c(replay_stream, np.float64)
+            self._hold.append(st)
+            p.replay_stream, p.replay_len = _p(st), len(st)
+        p.slice_left, p.slice_right = float(slice_left), float(slice_right)
+        self.struct = p
+
+
+class Context:
+    """One GPU context: upload a tree sequence once, overlay mutations many times."""
+
+    def __init__(self, device: int = 0):
+        self._h = C.c_void_p()
+        check(lib().mspb_ctx_create(int(device), C.byref(self._h)))
+        self.device = int(device)
+        self.counts = None
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h:
+            lib().mspb_ctx_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def load_tables(self, d):
+        """``d`` is a tskit ``asdict()``-style dict of numpy columns."""
+        hold = []
+        t = _Tables()
+        t.sequence_length = float(d["sequence_length"])
+        nt = _c(d["nodes"]["time"], np.float64)
+        e = d["edges"]
+        el, er = _c(e["left"], np.float64), _c(e["right"], np.float64)
+        ep, ec = _c(e["parent"], np.int32), _c(e["child"], np.int32)
+        hold += [nt, el, er, ep, ec]
+        t.num_nodes, t.node_time = len(nt), _p(nt)
+        t.num_edges = len(el)
+        t.edge_left, t.edge_right, t.edge_parent, t.edge_child = _p(el), _p(er), _p(ep), _p(ec)
+        s = d.get("sites")
+        ns = 0 if s is None else len(s["position"])
+        t.num_sites = ns
+        if ns > 0:
+            sp = _c(s["position"], np.float64)
+            sa, sao = _tables.ragged_u64(s, "ancestral_state", ns)
+            sm, smo = _tables.ragged_u64(s, "metadata", ns)
+            hold += [sp, sa, sao, sm, smo]
+            t.site_position = _p(sp)
+            t.site_ancestral_state, t.site_ancestral_state_offset = _p(sa), _p(sao)
+            t.site_metadata, t.site_metadata_offset = _p(sm), _p(smo)
+        m = d.get("mutations")
+        nm = 0 if m is None else len(m["site"])
+        t.num_mutations = nm
+        if nm > 0:
+            ms, mn = _c(m["site"], np.int32), _c(m["node"], np.int32)
+            md, mdo = _tables.ragged_u64(m, "derived_state", nm)
+            mm, mmo = _tables.ragged_u64(m, "metadata", nm)
+            hold += [ms, mn, md, mdo, mm, mmo]
+            t.mutation_site, t.mutation_node = _p(ms), _p(mn)
+            if m.get("time") is not None:
+                mt = _c(m["time"], np.float64)
+                hold.append(mt)
+                t.mutation_time = _p(mt)
+            t.mutation_derived_state, t.mutation_derived_state_offset = _p(md), _p(mdo)
+            t.mutation_metadata, t.mutation_metadata_offset = _p(mm), _p(mmo)
+        check(lib().mspb_ctx_load_tables(self._h, C.byref(t)))
+        del hold
+
+    def generate(self, params: Params):
+        c = _Counts()
+        check(lib().mspb_generate(self._h, C.byref(params.struct), C.byref(c)))
+        self.counts = {name: getattr(c, name) for name, _ in _Counts._fields_}
+        return self.counts
+
+    def fetch(self):
+        """Copies the resident result to fresh numpy arrays: ``{"sites": {...}, "mutations": {...}}``."""
+        c = self.counts
+        S, M = c["num_sites"], c["num_mutations"]
+        sizes = {
+            "site_position": S, "site_ancestral_state": c["ancestral_state_bytes"],
+            "site_ancestral_state_offset": S + 1, "site_metadata": c["site_metadata_bytes"],
+            "site_metadata_offset": S + 1, "mutation_site": M, "mutation_node": M, "mutation_parent": M,
+            "mutation_time": M, "mutation_derived_state": c["derived_state_bytes"],
+            "mutation_derived_state_offset": M + 1, "mutation_metadata": c["mutation_metadata_bytes"],
+            "mutation_metadata_offset": M + 1,
+        }
+        cols = _Columns()
+        arrays = {}
+        for name, dtype in _COLUMNS:
+            a = np.empty(sizes[name], dtype=dtype)
+            arrays[name] = a
+            setattr(cols, name, _p(a) if a.size > 0 else None)
+        check(lib().mspb_fetch(self._h, C.byref(cols)))
+        sites = {k[len("site_"):]: v for k, v in arrays.items() if k.startswith("site_")}
+        muts = {k[len("mutation_"):]: v for k, v in arrays.items() if k.startswith("mutation_")}
+        return {"sites": sites, "mutations": muts}
+
+    def device_columns(self):
+        """Raw device pointers (ints) of the resident result, with element counts and dtypes."""
+        cols = _Columns()
+        check(lib().mspb_device_columns(self._h, C.byref(cols)))
+        return {name: getattr(cols, name) for name, _ in _COLUMNS}
+
+    def kernel_launches(self) -> int:
+        return int(lib().mspb_kernel_launches(self._h))
+
+    def phase_ms(self):
+        buf = (C.c_float * NUM_PHASES)()
+        check(lib().mspb_phase_ms(self._h, buf, NUM_PHASES))
+        return {lib().mspb_phase_name(i).decode(): float(buf[i]) for i in range(NUM_PHASES)}

@@ -1,0 +1,43 @@
+"""Builds the CUDA extension in-tree for sm_100a: ``python -m msprime_b200.build``.
+
+nvcc cross-compiles without a GPU.  ``-fmad=false`` keeps the arithmetic of the
+replay harness identical to the reference's (no fused multiply-add contraction)."""
+from __future__ import annotations
+
+import os
+import subprocess
+import sys
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+SRC = os.path.join(HERE, "csrc", "mspb_api.cu")
+OUT = os.path.join(HERE, "_mspb.so")
+DEPS = [os.path.join(HERE, "csrc", f) for f in
+        ("mspb_api.cu", "kernels.cuh", "sort.cuh", "common.cuh", "replay.cuh")] + [
+    os.path.join(HERE, "..", "include", "msprime_b200.h")]
+
+NVCC_FLAGS = [
+    "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
+    "--extended-lambda", "-fmad=false", "-Xcompiler", "-fPIC", "-shared",
+]
+
+
+def needs_build() -> bool:
+    if not os.path.exists(OUT):
+        return True
+    t = os.path.getmtime(OUT)
+    return any(os.path.exists(d) and os.path.getmtime(d) > t for d in DEPS)
+
+
+def build(force: bool = False, verbose: bool = False) -> str:
+    if force or needs_build():
+        nvcc = os.environ.get("NVCC", "nvcc")
+        cmd = [nvcc, *NVCC_FLAGS, "-o", OUT, SRC]
+        if verbose:
+            cmd.insert(1, "-Xptxas=-v")
+            print(" ".join(cmd), file=sys.stderr)
+        subprocess.run(cmd, check=True)
+    return OUT
+
+
+if __name__ == "__main__":
+    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))

@@ -1,0 +1,1193 @@
+// msprime_b200: C ABI and host orchestration (see include/msprime_b200.h).
+//
+// The host side only validates parameters, sizes buffers and launches kernels; all
+// table work happens on the device.  There is no CPU fallback: without a usable GPU
+// mspb_ctx_create fails with MSPB_ERR_NO_DEVICE.
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <cmath>
+#include <cfloat>
+#include <vector>
+
+#include "../../include/msprime_b200.h"
+#include "kernels.cuh"
+
+using namespace mspb;
+
+#define TSK_E(code) ((code) ^ (1 << 13))
+
+namespace {
+
+template <typename T>
+struct DBuf {
+    T *p = nullptr;
+    size_t cap = 0;
+    int ensure(size_t n)
+    {
+        if (n <= cap && p != nullptr) {
+            return 0;
+        }
+        if (p != nullptr) {
+            cudaFree(p);
+            p = nullptr;
+        }
+        size_t want = n + n / 8 + 64;
+        if (cudaMalloc((void **) &p, want * sizeof(T)) != cudaSuccess) {
+            cap = 0;
+            p = nullptr;
+            cudaGetLastError();
+            return MSPB_ERR_NO_MEMORY;
+        }
+        cap = want;
+        return 0;
+    }
+    void release()
+    {
+        if (p != nullptr) {
+            cudaFree(p);
+        }
+        p = nullptr;
+        cap = 0;
+    }
+};
+
+struct HostTotals {
+    uint32_t count_total, local_total;
+    uint32_t num_sites, num_mut_rows, num_draws, collisions;
+    uint64_t der_bytes, mmd_bytes, anc_bytes, smd_bytes;
+    unsigned long long first_bad; // validation: (row << 16 | code index), min wins
+    int err;
+    uint32_t fractional_sites; // kept site positions that are not integers < 2^32
+    ReplayTotals replay;
+};
+
+} // namespace
+
+struct mspb_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[MSPB_NUM_PHASES + 1] = {};
+    float phase_ms[MSPB_NUM_PHASES] = {};
+    uint64_t launches = 0;
+    bool tables_loaded = false, generated = false;
+    // tables
+    double L = 0;
+    uint64_t N = 0, E = 0, S0 = 0, M0 = 0;
+    bool have_mut_time = false, kept_fractional = false;
+    DBuf<double> node_time, edge_left, edge_right, ci_left, ci_right;
+    DBuf<int32_t> edge_parent, edge_child, ci_parent;
+    DBuf<uint32_t> child_start;
+    DBuf<double> k_site_pos, k_mut_time;
+    DBuf<uint64_t> k_site_anc_off, k_site_md_off, k_mut_der_off, k_mut_md_off;
+    DBuf<char> k_site_anc, k_site_md, k_mut_der, k_mut_md;
+    DBuf<int32_t> k_mut_site, k_mut_node, k_site_allele, k_mut_allele;
+    // call parameters on the device
+    DBuf<double> map_pos, map_rate, map_cum, model_root, model_matrix, replay;
+    DBuf<char> model_alleles;
+    DBuf<uint64_t> model_allele_off;
+    // work
+    DBuf<uint32_t> count, local, goff, loff, scan_tiles32;
+    DBuf<uint64_t> scan_tiles64;
+    DBuf<double> rec_pos, rec_time;
+    DBuf<int32_t> rec_node;
+    DBuf<uint32_t> rec_ord;
+    DBuf<uint64_t> keys0, keys1;
+    DBuf<uint32_t> vals0, vals1, tile_hist, rs_scan_tiles;
+    DBuf<uint64_t> or_and;
+    DBuf<uint32_t> site_scan, mut_scan, draw_scan;
+    DBuf<int32_t> parent, state, site_state;
+    DBuf<uint64_t> der_scan, mmd_scan, anc_scan, smd_scan;
+    DBuf<uint32_t> rp_edge, rp_interval, rp_count, rp_out_off;
+    DBuf<uint64_t> rp_stream_off;
+    DBuf<char> dev_totals; // HostTotals mirror
+    HostTotals *host = nullptr; // pinned
+    uint64_t *or_and_host = nullptr; // pinned
+    // outputs
+    DBuf<double> o_site_pos, o_mut_time;
+    DBuf<char> o_site_anc, o_site_md, o_mut_der, o_mut_md;
+    DBuf<uint64_t> o_site_anc_off, o_site_md_off, o_mut_der_off, o_mut_md_off;
+    DBuf<int32_t> o_mut_site, o_mut_node, o_mut_parent;
+    mspb_counts_t counts = {};
+};
+
+static const char *const PHASE_NAMES[MSPB_NUM_PHASES] = { "params+kept", "K1 count+scan", "K2 place", "K3 sort",
+    "order+flags", "K4 resolve", "byte scans", "K5 emit" };
+
+extern "C" const char *mspb_phase_name(int phase)
+{
+    return (phase >= 0 && phase < MSPB_NUM_PHASES) ? PHASE_NAMES[phase] : "";
+}
+
+extern "C" const char *mspb_version(void)
+{
+    return MSPB_VERSION;
+}
+
+extern "C" const char *mspb_strerror(int err)
+{
+    switch (err) {
+        case 0:
+            return "ok";
+        case MSPB_ERR_GENERIC:
+            return "Generic error; please file a bug report";
+        case MSPB_ERR_NO_MEMORY:
+            return "Out of memory";
+        case MSPB_ERR_BAD_PARAM_VALUE:
+            return "Bad parameter value provided";
+        case MSPB_ERR_DUPLICATE_SITE_POSITION:
+            return "Duplicate site positions.";
+        case MSPB_ERR_BAD_RATE_VALUE:
+            return "Rates must be non-negative and finite";
+        case MSPB_ERR_INCOMPATIBLE_MUTATION_MAP_LENGTH:
+            return "Incompatible mutation map: sequence length differs from that of the tree sequence.";
+        case MSPB_ERR_INSUFFICIENT_INTERVALS:
+            return "At least one interval must be specified.";
+        case MSPB_ERR_INTERVAL_MAP_START_NON_ZERO:
+            return "The first interval must start with zero";
+        case MSPB_ERR_NONFINITE_INTERVAL_POSITION:
+            return "Interval positions must be finite.";
+        case MSPB_ERR_INTERVAL_POSITIONS_UNSORTED:
+            return "Interval positions must be listed in increasing order";
+        case MSPB_ERR_UNKNOWN_ALLELE:
+            return "Existing allele(s) incompatible with mutation model alphabet.";
+        case MSPB_ERR_INSUFFICIENT_ALLELES:
+            return "Must have at least two alleles.";
+        case MSPB_ERR_BAD_ROOT_PROBABILITIES:
+            return "Root probabilities must be nonnegative and sum to one.";
+        case MSPB_ERR_BAD_TRANSITION_MATRIX:
+            return "Each row of the transition matrix must be nonnegative and sum to one.";
+        case MSPB_ERR_UNKNOWN_TIME_NOT_SUPPORTED:
+            return "Kept mutations must have known mutation times (which can be added using "
+                   "compute_mutation_times).";
+        case MSPB_ERR_CUDA:
+            return "CUDA runtime error";
+        case MSPB_ERR_NO_DEVICE:
+            return "No usable CUDA device (this library has no CPU fallback)";
+        case MSPB_ERR_TABLES_NOT_LOADED:
+            return "Tables have not been loaded into the context";
+        case MSPB_ERR_REPLAY_STREAM_EXHAUSTED:
+            return "Replay stream exhausted";
+        case MSPB_ERR_REPLAY_REDRAW:
+            return "Replay stream needs a redraw (value >= 1, x >= hi or a position collision)";
+        case MSPB_ERR_TOO_MANY_ROWS:
+            return "Too many rows for 32-bit ids";
+        case MSPB_ERR_UNSORTED_MUTATIONS:
+            return "Kept mutations must be grouped by site in site order";
+        case MSPB_ERR_NOT_GENERATED:
+            return "No result is resident: call mspb_generate first";
+        default:
+            break;
+    }
+    if (err < 0 && !(err & (1 << 13))) {
+        return "tskit table integrity error (code = err ^ 8192)";
+    }
+    return "Unknown error";
+}
+
+#define CUDA_OK(call)                                                                                                  \
+    do {                                                                                                               \
+        cudaError_t e__ = (call);                                                                                      \
+        if (e__ != cudaSuccess) {                                                                                      \
+            fprintf(stderr, "msprime_b200: CUDA error %s at %s:%d\n", cudaGetErrorString(e__), __FILE__, __LINE__);    \
+            return MSPB_ERR_CUDA;                                                                                      \
+        }                                                                                                              \
+    } while (0)
+
+#define TRY(call)                                                                                                      \
+    do {                                                                                                               \
+        int r__ = (call);                                                                                              \
+        if (r__ != 0) {                                                                                                \
+            return r__;                                                                                                \
+        }                                                                                                              \
+    } while (0)
+
+static inline unsigned grid_for(uint64_t n, unsigned threads)
+{
+    return (unsigned) ((n + threads - 1) / threads);
+}
+
+template <typename T>
+static int upload(DBuf<T> &dst, const T *src, size_t n, cudaStream_t st)
+{
+    TRY(dst.ensure(n > 0 ? n : 1));
+    if (n > 0) {
+        CUDA_OK(cudaMemcpyAsync(dst.p, src, n * sizeof(T), cudaMemcpyHostToDevice, st));
+    }
+    return 0;
+}
+
+extern "C" int mspb_ctx_create(int device, mspb_ctx_t **out)
+{
+    int count = 0;
+    if (out == nullptr) {
+        return MSPB_ERR_BAD_PARAM_VALUE;
+    }
+    *out = nullptr;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count <= 0 || device < 0 || device >= count) {
+        cudaGetLastError();
+        return MSPB_ERR_NO_DEVICE;
+    }
+    if (cudaSetDevice(device) != cudaSuccess) {
+        cudaGetLastError();
+        return MSPB_ERR_NO_DEVICE;
+    }
+    mspb_ctx *ctx = new mspb_ctx();
+    ctx->device = device;
+    if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) {
+        delete ctx;
+        return MSPB_ERR_CUDA;
+    }
+    for (auto &e : ctx->ev) {
+        cudaEventCreate(&e);
+    }
+    if (cudaMallocHost((void **) &ctx->host, sizeof(HostTotals)) != cudaSuccess
+        || cudaMallocHost((void **) &ctx->or_and_host, 2 * sizeof(uint64_t)) != cudaSuccess
+        || ctx->dev_totals.ensure(sizeof(HostTotals)) != 0 || ctx->or_and.ensure(2) != 0) {
+        mspb_ctx_destroy(ctx);
+        return MSPB_ERR_NO_MEMORY;
+    }
+    *out = ctx;
+    return 0;
+}
+
+extern "C" void mspb_ctx_destroy(mspb_ctx_t *ctx)
+{
+    if (ctx == nullptr) {
+        return;
+    }
+    cudaSetDevice(ctx->device);
+    if (ctx->stream != nullptr) {
+        cudaStreamSynchronize(ctx->stream);
+    }
+#define REL(b) ctx->b.release()
+    REL(node_time); REL(edge_left); REL(edge_right); REL(ci_left); REL(ci_right);
+    REL(edge_parent); REL(edge_child); REL(ci_parent); REL(child_start);
+    REL(k_site_pos); REL(k_mut_time); REL(k_site_anc_off); REL(k_site_md_off); REL(k_mut_der_off);
+    REL(k_mut_md_off); REL(k_site_anc); REL(k_site_md); REL(k_mut_der); REL(k_mut_md);
+    REL(k_mut_site); REL(k_mut_node); REL(k_site_allele); REL(k_mut_allele);
+    REL(map_pos); REL(map_rate); REL(map_cum); REL(model_root); REL(model_matrix); REL(replay);
+    REL(model_alleles); REL(model_allele_off);
+    REL(count); REL(local); REL(goff); REL(loff); REL(scan_tiles32); REL(scan_tiles64);
+    REL(rec_pos); REL(rec_time); REL(rec_node); REL(rec_ord); REL(keys0); REL(keys1); REL(vals0); REL(vals1);
+    REL(tile_hist); REL(rs_scan_tiles); REL(or_and); REL(site_scan); REL(mut_scan); REL(draw_scan);
+    REL(parent); REL(state); REL(site_state); REL(der_scan); REL(mmd_scan); REL(anc_scan); REL(smd_scan);
+    REL(rp_edge); REL(rp_interval); REL(rp_count); REL(rp_out_off); REL(rp_stream_off); REL(dev_totals);
+    REL(o_site_pos); REL(o_mut_time); REL(o_site_anc); REL(o_site_md); REL(o_mut_der); REL(o_mut_md);
+    REL(o_site_anc_off); REL(o_site_md_off); REL(o_mut_der_off); REL(o_mut_md_off);
+    REL(o_mut_site); REL(o_mut_node); REL(o_mut_parent);
+#undef REL
+    if (ctx->host != nullptr) {
+        cudaFreeHost(ctx->host);
+    }
+    if (ctx->or_and_host != nullptr) {
+        cudaFreeHost(ctx->or_and_host);
+    }
+    for (auto &e : ctx->ev) {
+        if (e != nullptr) {
+            cudaEventDestroy(e);
+        }
+    }
+    if (ctx->stream != nullptr) {
+        cudaStreamDestroy(ctx->stream);
+    }
+    delete ctx;
+}
+
+extern "C" uint64_t mspb_kernel_launches(const mspb_ctx_t *ctx)
+{
+    return ctx == nullptr ? 0 : ctx->launches;
+}
+
+extern "C" int mspb_phase_ms(const mspb_ctx_t *ctx, float *ms, int n)
+{
+    if (ctx == nullptr || ms == nullptr) {
+        return MSPB_ERR_BAD_PARAM_VALUE;
+    }
+    for (int i = 0; i < n && i < MSPB_NUM_PHASES; i++) {
+        ms[i] = ctx->phase_ms[i];
+    }
+    return 0;
+}
+
+// ---------------------------------------------------------------- table validation
+// The subset of tskit's check_integrity(options=0) that the reference runs before
+// generating (lib/mutgen.c:1316; tskit tables.c:10397-10470, 10519-10531, 10565-10598).
+// The lowest (table, row) wins so the reported error matches a serial scan.
+namespace {
+
+__device__ __forceinline__ void report_bad(unsigned long long *first_bad, int table, uint64_t row, int code)
+{
+    const unsigned long long v
+        = ((unsigned long long) table << 60) | ((unsigned long long) row << 16) | (unsigned long long) (-code);
+    atomicMin(first_bad, v);
+}
+
+__global__ void validate_nodes_kernel(uint64_t n, const double *time, unsigned long long *first_bad)
+{
+    const uint64_t j = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (j < n && !isfinite(time[j])) {
+        report_bad(first_bad, 0, j, -210);
+    }
+}
+
+__global__ void validate_edges_kernel(TreeSeqView ts, unsigned long long *first_bad)
+{
+    const uint64_t j = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= ts.num_edges) {
+        return;
+    }
+    const int32_t p = ts.edge_parent[j], c = ts.edge_child[j];
+    const double l = ts.edge_left[j], r = ts.edge_right[j];
+    int code = 0;
+    if (p == -1) {
+        code = -300;
+    } else if (p < 0 || (uint64_t) p >= ts.num_nodes) {
+        code = -202;
+    } else if (c == -1) {
+        code = -301;
+    } else if (c < 0 || (uint64_t) c >= ts.num_nodes) {
+        code = -202;
+    } else if (!(isfinite(l) && isfinite(r))) {
+        code = -211;
+    } else if (l < 0) {
+        code = -310;
+    } else if (r > ts.sequence_length) {
+        code = -309;
+    } else if (l >= r) {
+        code = -307;
+    } else if (ts.node_time[c] >= ts.node_time[p]) {
+        code = -306;
+    }
+    if (code != 0) {
+        report_bad(first_bad, 1, j, code);
+    }
+}
+
+__global__ void validate_sites_kernel(
+    uint64_t n, const double *pos, double L, unsigned long long *first_bad, uint32_t *fractional)
+{
+    const uint64_t j = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) {
+        return;
+    }
+    if (!isfinite(pos[j]) || pos[j] < 0 || pos[j] >= L) {
+        report_bad(first_bad, 2, j, -402);
+    } else if (pos[j] != floor(pos[j]) || pos[j] >= 4294967296.0) {
+        atomicAdd(fractional, 1u);
+    }
+}
+
+__global__ void validate_mutations_kernel(uint64_t n, const int32_t *site, const int32_t *node, const double *time,
+    uint64_t num_sites, uint64_t num_nodes, const double *node_time, unsigned long long *first_bad)
+{
+    const uint64_t j = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) {
+        return;
+    }
+    int code = 0;
+    if (site[j] < 0 || (uint64_t) site[j] >= num_sites) {
+        code = -205;
+    } else if (node[j] < 0 || (uint64_t) node[j] >= num_nodes) {
+        code = -202;
+    } else if (time != nullptr) {
+        const double t = time[j];
+        if ((uint64_t) __double_as_longlong(t) != 0x7FF874736B697421ull) {
+            if (!isfinite(t)) {
+                code = -210;
+            } else if (t < node_time[node[j]]) {
+                code = -506;
+            }
+        }
+    }
+    if (code != 0) {
+        report_bad(first_bad, 3, j, code);
+    }
+}
+
+TreeSeqView make_ts_view(const mspb_ctx *ctx)
+{
+    TreeSeqView v;
+    v.num_nodes = ctx->N;
+    v.num_edges = ctx->E;
+    v.sequence_length = ctx->L;
+    v.node_time = ctx->node_time.p;
+    v.edge_left = ctx->edge_left.p;
+    v.edge_right = ctx->edge_right.p;
+    v.edge_parent = ctx->edge_parent.p;
+    v.edge_child = ctx->edge_child.p;
+    v.child_start = ctx->child_start.p;
+    v.ci_left = ctx->ci_left.p;
+    v.ci_right = ctx->ci_right.p;
+    v.ci_parent = ctx->ci_parent.p;
+    return v;
+}
+
+int ensure_sort_buffers(mspb_ctx *ctx, uint64_t n)
+{
+    const uint64_t tiles = rs_num_tiles(n > 0 ? n : 1);
+    TRY(ctx->keys0.ensure(n + 1));
+    TRY(ctx->keys1.ensure(n + 1));
+    TRY(ctx->vals0.ensure(n + 1));
+    TRY(ctx->vals1.ensure(n + 1));
+    TRY(ctx->tile_hist.ensure(RS_BINS * tiles));
+    TRY(ctx->rs_scan_tiles.ensure(scan_num_tiles(RS_BINS * tiles) + 1));
+    return 0;
+}
+
+RadixSortBuffers sort_buffers(mspb_ctx *ctx)
+{
+    RadixSortBuffers b;
+    b.keys[0] = ctx->keys0.p;
+    b.keys[1] = ctx->keys1.p;
+    b.vals[0] = ctx->vals0.p;
+    b.vals[1] = ctx->vals1.p;
+    b.tile_hist = ctx->tile_hist.p;
+    b.scan_tiles = ctx->rs_scan_tiles.p;
+    b.or_and = ctx->or_and.p;
+    b.or_and_host = ctx->or_and_host;
+    return b;
+}
+
+} // namespace
+
+extern "C" int mspb_ctx_load_tables(mspb_ctx_t *ctx, const mspb_tables_t *t)
+{
+    if (ctx == nullptr || t == nullptr) {
+        return MSPB_ERR_BAD_PARAM_VALUE;
+    }
+    CUDA_OK(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    ctx->tables_loaded = false;
+    ctx->generated = false;
+    if (!std::isfinite(t->sequence_length) || t->sequence_length <= 0) {
+        /* mutgen_alloc rejects L <= 0 before anything else (lib/mutgen.c:760) */
+        return MSPB_ERR_BAD_PARAM_VALUE;
+    }
+    if (t->num_nodes > 0x7fffffffull || t->num_edges > 0x7fffffffull || t->num_sites > 0x7fffffffull
+        || t->num_mutations > 0x7fffffffull) {
+        return MSPB_ERR_TOO_MANY_ROWS;
+    }
+    ctx->L = t->sequence_length;
+    ctx->N = t->num_nodes;
+    ctx->E = t->num_edges;
+    ctx->S0 = t->num_sites;
+    ctx->M0 = t->num_mutations;
+    TRY(upload(ctx->node_time, t->node_time, ctx->N, st));
+    TRY(upload(ctx->edge_left, t->edge_left, ctx->E, st));
+    TRY(upload(ctx->edge_right, t->edge_right, ctx->E, st));
+    TRY(upload(ctx->edge_parent, t->edge_parent, ctx->E, st));
+    TRY(upload(ctx->edge_child, t->edge_child, ctx->E, st));
+    static const uint64_t zero_off[1] = { 0 };
+    if (ctx->S0 > 0) {
+        const uint64_t *ao = t->site_ancestral_state_offset, *mo = t->site_metadata_offset;
+        TRY(upload(ctx->k_site_pos, t->site_position, ctx->S0, st));
+        TRY(upload(ctx->k_site_anc_off, ao, ctx->S0 + 1, st));
+        TRY(upload(ctx->k_site_anc, t->site_ancestral_state, (size_t) ao[ctx->S0], st));
+        if (mo != nullptr) {
+            TRY(upload(ctx->k_site_md_off, mo, ctx->S0 + 1, st));
+            TRY(upload(ctx->k_site_md, t->site_metadata, (size_t) mo[ctx->S0], st));
+        } else {
+            TRY(ctx->k_site_md_off.ensure(ctx->S0 + 1));
+            CUDA_OK(cudaMemsetAsync(ctx->k_site_md_off.p, 0, (ctx->S0 + 1) * sizeof(uint64_t), st));
+            TRY(ctx->k_site_md.ensure(1));
+        }
+    }
+    if (ctx->M0 > 0) {
+        const uint64_t *dof = t->mutation_derived_state_offset, *mo = t->mutation_metadata_offset;
+        TRY(upload(ctx->k_mut_site, t->mutation_site, ctx->M0, st));
+        TRY(upload(ctx->k_mut_node, t->mutation_node, ctx->M0, st));
+        ctx->have_mut_time = t->mutation_time != nullptr;
+        if (ctx->have_mut_time) {
+            TRY(upload(ctx->k_mut_time, t->mutation_time, ctx->M0, st));
+        }
+        TRY(upload(ctx->k_mut_der_off, dof, ctx->M0 + 1, st));
+        TRY(upload(ctx->k_mut_der, t->mutation_derived_state, (size_t) dof[ctx->M0], st));
+        if (mo != nullptr) {
+            TRY(upload(ctx->k_mut_md_off, mo, ctx->M0 + 1, st));
+            TRY(upload(ctx->k_mut_md, t->mutation_metadata, (size_t) mo[ctx->M0], st));
+        } else {
+            TRY(ctx->k_mut_md_off.ensure(ctx->M0 + 1));
+            CUDA_OK(cudaMemsetAsync(ctx->k_mut_md_off.p, 0, (ctx->M0 + 1) * sizeof(uint64_t), st));
+            TRY(ctx->k_mut_md.ensure(1));
+        }
+    }
+    (void) zero_off;
+    TRY(ctx->child_start.ensure(ctx->N + 2));
+    TRY(ctx->ci_left.ensure(ctx->E + 1));
+    TRY(ctx->ci_right.ensure(ctx->E + 1));
+    TRY(ctx->ci_parent.ensure(ctx->E + 1));
+
+    // validation
+    HostTotals *dt = (HostTotals *) ctx->dev_totals.p;
+    CUDA_OK(cudaMemsetAsync(&dt->first_bad, 0xff, sizeof(unsigned long long), st));
+    CUDA_OK(cudaMemsetAsync(&dt->fractional_sites, 0, sizeof(uint32_t), st));
+    TreeSeqView ts = make_ts_view(ctx);
+    if (ctx->N > 0) {
+        validate_nodes_kernel<<<grid_for(ctx->N, 256), 256, 0, st>>>(ctx->N, ctx->node_time.p, &dt->first_bad);
+        ctx->launches++;
+    }
+    if (ctx->E > 0) {
+        validate_edges_kernel<<<grid_for(ctx->E, 256), 256, 0, st>>>(ts, &dt->first_bad);
+        ctx->launches++;
+    }
+    if (ctx->S0 > 0) {
+        validate_sites_kernel<<<grid_for(ctx->S0, 256), 256, 0, st>>>(
+            ctx->S0, ctx->k_site_pos.p, ctx->L, &dt->first_bad, &dt->fractional_sites);
+        ctx->launches++;
+    }
+    if (ctx->M0 > 0) {
+        validate_mutations_kernel<<<grid_for(ctx->M0, 256), 256, 0, st>>>(ctx->M0, ctx->k_mut_site.p, ctx->k_mut_node.p,
+            ctx->have_mut_time ? ctx->k_mut_time.p : nullptr, ctx->S0, ctx->N, ctx->node_time.p, &dt->first_bad);
+        ctx->launches++;
+    }
+    CUDA_OK(cudaMemcpyAsync(&ctx->host->first_bad, &dt->first_bad, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+    CUDA_OK(cudaMemcpyAsync(
+        &ctx->host->fractional_sites, &dt->fractional_sites, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    CUDA_OK(cudaStreamSynchronize(st));
+    ctx->kept_fractional = ctx->host->fractional_sites > 0;
+    if (ctx->host->first_bad != ~0ull) {
+        const int code = -(int) (ctx->host->first_bad & 0xffffull);
+        return TSK_E(code);
+    }
+
+    // K0: child-sorted interval index = stable sort by left, then by child
+    if (ctx->E == 0) {
+        CUDA_OK(cudaMemsetAsync(ctx->child_start.p, 0, (ctx->N + 2) * sizeof(uint32_t), st));
+    } else {
+        TRY(ensure_sort_buffers(ctx, ctx->E));
+        RadixSortBuffers sb = sort_buffers(ctx);
+        k0_child_keys_kernel<<<grid_for(ctx->E, 256), 256, 0, st>>>(ts, sb.keys[0], sb.vals[0]);
+        ctx->launches++;
+        int cur = device_radix_sort(sb, ctx->E, st, &ctx->launches, nullptr);
+        if (cur != 0) {
+            std::swap(sb.keys[0], sb.keys[1]);
+            std::swap(sb.vals[0], sb.vals[1]);
+        }
+        k0_child_keys2_kernel<<<grid_for(ctx->E, 256), 256, 0, st>>>(ts, sb.vals[0], sb.keys[0]);
+        ctx->launches++;
+        cur = device_radix_sort(sb, ctx->E, st, &ctx->launches, nullptr);
+        k0_permute_kernel<<<grid_for(ctx->E, 256), 256, 0, st>>>(
+            ts, sb.vals[cur], ctx->ci_left.p, ctx->ci_right.p, ctx->ci_parent.p, ctx->child_start.p);
+        ctx->launches++;
+    }
+    CUDA_OK(cudaStreamSynchronize(st));
+    CUDA_OK(cudaGetLastError());
+    ctx->tables_loaded = true;
+    return 0;
+}
+
+// ---------------------------------------------------------------- generate
+namespace {
+
+// Knuth's relative comparison, as the reference's doubles_almost_equal uses it
+// (lib/util.c:372-376 via gsl_fcmp).
+bool almost_equal(double a, double b, double eps)
+{
+    if (std::fabs(a) < eps && std::fabs(b) < eps) {
+        return true;
+    }
+    int exponent;
+    const double mx = (std::fabs(a) > std::fabs(b)) ? a : b;
+    std::frexp(mx, &exponent);
+    const double delta = std::ldexp(eps, exponent);
+    const double diff = a - b;
+    return !(diff > delta) && !(diff < -delta);
+}
+
+bool valid_probabilities(uint64_t n, const double *p)
+{
+    double sum = 0, lo = 0;
+    for (uint64_t j = 0; j < n; j++) {
+        sum += p[j];
+        lo = p[j] < lo ? p[j] : lo;
+    }
+    return almost_equal(sum, 1.0, 1e-12) && lo >= 0.0;
+}
+
+// lib/mutgen.c:501-524
+int check_model(const mspb_params_t *p)
+{
+    if (p->model_kind == MSPB_MODEL_INFINITE_ALLELES) {
+        return 0;
+    }
+    if (p->model_kind != MSPB_MODEL_MATRIX) {
+        return MSPB_ERR_BAD_PARAM_VALUE;
+    }
+    if (p->num_alleles < 2) {
+        return MSPB_ERR_INSUFFICIENT_ALLELES;
+    }
+    if (p->alleles == nullptr || p->allele_offset == nullptr || p->root_distribution == nullptr
+        || p->transition_matrix == nullptr) {
+        return MSPB_ERR_BAD_PARAM_VALUE;
+    }
+    if (!valid_probabilities(p->num_alleles, p->root_distribution)) {
+        return MSPB_ERR_BAD_ROOT_PROBABILITIES;
+    }
+    for (uint64_t i = 0; i < p->num_alleles; i++) {
+        if (!valid_probabilities(p->num_alleles, p->transition_matrix + i * p->num_alleles)) {
+            return MSPB_ERR_BAD_TRANSITION_MATRIX;
+        }
+    }
+    return 0;
+}
+
+// lib/rate_map.c:45-100 and lib/mutgen.c:796-813
+int check_rate_map(const mspb_params_t *p, double L)
+{
+    if (p->map_size < 1 || p->map_position == nullptr || p->map_rate == nullptr) {
+        return MSPB_ERR_INSUFFICIENT_INTERVALS;
+    }
+    if (p->map_position[0] != 0.0) {
+        return MSPB_ERR_INTERVAL_MAP_START_NON_ZERO;
+    }
+    for (uint64_t j = 0; j <= p->map_size; j++) {
+        if (!std::isfinite(p->map_position[j])) {
+            return MSPB_ERR_NONFINITE_INTERVAL_POSITION;
+        }
+        if (j < p->map_size) {
+            if (p->map_position[j] >= p->map_position[j + 1]) {
+                return MSPB_ERR_INTERVAL_POSITIONS_UNSORTED;
+            }
+            if (!std::isfinite(p->map_rate[j]) || p->map_rate[j] < 0) {
+                return MSPB_ERR_BAD_RATE_VALUE;
+            }
+        }
+    }
+    if (p->map_position[p->map_size] != L) {
+        return MSPB_ERR_INCOMPATIBLE_MUTATION_MAP_LENGTH;
+    }
+    return 0;
+}
+
+int upload_params(mspb_ctx *ctx, const mspb_params_t *p, RateMapView *map, ModelView *model)
+{
+    cudaStream_t st = ctx->stream;
+    const uint64_t R = p->map_size;
+    const bool discrete = p->discrete_genome != 0;
+    std::vector<double> rate(R + 1), cum(R + 1);
+    double sum = 0;
+    for (uint64_t j = 0; j <= R; j++) {
+        cum[j] = sum;
+        rate[j] = j < R ? p->map_rate[j] : 0.0;
+        if (j < R) {
+            const double a = discrete ? std::ceil(p->map_position[j]) : p->map_position[j];
+            const double b = discrete ? std::ceil(p->map_position[j + 1]) : p->map_position[j + 1];
+            sum += (b - a) * rate[j];
+        }
+    }
+    TRY(upload(ctx->map_pos, p->map_position, R + 1, st));
+    TRY(upload(ctx->map_rate, rate.data(), R + 1, st));
+    TRY(upload(ctx->map_cum, cum.data(), R + 1, st));
+    // the vectors must outlive the async copies
+    CUDA_OK(cudaStreamSynchronize(st));
+    map->pos = ctx->map_pos.p;
+    map->rate = ctx->map_rate.p;
+    map->cum = ctx->map_cum.p;
+    map->size = (uint32_t) R;
+    map->discrete = discrete ? 1 : 0;
+
+    model->kind = p->model_kind;
+    model->start_allele = p->start_allele;
+    model->num_alleles = 0;
+    model->alleles = nullptr;
+    model->allele_off = nullptr;
+    model->root = nullptr;
+    model->matrix = nullptr;
+    if (p->model_kind == MSPB_MODEL_MATRIX) {
+        const uint64_t A = p->num_alleles;
+        TRY(upload(ctx->model_alleles, p->alleles, (size_t) p->allele_offset[A], st));
+        TRY(upload(ctx->model_allele_off, p->allele_offset, A + 1, st));
+        TRY(upload(ctx->model_root, p->root_distribution, A, st));
+        TRY(upload(ctx->model_matrix, p->transition_matrix, A * A, st));
+        model->num_alleles = (uint32_t) A;
+        model->alleles = ctx->model_alleles.p;
+        model->allele_off = ctx->model_allele_off.p;
+        model->root = ctx->model_root.p;
+        model->matrix = ctx->model_matrix.p;
+    }
+    return 0;
+}
+
+KeptView make_kept_view(const mspb_ctx *ctx, bool keep)
+{
+    KeptView k;
+    memset(&k, 0, sizeof(k));
+    if (!keep) {
+        return k;
+    }
+    k.num_sites = ctx->S0;
+    k.num_mutations = ctx->M0;
+    k.site_position = ctx->k_site_pos.p;
+    k.site_anc_off = ctx->k_site_anc_off.p;
+    k.site_md_off = ctx->k_site_md_off.p;
+    k.site_anc = ctx->k_site_anc.p;
+    k.site_md = ctx->k_site_md.p;
+    k.mut_site = ctx->k_mut_site.p;
+    k.mut_node = ctx->k_mut_node.p;
+    k.mut_time = ctx->have_mut_time ? ctx->k_mut_time.p : nullptr;
+    k.mut_der_off = ctx->k_mut_der_off.p;
+    k.mut_md_off = ctx->k_mut_md_off.p;
+    k.mut_der = ctx->k_mut_der.p;
+    k.mut_md = ctx->k_mut_md.p;
+    k.site_allele = ctx->k_site_allele.p;
+    k.mut_allele = ctx->k_mut_allele.p;
+    return k;
+}
+
+__global__ void write_final_offsets_kernel(OutView out, uint64_t S, uint64_t M, uint64_t anc, uint64_t smd, uint64_t der,
+    uint64_t mmd)
+{
+    out.site_anc_off[S] = anc;
+    out.site_md_off[S] = smd;
+    out.mut_der_off[M] = der;
+    out.mut_md_off[M] = mmd;
+}
+
+} // namespace
+
+extern "C" int mspb_generate(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t *counts_out)
+{
+    if (ctx == nullptr || p == nullptr) {
+        return MSPB_ERR_BAD_PARAM_VALUE;
+    }
+    if (!ctx->tables_loaded) {
+        return MSPB_ERR_TABLES_NOT_LOADED;
+    }
+    CUDA_OK(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    ctx->generated = false;
+    // same order of checks as the reference call sequence: model, rate map, time window
+    TRY(check_model(p));
+    TRY(check_rate_map(p, ctx->L));
+    if (p->end_time < p->start_time) {
+        return MSPB_ERR_BAD_PARAM_VALUE; /* lib/mutgen.c:786 */
+    }
+    const bool replay = p->replay_stream != nullptr;
+    const bool sliced = !(p->slice_left == 0.0 && (p->slice_right == 0.0 || p->slice_right >= ctx->L));
+    if (sliced && (replay || !(p->slice_left < p->slice_right) || p->slice_left < 0)) {
+        return MSPB_ERR_BAD_PARAM_VALUE;
+    }
+    const bool keep = p->keep != 0;
+    const bool discrete = p->discrete_genome != 0;
+    const uint64_t S0 = keep ? ctx->S0 : 0, M0 = keep ? ctx->M0 : 0;
+    HostTotals *dt = (HostTotals *) ctx->dev_totals.p;
+    HostTotals *ht = ctx->host;
+
+    CUDA_OK(cudaEventRecord(ctx->ev[0], st));
+    RateMapView map;
+    ModelView model;
+    TRY(upload_params(ctx, p, &map, &model));
+    CUDA_OK(cudaMemsetAsync(dt, 0, sizeof(HostTotals), st));
+    TreeSeqView ts = make_ts_view(ctx);
+    CallView call;
+    call.start_time = p->start_time;
+    call.end_time = p->end_time;
+    call.slice_left = p->slice_left;
+    call.slice_right = sliced ? p->slice_right : ctx->L;
+    call.discrete = discrete ? 1 : 0;
+    call.sliced = sliced ? 1 : 0;
+    call.seed = p->seed;
+    call.pos_shift = (discrete && ctx->L <= 4294967296.0 && !(keep && ctx->kept_fractional)) ? 32 : -1;
+    if (keep && p->model_kind == MSPB_MODEL_MATRIX) {
+        TRY(ctx->k_site_allele.ensure(S0 + 1));
+        TRY(ctx->k_mut_allele.ensure(M0 + 1));
+        if (S0 > 0) {
+            kept_allele_index_kernel<<<grid_for(S0, 256), 256, 0, st>>>(
+                model, S0, ctx->k_site_anc.p, ctx->k_site_anc_off.p, ctx->k_site_allele.p);
+            ctx->launches++;
+        }
+        if (M0 > 0) {
+            kept_allele_index_kernel<<<grid_for(M0, 256), 256, 0, st>>>(
+                model, M0, ctx->k_mut_der.p, ctx->k_mut_der_off.p, ctx->k_mut_allele.p);
+            ctx->launches++;
+        }
+    }
+    KeptView kept = make_kept_view(ctx, keep);
+
+    // ---- K1: how many new mutations, and where they go
+    CUDA_OK(cudaEventRecord(ctx->ev[1], st));
+    uint64_t Mnew = 0, num_pairs = 0;
+    ReplayPairs pairs;
+    memset(&pairs, 0, sizeof(pairs));
+    if (!replay) {
+        TRY(ctx->count.ensure(ctx->E + 1));
+        TRY(ctx->goff.ensure(ctx->E + 1));
+        TRY(ctx->scan_tiles32.ensure(scan_num_tiles(ctx->E + 1) + 1));
+        if (sliced) {
+            TRY(ctx->local.ensure(ctx->E + 1));
+            TRY(ctx->loff.ensure(ctx->E + 1));
+        }
+        if (ctx->E > 0) {
+            k1_count_kernel<<<grid_for(ctx->E, 256), 256, 0, st>>>(ts, map, call, ctx->count.p, ctx->local.p);
+            ctx->launches++;
+            const uint32_t *c = ctx->count.p;
+            ctx->launches += device_exclusive_scan<uint32_t>(
+                ctx->E, [c] __device__(uint64_t i) { return c[i]; }, ctx->goff.p, ctx->scan_tiles32.p,
+                &dt->count_total, st);
+            if (sliced) {
+                const uint32_t *l = ctx->local.p;
+                ctx->launches += device_exclusive_scan<uint32_t>(
+                    ctx->E, [l] __device__(uint64_t i) { return l[i]; }, ctx->loff.p, ctx->scan_tiles32.p,
+                    &dt->local_total, st);
+            }
+        }
+        CUDA_OK(cudaMemcpyAsync(ht, dt, sizeof(HostTotals), cudaMemcpyDeviceToHost, st));
+        CUDA_OK(cudaStreamSynchronize(st));
+        Mnew = sliced ? ht->local_total : ht->count_total;
+    } else {
+        const uint64_t cap = p->replay_len / 2 + 1;
+        TRY(upload(ctx->replay, p->replay_stream, p->replay_len, st));
+        TRY(ctx->rp_edge.ensure(cap));
+        TRY(ctx->rp_interval.ensure(cap));
+        TRY(ctx->rp_count.ensure(cap));
+        TRY(ctx->rp_out_off.ensure(cap));
+        TRY(ctx->rp_stream_off.ensure(cap));
+        pairs.edge = ctx->rp_edge.p;
+        pairs.interval = ctx->rp_interval.p;
+        pairs.count = ctx->rp_count.p;
+        pairs.out_off = ctx->rp_out_off.p;
+        pairs.stream_off = ctx->rp_stream_off.p;
+        pairs.capacity = cap;
+        replay_resolve_kernel<<<1, 32, 0, st>>>(ts, map, call, ctx->replay.p, p->replay_len, pairs, &dt->replay, &dt->err);
+        ctx->launches++;
+        CUDA_OK(cudaMemcpyAsync(ht, dt, sizeof(HostTotals), cudaMemcpyDeviceToHost, st));
+        CUDA_OK(cudaStreamSynchronize(st));
+        if (ht->err != 0) {
+            return ht->err;
+        }
+        if (ht->replay.exhausted) {
+            return MSPB_ERR_REPLAY_STREAM_EXHAUSTED;
+        }
+        Mnew = ht->replay.num_mutations;
+        num_pairs = ht->replay.num_pairs;
+    }
+    const uint64_t R = S0 + M0 + Mnew;
+    if (R > 0x7fffffffull) {
+        return MSPB_ERR_TOO_MANY_ROWS;
+    }
+
+    // ---- K2: records (kept markers, kept mutations, new mutations) and their sort keys
+    CUDA_OK(cudaEventRecord(ctx->ev[2], st));
+    TRY(ctx->rec_pos.ensure(R + 1));
+    TRY(ctx->rec_time.ensure(R + 1));
+    TRY(ctx->rec_node.ensure(R + 1));
+    TRY(ctx->rec_ord.ensure(Mnew + 1));
+    TRY(ensure_sort_buffers(ctx, R));
+    RadixSortBuffers sb = sort_buffers(ctx);
+    if (S0 + M0 > 0) {
+        fill_kept_kernel<<<grid_for(S0 + M0, 256), 256, 0, st>>>(
+            kept, call, ctx->rec_pos.p, ctx->rec_time.p, ctx->rec_node.p, sb.keys[0], sb.vals[0], &dt->err);
+        ctx->launches++;
+    }
+    if (Mnew > 0) {
+        if (!replay) {
+            k2_place_kernel<<<grid_for(ctx->E, 256), 256, 0, st>>>(ts, map, call, ctx->count.p, ctx->goff.p,
+                sliced ? ctx->loff.p : ctx->goff.p, (uint32_t) (S0 + M0), ctx->rec_pos.p, ctx->rec_time.p,
+                ctx->rec_node.p, ctx->rec_ord.p, sb.keys[0], sb.vals[0]);
+        } else {
+            replay_place_kernel<<<grid_for(num_pairs, 128), 128, 0, st>>>(ts, map, call, ctx->replay.p, pairs, num_pairs,
+                (uint32_t) (S0 + M0), ctx->rec_pos.p, ctx->rec_time.p, ctx->rec_node.p, ctx->rec_ord.p, sb.keys[0],
+                sb.vals[0], &dt->err);
+        }
+        ctx->launches++;
+    }
+
+    // ---- K3: order all records by (position, time descending)
+    CUDA_OK(cudaEventRecord(ctx->ev[3], st));
+    int sort_passes = 0;
+    const int cur = device_radix_sort(sb, R, st, &ctx->launches, &sort_passes);
+
+    // ---- exact order inside equal-key runs, site boundaries, row numbers
+    CUDA_OK(cudaEventRecord(ctx->ev[4], st));
+    SortedView sv;
+    sv.n = R;
+    sv.S0 = S0;
+    sv.M0 = M0;
+    sv.key = sb.keys[cur];
+    sv.val = sb.vals[cur];
+    sv.rec_pos = ctx->rec_pos.p;
+    sv.rec_time = ctx->rec_time.p;
+    sv.rec_node = ctx->rec_node.p;
+    sv.rec_ord = ctx->rec_ord.p;
+    sv.pos_mask = call.pos_shift >= 0 ? 0xffffffff00000000ull : ~0ull;
+    TRY(ctx->site_scan.ensure(R + 1));
+    TRY(ctx->mut_scan.ensure(R + 1));
+    TRY(ctx->draw_scan.ensure(R + 1));
+    TRY(ctx->parent.ensure(R + 1));
+    TRY(ctx->state.ensure(R + 1));
+    TRY(ctx->site_state.ensure(R + 1));
+    TRY(ctx->scan_tiles32.ensure(scan_num_tiles(R + 1) + 1));
+    TRY(ctx->scan_tiles64.ensure(scan_num_tiles(R + 1) + 1));
+    TRY(ctx->der_scan.ensure(R + 1));
+    TRY(ctx->mmd_scan.ensure(R + 1));
+    TRY(ctx->anc_scan.ensure(R + 1));
+    TRY(ctx->smd_scan.ensure(R + 1));
+    ResolveView rv;
+    rv.site_scan = ctx->site_scan.p;
+    rv.mut_scan = ctx->mut_scan.p;
+    rv.draw_scan = ctx->draw_scan.p;
+    rv.parent = ctx->parent.p;
+    rv.state = ctx->state.p;
+    rv.site_state = ctx->site_state.p;
+    rv.replay = nullptr;
+    rv.replay_len = 0;
+    if (replay) {
+        const uint64_t used = ht->replay.draws;
+        rv.replay = ctx->replay.p + used;
+        rv.replay_len = p->replay_len - used;
+    }
+    EmitView evw;
+    evw.sv = sv;
+    evw.rv = rv;
+    evw.kept = kept;
+    evw.model = model;
+    if (R > 0) {
+        if (R > 1) {
+            finalize_runs_kernel<<<grid_for(R, 256), 256, 0, st>>>(sv);
+            post_sort_check_kernel<<<grid_for(R, 256), 256, 0, st>>>(sv, call.discrete, &dt->collisions, &dt->err);
+            ctx->launches += 2;
+        }
+        ctx->launches += device_exclusive_scan<uint32_t>(
+            R, [evw] __device__(uint64_t i) { return evw.head(i) ? 1u : 0u; }, ctx->site_scan.p, ctx->scan_tiles32.p,
+            &dt->num_sites, st);
+        ctx->launches += device_exclusive_scan<uint32_t>(
+            R, [evw] __device__(uint64_t i) { return evw.is_mut(i) ? 1u : 0u; }, ctx->mut_scan.p, ctx->scan_tiles32.p,
+            &dt->num_mut_rows, st);
+        ctx->launches += device_exclusive_scan<uint32_t>(
+            R, [evw] __device__(uint64_t i) { return (evw.is_new(i) ? 1u : 0u) + (evw.new_site(i) ? 1u : 0u); },
+            ctx->draw_scan.p, ctx->scan_tiles32.p, &dt->num_draws, st);
+    }
+
+    // ---- K4: parents and alleles, one site at a time
+    CUDA_OK(cudaEventRecord(ctx->ev[5], st));
+    if (R > 0) {
+        k4_resolve_kernel<<<grid_for(R, 128), 128, 0, st>>>(ts, kept, model, call, sv, rv, &dt->err);
+        ctx->launches++;
+    }
+
+    // ---- ragged column offsets
+    CUDA_OK(cudaEventRecord(ctx->ev[6], st));
+    if (R > 0) {
+        ctx->launches += device_exclusive_scan<uint64_t>(
+            R, [evw] __device__(uint64_t i) { return evw.der_len(i); }, ctx->der_scan.p, ctx->scan_tiles64.p,
+            &dt->der_bytes, st);
+        ctx->launches += device_exclusive_scan<uint64_t>(
+            R, [evw] __device__(uint64_t i) { return evw.mut_md_len(i); }, ctx->mmd_scan.p, ctx->scan_tiles64.p,
+            &dt->mmd_bytes, st);
+        ctx->launches += device_exclusive_scan<uint64_t>(
+            R, [evw] __device__(uint64_t i) { return evw.anc_len(i); }, ctx->anc_scan.p, ctx->scan_tiles64.p,
+            &dt->anc_bytes, st);
+        ctx->launches += device_exclusive_scan<uint64_t>(
+            R, [evw] __device__(uint64_t i) { return evw.site_md_len(i); }, ctx->smd_scan.p, ctx->scan_tiles64.p,
+            &dt->smd_bytes, st);
+    }
+    CUDA_OK(cudaMemcpyAsync(ht, dt, sizeof(HostTotals), cudaMemcpyDeviceToHost, st));
+    CUDA_OK(cudaStreamSynchronize(st));
+    CUDA_OK(cudaGetLastError());
+    if (ht->err != 0) {
+        return ht->err;
+    }
+    if (ht->collisions > 0) {
+        return MSPB_ERR_REPLAY_REDRAW;
+    }
+    if (replay && p->model_kind == MSPB_MODEL_MATRIX && ht->replay.draws + ht->num_draws > p->replay_len) {
+        return MSPB_ERR_REPLAY_STREAM_EXHAUSTED;
+    }
+    const uint64_t S = ht->num_sites, M = ht->num_mut_rows;
+
+    // ---- K5: write the site and mutation tables
+    CUDA_OK(cudaEventRecord(ctx->ev[7], st));
+    TRY(ctx->o_site_pos.ensure(S + 1));
+    TRY(ctx->o_site_anc.ensure(ht->anc_bytes + 1));
+    TRY(ctx->o_site_anc_off.ensure(S + 2));
+    TRY(ctx->o_site_md.ensure(ht->smd_bytes + 1));
+    TRY(ctx->o_site_md_off.ensure(S + 2));
+    TRY(ctx->o_mut_site.ensure(M + 1));
+    TRY(ctx->o_mut_node.ensure(M + 1));
+    TRY(ctx->o_mut_parent.ensure(M + 1));
+    TRY(ctx->o_mut_time.ensure(M + 1));
+    TRY(ctx->o_mut_der.ensure(ht->der_bytes + 1));
+    TRY(ctx->o_mut_der_off.ensure(M + 2));
+    TRY(ctx->o_mut_md.ensure(ht->mmd_bytes + 1));
+    TRY(ctx->o_mut_md_off.ensure(M + 2));
+    OutView out;
+    out.site_position = ctx->o_site_pos.p;
+    out.site_anc = ctx->o_site_anc.p;
+    out.site_anc_off = ctx->o_site_anc_off.p;
+    out.site_md = ctx->o_site_md.p;
+    out.site_md_off = ctx->o_site_md_off.p;
+    out.mut_site = ctx->o_mut_site.p;
+    out.mut_node = ctx->o_mut_node.p;
+    out.mut_parent = ctx->o_mut_parent.p;
+    out.mut_time = ctx->o_mut_time.p;
+    out.mut_der = ctx->o_mut_der.p;
+    out.mut_der_off = ctx->o_mut_der_off.p;
+    out.mut_md = ctx->o_mut_md.p;
+    out.mut_md_off = ctx->o_mut_md_off.p;
+    if (R > 0) {
+        k5_emit_kernel<<<grid_for(R, 256), 256, 0, st>>>(
+            evw, out, ctx->der_scan.p, ctx->mmd_scan.p, ctx->anc_scan.p, ctx->smd_scan.p);
+        ctx->launches++;
+    }
+    write_final_offsets_kernel<<<1, 1, 0, st>>>(out, S, M, ht->anc_bytes, ht->smd_bytes, ht->der_bytes, ht->mmd_bytes);
+    ctx->launches++;
+    CUDA_OK(cudaEventRecord(ctx->ev[8], st));
+    CUDA_OK(cudaStreamSynchronize(st));
+    CUDA_OK(cudaGetLastError());
+    float total = 0;
+    for (int i = 0; i < MSPB_NUM_PHASES; i++) {
+        cudaEventElapsedTime(&ctx->phase_ms[i], ctx->ev[i], ctx->ev[i + 1]);
+    }
+    cudaEventElapsedTime(&total, ctx->ev[0], ctx->ev[8]);
+    mspb_counts_t &c = ctx->counts;
+    memset(&c, 0, sizeof(c));
+    c.num_sites = S;
+    c.num_mutations = M;
+    c.num_new_mutations = Mnew;
+    c.ancestral_state_bytes = ht->anc_bytes;
+    c.site_metadata_bytes = ht->smd_bytes;
+    c.derived_state_bytes = ht->der_bytes;
+    c.mutation_metadata_bytes = ht->mmd_bytes;
+    c.num_new_sites = S - S0;
+    c.next_allele = p->start_allele + (p->model_kind == MSPB_MODEL_INFINITE_ALLELES ? (uint64_t) ht->num_draws : 0);
+    c.draws = replay ? ht->replay.draws + (p->model_kind == MSPB_MODEL_MATRIX ? ht->num_draws : 0) : 0;
+    c.device_ms = total;
+    (void) sort_passes;
+    ctx->generated = true;
+    if (counts_out != nullptr) {
+        *counts_out = c;
+    }
+    return 0;
+}
+
+extern "C" int mspb_device_columns(mspb_ctx_t *ctx, mspb_columns_t *d)
+{
+    if (ctx == nullptr || d == nullptr) {
+        return MSPB_ERR_BAD_PARAM_VALUE;
+    }
+    if (!ctx->generated) {
+        return MSPB_ERR_NOT_GENERATED;
+    }
+    d->site_position = ctx->o_site_pos.p;
+    d->site_ancestral_state = ctx->o_site_anc.p;
+    d->site_ancestral_state_offset = ctx->o_site_anc_off.p;
+    d->site_metadata = ctx->o_site_md.p;
+    d->site_metadata_offset = ctx->o_site_md_off.p;
+    d->mutation_site = ctx->o_mut_site.p;
+    d->mutation_node = ctx->o_mut_node.p;
+    d->mutation_parent = ctx->o_mut_parent.p;
+    d->mutation_time = ctx->o_mut_time.p;
+    d->mutation_derived_state = ctx->o_mut_der.p;
+    d->mutation_derived_state_offset = ctx->o_mut_der_off.p;
+    d->mutation_metadata = ctx->o_mut_md.p;
+    d->mutation_metadata_offset = ctx->o_mut_md_off.p;
+    return 0;
+}
+
+extern "C" int mspb_fetch(mspb_ctx_t *ctx, const mspb_columns_t *h)
+{
+    if (ctx == nullptr || h == nullptr) {
+        return MSPB_ERR_BAD_PARAM_VALUE;
+    }
+    if (!ctx->generated) {
+        return MSPB_ERR_NOT_GENERATED;
+    }
+    CUDA_OK(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    const mspb_counts_t &c = ctx->counts;
+    const uint64_t S = c.num_sites, M = c.num_mutations;
+#define D2H(dst, src, bytes)                                                                                           \
+    do {                                                                                                               \
+        if ((dst) != nullptr && (bytes) > 0) {                                                                         \
+            CUDA_OK(cudaMemcpyAsync((dst), (src), (bytes), cudaMemcpyDeviceToHost, st));                               \
+        }                                                                                                              \
+    } while (0)
+    D2H(h->site_position, ctx->o_site_pos.p, S * sizeof(double));
+    D2H(h->site_ancestral_state, ctx->o_site_anc.p, c.ancestral_state_bytes);
+    D2H(h->site_ancestral_state_offset, ctx->o_site_anc_off.p, (S + 1) * sizeof(uint64_t));
+    D2H(h->site_metadata, ctx->o_site_md.p, c.site_metadata_bytes);
+    D2H(h->site_metadata_offset, ctx->o_site_md_off.p, (S + 1) * sizeof(uint64_t));
+    D2H(h->mutation_site, ctx->o_mut_site.p, M * sizeof(int32_t));
+    D2H(h->mutation_node, ctx->o_mut_node.p, M * sizeof(int32_t));
+    D2H(h->mutation_parent, ctx->o_mut_parent.p, M * sizeof(int32_t));
+    D2H(h->mutation_time, ctx->o_mut_time.p, M * sizeof(double));
+    D2H(h->mutation_derived_state, ctx->o_mut_der.p, c.derived_state_bytes);
+    D2H(h->mutation_derived_state_offset, ctx->o_mut_der_off.p, (M + 1) * sizeof(uint64_t));
+    D2H(h->mutation_metadata, ctx->o_mut_md.p, c.mutation_metadata_bytes);
+    D2H(h->mutation_metadata_offset, ctx->o_mut_md_off.p, (M + 1) * sizeof(uint64_t));
+#undef D2H
+    CUDA_OK(cudaStreamSynchronize(st));
+    return 0;
+}
+
+extern "C" void mspb_columns_free(mspb_columns_t *c)
+{
+    if (c == nullptr) {
+        return;
+    }
+    free(c->site_position);
+    free(c->site_ancestral_state);
+    free(c->site_ancestral_state_offset);
+    free(c->site_metadata);
+    free(c->site_metadata_offset);
+    free(c->mutation_site);
+    free(c->mutation_node);
+    free(c->mutation_parent);
+    free(c->mutation_time);
+    free(c->mutation_derived_state);
+    free(c->mutation_derived_state_offset);
+    free(c->mutation_metadata);
+    free(c->mutation_metadata_offset);
+    memset(c, 0, sizeof(*c));
+}
+
+extern "C" int mspb_sim_mutations(int device, const mspb_tables_t *tables, const mspb_params_t *params,
+    mspb_counts_t *counts, mspb_columns_t *out)
+{
+    mspb_ctx_t *ctx = nullptr;
+    mspb_counts_t c;
+    if (tables == nullptr || params == nullptr || out == nullptr) {
+        return MSPB_ERR_BAD_PARAM_VALUE;
+    }
+    memset(out, 0, sizeof(*out));
+    int ret = mspb_ctx_create(device, &ctx);
+    if (ret != 0) {
+        return ret;
+    }
+    ret = mspb_ctx_load_tables(ctx, tables);
+    if (ret == 0) {
+        ret = mspb_generate(ctx, params, &c);
+    }
+    if (ret == 0) {
+        const uint64_t S = c.num_sites, M = c.num_mutations;
+        out->site_position = (double *) malloc((S + 1) * sizeof(double));
+        out->site_ancestral_state = (char *) malloc(c.ancestral_state_bytes + 1);
+        out->site_ancestral_state_offset = (uint64_t *) malloc((S + 1) * sizeof(uint64_t));
+        out->site_metadata = (char *) malloc(c.site_metadata_bytes + 1);
+        out->site_metadata_offset = (uint64_t *) malloc((S + 1) * sizeof(uint64_t));
+        out->mutation_site = (int32_t *) malloc((M + 1) * sizeof(int32_t));
+        out->mutation_node = (int32_t *) malloc((M + 1) * sizeof(int32_t));
+        out->mutation_parent = (int32_t *) malloc((M + 1) * sizeof(int32_t));
+        out->mutation_time = (double *) malloc((M + 1) * sizeof(double));
+        out->mutation_derived_state = (char *) malloc(c.derived_state_bytes + 1);
+        out->mutation_derived_state_offset = (uint64_t *) malloc((M + 1) * sizeof(uint64_t));
+        out->mutation_metadata = (char *) malloc(c.mutation_metadata_bytes + 1);
+        out->mutation_metadata_offset = (uint64_t *) malloc((M + 1) * sizeof(uint64_t));
+        if (!out->site_position || !out->site_ancestral_state || !out->site_ancestral_state_offset
+            || !out->site_metadata || !out->site_metadata_offset || !out->mutation_site || !out->mutation_node
+            || !out->mutation_parent || !out->mutation_time || !out->mutation_derived_state
+            || !out->mutation_derived_state_offset || !out->mutation_metadata || !out->mutation_metadata_offset) {
+            ret = MSPB_ERR_NO_MEMORY;
+        } else {
+            ret = mspb_fetch(ctx, out);
+        }
+        if (ret != 0) {
+            mspb_columns_free(out);
+        } else if (counts != nullptr) {
+            *counts = c;
+        }
+    }
+    mspb_ctx_destroy(ctx);
+    return ret;
+}

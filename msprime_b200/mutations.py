@@ -1,0 +1,427 @@
+"""``sim_mutations`` and the mutation models: the Python surface of the path.
+
+Re-authored drop-in for ``msprime/mutations.py``: same function signatures, argument
+meaning, defaults and error behaviour (``sim_mutations`` :1551-1702, ``mutate``
+:1423-1505, ``mutation_model_factory`` :1522-1548, model classes :78-201, 516-850),
+with the C call ``_msprime.sim_mutations`` (``_msprimemodule.c:3047``) replaced by the
+CUDA library behind ``include/msprime_b200.h``.
+"""
+from __future__ import annotations
+
+import inspect
+import math
+import sys
+
+import numpy as np
+
+from . import _native, core, intervals, provenance, tables as _tables
+from ._native import InputError, LibraryError  # noqa: F401  (re-exported)
+
+_ACGT_ALLELES = ["A", "C", "G", "T"]
+BINARY = 0
+NUCLEOTIDES = 1
+
+
+class MutationModel:
+    """Abstract superclass of the mutation models (``msprime/mutations.py:60-75``)."""
+
+    def asdict(self):
+        return {
+            key: getattr(self, key)
+            for key in inspect.signature(self.__init__).parameters.keys()
+            if hasattr(self, key)
+        }
+
+
+def _almost_equal(a, b, eps):
+    # doubles_almost_equal, lib/util.c:372-376 (Knuth's relative comparison)
+    if abs(a) < eps and abs(b) < eps:
+        return True
+    mx = a if abs(a) > abs(b) else b
+    _, exponent = math.frexp(mx)
+    delta = math.ldexp(eps, exponent)
+    return not (a - b > delta) and not (a - b < -delta)
+
+
+def _valid_probabilities(p):
+    total, low = 0.0, 0.0
+    for x in p:
+        total += float(x)
+        low = min(low, float(x))
+    return _almost_equal(total, 1.0, 1e-12) and low >= 0.0
+
+
+class MatrixMutationModel(MutationModel):
+    """Finite-state model: ``alleles``, ``root_distribution`` and a row-stochastic
+    ``transition_matrix``.  Validation follows ``matrix_mutation_model_alloc``
+    (``lib/mutgen.c:501-524``) and the argument parsing of
+    ``_msprimemodule.c:477-560`` (shape mismatches are ValueErrors)."""
+
+    def __init__(self, alleles, root_distribution, transition_matrix):
+        if isinstance(alleles, (str, bytes)):
+            raise TypeError("alleles must be a list of strings")
+        alleles = list(alleles)
+        for a in alleles:
+            if not isinstance(a, str):
+                raise TypeError("alleles must be unicode strings")
+        root = np.array(root_distribution, dtype=np.float64)
+        matrix = np.array(transition_matrix, dtype=np.float64)
+        n = len(alleles)
+        if root.ndim != 1 or root.shape[0] != n:
+            raise ValueError("root_distribution must have num_alleles elements")
+        if matrix.ndim != 2 or matrix.shape != (n, n):
+            raise ValueError("transition_matrix must be a square matrix with num_alleles rows")
+        if n < 2:
+            raise LibraryError(_native_message(-52), -52)
+        if not _valid_probabilities(root):
+            raise LibraryError(_native_message(-53), -53)
+        for row in matrix:
+            if not _valid_probabilities(row):
+                raise LibraryError(_native_message(-54), -54)
+        self._alleles = alleles
+        self._root_distribution = root
+        self._transition_matrix = matrix
+
+    alleles = property(lambda self: list(self._alleles))
+    root_distribution = property(lambda self: self._root_distribution.copy())
+    transition_matrix = property(lambda self: self._transition_matrix.copy())
+
+    def _native(self):
+        return {
+            "kind": _native.MODEL_MATRIX,
+            "alleles": self._alleles,
+            "root_distribution": self._root_distribution,
+            "transition_matrix": self._transition_matrix,
+        }
+
+    def __str__(self):
+        s = f"Mutation model with alleles {self.alleles}\n"
+        s += "  root distribution: {}\n".format(" ".join(map(str, self.root_distribution)))
+        s += "  transition matrix:\n"
+        for row in self.transition_matrix:
+            s += "     {}\n".format(" ".join(map(str, row)))
+        return s
+
+
+_MESSAGES = {
+    -52: "Must have at least two alleles.",
+    -53: "Root probabilities must be nonnegative and sum to one.",
+    -54: "Each row of the transition matrix must be nonnegative and sum to one.",
+}
+
+
+def _native_message(code):
+    return _MESSAGES[code]
+
+
+class InfiniteAlleles(MutationModel):
+    """Every new allele (ancestral or derived) is the next unused integer.  The counter
+    lives on the model object and persists across calls (``lib/mutgen.c:431-481``,
+    ``_msprimemodule.c:876-890``)."""
+
+    def __init__(self, start_allele=0):
+        start_allele = int(start_allele)
+        if start_allele < 0 or start_allele >= 2**64:
+            raise OverflowError("start_allele must fit an unsigned 64 bit integer")
+        self._start_allele = start_allele
+        self._next_allele = start_allele
+
+    start_allele = property(lambda self: self._start_allele)
+    next_allele = property(lambda self: self._next_allele)
+
+    def _native(self):
+        return {"kind": _native.MODEL_INFINITE_ALLELES, "start_allele": self._next_allele}
+
+    def __str__(self):
+        return (
+            f"Infinite alleles mutation model, beginning with allele"
+            f" {self.start_allele}\n    next allele: {self.next_allele}\n"
+        )
+
+
+class BinaryMutationModel(MatrixMutationModel):
+    """Alleles "0"/"1", ancestral state always "0" (``msprime/mutations.py:179-201``)."""
+
+    def __init__(self, state_independent=False):
+        if state_independent:
+            matrix = [[0.5, 0.5], [0.5, 0.5]]
+        else:
+            matrix = [[0.0, 1.0], [1.0, 0.0]]
+        self.state_independent = state_independent
+        super().__init__(["0", "1"], [1, 0], matrix)
+
+
+class JC69(MatrixMutationModel):
+    """Jukes-Cantor: all nucleotide changes equally likely (``msprime/mutations.py:516-547``)."""
+
+    def __init__(self, state_independent=False):
+        matrix = np.zeros((4, 4))
+        if state_independent:
+            matrix[:] = 1 / 4
+        else:
+            matrix[:] = 1 / 3
+            np.fill_diagonal(matrix, 0)
+        self.state_independent = state_independent
+        super().__init__(_ACGT_ALLELES, [0.25, 0.25, 0.25, 0.25], matrix)
+
+
+class HKY(MatrixMutationModel):
+    """Hasegawa-Kishino-Yano: transitions ``kappa`` times as likely as transversions,
+    scaled by the equilibrium frequencies (``msprime/mutations.py:550-649``).  The
+    arithmetic order below matches the reference so the matrix entries are identical."""
+
+    def __init__(self, kappa, equilibrium_frequencies=None, root_distribution=None,
+                 state_independent=False):
+        self.kappa = kappa
+        self.state_independent = state_independent
+        if equilibrium_frequencies is None:
+            freqs = np.array([0.25, 0.25, 0.25, 0.25], dtype="float64")
+        else:
+            freqs = np.array(equilibrium_frequencies, dtype="float64")
+        self.equilibrium_frequencies = freqs
+        if root_distribution is None:
+            root_distribution = freqs.copy()
+        q = np.full((4, 4), 1.0)
+        q[((0, 1, 2, 3), (2, 3, 0, 1))] = kappa  # A<->G, C<->T
+        q *= freqs
+        if state_independent:
+            np.fill_diagonal(q, kappa * freqs)
+        else:
+            np.fill_diagonal(q, 0.0)
+        q /= max(q.sum(axis=1, dtype="float64"))
+        sums = q.sum(axis=1, dtype="float64")
+        np.fill_diagonal(q, 1.0 - (sums - np.diag(q)))
+        super().__init__(_ACGT_ALLELES, root_distribution, q)
+
+
+class F84(MatrixMutationModel):
+    """Felsenstein 1984 (``msprime/mutations.py:652-760``)."""
+
+    def __init__(self, kappa, equilibrium_frequencies=None, root_distribution=None,
+                 state_independent=False):
+        self.kappa = kappa
+        self.state_independent = state_independent
+        if equilibrium_frequencies is None:
+            equilibrium_frequencies = [0.25, 0.25, 0.25, 0.25]
+        self.equilibrium_frequencies = equilibrium_frequencies
+        if root_distribution is None:
+            root_distribution = equilibrium_frequencies.copy()
+        f = equilibrium_frequencies
+        q = np.full((4, 4), 1.0, dtype="float64")
+        gamma = np.float64(1 + (kappa - 1) / np.array([f[0] + f[2], f[1] + f[3]]))
+        q[((0, 2), (2, 0))] = gamma[0]
+        q[((1, 3), (3, 1))] = gamma[1]
+        q *= f
+        if state_independent:
+            np.fill_diagonal(q, f * np.concatenate([gamma, gamma]))
+        else:
+            np.fill_diagonal(q, 0.0)
+        q = q / max(q.sum(axis=1))
+        sums = q.sum(axis=1, dtype="float64")
+        np.fill_diagonal(q, 1.0 - (sums - np.diag(q)))
+        super().__init__(_ACGT_ALLELES, root_distribution, q)
+
+
+class GTR(MatrixMutationModel):
+    """General time-reversible model; ``relative_rates`` are A<->C, A<->G, A<->T, C<->G,
+    C<->T, G<->T (``msprime/mutations.py:763-850``)."""
+
+    def __init__(self, relative_rates, equilibrium_frequencies=None, root_distribution=None,
+                 state_independent=False):
+        assert len(relative_rates) == 6
+        self.relative_rates = relative_rates
+        self.state_independent = state_independent
+        if equilibrium_frequencies is None:
+            equilibrium_frequencies = [0.25, 0.25, 0.25, 0.25]
+        self.equilibrium_frequencies = equilibrium_frequencies
+        if root_distribution is None:
+            root_distribution = equilibrium_frequencies
+        q = np.zeros((4, 4))
+        q[np.triu_indices_from(q, k=1)] = relative_rates
+        q += q.T
+        if state_independent:
+            np.fill_diagonal(q, 1.0)
+        q *= equilibrium_frequencies
+        q = q / max(q.sum(axis=1))
+        sums = q.sum(axis=1, dtype="float64")
+        np.fill_diagonal(q, np.diag(q) + 1.0 - sums)
+        super().__init__(_ACGT_ALLELES, root_distribution, q)
+
+
+class InfiniteSites(MatrixMutationModel):
+    """Legacy model object accepted by ``mutate`` (``msprime/mutations.py:1390-1400``)."""
+
+    def __init__(self, alphabet=BINARY):
+        self.alphabet = alphabet
+        models = {BINARY: BinaryMutationModel, NUCLEOTIDES: JC69}
+        if alphabet not in models:
+            raise ValueError("Bad alphabet")
+        model = models[alphabet]()
+        super().__init__(model.alleles, model.root_distribution, model.transition_matrix)
+
+
+MODEL_MAP = {
+    "infinite_alleles": InfiniteAlleles,
+    "binary": BinaryMutationModel,
+    "jc69": JC69,
+}
+
+
+def mutation_model_factory(model):
+    """None -> JC69, a name -> that model, an instance -> itself; otherwise TypeError."""
+    if model is None:
+        return JC69()
+    if isinstance(model, str):
+        lower = model.lower()
+        if lower not in MODEL_MAP:
+            raise ValueError(
+                "Model '{}' unknown. Choose from {}".format(model, sorted(MODEL_MAP.keys())))
+        return MODEL_MAP[lower]()
+    if isinstance(model, MutationModel):
+        return model
+    raise TypeError("Mutation model must be a string or an instance of MutationModel")
+
+
+_contexts: dict[int, _native.Context] = {}
+
+
+def _context(device: int) -> _native.Context:
+    ctx = _contexts.get(device)
+    if ctx is None:
+        ctx = _contexts[device] = _native.Context(device)
+    return ctx
+
+
+def _overlay(ctx, tables_dict, *, rate_map, model, discrete_genome, keep, start_time, end_time,
+             seed, replay_stream=None, slice_left=0.0, slice_right=0.0, load=True):
+    """Runs the device overlay and returns ``(result_columns, counts)``; updates the
+    model's allele counter like the C call does."""
+    if load:
+        ctx.load_tables(tables_dict)
+    params = _native.Params(
+        map_position=rate_map["position"], map_rate=rate_map["rate"], model=model._native(),
+        discrete_genome=discrete_genome, keep=keep, start_time=start_time, end_time=end_time,
+        seed=seed, replay_stream=replay_stream, slice_left=slice_left, slice_right=slice_right)
+    counts = ctx.generate(params)
+    if isinstance(model, InfiniteAlleles):
+        model._next_allele = counts["next_allele"]
+    return ctx.fetch(), counts
+
+
+def _merge_result(tables_dict, result):
+    """New table dict: everything as in the input, sites and mutations replaced
+    (``_msprime.sim_mutations`` touches nothing else, tests/test_mutations.py:593-598)."""
+    out = dict(tables_dict)
+    s, m = result["sites"], result["mutations"]
+    out["sites"] = {
+        "position": s["position"],
+        "ancestral_state": s["ancestral_state"].view(np.int8),
+        "ancestral_state_offset": s["ancestral_state_offset"],
+        "metadata": s["metadata"].view(np.int8),
+        "metadata_offset": s["metadata_offset"],
+    }
+    for key in ("metadata_schema",):
+        if tables_dict.get("sites") is not None and key in tables_dict["sites"]:
+            out["sites"][key] = tables_dict["sites"][key]
+    out["mutations"] = {
+        "site": m["site"],
+        "node": m["node"],
+        "parent": m["parent"],
+        "time": m["time"],
+        "derived_state": m["derived_state"].view(np.int8),
+        "derived_state_offset": m["derived_state_offset"],
+        "metadata": m["metadata"].view(np.int8),
+        "metadata_offset": m["metadata_offset"],
+    }
+    for key in ("metadata_schema",):
+        if tables_dict.get("mutations") is not None and key in tables_dict["mutations"]:
+            out["mutations"][key] = tables_dict["mutations"][key]
+    # edge indexes stay valid (edges are untouched); tskit rebuilds them otherwise
+    return out
+
+
+def sim_mutations(
+    tree_sequence,
+    rate=None,
+    *,
+    random_seed=None,
+    model=None,
+    start_time=None,
+    end_time=None,
+    discrete_genome=None,
+    keep=None,
+    record_provenance=True,
+    device=0,
+):
+    """Simulates mutations on ``tree_sequence`` on a B200 and returns the new tree sequence.
+
+    Same contract as ``msprime.sim_mutations`` (``msprime/mutations.py:1551-1702``):
+    ``rate`` is a float or a :class:`RateMap` (default 0); ``model`` is a name, a
+    :class:`MutationModel` or None (JC69); ``discrete_genome`` and ``keep`` default to
+    True and must be real booleans; ``start_time``/``end_time`` bound the mutation
+    times; ``random_seed`` lies in 1 .. 2**32 - 1.  The only extra argument is
+    ``device`` (CUDA ordinal).  The input is never modified.
+
+    The random stream is Philox4x32-10 keyed by the seed, so results are reproducible
+    for a seed but differ from stock msprime's MT19937 stream; the distribution is
+    the same (tests/test_statistics.py).
+    """
+    tables_dict, kind = _tables.from_tree_sequence(tree_sequence)
+    if random_seed is None:
+        seed = core.get_random_seed()
+    else:
+        seed = int(random_seed)
+
+    provenance_dict = None
+    if record_provenance:
+        provenance_dict = provenance.get_provenance_dict(dict(
+            command="sim_mutations", tree_sequence=tree_sequence, rate=rate, model=model,
+            start_time=start_time, end_time=end_time, discrete_genome=discrete_genome,
+            keep=keep, random_seed=seed))
+
+    if rate is None:
+        rate = 0
+    try:
+        rate = float(rate)
+        rate_map = intervals.RateMap.uniform(tree_sequence.sequence_length, rate)
+    except TypeError:
+        rate_map = rate
+    if not isinstance(rate_map, intervals.RateMap):
+        raise TypeError("rate must be a float or a RateMap")
+
+    if tables_dict.get("time_units") == _tables.TIME_UNITS_UNCALIBRATED:
+        raise ValueError("Simulating mutations doesn't make sense when time is uncalibrated")
+
+    start_time = -sys.float_info.max if start_time is None else float(start_time)
+    end_time = sys.float_info.max if end_time is None else float(end_time)
+    if start_time > end_time:
+        raise ValueError("start_time must be <= end_time")
+    discrete_genome = core.parse_flag(discrete_genome, default=True)
+    keep = core.parse_flag(keep, default=True)
+    model = mutation_model_factory(model)
+    seed = core.check_seed(seed)
+
+    result, _ = _overlay(
+        _context(device), tables_dict, rate_map=rate_map.asdict(), model=model,
+        discrete_genome=discrete_genome, keep=keep, start_time=start_time, end_time=end_time,
+        seed=seed)
+    out = _merge_result(tables_dict, result)
+    record = None
+    if provenance_dict is not None:
+        record = provenance.json_encode_provenance(provenance_dict)
+    return _tables.to_tree_sequence(out, kind, record)
+
+
+def mutate(tree_sequence, rate=None, random_seed=None, model=None, keep=False,
+           start_time=None, end_time=None):
+    """Legacy interface (``msprime/mutations.py:1423-1505``): infinite-sites mutations on
+    a continuous genome, binary alleles by default, ``keep=False`` by default."""
+    if model is not None and not isinstance(model, InfiniteSites):
+        raise ValueError(
+            "This is a legacy interface which does not support general "
+            "mutation models. Please use the sim_ancestry function instead.")
+    if model is None:
+        model = BinaryMutationModel()
+    return sim_mutations(
+        tree_sequence, rate=rate, random_seed=random_seed, model=model, keep=keep,
+        start_time=start_time, end_time=end_time, discrete_genome=False)
