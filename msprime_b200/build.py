@@ -21,11 +21,23 @@ NVCC_FLAGS = [
 ]
 
 
+TREEGEN_SRC = os.path.join(HERE, "csrc", "treegen.c")
+TREEGEN_OUT = os.path.join(HERE, "_treegen.so")
+
+
 def needs_build() -> bool:
     if not os.path.exists(OUT):
         return True
     t = os.path.getmtime(OUT)
     return any(os.path.exists(d) and os.path.getmtime(d) > t for d in DEPS)
+
+
+def build_treegen(force: bool = False) -> str:
+    """The synthetic-input generator (plain C, benchmark / test inputs only)."""
+    if force or not os.path.exists(TREEGEN_OUT) or os.path.getmtime(TREEGEN_SRC) > os.path.getmtime(TREEGEN_OUT):
+        cc = os.environ.get("CC", "gcc")
+        subprocess.run([cc, "-O2", "-std=c99", "-fPIC", "-shared", "-o", TREEGEN_OUT, TREEGEN_SRC, "-lm"], check=True)
+    return TREEGEN_OUT
 
 
 def build(force: bool = False, verbose: bool = False) -> str:
@@ -36,6 +48,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
             cmd.insert(1, "-Xptxas=-v")
             print(" ".join(cmd), file=sys.stderr)
         subprocess.run(cmd, check=True)
+    build_treegen(force)
     return OUT
 
 

@@ -16,7 +16,81 @@ implementation of the same construction (``csrc/treegen.c``, ``native_treeseq``)
 """
 from __future__ import annotations
 
+import ctypes as C
+import os
+
 import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_TREEGEN_SO = os.path.join(_HERE, "_treegen.so")
+
+
+class _TreegenResult(C.Structure):
+    _fields_ = [
+        ("num_nodes", C.c_uint64), ("num_samples", C.c_uint64), ("num_edges", C.c_uint64),
+        ("num_trees", C.c_uint64), ("node_time", C.POINTER(C.c_double)),
+        ("edge_left", C.POINTER(C.c_double)), ("edge_right", C.POINTER(C.c_double)),
+        ("edge_parent", C.POINTER(C.c_int32)), ("edge_child", C.POINTER(C.c_int32)),
+    ]
+
+
+_treegen = None
+
+
+def _treegen_lib():
+    global _treegen
+    if _treegen is None:
+        if not os.path.exists(_TREEGEN_SO):
+            from . import build
+
+            build.build_treegen()
+        lib = C.CDLL(_TREEGEN_SO)
+        lib.treegen_smc.argtypes = [C.c_uint64, C.c_double, C.c_double, C.c_double, C.c_uint64, C.c_int,
+                                    C.POINTER(_TreegenResult)]
+        lib.treegen_smc.restype = C.c_int
+        lib.treegen_free.argtypes = [C.POINTER(_TreegenResult)]
+        lib.treegen_free.restype = None
+        _treegen = lib
+    return _treegen
+
+
+def native_treeseq(samples, sequence_length, recombination_rate, population_size, random_seed, ploidy=2,
+                   discrete_genome=True):
+    """Large SMC' tree sequence from the C generator (``csrc/treegen.c``); same arguments
+    and output layout as :func:`sim_ancestry_smc`.  Adds ``num_trees`` to the dict."""
+    lib = _treegen_lib()
+    res = _TreegenResult()
+    n = int(samples) * int(ploidy)
+    ret = lib.treegen_smc(n, float(sequence_length), float(recombination_rate),
+                          float(ploidy) * float(population_size), int(random_seed), int(bool(discrete_genome)),
+                          C.byref(res))
+    if ret != 0:
+        raise RuntimeError(f"treegen_smc failed with status {ret}")
+    try:
+        N, E = res.num_nodes, res.num_edges
+        flags = np.zeros(N, dtype=np.uint32)
+        flags[:n] = 1
+
+        def arr(ptr, count, dtype):
+            if count == 0:
+                return np.zeros(0, dtype=dtype)
+            return np.ctypeslib.as_array(ptr, shape=(count,)).astype(dtype, copy=True)
+
+        d = {
+            "sequence_length": float(sequence_length),
+            "time_units": "generations",
+            "nodes": {"time": arr(res.node_time, N, np.float64), "flags": flags},
+            "edges": {
+                "left": arr(res.edge_left, E, np.float64), "right": arr(res.edge_right, E, np.float64),
+                "parent": arr(res.edge_parent, E, np.int32), "child": arr(res.edge_child, E, np.int32),
+            },
+            "sites": empty_sites(),
+            "mutations": empty_mutations(),
+            "num_trees": int(res.num_trees),
+        }
+    finally:
+        lib.treegen_free(C.byref(res))
+    return d
 
 
 def _kingman(n, two_ne, rng):
