@@ -1,0 +1,492 @@
+#!/usr/bin/env python
+"""Benchmark of the mutation-overlay hot path (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--workload NAME]
+
+One "step" is one overlay of the whole workload.  At N > 1 (torchrun, one rank per
+GPU) the genome is cut into N position slices, edges are replicated, and the only
+collective is an all-reduce of the per-rank counts/times (strong scaling of a fixed
+workload).  Rank 0 prints ONE JSON line:
+
+* ``value``        new mutations per second with the tree sequence resident in HBM
+                   (CUDA events on the library's stream, max over ranks);
+* ``e2e``          the same metric through the host-buffer call sequence
+                   load_tables -> generate -> fetch (H2D and D2H inside the timed region);
+* ``roofline``     the dominant kernel's algorithmic bytes / its measured duration
+                   against MEASURED_PEAKS.json;
+* ``cpu_baseline`` the compiled reference mutgen (oracle/_ref) on the host cores, on a
+                   bounded sample (a genome prefix) of the same workload.
+
+``--impl reference`` times only the CPU reference (all host cores) and prints the
+same line with ``"impl": "reference"``.
+
+The oracle is used here only as the CPU baseline, never as the measured product path.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import multiprocessing as mp
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+FMAX = float(np.finfo(np.float64).max)
+METRIC = "sim_mutations_new_mutations_per_second"
+UNIT = "mutations/s"
+
+WORKLOADS = {
+    # BASELINE.json configs[4]: the configuration the metric's target is quoted on
+    "config5": dict(samples=1_000_000, L=2.5e8, recomb=1e-8, ne=1e4, ts_seed=1, rate=1e-7,
+                    model="infinite_alleles", discrete=True,
+                    text="config5: InfiniteAlleles rate=1e-7 discrete keep=False, 1e6 diploid samples x 2.5e8 bp"),
+    # smaller cases for quick checks (not bench lines)
+    "config3": dict(samples=100_000, L=1e8, recomb=1e-8, ne=1e4, ts_seed=1, rate=1e-8, model="jc69",
+                    discrete=True, text="1e5 samples x 1e8 bp, JC69 rate=1e-8"),
+    "small": dict(samples=2_000, L=2e6, recomb=1e-8, ne=1e4, ts_seed=1, rate=1e-7, model="infinite_alleles",
+                  discrete=True, text="small: 2e3 samples x 2e6 bp, InfiniteAlleles rate=1e-7"),
+}
+
+
+def log(*a):
+    print(*a, file=sys.stderr, flush=True)
+
+
+def make_input(w):
+    from msprime_b200 import synth
+
+    t0 = time.time()
+    ts = synth.native_treeseq(w["samples"], w["L"], w["recomb"], w["ne"], w["ts_seed"])
+    log(f"[bench] input: N={len(ts['nodes']['time'])} E={len(ts['edges']['left'])} trees={ts['num_trees']} "
+        f"({time.time() - t0:.1f} s, synthetic SMC' generator)")
+    return ts
+
+
+def oracle_model(name):
+    if name == "infinite_alleles":
+        return {"kind": "infinite_alleles", "start_allele": 0}
+    if name == "jc69":
+        m = (np.full((4, 4), 1 / 3) - np.eye(4) / 3).tolist()
+        return {"kind": "matrix", "alleles": ["A", "C", "G", "T"], "root_distribution": [0.25] * 4,
+                "transition_matrix": m}
+    raise ValueError(name)
+
+
+def native_model(name):
+    m = oracle_model(name)
+    if m["kind"] == "matrix":
+        return {"kind": 0, "alleles": m["alleles"], "root_distribution": m["root_distribution"],
+                "transition_matrix": m["transition_matrix"]}
+    return {"kind": 1, "start_allele": 0}
+
+
+def genome_prefix(ts, frac):
+    """The bounded CPU sample: the same tree sequence restricted to [0, frac * L)."""
+    L = float(ts["sequence_length"])
+    X = float(max(1.0, np.floor(L * frac)))
+    if X >= L:
+        return ts, 1.0
+    e = ts["edges"]
+    keep = e["left"] < X
+    out = dict(ts)
+    out["sequence_length"] = X
+    out["edges"] = {"left": e["left"][keep], "right": np.minimum(e["right"][keep], X),
+                    "parent": e["parent"][keep], "child": e["child"][keep]}
+    return out, X / L
+
+
+# ------------------------------------------------------------------ CPU reference
+_CPU_JOB = {}
+
+
+def _cpu_worker(seed):
+    from oracle import oracle
+
+    j = _CPU_JOB
+    t0 = time.perf_counter()
+    r = oracle.sim_mutations(j["ts"], which=j["which"], map_position=[0, j["ts"]["sequence_length"]],
+                             map_rate=[j["rate"]], model=oracle_model(j["model"]), discrete_genome=j["discrete"],
+                             keep=False, seed=seed)
+    return len(r["mutations"]["site"]), r["seconds"], time.perf_counter() - t0
+
+
+def cpu_reference_pass(ts, w, cores, seed0, which):
+    """One pass: ``cores`` independent processes, each overlaying the sample with its own
+    seed (the reference is single-threaded, so this is how it uses a whole host)."""
+    _CPU_JOB.update(ts=ts, which=which, rate=w["rate"], model=w["model"], discrete=w["discrete"])
+    t0 = time.perf_counter()
+    if cores == 1:
+        res = [_cpu_worker(seed0)]
+    else:
+        ctx = mp.get_context("fork")
+        with ctx.Pool(cores) as pool:
+            res = pool.map(_cpu_worker, [seed0 + i for i in range(cores)])
+    wall = time.perf_counter() - t0
+    muts = sum(r[0] for r in res)
+    inner = max(r[1] for r in res)
+    return muts, inner, wall
+
+
+def cpu_kind():
+    from oracle import oracle
+
+    if oracle.have("ref"):
+        return "reference", "ref"
+    oracle.build(("port",))
+    return "port", "port"
+
+
+def run_reference_arm(args, rank, world):
+    """``--impl reference``: the reference's own CPU implementation on the host cores."""
+    if rank != 0:
+        return
+    w = WORKLOADS[args.workload]
+    kind, which = cpu_kind()
+    ts = make_input(w)
+    cores = os.cpu_count() or 1
+    # bounded sample: about 120 s of single-core reference time spread over all steps
+    # (the reference runs config5 at ~1.7e5 mutations/s per core)
+    expected = float(((ts["edges"]["right"] - ts["edges"]["left"])
+                      * (ts["nodes"]["time"][ts["edges"]["parent"]] - ts["nodes"]["time"][ts["edges"]["child"]])).sum()
+                     ) * w["rate"]
+    per_step = 120.0 / max(1, args.steps + args.warmup)
+    frac = min(1.0, max(1e-3, per_step * 1.7e5 / max(expected, 1.0)))
+    sample, frac = genome_prefix(ts, frac)
+    for i in range(args.warmup):
+        cpu_reference_pass(sample, w, cores, 1000 + 100 * i, which)
+    muts = 0
+    wall = 0.0
+    for i in range(args.steps):
+        m, _, t = cpu_reference_pass(sample, w, cores, 5000 + 100 * i, which)
+        muts += m
+        wall += t
+    value = muts / wall
+    sample_txt = (f"genome prefix [0, {sample['sequence_length']:.0f}) = {frac:.4f} of the workload, "
+                  f"{cores} processes x 1 overlay each per step, MT19937 seeds differ per process")
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * wall / max(1, args.steps),
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": w["text"], "input": "synthetic SMC' tree sequence (msprime_b200/csrc/treegen.c)"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample_txt},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------ clocks
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons through NVML while the timed region runs."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index = index
+        self.samples = []
+        self.reasons = set()
+        self.max_mhz = None
+        self._stop_evt = threading.Event()
+        self.ok = False
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception as e:  # noqa: BLE001
+            log(f"[bench] NVML unavailable: {e}")
+
+    def run(self):
+        if not self.ok:
+            return
+        nv = self.nv
+        names = {
+            "hw_slowdown": nv.nvmlClocksThrottleReasonHwSlowdown,
+            "hw_thermal_slowdown": nv.nvmlClocksThrottleReasonHwThermalSlowdown,
+            "sw_thermal_slowdown": nv.nvmlClocksThrottleReasonSwThermalSlowdown,
+            "sw_power_cap": nv.nvmlClocksThrottleReasonSwPowerCap,
+        }
+        while not self._stop_evt.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for k, bit in names.items():
+                    if r & bit:
+                        self.reasons.add(k)
+            except Exception:  # noqa: BLE001
+                pass
+            self._stop_evt.wait(0.02)
+
+    def stop(self):
+        self._stop_evt.set()
+        self.join(timeout=2)
+        med = float(np.median(self.samples)) if self.samples else None
+        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(self.samples)}
+
+
+# ------------------------------------------------------------------ roofline bookkeeping
+def algorithmic_bytes(kernel, n):
+    """Compulsory bytes of ONE launch of ``kernel`` (DESIGN.md, section "Kernels").
+    n: E edges, R records entering the sort, M mutation rows, S site rows, DB/AB
+    derived/ancestral state bytes."""
+    E, R, M, S = n["E"], n["R"], n["M"], n["S"]
+    table = {
+        # left,right f64 + parent,child i32 + two node-time gathers, count out
+        "k1_count": E * (8 + 8 + 4 + 4 + 16) + E * 4,
+        # edge columns again + count/offset in, pos,time f64 + node,ord i32 + key u64 + val u32 out
+        "k2_place": E * (8 + 8 + 4 + 4 + 16 + 8) + M * (8 + 8 + 4 + 4 + 8 + 4),
+        "rs_key_bits": R * 8,
+        "rs_hist": R * 8,
+        # key u64 + val u32, read and written once per pass
+        "rs_scatter": R * 2 * (8 + 4),
+        "finalize_runs": R * 8,
+        "post_sort_check": R * (8 + 4),
+        # key + val + node + pos gathers in, parent (+ state) out
+        "k4_resolve": R * (8 + 4 + 4 + 8) + R * 4,
+        # val, key, scans (site,mut u32; 4 x u64 byte scans), rec gathers in; table rows out
+        "k5_emit": R * (4 + 8 + 4 + 4 + 32 + 8 + 8 + 4 + 4) + M * (4 + 4 + 4 + 8 + 16) + S * (8 + 16)
+        + n["DB"] + n["AB"],
+        "scan_tile_sums": None, "scan_apply": None, "scan_spine": None,
+    }
+    return table.get(kernel)
+
+
+# ------------------------------------------------------------------ the B200 arm
+def pinned_like(a):
+    """A pinned-host copy of numpy array ``a`` (torch owns the buffer)."""
+    import torch
+
+    t = torch.from_numpy(np.ascontiguousarray(a)).pin_memory()
+    return t, t.numpy()
+
+
+def pinned_empty(n, dtype):
+    import torch
+
+    tdt = {np.float64: torch.float64, np.int32: torch.int32, np.uint8: torch.uint8, np.uint64: torch.int64}[dtype]
+    t = torch.empty(int(n), dtype=tdt, pin_memory=True)
+    a = t.numpy()
+    return t, (a.view(np.uint64) if dtype is np.uint64 else a)
+
+
+def slice_cuts(L, world):
+    return [float(np.floor(L * r / world)) for r in range(world)] + [float(L)]
+
+
+def run_b200_arm(args, rank, local_rank, world):
+    import torch
+    import torch.distributed as dist
+
+    from msprime_b200 import _native, build
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the B200 arm has no CPU fallback "
+                         "(use --impl reference for the CPU baseline)")
+    if rank == 0:
+        build.build()
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        dist.barrier()
+    torch.cuda.set_device(local_rank)
+    w = WORKLOADS[args.workload]
+    ts = make_input(w)
+    L = float(ts["sequence_length"])
+    cuts = slice_cuts(L, world)
+    sl, sr = (0.0, 0.0) if world == 1 else (cuts[rank], cuts[rank + 1])
+
+    # host inputs in pinned memory (what a caller hands to the C ABI)
+    hold = []
+    host_ts = {"sequence_length": L, "time_units": ts["time_units"], "nodes": {}, "edges": {},
+               "sites": ts["sites"], "mutations": ts["mutations"]}
+    t, host_ts["nodes"]["time"] = pinned_like(ts["nodes"]["time"])
+    hold.append(t)
+    for k in ("left", "right", "parent", "child"):
+        t, host_ts["edges"][k] = pinned_like(ts["edges"][k])
+        hold.append(t)
+    E, N = len(ts["edges"]["left"]), len(ts["nodes"]["time"])
+    h2d_bytes = E * (8 + 8 + 4 + 4) + N * 8
+
+    ctx = _native.Context(local_rank)
+    stream = torch.cuda.ExternalStream(ctx.stream(), device=torch.device("cuda", local_rank))
+
+    def params(step):
+        return _native.Params(map_position=[0, L], map_rate=[w["rate"]], model=native_model(w["model"]),
+                              discrete_genome=w["discrete"], keep=False, start_time=-FMAX, end_time=FMAX,
+                              seed=1000 + step, slice_left=sl, slice_right=sr)
+
+    def sync_all():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def reduce(x, op):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=f"cuda:{local_rank}")
+        dist.all_reduce(t, op=op)
+        return float(t.item())
+
+    ctx.load_tables(host_ts)
+    # ---- device-resident throughput
+    for i in range(args.warmup):
+        ctx.generate(params(i))
+    c = ctx.counts
+    sizes = ctx.result_sizes()
+    out_bufs = {}
+    for name, dtype in _native._COLUMNS:
+        t, out_bufs[name] = pinned_empty(int(sizes[name] * 1.3) + 4096, dtype)
+        hold.append(t)
+    ctx.kernel_timing(True)
+    launches0 = ctx.kernel_launches()
+    sampler = ClockSampler(local_rank)
+    sync_all()
+    sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record(stream)
+    muts = 0
+    lib_ms = 0.0
+    for i in range(args.steps):
+        c = ctx.generate(params(100 + i))
+        muts += c["num_new_mutations"]
+        lib_ms += c["device_ms"]
+    ev1.record(stream)
+    sync_all()
+    clocks = sampler.stop()
+    dev_ms = reduce(ev0.elapsed_time(ev1), dist.ReduceOp.MAX if world > 1 else None)
+    total_muts = reduce(float(muts), dist.ReduceOp.SUM if world > 1 else None)
+    launches = ctx.kernel_launches() - launches0
+    ktimes = ctx.kernel_times()
+    phases = ctx.phase_ms()
+    ctx.kernel_timing(False)
+    value = total_muts / (dev_ms * 1e-3)
+
+    # ---- end to end through the host-buffer calls
+    d2h_bytes = 0
+    for i in range(min(2, args.warmup)):
+        ctx.load_tables(host_ts)
+        ctx.generate(params(200 + i))
+        ctx.fetch(out_bufs)
+    sync_all()
+    ev2, ev3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    wall0 = time.perf_counter()
+    ev2.record(stream)
+    e2e_muts = 0
+    for i in range(args.steps):
+        ctx.load_tables(host_ts)
+        c = ctx.generate(params(300 + i))
+        res = ctx.fetch(out_bufs)
+        e2e_muts += c["num_new_mutations"]
+        d2h_bytes = sum(int(a.nbytes) for tbl in res.values() for a in tbl.values())
+    ev3.record(stream)
+    sync_all()
+    wall = time.perf_counter() - wall0
+    e2e_ms = reduce(max(ev2.elapsed_time(ev3), wall * 1e3), dist.ReduceOp.MAX if world > 1 else None)
+    e2e_total = reduce(float(e2e_muts), dist.ReduceOp.SUM if world > 1 else None)
+    e2e_value = e2e_total / (e2e_ms * 1e-3)
+    h2d_total = reduce(float(h2d_bytes), dist.ReduceOp.SUM if world > 1 else None)
+    d2h_total = reduce(float(d2h_bytes), dist.ReduceOp.SUM if world > 1 else None)
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline of the dominant kernel (rank 0's launches)
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:  # noqa: BLE001
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
+    kt = sorted(ktimes.items(), key=lambda kv: -kv[1][1])
+    total_kernel_ms = sum(v[1] for v in ktimes.values()) or 1.0
+    last = ctx.counts
+    nn = {"E": E, "R": last["num_mutations"], "M": last["num_mutations"],
+          "S": last["num_sites"], "DB": last["derived_state_bytes"], "AB": last["ancestral_state_bytes"]}
+    roofline = None
+    for name, (n_launch, ms) in kt:
+        ab = algorithmic_bytes(name, nn)
+        if ab is None:
+            continue
+        avg_ms = ms / n_launch
+        achieved = ab / (avg_ms * 1e-3) / 1e9
+        roofline = {"bound": "hbm", "kernel": name, "achieved": achieved, "peak": peak, "unit": "GB/s",
+                    "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                    "avg_launch_ms": avg_ms, "launches_per_step": n_launch / args.steps,
+                    "share_of_kernel_time": ms / total_kernel_ms, "algorithmic_bytes_per_launch": ab}
+        break
+    kernels = {k: {"launches": v[0], "ms_total": round(v[1], 4)} for k, v in kt[:12]}
+
+    # ---- CPU baseline (N = 1 only): the compiled reference on all host cores
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        kind, which = cpu_kind()
+        cores = os.cpu_count() or 1
+        expected = float(last["num_new_mutations"])
+        frac = min(1.0, max(1e-3, 12.0 * 1.7e5 / max(expected, 1.0)))
+        sample, frac = genome_prefix(ts, frac)
+        m, inner, wall_cpu = cpu_reference_pass(sample, w, cores, 7000, which)
+        cpu = {"value": m / wall_cpu, "unit": UNIT, "cores": cores, "kind": kind,
+               "sample": f"genome prefix [0, {sample['sequence_length']:.0f}) = {frac:.4f} of the workload; "
+                         f"{cores} processes x 1 overlay each ({m} mutations in {wall_cpu:.1f} s wall, "
+                         f"slowest mutgen_generate {inner:.1f} s)"}
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": w["text"], "input": "synthetic SMC' tree sequence (msprime_b200/csrc/treegen.c)",
+                   "edges": E, "nodes": N, "mutations_per_step": total_muts / args.steps,
+                   "l2": "inputs larger than L2 (edge columns + records > 126 MB), no flush",
+                   "sharding": "whole genome on one GPU" if world == 1 else
+                   f"{world} genome position slices, edges replicated, no data-path collective"},
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d_total, "d2h_bytes_per_step": d2h_total,
+                "ms_per_step": e2e_ms / args.steps, "path": "mspb_ctx_load_tables + mspb_generate + mspb_fetch, "
+                "pinned host buffers"},
+        "gpu_launches": launches,
+        "clocks": clocks,
+        "roofline": roofline,
+        "cpu_baseline": cpu,
+        "phases_ms_last_step": {k: round(v, 4) for k, v in phases.items()},
+        "kernels": kernels,
+        "library_device_ms_per_step": lib_ms / args.steps,
+    }
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="config5", choices=sorted(WORKLOADS))
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    args.warmup = max(args.warmup, 0)
+    if args.impl == "reference":
+        run_reference_arm(args, rank, world)
+        return
+    args.warmup = max(args.warmup, 3)
+    run_b200_arm(args, rank, local_rank, world)
+
+
+if __name__ == "__main__":
+    main()

@@ -172,6 +172,14 @@ int mspb_fetch(mspb_ctx_t *ctx, const mspb_columns_t *host_columns);
 int mspb_device_columns(mspb_ctx_t *ctx, mspb_columns_t *device_columns);
 /* Number of kernels this library launched since the context was created. */
 uint64_t mspb_kernel_launches(const mspb_ctx_t *ctx);
+/* The CUDA stream (cudaStream_t) every kernel and copy of this context runs on, so
+ * a caller can bracket calls with its own events on that stream. */
+void *mspb_ctx_stream(const mspb_ctx_t *ctx);
+/* Per-kernel timing: enable != 0 brackets every launch with CUDA events from now on
+ * (and clears the accumulated table); mspb_kernel_time reads entry `index` of the
+ * table (kernel name, launches, summed milliseconds) and fails past the end. */
+int mspb_kernel_timing(mspb_ctx_t *ctx, int enable);
+int mspb_kernel_time(const mspb_ctx_t *ctx, int index, const char **name, uint64_t *launches, double *ms);
 /* Per-phase device milliseconds of the last mspb_generate (n <= MSPB_NUM_PHASES). */
 #define MSPB_NUM_PHASES 8
 int mspb_phase_ms(const mspb_ctx_t *ctx, float *ms, int n);

@@ -100,6 +100,7 @@ EXPORTED_SYMBOLS = [
     "mspb_ctx_create", "mspb_ctx_destroy", "mspb_ctx_load_tables", "mspb_generate", "mspb_fetch",
     "mspb_device_columns", "mspb_kernel_launches", "mspb_phase_ms", "mspb_phase_name",
     "mspb_sim_mutations", "mspb_columns_free", "mspb_strerror", "mspb_version",
+    "mspb_ctx_stream", "mspb_kernel_timing", "mspb_kernel_time",
 ]
 
 _lib = None
@@ -129,6 +130,11 @@ def lib():
         L.mspb_strerror.argtypes = [C.c_int]
         L.mspb_strerror.restype = C.c_char_p
         L.mspb_version.restype = C.c_char_p
+        L.mspb_ctx_stream.argtypes = [C.c_void_p]
+        L.mspb_ctx_stream.restype = C.c_void_p
+        L.mspb_kernel_timing.argtypes = [C.c_void_p, C.c_int]
+        L.mspb_kernel_time.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_uint64),
+                                       C.POINTER(C.c_double)]
         _lib = L
     return _lib
 
@@ -259,11 +265,11 @@ class Context:
         self.counts = {name: getattr(c, name) for name, _ in _Counts._fields_}
         return self.counts
 
-    def fetch(self):
-        """Copies the resident result to fresh numpy arrays: ``{"sites": {...}, "mutations": {...}}``."""
+    def result_sizes(self):
+        """Element counts of the output columns of the last ``generate``."""
         c = self.counts
         S, M = c["num_sites"], c["num_mutations"]
-        sizes = {
+        return {
             "site_position": S, "site_ancestral_state": c["ancestral_state_bytes"],
             "site_ancestral_state_offset": S + 1, "site_metadata": c["site_metadata_bytes"],
             "site_metadata_offset": S + 1, "mutation_site": M, "mutation_node": M, "mutation_parent": M,
@@ -271,10 +277,24 @@ class Context:
             "mutation_derived_state_offset": M + 1, "mutation_metadata": c["mutation_metadata_bytes"],
             "mutation_metadata_offset": M + 1,
         }
+
+    def fetch(self, out=None):
+        """Copies the resident result to the host: ``{"sites": {...}, "mutations": {...}}``.
+
+        ``out`` may map column names (``_COLUMNS``) to preallocated host arrays (pinned
+        memory makes the copy a single DMA); each must be at least as long as the
+        column.  Without it fresh numpy arrays are allocated."""
+        sizes = self.result_sizes()
         cols = _Columns()
         arrays = {}
         for name, dtype in _COLUMNS:
-            a = np.empty(sizes[name], dtype=dtype)
+            if out is not None:
+                buf = out[name]
+                if buf.dtype != dtype or buf.size < sizes[name]:
+                    raise ValueError(f"output buffer for {name} is too small or of the wrong dtype")
+                a = buf[:sizes[name]]
+            else:
+                a = np.empty(sizes[name], dtype=dtype)
             arrays[name] = a
             setattr(cols, name, _p(a) if a.size > 0 else None)
         check(lib().mspb_fetch(self._h, C.byref(cols)))
@@ -290,6 +310,23 @@ class Context:
 
     def kernel_launches(self) -> int:
         return int(lib().mspb_kernel_launches(self._h))
+
+    def stream(self) -> int:
+        """The context's cudaStream_t as an integer (wrap with ``torch.cuda.ExternalStream``)."""
+        return int(lib().mspb_ctx_stream(self._h) or 0)
+
+    def kernel_timing(self, enable=True):
+        check(lib().mspb_kernel_timing(self._h, int(bool(enable))))
+
+    def kernel_times(self):
+        """``{kernel name: (launches, total ms)}`` accumulated since ``kernel_timing(True)``."""
+        out = {}
+        i = 0
+        name, n, ms = C.c_char_p(), C.c_uint64(), C.c_double()
+        while lib().mspb_kernel_time(self._h, i, C.byref(name), C.byref(n), C.byref(ms)) == 0:
+            out[name.value.decode()] = (int(n.value), float(ms.value))
+            i += 1
+        return out
 
     def phase_ms(self):
         buf = (C.c_float * NUM_PHASES)()

@@ -8,9 +8,108 @@
 #include <stdint.h>
 #include <math.h>
 
+#include <map>
+#include <string>
+#include <vector>
+
 #define MSPB_DEVFN __device__ __forceinline__
 
 namespace mspb {
+
+// ---------------------------------------------------------------- launch log (host)
+// Counts every kernel this library launches and, when timing is on, brackets each
+// launch with CUDA events on the launching stream so that bench.py can report the
+// average duration of the dominant kernel live (no profiler attached).
+struct LaunchLog {
+    struct Rec {
+        const char *name;
+        cudaEvent_t a, b;
+    };
+    struct Stat {
+        uint64_t launches = 0;
+        double ms = 0;
+    };
+    uint64_t count = 0;
+    bool timing = false;
+    cudaStream_t stream = nullptr;
+    std::vector<Rec> pending;
+    std::vector<cudaEvent_t> pool;
+    std::map<std::string, Stat> stats;
+    std::vector<std::string> names; // stable iteration order for the C ABI
+
+    cudaEvent_t get_event()
+    {
+        if (!pool.empty()) {
+            cudaEvent_t e = pool.back();
+            pool.pop_back();
+            return e;
+        }
+        cudaEvent_t e = nullptr;
+        cudaEventCreate(&e);
+        return e;
+    }
+    void begin(const char *name)
+    {
+        count++;
+        if (timing) {
+            Rec r { name, get_event(), get_event() };
+            cudaEventRecord(r.a, stream);
+            pending.push_back(r);
+        }
+    }
+    void end()
+    {
+        if (timing) {
+            cudaEventRecord(pending.back().b, stream);
+        }
+    }
+    // call after the stream has been synchronised
+    void collect()
+    {
+        for (const Rec &r : pending) {
+            float ms = 0;
+            if (cudaEventElapsedTime(&ms, r.a, r.b) == cudaSuccess) {
+                Stat &s = stats[r.name];
+                if (s.launches == 0) {
+                    bool known = false;
+                    for (const auto &n : names) {
+                        known = known || n == r.name;
+                    }
+                    if (!known) {
+                        names.push_back(r.name);
+                    }
+                }
+                s.launches++;
+                s.ms += ms;
+            }
+            pool.push_back(r.a);
+            pool.push_back(r.b);
+        }
+        pending.clear();
+        cudaGetLastError();
+    }
+    void reset()
+    {
+        collect();
+        stats.clear();
+        names.clear();
+    }
+    void release()
+    {
+        collect();
+        for (cudaEvent_t e : pool) {
+            cudaEventDestroy(e);
+        }
+        pool.clear();
+    }
+};
+
+#define MSPB_LAUNCH(log, name, ...)                                                                                    \
+    do {                                                                                                               \
+        (log).begin(name);                                                                                             \
+        __VA_ARGS__;                                                                                                   \
+        (log).end();                                                                                                   \
+    } while (0)
 
 // ---------------------------------------------------------------- Philox4x32-10
 struct Philox {

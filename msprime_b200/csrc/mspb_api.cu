@@ -69,7 +69,7 @@ struct mspb_ctx {
     cudaStream_t stream = nullptr;
     cudaEvent_t ev[MSPB_NUM_PHASES + 1] = {};
     float phase_ms[MSPB_NUM_PHASES] = {};
-    uint64_t launches = 0;
+    LaunchLog log;
     bool tables_loaded = false, generated = false;
     // tables
     double L = 0;
@@ -241,6 +241,7 @@ extern "C" int mspb_ctx_create(int device, mspb_ctx_t **out)
     for (auto &e : ctx->ev) {
         cudaEventCreate(&e);
     }
+    ctx->log.stream = ctx->stream;
     if (cudaMallocHost((void **) &ctx->host, sizeof(HostTotals)) != cudaSuccess
         || cudaMallocHost((void **) &ctx->or_and_host, 2 * sizeof(uint64_t)) != cudaSuccess
         || ctx->dev_totals.ensure(sizeof(HostTotals)) != 0 || ctx->or_and.ensure(2) != 0) {
@@ -277,6 +278,7 @@ extern "C" void mspb_ctx_destroy(mspb_ctx_t *ctx)
     REL(o_site_anc_off); REL(o_site_md_off); REL(o_mut_der_off); REL(o_mut_md_off);
     REL(o_mut_site); REL(o_mut_node); REL(o_mut_parent);
 #undef REL
+    ctx->log.release();
     if (ctx->host != nullptr) {
         cudaFreeHost(ctx->host);
     }
@@ -296,7 +298,43 @@ extern "C" void mspb_ctx_destroy(mspb_ctx_t *ctx)
 
 extern "C" uint64_t mspb_kernel_launches(const mspb_ctx_t *ctx)
 {
-    return ctx == nullptr ? 0 : ctx->launches;
+    return ctx == nullptr ? 0 : ctx->log.count;
+}
+
+extern "C" void *mspb_ctx_stream(const mspb_ctx_t *ctx)
+{
+    return ctx == nullptr ? nullptr : (void *) ctx->stream;
+}
+
+extern "C" int mspb_kernel_timing(mspb_ctx_t *ctx, int enable)
+{
+    if (ctx == nullptr) {
+        return MSPB_ERR_BAD_PARAM_VALUE;
+    }
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    ctx->log.reset();
+    ctx->log.timing = enable != 0;
+    return 0;
+}
+
+extern "C" int mspb_kernel_time(const mspb_ctx_t *ctx, int index, const char **name, uint64_t *launches, double *ms)
+{
+    if (ctx == nullptr || index < 0 || (size_t) index >= ctx->log.names.size()) {
+        return MSPB_ERR_BAD_PARAM_VALUE;
+    }
+    const std::string &n = ctx->log.names[(size_t) index];
+    const auto it = ctx->log.stats.find(n);
+    if (name != nullptr) {
+        *name = n.c_str();
+    }
+    if (launches != nullptr) {
+        *launches = it->second.launches;
+    }
+    if (ms != nullptr) {
+        *ms = it->second.ms;
+    }
+    return 0;
 }
 
 extern "C" int mspb_phase_ms(const mspb_ctx_t *ctx, float *ms, int n)
@@ -524,22 +562,18 @@ extern "C" int mspb_ctx_load_tables(mspb_ctx_t *ctx, const mspb_tables_t *t)
     CUDA_OK(cudaMemsetAsync(&dt->fractional_sites, 0, sizeof(uint32_t), st));
     TreeSeqView ts = make_ts_view(ctx);
     if (ctx->N > 0) {
-        validate_nodes_kernel<<<grid_for(ctx->N, 256), 256, 0, st>>>(ctx->N, ctx->node_time.p, &dt->first_bad);
-        ctx->launches++;
+        MSPB_LAUNCH(ctx->log, "validate_nodes", validate_nodes_kernel<<<grid_for(ctx->N, 256), 256, 0, st>>>(ctx->N, ctx->node_time.p, &dt->first_bad));
     }
     if (ctx->E > 0) {
-        validate_edges_kernel<<<grid_for(ctx->E, 256), 256, 0, st>>>(ts, &dt->first_bad);
-        ctx->launches++;
+        MSPB_LAUNCH(ctx->log, "validate_edges", validate_edges_kernel<<<grid_for(ctx->E, 256), 256, 0, st>>>(ts, &dt->first_bad));
     }
     if (ctx->S0 > 0) {
-        validate_sites_kernel<<<grid_for(ctx->S0, 256), 256, 0, st>>>(
-            ctx->S0, ctx->k_site_pos.p, ctx->L, &dt->first_bad, &dt->fractional_sites);
-        ctx->launches++;
+        MSPB_LAUNCH(ctx->log, "validate_sites", validate_sites_kernel<<<grid_for(ctx->S0, 256), 256, 0, st>>>(
+            ctx->S0, ctx->k_site_pos.p, ctx->L, &dt->first_bad, &dt->fractional_sites));
     }
     if (ctx->M0 > 0) {
-        validate_mutations_kernel<<<grid_for(ctx->M0, 256), 256, 0, st>>>(ctx->M0, ctx->k_mut_site.p, ctx->k_mut_node.p,
-            ctx->have_mut_time ? ctx->k_mut_time.p : nullptr, ctx->S0, ctx->N, ctx->node_time.p, &dt->first_bad);
-        ctx->launches++;
+        MSPB_LAUNCH(ctx->log, "validate_mutations", validate_mutations_kernel<<<grid_for(ctx->M0, 256), 256, 0, st>>>(ctx->M0, ctx->k_mut_site.p, ctx->k_mut_node.p,
+            ctx->have_mut_time ? ctx->k_mut_time.p : nullptr, ctx->S0, ctx->N, ctx->node_time.p, &dt->first_bad));
     }
     CUDA_OK(cudaMemcpyAsync(&ctx->host->first_bad, &dt->first_bad, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
     CUDA_OK(cudaMemcpyAsync(
@@ -557,22 +591,20 @@ extern "C" int mspb_ctx_load_tables(mspb_ctx_t *ctx, const mspb_tables_t *t)
     } else {
         TRY(ensure_sort_buffers(ctx, ctx->E));
         RadixSortBuffers sb = sort_buffers(ctx);
-        k0_child_keys_kernel<<<grid_for(ctx->E, 256), 256, 0, st>>>(ts, sb.keys[0], sb.vals[0]);
-        ctx->launches++;
-        int cur = device_radix_sort(sb, ctx->E, st, &ctx->launches, nullptr);
+        MSPB_LAUNCH(ctx->log, "k0_child_keys", k0_child_keys_kernel<<<grid_for(ctx->E, 256), 256, 0, st>>>(ts, sb.keys[0], sb.vals[0]));
+        int cur = device_radix_sort(sb, ctx->E, st, ctx->log, nullptr);
         if (cur != 0) {
             std::swap(sb.keys[0], sb.keys[1]);
             std::swap(sb.vals[0], sb.vals[1]);
         }
-        k0_child_keys2_kernel<<<grid_for(ctx->E, 256), 256, 0, st>>>(ts, sb.vals[0], sb.keys[0]);
-        ctx->launches++;
-        cur = device_radix_sort(sb, ctx->E, st, &ctx->launches, nullptr);
-        k0_permute_kernel<<<grid_for(ctx->E, 256), 256, 0, st>>>(
-            ts, sb.vals[cur], ctx->ci_left.p, ctx->ci_right.p, ctx->ci_parent.p, ctx->child_start.p);
-        ctx->launches++;
+        MSPB_LAUNCH(ctx->log, "k0_child_keys2", k0_child_keys2_kernel<<<grid_for(ctx->E, 256), 256, 0, st>>>(ts, sb.vals[0], sb.keys[0]));
+        cur = device_radix_sort(sb, ctx->E, st, ctx->log, nullptr);
+        MSPB_LAUNCH(ctx->log, "k0_permute", k0_permute_kernel<<<grid_for(ctx->E, 256), 256, 0, st>>>(
+            ts, sb.vals[cur], ctx->ci_left.p, ctx->ci_right.p, ctx->ci_parent.p, ctx->child_start.p));
     }
     CUDA_OK(cudaStreamSynchronize(st));
     CUDA_OK(cudaGetLastError());
+    ctx->log.collect();
     ctx->tables_loaded = true;
     return 0;
 }
@@ -793,14 +825,12 @@ extern "C" int mspb_generate(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_count
         TRY(ctx->k_site_allele.ensure(S0 + 1));
         TRY(ctx->k_mut_allele.ensure(M0 + 1));
         if (S0 > 0) {
-            kept_allele_index_kernel<<<grid_for(S0, 256), 256, 0, st>>>(
-                model, S0, ctx->k_site_anc.p, ctx->k_site_anc_off.p, ctx->k_site_allele.p);
-            ctx->launches++;
+            MSPB_LAUNCH(ctx->log, "kept_allele_index", kept_allele_index_kernel<<<grid_for(S0, 256), 256, 0, st>>>(
+                model, S0, ctx->k_site_anc.p, ctx->k_site_anc_off.p, ctx->k_site_allele.p));
         }
         if (M0 > 0) {
-            kept_allele_index_kernel<<<grid_for(M0, 256), 256, 0, st>>>(
-                model, M0, ctx->k_mut_der.p, ctx->k_mut_der_off.p, ctx->k_mut_allele.p);
-            ctx->launches++;
+            MSPB_LAUNCH(ctx->log, "kept_allele_index", kept_allele_index_kernel<<<grid_for(M0, 256), 256, 0, st>>>(
+                model, M0, ctx->k_mut_der.p, ctx->k_mut_der_off.p, ctx->k_mut_allele.p));
         }
     }
     KeptView kept = make_kept_view(ctx, keep);
@@ -819,15 +849,14 @@ extern "C" int mspb_generate(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_count
             TRY(ctx->loff.ensure(ctx->E + 1));
         }
         if (ctx->E > 0) {
-            k1_count_kernel<<<grid_for(ctx->E, 256), 256, 0, st>>>(ts, map, call, ctx->count.p, ctx->local.p);
-            ctx->launches++;
+            MSPB_LAUNCH(ctx->log, "k1_count", k1_count_kernel<<<grid_for(ctx->E, 256), 256, 0, st>>>(ts, map, call, ctx->count.p, ctx->local.p));
             const uint32_t *c = ctx->count.p;
-            ctx->launches += device_exclusive_scan<uint32_t>(
+            device_exclusive_scan<uint32_t>(ctx->log,
                 ctx->E, [c] __device__(uint64_t i) { return c[i]; }, ctx->goff.p, ctx->scan_tiles32.p,
                 &dt->count_total, st);
             if (sliced) {
                 const uint32_t *l = ctx->local.p;
-                ctx->launches += device_exclusive_scan<uint32_t>(
+                device_exclusive_scan<uint32_t>(ctx->log,
                     ctx->E, [l] __device__(uint64_t i) { return l[i]; }, ctx->loff.p, ctx->scan_tiles32.p,
                     &dt->local_total, st);
             }
@@ -849,8 +878,7 @@ extern "C" int mspb_generate(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_count
         pairs.out_off = ctx->rp_out_off.p;
         pairs.stream_off = ctx->rp_stream_off.p;
         pairs.capacity = cap;
-        replay_resolve_kernel<<<1, 32, 0, st>>>(ts, map, call, ctx->replay.p, p->replay_len, pairs, &dt->replay, &dt->err);
-        ctx->launches++;
+        MSPB_LAUNCH(ctx->log, "replay_resolve", replay_resolve_kernel<<<1, 32, 0, st>>>(ts, map, call, ctx->replay.p, p->replay_len, pairs, &dt->replay, &dt->err));
         CUDA_OK(cudaMemcpyAsync(ht, dt, sizeof(HostTotals), cudaMemcpyDeviceToHost, st));
         CUDA_OK(cudaStreamSynchronize(st));
         if (ht->err != 0) {
@@ -876,27 +904,27 @@ extern "C" int mspb_generate(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_count
     TRY(ensure_sort_buffers(ctx, R));
     RadixSortBuffers sb = sort_buffers(ctx);
     if (S0 + M0 > 0) {
-        fill_kept_kernel<<<grid_for(S0 + M0, 256), 256, 0, st>>>(
-            kept, call, ctx->rec_pos.p, ctx->rec_time.p, ctx->rec_node.p, sb.keys[0], sb.vals[0], &dt->err);
-        ctx->launches++;
+        MSPB_LAUNCH(ctx->log, "fill_kept", fill_kept_kernel<<<grid_for(S0 + M0, 256), 256, 0, st>>>(
+            kept, call, ctx->rec_pos.p, ctx->rec_time.p, ctx->rec_node.p, sb.keys[0], sb.vals[0], &dt->err));
     }
     if (Mnew > 0) {
         if (!replay) {
-            k2_place_kernel<<<grid_for(ctx->E, 256), 256, 0, st>>>(ts, map, call, ctx->count.p, ctx->goff.p,
-                sliced ? ctx->loff.p : ctx->goff.p, (uint32_t) (S0 + M0), ctx->rec_pos.p, ctx->rec_time.p,
-                ctx->rec_node.p, ctx->rec_ord.p, sb.keys[0], sb.vals[0]);
+            MSPB_LAUNCH(ctx->log, "k2_place",
+                k2_place_kernel<<<grid_for(ctx->E, 256), 256, 0, st>>>(ts, map, call, ctx->count.p, ctx->goff.p,
+                    sliced ? ctx->loff.p : ctx->goff.p, (uint32_t) (S0 + M0), ctx->rec_pos.p, ctx->rec_time.p,
+                    ctx->rec_node.p, ctx->rec_ord.p, sb.keys[0], sb.vals[0]));
         } else {
-            replay_place_kernel<<<grid_for(num_pairs, 128), 128, 0, st>>>(ts, map, call, ctx->replay.p, pairs, num_pairs,
-                (uint32_t) (S0 + M0), ctx->rec_pos.p, ctx->rec_time.p, ctx->rec_node.p, ctx->rec_ord.p, sb.keys[0],
-                sb.vals[0], &dt->err);
+            MSPB_LAUNCH(ctx->log, "replay_place",
+                replay_place_kernel<<<grid_for(num_pairs, 128), 128, 0, st>>>(ts, map, call, ctx->replay.p, pairs,
+                    num_pairs, (uint32_t) (S0 + M0), ctx->rec_pos.p, ctx->rec_time.p, ctx->rec_node.p, ctx->rec_ord.p,
+                    sb.keys[0], sb.vals[0], &dt->err));
         }
-        ctx->launches++;
     }
 
     // ---- K3: order all records by (position, time descending)
     CUDA_OK(cudaEventRecord(ctx->ev[3], st));
     int sort_passes = 0;
-    const int cur = device_radix_sort(sb, R, st, &ctx->launches, &sort_passes);
+    const int cur = device_radix_sort(sb, R, st, ctx->log, &sort_passes);
 
     // ---- exact order inside equal-key runs, site boundaries, row numbers
     CUDA_OK(cudaEventRecord(ctx->ev[4], st));
@@ -944,17 +972,17 @@ extern "C" int mspb_generate(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_count
     evw.model = model;
     if (R > 0) {
         if (R > 1) {
-            finalize_runs_kernel<<<grid_for(R, 256), 256, 0, st>>>(sv);
-            post_sort_check_kernel<<<grid_for(R, 256), 256, 0, st>>>(sv, call.discrete, &dt->collisions, &dt->err);
-            ctx->launches += 2;
+            MSPB_LAUNCH(ctx->log, "finalize_runs", finalize_runs_kernel<<<grid_for(R, 256), 256, 0, st>>>(sv));
+            MSPB_LAUNCH(ctx->log, "post_sort_check",
+                post_sort_check_kernel<<<grid_for(R, 256), 256, 0, st>>>(sv, call.discrete, &dt->collisions, &dt->err));
         }
-        ctx->launches += device_exclusive_scan<uint32_t>(
+        device_exclusive_scan<uint32_t>(ctx->log,
             R, [evw] __device__(uint64_t i) { return evw.head(i) ? 1u : 0u; }, ctx->site_scan.p, ctx->scan_tiles32.p,
             &dt->num_sites, st);
-        ctx->launches += device_exclusive_scan<uint32_t>(
+        device_exclusive_scan<uint32_t>(ctx->log,
             R, [evw] __device__(uint64_t i) { return evw.is_mut(i) ? 1u : 0u; }, ctx->mut_scan.p, ctx->scan_tiles32.p,
             &dt->num_mut_rows, st);
-        ctx->launches += device_exclusive_scan<uint32_t>(
+        device_exclusive_scan<uint32_t>(ctx->log,
             R, [evw] __device__(uint64_t i) { return (evw.is_new(i) ? 1u : 0u) + (evw.new_site(i) ? 1u : 0u); },
             ctx->draw_scan.p, ctx->scan_tiles32.p, &dt->num_draws, st);
     }
@@ -962,23 +990,23 @@ extern "C" int mspb_generate(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_count
     // ---- K4: parents and alleles, one site at a time
     CUDA_OK(cudaEventRecord(ctx->ev[5], st));
     if (R > 0) {
-        k4_resolve_kernel<<<grid_for(R, 128), 128, 0, st>>>(ts, kept, model, call, sv, rv, &dt->err);
-        ctx->launches++;
+        MSPB_LAUNCH(ctx->log, "k4_resolve",
+            k4_resolve_kernel<<<grid_for(R, 128), 128, 0, st>>>(ts, kept, model, call, sv, rv, &dt->err));
     }
 
     // ---- ragged column offsets
     CUDA_OK(cudaEventRecord(ctx->ev[6], st));
     if (R > 0) {
-        ctx->launches += device_exclusive_scan<uint64_t>(
+        device_exclusive_scan<uint64_t>(ctx->log,
             R, [evw] __device__(uint64_t i) { return evw.der_len(i); }, ctx->der_scan.p, ctx->scan_tiles64.p,
             &dt->der_bytes, st);
-        ctx->launches += device_exclusive_scan<uint64_t>(
+        device_exclusive_scan<uint64_t>(ctx->log,
             R, [evw] __device__(uint64_t i) { return evw.mut_md_len(i); }, ctx->mmd_scan.p, ctx->scan_tiles64.p,
             &dt->mmd_bytes, st);
-        ctx->launches += device_exclusive_scan<uint64_t>(
+        device_exclusive_scan<uint64_t>(ctx->log,
             R, [evw] __device__(uint64_t i) { return evw.anc_len(i); }, ctx->anc_scan.p, ctx->scan_tiles64.p,
             &dt->anc_bytes, st);
-        ctx->launches += device_exclusive_scan<uint64_t>(
+        device_exclusive_scan<uint64_t>(ctx->log,
             R, [evw] __device__(uint64_t i) { return evw.site_md_len(i); }, ctx->smd_scan.p, ctx->scan_tiles64.p,
             &dt->smd_bytes, st);
     }
@@ -1026,15 +1054,14 @@ extern "C" int mspb_generate(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_count
     out.mut_md = ctx->o_mut_md.p;
     out.mut_md_off = ctx->o_mut_md_off.p;
     if (R > 0) {
-        k5_emit_kernel<<<grid_for(R, 256), 256, 0, st>>>(
-            evw, out, ctx->der_scan.p, ctx->mmd_scan.p, ctx->anc_scan.p, ctx->smd_scan.p);
-        ctx->launches++;
+        MSPB_LAUNCH(ctx->log, "k5_emit", k5_emit_kernel<<<grid_for(R, 256), 256, 0, st>>>(
+            evw, out, ctx->der_scan.p, ctx->mmd_scan.p, ctx->anc_scan.p, ctx->smd_scan.p));
     }
-    write_final_offsets_kernel<<<1, 1, 0, st>>>(out, S, M, ht->anc_bytes, ht->smd_bytes, ht->der_bytes, ht->mmd_bytes);
-    ctx->launches++;
+    MSPB_LAUNCH(ctx->log, "write_final_offsets", write_final_offsets_kernel<<<1, 1, 0, st>>>(out, S, M, ht->anc_bytes, ht->smd_bytes, ht->der_bytes, ht->mmd_bytes));
     CUDA_OK(cudaEventRecord(ctx->ev[8], st));
     CUDA_OK(cudaStreamSynchronize(st));
     CUDA_OK(cudaGetLastError());
+    ctx->log.collect();
     float total = 0;
     for (int i = 0; i < MSPB_NUM_PHASES; i++) {
         cudaEventElapsedTime(&ctx->phase_ms[i], ctx->ev[i], ctx->ev[i + 1]);

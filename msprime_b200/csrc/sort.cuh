@@ -133,19 +133,18 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_apply_kernel(uint64_t n, F 
 // tile_sums must hold ceil(n / SCAN_TILE) entries.  Launches 3 kernels (0 if n == 0,
 // in which case *total_out is set by a memset).
 template <typename T, typename F>
-inline int device_exclusive_scan(uint64_t n, F f, T *out, T *tile_sums, T *total_out, cudaStream_t st)
+inline void device_exclusive_scan(LaunchLog &log, uint64_t n, F f, T *out, T *tile_sums, T *total_out, cudaStream_t st)
 {
     if (n == 0) {
         if (total_out != nullptr) {
             cudaMemsetAsync(total_out, 0, sizeof(T), st);
         }
-        return 0;
+        return;
     }
     const uint32_t tiles = (uint32_t) ((n + SCAN_TILE - 1) / SCAN_TILE);
-    scan_tile_sums_kernel<T, F><<<tiles, SCAN_THREADS, 0, st>>>(n, f, tile_sums);
-    scan_spine_kernel<T><<<1, SCAN_THREADS, 0, st>>>(tiles, tile_sums, total_out);
-    scan_apply_kernel<T, F><<<tiles, SCAN_THREADS, 0, st>>>(n, f, tile_sums, out);
-    return 3;
+    MSPB_LAUNCH(log, "scan_tile_sums", scan_tile_sums_kernel<T, F><<<tiles, SCAN_THREADS, 0, st>>>(n, f, tile_sums));
+    MSPB_LAUNCH(log, "scan_spine", scan_spine_kernel<T><<<1, SCAN_THREADS, 0, st>>>(tiles, tile_sums, total_out));
+    MSPB_LAUNCH(log, "scan_apply", scan_apply_kernel<T, F><<<tiles, SCAN_THREADS, 0, st>>>(n, f, tile_sums, out));
 }
 
 inline uint64_t scan_num_tiles(uint64_t n)
@@ -283,7 +282,7 @@ inline uint32_t rs_num_tiles(uint64_t n)
 // Sorts n (key, val) pairs held in buf.keys[0] / buf.vals[0]; returns the index
 // (0 or 1) of the buffer holding the result.  *launches is incremented by the
 // number of kernels launched.  Synchronises the stream once (to read the bit mask).
-inline int device_radix_sort(RadixSortBuffers &buf, uint64_t n, cudaStream_t st, uint64_t *launches, int *passes_out)
+inline int device_radix_sort(RadixSortBuffers &buf, uint64_t n, cudaStream_t st, LaunchLog &log, int *passes_out)
 {
     if (passes_out != nullptr) {
         *passes_out = 0;
@@ -293,10 +292,9 @@ inline int device_radix_sort(RadixSortBuffers &buf, uint64_t n, cudaStream_t st,
     }
     const uint64_t init[2] = { 0ull, ~0ull };
     cudaMemcpyAsync(buf.or_and, init, sizeof(init), cudaMemcpyHostToDevice, st);
-    rs_key_bits_kernel<<<148 * 4, 256, 0, st>>>(buf.keys[0], n, buf.or_and);
+    MSPB_LAUNCH(log, "rs_key_bits", rs_key_bits_kernel<<<148 * 4, 256, 0, st>>>(buf.keys[0], n, buf.or_and));
     cudaMemcpyAsync(buf.or_and_host, buf.or_and, 2 * sizeof(uint64_t), cudaMemcpyDeviceToHost, st);
     cudaStreamSynchronize(st);
-    *launches += 1;
     const uint64_t varying = buf.or_and_host[0] & ~buf.or_and_host[1];
     const uint32_t tiles = rs_num_tiles(n);
     int cur = 0;
@@ -305,14 +303,15 @@ inline int device_radix_sort(RadixSortBuffers &buf, uint64_t n, cudaStream_t st,
         if (((varying >> shift) & 0xffull) == 0) {
             continue;
         }
-        rs_hist_kernel<<<tiles, RS_THREADS, 0, st>>>(buf.keys[cur], n, shift, tiles, buf.tile_hist);
+        MSPB_LAUNCH(log, "rs_hist",
+            rs_hist_kernel<<<tiles, RS_THREADS, 0, st>>>(buf.keys[cur], n, shift, tiles, buf.tile_hist));
         const uint32_t *th = buf.tile_hist;
-        *launches += 1 + device_exclusive_scan<uint32_t>(
-            (uint64_t) RS_BINS * tiles, [th] __device__(uint64_t i) { return th[i]; }, buf.tile_hist, buf.scan_tiles,
-            (uint32_t *) nullptr, st);
-        rs_scatter_kernel<<<tiles, RS_THREADS, 0, st>>>(
-            buf.keys[cur], buf.vals[cur], buf.keys[cur ^ 1], buf.vals[cur ^ 1], n, shift, tiles, buf.tile_hist);
-        *launches += 1;
+        device_exclusive_scan<uint32_t>(
+            log, (uint64_t) RS_BINS * tiles, [th] __device__(uint64_t i) { return th[i]; }, buf.tile_hist,
+            buf.scan_tiles, (uint32_t *) nullptr, st);
+        MSPB_LAUNCH(log, "rs_scatter",
+            rs_scatter_kernel<<<tiles, RS_THREADS, 0, st>>>(
+                buf.keys[cur], buf.vals[cur], buf.keys[cur ^ 1], buf.vals[cur ^ 1], n, shift, tiles, buf.tile_hist));
         cur ^= 1;
         if (passes_out != nullptr) {
             (*passes_out)++;
