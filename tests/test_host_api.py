@@ -1,0 +1,142 @@
+"""CPU: the Python surface (models, RateMap, argument handling) mirrors the reference's
+behaviour (msprime/mutations.py, msprime/intervals.py; tests/test_mutations.py:271-335,
+686-835).  Nothing here needs a GPU: every check fails before the device call."""
+import numpy as np
+import pytest
+
+import cases
+import msprime_b200 as msp
+from msprime_b200 import tables as mtables
+
+
+def light_ts(d):
+    return mtables.TableCollection.fromdict(d).tree_sequence()
+
+
+def test_jc69_matrix():
+    m = msp.JC69()
+    assert m.alleles == ["A", "C", "G", "T"]
+    assert np.array_equal(m.root_distribution, [0.25] * 4)
+    want = np.full((4, 4), 1 / 3)
+    np.fill_diagonal(want, 0)
+    assert np.array_equal(m.transition_matrix, want)
+    assert np.array_equal(msp.JC69(state_independent=True).transition_matrix, np.full((4, 4), 0.25))
+
+
+def test_binary_model():
+    m = msp.BinaryMutationModel()
+    assert m.alleles == ["0", "1"]
+    assert np.array_equal(m.root_distribution, [1, 0])
+    assert np.array_equal(m.transition_matrix, [[0, 1], [1, 0]])
+
+
+def test_hky_rows_and_kappa():
+    # tests/test_mutations.py:271-300: rows sum to one, transitions kappa times transversions
+    freqs = [0.3, 0.2, 0.2, 0.3]
+    m = msp.HKY(kappa=2.0, equilibrium_frequencies=freqs)
+    P = m.transition_matrix
+    assert np.allclose(P.sum(axis=1), 1.0, atol=1e-15)
+    assert np.isclose(P[0, 2] / freqs[2], 2 * P[0, 1] / freqs[1])
+    assert np.array_equal(m.root_distribution, freqs)
+
+
+def test_gtr_reversible():
+    freqs = np.array([0.3, 0.2, 0.2, 0.3])
+    m = msp.GTR(relative_rates=[1, 2, 1, 1, 2, 1], equilibrium_frequencies=freqs)
+    P = m.transition_matrix
+    assert np.allclose(P.sum(axis=1), 1.0, atol=1e-15)
+    flow = freqs[:, None] * P
+    off = ~np.eye(4, dtype=bool)
+    assert np.allclose(flow[off], flow.T[off])
+
+
+def test_f84_is_stochastic():
+    P = msp.F84(kappa=1.5, equilibrium_frequencies=[0.1, 0.2, 0.3, 0.4]).transition_matrix
+    assert np.allclose(P.sum(axis=1), 1.0) and (P >= 0).all()
+
+
+@pytest.mark.parametrize("alleles,root,matrix,status", [
+    (["A"], [1.0], [[1.0]], -52),
+    (["A", "B"], [0.5, 0.6], [[0.5, 0.5], [0.5, 0.5]], -53),
+    (["A", "B"], [-0.5, 1.5], [[0.5, 0.5], [0.5, 0.5]], -53),
+    (["A", "B"], [0.5, 0.5], [[0.5, 0.6], [0.5, 0.5]], -54),
+])
+def test_matrix_model_validation(alleles, root, matrix, status):
+    # lib/mutgen.c:501-524, lib/tests/test_mutations.c:1152-1265
+    with pytest.raises(msp.LibraryError) as e:
+        msp.MatrixMutationModel(alleles, root, matrix)
+    assert e.value.status == status
+
+
+def test_matrix_model_shape_errors():
+    with pytest.raises(ValueError):
+        msp.MatrixMutationModel(["A", "B"], [1.0], [[0.5, 0.5], [0.5, 0.5]])
+    with pytest.raises(ValueError):
+        msp.MatrixMutationModel(["A", "B"], [0.5, 0.5], [[0.5, 0.5]])
+    with pytest.raises(TypeError):
+        msp.MatrixMutationModel("AB", [0.5, 0.5], [[0.5, 0.5], [0.5, 0.5]])
+
+
+def test_model_factory():
+    assert isinstance(msp.mutation_model_factory(None), msp.JC69)
+    assert isinstance(msp.mutation_model_factory("binary"), msp.BinaryMutationModel)
+    assert isinstance(msp.mutation_model_factory("JC69"), msp.JC69)
+    assert isinstance(msp.mutation_model_factory("infinite_alleles"), msp.InfiniteAlleles)
+    m = msp.JC69()
+    assert msp.mutation_model_factory(m) is m
+    with pytest.raises(ValueError):
+        msp.mutation_model_factory("nope")
+    with pytest.raises(TypeError):
+        msp.mutation_model_factory(3)
+
+
+def test_rate_map_validation():
+    # msprime/intervals.py:61-87
+    r = msp.RateMap(position=[0, 5, 10], rate=[1, 2])
+    assert r.sequence_length == 10 and r.num_intervals == 2
+    assert np.array_equal(r.asdict()["position"], [0, 5, 10])
+    for bad in (dict(position=[1, 10], rate=[1]), dict(position=[0, 5, 5], rate=[1, 1]),
+                dict(position=[0, 10], rate=[-1]), dict(position=[0], rate=[]),
+                dict(position=[0, 10], rate=[1, 2]), dict(position=[0, 10], rate=[np.nan])):
+        with pytest.raises(ValueError):
+            msp.RateMap(**bad)
+    u = msp.RateMap.uniform(100, 0.5)
+    assert np.array_equal(u.position, [0, 100]) and np.array_equal(u.rate, [0.5])
+
+
+def test_sim_mutations_argument_errors():
+    # msprime/mutations.py:1637-1684; tests/test_mutations.py:686-835
+    ts = light_ts(cases.four_leaf_tree())
+    with pytest.raises(ValueError):
+        msp.sim_mutations("not a tree sequence", rate=1)
+    with pytest.raises(TypeError):
+        msp.sim_mutations(ts, rate=[1.0, 2.0])
+    with pytest.raises(ValueError):
+        msp.sim_mutations(ts, rate=1, start_time=2, end_time=1)
+    with pytest.raises(TypeError):
+        msp.sim_mutations(ts, rate=1, keep=1)
+    with pytest.raises(TypeError):
+        msp.sim_mutations(ts, rate=1, discrete_genome="yes")
+    with pytest.raises(ValueError):
+        msp.sim_mutations(ts, rate=1, model="nope")
+    with pytest.raises(ValueError):
+        msp.sim_mutations(ts, rate=1, random_seed=0)
+    with pytest.raises(ValueError):
+        msp.sim_mutations(ts, rate=1, random_seed=2**32)
+    d = cases.four_leaf_tree()
+    d["time_units"] = "uncalibrated"
+    with pytest.raises(ValueError):
+        msp.sim_mutations(light_ts(d), rate=1)
+
+
+def test_mutate_rejects_general_models():
+    ts = light_ts(cases.four_leaf_tree())
+    with pytest.raises(ValueError):
+        msp.mutate(ts, rate=1, model=msp.JC69())
+
+
+def test_infinite_alleles_start():
+    m = msp.InfiniteAlleles(start_allele=7)
+    assert m.start_allele == 7 and m.next_allele == 7
+    with pytest.raises(OverflowError):
+        msp.InfiniteAlleles(start_allele=-1)
