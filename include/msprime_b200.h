@@ -185,6 +185,12 @@ int mspb_kernel_time(const mspb_ctx_t *ctx, int index, const char **name, uint64
 int mspb_phase_ms(const mspb_ctx_t *ctx, float *ms, int n);
 const char *mspb_phase_name(int phase);
 
+/* Diagnostic: sorts n pseudo-random keys (key_bytes 4 or 8, masked with key_mask) with
+ * the library's device radix sort and checks order, stability and payload on the host.
+ * measure_bits != 0 lets the sort measure the varying bits itself.  0 = pass. */
+int mspb_selftest_sort(mspb_ctx_t *ctx, uint64_t n, int key_bytes, uint64_t key_mask, uint64_t seed,
+    int measure_bits, int *passes);
+
 /* One-shot form with the semantics of _msprime.sim_mutations: host tables in,
  * malloc'd host columns out (release with mspb_columns_free). */
 int mspb_sim_mutations(int device, const mspb_tables_t *tables, const mspb_params_t *params,

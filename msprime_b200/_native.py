@@ -100,7 +100,7 @@ EXPORTED_SYMBOLS = [
     "mspb_ctx_create", "mspb_ctx_destroy", "mspb_ctx_load_tables", "mspb_generate", "mspb_fetch",
     "mspb_device_columns", "mspb_kernel_launches", "mspb_phase_ms", "mspb_phase_name",
     "mspb_sim_mutations", "mspb_columns_free", "mspb_strerror", "mspb_version",
-    "mspb_ctx_stream", "mspb_kernel_timing", "mspb_kernel_time",
+    "mspb_ctx_stream", "mspb_kernel_timing", "mspb_kernel_time", "mspb_selftest_sort",
 ]
 
 _lib = None
@@ -130,6 +130,8 @@ def lib():
         L.mspb_strerror.argtypes = [C.c_int]
         L.mspb_strerror.restype = C.c_char_p
         L.mspb_version.restype = C.c_char_p
+        L.mspb_selftest_sort.argtypes = [C.c_void_p, C.c_uint64, C.c_int, C.c_uint64, C.c_uint64, C.c_int,
+                                         C.POINTER(C.c_int)]
         L.mspb_ctx_stream.argtypes = [C.c_void_p]
         L.mspb_ctx_stream.restype = C.c_void_p
         L.mspb_kernel_timing.argtypes = [C.c_void_p, C.c_int]
@@ -310,6 +312,13 @@ class Context:
 
     def kernel_launches(self) -> int:
         return int(lib().mspb_kernel_launches(self._h))
+
+    def selftest_sort(self, n, key_bytes=8, key_mask=0xFFFFFFFFFFFFFFFF, seed=1, measure_bits=True):
+        """Runs the device radix sort on random keys and verifies it; returns the pass count."""
+        passes = C.c_int(0)
+        check(lib().mspb_selftest_sort(self._h, int(n), int(key_bytes), int(key_mask) & 0xFFFFFFFFFFFFFFFF,
+                                       int(seed), int(bool(measure_bits)), C.byref(passes)))
+        return passes.value
 
     def stream(self) -> int:
         """The context's cudaStream_t as an integer (wrap with ``torch.cuda.ExternalStream``)."""

@@ -468,20 +468,21 @@ int ensure_sort_buffers(mspb_ctx *ctx, uint64_t n)
     TRY(ctx->keys1.ensure(n + 1));
     TRY(ctx->vals0.ensure(n + 1));
     TRY(ctx->vals1.ensure(n + 1));
-    TRY(ctx->tile_hist.ensure(RS_BINS * tiles));
-    TRY(ctx->rs_scan_tiles.ensure(scan_num_tiles(RS_BINS * tiles) + 1));
+    TRY(ctx->tile_hist.ensure((size_t) RS_MAX_PASSES * RS_BINS));
+    TRY(ctx->rs_scan_tiles.ensure(rs_state_words(n)));
+    (void) tiles;
     return 0;
 }
 
-RadixSortBuffers sort_buffers(mspb_ctx *ctx)
+RadixSortBuffers<uint64_t> sort_buffers(mspb_ctx *ctx)
 {
-    RadixSortBuffers b;
+    RadixSortBuffers<uint64_t> b;
     b.keys[0] = ctx->keys0.p;
     b.keys[1] = ctx->keys1.p;
     b.vals[0] = ctx->vals0.p;
     b.vals[1] = ctx->vals1.p;
-    b.tile_hist = ctx->tile_hist.p;
-    b.scan_tiles = ctx->rs_scan_tiles.p;
+    b.hist = ctx->tile_hist.p;
+    b.tile_state = ctx->rs_scan_tiles.p;
     b.or_and = ctx->or_and.p;
     b.or_and_host = ctx->or_and_host;
     return b;
@@ -590,15 +591,15 @@ extern "C" int mspb_ctx_load_tables(mspb_ctx_t *ctx, const mspb_tables_t *t)
         CUDA_OK(cudaMemsetAsync(ctx->child_start.p, 0, (ctx->N + 2) * sizeof(uint32_t), st));
     } else {
         TRY(ensure_sort_buffers(ctx, ctx->E));
-        RadixSortBuffers sb = sort_buffers(ctx);
+        RadixSortBuffers<uint64_t> sb = sort_buffers(ctx);
         MSPB_LAUNCH(ctx->log, "k0_child_keys", k0_child_keys_kernel<<<grid_for(ctx->E, 256), 256, 0, st>>>(ts, sb.keys[0], sb.vals[0]));
-        int cur = device_radix_sort(sb, ctx->E, st, ctx->log, nullptr);
+        int cur = device_radix_sort<uint64_t>(sb, ctx->E, 0, false, st, ctx->log, nullptr);
         if (cur != 0) {
             std::swap(sb.keys[0], sb.keys[1]);
             std::swap(sb.vals[0], sb.vals[1]);
         }
         MSPB_LAUNCH(ctx->log, "k0_child_keys2", k0_child_keys2_kernel<<<grid_for(ctx->E, 256), 256, 0, st>>>(ts, sb.vals[0], sb.keys[0]));
-        cur = device_radix_sort(sb, ctx->E, st, ctx->log, nullptr);
+        cur = device_radix_sort<uint64_t>(sb, ctx->E, 0, false, st, ctx->log, nullptr);
         MSPB_LAUNCH(ctx->log, "k0_permute", k0_permute_kernel<<<grid_for(ctx->E, 256), 256, 0, st>>>(
             ts, sb.vals[cur], ctx->ci_left.p, ctx->ci_right.p, ctx->ci_parent.p, ctx->child_start.p));
     }
@@ -891,7 +892,7 @@ extern "C" int mspb_generate(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_count
         num_pairs = ht->replay.num_pairs;
     }
     const uint64_t R = S0 + M0 + Mnew;
-    if (R > 0x7fffffffull) {
+    if (R > RS_MAX_N) {
         return MSPB_ERR_TOO_MANY_ROWS;
     }
 
@@ -902,7 +903,7 @@ extern "C" int mspb_generate(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_count
     TRY(ctx->rec_node.ensure(R + 1));
     TRY(ctx->rec_ord.ensure(Mnew + 1));
     TRY(ensure_sort_buffers(ctx, R));
-    RadixSortBuffers sb = sort_buffers(ctx);
+    RadixSortBuffers<uint64_t> sb = sort_buffers(ctx);
     if (S0 + M0 > 0) {
         MSPB_LAUNCH(ctx->log, "fill_kept", fill_kept_kernel<<<grid_for(S0 + M0, 256), 256, 0, st>>>(
             kept, call, ctx->rec_pos.p, ctx->rec_time.p, ctx->rec_node.p, sb.keys[0], sb.vals[0], &dt->err));
@@ -924,7 +925,7 @@ extern "C" int mspb_generate(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_count
     // ---- K3: order all records by (position, time descending)
     CUDA_OK(cudaEventRecord(ctx->ev[3], st));
     int sort_passes = 0;
-    const int cur = device_radix_sort(sb, R, st, ctx->log, &sort_passes);
+    const int cur = device_radix_sort<uint64_t>(sb, R, 0, false, st, ctx->log, &sort_passes);
 
     // ---- exact order inside equal-key runs, site boundaries, row numbers
     CUDA_OK(cudaEventRecord(ctx->ev[4], st));
@@ -1217,4 +1218,81 @@ extern "C" int mspb_sim_mutations(int device, const mspb_tables_t *tables, const
     }
     mspb_ctx_destroy(ctx);
     return ret;
+}
+
+// ---------------------------------------------------------------- diagnostics
+namespace {
+
+template <typename KeyT>
+int selftest_sort_impl(mspb_ctx *ctx, uint64_t n, uint64_t key_mask, uint64_t seed, bool measure_bits, int *passes)
+{
+    cudaStream_t st = ctx->stream;
+    std::vector<KeyT> h(n > 0 ? n : 1);
+    uint64_t x = seed;
+    for (uint64_t i = 0; i < n; i++) {
+        x += 0x9E3779B97F4A7C15ull;
+        uint64_t z = x;
+        z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+        z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+        z ^= z >> 31;
+        h[i] = (KeyT) (z & key_mask);
+    }
+    DBuf<KeyT> k0, k1;
+    DBuf<uint32_t> v0, v1, hist, state;
+    int ret = 0;
+    if (k0.ensure(n + 1) || k1.ensure(n + 1) || v0.ensure(n + 1) || v1.ensure(n + 1)
+        || hist.ensure((size_t) RS_MAX_PASSES * RS_BINS) || state.ensure(rs_state_words(n))) {
+        ret = MSPB_ERR_NO_MEMORY;
+    }
+    if (ret == 0) {
+        cudaMemcpyAsync(k0.p, h.data(), n * sizeof(KeyT), cudaMemcpyHostToDevice, st);
+        RadixSortBuffers<KeyT> b;
+        b.keys[0] = k0.p;
+        b.keys[1] = k1.p;
+        b.vals[0] = v0.p;
+        b.vals[1] = v1.p;
+        b.hist = hist.p;
+        b.tile_state = state.p;
+        b.or_and = ctx->or_and.p;
+        b.or_and_host = ctx->or_and_host;
+        const int cur = device_radix_sort<KeyT>(b, n, measure_bits ? 0 : (key_mask != 0 ? key_mask : 1), true, st, ctx->log,
+            passes);
+        std::vector<KeyT> ok(n > 0 ? n : 1);
+        std::vector<uint32_t> ov(n > 0 ? n : 1);
+        cudaMemcpyAsync(ok.data(), b.keys[cur], n * sizeof(KeyT), cudaMemcpyDeviceToHost, st);
+        cudaMemcpyAsync(ov.data(), b.vals[cur], n * sizeof(uint32_t), cudaMemcpyDeviceToHost, st);
+        if (cudaStreamSynchronize(st) != cudaSuccess || cudaGetLastError() != cudaSuccess) {
+            ret = MSPB_ERR_CUDA;
+        }
+        ctx->log.collect();
+        for (uint64_t i = 0; i < n && ret == 0; i++) {
+            if (ov[i] >= n || h[ov[i]] != ok[i]) {
+                ret = MSPB_ERR_GENERIC; // payload does not travel with its key
+            } else if (i > 0 && (ok[i - 1] > ok[i] || (ok[i - 1] == ok[i] && ov[i - 1] >= ov[i]))) {
+                ret = MSPB_ERR_GENERIC; // not sorted, or not stable
+            }
+        }
+    }
+    k0.release();
+    k1.release();
+    v0.release();
+    v1.release();
+    hist.release();
+    state.release();
+    return ret;
+}
+
+} // namespace
+
+extern "C" int mspb_selftest_sort(mspb_ctx_t *ctx, uint64_t n, int key_bytes, uint64_t key_mask, uint64_t seed,
+    int measure_bits, int *passes)
+{
+    if (ctx == nullptr || n > RS_MAX_N || (key_bytes != 4 && key_bytes != 8)) {
+        return MSPB_ERR_BAD_PARAM_VALUE;
+    }
+    CUDA_OK(cudaSetDevice(ctx->device));
+    if (key_bytes == 4) {
+        return selftest_sort_impl<uint32_t>(ctx, n, key_mask & 0xffffffffull, seed, measure_bits != 0, passes);
+    }
+    return selftest_sort_impl<uint64_t>(ctx, n, key_mask, seed, measure_bits != 0, passes);
 }

@@ -5,10 +5,12 @@
 // once by a 64-bit key (position, coarse time) with a 32-bit payload (record id).
 //
 // Layout: keys and payloads are separate SoA arrays, ping-ponged between passes.
-// Each pass handles one 8-bit digit with three launches: per-tile digit histogram,
-// one exclusive scan of the (digit-major) histogram matrix, and a stable scatter
-// that ranks keys with warp match-any.  Passes whose digit is constant over all
-// keys are skipped (the varying-bit mask comes from one OR/AND reduction).
+// One launch builds the digit histograms of every pass; then each pass is ONE
+// kernel ("onesweep"): a tile ranks its keys with warp match-any, publishes its
+// per-digit counts, obtains its global offsets by decoupled look-back over the
+// preceding tiles, stages the tile in shared memory in sorted order and writes
+// contiguous runs.  Digit widths are chosen per call (<= 8 bits) so that only the
+// bits that vary are sorted.
 #pragma once
 #include "common.cuh"
 
@@ -158,12 +160,83 @@ constexpr int RS_WARPS = RS_THREADS / 32;
 constexpr int RS_ITEMS = 16;
 constexpr int RS_TILE = RS_THREADS * RS_ITEMS;
 constexpr int RS_BINS = 256;
+constexpr int RS_MAX_PASSES = 8;
+// look-back word: 2 flag bits + 30-bit count
+constexpr uint32_t RS_FLAG_AGG = 1u << 30, RS_FLAG_INCL = 2u << 30, RS_COUNT_MASK = (1u << 30) - 1u;
+constexpr uint64_t RS_MAX_N = (1ull << 30) - 1ull;
 
-__global__ void __launch_bounds__(256) rs_key_bits_kernel(const uint64_t *__restrict__ keys, uint64_t n, uint64_t *or_and)
+struct RadixPlan {
+    int passes;
+    int shift[RS_MAX_PASSES];
+    int bits[RS_MAX_PASSES];
+};
+
+// Digits covering the set bits of `varying` (bit i set = bit i differs between keys),
+// at most 8 bits wide, as few passes as possible and as even as possible.
+inline RadixPlan radix_plan(uint64_t varying)
+{
+    RadixPlan p;
+    p.passes = 0;
+    int pos = 0;
+    while (pos < 64) {
+        while (pos < 64 && !((varying >> pos) & 1ull)) {
+            pos++;
+        }
+        if (pos >= 64) {
+            break;
+        }
+        // contiguous stretch [pos, end) up to the highest varying bit
+        int end = 64;
+        while (end > pos && !((varying >> (end - 1)) & 1ull)) {
+            end--;
+        }
+        // find a run of constant bits >= 8 wide to split on (skipping it saves a pass)
+        int gap_start = -1;
+        for (int i = pos, run = 0; i < end; i++) {
+            if (!((varying >> i) & 1ull)) {
+                run++;
+                if (run == 8) {
+                    gap_start = i - 7;
+                    break;
+                }
+            } else {
+                run = 0;
+            }
+        }
+        const int stretch_end = gap_start >= 0 ? gap_start : end;
+        const int width = stretch_end - pos;
+        const int np = (width + 7) / 8;
+        for (int k = 0; k < np; k++) {
+            const int lo = pos + (int) ((long long) width * k / np);
+            const int hi = pos + (int) ((long long) width * (k + 1) / np);
+            p.shift[p.passes] = lo;
+            p.bits[p.passes] = hi - lo;
+            p.passes++;
+        }
+        pos = stretch_end;
+    }
+    return p;
+}
+
+struct RadixPlanDev {
+    int passes;
+    int shift[RS_MAX_PASSES];
+    uint32_t mask[RS_MAX_PASSES];
+};
+
+template <typename KeyT>
+MSPB_DEVFN uint32_t rs_digit(KeyT k, int shift, uint32_t mask)
+{
+    return (uint32_t) (k >> shift) & mask;
+}
+
+// OR / AND of all keys (which bits vary)
+template <typename KeyT>
+__global__ void __launch_bounds__(256) rs_key_bits_kernel(const KeyT *__restrict__ keys, uint64_t n, uint64_t *or_and)
 {
     uint64_t o = 0, a = ~0ull;
     for (uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t) gridDim.x * blockDim.x) {
-        const uint64_t k = keys[i];
+        const uint64_t k = (uint64_t) keys[i];
         o |= k;
         a &= k;
     }
@@ -178,56 +251,78 @@ __global__ void __launch_bounds__(256) rs_key_bits_kernel(const uint64_t *__rest
     }
 }
 
-// tile_hist is digit-major: tile_hist[d * num_tiles + tile]
-__global__ void __launch_bounds__(RS_THREADS) rs_hist_kernel(const uint64_t *__restrict__ keys, uint64_t n, int shift,
-    uint32_t num_tiles, uint32_t *__restrict__ tile_hist)
+// Global digit histograms of every pass in one read of the keys:
+// hist[pass * RS_BINS + digit].
+template <typename KeyT>
+__global__ void __launch_bounds__(RS_THREADS) rs_global_hist_kernel(const KeyT *__restrict__ keys, uint64_t n,
+    RadixPlanDev plan, uint32_t *__restrict__ hist)
 {
-    __shared__ uint32_t hist[RS_BINS];
-    hist[threadIdx.x] = 0;
+    __shared__ uint32_t sh[RS_MAX_PASSES * RS_BINS];
+    for (int i = threadIdx.x; i < plan.passes * RS_BINS; i += RS_THREADS) {
+        sh[i] = 0;
+    }
     __syncthreads();
-    const uint64_t base = (uint64_t) blockIdx.x * RS_TILE;
-#pragma unroll
-    for (int k = 0; k < RS_ITEMS; k++) {
-        const uint64_t i = base + (uint64_t) k * RS_THREADS + threadIdx.x;
-        const bool valid = i < n;
-        const uint32_t d = valid ? (uint32_t) ((keys[i] >> shift) & 0xffu) : 0xffffffffu;
-        const uint32_t peers = __match_any_sync(0xffffffffu, d);
-        if (valid && (peers & ((1u << (threadIdx.x & 31)) - 1u)) == 0) {
-            atomicAdd(&hist[d], (uint32_t) __popc(peers));
+    const uint64_t stride = (uint64_t) gridDim.x * RS_THREADS;
+    for (uint64_t i = (uint64_t) blockIdx.x * RS_THREADS + threadIdx.x; i < n; i += stride) {
+        const KeyT k = keys[i];
+        for (int p = 0; p < plan.passes; p++) {
+            atomicAdd(&sh[p * RS_BINS + rs_digit(k, plan.shift[p], plan.mask[p])], 1u);
         }
     }
     __syncthreads();
-    tile_hist[(uint64_t) threadIdx.x * num_tiles + blockIdx.x] = hist[threadIdx.x];
+    for (int i = threadIdx.x; i < plan.passes * RS_BINS; i += RS_THREADS) {
+        const uint32_t c = sh[i];
+        if (c != 0) {
+            atomicAdd(&hist[i], c);
+        }
+    }
 }
 
-// Stable scatter.  Warp w of a tile owns the contiguous chunk [w*512, (w+1)*512) of
-// the tile; iteration k covers 32 consecutive keys, so element order is (warp,
-// iteration, lane) and ranks are accumulated in that order.
-__global__ void __launch_bounds__(RS_THREADS) rs_scatter_kernel(const uint64_t *__restrict__ keys_in,
-    const uint32_t *__restrict__ vals_in, uint64_t *__restrict__ keys_out, uint32_t *__restrict__ vals_out, uint64_t n,
-    int shift, uint32_t num_tiles, const uint32_t *__restrict__ tile_base)
+__global__ void __launch_bounds__(256) rs_iota_kernel(uint32_t *vals, uint64_t n)
+{
+    const uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) {
+        vals[i] = (uint32_t) i;
+    }
+}
+
+// One pass.  Warp w of a tile owns the contiguous chunk [w*512, (w+1)*512) of the tile
+// and iteration k covers 32 consecutive keys, so (warp, iteration, lane) order is index
+// order and ranks accumulated in that order make the pass stable.
+// vals_in == nullptr means the identity payload (first pass).
+template <typename KeyT>
+__global__ void __launch_bounds__(RS_THREADS) rs_onesweep_kernel(const KeyT *__restrict__ keys_in,
+    const uint32_t *__restrict__ vals_in, KeyT *__restrict__ keys_out, uint32_t *__restrict__ vals_out, uint64_t n,
+    int shift, uint32_t mask, const uint32_t *__restrict__ global_hist, volatile uint32_t *tile_state)
 {
     __shared__ uint32_t cnt[RS_WARPS][RS_BINS];
+    __shared__ uint32_t local_start[RS_BINS];
+    __shared__ uint32_t global_base[RS_BINS];
+    __shared__ uint32_t scan_tmp[9];
+    __shared__ KeyT stage[RS_TILE];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t tile = blockIdx.x;
 #pragma unroll
     for (int w = 0; w < RS_WARPS; w++) {
         cnt[w][threadIdx.x] = 0;
     }
     __syncthreads();
-    const uint64_t base = (uint64_t) blockIdx.x * RS_TILE + (uint64_t) warp * (32 * RS_ITEMS);
-    uint64_t key[RS_ITEMS];
-    uint32_t rank[RS_ITEMS];
+    const uint64_t tile_base = (uint64_t) tile * RS_TILE;
+    const uint64_t base = tile_base + (uint64_t) warp * (32 * RS_ITEMS);
+    const uint32_t tile_n = (uint32_t) ((n - tile_base) < (uint64_t) RS_TILE ? (n - tile_base) : (uint64_t) RS_TILE);
+    KeyT key[RS_ITEMS];
+    uint32_t pos[RS_ITEMS];
 #pragma unroll
     for (int k = 0; k < RS_ITEMS; k++) {
         const uint64_t i = base + (uint64_t) k * 32 + lane;
-        key[k] = i < n ? keys_in[i] : ~0ull;
+        key[k] = i < n ? keys_in[i] : (KeyT) 0;
     }
     const uint32_t lt = (1u << lane) - 1u;
 #pragma unroll
     for (int k = 0; k < RS_ITEMS; k++) {
         const uint64_t i = base + (uint64_t) k * 32 + lane;
         const bool valid = i < n;
-        const uint32_t d = valid ? (uint32_t) ((key[k] >> shift) & 0xffu) : 0xffffffffu;
+        const uint32_t d = valid ? rs_digit(key[k], shift, mask) : 0xffffffffu;
         const uint32_t peers = __match_any_sync(0xffffffffu, d);
         const uint32_t before = __popc(peers & lt);
         uint32_t prev = 0;
@@ -239,37 +334,93 @@ __global__ void __launch_bounds__(RS_THREADS) rs_scatter_kernel(const uint64_t *
             cnt[warp][d] = prev + (uint32_t) __popc(peers);
         }
         __syncwarp();
-        rank[k] = prev + before;
+        pos[k] = prev + before;
     }
     __syncthreads();
+    // thread b owns digit b
+    uint32_t tile_count = 0;
     {
-        // thread t owns digit t: turn per-warp counts into global offsets
-        uint32_t run = tile_base[(uint64_t) threadIdx.x * num_tiles + blockIdx.x];
 #pragma unroll
         for (int w = 0; w < RS_WARPS; w++) {
             const uint32_t c = cnt[w][threadIdx.x];
-            cnt[w][threadIdx.x] = run;
-            run += c;
+            cnt[w][threadIdx.x] = tile_count;
+            tile_count += c;
+        }
+    }
+    // publish, then look back for the number of keys with this digit in earlier tiles
+    volatile uint32_t *mine = tile_state + (uint64_t) tile * RS_BINS + threadIdx.x;
+    uint32_t prefix = 0;
+    if (tile == 0) {
+        *mine = RS_FLAG_INCL | tile_count;
+    } else {
+        *mine = RS_FLAG_AGG | tile_count;
+        for (int64_t p = (int64_t) tile - 1; p >= 0; p--) {
+            volatile uint32_t *theirs = tile_state + (uint64_t) p * RS_BINS + threadIdx.x;
+            uint32_t v;
+            do {
+                v = *theirs;
+            } while ((v & ~RS_COUNT_MASK) == 0);
+            prefix += v & RS_COUNT_MASK;
+            if (v & RS_FLAG_INCL) {
+                break;
+            }
+        }
+        *mine = RS_FLAG_INCL | (prefix + tile_count);
+    }
+    // exclusive scans over the 256 digits: within the tile, and of the global histogram
+    uint32_t tot;
+    const uint32_t ls = block_exclusive_scan<uint32_t>(tile_count, scan_tmp, &tot);
+    const uint32_t gh = global_hist[threadIdx.x];
+    const uint32_t gs = block_exclusive_scan<uint32_t>(gh, scan_tmp, &tot);
+    local_start[threadIdx.x] = ls;
+    global_base[threadIdx.x] = gs + prefix - ls; // dst = global_base[d] + local position
+    __syncthreads();
+    // stage keys in sorted order
+#pragma unroll
+    for (int k = 0; k < RS_ITEMS; k++) {
+        const uint64_t i = base + (uint64_t) k * 32 + lane;
+        if (i < n) {
+            const uint32_t d = rs_digit(key[k], shift, mask);
+            pos[k] += local_start[d] + cnt[warp][d];
+            stage[pos[k]] = key[k];
+        }
+    }
+    __syncthreads();
+    uint32_t dst[RS_ITEMS];
+#pragma unroll
+    for (int k = 0; k < RS_ITEMS; k++) {
+        const uint32_t j = (uint32_t) k * RS_THREADS + threadIdx.x;
+        if (j < tile_n) {
+            const KeyT kk = stage[j];
+            dst[k] = global_base[rs_digit(kk, shift, mask)] + j;
+            keys_out[dst[k]] = kk;
+        }
+    }
+    __syncthreads();
+    uint32_t *vstage = reinterpret_cast<uint32_t *>(stage);
+#pragma unroll
+    for (int k = 0; k < RS_ITEMS; k++) {
+        const uint64_t i = base + (uint64_t) k * 32 + lane;
+        if (i < n) {
+            vstage[pos[k]] = vals_in != nullptr ? vals_in[i] : (uint32_t) i;
         }
     }
     __syncthreads();
 #pragma unroll
     for (int k = 0; k < RS_ITEMS; k++) {
-        const uint64_t i = base + (uint64_t) k * 32 + lane;
-        if (i < n) {
-            const uint32_t d = (uint32_t) ((key[k] >> shift) & 0xffu);
-            const uint32_t dst = cnt[warp][d] + rank[k];
-            keys_out[dst] = key[k];
-            vals_out[dst] = vals_in[i];
+        const uint32_t j = (uint32_t) k * RS_THREADS + threadIdx.x;
+        if (j < tile_n) {
+            vals_out[dst[k]] = vstage[j];
         }
     }
 }
 
+template <typename KeyT>
 struct RadixSortBuffers {
-    uint64_t *keys[2];
+    KeyT *keys[2];
     uint32_t *vals[2];
-    uint32_t *tile_hist; // RS_BINS * num_tiles
-    uint32_t *scan_tiles; // scan_num_tiles(RS_BINS * num_tiles)
+    uint32_t *hist; // RS_MAX_PASSES * RS_BINS
+    uint32_t *tile_state; // RS_MAX_PASSES * num_tiles * RS_BINS
     uint64_t *or_and; // 2 (device)
     uint64_t *or_and_host; // 2 (pinned)
 };
@@ -279,43 +430,66 @@ inline uint32_t rs_num_tiles(uint64_t n)
     return (uint32_t) ((n + RS_TILE - 1) / RS_TILE);
 }
 
-// Sorts n (key, val) pairs held in buf.keys[0] / buf.vals[0]; returns the index
-// (0 or 1) of the buffer holding the result.  *launches is incremented by the
-// number of kernels launched.  Synchronises the stream once (to read the bit mask).
-inline int device_radix_sort(RadixSortBuffers &buf, uint64_t n, cudaStream_t st, LaunchLog &log, int *passes_out)
+inline uint64_t rs_state_words(uint64_t n)
+{
+    return (uint64_t) RS_MAX_PASSES * rs_num_tiles(n > 0 ? n : 1) * RS_BINS;
+}
+
+// Sorts n (key, val) pairs held in buf.keys[0] (payload: buf.vals[0], or the identity
+// 0..n-1 when identity_vals); returns the index (0 or 1) of the buffers holding the
+// result.  `varying` names the key bits that may differ; pass 0 to have them measured
+// (one reduction kernel and one stream synchronisation).  n must be <= RS_MAX_N.
+template <typename KeyT>
+inline int device_radix_sort(RadixSortBuffers<KeyT> &buf, uint64_t n, uint64_t varying, bool identity_vals,
+    cudaStream_t st, LaunchLog &log, int *passes_out)
 {
     if (passes_out != nullptr) {
         *passes_out = 0;
     }
     if (n <= 1) {
+        if (n == 1 && identity_vals) {
+            cudaMemsetAsync(buf.vals[0], 0, sizeof(uint32_t), st);
+        }
         return 0;
     }
-    const uint64_t init[2] = { 0ull, ~0ull };
-    cudaMemcpyAsync(buf.or_and, init, sizeof(init), cudaMemcpyHostToDevice, st);
-    MSPB_LAUNCH(log, "rs_key_bits", rs_key_bits_kernel<<<148 * 4, 256, 0, st>>>(buf.keys[0], n, buf.or_and));
-    cudaMemcpyAsync(buf.or_and_host, buf.or_and, 2 * sizeof(uint64_t), cudaMemcpyDeviceToHost, st);
-    cudaStreamSynchronize(st);
-    const uint64_t varying = buf.or_and_host[0] & ~buf.or_and_host[1];
+    if (varying == 0) {
+        const uint64_t init[2] = { 0ull, ~0ull };
+        cudaMemcpyAsync(buf.or_and, init, sizeof(init), cudaMemcpyHostToDevice, st);
+        MSPB_LAUNCH(log, "rs_key_bits", rs_key_bits_kernel<KeyT><<<148 * 4, 256, 0, st>>>(buf.keys[0], n, buf.or_and));
+        cudaMemcpyAsync(buf.or_and_host, buf.or_and, 2 * sizeof(uint64_t), cudaMemcpyDeviceToHost, st);
+        cudaStreamSynchronize(st);
+        varying = buf.or_and_host[0] & ~buf.or_and_host[1];
+    }
+    const RadixPlan plan = radix_plan(varying);
     const uint32_t tiles = rs_num_tiles(n);
+    if (plan.passes == 0) {
+        // all keys equal: the input order is the sorted order
+        if (identity_vals) {
+            MSPB_LAUNCH(log, "rs_iota", rs_iota_kernel<<<(unsigned) ((n + 255) / 256), 256, 0, st>>>(buf.vals[0], n));
+        }
+        return 0;
+    }
+    RadixPlanDev pd;
+    pd.passes = plan.passes;
+    for (int p = 0; p < plan.passes; p++) {
+        pd.shift[p] = plan.shift[p];
+        pd.mask[p] = (1u << plan.bits[p]) - 1u;
+    }
+    cudaMemsetAsync(buf.hist, 0, (size_t) RS_MAX_PASSES * RS_BINS * sizeof(uint32_t), st);
+    cudaMemsetAsync(buf.tile_state, 0, (size_t) plan.passes * tiles * RS_BINS * sizeof(uint32_t), st);
+    const unsigned hist_blocks = tiles < 148u * 8u ? tiles : 148u * 8u;
+    MSPB_LAUNCH(log, "rs_global_hist",
+        rs_global_hist_kernel<KeyT><<<hist_blocks, RS_THREADS, 0, st>>>(buf.keys[0], n, pd, buf.hist));
     int cur = 0;
-    for (int pass = 0; pass < 8; pass++) {
-        const int shift = pass * 8;
-        if (((varying >> shift) & 0xffull) == 0) {
-            continue;
-        }
-        MSPB_LAUNCH(log, "rs_hist",
-            rs_hist_kernel<<<tiles, RS_THREADS, 0, st>>>(buf.keys[cur], n, shift, tiles, buf.tile_hist));
-        const uint32_t *th = buf.tile_hist;
-        device_exclusive_scan<uint32_t>(
-            log, (uint64_t) RS_BINS * tiles, [th] __device__(uint64_t i) { return th[i]; }, buf.tile_hist,
-            buf.scan_tiles, (uint32_t *) nullptr, st);
-        MSPB_LAUNCH(log, "rs_scatter",
-            rs_scatter_kernel<<<tiles, RS_THREADS, 0, st>>>(
-                buf.keys[cur], buf.vals[cur], buf.keys[cur ^ 1], buf.vals[cur ^ 1], n, shift, tiles, buf.tile_hist));
+    for (int p = 0; p < plan.passes; p++) {
+        MSPB_LAUNCH(log, "rs_onesweep",
+            rs_onesweep_kernel<KeyT><<<tiles, RS_THREADS, 0, st>>>(buf.keys[cur],
+                (p == 0 && identity_vals) ? nullptr : buf.vals[cur], buf.keys[cur ^ 1], buf.vals[cur ^ 1], n,
+                pd.shift[p], pd.mask[p], buf.hist + p * RS_BINS, buf.tile_state + (size_t) p * tiles * RS_BINS));
         cur ^= 1;
-        if (passes_out != nullptr) {
-            (*passes_out)++;
-        }
+    }
+    if (passes_out != nullptr) {
+        *passes_out = plan.passes;
     }
     return cur;
 }
