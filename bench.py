@@ -241,22 +241,19 @@ def algorithmic_bytes(kernel, n):
     derived/ancestral state bytes."""
     E, R, M, S = n["E"], n["R"], n["M"], n["S"]
     table = {
-        # left,right f64 + parent,child i32 + two node-time gathers, count out
-        "k1_count": E * (8 + 8 + 4 + 4 + 16) + E * 4,
-        # edge columns again + count/offset in, pos,time f64 + node,ord i32 + key u64 + val u32 out
-        "k2_place": E * (8 + 8 + 4 + 4 + 16 + 8) + M * (8 + 8 + 4 + 4 + 8 + 4),
-        "rs_key_bits": R * 8,
-        "rs_hist": R * 8,
-        # key u64 + val u32, read and written once per pass
-        "rs_scatter": R * 2 * (8 + 4),
-        "finalize_runs": R * 8,
-        "post_sort_check": R * (8 + 4),
-        # key + val + node + pos gathers in, parent (+ state) out
-        "k4_resolve": R * (8 + 4 + 4 + 8) + R * 4,
-        # val, key, scans (site,mut u32; 4 x u64 byte scans), rec gathers in; table rows out
-        "k5_emit": R * (4 + 8 + 4 + 4 + 32 + 8 + 8 + 4 + 4) + M * (4 + 4 + 4 + 8 + 16) + S * (8 + 16)
-        + n["DB"] + n["AB"],
-        "scan_tile_sums": None, "scan_apply": None, "scan_spine": None,
+        # left,right f64 + parent,child i32 + two node-time gathers in, goff u32 out
+        "k1_count_scan": E * (8 + 8 + 4 + 4 + 16) + E * 4,
+        # goff in, edge columns of edges that mutate (<= E), Rec 16 B + key 4 B out
+        "k2_place": E * 4 + min(E, M) * (8 + 8 + 4 + 4 + 16) + M * (16 + 4),
+        "rs_global_hist": R * n["KB"],
+        # key + u32 payload read and written once per pass (first pass has no payload read)
+        "rs_onesweep": R * 2 * (n["KB"] + 4),
+        # key in, site row out
+        "p1_sites": R * (n["KB"] + 4),
+        # key in (records of multi-mutation sites are a small fraction)
+        "k4_resolve": R * n["KB"],
+        # key, val, site row, one 32 B sector per gathered Rec in; table rows + ragged bytes out
+        "k5_emit": R * (n["KB"] + 4 + 4 + 32) + M * (4 + 4 + 4 + 8 + 16) + S * (8 + 16) + n["DB"] + n["AB"],
     }
     return table.get(kernel)
 
@@ -414,7 +411,8 @@ def run_b200_arm(args, rank, local_rank, world):
     total_kernel_ms = sum(v[1] for v in ktimes.values()) or 1.0
     last = ctx.counts
     nn = {"E": E, "R": last["num_mutations"], "M": last["num_mutations"],
-          "S": last["num_sites"], "DB": last["derived_state_bytes"], "AB": last["ancestral_state_bytes"]}
+          "S": last["num_sites"], "DB": last["derived_state_bytes"], "AB": last["ancestral_state_bytes"],
+          "KB": 4 if (w["discrete"] and L <= 2**32) else 8}
     roofline = None
     for name, (n_launch, ms) in kt:
         ab = algorithmic_bytes(name, nn)

@@ -291,3 +291,131 @@ struct RateMapView {
 };
 
 } // namespace mspb
+
+namespace mspb {
+
+// ---------------------------------------------------------------- decoupled look-back
+// Single-pass prefix sums over tiles (Merrill & Garland): a tile publishes its
+// aggregate, then sums the aggregates of the tiles before it until it meets one
+// whose inclusive prefix is already known.  T is a small POD with operator+ and a
+// multiple of 4 bytes in size.  Flags: 0 = nothing yet, 1 = aggregate, 2 = inclusive.
+template <typename T>
+struct Lookback {
+    uint32_t *flag;
+    T *agg;
+    T *incl;
+};
+
+template <typename T>
+MSPB_DEVFN T ld_cg_pod(const T *p)
+{
+    static_assert(sizeof(T) % 4 == 0, "POD of 32-bit words");
+    T v;
+    uint32_t *w = reinterpret_cast<uint32_t *>(&v);
+    const uint32_t *s = reinterpret_cast<const uint32_t *>(p);
+#pragma unroll
+    for (int i = 0; i < (int) (sizeof(T) / 4); i++) {
+        w[i] = __ldcg(s + i);
+    }
+    return v;
+}
+
+template <typename T>
+MSPB_DEVFN void st_cg_pod(T *p, const T &v)
+{
+    const uint32_t *w = reinterpret_cast<const uint32_t *>(&v);
+    uint32_t *d = reinterpret_cast<uint32_t *>(p);
+#pragma unroll
+    for (int i = 0; i < (int) (sizeof(T) / 4); i++) {
+        __stcg(d + i, w[i]);
+    }
+}
+
+template <typename T>
+MSPB_DEVFN T shfl_xor_pod(const T &v, int mask)
+{
+    T r;
+    const uint32_t *w = reinterpret_cast<const uint32_t *>(&v);
+    uint32_t *o = reinterpret_cast<uint32_t *>(&r);
+#pragma unroll
+    for (int i = 0; i < (int) (sizeof(T) / 4); i++) {
+        o[i] = __shfl_xor_sync(0xffffffffu, w[i], mask);
+    }
+    return r;
+}
+
+// Called by every thread of the block with the block's aggregate (thread 0's value is
+// used); returns the sum over all earlier tiles.  *total (optional, device memory)
+// receives the grand total from the last tile.  `bcast` is one T in shared memory.
+template <typename T>
+MSPB_DEVFN T lookback_exclusive(const Lookback<T> &lb, uint32_t tile, uint32_t num_tiles, const T &aggregate, T *bcast,
+    T *total)
+{
+    if (threadIdx.x < 32) {
+        const int lane = threadIdx.x;
+        T prefix = T();
+        if (tile > 0) {
+            if (lane == 0) {
+                st_cg_pod(&lb.agg[tile], aggregate);
+                __threadfence();
+                *((volatile uint32_t *) &lb.flag[tile]) = 1u;
+            }
+            int64_t base = (int64_t) tile - 1;
+            for (;;) {
+                const int64_t p = base - lane;
+                uint32_t f = 2u;
+                if (p >= 0) {
+                    do {
+                        f = *((volatile uint32_t *) &lb.flag[p]);
+                    } while (f == 0u);
+                }
+                __threadfence();
+                const uint32_t incl_mask = __ballot_sync(0xffffffffu, f == 2u);
+                const int stop = incl_mask != 0u ? (__ffs(incl_mask) - 1) : 32;
+                T v = T();
+                if (p >= 0 && lane <= stop) {
+                    v = f == 2u ? ld_cg_pod(&lb.incl[p]) : ld_cg_pod(&lb.agg[p]);
+                }
+#pragma unroll
+                for (int s = 16; s > 0; s >>= 1) {
+                    v = v + shfl_xor_pod(v, s);
+                }
+                prefix = prefix + v;
+                if (incl_mask != 0u) {
+                    break;
+                }
+                base -= 32;
+            }
+        }
+        if (lane == 0) {
+            const T inclusive = prefix + aggregate;
+            st_cg_pod(&lb.incl[tile], inclusive);
+            __threadfence();
+            *((volatile uint32_t *) &lb.flag[tile]) = 2u;
+            *bcast = prefix;
+            if (total != nullptr && tile + 1 == num_tiles) {
+                *total = inclusive;
+            }
+        }
+    }
+    __syncthreads();
+    const T r = *bcast;
+    __syncthreads();
+    return r;
+}
+
+// ---------------------------------------------------------------- records
+// One per kept site ("marker"), kept mutation and new mutation, indexed by slot.
+struct __align__(16) Rec {
+    double time;
+    int32_t node;
+    uint32_t ord; // new mutations: global ordinal (counter of the allele draws)
+};
+
+MSPB_DEVFN double from_ordered_bits(uint64_t b)
+{
+    b = (b & 0x8000000000000000ull) ? (b & 0x7fffffffffffffffull) : ~b;
+    return __longlong_as_double((long long) b);
+}
+
+} // namespace mspb

@@ -1,16 +1,21 @@
 // msprime_b200: the mutation-overlay kernels (sm_100a).
 //
 // Pipeline (DESIGN.md has the data layout and the byte counts):
-//   K0  child-sorted edge interval index            (once per tree sequence)
-//   K1  per-edge Poisson count + exclusive scan     <- lib/mutgen.c:1103-1120
-//   K2  position / time placement                   <- lib/mutgen.c:1121-1151
-//   K3  radix sort by (position, time desc)         <- AVL map + per-site qsort
-//   K4  per-site parent search + allele assignment  <- lib/mutgen.c:1160-1224
-//   K5  site / mutation table emission              <- lib/mutgen.c:1027-1074
+//   K0  child-sorted edge interval index              (once per tree sequence)
+//   K1  per-edge Poisson count, scanned in the same   <- lib/mutgen.c:1103-1120
+//       kernel by decoupled look-back
+//   K2  position / time placement, one thread per     <- lib/mutgen.c:1121-1151
+//       mutation (edges staged in shared memory)
+//   K3  stable radix sort by position (sort.cuh)      <- AVL map, lib/mutgen.c:858-883
+//   P1  site boundaries + row / draw numbering        <- site order, lib/mutgen.c:1027-1074
+//   K4  sites with several records: time order,       <- lib/mutgen.c:36-95, 1160-1224
+//       parent search, allele chain
+//   K5  byte offsets (look-back) + table emission     <- lib/mutgen.c:1027-1074
 //
 // Records: one per kept site ("marker"), kept mutation and new mutation, in that
 // slot order, so a record's kind follows from its slot index and slot order is the
 // final tie-break (kept before new, kept by row id, new by creation order).
+// A record is 16 bytes (Rec: time, node, ordinal); its position lives in the sort key.
 #pragma once
 #include "common.cuh"
 #include "replay.cuh"
@@ -59,13 +64,60 @@ struct ModelView {
     uint64_t start_allele;
 };
 
+// How positions are packed into sort keys.
+enum KeyMode : int {
+    KEY32_POS = 0, // uint32 key = integer position (discrete genome below 2^32)
+    KEY64_POS = 1, // uint64 key = ordered_bits(position): exact, any genome
+    KEY64_POS_TIME = 2 // uint64 key = integer position << 32 | coarse descending time
+};
+
 struct CallView {
     double start_time, end_time;
     double slice_left, slice_right;
     int discrete;
     int sliced;
     uint64_t seed;
-    int pos_shift; // key = (uint64(pos) << 32 | coarse time) when >= 0; else key = ordered_bits(pos)
+    int key_mode;
+};
+
+// keys of the records, before or after the sort
+struct KeyView {
+    uint32_t *k32;
+    uint64_t *k64;
+    int mode;
+    MSPB_DEVFN void store(uint64_t i, double pos, double time, bool marker) const
+    {
+        if (mode == KEY32_POS) {
+            k32[i] = (uint32_t) pos;
+        } else if (mode == KEY64_POS) {
+            k64[i] = ordered_bits(pos);
+        } else {
+            const uint64_t t = marker ? 0ull : ((~ordered_bits(time)) >> 32);
+            k64[i] = ((uint64_t) pos << 32) | t;
+        }
+    }
+    MSPB_DEVFN bool same_pos(uint64_t i, uint64_t j) const
+    {
+        if (mode == KEY32_POS) {
+            return k32[i] == k32[j];
+        }
+        const uint64_t m = mode == KEY64_POS ? ~0ull : 0xffffffff00000000ull;
+        return ((k64[i] ^ k64[j]) & m) == 0;
+    }
+    MSPB_DEVFN bool same_key(uint64_t i, uint64_t j) const
+    {
+        return mode == KEY32_POS ? k32[i] == k32[j] : k64[i] == k64[j];
+    }
+    MSPB_DEVFN double position(uint64_t i) const
+    {
+        if (mode == KEY32_POS) {
+            return (double) k32[i];
+        }
+        if (mode == KEY64_POS) {
+            return from_ordered_bits(k64[i]);
+        }
+        return (double) (k64[i] >> 32);
+    }
 };
 
 // ---------------------------------------------------------------- K0
@@ -130,6 +182,7 @@ MSPB_DEVFN int32_t parent_at(const TreeSeqView &ts, int32_t u, double x)
     return x < ts.ci_right[lo] ? ts.ci_parent[lo] : -1;
 }
 
+
 // ---------------------------------------------------------------- K1 (native)
 struct EdgeDraw {
     double branch_start, branch_end, mass_lo, mass, left, right;
@@ -164,75 +217,131 @@ MSPB_DEVFN void place_one(const Philox &ph, const RateMapView &map, const EdgeDr
     *time = t;
 }
 
-// count[e] = Poisson(branch length x rate mass); local[e] = how many fall in the slice
-__global__ void __launch_bounds__(256) k1_count_kernel(TreeSeqView ts, RateMapView map, CallView call,
-    uint32_t *__restrict__ count, uint32_t *__restrict__ local)
+constexpr int K1_ITEMS = 4;
+constexpr int K1_TILE = SCAN_THREADS * K1_ITEMS;
+
+// count[e] = Poisson(branch length x rate mass), and how many of those fall in this
+// call's genome slice.  Both are prefix-summed here (low / high half of one 64-bit sum):
+// goff[e] = mutations of earlier edges (goff[E] = all), loff[e] = in-slice ones.
+__global__ void __launch_bounds__(SCAN_THREADS) k1_count_scan_kernel(TreeSeqView ts, RateMapView map, CallView call,
+    Lookback<uint64_t> lb, uint32_t num_tiles, uint32_t *__restrict__ goff, uint32_t *__restrict__ loff,
+    uint64_t *total)
 {
-    const uint64_t e = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
-    if (e >= ts.num_edges) {
-        return;
+    __shared__ uint64_t sm[9];
+    __shared__ uint64_t bcast;
+    const uint64_t e0 = (uint64_t) blockIdx.x * K1_TILE + (uint64_t) threadIdx.x * K1_ITEMS;
+    uint64_t c[K1_ITEMS];
+    uint64_t acc = 0;
+    const Philox ph(call.seed);
+#pragma unroll
+    for (int k = 0; k < K1_ITEMS; k++) {
+        const uint64_t e = e0 + k;
+        c[k] = 0;
+        if (e < ts.num_edges) {
+            const EdgeDraw d = edge_draw(ts, map, call, e);
+            const double mu = (d.branch_end - d.branch_start) * d.mass;
+            PhiloxSeq rng(call.seed, e, TAG_COUNT);
+            const uint32_t n = poisson_native(rng, mu);
+            uint32_t in = 0;
+            if (call.sliced && n > 0 && d.left < call.slice_right && d.right > call.slice_left) {
+                for (uint32_t j = 0; j < n; j++) {
+                    double x, t;
+                    place_one(ph, map, d, e, j, &x, &t);
+                    in += (x >= call.slice_left && x < call.slice_right) ? 1u : 0u;
+                }
+            }
+            c[k] = (uint64_t) n | ((uint64_t) in << 32);
+        }
+        acc += c[k];
     }
-    const EdgeDraw d = edge_draw(ts, map, call, e);
-    const double mu = (d.branch_end - d.branch_start) * d.mass;
-    PhiloxSeq rng(call.seed, e, TAG_COUNT);
-    const uint32_t n = poisson_native(rng, mu);
-    count[e] = n;
-    if (call.sliced) {
-        uint32_t in = 0;
-        if (n > 0 && d.left < call.slice_right && d.right > call.slice_left) {
-            const Philox ph(call.seed);
-            for (uint32_t k = 0; k < n; k++) {
-                double x, t;
-                place_one(ph, map, d, e, k, &x, &t);
-                in += (x >= call.slice_left && x < call.slice_right) ? 1u : 0u;
+    uint64_t block_total;
+    const uint64_t ex = block_exclusive_scan<uint64_t>(acc, sm, &block_total);
+    uint64_t run = lookback_exclusive<uint64_t>(lb, blockIdx.x, num_tiles, block_total, &bcast, total) + ex;
+#pragma unroll
+    for (int k = 0; k < K1_ITEMS; k++) {
+        const uint64_t e = e0 + k;
+        if (e < ts.num_edges) {
+            goff[e] = (uint32_t) run;
+            if (loff != nullptr) {
+                loff[e] = (uint32_t) (run >> 32);
+            }
+            run += c[k];
+            if (e + 1 == ts.num_edges) {
+                goff[e + 1] = (uint32_t) run;
             }
         }
-        local[e] = in;
     }
-}
-
-MSPB_DEVFN uint64_t make_key(const CallView &call, double pos, double time, bool marker)
-{
-    if (call.pos_shift >= 0) {
-        const uint64_t t = marker ? 0ull : ((~ordered_bits(time)) >> 32);
-        return ((uint64_t) pos << 32) | t;
-    }
-    return ordered_bits(pos);
 }
 
 // ---------------------------------------------------------------- K2 (native)
-// goff: exclusive scan of count (global ordinal); loff: exclusive scan of the in-slice
-// counts (== goff when not sliced).  Records go to slots base + loff[e] + j.
-__global__ void __launch_bounds__(256) k2_place_kernel(TreeSeqView ts, RateMapView map, CallView call,
-    const uint32_t *__restrict__ count, const uint32_t *__restrict__ goff, const uint32_t *__restrict__ loff,
-    uint32_t base, double *__restrict__ rec_pos, double *__restrict__ rec_time, int32_t *__restrict__ rec_node,
-    uint32_t *__restrict__ rec_ord, uint64_t *__restrict__ key, uint32_t *__restrict__ val)
+// One block per 256 edges: their draw parameters are staged in shared memory, then
+// each thread places one mutation (slot j of the tile's contiguous slot range), so
+// record and key writes are coalesced whatever the per-edge counts are.
+constexpr int K2_EDGES = 256;
+
+__global__ void __launch_bounds__(K2_EDGES) k2_place_kernel(TreeSeqView ts, RateMapView map, CallView call,
+    const uint32_t *__restrict__ goff, const uint32_t *__restrict__ loff, uint32_t base, Rec *__restrict__ rec,
+    KeyView keys)
 {
-    const uint64_t e = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
-    if (e >= ts.num_edges) {
+    __shared__ EdgeDraw sd[K2_EDGES];
+    __shared__ uint32_t soff[K2_EDGES + 1];
+    __shared__ uint32_t sm[9];
+    const uint64_t E = ts.num_edges;
+    const uint64_t ebase = (uint64_t) blockIdx.x * K2_EDGES;
+    const uint64_t e = ebase + threadIdx.x;
+    soff[threadIdx.x] = goff[e < E ? e : E];
+    if (threadIdx.x == 0) {
+        soff[K2_EDGES] = goff[ebase + K2_EDGES < E ? ebase + K2_EDGES : E];
+    }
+    __syncthreads();
+    const uint32_t s0 = soff[0], s1 = soff[K2_EDGES];
+    if (s0 == s1) {
         return;
     }
-    const uint32_t n = count[e];
-    if (n == 0) {
-        return;
+    if (e < E && soff[threadIdx.x + 1] > soff[threadIdx.x]) {
+        sd[threadIdx.x] = edge_draw(ts, map, call, e);
     }
-    const EdgeDraw d = edge_draw(ts, map, call, e);
+    __syncthreads();
     const Philox ph(call.seed);
-    uint32_t slot = base + loff[e];
-    const uint32_t g0 = goff[e];
-    for (uint32_t k = 0; k < n; k++) {
-        double x, t;
-        place_one(ph, map, d, e, k, &x, &t);
-        if (call.sliced && !(x >= call.slice_left && x < call.slice_right)) {
-            continue;
+    uint32_t out = base + (call.sliced ? loff[ebase] : s0);
+    for (uint32_t j0 = s0; j0 < s1; j0 += K2_EDGES) {
+        const uint32_t j = j0 + threadIdx.x;
+        const bool valid = j < s1;
+        double x = 0, t = 0;
+        int32_t child = 0;
+        bool in = false;
+        if (valid) {
+            uint32_t lo = 0, hi = K2_EDGES; // largest el with soff[el] <= j
+            while (hi - lo > 1) {
+                const uint32_t mid = (lo + hi) >> 1;
+                if (soff[mid] <= j) {
+                    lo = mid;
+                } else {
+                    hi = mid;
+                }
+            }
+            const EdgeDraw &d = sd[lo];
+            place_one(ph, map, d, ebase + lo, j - soff[lo], &x, &t);
+            child = d.child;
+            in = !call.sliced || (x >= call.slice_left && x < call.slice_right);
         }
-        rec_pos[slot] = x;
-        rec_time[slot] = t;
-        rec_node[slot] = d.child;
-        rec_ord[slot - base] = g0 + k;
-        key[slot] = make_key(call, x, t, false);
-        val[slot] = slot;
-        slot++;
+        uint32_t slot;
+        if (call.sliced) {
+            uint32_t tot;
+            slot = out + block_exclusive_scan<uint32_t>(in ? 1u : 0u, sm, &tot);
+            out += tot;
+        } else {
+            slot = out + threadIdx.x;
+            out += K2_EDGES;
+        }
+        if (in) {
+            Rec r;
+            r.time = t;
+            r.node = child;
+            r.ord = j;
+            rec[slot] = r;
+            keys.store(slot, x, t, false);
+        }
     }
 }
 
@@ -315,9 +424,8 @@ MSPB_DEVFN double replay_flat(double lo, double hi, double u, int *err)
 }
 
 __global__ void __launch_bounds__(128) replay_place_kernel(TreeSeqView ts, RateMapView map, CallView call,
-    const double *__restrict__ stream, ReplayPairs pairs, uint64_t num_pairs, uint32_t base,
-    double *__restrict__ rec_pos, double *__restrict__ rec_time, int32_t *__restrict__ rec_node,
-    uint32_t *__restrict__ rec_ord, uint64_t *__restrict__ key, uint32_t *__restrict__ val, int *err)
+    const double *__restrict__ stream, ReplayPairs pairs, uint64_t num_pairs, uint32_t base, Rec *__restrict__ rec,
+    KeyView keys, int *err)
 {
     const uint64_t p = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= num_pairs) {
@@ -340,20 +448,19 @@ __global__ void __launch_bounds__(128) replay_place_kernel(TreeSeqView ts, RateM
             x = floor(x);
         }
         const double t = replay_flat(branch_start, branch_end, u[2 * k + 1], err);
-        rec_pos[slot] = x;
-        rec_time[slot] = t;
-        rec_node[slot] = child;
-        rec_ord[slot - base] = slot - base;
-        key[slot] = make_key(call, x, t, false);
-        val[slot] = slot;
+        Rec r;
+        r.time = t;
+        r.node = child;
+        r.ord = slot - base;
+        rec[slot] = r;
+        keys.store(slot, x, t, false);
     }
 }
 
 // ---------------------------------------------------------------- kept records
 // slots [0, S0): site markers; [S0, S0 + M0): kept mutations (lib/mutgen.c:974-1025)
-__global__ void __launch_bounds__(256) fill_kept_kernel(KeptView kept, CallView call, double *__restrict__ rec_pos,
-    double *__restrict__ rec_time, int32_t *__restrict__ rec_node, uint64_t *__restrict__ key,
-    uint32_t *__restrict__ val, int *err)
+__global__ void __launch_bounds__(256) fill_kept_kernel(KeptView kept, CallView call, Rec *__restrict__ rec,
+    KeyView keys, int *err)
 {
     const uint64_t r = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
     const uint64_t S0 = kept.num_sites, M0 = kept.num_mutations;
@@ -377,11 +484,12 @@ __global__ void __launch_bounds__(256) fill_kept_kernel(KeptView kept, CallView 
             set_error(err, -1006);
         }
     }
-    rec_pos[r] = x;
-    rec_time[r] = t;
-    rec_node[r] = node;
-    key[r] = make_key(call, x, t, r < S0);
-    val[r] = (uint32_t) r;
+    Rec q;
+    q.time = t;
+    q.node = node;
+    q.ord = 0;
+    rec[r] = q;
+    keys.store(r, x, t, r < S0);
 }
 
 // model allele index of each kept state (exact byte comparison, lib/mutgen.c:184-198)
@@ -413,14 +521,105 @@ __global__ void __launch_bounds__(256) kept_allele_index_kernel(ModelView model,
 struct SortedView {
     uint64_t n; // records
     uint64_t S0, M0; // kept sites / kept mutations (slot ranges)
-    const uint64_t *key;
-    uint32_t *val; // slot of the record at each sorted index
-    const double *rec_pos, *rec_time;
-    const int32_t *rec_node;
-    const uint32_t *rec_ord;
-    uint64_t pos_mask; // bits of the key that hold the position
+    KeyView key; // sorted keys
+    uint32_t *val; // slot of the record at each sorted index (K4 reorders inside sites)
+    const Rec *rec;
+    int has_kept; // S0 + M0 > 0
+    // P1 results
+    uint32_t *site_row; // row of the site that record i belongs to
+    uint32_t *mut_scan; // mutation rows before i (has_kept only; otherwise it is i)
+    uint32_t *draw_scan; // root + transition draws before i (has_kept only)
+
+    MSPB_DEVFN bool head(uint64_t i) const { return i == 0 || !key.same_pos(i, i - 1); }
+    MSPB_DEVFN bool is_mut(uint64_t i) const { return !has_kept || val[i] >= S0; }
+    MSPB_DEVFN bool is_new(uint64_t i) const { return !has_kept || val[i] >= S0 + M0; }
+    // a site with exactly one record: nothing to order, no parent to find
+    MSPB_DEVFN bool single(uint64_t i) const { return head(i) && (i + 1 >= n || head(i + 1)); }
+    MSPB_DEVFN uint32_t mut_row(uint64_t i) const { return has_kept ? mut_scan[i] : (uint32_t) i; }
+    MSPB_DEVFN uint32_t draws_before(uint64_t i) const
+    {
+        return has_kept ? draw_scan[i] : (uint32_t) i + site_row[i] + 1u - (head(i) ? 1u : 0u);
+    }
 };
 
+struct Counts3 {
+    uint32_t s, m, d;
+    MSPB_DEVFN Counts3 operator+(const Counts3 &o) const
+    {
+        Counts3 r;
+        r.s = s + o.s;
+        r.m = m + o.m;
+        r.d = d + o.d;
+        return r;
+    }
+};
+
+constexpr int P1_ITEMS = 8;
+constexpr int P1_TILE = SCAN_THREADS * P1_ITEMS;
+
+// Site boundaries and numbering in one pass: site row of every record, mutation rows
+// and allele draws before it, plus the input checks that need the sorted order (two
+// kept sites at one position, lib/mutgen.c:875-879; a new mutation sharing a position
+// in the continuous genome, which the reference redraws, lib/mutgen.c:1127-1134).
+__global__ void __launch_bounds__(SCAN_THREADS) p1_sites_kernel(SortedView sv, int discrete, Lookback<Counts3> lb,
+    uint32_t num_tiles, Counts3 *total, uint32_t *collisions, uint32_t *dense, int *err)
+{
+    __shared__ uint64_t sm[9];
+    __shared__ Counts3 bcast;
+    const uint64_t i0 = (uint64_t) blockIdx.x * P1_TILE + (uint64_t) threadIdx.x * P1_ITEMS;
+    uint32_t hb = 0, mb = 0, db = 0; // per-item bit flags
+    uint64_t acc = 0; // s | m << 21 | d << 42 (tile-local, each < 2^21)
+#pragma unroll
+    for (int k = 0; k < P1_ITEMS; k++) {
+        const uint64_t i = i0 + k;
+        if (i < sv.n) {
+            const bool h = sv.head(i);
+            const bool mu = sv.is_mut(i), nw = sv.is_new(i);
+            const uint32_t d = (nw ? 1u : 0u) + ((h && mu) ? 1u : 0u);
+            hb |= (h ? 1u : 0u) << k;
+            mb |= (mu ? 1u : 0u) << k;
+            db |= d << (2 * k);
+            acc += (h ? 1ull : 0ull) | ((mu ? 1ull : 0ull) << 21) | ((uint64_t) d << 42);
+            if (!h) {
+                if (sv.has_kept && sv.val[i] < sv.S0) {
+                    set_error(err, -21); // MSP_ERR_DUPLICATE_SITE_POSITION
+                }
+                if (!discrete && (nw || sv.is_new(i - 1))) {
+                    atomicAdd(collisions, 1u);
+                }
+                if (sv.key.mode == KEY32_POS && i >= 32 && sv.key.same_pos(i, i - 32)) {
+                    *dense = 1u;
+                }
+            }
+        }
+    }
+    uint64_t block_total;
+    const uint64_t ex = block_exclusive_scan<uint64_t>(acc, sm, &block_total);
+    Counts3 agg;
+    agg.s = (uint32_t) (block_total & 0x1fffffull);
+    agg.m = (uint32_t) ((block_total >> 21) & 0x1fffffull);
+    agg.d = (uint32_t) (block_total >> 42);
+    const Counts3 pre = lookback_exclusive<Counts3>(lb, blockIdx.x, num_tiles, agg, &bcast, total);
+    uint32_t s = pre.s + (uint32_t) (ex & 0x1fffffull);
+    uint32_t m = pre.m + (uint32_t) ((ex >> 21) & 0x1fffffull);
+    uint32_t d = pre.d + (uint32_t) (ex >> 42);
+#pragma unroll
+    for (int k = 0; k < P1_ITEMS; k++) {
+        const uint64_t i = i0 + k;
+        if (i < sv.n) {
+            s += (hb >> k) & 1u;
+            sv.site_row[i] = s - 1u;
+            if (sv.has_kept) {
+                sv.mut_scan[i] = m;
+                sv.draw_scan[i] = d;
+            }
+            m += (mb >> k) & 1u;
+            d += (db >> (2 * k)) & 3u;
+        }
+    }
+}
+
+// ---------------------------------------------------------------- K4
 // The reference's within-site order (lib/mutgen.c:36-49) on two records of one site:
 // marker first; kept vs kept by row; otherwise time descending; ties by slot.
 MSPB_DEVFN bool rec_before(const SortedView &sv, uint32_t a, uint32_t b)
@@ -433,54 +632,18 @@ MSPB_DEVFN bool rec_before(const SortedView &sv, uint32_t a, uint32_t b)
     if (ak && bk) {
         return a < b;
     }
-    const double ta = sv.rec_time[a], tb = sv.rec_time[b];
+    const double ta = sv.rec[a].time, tb = sv.rec[b].time;
     if (ta != tb) {
         return ta > tb;
     }
     return a < b;
 }
 
-// Runs of equal keys are ordered only coarsely by the sort; finish them exactly.
-__global__ void __launch_bounds__(256) finalize_runs_kernel(SortedView sv)
-{
-    const uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
-    if (i + 1 >= sv.n) {
-        return;
-    }
-    const uint64_t k = sv.key[i];
-    if (sv.key[i + 1] != k || (i > 0 && sv.key[i - 1] == k)) {
-        return;
-    }
-    uint64_t end = i + 2;
-    while (end < sv.n && sv.key[end] == k) {
-        end++;
-    }
-    // insertion sort of val[i .. end)
-    for (uint64_t a = i + 1; a < end; a++) {
-        const uint32_t v = sv.val[a];
-        uint64_t b = a;
-        while (b > i && rec_before(sv, v, sv.val[b - 1])) {
-            sv.val[b] = sv.val[b - 1];
-            b--;
-        }
-        sv.val[b] = v;
-    }
-}
-
-MSPB_DEVFN bool is_head(const SortedView &sv, uint64_t i)
-{
-    return i == 0 || ((sv.key[i] ^ sv.key[i - 1]) & sv.pos_mask) != 0;
-}
-
-// ---------------------------------------------------------------- K4
-// Per-record results of the per-site step, indexed by sorted position.
+// Per-record results of the per-site step (written for sites with several records only).
 struct ResolveView {
-    const uint32_t *site_scan; // sites before i
-    const uint32_t *mut_scan; // mutation rows before i
-    const uint32_t *draw_scan; // phase-B draws (or new alleles) before i
     int32_t *parent; // sorted index of the parent mutation, or -1
     int32_t *state; // matrix: allele index (new and kept; -1 = unknown kept allele)
-    int32_t *site_state; // matrix: allele index of a new site's ancestral state (by sorted head index)
+    int32_t *site_state; // matrix: allele index of a new site's ancestral state (at the head)
     const double *replay; // phase-B uniforms (replay mode), else nullptr
     uint64_t replay_len;
 };
@@ -513,46 +676,80 @@ MSPB_DEVFN double phase_b_uniform(const ResolveView &rv, uint64_t idx, int *err)
     return u;
 }
 
-// One thread per site: root state for a new site, then for each mutation in order the
-// nearest ancestor-or-self node already holding a mutation at this site gives the parent
-// (lib/mutgen.c:1185-1216).  The walk uses the child-sorted interval index instead of a
-// tree sweep and stops once the node is older than every earlier mutation's node.
+// uniforms of the allele draws of the new mutation with ordinal `ord`:
+// root (if it opens a new site) and transition
+MSPB_DEVFN void allele_uniforms(const Philox &ph, uint32_t ord, double *u_root, double *u_trans)
+{
+    const uint4 w = ph(ord, 0u, 0u, TAG_ALLELE);
+    *u_trans = u53(w.x, w.y);
+    *u_root = u53(w.z, w.w);
+}
+
+// One thread per site that has more than one record: put the records in the
+// reference's order, then for each mutation find the nearest ancestor-or-self node
+// already holding a mutation at this site (lib/mutgen.c:1185-1216) and draw its state.
+// The walk uses the child-sorted interval index instead of a tree sweep and stops once
+// the node is older than every earlier mutation's node.
 __global__ void __launch_bounds__(128) k4_resolve_kernel(TreeSeqView ts, KeptView kept, ModelView model, CallView call,
-    SortedView sv, ResolveView rv, int *err)
+    SortedView sv, ResolveView rv, const uint32_t *dense, int *err)
 {
     const uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= sv.n || !is_head(sv, i)) {
+    if (*dense != 0u && sv.key.mode == KEY32_POS) {
+        return; // the host re-sorts with time in the key and runs this step again
+    }
+    if (i >= sv.n || !sv.head(i) || i + 1 >= sv.n || sv.head(i + 1)) {
         return;
+    }
+    uint64_t end = i + 2;
+    while (end < sv.n && !sv.head(end)) {
+        end++;
+    }
+    // insertion sort of val[i .. end) (runs are short, or nearly sorted in KEY64_POS_TIME mode)
+    for (uint64_t a = i + 1; a < end; a++) {
+        const uint32_t v = sv.val[a];
+        uint64_t b = a;
+        while (b > i && rec_before(sv, v, sv.val[b - 1])) {
+            sv.val[b] = sv.val[b - 1];
+            b--;
+        }
+        sv.val[b] = v;
     }
     const uint64_t S0 = sv.S0, KM = sv.S0 + sv.M0;
     const uint32_t r0 = sv.val[i];
-    const bool kept_site = r0 < S0;
+    const bool kept_site = sv.has_kept && r0 < S0;
     const uint64_t first = i + (kept_site ? 1 : 0);
     const bool matrix = model.kind == 0;
     const Philox ph(call.seed);
+    const uint32_t draw0 = sv.draws_before(i);
 
     int32_t anc = -1;
     if (matrix) {
         if (kept_site) {
             anc = kept.site_allele[r0];
         } else {
-            double u;
+            double u, ut;
             if (rv.replay != nullptr) {
-                u = phase_b_uniform(rv, rv.draw_scan[i], err);
+                u = phase_b_uniform(rv, draw0, err);
             } else {
-                const uint32_t g = sv.rec_ord[r0 - KM];
-                const uint4 w = ph(g, 0u, 0u, TAG_ALLELE);
-                u = u53(w.z, w.w);
+                allele_uniforms(ph, sv.rec[r0].ord, &u, &ut);
             }
             anc = (int32_t) select_prob(u, model.num_alleles, model.root);
             rv.site_state[i] = anc;
         }
     }
-    const double x = sv.rec_pos[r0];
+    const double x = sv.key.position(i);
     double tmax = -INFINITY; // oldest node among the mutations seen so far
-    for (uint64_t j = first; j < sv.n && (j == i || !is_head(sv, j)); j++) {
+    // draws (matrix: uniforms; infinite alleles: allele numbers) before record j, redone
+    // here because the reordering above may have interleaved kept and new mutations
+    uint32_t cur = draw0;
+    for (uint64_t j = first; j < end; j++) {
         const uint32_t r = sv.val[j];
-        const int32_t node = sv.rec_node[r];
+        const bool is_new = !sv.has_kept || r >= KM;
+        const uint32_t opens = (j == i) ? 1u : 0u; // a new site's first record also takes the root draw
+        if (sv.has_kept) {
+            sv.draw_scan[j] = cur;
+        }
+        const int32_t node = sv.rec[r].node;
         int32_t par = -1;
         if (j > first) {
             int32_t u = node;
@@ -561,7 +758,7 @@ __global__ void __launch_bounds__(128) k4_resolve_kernel(TreeSeqView ts, KeptVie
                     break;
                 }
                 for (uint64_t q = j; q-- > first;) {
-                    if (sv.rec_node[sv.val[q]] == u) {
+                    if (sv.rec[sv.val[q]].node == u) {
                         par = (int32_t) q;
                         break;
                     }
@@ -575,17 +772,15 @@ __global__ void __launch_bounds__(128) k4_resolve_kernel(TreeSeqView ts, KeptVie
         rv.parent[j] = par;
         if (matrix) {
             int32_t st;
-            if (r < KM) {
+            if (!is_new) {
                 st = kept.mut_allele[r - S0];
             } else {
                 const int32_t pa = par < 0 ? anc : rv.state[par];
-                double u;
+                double u, ur;
                 if (rv.replay != nullptr) {
-                    u = phase_b_uniform(rv, (uint64_t) rv.draw_scan[j] + ((j == i) ? 1u : 0u), err);
+                    u = phase_b_uniform(rv, (uint64_t) cur + opens, err);
                 } else {
-                    const uint32_t g = sv.rec_ord[r - KM];
-                    const uint4 w = ph(g, 0u, 0u, TAG_ALLELE);
-                    u = u53(w.x, w.y);
+                    allele_uniforms(ph, sv.rec[r].ord, &ur, &u);
                 }
                 if (pa < 0) {
                     set_error(err, -51); // MSP_ERR_UNKNOWN_ALLELE
@@ -596,6 +791,7 @@ __global__ void __launch_bounds__(128) k4_resolve_kernel(TreeSeqView ts, KeptVie
             }
             rv.state[j] = st;
         }
+        cur += (is_new ? 1u : 0u) + opens;
         tmax = fmax(tmax, ts.node_time[node]);
     }
 }
@@ -619,70 +815,12 @@ MSPB_DEVFN void write_digits(char *dst, uint64_t v, uint32_t n)
     }
 }
 
-struct EmitView {
-    SortedView sv;
-    ResolveView rv;
-    KeptView kept;
-    ModelView model;
-
-    MSPB_DEVFN bool head(uint64_t i) const { return is_head(sv, i); }
-    MSPB_DEVFN bool is_mut(uint64_t i) const { return sv.val[i] >= sv.S0; }
-    MSPB_DEVFN bool is_new(uint64_t i) const { return sv.val[i] >= sv.S0 + sv.M0; }
-    MSPB_DEVFN bool new_site(uint64_t i) const { return head(i) && is_mut(i); }
-    // infinite alleles: the number given to record i's root / mutation
-    MSPB_DEVFN uint64_t root_number(uint64_t i) const { return model.start_allele + rv.draw_scan[i]; }
-    MSPB_DEVFN uint64_t mut_number(uint64_t i) const
-    {
-        return model.start_allele + rv.draw_scan[i] + (new_site(i) ? 1u : 0u);
+MSPB_DEVFN void copy_bytes(char *dst, const char *src, uint64_t n)
+{
+    for (uint64_t k = 0; k < n; k++) {
+        dst[k] = src[k];
     }
-    MSPB_DEVFN uint64_t der_len(uint64_t i) const
-    {
-        if (!is_mut(i)) {
-            return 0;
-        }
-        const uint32_t r = sv.val[i];
-        if (!is_new(i)) {
-            const uint64_t m = r - sv.S0;
-            return kept.mut_der_off[m + 1] - kept.mut_der_off[m];
-        }
-        if (model.kind == 0) {
-            const int32_t s = rv.state[i];
-            return model.allele_off[s + 1] - model.allele_off[s];
-        }
-        return num_digits(mut_number(i));
-    }
-    MSPB_DEVFN uint64_t mut_md_len(uint64_t i) const
-    {
-        if (!is_mut(i) || is_new(i)) {
-            return 0;
-        }
-        const uint64_t m = sv.val[i] - sv.S0;
-        return kept.mut_md_off[m + 1] - kept.mut_md_off[m];
-    }
-    MSPB_DEVFN uint64_t anc_len(uint64_t i) const
-    {
-        if (!head(i)) {
-            return 0;
-        }
-        const uint32_t r = sv.val[i];
-        if (r < sv.S0) {
-            return kept.site_anc_off[r + 1] - kept.site_anc_off[r];
-        }
-        if (model.kind == 0) {
-            const int32_t s = rv.site_state[i];
-            return model.allele_off[s + 1] - model.allele_off[s];
-        }
-        return num_digits(root_number(i));
-    }
-    MSPB_DEVFN uint64_t site_md_len(uint64_t i) const
-    {
-        if (!head(i) || sv.val[i] >= sv.S0) {
-            return 0;
-        }
-        const uint32_t r = sv.val[i];
-        return kept.site_md_off[r + 1] - kept.site_md_off[r];
-    }
-};
+}
 
 struct OutView {
     double *site_position;
@@ -698,80 +836,201 @@ struct OutView {
     uint64_t *mut_md_off;
 };
 
-MSPB_DEVFN void copy_bytes(char *dst, const char *src, uint64_t n)
+struct Bytes4 {
+    uint64_t der, mmd, anc, smd;
+    MSPB_DEVFN Bytes4 operator+(const Bytes4 &o) const
+    {
+        Bytes4 r;
+        r.der = der + o.der;
+        r.mmd = mmd + o.mmd;
+        r.anc = anc + o.anc;
+        r.smd = smd + o.smd;
+        return r;
+    }
+};
+
+constexpr int K5_ITEMS = 4;
+constexpr int K5_TILE = SCAN_THREADS * K5_ITEMS;
+
+// Everything K5 needs to know about one sorted record.
+struct EmitRec {
+    uint32_t r; // slot
+    bool head, is_mut, is_new, new_site;
+    int32_t state, site_state; // matrix model allele indexes
+    uint64_t mut_number, root_number; // infinite alleles
+    uint32_t der_len, mmd_len, anc_len, smd_len;
+};
+
+MSPB_DEVFN EmitRec emit_record(const SortedView &sv, const ResolveView &rv, const KeptView &kept,
+    const ModelView &model, const Philox &ph, uint64_t i, int *err)
 {
-    for (uint64_t k = 0; k < n; k++) {
-        dst[k] = src[k];
+    EmitRec q;
+    q.r = sv.has_kept ? sv.val[i] : 0u;
+    q.head = sv.head(i);
+    q.is_mut = sv.is_mut(i);
+    q.is_new = sv.is_new(i);
+    q.new_site = q.head && q.is_mut;
+    q.state = q.site_state = -1;
+    q.mut_number = q.root_number = 0;
+    q.der_len = q.mmd_len = q.anc_len = q.smd_len = 0;
+    const bool single = q.head && (i + 1 >= sv.n || sv.head(i + 1));
+    if (model.kind == 0) {
+        if (q.is_new) {
+            if (single) {
+                // a new site with one new mutation: root draw, then one transition
+                double ur, ut;
+                if (rv.replay != nullptr) {
+                    const uint64_t d = sv.draws_before(i);
+                    ur = phase_b_uniform(rv, d, err);
+                    ut = phase_b_uniform(rv, d + 1, err);
+                } else {
+                    allele_uniforms(ph, sv.rec[sv.val[i]].ord, &ur, &ut);
+                }
+                q.site_state = (int32_t) select_prob(ur, model.num_alleles, model.root);
+                q.state = (int32_t) select_prob(
+                    ut, model.num_alleles, model.matrix + (uint64_t) q.site_state * model.num_alleles);
+            } else {
+                q.state = rv.state[i];
+                if (q.new_site) {
+                    q.site_state = rv.site_state[i];
+                }
+            }
+            q.der_len = (uint32_t) (model.allele_off[q.state + 1] - model.allele_off[q.state]);
+            if (q.new_site) {
+                q.anc_len = (uint32_t) (model.allele_off[q.site_state + 1] - model.allele_off[q.site_state]);
+            }
+        }
+    } else if (q.is_new) {
+        const uint64_t d = model.start_allele + sv.draws_before(i);
+        q.root_number = d;
+        q.mut_number = d + (q.new_site ? 1u : 0u);
+        q.der_len = num_digits(q.mut_number);
+        if (q.new_site) {
+            q.anc_len = num_digits(q.root_number);
+        }
+    }
+    if (sv.has_kept) {
+        if (!q.is_mut) {
+            q.anc_len = (uint32_t) (kept.site_anc_off[q.r + 1] - kept.site_anc_off[q.r]);
+            q.smd_len = (uint32_t) (kept.site_md_off[q.r + 1] - kept.site_md_off[q.r]);
+        } else if (!q.is_new) {
+            const uint64_t m = q.r - sv.S0;
+            q.der_len = (uint32_t) (kept.mut_der_off[m + 1] - kept.mut_der_off[m]);
+            q.mmd_len = (uint32_t) (kept.mut_md_off[m + 1] - kept.mut_md_off[m]);
+        }
+    }
+    return q;
+}
+
+// Byte offsets of the ragged columns by look-back scan, and the table rows, in one pass
+// over the sorted records (lib/mutgen.c:1027-1074).  Single-record sites get their
+// alleles here; sites with several records read what K4 stored.
+__global__ void __launch_bounds__(SCAN_THREADS) k5_emit_kernel(SortedView sv, ResolveView rv, KeptView kept,
+    ModelView model, CallView call, OutView out, Lookback<Bytes4> lb, uint32_t num_tiles, const Counts3 *p1_total,
+    Bytes4 *total, const uint32_t *dense, int *err)
+{
+    __shared__ uint64_t sm[9];
+    __shared__ Bytes4 bcast;
+    if (*dense != 0u && sv.key.mode == KEY32_POS) {
+        return;
+    }
+    const uint64_t i0 = (uint64_t) blockIdx.x * K5_TILE + (uint64_t) threadIdx.x * K5_ITEMS;
+    const Philox ph(call.seed);
+    EmitRec q[K5_ITEMS];
+    Bytes4 acc = Bytes4();
+#pragma unroll
+    for (int k = 0; k < K5_ITEMS; k++) {
+        const uint64_t i = i0 + k;
+        if (i < sv.n) {
+            q[k] = emit_record(sv, rv, kept, model, ph, i, err);
+            acc.der += q[k].der_len;
+            acc.mmd += q[k].mmd_len;
+            acc.anc += q[k].anc_len;
+            acc.smd += q[k].smd_len;
+        }
+    }
+    Bytes4 agg = Bytes4(), ex = Bytes4();
+    ex.der = block_exclusive_scan<uint64_t>(acc.der, sm, &agg.der);
+    ex.anc = block_exclusive_scan<uint64_t>(acc.anc, sm, &agg.anc);
+    if (sv.has_kept) {
+        ex.mmd = block_exclusive_scan<uint64_t>(acc.mmd, sm, &agg.mmd);
+        ex.smd = block_exclusive_scan<uint64_t>(acc.smd, sm, &agg.smd);
+    }
+    Bytes4 run = lookback_exclusive<Bytes4>(lb, blockIdx.x, num_tiles, agg, &bcast, total) + ex;
+    if (blockIdx.x + 1 == num_tiles && threadIdx.x == 0) {
+        const Bytes4 all = bcast + agg; // bcast still holds this tile's exclusive prefix
+        out.site_anc_off[p1_total->s] = all.anc;
+        out.site_md_off[p1_total->s] = all.smd;
+        out.mut_der_off[p1_total->m] = all.der;
+        out.mut_md_off[p1_total->m] = all.mmd;
+    }
+#pragma unroll
+    for (int k = 0; k < K5_ITEMS; k++) {
+        const uint64_t i = i0 + k;
+        if (i >= sv.n) {
+            break;
+        }
+        const EmitRec &e = q[k];
+        const uint32_t site_row = sv.site_row[i];
+        if (e.head) {
+            out.site_position[site_row] = sv.key.position(i);
+            out.site_anc_off[site_row] = run.anc;
+            out.site_md_off[site_row] = run.smd;
+            if (!e.is_mut) {
+                copy_bytes(out.site_anc + run.anc, kept.site_anc + kept.site_anc_off[e.r], e.anc_len);
+                copy_bytes(out.site_md + run.smd, kept.site_md + kept.site_md_off[e.r], e.smd_len);
+            } else if (model.kind == 0) {
+                copy_bytes(out.site_anc + run.anc, model.alleles + model.allele_off[e.site_state], e.anc_len);
+            } else {
+                write_digits(out.site_anc + run.anc, e.root_number, e.anc_len);
+            }
+        }
+        if (e.is_mut) {
+            const uint32_t row = sv.mut_row(i);
+            const bool single = e.head && (i + 1 >= sv.n || sv.head(i + 1));
+            const Rec rc = sv.rec[sv.val[i]];
+            int32_t par = -1;
+            if (!single) {
+                const int32_t p = rv.parent[i];
+                par = p < 0 ? -1 : (int32_t) sv.mut_row((uint64_t) p);
+            }
+            out.mut_site[row] = (int32_t) site_row;
+            out.mut_node[row] = rc.node;
+            out.mut_time[row] = rc.time;
+            out.mut_parent[row] = par;
+            out.mut_der_off[row] = run.der;
+            out.mut_md_off[row] = run.mmd;
+            if (!e.is_new) {
+                const uint64_t km = e.r - sv.S0;
+                copy_bytes(out.mut_der + run.der, kept.mut_der + kept.mut_der_off[km], e.der_len);
+                copy_bytes(out.mut_md + run.mmd, kept.mut_md + kept.mut_md_off[km], e.mmd_len);
+            } else if (model.kind == 0) {
+                copy_bytes(out.mut_der + run.der, model.alleles + model.allele_off[e.state], e.der_len);
+            } else {
+                write_digits(out.mut_der + run.der, e.mut_number, e.der_len);
+            }
+        }
+        run.der += e.der_len;
+        run.mmd += e.mmd_len;
+        run.anc += e.anc_len;
+        run.smd += e.smd_len;
     }
 }
 
-// byte offsets come from four scans over the sorted records (der, mut md, anc, site md)
-__global__ void __launch_bounds__(256) k5_emit_kernel(EmitView ev, OutView out, const uint64_t *__restrict__ der_scan,
-    const uint64_t *__restrict__ mmd_scan, const uint64_t *__restrict__ anc_scan, const uint64_t *__restrict__ smd_scan)
+// Dense-genome fallback: rebuild keys as position << 32 | coarse descending time from the
+// position-sorted records, so that the next sort also orders sites internally.
+__global__ void __launch_bounds__(256) rekey_pos_time_kernel(SortedView sv, uint64_t *__restrict__ key_out,
+    uint32_t *__restrict__ val_out)
 {
     const uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
-    const SortedView &sv = ev.sv;
     if (i >= sv.n) {
         return;
     }
     const uint32_t r = sv.val[i];
-    const bool head = ev.head(i);
-    const uint32_t site_row = ev.rv.site_scan[i] + (head ? 1u : 0u) - 1u;
-    if (head) {
-        out.site_position[site_row] = sv.rec_pos[r];
-        const uint64_t ao = anc_scan[i], mo = smd_scan[i];
-        out.site_anc_off[site_row] = ao;
-        out.site_md_off[site_row] = mo;
-        if (r < sv.S0) {
-            copy_bytes(out.site_anc + ao, ev.kept.site_anc + ev.kept.site_anc_off[r], ev.anc_len(i));
-            copy_bytes(out.site_md + mo, ev.kept.site_md + ev.kept.site_md_off[r], ev.site_md_len(i));
-        } else if (ev.model.kind == 0) {
-            const int32_t s = ev.rv.site_state[i];
-            copy_bytes(out.site_anc + ao, ev.model.alleles + ev.model.allele_off[s], ev.anc_len(i));
-        } else {
-            const uint64_t v = ev.root_number(i);
-            write_digits(out.site_anc + ao, v, num_digits(v));
-        }
-    }
-    if (r >= sv.S0) {
-        const uint32_t row = ev.rv.mut_scan[i];
-        const int32_t par = ev.rv.parent[i];
-        out.mut_site[row] = (int32_t) site_row;
-        out.mut_node[row] = sv.rec_node[r];
-        out.mut_time[row] = sv.rec_time[r];
-        out.mut_parent[row] = par < 0 ? -1 : (int32_t) ev.rv.mut_scan[par];
-        const uint64_t d = der_scan[i], m = mmd_scan[i];
-        out.mut_der_off[row] = d;
-        out.mut_md_off[row] = m;
-        if (!ev.is_new(i)) {
-            const uint64_t km = r - sv.S0;
-            copy_bytes(out.mut_der + d, ev.kept.mut_der + ev.kept.mut_der_off[km], ev.der_len(i));
-            copy_bytes(out.mut_md + m, ev.kept.mut_md + ev.kept.mut_md_off[km], ev.mut_md_len(i));
-        } else if (ev.model.kind == 0) {
-            const int32_t s = ev.rv.state[i];
-            copy_bytes(out.mut_der + d, ev.model.alleles + ev.model.allele_off[s], ev.der_len(i));
-        } else {
-            const uint64_t v = ev.mut_number(i);
-            write_digits(out.mut_der + d, v, num_digits(v));
-        }
-    }
-}
-
-// After the sort: two kept sites at one position are an input error
-// (lib/mutgen.c:875-879); in the continuous genome a new mutation must not share a
-// position with any other record (the reference redraws, lib/mutgen.c:1127-1134).
-__global__ void __launch_bounds__(256) post_sort_check_kernel(SortedView sv, int discrete, uint32_t *collisions, int *err)
-{
-    const uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= sv.n || i == 0 || is_head(sv, i)) {
-        return;
-    }
-    if (sv.val[i] < sv.S0) {
-        set_error(err, -21); // MSP_ERR_DUPLICATE_SITE_POSITION
-    }
-    if (!discrete && (sv.val[i] >= sv.S0 + sv.M0 || sv.val[i - 1] >= sv.S0 + sv.M0)) {
-        atomicAdd(collisions, 1u);
-    }
+    const bool marker = sv.has_kept && r < sv.S0;
+    const uint64_t t = marker ? 0ull : ((~ordered_bits(sv.rec[r].time)) >> 32);
+    key_out[i] = ((uint64_t) sv.key.k32[i] << 32) | t;
+    val_out[i] = r;
 }
 
 } // namespace mspb

@@ -53,9 +53,10 @@ struct DBuf {
 };
 
 struct HostTotals {
-    uint32_t count_total, local_total;
-    uint32_t num_sites, num_mut_rows, num_draws, collisions;
-    uint64_t der_bytes, mmd_bytes, anc_bytes, smd_bytes;
+    uint64_t k1_total; // new mutations (low half) | those inside the slice (high half)
+    Counts3 p1; // sites, mutation rows, allele draws
+    uint32_t collisions, dense;
+    Bytes4 bytes; // ragged column sizes
     unsigned long long first_bad; // validation: (row << 16 | code index), min wins
     int err;
     uint32_t fractional_sites; // kept site positions that are not integers < 2^32
@@ -86,18 +87,18 @@ struct mspb_ctx {
     DBuf<double> map_pos, map_rate, map_cum, model_root, model_matrix, replay;
     DBuf<char> model_alleles;
     DBuf<uint64_t> model_allele_off;
+    uint64_t kept_anc_bytes = 0, kept_smd_bytes = 0, kept_der_bytes = 0, kept_mmd_bytes = 0;
     // work
-    DBuf<uint32_t> count, local, goff, loff, scan_tiles32;
-    DBuf<uint64_t> scan_tiles64;
-    DBuf<double> rec_pos, rec_time;
-    DBuf<int32_t> rec_node;
-    DBuf<uint32_t> rec_ord;
-    DBuf<uint64_t> keys0, keys1;
+    DBuf<uint32_t> goff, loff;
+    DBuf<Rec> rec;
+    DBuf<uint64_t> keys0, keys1; // 64-bit keys (ping-pong)
+    DBuf<uint32_t> k32_0, k32_1; // 32-bit keys (ping-pong)
     DBuf<uint32_t> vals0, vals1, tile_hist, rs_scan_tiles;
     DBuf<uint64_t> or_and;
+    DBuf<uint32_t> lb_flag; // look-back scan state, shared by K1, P1 and K5 (stream ordered)
+    DBuf<char> lb_agg, lb_incl;
     DBuf<uint32_t> site_scan, mut_scan, draw_scan;
     DBuf<int32_t> parent, state, site_state;
-    DBuf<uint64_t> der_scan, mmd_scan, anc_scan, smd_scan;
     DBuf<uint32_t> rp_edge, rp_interval, rp_count, rp_out_off;
     DBuf<uint64_t> rp_stream_off;
     DBuf<char> dev_totals; // HostTotals mirror
@@ -109,10 +110,11 @@ struct mspb_ctx {
     DBuf<uint64_t> o_site_anc_off, o_site_md_off, o_mut_der_off, o_mut_md_off;
     DBuf<int32_t> o_mut_site, o_mut_node, o_mut_parent;
     mspb_counts_t counts = {};
+    SortedView last_sv = {};
 };
 
 static const char *const PHASE_NAMES[MSPB_NUM_PHASES] = { "params+kept", "K1 count+scan", "K2 place", "K3 sort",
-    "order+flags", "K4 resolve", "byte scans", "K5 emit" };
+    "P1 sites", "K4 resolve", "K5 emit", "dense re-sort" };
 
 extern "C" const char *mspb_phase_name(int phase)
 {
@@ -269,10 +271,9 @@ extern "C" void mspb_ctx_destroy(mspb_ctx_t *ctx)
     REL(k_mut_site); REL(k_mut_node); REL(k_site_allele); REL(k_mut_allele);
     REL(map_pos); REL(map_rate); REL(map_cum); REL(model_root); REL(model_matrix); REL(replay);
     REL(model_alleles); REL(model_allele_off);
-    REL(count); REL(local); REL(goff); REL(loff); REL(scan_tiles32); REL(scan_tiles64);
-    REL(rec_pos); REL(rec_time); REL(rec_node); REL(rec_ord); REL(keys0); REL(keys1); REL(vals0); REL(vals1);
-    REL(tile_hist); REL(rs_scan_tiles); REL(or_and); REL(site_scan); REL(mut_scan); REL(draw_scan);
-    REL(parent); REL(state); REL(site_state); REL(der_scan); REL(mmd_scan); REL(anc_scan); REL(smd_scan);
+    REL(goff); REL(loff); REL(rec); REL(keys0); REL(keys1); REL(k32_0); REL(k32_1); REL(vals0); REL(vals1);
+    REL(tile_hist); REL(rs_scan_tiles); REL(or_and); REL(lb_flag); REL(lb_agg); REL(lb_incl);
+    REL(site_scan); REL(mut_scan); REL(draw_scan); REL(parent); REL(state); REL(site_state);
     REL(rp_edge); REL(rp_interval); REL(rp_count); REL(rp_out_off); REL(rp_stream_off); REL(dev_totals);
     REL(o_site_pos); REL(o_mut_time); REL(o_site_anc); REL(o_site_md); REL(o_mut_der); REL(o_mut_md);
     REL(o_site_anc_off); REL(o_site_md_off); REL(o_mut_der_off); REL(o_mut_md_off);
@@ -461,20 +462,24 @@ TreeSeqView make_ts_view(const mspb_ctx *ctx)
     return v;
 }
 
-int ensure_sort_buffers(mspb_ctx *ctx, uint64_t n)
+int ensure_sort_buffers(mspb_ctx *ctx, uint64_t n, bool k32, bool k64)
 {
-    const uint64_t tiles = rs_num_tiles(n > 0 ? n : 1);
-    TRY(ctx->keys0.ensure(n + 1));
-    TRY(ctx->keys1.ensure(n + 1));
+    if (k64) {
+        TRY(ctx->keys0.ensure(n + 1));
+        TRY(ctx->keys1.ensure(n + 1));
+    }
+    if (k32) {
+        TRY(ctx->k32_0.ensure(n + 1));
+        TRY(ctx->k32_1.ensure(n + 1));
+    }
     TRY(ctx->vals0.ensure(n + 1));
     TRY(ctx->vals1.ensure(n + 1));
     TRY(ctx->tile_hist.ensure((size_t) RS_MAX_PASSES * RS_BINS));
     TRY(ctx->rs_scan_tiles.ensure(rs_state_words(n)));
-    (void) tiles;
     return 0;
 }
 
-RadixSortBuffers<uint64_t> sort_buffers(mspb_ctx *ctx)
+RadixSortBuffers<uint64_t> sort_buffers64(mspb_ctx *ctx)
 {
     RadixSortBuffers<uint64_t> b;
     b.keys[0] = ctx->keys0.p;
@@ -486,6 +491,34 @@ RadixSortBuffers<uint64_t> sort_buffers(mspb_ctx *ctx)
     b.or_and = ctx->or_and.p;
     b.or_and_host = ctx->or_and_host;
     return b;
+}
+
+RadixSortBuffers<uint32_t> sort_buffers32(mspb_ctx *ctx)
+{
+    RadixSortBuffers<uint32_t> b;
+    b.keys[0] = ctx->k32_0.p;
+    b.keys[1] = ctx->k32_1.p;
+    b.vals[0] = ctx->vals0.p;
+    b.vals[1] = ctx->vals1.p;
+    b.hist = ctx->tile_hist.p;
+    b.tile_state = ctx->rs_scan_tiles.p;
+    b.or_and = ctx->or_and.p;
+    b.or_and_host = ctx->or_and_host;
+    return b;
+}
+
+// look-back state for `tiles` tiles of a scan over T; flags are cleared on the stream
+template <typename T>
+int lookback_state(mspb_ctx *ctx, uint64_t tiles, Lookback<T> *lb)
+{
+    TRY(ctx->lb_flag.ensure(tiles + 1));
+    TRY(ctx->lb_agg.ensure((tiles + 1) * sizeof(T)));
+    TRY(ctx->lb_incl.ensure((tiles + 1) * sizeof(T)));
+    CUDA_OK(cudaMemsetAsync(ctx->lb_flag.p, 0, (tiles + 1) * sizeof(uint32_t), ctx->stream));
+    lb->flag = ctx->lb_flag.p;
+    lb->agg = reinterpret_cast<T *>(ctx->lb_agg.p);
+    lb->incl = reinterpret_cast<T *>(ctx->lb_incl.p);
+    return 0;
 }
 
 } // namespace
@@ -507,6 +540,7 @@ extern "C" int mspb_ctx_load_tables(mspb_ctx_t *ctx, const mspb_tables_t *t)
         || t->num_mutations > 0x7fffffffull) {
         return MSPB_ERR_TOO_MANY_ROWS;
     }
+    ctx->kept_anc_bytes = ctx->kept_smd_bytes = ctx->kept_der_bytes = ctx->kept_mmd_bytes = 0;
     ctx->L = t->sequence_length;
     ctx->N = t->num_nodes;
     ctx->E = t->num_edges;
@@ -523,6 +557,8 @@ extern "C" int mspb_ctx_load_tables(mspb_ctx_t *ctx, const mspb_tables_t *t)
         TRY(upload(ctx->k_site_pos, t->site_position, ctx->S0, st));
         TRY(upload(ctx->k_site_anc_off, ao, ctx->S0 + 1, st));
         TRY(upload(ctx->k_site_anc, t->site_ancestral_state, (size_t) ao[ctx->S0], st));
+        ctx->kept_anc_bytes = ao[ctx->S0];
+        ctx->kept_smd_bytes = mo != nullptr ? mo[ctx->S0] : 0;
         if (mo != nullptr) {
             TRY(upload(ctx->k_site_md_off, mo, ctx->S0 + 1, st));
             TRY(upload(ctx->k_site_md, t->site_metadata, (size_t) mo[ctx->S0], st));
@@ -542,6 +578,8 @@ extern "C" int mspb_ctx_load_tables(mspb_ctx_t *ctx, const mspb_tables_t *t)
         }
         TRY(upload(ctx->k_mut_der_off, dof, ctx->M0 + 1, st));
         TRY(upload(ctx->k_mut_der, t->mutation_derived_state, (size_t) dof[ctx->M0], st));
+        ctx->kept_der_bytes = dof[ctx->M0];
+        ctx->kept_mmd_bytes = mo != nullptr ? mo[ctx->M0] : 0;
         if (mo != nullptr) {
             TRY(upload(ctx->k_mut_md_off, mo, ctx->M0 + 1, st));
             TRY(upload(ctx->k_mut_md, t->mutation_metadata, (size_t) mo[ctx->M0], st));
@@ -590,8 +628,8 @@ extern "C" int mspb_ctx_load_tables(mspb_ctx_t *ctx, const mspb_tables_t *t)
     if (ctx->E == 0) {
         CUDA_OK(cudaMemsetAsync(ctx->child_start.p, 0, (ctx->N + 2) * sizeof(uint32_t), st));
     } else {
-        TRY(ensure_sort_buffers(ctx, ctx->E));
-        RadixSortBuffers<uint64_t> sb = sort_buffers(ctx);
+        TRY(ensure_sort_buffers(ctx, ctx->E, false, true));
+        RadixSortBuffers<uint64_t> sb = sort_buffers64(ctx);
         MSPB_LAUNCH(ctx->log, "k0_child_keys", k0_child_keys_kernel<<<grid_for(ctx->E, 256), 256, 0, st>>>(ts, sb.keys[0], sb.vals[0]));
         int cur = device_radix_sort<uint64_t>(sb, ctx->E, 0, false, st, ctx->log, nullptr);
         if (cur != 0) {
@@ -768,13 +806,128 @@ KeptView make_kept_view(const mspb_ctx *ctx, bool keep)
     return k;
 }
 
-__global__ void write_final_offsets_kernel(OutView out, uint64_t S, uint64_t M, uint64_t anc, uint64_t smd, uint64_t der,
-    uint64_t mmd)
+} // namespace
+
+namespace {
+
+uint32_t digits_u64(uint64_t v)
 {
-    out.site_anc_off[S] = anc;
-    out.site_md_off[S] = smd;
-    out.mut_der_off[M] = der;
-    out.mut_md_off[M] = mmd;
+    uint32_t n = 1;
+    while (v >= 10) {
+        v /= 10;
+        n++;
+    }
+    return n;
+}
+
+// longest state a new mutation or new site can get under this model
+uint64_t max_new_state_len(const mspb_params_t *p, uint64_t Mnew)
+{
+    if (p->model_kind == MSPB_MODEL_MATRIX) {
+        uint64_t m = 0;
+        for (uint64_t a = 0; a < p->num_alleles; a++) {
+            const uint64_t len = p->allele_offset[a + 1] - p->allele_offset[a];
+            m = len > m ? len : m;
+        }
+        return m;
+    }
+    const uint64_t last = p->start_allele + 2 * Mnew + 1;
+    return last < p->start_allele ? 20 : digits_u64(last); /* 20 digits if the counter wraps */
+}
+
+struct StageB {
+    SortedView sv;
+    ResolveView rv;
+};
+
+// sort -> P1 -> K4 -> K5 for one key mode; everything is enqueued, nothing is awaited
+int run_sorted_stages(mspb_ctx *ctx, const mspb_params_t *p, const TreeSeqView &ts, const KeptView &kept,
+    const ModelView &model, CallView call, uint64_t R, uint64_t S0, uint64_t M0, const OutView &out, bool first_sort)
+{
+    cudaStream_t st = ctx->stream;
+    HostTotals *dt = (HostTotals *) ctx->dev_totals.p;
+    const bool replay = p->replay_stream != nullptr;
+    SortedView sv;
+    memset(&sv, 0, sizeof(sv));
+    sv.n = R;
+    sv.S0 = S0;
+    sv.M0 = M0;
+    sv.rec = ctx->rec.p;
+    sv.has_kept = (S0 + M0) > 0 ? 1 : 0;
+    sv.site_row = ctx->site_scan.p;
+    sv.mut_scan = ctx->mut_scan.p;
+    sv.draw_scan = ctx->draw_scan.p;
+    sv.key.mode = call.key_mode;
+    sv.key.k32 = nullptr;
+    sv.key.k64 = nullptr;
+
+    // ---- K3: stable sort by position
+    if (first_sort) {
+        CUDA_OK(cudaEventRecord(ctx->ev[3], st));
+    }
+    if (call.key_mode == KEY32_POS) {
+        RadixSortBuffers<uint32_t> sb = sort_buffers32(ctx);
+        uint64_t top = (uint64_t) std::ceil(ctx->L) - 1;
+        uint64_t varying = 1;
+        while (varying <= top) {
+            varying <<= 1;
+        }
+        varying -= 1;
+        const int cur = device_radix_sort<uint32_t>(sb, R, varying != 0 ? varying : 1, true, st, ctx->log, nullptr);
+        sv.key.k32 = sb.keys[cur];
+        sv.val = sb.vals[cur];
+    } else {
+        RadixSortBuffers<uint64_t> sb = sort_buffers64(ctx);
+        const int cur = device_radix_sort<uint64_t>(sb, R, 0, call.key_mode == KEY64_POS, st, ctx->log, nullptr);
+        sv.key.k64 = sb.keys[cur];
+        sv.val = sb.vals[cur];
+    }
+
+    // ---- P1: site boundaries, row and draw numbering
+    if (first_sort) {
+        CUDA_OK(cudaEventRecord(ctx->ev[4], st));
+    }
+    const uint32_t p1_tiles = (uint32_t) ((R + P1_TILE - 1) / P1_TILE);
+    Lookback<Counts3> lb3;
+    TRY(lookback_state<Counts3>(ctx, p1_tiles, &lb3));
+    CUDA_OK(cudaMemsetAsync(&dt->dense, 0, sizeof(uint32_t), st));
+    MSPB_LAUNCH(ctx->log, "p1_sites",
+        p1_sites_kernel<<<p1_tiles, SCAN_THREADS, 0, st>>>(sv, call.discrete, lb3, p1_tiles, &dt->p1, &dt->collisions,
+            &dt->dense, &dt->err));
+
+    // ---- K4: sites with several records
+    if (first_sort) {
+        CUDA_OK(cudaEventRecord(ctx->ev[5], st));
+    }
+    ResolveView rv;
+    rv.parent = ctx->parent.p;
+    rv.state = ctx->state.p;
+    rv.site_state = ctx->site_state.p;
+    rv.replay = nullptr;
+    rv.replay_len = 0;
+    if (replay) {
+        const uint64_t used = ctx->host->replay.draws;
+        rv.replay = ctx->replay.p + used;
+        rv.replay_len = p->replay_len - used;
+    }
+    MSPB_LAUNCH(ctx->log, "k4_resolve",
+        k4_resolve_kernel<<<grid_for(R, 128), 128, 0, st>>>(ts, kept, model, call, sv, rv, &dt->dense, &dt->err));
+
+    // ---- K5: byte offsets + rows
+    if (first_sort) {
+        CUDA_OK(cudaEventRecord(ctx->ev[6], st));
+    }
+    const uint32_t k5_tiles = (uint32_t) ((R + K5_TILE - 1) / K5_TILE);
+    Lookback<Bytes4> lb4;
+    TRY(lookback_state<Bytes4>(ctx, k5_tiles, &lb4));
+    MSPB_LAUNCH(ctx->log, "k5_emit",
+        k5_emit_kernel<<<k5_tiles, SCAN_THREADS, 0, st>>>(sv, rv, kept, model, call, out, lb4, k5_tiles, &dt->p1,
+            &dt->bytes, &dt->dense, &dt->err));
+    if (first_sort) {
+        CUDA_OK(cudaEventRecord(ctx->ev[7], st));
+    }
+    ctx->last_sv = sv;
+    return 0;
 }
 
 } // namespace
@@ -821,17 +974,19 @@ extern "C" int mspb_generate(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_count
     call.discrete = discrete ? 1 : 0;
     call.sliced = sliced ? 1 : 0;
     call.seed = p->seed;
-    call.pos_shift = (discrete && ctx->L <= 4294967296.0 && !(keep && ctx->kept_fractional)) ? 32 : -1;
+    call.key_mode = (discrete && ctx->L <= 4294967296.0 && !(keep && ctx->kept_fractional)) ? KEY32_POS : KEY64_POS;
     if (keep && p->model_kind == MSPB_MODEL_MATRIX) {
         TRY(ctx->k_site_allele.ensure(S0 + 1));
         TRY(ctx->k_mut_allele.ensure(M0 + 1));
         if (S0 > 0) {
-            MSPB_LAUNCH(ctx->log, "kept_allele_index", kept_allele_index_kernel<<<grid_for(S0, 256), 256, 0, st>>>(
-                model, S0, ctx->k_site_anc.p, ctx->k_site_anc_off.p, ctx->k_site_allele.p));
+            MSPB_LAUNCH(ctx->log, "kept_allele_index",
+                kept_allele_index_kernel<<<grid_for(S0, 256), 256, 0, st>>>(
+                    model, S0, ctx->k_site_anc.p, ctx->k_site_anc_off.p, ctx->k_site_allele.p));
         }
         if (M0 > 0) {
-            MSPB_LAUNCH(ctx->log, "kept_allele_index", kept_allele_index_kernel<<<grid_for(M0, 256), 256, 0, st>>>(
-                model, M0, ctx->k_mut_der.p, ctx->k_mut_der_off.p, ctx->k_mut_allele.p));
+            MSPB_LAUNCH(ctx->log, "kept_allele_index",
+                kept_allele_index_kernel<<<grid_for(M0, 256), 256, 0, st>>>(
+                    model, M0, ctx->k_mut_der.p, ctx->k_mut_der_off.p, ctx->k_mut_allele.p));
         }
     }
     KeptView kept = make_kept_view(ctx, keep);
@@ -842,29 +997,21 @@ extern "C" int mspb_generate(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_count
     ReplayPairs pairs;
     memset(&pairs, 0, sizeof(pairs));
     if (!replay) {
-        TRY(ctx->count.ensure(ctx->E + 1));
-        TRY(ctx->goff.ensure(ctx->E + 1));
-        TRY(ctx->scan_tiles32.ensure(scan_num_tiles(ctx->E + 1) + 1));
+        TRY(ctx->goff.ensure(ctx->E + 2));
         if (sliced) {
-            TRY(ctx->local.ensure(ctx->E + 1));
-            TRY(ctx->loff.ensure(ctx->E + 1));
+            TRY(ctx->loff.ensure(ctx->E + 2));
         }
         if (ctx->E > 0) {
-            MSPB_LAUNCH(ctx->log, "k1_count", k1_count_kernel<<<grid_for(ctx->E, 256), 256, 0, st>>>(ts, map, call, ctx->count.p, ctx->local.p));
-            const uint32_t *c = ctx->count.p;
-            device_exclusive_scan<uint32_t>(ctx->log,
-                ctx->E, [c] __device__(uint64_t i) { return c[i]; }, ctx->goff.p, ctx->scan_tiles32.p,
-                &dt->count_total, st);
-            if (sliced) {
-                const uint32_t *l = ctx->local.p;
-                device_exclusive_scan<uint32_t>(ctx->log,
-                    ctx->E, [l] __device__(uint64_t i) { return l[i]; }, ctx->loff.p, ctx->scan_tiles32.p,
-                    &dt->local_total, st);
-            }
+            const uint32_t tiles = (uint32_t) ((ctx->E + K1_TILE - 1) / K1_TILE);
+            Lookback<uint64_t> lb;
+            TRY(lookback_state<uint64_t>(ctx, tiles, &lb));
+            MSPB_LAUNCH(ctx->log, "k1_count_scan",
+                k1_count_scan_kernel<<<tiles, SCAN_THREADS, 0, st>>>(
+                    ts, map, call, lb, tiles, ctx->goff.p, sliced ? ctx->loff.p : nullptr, &dt->k1_total));
         }
         CUDA_OK(cudaMemcpyAsync(ht, dt, sizeof(HostTotals), cudaMemcpyDeviceToHost, st));
         CUDA_OK(cudaStreamSynchronize(st));
-        Mnew = sliced ? ht->local_total : ht->count_total;
+        Mnew = sliced ? (ht->k1_total >> 32) : (ht->k1_total & 0xffffffffull);
     } else {
         const uint64_t cap = p->replay_len / 2 + 1;
         TRY(upload(ctx->replay, p->replay_stream, p->replay_len, st));
@@ -879,7 +1026,9 @@ extern "C" int mspb_generate(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_count
         pairs.out_off = ctx->rp_out_off.p;
         pairs.stream_off = ctx->rp_stream_off.p;
         pairs.capacity = cap;
-        MSPB_LAUNCH(ctx->log, "replay_resolve", replay_resolve_kernel<<<1, 32, 0, st>>>(ts, map, call, ctx->replay.p, p->replay_len, pairs, &dt->replay, &dt->err));
+        MSPB_LAUNCH(ctx->log, "replay_resolve",
+            replay_resolve_kernel<<<1, 32, 0, st>>>(ts, map, call, ctx->replay.p, p->replay_len, pairs, &dt->replay,
+                &dt->err));
         CUDA_OK(cudaMemcpyAsync(ht, dt, sizeof(HostTotals), cudaMemcpyDeviceToHost, st));
         CUDA_OK(cudaStreamSynchronize(st));
         if (ht->err != 0) {
@@ -896,149 +1045,35 @@ extern "C" int mspb_generate(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_count
         return MSPB_ERR_TOO_MANY_ROWS;
     }
 
-    // ---- K2: records (kept markers, kept mutations, new mutations) and their sort keys
+    // ---- buffers: rows are bounded before the sort (M is exact, S <= S0 + Mnew)
     CUDA_OK(cudaEventRecord(ctx->ev[2], st));
-    TRY(ctx->rec_pos.ensure(R + 1));
-    TRY(ctx->rec_time.ensure(R + 1));
-    TRY(ctx->rec_node.ensure(R + 1));
-    TRY(ctx->rec_ord.ensure(Mnew + 1));
-    TRY(ensure_sort_buffers(ctx, R));
-    RadixSortBuffers<uint64_t> sb = sort_buffers(ctx);
-    if (S0 + M0 > 0) {
-        MSPB_LAUNCH(ctx->log, "fill_kept", fill_kept_kernel<<<grid_for(S0 + M0, 256), 256, 0, st>>>(
-            kept, call, ctx->rec_pos.p, ctx->rec_time.p, ctx->rec_node.p, sb.keys[0], sb.vals[0], &dt->err));
-    }
-    if (Mnew > 0) {
-        if (!replay) {
-            MSPB_LAUNCH(ctx->log, "k2_place",
-                k2_place_kernel<<<grid_for(ctx->E, 256), 256, 0, st>>>(ts, map, call, ctx->count.p, ctx->goff.p,
-                    sliced ? ctx->loff.p : ctx->goff.p, (uint32_t) (S0 + M0), ctx->rec_pos.p, ctx->rec_time.p,
-                    ctx->rec_node.p, ctx->rec_ord.p, sb.keys[0], sb.vals[0]));
-        } else {
-            MSPB_LAUNCH(ctx->log, "replay_place",
-                replay_place_kernel<<<grid_for(num_pairs, 128), 128, 0, st>>>(ts, map, call, ctx->replay.p, pairs,
-                    num_pairs, (uint32_t) (S0 + M0), ctx->rec_pos.p, ctx->rec_time.p, ctx->rec_node.p, ctx->rec_ord.p,
-                    sb.keys[0], sb.vals[0], &dt->err));
-        }
-    }
-
-    // ---- K3: order all records by (position, time descending)
-    CUDA_OK(cudaEventRecord(ctx->ev[3], st));
-    int sort_passes = 0;
-    const int cur = device_radix_sort<uint64_t>(sb, R, 0, false, st, ctx->log, &sort_passes);
-
-    // ---- exact order inside equal-key runs, site boundaries, row numbers
-    CUDA_OK(cudaEventRecord(ctx->ev[4], st));
-    SortedView sv;
-    sv.n = R;
-    sv.S0 = S0;
-    sv.M0 = M0;
-    sv.key = sb.keys[cur];
-    sv.val = sb.vals[cur];
-    sv.rec_pos = ctx->rec_pos.p;
-    sv.rec_time = ctx->rec_time.p;
-    sv.rec_node = ctx->rec_node.p;
-    sv.rec_ord = ctx->rec_ord.p;
-    sv.pos_mask = call.pos_shift >= 0 ? 0xffffffff00000000ull : ~0ull;
+    const uint64_t M = M0 + Mnew, Scap = S0 + Mnew;
+    const uint64_t maxlen = max_new_state_len(p, Mnew);
+    const uint64_t der_cap = (keep ? ctx->kept_der_bytes : 0) + Mnew * maxlen;
+    const uint64_t anc_cap = (keep ? ctx->kept_anc_bytes : 0) + Mnew * maxlen;
+    const uint64_t smd_cap = keep ? ctx->kept_smd_bytes : 0, mmd_cap = keep ? ctx->kept_mmd_bytes : 0;
+    TRY(ctx->rec.ensure(R + 1));
+    TRY(ensure_sort_buffers(ctx, R, call.key_mode == KEY32_POS, call.key_mode != KEY32_POS));
     TRY(ctx->site_scan.ensure(R + 1));
-    TRY(ctx->mut_scan.ensure(R + 1));
-    TRY(ctx->draw_scan.ensure(R + 1));
     TRY(ctx->parent.ensure(R + 1));
     TRY(ctx->state.ensure(R + 1));
     TRY(ctx->site_state.ensure(R + 1));
-    TRY(ctx->scan_tiles32.ensure(scan_num_tiles(R + 1) + 1));
-    TRY(ctx->scan_tiles64.ensure(scan_num_tiles(R + 1) + 1));
-    TRY(ctx->der_scan.ensure(R + 1));
-    TRY(ctx->mmd_scan.ensure(R + 1));
-    TRY(ctx->anc_scan.ensure(R + 1));
-    TRY(ctx->smd_scan.ensure(R + 1));
-    ResolveView rv;
-    rv.site_scan = ctx->site_scan.p;
-    rv.mut_scan = ctx->mut_scan.p;
-    rv.draw_scan = ctx->draw_scan.p;
-    rv.parent = ctx->parent.p;
-    rv.state = ctx->state.p;
-    rv.site_state = ctx->site_state.p;
-    rv.replay = nullptr;
-    rv.replay_len = 0;
-    if (replay) {
-        const uint64_t used = ht->replay.draws;
-        rv.replay = ctx->replay.p + used;
-        rv.replay_len = p->replay_len - used;
+    if (S0 + M0 > 0) {
+        TRY(ctx->mut_scan.ensure(R + 1));
+        TRY(ctx->draw_scan.ensure(R + 1));
     }
-    EmitView evw;
-    evw.sv = sv;
-    evw.rv = rv;
-    evw.kept = kept;
-    evw.model = model;
-    if (R > 0) {
-        if (R > 1) {
-            MSPB_LAUNCH(ctx->log, "finalize_runs", finalize_runs_kernel<<<grid_for(R, 256), 256, 0, st>>>(sv));
-            MSPB_LAUNCH(ctx->log, "post_sort_check",
-                post_sort_check_kernel<<<grid_for(R, 256), 256, 0, st>>>(sv, call.discrete, &dt->collisions, &dt->err));
-        }
-        device_exclusive_scan<uint32_t>(ctx->log,
-            R, [evw] __device__(uint64_t i) { return evw.head(i) ? 1u : 0u; }, ctx->site_scan.p, ctx->scan_tiles32.p,
-            &dt->num_sites, st);
-        device_exclusive_scan<uint32_t>(ctx->log,
-            R, [evw] __device__(uint64_t i) { return evw.is_mut(i) ? 1u : 0u; }, ctx->mut_scan.p, ctx->scan_tiles32.p,
-            &dt->num_mut_rows, st);
-        device_exclusive_scan<uint32_t>(ctx->log,
-            R, [evw] __device__(uint64_t i) { return (evw.is_new(i) ? 1u : 0u) + (evw.new_site(i) ? 1u : 0u); },
-            ctx->draw_scan.p, ctx->scan_tiles32.p, &dt->num_draws, st);
-    }
-
-    // ---- K4: parents and alleles, one site at a time
-    CUDA_OK(cudaEventRecord(ctx->ev[5], st));
-    if (R > 0) {
-        MSPB_LAUNCH(ctx->log, "k4_resolve",
-            k4_resolve_kernel<<<grid_for(R, 128), 128, 0, st>>>(ts, kept, model, call, sv, rv, &dt->err));
-    }
-
-    // ---- ragged column offsets
-    CUDA_OK(cudaEventRecord(ctx->ev[6], st));
-    if (R > 0) {
-        device_exclusive_scan<uint64_t>(ctx->log,
-            R, [evw] __device__(uint64_t i) { return evw.der_len(i); }, ctx->der_scan.p, ctx->scan_tiles64.p,
-            &dt->der_bytes, st);
-        device_exclusive_scan<uint64_t>(ctx->log,
-            R, [evw] __device__(uint64_t i) { return evw.mut_md_len(i); }, ctx->mmd_scan.p, ctx->scan_tiles64.p,
-            &dt->mmd_bytes, st);
-        device_exclusive_scan<uint64_t>(ctx->log,
-            R, [evw] __device__(uint64_t i) { return evw.anc_len(i); }, ctx->anc_scan.p, ctx->scan_tiles64.p,
-            &dt->anc_bytes, st);
-        device_exclusive_scan<uint64_t>(ctx->log,
-            R, [evw] __device__(uint64_t i) { return evw.site_md_len(i); }, ctx->smd_scan.p, ctx->scan_tiles64.p,
-            &dt->smd_bytes, st);
-    }
-    CUDA_OK(cudaMemcpyAsync(ht, dt, sizeof(HostTotals), cudaMemcpyDeviceToHost, st));
-    CUDA_OK(cudaStreamSynchronize(st));
-    CUDA_OK(cudaGetLastError());
-    if (ht->err != 0) {
-        return ht->err;
-    }
-    if (ht->collisions > 0) {
-        return MSPB_ERR_REPLAY_REDRAW;
-    }
-    if (replay && p->model_kind == MSPB_MODEL_MATRIX && ht->replay.draws + ht->num_draws > p->replay_len) {
-        return MSPB_ERR_REPLAY_STREAM_EXHAUSTED;
-    }
-    const uint64_t S = ht->num_sites, M = ht->num_mut_rows;
-
-    // ---- K5: write the site and mutation tables
-    CUDA_OK(cudaEventRecord(ctx->ev[7], st));
-    TRY(ctx->o_site_pos.ensure(S + 1));
-    TRY(ctx->o_site_anc.ensure(ht->anc_bytes + 1));
-    TRY(ctx->o_site_anc_off.ensure(S + 2));
-    TRY(ctx->o_site_md.ensure(ht->smd_bytes + 1));
-    TRY(ctx->o_site_md_off.ensure(S + 2));
+    TRY(ctx->o_site_pos.ensure(Scap + 1));
+    TRY(ctx->o_site_anc.ensure(anc_cap + 1));
+    TRY(ctx->o_site_anc_off.ensure(Scap + 2));
+    TRY(ctx->o_site_md.ensure(smd_cap + 1));
+    TRY(ctx->o_site_md_off.ensure(Scap + 2));
     TRY(ctx->o_mut_site.ensure(M + 1));
     TRY(ctx->o_mut_node.ensure(M + 1));
     TRY(ctx->o_mut_parent.ensure(M + 1));
     TRY(ctx->o_mut_time.ensure(M + 1));
-    TRY(ctx->o_mut_der.ensure(ht->der_bytes + 1));
+    TRY(ctx->o_mut_der.ensure(der_cap + 1));
     TRY(ctx->o_mut_der_off.ensure(M + 2));
-    TRY(ctx->o_mut_md.ensure(ht->mmd_bytes + 1));
+    TRY(ctx->o_mut_md.ensure(mmd_cap + 1));
     TRY(ctx->o_mut_md_off.ensure(M + 2));
     OutView out;
     out.site_position = ctx->o_site_pos.p;
@@ -1054,15 +1089,76 @@ extern "C" int mspb_generate(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_count
     out.mut_der_off = ctx->o_mut_der_off.p;
     out.mut_md = ctx->o_mut_md.p;
     out.mut_md_off = ctx->o_mut_md_off.p;
-    if (R > 0) {
-        MSPB_LAUNCH(ctx->log, "k5_emit", k5_emit_kernel<<<grid_for(R, 256), 256, 0, st>>>(
-            evw, out, ctx->der_scan.p, ctx->mmd_scan.p, ctx->anc_scan.p, ctx->smd_scan.p));
+
+    // ---- K2: records (kept markers, kept mutations, new mutations) and their sort keys
+    KeyView keys;
+    keys.mode = call.key_mode;
+    keys.k32 = ctx->k32_0.p;
+    keys.k64 = ctx->keys0.p;
+    if (S0 + M0 > 0) {
+        MSPB_LAUNCH(ctx->log, "fill_kept",
+            fill_kept_kernel<<<grid_for(S0 + M0, 256), 256, 0, st>>>(kept, call, ctx->rec.p, keys, &dt->err));
     }
-    MSPB_LAUNCH(ctx->log, "write_final_offsets", write_final_offsets_kernel<<<1, 1, 0, st>>>(out, S, M, ht->anc_bytes, ht->smd_bytes, ht->der_bytes, ht->mmd_bytes));
+    if (Mnew > 0) {
+        if (!replay) {
+            MSPB_LAUNCH(ctx->log, "k2_place",
+                k2_place_kernel<<<grid_for(ctx->E, K2_EDGES), K2_EDGES, 0, st>>>(ts, map, call, ctx->goff.p,
+                    sliced ? ctx->loff.p : nullptr, (uint32_t) (S0 + M0), ctx->rec.p, keys));
+        } else {
+            MSPB_LAUNCH(ctx->log, "replay_place",
+                replay_place_kernel<<<grid_for(num_pairs, 128), 128, 0, st>>>(ts, map, call, ctx->replay.p, pairs,
+                    num_pairs, (uint32_t) (S0 + M0), ctx->rec.p, keys, &dt->err));
+        }
+    }
+    if (R == 0) {
+        // no sites and no mutations: only the leading zero offsets exist
+        CUDA_OK(cudaMemsetAsync(out.site_anc_off, 0, sizeof(uint64_t), st));
+        CUDA_OK(cudaMemsetAsync(out.site_md_off, 0, sizeof(uint64_t), st));
+        CUDA_OK(cudaMemsetAsync(out.mut_der_off, 0, sizeof(uint64_t), st));
+        CUDA_OK(cudaMemsetAsync(out.mut_md_off, 0, sizeof(uint64_t), st));
+        for (int e = 3; e <= 7; e++) {
+            CUDA_OK(cudaEventRecord(ctx->ev[e], st));
+        }
+    } else {
+        TRY(run_sorted_stages(ctx, p, ts, kept, model, call, R, S0, M0, out, true));
+    }
+    CUDA_OK(cudaMemcpyAsync(ht, dt, sizeof(HostTotals), cudaMemcpyDeviceToHost, st));
+    CUDA_OK(cudaStreamSynchronize(st));
+    CUDA_OK(cudaGetLastError());
+    if (R > 0 && ht->err == 0 && ht->dense != 0 && call.key_mode == KEY32_POS) {
+        // dense genome: many mutations per site.  Sort again with time in the key so that
+        // the per-site ordering step starts from a nearly sorted run.
+        TRY(ensure_sort_buffers(ctx, R, false, true));
+        RadixSortBuffers<uint64_t> sb = sort_buffers64(ctx);
+        // the sorted values live in vals0 or vals1; write the new pairs into the other one
+        uint32_t *val_in = ctx->last_sv.val;
+        uint32_t *val_tmp = val_in == ctx->vals0.p ? ctx->vals1.p : ctx->vals0.p;
+        MSPB_LAUNCH(ctx->log, "rekey_pos_time",
+            rekey_pos_time_kernel<<<grid_for(R, 256), 256, 0, st>>>(ctx->last_sv, sb.keys[0], val_tmp));
+        if (val_tmp != sb.vals[0]) {
+            CUDA_OK(cudaMemcpyAsync(sb.vals[0], val_tmp, R * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
+        }
+        call.key_mode = KEY64_POS_TIME;
+        CUDA_OK(cudaMemsetAsync(&dt->p1, 0, sizeof(Counts3), st));
+        CUDA_OK(cudaMemsetAsync(&dt->collisions, 0, sizeof(uint32_t), st));
+        TRY(run_sorted_stages(ctx, p, ts, kept, model, call, R, S0, M0, out, false));
+        CUDA_OK(cudaMemcpyAsync(ht, dt, sizeof(HostTotals), cudaMemcpyDeviceToHost, st));
+    }
     CUDA_OK(cudaEventRecord(ctx->ev[8], st));
     CUDA_OK(cudaStreamSynchronize(st));
     CUDA_OK(cudaGetLastError());
     ctx->log.collect();
+    if (ht->err != 0) {
+        return ht->err;
+    }
+    if (ht->collisions > 0) {
+        return MSPB_ERR_REPLAY_REDRAW;
+    }
+    const uint64_t draws = ht->p1.d;
+    if (replay && p->model_kind == MSPB_MODEL_MATRIX && ht->replay.draws + draws > p->replay_len) {
+        return MSPB_ERR_REPLAY_STREAM_EXHAUSTED;
+    }
+    const uint64_t S = ht->p1.s;
     float total = 0;
     for (int i = 0; i < MSPB_NUM_PHASES; i++) {
         cudaEventElapsedTime(&ctx->phase_ms[i], ctx->ev[i], ctx->ev[i + 1]);
@@ -1073,15 +1169,14 @@ extern "C" int mspb_generate(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_count
     c.num_sites = S;
     c.num_mutations = M;
     c.num_new_mutations = Mnew;
-    c.ancestral_state_bytes = ht->anc_bytes;
-    c.site_metadata_bytes = ht->smd_bytes;
-    c.derived_state_bytes = ht->der_bytes;
-    c.mutation_metadata_bytes = ht->mmd_bytes;
+    c.ancestral_state_bytes = ht->bytes.anc;
+    c.site_metadata_bytes = ht->bytes.smd;
+    c.derived_state_bytes = ht->bytes.der;
+    c.mutation_metadata_bytes = ht->bytes.mmd;
     c.num_new_sites = S - S0;
-    c.next_allele = p->start_allele + (p->model_kind == MSPB_MODEL_INFINITE_ALLELES ? (uint64_t) ht->num_draws : 0);
-    c.draws = replay ? ht->replay.draws + (p->model_kind == MSPB_MODEL_MATRIX ? ht->num_draws : 0) : 0;
+    c.next_allele = p->start_allele + (p->model_kind == MSPB_MODEL_INFINITE_ALLELES ? draws : 0);
+    c.draws = replay ? ht->replay.draws + (p->model_kind == MSPB_MODEL_MATRIX ? draws : 0) : 0;
     c.device_ms = total;
-    (void) sort_passes;
     ctx->generated = true;
     if (counts_out != nullptr) {
         *counts_out = c;
