@@ -270,10 +270,11 @@ def pinned_like(a):
 def pinned_empty(n, dtype):
     import torch
 
-    tdt = {np.float64: torch.float64, np.int32: torch.int32, np.uint8: torch.uint8, np.uint64: torch.int64}[dtype]
+    tdt = {np.float64: torch.float64, np.int32: torch.int32, np.uint8: torch.uint8, np.uint64: torch.int64,
+           np.uint32: torch.int32}[dtype]
     t = torch.empty(int(n), dtype=tdt, pin_memory=True)
     a = t.numpy()
-    return t, (a.view(np.uint64) if dtype is np.uint64 else a)
+    return t, (a.view(dtype) if dtype in (np.uint64, np.uint32) else a)
 
 
 def slice_cuts(L, world):
@@ -319,7 +320,7 @@ def run_b200_arm(args, rank, local_rank, world):
     def params(step):
         return _native.Params(map_position=[0, L], map_rate=[w["rate"]], model=native_model(w["model"]),
                               discrete_genome=w["discrete"], keep=False, start_time=-FMAX, end_time=FMAX,
-                              seed=1000 + step, slice_left=sl, slice_right=sr)
+                              seed=1000 + step, slice_left=sl, slice_right=sr, offsets32=True)
 
     def sync_all():
         torch.cuda.synchronize()
@@ -342,6 +343,8 @@ def run_b200_arm(args, rank, local_rank, world):
     sizes = ctx.result_sizes()
     out_bufs = {}
     for name, dtype in _native._COLUMNS:
+        if name.endswith("_offset"):
+            dtype = np.uint32  # offsets32=True
         t, out_bufs[name] = pinned_empty(int(sizes[name] * 1.3) + 4096, dtype)
         hold.append(t)
     ctx.kernel_timing(True)

@@ -59,6 +59,7 @@ extern "C" {
 #define MSPB_ERR_TOO_MANY_ROWS (-1005) /* more than 2^31 - 1 sites or mutations */
 #define MSPB_ERR_UNSORTED_MUTATIONS (-1006) /* kept mutations not grouped by site */
 #define MSPB_ERR_NOT_GENERATED (-1007)
+#define MSPB_ERR_OFFSET_OVERFLOW (-1008) /* offsets32 asked for, but a column may reach 4 GiB */
 
 enum { MSPB_MODEL_MATRIX = 0, MSPB_MODEL_INFINITE_ALLELES = 1 };
 
@@ -119,6 +120,9 @@ typedef struct {
      * outputs is identical to the single-slice output. */
     double slice_left;
     double slice_right;
+    /* nonzero: the offset columns of the result are uint32 instead of uint64, as tskit's
+     * dict protocol exports them when they fit (tskit_lwt_interface.h:1634-1635) */
+    int32_t offsets32;
 } mspb_params_t;
 
 /* Row and byte counts of the result of the last mspb_generate. */
@@ -134,25 +138,27 @@ typedef struct {
     uint64_t draws; /* replay: uniforms consumed */
     uint64_t num_new_sites;
     double device_ms; /* CUDA-event time of the generate step */
+    uint64_t offset_bytes; /* width of one offset entry in the result: 8, or 4 with offsets32 */
 } mspb_counts_t;
 
 /* Output columns; caller-allocated to the sizes in mspb_counts_t (offset arrays
- * are num_rows + 1 long).  Host pointers for mspb_fetch; mspb_device_columns
- * fills the same struct with device pointers owned by the context. */
+ * are num_rows + 1 entries of counts.offset_bytes bytes: uint64, or uint32 with
+ * params.offsets32).  Host pointers for mspb_fetch; mspb_device_columns fills the
+ * same struct with device pointers owned by the context. */
 typedef struct {
     double *site_position;
     char *site_ancestral_state;
-    uint64_t *site_ancestral_state_offset;
+    void *site_ancestral_state_offset;
     char *site_metadata;
-    uint64_t *site_metadata_offset;
+    void *site_metadata_offset;
     int32_t *mutation_site;
     int32_t *mutation_node;
     int32_t *mutation_parent;
     double *mutation_time;
     char *mutation_derived_state;
-    uint64_t *mutation_derived_state_offset;
+    void *mutation_derived_state_offset;
     char *mutation_metadata;
-    uint64_t *mutation_metadata_offset;
+    void *mutation_metadata_offset;
 } mspb_columns_t;
 
 typedef struct mspb_ctx mspb_ctx_t;

@@ -69,6 +69,7 @@ class _Params(C.Structure):
         ("start_time", C.c_double), ("end_time", C.c_double),
         ("seed", C.c_uint64), ("replay_stream", C.c_void_p), ("replay_len", C.c_uint64),
         ("slice_left", C.c_double), ("slice_right", C.c_double),
+        ("offsets32", C.c_int32),
     ]
 
 
@@ -78,7 +79,7 @@ class _Counts(C.Structure):
         ("ancestral_state_bytes", C.c_uint64), ("site_metadata_bytes", C.c_uint64),
         ("derived_state_bytes", C.c_uint64), ("mutation_metadata_bytes", C.c_uint64),
         ("next_allele", C.c_uint64), ("draws", C.c_uint64), ("num_new_sites", C.c_uint64),
-        ("device_ms", C.c_double),
+        ("device_ms", C.c_double), ("offset_bytes", C.c_uint64),
     ]
 
 
@@ -166,7 +167,7 @@ class Params:
     """Keeps the numpy arrays behind a ``mspb_params_t`` alive."""
 
     def __init__(self, *, map_position, map_rate, model, discrete_genome, keep, start_time, end_time,
-                 seed=0, replay_stream=None, slice_left=0.0, slice_right=0.0):
+                 seed=0, replay_stream=None, slice_left=0.0, slice_right=0.0, offsets32=False):
         self._hold = []
         p = _Params()
         pos, rate = _c(map_position, np.float64), _c(map_rate, np.float64)
@@ -194,6 +195,7 @@ class Params:
             self._hold.append(st)
             p.replay_stream, p.replay_len = _p(st), len(st)
         p.slice_left, p.slice_right = float(slice_left), float(slice_right)
+        p.offsets32 = int(bool(offsets32))
         self.struct = p
 
 
@@ -289,7 +291,10 @@ class Context:
         sizes = self.result_sizes()
         cols = _Columns()
         arrays = {}
+        off_dtype = np.uint32 if self.counts["offset_bytes"] == 4 else np.uint64
         for name, dtype in _COLUMNS:
+            if name.endswith("_offset"):
+                dtype = off_dtype
             if out is not None:
                 buf = out[name]
                 if buf.dtype != dtype or buf.size < sizes[name]:

@@ -543,13 +543,15 @@ struct SortedView {
 };
 
 struct Counts3 {
-    uint32_t s, m, d;
+    uint32_t s, m, d; // sites, mutation rows, allele draws
+    uint32_t u; // sites with more than one record (K4's work list)
     MSPB_DEVFN Counts3 operator+(const Counts3 &o) const
     {
         Counts3 r;
         r.s = s + o.s;
         r.m = m + o.m;
         r.d = d + o.d;
+        r.u = u + o.u;
         return r;
     }
 };
@@ -562,13 +564,14 @@ constexpr int P1_TILE = SCAN_THREADS * P1_ITEMS;
 // kept sites at one position, lib/mutgen.c:875-879; a new mutation sharing a position
 // in the continuous genome, which the reference redraws, lib/mutgen.c:1127-1134).
 __global__ void __launch_bounds__(SCAN_THREADS) p1_sites_kernel(SortedView sv, int discrete, Lookback<Counts3> lb,
-    uint32_t num_tiles, Counts3 *total, uint32_t *collisions, uint32_t *dense, int *err)
+    uint32_t num_tiles, Counts3 *total, uint32_t *__restrict__ multi_list, uint32_t *collisions, uint32_t *dense,
+    int *err)
 {
     __shared__ uint64_t sm[9];
     __shared__ Counts3 bcast;
     const uint64_t i0 = (uint64_t) blockIdx.x * P1_TILE + (uint64_t) threadIdx.x * P1_ITEMS;
-    uint32_t hb = 0, mb = 0, db = 0; // per-item bit flags
-    uint64_t acc = 0; // s | m << 21 | d << 42 (tile-local, each < 2^21)
+    uint32_t hb = 0, mb = 0, db = 0, ub = 0; // per-item bit flags
+    uint64_t acc = 0; // s | m << 16 | d << 32 | u << 48 (tile-local, each < 2^16)
 #pragma unroll
     for (int k = 0; k < P1_ITEMS; k++) {
         const uint64_t i = i0 + k;
@@ -576,10 +579,12 @@ __global__ void __launch_bounds__(SCAN_THREADS) p1_sites_kernel(SortedView sv, i
             const bool h = sv.head(i);
             const bool mu = sv.is_mut(i), nw = sv.is_new(i);
             const uint32_t d = (nw ? 1u : 0u) + ((h && mu) ? 1u : 0u);
+            const bool multi = h && i + 1 < sv.n && !sv.head(i + 1);
             hb |= (h ? 1u : 0u) << k;
             mb |= (mu ? 1u : 0u) << k;
             db |= d << (2 * k);
-            acc += (h ? 1ull : 0ull) | ((mu ? 1ull : 0ull) << 21) | ((uint64_t) d << 42);
+            ub |= (multi ? 1u : 0u) << k;
+            acc += (h ? 1ull : 0ull) | ((mu ? 1ull : 0ull) << 16) | ((uint64_t) d << 32) | ((multi ? 1ull : 0ull) << 48);
             if (!h) {
                 if (sv.has_kept && sv.val[i] < sv.S0) {
                     set_error(err, -21); // MSP_ERR_DUPLICATE_SITE_POSITION
@@ -596,13 +601,15 @@ __global__ void __launch_bounds__(SCAN_THREADS) p1_sites_kernel(SortedView sv, i
     uint64_t block_total;
     const uint64_t ex = block_exclusive_scan<uint64_t>(acc, sm, &block_total);
     Counts3 agg;
-    agg.s = (uint32_t) (block_total & 0x1fffffull);
-    agg.m = (uint32_t) ((block_total >> 21) & 0x1fffffull);
-    agg.d = (uint32_t) (block_total >> 42);
+    agg.s = (uint32_t) (block_total & 0xffffull);
+    agg.m = (uint32_t) ((block_total >> 16) & 0xffffull);
+    agg.d = (uint32_t) ((block_total >> 32) & 0xffffull);
+    agg.u = (uint32_t) (block_total >> 48);
     const Counts3 pre = lookback_exclusive<Counts3>(lb, blockIdx.x, num_tiles, agg, &bcast, total);
-    uint32_t s = pre.s + (uint32_t) (ex & 0x1fffffull);
-    uint32_t m = pre.m + (uint32_t) ((ex >> 21) & 0x1fffffull);
-    uint32_t d = pre.d + (uint32_t) (ex >> 42);
+    uint32_t s = pre.s + (uint32_t) (ex & 0xffffull);
+    uint32_t m = pre.m + (uint32_t) ((ex >> 16) & 0xffffull);
+    uint32_t d = pre.d + (uint32_t) ((ex >> 32) & 0xffffull);
+    uint32_t u = pre.u + (uint32_t) (ex >> 48);
 #pragma unroll
     for (int k = 0; k < P1_ITEMS; k++) {
         const uint64_t i = i0 + k;
@@ -615,6 +622,9 @@ __global__ void __launch_bounds__(SCAN_THREADS) p1_sites_kernel(SortedView sv, i
             }
             m += (mb >> k) & 1u;
             d += (db >> (2 * k)) & 3u;
+            if ((ub >> k) & 1u) {
+                multi_list[u++] = (uint32_t) i;
+            }
         }
     }
 }
@@ -685,21 +695,32 @@ MSPB_DEVFN void allele_uniforms(const Philox &ph, uint32_t ord, double *u_root, 
     *u_root = u53(w.z, w.w);
 }
 
-// One thread per site that has more than one record: put the records in the
+// One thread per site that has more than one record (P1's work list, so that all lanes
+// of a warp are busy even when such sites are rare): put the records in the
 // reference's order, then for each mutation find the nearest ancestor-or-self node
 // already holding a mutation at this site (lib/mutgen.c:1185-1216) and draw its state.
 // The walk uses the child-sorted interval index instead of a tree sweep and stops once
 // the node is older than every earlier mutation's node.
+MSPB_DEVFN void resolve_site(const TreeSeqView &ts, const KeptView &kept, const ModelView &model, const CallView &call,
+    const SortedView &sv, const ResolveView &rv, uint64_t i, int *err);
+
 __global__ void __launch_bounds__(128) k4_resolve_kernel(TreeSeqView ts, KeptView kept, ModelView model, CallView call,
-    SortedView sv, ResolveView rv, const uint32_t *dense, int *err)
+    SortedView sv, ResolveView rv, const uint32_t *__restrict__ multi_list, const Counts3 *p1_total,
+    const uint32_t *dense, int *err)
 {
-    const uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
     if (*dense != 0u && sv.key.mode == KEY32_POS) {
         return; // the host re-sorts with time in the key and runs this step again
     }
-    if (i >= sv.n || !sv.head(i) || i + 1 >= sv.n || sv.head(i + 1)) {
-        return;
+    const uint32_t n_multi = p1_total->u;
+    for (uint64_t w = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; w < n_multi;
+         w += (uint64_t) gridDim.x * blockDim.x) {
+        resolve_site(ts, kept, model, call, sv, rv, multi_list[w], err);
     }
+}
+
+MSPB_DEVFN void resolve_site(const TreeSeqView &ts, const KeptView &kept, const ModelView &model, const CallView &call,
+    const SortedView &sv, const ResolveView &rv, uint64_t i, int *err)
+{
     uint64_t end = i + 2;
     while (end < sv.n && !sv.head(end)) {
         end++;
@@ -825,15 +846,25 @@ MSPB_DEVFN void copy_bytes(char *dst, const char *src, uint64_t n)
 struct OutView {
     double *site_position;
     char *site_anc;
-    uint64_t *site_anc_off;
+    void *site_anc_off;
     char *site_md;
-    uint64_t *site_md_off;
+    void *site_md_off;
     int32_t *mut_site, *mut_node, *mut_parent;
     double *mut_time;
     char *mut_der;
-    uint64_t *mut_der_off;
+    void *mut_der_off;
     char *mut_md;
-    uint64_t *mut_md_off;
+    void *mut_md_off;
+    int off32; // offset columns are uint32 (else uint64)
+    int write_md_off; // 0: the metadata offset columns are known to be all zero already
+    MSPB_DEVFN void store_off(void *col, uint64_t row, uint64_t v) const
+    {
+        if (off32) {
+            static_cast<uint32_t *>(col)[row] = (uint32_t) v;
+        } else {
+            static_cast<uint64_t *>(col)[row] = v;
+        }
+    }
 };
 
 struct Bytes4 {
@@ -851,11 +882,12 @@ struct Bytes4 {
 
 constexpr int K5_ITEMS = 4;
 constexpr int K5_TILE = SCAN_THREADS * K5_ITEMS;
+constexpr int K5_STAGE = 12 * 1024; // bytes of one ragged column staged per tile
 
 // Everything K5 needs to know about one sorted record.
 struct EmitRec {
     uint32_t r; // slot
-    bool head, is_mut, is_new, new_site;
+    bool head, is_mut, is_new, new_site, single;
     int32_t state, site_state; // matrix model allele indexes
     uint64_t mut_number, root_number; // infinite alleles
     uint32_t der_len, mmd_len, anc_len, smd_len;
@@ -873,10 +905,10 @@ MSPB_DEVFN EmitRec emit_record(const SortedView &sv, const ResolveView &rv, cons
     q.state = q.site_state = -1;
     q.mut_number = q.root_number = 0;
     q.der_len = q.mmd_len = q.anc_len = q.smd_len = 0;
-    const bool single = q.head && (i + 1 >= sv.n || sv.head(i + 1));
+    q.single = q.head && (i + 1 >= sv.n || sv.head(i + 1));
     if (model.kind == 0) {
         if (q.is_new) {
-            if (single) {
+            if (q.single) {
                 // a new site with one new mutation: root draw, then one transition
                 double ur, ut;
                 if (rv.replay != nullptr) {
@@ -922,98 +954,167 @@ MSPB_DEVFN EmitRec emit_record(const SortedView &sv, const ResolveView &rv, cons
     return q;
 }
 
+// Tile-local exclusive offsets of one length column held in shared memory (striped by
+// record), returning the tile total.  Thread t scans the K5_ITEMS consecutive records it
+// owns in blocked order; lens[] is overwritten with the offsets.
+MSPB_DEVFN uint64_t tile_offsets(uint32_t *lens, uint64_t *scan_tmp)
+{
+    uint32_t l[K5_ITEMS];
+    uint64_t sum = 0;
+#pragma unroll
+    for (int k = 0; k < K5_ITEMS; k++) {
+        l[k] = lens[threadIdx.x * K5_ITEMS + k];
+        sum += l[k];
+    }
+    uint64_t total;
+    uint64_t run = block_exclusive_scan<uint64_t>(sum, scan_tmp, &total);
+#pragma unroll
+    for (int k = 0; k < K5_ITEMS; k++) {
+        lens[threadIdx.x * K5_ITEMS + k] = (uint32_t) run;
+        run += l[k];
+    }
+    return total;
+}
+
+// Copies a tile's staged bytes to global memory with 16-byte stores.  The stage is
+// shifted by (global offset mod 16) so that aligned chunks line up on both sides.
+MSPB_DEVFN void flush_stage(const char *stage, char *dst_base, uint64_t g0, uint64_t total)
+{
+    const uint32_t shift = (uint32_t) (g0 & 15ull);
+    const uint64_t span = shift + total;
+    char *aligned = dst_base + (g0 - shift);
+    for (uint64_t c = threadIdx.x; c * 16 < span; c += SCAN_THREADS) {
+        const uint64_t lo = c * 16, hi = lo + 16;
+        if (lo >= shift && hi <= span) {
+            *reinterpret_cast<uint4 *>(aligned + lo) = *reinterpret_cast<const uint4 *>(stage + lo);
+        } else {
+            for (uint64_t b = lo < shift ? shift : lo; b < hi && b < span; b++) {
+                aligned[b] = stage[b];
+            }
+        }
+    }
+}
+
 // Byte offsets of the ragged columns by look-back scan, and the table rows, in one pass
 // over the sorted records (lib/mutgen.c:1027-1074).  Single-record sites get their
-// alleles here; sites with several records read what K4 stored.
+// alleles here; sites with several records read what K4 stored.  Records are handled
+// striped (thread t takes t, t + 256, ...) so that row stores are coalesced; state bytes
+// are assembled in shared memory and flushed with 16-byte stores.
 __global__ void __launch_bounds__(SCAN_THREADS) k5_emit_kernel(SortedView sv, ResolveView rv, KeptView kept,
     ModelView model, CallView call, OutView out, Lookback<Bytes4> lb, uint32_t num_tiles, const Counts3 *p1_total,
     Bytes4 *total, const uint32_t *dense, int *err)
 {
     __shared__ uint64_t sm[9];
     __shared__ Bytes4 bcast;
+    __shared__ uint32_t s_der[K5_TILE], s_anc[K5_TILE], s_mmd[K5_TILE], s_smd[K5_TILE];
+    __shared__ __align__(16) char st_der[K5_STAGE + 32];
+    __shared__ __align__(16) char st_anc[K5_STAGE + 32];
     if (*dense != 0u && sv.key.mode == KEY32_POS) {
         return;
     }
-    const uint64_t i0 = (uint64_t) blockIdx.x * K5_TILE + (uint64_t) threadIdx.x * K5_ITEMS;
+    const uint64_t base = (uint64_t) blockIdx.x * K5_TILE;
     const Philox ph(call.seed);
-    EmitRec q[K5_ITEMS];
-    Bytes4 acc = Bytes4();
+    // ---- lengths
 #pragma unroll
     for (int k = 0; k < K5_ITEMS; k++) {
-        const uint64_t i = i0 + k;
+        const uint32_t j = (uint32_t) k * SCAN_THREADS + threadIdx.x;
+        const uint64_t i = base + j;
+        uint32_t d = 0, a = 0, md = 0, sd = 0;
         if (i < sv.n) {
-            q[k] = emit_record(sv, rv, kept, model, ph, i, err);
-            acc.der += q[k].der_len;
-            acc.mmd += q[k].mmd_len;
-            acc.anc += q[k].anc_len;
-            acc.smd += q[k].smd_len;
+            const EmitRec q = emit_record(sv, rv, kept, model, ph, i, err);
+            d = q.der_len;
+            a = q.anc_len;
+            md = q.mmd_len;
+            sd = q.smd_len;
+        }
+        s_der[j] = d;
+        s_anc[j] = a;
+        if (sv.has_kept) {
+            s_mmd[j] = md;
+            s_smd[j] = sd;
         }
     }
-    Bytes4 agg = Bytes4(), ex = Bytes4();
-    ex.der = block_exclusive_scan<uint64_t>(acc.der, sm, &agg.der);
-    ex.anc = block_exclusive_scan<uint64_t>(acc.anc, sm, &agg.anc);
+    __syncthreads();
+    // ---- offsets: inside the tile, then across tiles
+    Bytes4 agg = Bytes4();
+    agg.der = tile_offsets(s_der, sm);
+    agg.anc = tile_offsets(s_anc, sm);
     if (sv.has_kept) {
-        ex.mmd = block_exclusive_scan<uint64_t>(acc.mmd, sm, &agg.mmd);
-        ex.smd = block_exclusive_scan<uint64_t>(acc.smd, sm, &agg.smd);
+        agg.mmd = tile_offsets(s_mmd, sm);
+        agg.smd = tile_offsets(s_smd, sm);
     }
-    Bytes4 run = lookback_exclusive<Bytes4>(lb, blockIdx.x, num_tiles, agg, &bcast, total) + ex;
+    const Bytes4 pre = lookback_exclusive<Bytes4>(lb, blockIdx.x, num_tiles, agg, &bcast, total);
     if (blockIdx.x + 1 == num_tiles && threadIdx.x == 0) {
-        const Bytes4 all = bcast + agg; // bcast still holds this tile's exclusive prefix
-        out.site_anc_off[p1_total->s] = all.anc;
-        out.site_md_off[p1_total->s] = all.smd;
-        out.mut_der_off[p1_total->m] = all.der;
-        out.mut_md_off[p1_total->m] = all.mmd;
+        out.store_off(out.site_anc_off, p1_total->s, pre.anc + agg.anc);
+        out.store_off(out.mut_der_off, p1_total->m, pre.der + agg.der);
+        if (out.write_md_off) {
+            out.store_off(out.site_md_off, p1_total->s, pre.smd + agg.smd);
+            out.store_off(out.mut_md_off, p1_total->m, pre.mmd + agg.mmd);
+        }
     }
+    const bool stage_der = agg.der <= K5_STAGE, stage_anc = agg.anc <= K5_STAGE;
+    char *der_base = stage_der ? st_der + (pre.der & 15ull) : out.mut_der + pre.der;
+    char *anc_base = stage_anc ? st_anc + (pre.anc & 15ull) : out.site_anc + pre.anc;
+    // ---- rows and bytes
 #pragma unroll
     for (int k = 0; k < K5_ITEMS; k++) {
-        const uint64_t i = i0 + k;
+        const uint32_t j = (uint32_t) k * SCAN_THREADS + threadIdx.x;
+        const uint64_t i = base + j;
         if (i >= sv.n) {
-            break;
+            continue;
         }
-        const EmitRec &e = q[k];
+        const EmitRec e = emit_record(sv, rv, kept, model, ph, i, err);
         const uint32_t site_row = sv.site_row[i];
         if (e.head) {
+            char *anc_dst = anc_base + s_anc[j];
             out.site_position[site_row] = sv.key.position(i);
-            out.site_anc_off[site_row] = run.anc;
-            out.site_md_off[site_row] = run.smd;
+            out.store_off(out.site_anc_off, site_row, pre.anc + s_anc[j]);
+            if (out.write_md_off) {
+                out.store_off(out.site_md_off, site_row, pre.smd + (sv.has_kept ? s_smd[j] : 0u));
+            }
             if (!e.is_mut) {
-                copy_bytes(out.site_anc + run.anc, kept.site_anc + kept.site_anc_off[e.r], e.anc_len);
-                copy_bytes(out.site_md + run.smd, kept.site_md + kept.site_md_off[e.r], e.smd_len);
+                copy_bytes(anc_dst, kept.site_anc + kept.site_anc_off[e.r], e.anc_len);
+                copy_bytes(out.site_md + pre.smd + s_smd[j], kept.site_md + kept.site_md_off[e.r], e.smd_len);
             } else if (model.kind == 0) {
-                copy_bytes(out.site_anc + run.anc, model.alleles + model.allele_off[e.site_state], e.anc_len);
+                copy_bytes(anc_dst, model.alleles + model.allele_off[e.site_state], e.anc_len);
             } else {
-                write_digits(out.site_anc + run.anc, e.root_number, e.anc_len);
+                write_digits(anc_dst, e.root_number, e.anc_len);
             }
         }
         if (e.is_mut) {
             const uint32_t row = sv.mut_row(i);
-            const bool single = e.head && (i + 1 >= sv.n || sv.head(i + 1));
             const Rec rc = sv.rec[sv.val[i]];
             int32_t par = -1;
-            if (!single) {
+            if (!e.single) {
                 const int32_t p = rv.parent[i];
                 par = p < 0 ? -1 : (int32_t) sv.mut_row((uint64_t) p);
             }
+            char *der_dst = der_base + s_der[j];
             out.mut_site[row] = (int32_t) site_row;
             out.mut_node[row] = rc.node;
             out.mut_time[row] = rc.time;
             out.mut_parent[row] = par;
-            out.mut_der_off[row] = run.der;
-            out.mut_md_off[row] = run.mmd;
+            out.store_off(out.mut_der_off, row, pre.der + s_der[j]);
+            if (out.write_md_off) {
+                out.store_off(out.mut_md_off, row, pre.mmd + (sv.has_kept ? s_mmd[j] : 0u));
+            }
             if (!e.is_new) {
                 const uint64_t km = e.r - sv.S0;
-                copy_bytes(out.mut_der + run.der, kept.mut_der + kept.mut_der_off[km], e.der_len);
-                copy_bytes(out.mut_md + run.mmd, kept.mut_md + kept.mut_md_off[km], e.mmd_len);
+                copy_bytes(der_dst, kept.mut_der + kept.mut_der_off[km], e.der_len);
+                copy_bytes(out.mut_md + pre.mmd + s_mmd[j], kept.mut_md + kept.mut_md_off[km], e.mmd_len);
             } else if (model.kind == 0) {
-                copy_bytes(out.mut_der + run.der, model.alleles + model.allele_off[e.state], e.der_len);
+                copy_bytes(der_dst, model.alleles + model.allele_off[e.state], e.der_len);
             } else {
-                write_digits(out.mut_der + run.der, e.mut_number, e.der_len);
+                write_digits(der_dst, e.mut_number, e.der_len);
             }
         }
-        run.der += e.der_len;
-        run.mmd += e.mmd_len;
-        run.anc += e.anc_len;
-        run.smd += e.smd_len;
+    }
+    __syncthreads();
+    if (stage_der) {
+        flush_stage(st_der, out.mut_der, pre.der, agg.der);
+    }
+    if (stage_anc) {
+        flush_stage(st_anc, out.site_anc, pre.anc, agg.anc);
     }
 }
 

@@ -97,7 +97,7 @@ struct mspb_ctx {
     DBuf<uint64_t> or_and;
     DBuf<uint32_t> lb_flag; // look-back scan state, shared by K1, P1 and K5 (stream ordered)
     DBuf<char> lb_agg, lb_incl;
-    DBuf<uint32_t> site_scan, mut_scan, draw_scan;
+    DBuf<uint32_t> site_scan, mut_scan, draw_scan, multi_list;
     DBuf<int32_t> parent, state, site_state;
     DBuf<uint32_t> rp_edge, rp_interval, rp_count, rp_out_off;
     DBuf<uint64_t> rp_stream_off;
@@ -111,6 +111,9 @@ struct mspb_ctx {
     DBuf<int32_t> o_mut_site, o_mut_node, o_mut_parent;
     mspb_counts_t counts = {};
     SortedView last_sv = {};
+    // leading bytes of the metadata offset columns known to be zero (and for which buffer)
+    const void *md_zero_site_ptr = nullptr, *md_zero_mut_ptr = nullptr;
+    uint64_t md_zero_site_bytes = 0, md_zero_mut_bytes = 0;
 };
 
 static const char *const PHASE_NAMES[MSPB_NUM_PHASES] = { "params+kept", "K1 count+scan", "K2 place", "K3 sort",
@@ -176,6 +179,8 @@ extern "C" const char *mspb_strerror(int err)
             return "Too many rows for 32-bit ids";
         case MSPB_ERR_UNSORTED_MUTATIONS:
             return "Kept mutations must be grouped by site in site order";
+        case MSPB_ERR_OFFSET_OVERFLOW:
+            return "A ragged column may exceed 4 GiB: 32-bit offsets cannot be used";
         case MSPB_ERR_NOT_GENERATED:
             return "No result is resident: call mspb_generate first";
         default:
@@ -273,7 +278,7 @@ extern "C" void mspb_ctx_destroy(mspb_ctx_t *ctx)
     REL(model_alleles); REL(model_allele_off);
     REL(goff); REL(loff); REL(rec); REL(keys0); REL(keys1); REL(k32_0); REL(k32_1); REL(vals0); REL(vals1);
     REL(tile_hist); REL(rs_scan_tiles); REL(or_and); REL(lb_flag); REL(lb_agg); REL(lb_incl);
-    REL(site_scan); REL(mut_scan); REL(draw_scan); REL(parent); REL(state); REL(site_state);
+    REL(site_scan); REL(mut_scan); REL(draw_scan); REL(multi_list); REL(parent); REL(state); REL(site_state);
     REL(rp_edge); REL(rp_interval); REL(rp_count); REL(rp_out_off); REL(rp_stream_off); REL(dev_totals);
     REL(o_site_pos); REL(o_mut_time); REL(o_site_anc); REL(o_site_md); REL(o_mut_der); REL(o_mut_md);
     REL(o_site_anc_off); REL(o_site_md_off); REL(o_mut_der_off); REL(o_mut_md_off);
@@ -892,8 +897,8 @@ int run_sorted_stages(mspb_ctx *ctx, const mspb_params_t *p, const TreeSeqView &
     TRY(lookback_state<Counts3>(ctx, p1_tiles, &lb3));
     CUDA_OK(cudaMemsetAsync(&dt->dense, 0, sizeof(uint32_t), st));
     MSPB_LAUNCH(ctx->log, "p1_sites",
-        p1_sites_kernel<<<p1_tiles, SCAN_THREADS, 0, st>>>(sv, call.discrete, lb3, p1_tiles, &dt->p1, &dt->collisions,
-            &dt->dense, &dt->err));
+        p1_sites_kernel<<<p1_tiles, SCAN_THREADS, 0, st>>>(sv, call.discrete, lb3, p1_tiles, &dt->p1,
+            ctx->multi_list.p, &dt->collisions, &dt->dense, &dt->err));
 
     // ---- K4: sites with several records
     if (first_sort) {
@@ -911,7 +916,8 @@ int run_sorted_stages(mspb_ctx *ctx, const mspb_params_t *p, const TreeSeqView &
         rv.replay_len = p->replay_len - used;
     }
     MSPB_LAUNCH(ctx->log, "k4_resolve",
-        k4_resolve_kernel<<<grid_for(R, 128), 128, 0, st>>>(ts, kept, model, call, sv, rv, &dt->dense, &dt->err));
+        k4_resolve_kernel<<<148 * 16, 128, 0, st>>>(ts, kept, model, call, sv, rv, ctx->multi_list.p, &dt->p1,
+            &dt->dense, &dt->err));
 
     // ---- K5: byte offsets + rows
     if (first_sort) {
@@ -1055,6 +1061,7 @@ extern "C" int mspb_generate(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_count
     TRY(ctx->rec.ensure(R + 1));
     TRY(ensure_sort_buffers(ctx, R, call.key_mode == KEY32_POS, call.key_mode != KEY32_POS));
     TRY(ctx->site_scan.ensure(R + 1));
+    TRY(ctx->multi_list.ensure(R / 2 + 2));
     TRY(ctx->parent.ensure(R + 1));
     TRY(ctx->state.ensure(R + 1));
     TRY(ctx->site_state.ensure(R + 1));
@@ -1075,7 +1082,30 @@ extern "C" int mspb_generate(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_count
     TRY(ctx->o_mut_der_off.ensure(M + 2));
     TRY(ctx->o_mut_md.ensure(mmd_cap + 1));
     TRY(ctx->o_mut_md_off.ensure(M + 2));
+    const bool off32 = p->offsets32 != 0;
+    if (off32 && (der_cap >= 0xffffffffull || anc_cap >= 0xffffffffull || smd_cap >= 0xffffffffull
+                     || mmd_cap >= 0xffffffffull)) {
+        return MSPB_ERR_OFFSET_OVERFLOW;
+    }
+    const uint64_t ow = off32 ? 4 : 8;
     OutView out;
+    out.off32 = off32 ? 1 : 0;
+    out.write_md_off = (smd_cap + mmd_cap) > 0 ? 1 : 0;
+    if (out.write_md_off) {
+        ctx->md_zero_site_bytes = ctx->md_zero_mut_bytes = 0;
+    } else {
+        // metadata offsets are all zero: clear the columns only if they are not zero already
+        if (ctx->md_zero_site_ptr != ctx->o_site_md_off.p || ctx->md_zero_site_bytes < (Scap + 2) * ow) {
+            CUDA_OK(cudaMemsetAsync(ctx->o_site_md_off.p, 0, ctx->o_site_md_off.cap * sizeof(uint64_t), st));
+            ctx->md_zero_site_ptr = ctx->o_site_md_off.p;
+            ctx->md_zero_site_bytes = ctx->o_site_md_off.cap * sizeof(uint64_t);
+        }
+        if (ctx->md_zero_mut_ptr != ctx->o_mut_md_off.p || ctx->md_zero_mut_bytes < (M + 2) * ow) {
+            CUDA_OK(cudaMemsetAsync(ctx->o_mut_md_off.p, 0, ctx->o_mut_md_off.cap * sizeof(uint64_t), st));
+            ctx->md_zero_mut_ptr = ctx->o_mut_md_off.p;
+            ctx->md_zero_mut_bytes = ctx->o_mut_md_off.cap * sizeof(uint64_t);
+        }
+    }
     out.site_position = ctx->o_site_pos.p;
     out.site_anc = ctx->o_site_anc.p;
     out.site_anc_off = ctx->o_site_anc_off.p;
@@ -1116,6 +1146,7 @@ extern "C" int mspb_generate(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_count
         CUDA_OK(cudaMemsetAsync(out.site_md_off, 0, sizeof(uint64_t), st));
         CUDA_OK(cudaMemsetAsync(out.mut_der_off, 0, sizeof(uint64_t), st));
         CUDA_OK(cudaMemsetAsync(out.mut_md_off, 0, sizeof(uint64_t), st));
+        ctx->md_zero_site_bytes = ctx->md_zero_mut_bytes = 0;
         for (int e = 3; e <= 7; e++) {
             CUDA_OK(cudaEventRecord(ctx->ev[e], st));
         }
@@ -1177,6 +1208,7 @@ extern "C" int mspb_generate(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_count
     c.next_allele = p->start_allele + (p->model_kind == MSPB_MODEL_INFINITE_ALLELES ? draws : 0);
     c.draws = replay ? ht->replay.draws + (p->model_kind == MSPB_MODEL_MATRIX ? draws : 0) : 0;
     c.device_ms = total;
+    c.offset_bytes = ow;
     ctx->generated = true;
     if (counts_out != nullptr) {
         *counts_out = c;
@@ -1219,7 +1251,7 @@ extern "C" int mspb_fetch(mspb_ctx_t *ctx, const mspb_columns_t *h)
     CUDA_OK(cudaSetDevice(ctx->device));
     cudaStream_t st = ctx->stream;
     const mspb_counts_t &c = ctx->counts;
-    const uint64_t S = c.num_sites, M = c.num_mutations;
+    const uint64_t S = c.num_sites, M = c.num_mutations, ow = c.offset_bytes;
 #define D2H(dst, src, bytes)                                                                                           \
     do {                                                                                                               \
         if ((dst) != nullptr && (bytes) > 0) {                                                                         \
@@ -1228,17 +1260,17 @@ extern "C" int mspb_fetch(mspb_ctx_t *ctx, const mspb_columns_t *h)
     } while (0)
     D2H(h->site_position, ctx->o_site_pos.p, S * sizeof(double));
     D2H(h->site_ancestral_state, ctx->o_site_anc.p, c.ancestral_state_bytes);
-    D2H(h->site_ancestral_state_offset, ctx->o_site_anc_off.p, (S + 1) * sizeof(uint64_t));
+    D2H(h->site_ancestral_state_offset, ctx->o_site_anc_off.p, (S + 1) * ow);
     D2H(h->site_metadata, ctx->o_site_md.p, c.site_metadata_bytes);
-    D2H(h->site_metadata_offset, ctx->o_site_md_off.p, (S + 1) * sizeof(uint64_t));
+    D2H(h->site_metadata_offset, ctx->o_site_md_off.p, (S + 1) * ow);
     D2H(h->mutation_site, ctx->o_mut_site.p, M * sizeof(int32_t));
     D2H(h->mutation_node, ctx->o_mut_node.p, M * sizeof(int32_t));
     D2H(h->mutation_parent, ctx->o_mut_parent.p, M * sizeof(int32_t));
     D2H(h->mutation_time, ctx->o_mut_time.p, M * sizeof(double));
     D2H(h->mutation_derived_state, ctx->o_mut_der.p, c.derived_state_bytes);
-    D2H(h->mutation_derived_state_offset, ctx->o_mut_der_off.p, (M + 1) * sizeof(uint64_t));
+    D2H(h->mutation_derived_state_offset, ctx->o_mut_der_off.p, (M + 1) * ow);
     D2H(h->mutation_metadata, ctx->o_mut_md.p, c.mutation_metadata_bytes);
-    D2H(h->mutation_metadata_offset, ctx->o_mut_md_off.p, (M + 1) * sizeof(uint64_t));
+    D2H(h->mutation_metadata_offset, ctx->o_mut_md_off.p, (M + 1) * ow);
 #undef D2H
     CUDA_OK(cudaStreamSynchronize(st));
     return 0;
@@ -1286,17 +1318,17 @@ extern "C" int mspb_sim_mutations(int device, const mspb_tables_t *tables, const
         const uint64_t S = c.num_sites, M = c.num_mutations;
         out->site_position = (double *) malloc((S + 1) * sizeof(double));
         out->site_ancestral_state = (char *) malloc(c.ancestral_state_bytes + 1);
-        out->site_ancestral_state_offset = (uint64_t *) malloc((S + 1) * sizeof(uint64_t));
+        out->site_ancestral_state_offset = malloc((S + 1) * sizeof(uint64_t));
         out->site_metadata = (char *) malloc(c.site_metadata_bytes + 1);
-        out->site_metadata_offset = (uint64_t *) malloc((S + 1) * sizeof(uint64_t));
+        out->site_metadata_offset = malloc((S + 1) * sizeof(uint64_t));
         out->mutation_site = (int32_t *) malloc((M + 1) * sizeof(int32_t));
         out->mutation_node = (int32_t *) malloc((M + 1) * sizeof(int32_t));
         out->mutation_parent = (int32_t *) malloc((M + 1) * sizeof(int32_t));
         out->mutation_time = (double *) malloc((M + 1) * sizeof(double));
         out->mutation_derived_state = (char *) malloc(c.derived_state_bytes + 1);
-        out->mutation_derived_state_offset = (uint64_t *) malloc((M + 1) * sizeof(uint64_t));
+        out->mutation_derived_state_offset = malloc((M + 1) * sizeof(uint64_t));
         out->mutation_metadata = (char *) malloc(c.mutation_metadata_bytes + 1);
-        out->mutation_metadata_offset = (uint64_t *) malloc((M + 1) * sizeof(uint64_t));
+        out->mutation_metadata_offset = malloc((M + 1) * sizeof(uint64_t));
         if (!out->site_position || !out->site_ancestral_state || !out->site_ancestral_state_offset
             || !out->site_metadata || !out->site_metadata_offset || !out->mutation_site || !out->mutation_node
             || !out->mutation_parent || !out->mutation_time || !out->mutation_derived_state
