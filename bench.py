@@ -253,7 +253,8 @@ def algorithmic_bytes(kernel, n):
         # key in (records of multi-mutation sites are a small fraction)
         "k4_resolve": R * n["KB"],
         # key, val, site row, one 32 B sector per gathered Rec in; table rows + ragged bytes out
-        "k5_emit": R * (n["KB"] + 4 + 4 + 32) + M * (4 + 4 + 4 + 8 + 16) + S * (8 + 16) + n["DB"] + n["AB"],
+        # (offset columns are uint32; all-zero metadata offsets are not rewritten)
+        "k5_emit": R * (n["KB"] + 4 + 4 + 32) + M * (4 + 4 + 4 + 8 + 4) + S * (8 + 4) + n["DB"] + n["AB"],
     }
     return table.get(kernel)
 

@@ -35,10 +35,17 @@ struct TreeSeqView {
     const double *node_time;
     const double *edge_left, *edge_right;
     const int32_t *edge_parent, *edge_child;
-    // child-sorted interval index (K0): edges of child c are ci_*[child_start[c] .. child_start[c+1])
+    // child-sorted interval index (K0): the edges of child c are ci[child_start[c] .. child_start[c+1]),
+    // one 32-byte entry per edge so that a step of the parent walk costs one sector
     const uint32_t *child_start;
-    const double *ci_left, *ci_right;
-    const int32_t *ci_parent;
+    const struct ChildIv *ci;
+};
+
+struct __align__(32) ChildIv {
+    double left, right;
+    double parent_time;
+    int32_t parent;
+    int32_t pad;
 };
 
 struct KeptView {
@@ -138,15 +145,18 @@ __global__ void k0_child_keys2_kernel(TreeSeqView ts, const uint32_t *val, uint6
     }
 }
 
-__global__ void k0_permute_kernel(TreeSeqView ts, const uint32_t *perm, double *ci_left, double *ci_right,
-    int32_t *ci_parent, uint32_t *child_start)
+__global__ void k0_permute_kernel(TreeSeqView ts, const uint32_t *perm, ChildIv *ci, uint32_t *child_start)
 {
     const uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
     if (i < ts.num_edges) {
         const uint32_t e = perm[i];
-        ci_left[i] = ts.edge_left[e];
-        ci_right[i] = ts.edge_right[e];
-        ci_parent[i] = ts.edge_parent[e];
+        ChildIv iv;
+        iv.left = ts.edge_left[e];
+        iv.right = ts.edge_right[e];
+        iv.parent = ts.edge_parent[e];
+        iv.parent_time = ts.node_time[iv.parent];
+        iv.pad = 0;
+        ci[i] = iv;
         // CSR starts: child c begins at the first i whose child is >= c
         const uint32_t c = (uint32_t) ts.edge_child[e];
         const uint32_t prev = i == 0 ? 0u : (uint32_t) ts.edge_child[perm[i - 1]] + 1u;
@@ -161,25 +171,24 @@ __global__ void k0_permute_kernel(TreeSeqView ts, const uint32_t *perm, double *
     }
 }
 
-// parent of node u at position x in the local tree, or -1
-MSPB_DEVFN int32_t parent_at(const TreeSeqView &ts, int32_t u, double x)
+// parent of node u at position x in the local tree (or -1), and that parent's time
+MSPB_DEVFN int32_t parent_at(const TreeSeqView &ts, int32_t u, double x, double *parent_time)
 {
     uint32_t lo = ts.child_start[u], hi = ts.child_start[u + 1];
-    const uint32_t first = lo;
-    // last interval with left <= x
+    // the interval that contains x, if any (intervals of one child are disjoint and sorted)
     while (lo < hi) {
         const uint32_t mid = (lo + hi) >> 1;
-        if (ts.ci_left[mid] <= x) {
+        const ChildIv iv = ts.ci[mid];
+        if (x < iv.left) {
+            hi = mid;
+        } else if (x >= iv.right) {
             lo = mid + 1;
         } else {
-            hi = mid;
+            *parent_time = iv.parent_time;
+            return iv.parent;
         }
     }
-    if (lo == first) {
-        return -1;
-    }
-    lo--;
-    return x < ts.ci_right[lo] ? ts.ci_parent[lo] : -1;
+    return -1;
 }
 
 
@@ -229,14 +238,15 @@ __global__ void __launch_bounds__(SCAN_THREADS) k1_count_scan_kernel(TreeSeqView
 {
     __shared__ uint64_t sm[9];
     __shared__ uint64_t bcast;
-    const uint64_t e0 = (uint64_t) blockIdx.x * K1_TILE + (uint64_t) threadIdx.x * K1_ITEMS;
-    uint64_t c[K1_ITEMS];
-    uint64_t acc = 0;
+    __shared__ uint64_t s_c[K1_TILE];
+    const uint64_t tile_base = (uint64_t) blockIdx.x * K1_TILE;
     const Philox ph(call.seed);
+    // striped: consecutive threads take consecutive edges (coalesced column reads)
 #pragma unroll
     for (int k = 0; k < K1_ITEMS; k++) {
-        const uint64_t e = e0 + k;
-        c[k] = 0;
+        const uint32_t j = (uint32_t) k * SCAN_THREADS + threadIdx.x;
+        const uint64_t e = tile_base + j;
+        uint64_t c = 0;
         if (e < ts.num_edges) {
             const EdgeDraw d = edge_draw(ts, map, call, e);
             const double mu = (d.branch_end - d.branch_start) * d.mass;
@@ -244,14 +254,23 @@ __global__ void __launch_bounds__(SCAN_THREADS) k1_count_scan_kernel(TreeSeqView
             const uint32_t n = poisson_native(rng, mu);
             uint32_t in = 0;
             if (call.sliced && n > 0 && d.left < call.slice_right && d.right > call.slice_left) {
-                for (uint32_t j = 0; j < n; j++) {
+                for (uint32_t q = 0; q < n; q++) {
                     double x, t;
-                    place_one(ph, map, d, e, j, &x, &t);
+                    place_one(ph, map, d, e, q, &x, &t);
                     in += (x >= call.slice_left && x < call.slice_right) ? 1u : 0u;
                 }
             }
-            c[k] = (uint64_t) n | ((uint64_t) in << 32);
+            c = (uint64_t) n | ((uint64_t) in << 32);
         }
+        s_c[j] = c;
+    }
+    __syncthreads();
+    // blocked: thread t scans the K1_ITEMS consecutive edges it owns
+    uint64_t c[K1_ITEMS];
+    uint64_t acc = 0;
+#pragma unroll
+    for (int k = 0; k < K1_ITEMS; k++) {
+        c[k] = s_c[threadIdx.x * K1_ITEMS + k];
         acc += c[k];
     }
     uint64_t block_total;
@@ -259,15 +278,23 @@ __global__ void __launch_bounds__(SCAN_THREADS) k1_count_scan_kernel(TreeSeqView
     uint64_t run = lookback_exclusive<uint64_t>(lb, blockIdx.x, num_tiles, block_total, &bcast, total) + ex;
 #pragma unroll
     for (int k = 0; k < K1_ITEMS; k++) {
-        const uint64_t e = e0 + k;
+        s_c[threadIdx.x * K1_ITEMS + k] = run;
+        run += c[k];
+    }
+    if (tile_base + (uint64_t) threadIdx.x * K1_ITEMS + K1_ITEMS >= ts.num_edges
+        && tile_base + (uint64_t) threadIdx.x * K1_ITEMS < ts.num_edges) {
+        goff[ts.num_edges] = (uint32_t) run; // the thread that owns the last edge
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < K1_ITEMS; k++) {
+        const uint32_t j = (uint32_t) k * SCAN_THREADS + threadIdx.x;
+        const uint64_t e = tile_base + j;
         if (e < ts.num_edges) {
-            goff[e] = (uint32_t) run;
+            const uint64_t v = s_c[j];
+            goff[e] = (uint32_t) v;
             if (loff != nullptr) {
-                loff[e] = (uint32_t) (run >> 32);
-            }
-            run += c[k];
-            if (e + 1 == ts.num_edges) {
-                goff[e + 1] = (uint32_t) run;
+                loff[e] = (uint32_t) (v >> 32);
             }
         }
     }
@@ -772,10 +799,12 @@ MSPB_DEVFN void resolve_site(const TreeSeqView &ts, const KeptView &kept, const 
         }
         const int32_t node = sv.rec[r].node;
         int32_t par = -1;
+        const double node_t = ts.node_time[node];
         if (j > first) {
             int32_t u = node;
+            double tu = node_t;
             while (u != -1) {
-                if (ts.node_time[u] > tmax) {
+                if (tu > tmax) {
                     break;
                 }
                 for (uint64_t q = j; q-- > first;) {
@@ -787,7 +816,7 @@ MSPB_DEVFN void resolve_site(const TreeSeqView &ts, const KeptView &kept, const 
                 if (par >= 0) {
                     break;
                 }
-                u = parent_at(ts, u, x);
+                u = parent_at(ts, u, x, &tu);
             }
         }
         rv.parent[j] = par;
@@ -813,7 +842,7 @@ MSPB_DEVFN void resolve_site(const TreeSeqView &ts, const KeptView &kept, const 
             rv.state[j] = st;
         }
         cur += (is_new ? 1u : 0u) + opens;
-        tmax = fmax(tmax, ts.node_time[node]);
+        tmax = fmax(tmax, node_t);
     }
 }
 

@@ -76,8 +76,9 @@ struct mspb_ctx {
     double L = 0;
     uint64_t N = 0, E = 0, S0 = 0, M0 = 0;
     bool have_mut_time = false, kept_fractional = false;
-    DBuf<double> node_time, edge_left, edge_right, ci_left, ci_right;
-    DBuf<int32_t> edge_parent, edge_child, ci_parent;
+    DBuf<double> node_time, edge_left, edge_right;
+    DBuf<ChildIv> ci;
+    DBuf<int32_t> edge_parent, edge_child;
     DBuf<uint32_t> child_start;
     DBuf<double> k_site_pos, k_mut_time;
     DBuf<uint64_t> k_site_anc_off, k_site_md_off, k_mut_der_off, k_mut_md_off;
@@ -269,8 +270,8 @@ extern "C" void mspb_ctx_destroy(mspb_ctx_t *ctx)
         cudaStreamSynchronize(ctx->stream);
     }
 #define REL(b) ctx->b.release()
-    REL(node_time); REL(edge_left); REL(edge_right); REL(ci_left); REL(ci_right);
-    REL(edge_parent); REL(edge_child); REL(ci_parent); REL(child_start);
+    REL(node_time); REL(edge_left); REL(edge_right); REL(ci);
+    REL(edge_parent); REL(edge_child); REL(child_start);
     REL(k_site_pos); REL(k_mut_time); REL(k_site_anc_off); REL(k_site_md_off); REL(k_mut_der_off);
     REL(k_mut_md_off); REL(k_site_anc); REL(k_site_md); REL(k_mut_der); REL(k_mut_md);
     REL(k_mut_site); REL(k_mut_node); REL(k_site_allele); REL(k_mut_allele);
@@ -461,9 +462,7 @@ TreeSeqView make_ts_view(const mspb_ctx *ctx)
     v.edge_parent = ctx->edge_parent.p;
     v.edge_child = ctx->edge_child.p;
     v.child_start = ctx->child_start.p;
-    v.ci_left = ctx->ci_left.p;
-    v.ci_right = ctx->ci_right.p;
-    v.ci_parent = ctx->ci_parent.p;
+    v.ci = ctx->ci.p;
     return v;
 }
 
@@ -596,9 +595,7 @@ extern "C" int mspb_ctx_load_tables(mspb_ctx_t *ctx, const mspb_tables_t *t)
     }
     (void) zero_off;
     TRY(ctx->child_start.ensure(ctx->N + 2));
-    TRY(ctx->ci_left.ensure(ctx->E + 1));
-    TRY(ctx->ci_right.ensure(ctx->E + 1));
-    TRY(ctx->ci_parent.ensure(ctx->E + 1));
+    TRY(ctx->ci.ensure(ctx->E + 1));
 
     // validation
     HostTotals *dt = (HostTotals *) ctx->dev_totals.p;
@@ -644,7 +641,7 @@ extern "C" int mspb_ctx_load_tables(mspb_ctx_t *ctx, const mspb_tables_t *t)
         MSPB_LAUNCH(ctx->log, "k0_child_keys2", k0_child_keys2_kernel<<<grid_for(ctx->E, 256), 256, 0, st>>>(ts, sb.vals[0], sb.keys[0]));
         cur = device_radix_sort<uint64_t>(sb, ctx->E, 0, false, st, ctx->log, nullptr);
         MSPB_LAUNCH(ctx->log, "k0_permute", k0_permute_kernel<<<grid_for(ctx->E, 256), 256, 0, st>>>(
-            ts, sb.vals[cur], ctx->ci_left.p, ctx->ci_right.p, ctx->ci_parent.p, ctx->child_start.p));
+            ts, sb.vals[cur], ctx->ci.p, ctx->child_start.p));
     }
     CUDA_OK(cudaStreamSynchronize(st));
     CUDA_OK(cudaGetLastError());

@@ -157,8 +157,6 @@ inline uint64_t scan_num_tiles(uint64_t n)
 // ---------------------------------------------------------------- radix sort
 constexpr int RS_THREADS = 256;
 constexpr int RS_WARPS = RS_THREADS / 32;
-constexpr int RS_ITEMS = 16;
-constexpr int RS_TILE = RS_THREADS * RS_ITEMS;
 constexpr int RS_BINS = 256;
 constexpr int RS_MAX_PASSES = 8;
 // look-back word: 2 flag bits + 30-bit count
@@ -286,20 +284,35 @@ __global__ void __launch_bounds__(256) rs_iota_kernel(uint32_t *vals, uint64_t n
     }
 }
 
-// One pass.  Warp w of a tile owns the contiguous chunk [w*512, (w+1)*512) of the tile
-// and iteration k covers 32 consecutive keys, so (warp, iteration, lane) order is index
-// order and ranks accumulated in that order make the pass stable.
+// Keys per thread and per tile: 16 x 256 for 32-bit keys, 8 x 256 for 64-bit keys (so that
+// four blocks fit one SM's shared memory either way).
+template <typename KeyT>
+struct RsTraits {
+    static constexpr int ITEMS = sizeof(KeyT) == 4 ? 16 : 8;
+    static constexpr int TILE = RS_THREADS * ITEMS;
+    static constexpr size_t SMEM = (size_t) RS_WARPS * RS_BINS * 4 + 2 * RS_BINS * 4 + 16 * 4
+                                   + (size_t) TILE * (sizeof(KeyT) + 4);
+};
+
+// One pass.  Warp w of a tile owns the contiguous chunk [w*32*ITEMS, (w+1)*32*ITEMS) of the
+// tile and iteration k covers 32 consecutive keys, so (warp, iteration, lane) order is
+// index order and ranks accumulated in that order make the pass stable.  Keys and
+// payloads are staged in shared memory in sorted order and written as contiguous runs.
 // vals_in == nullptr means the identity payload (first pass).
 template <typename KeyT>
-__global__ void __launch_bounds__(RS_THREADS) rs_onesweep_kernel(const KeyT *__restrict__ keys_in,
+__global__ void __launch_bounds__(RS_THREADS, 4) rs_onesweep_kernel(const KeyT *__restrict__ keys_in,
     const uint32_t *__restrict__ vals_in, KeyT *__restrict__ keys_out, uint32_t *__restrict__ vals_out, uint64_t n,
     int shift, uint32_t mask, const uint32_t *__restrict__ global_hist, volatile uint32_t *tile_state)
 {
-    __shared__ uint32_t cnt[RS_WARPS][RS_BINS];
-    __shared__ uint32_t local_start[RS_BINS];
-    __shared__ uint32_t global_base[RS_BINS];
-    __shared__ uint32_t scan_tmp[9];
-    __shared__ KeyT stage[RS_TILE];
+    constexpr int ITEMS = RsTraits<KeyT>::ITEMS;
+    constexpr int TILE = RsTraits<KeyT>::TILE;
+    extern __shared__ __align__(16) unsigned char rs_smem[];
+    KeyT *skeys = reinterpret_cast<KeyT *>(rs_smem);
+    uint32_t *svals = reinterpret_cast<uint32_t *>(skeys + TILE);
+    uint32_t(*cnt)[RS_BINS] = reinterpret_cast<uint32_t(*)[RS_BINS]>(svals + TILE);
+    uint32_t *local_start = reinterpret_cast<uint32_t *>(cnt + RS_WARPS);
+    uint32_t *global_base = local_start + RS_BINS;
+    uint32_t *scan_tmp = global_base + RS_BINS;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t tile = blockIdx.x;
 #pragma unroll
@@ -307,19 +320,23 @@ __global__ void __launch_bounds__(RS_THREADS) rs_onesweep_kernel(const KeyT *__r
         cnt[w][threadIdx.x] = 0;
     }
     __syncthreads();
-    const uint64_t tile_base = (uint64_t) tile * RS_TILE;
-    const uint64_t base = tile_base + (uint64_t) warp * (32 * RS_ITEMS);
-    const uint32_t tile_n = (uint32_t) ((n - tile_base) < (uint64_t) RS_TILE ? (n - tile_base) : (uint64_t) RS_TILE);
-    KeyT key[RS_ITEMS];
-    uint32_t pos[RS_ITEMS];
+    const uint64_t tile_base = (uint64_t) tile * TILE;
+    const uint64_t base = tile_base + (uint64_t) warp * (32 * ITEMS);
+    const uint32_t tile_n = (uint32_t) ((n - tile_base) < (uint64_t) TILE ? (n - tile_base) : (uint64_t) TILE);
+    KeyT key[ITEMS];
+    uint32_t pos2[ITEMS / 2]; // ranks inside the tile (< 4096), two per register
 #pragma unroll
-    for (int k = 0; k < RS_ITEMS; k++) {
+    for (int k = 0; k < ITEMS; k++) {
         const uint64_t i = base + (uint64_t) k * 32 + lane;
         key[k] = i < n ? keys_in[i] : (KeyT) 0;
     }
+#pragma unroll
+    for (int k = 0; k < ITEMS / 2; k++) {
+        pos2[k] = 0;
+    }
     const uint32_t lt = (1u << lane) - 1u;
 #pragma unroll
-    for (int k = 0; k < RS_ITEMS; k++) {
+    for (int k = 0; k < ITEMS; k++) {
         const uint64_t i = base + (uint64_t) k * 32 + lane;
         const bool valid = i < n;
         const uint32_t d = valid ? rs_digit(key[k], shift, mask) : 0xffffffffu;
@@ -334,7 +351,7 @@ __global__ void __launch_bounds__(RS_THREADS) rs_onesweep_kernel(const KeyT *__r
             cnt[warp][d] = prev + (uint32_t) __popc(peers);
         }
         __syncwarp();
-        pos[k] = prev + before;
+        pos2[k >> 1] |= (prev + before) << (16 * (k & 1));
     }
     __syncthreads();
     // thread b owns digit b
@@ -354,6 +371,26 @@ __global__ void __launch_bounds__(RS_THREADS) rs_onesweep_kernel(const KeyT *__r
         *mine = RS_FLAG_INCL | tile_count;
     } else {
         *mine = RS_FLAG_AGG | tile_count;
+    }
+    // exclusive scans over the 256 digits: within the tile, and of the global histogram
+    uint32_t tot;
+    const uint32_t ls = block_exclusive_scan<uint32_t>(tile_count, scan_tmp, &tot);
+    const uint32_t gh = global_hist[threadIdx.x];
+    const uint32_t gs = block_exclusive_scan<uint32_t>(gh, scan_tmp, &tot);
+    local_start[threadIdx.x] = ls;
+    __syncthreads();
+    // stage keys and payloads in sorted order (overlaps the look-back latency of other warps)
+#pragma unroll
+    for (int k = 0; k < ITEMS; k++) {
+        const uint64_t i = base + (uint64_t) k * 32 + lane;
+        if (i < n) {
+            const uint32_t d = rs_digit(key[k], shift, mask);
+            const uint32_t q = ((pos2[k >> 1] >> (16 * (k & 1))) & 0xffffu) + local_start[d] + cnt[warp][d];
+            skeys[q] = key[k];
+            svals[q] = vals_in != nullptr ? vals_in[i] : (uint32_t) i;
+        }
+    }
+    if (tile > 0) {
         for (int64_t p = (int64_t) tile - 1; p >= 0; p--) {
             volatile uint32_t *theirs = tile_state + (uint64_t) p * RS_BINS + threadIdx.x;
             uint32_t v;
@@ -367,50 +404,16 @@ __global__ void __launch_bounds__(RS_THREADS) rs_onesweep_kernel(const KeyT *__r
         }
         *mine = RS_FLAG_INCL | (prefix + tile_count);
     }
-    // exclusive scans over the 256 digits: within the tile, and of the global histogram
-    uint32_t tot;
-    const uint32_t ls = block_exclusive_scan<uint32_t>(tile_count, scan_tmp, &tot);
-    const uint32_t gh = global_hist[threadIdx.x];
-    const uint32_t gs = block_exclusive_scan<uint32_t>(gh, scan_tmp, &tot);
-    local_start[threadIdx.x] = ls;
     global_base[threadIdx.x] = gs + prefix - ls; // dst = global_base[d] + local position
     __syncthreads();
-    // stage keys in sorted order
 #pragma unroll
-    for (int k = 0; k < RS_ITEMS; k++) {
-        const uint64_t i = base + (uint64_t) k * 32 + lane;
-        if (i < n) {
-            const uint32_t d = rs_digit(key[k], shift, mask);
-            pos[k] += local_start[d] + cnt[warp][d];
-            stage[pos[k]] = key[k];
-        }
-    }
-    __syncthreads();
-    uint32_t dst[RS_ITEMS];
-#pragma unroll
-    for (int k = 0; k < RS_ITEMS; k++) {
+    for (int k = 0; k < ITEMS; k++) {
         const uint32_t j = (uint32_t) k * RS_THREADS + threadIdx.x;
         if (j < tile_n) {
-            const KeyT kk = stage[j];
-            dst[k] = global_base[rs_digit(kk, shift, mask)] + j;
-            keys_out[dst[k]] = kk;
-        }
-    }
-    __syncthreads();
-    uint32_t *vstage = reinterpret_cast<uint32_t *>(stage);
-#pragma unroll
-    for (int k = 0; k < RS_ITEMS; k++) {
-        const uint64_t i = base + (uint64_t) k * 32 + lane;
-        if (i < n) {
-            vstage[pos[k]] = vals_in != nullptr ? vals_in[i] : (uint32_t) i;
-        }
-    }
-    __syncthreads();
-#pragma unroll
-    for (int k = 0; k < RS_ITEMS; k++) {
-        const uint32_t j = (uint32_t) k * RS_THREADS + threadIdx.x;
-        if (j < tile_n) {
-            vals_out[dst[k]] = vstage[j];
+            const KeyT kk = skeys[j];
+            const uint32_t dst = global_base[rs_digit(kk, shift, mask)] + j;
+            keys_out[dst] = kk;
+            vals_out[dst] = svals[j];
         }
     }
 }
@@ -425,14 +428,16 @@ struct RadixSortBuffers {
     uint64_t *or_and_host; // 2 (pinned)
 };
 
+template <typename KeyT>
 inline uint32_t rs_num_tiles(uint64_t n)
 {
-    return (uint32_t) ((n + RS_TILE - 1) / RS_TILE);
+    return (uint32_t) ((n + RsTraits<KeyT>::TILE - 1) / RsTraits<KeyT>::TILE);
 }
 
+// words of look-back state for any key width (64-bit keys have the smaller tiles)
 inline uint64_t rs_state_words(uint64_t n)
 {
-    return (uint64_t) RS_MAX_PASSES * rs_num_tiles(n > 0 ? n : 1) * RS_BINS;
+    return (uint64_t) RS_MAX_PASSES * rs_num_tiles<uint64_t>(n > 0 ? n : 1) * RS_BINS;
 }
 
 // Sorts n (key, val) pairs held in buf.keys[0] (payload: buf.vals[0], or the identity
@@ -461,7 +466,7 @@ inline int device_radix_sort(RadixSortBuffers<KeyT> &buf, uint64_t n, uint64_t v
         varying = buf.or_and_host[0] & ~buf.or_and_host[1];
     }
     const RadixPlan plan = radix_plan(varying);
-    const uint32_t tiles = rs_num_tiles(n);
+    const uint32_t tiles = rs_num_tiles<KeyT>(n);
     if (plan.passes == 0) {
         // all keys equal: the input order is the sorted order
         if (identity_vals) {
@@ -481,9 +486,15 @@ inline int device_radix_sort(RadixSortBuffers<KeyT> &buf, uint64_t n, uint64_t v
     MSPB_LAUNCH(log, "rs_global_hist",
         rs_global_hist_kernel<KeyT><<<hist_blocks, RS_THREADS, 0, st>>>(buf.keys[0], n, pd, buf.hist));
     int cur = 0;
+    static bool smem_opt_in = false; // per key type (this is a template)
+    if (!smem_opt_in) {
+        cudaFuncSetAttribute(
+            rs_onesweep_kernel<KeyT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) RsTraits<KeyT>::SMEM);
+        smem_opt_in = true;
+    }
     for (int p = 0; p < plan.passes; p++) {
         MSPB_LAUNCH(log, "rs_onesweep",
-            rs_onesweep_kernel<KeyT><<<tiles, RS_THREADS, 0, st>>>(buf.keys[cur],
+            rs_onesweep_kernel<KeyT><<<tiles, RS_THREADS, RsTraits<KeyT>::SMEM, st>>>(buf.keys[cur],
                 (p == 0 && identity_vals) ? nullptr : buf.vals[cur], buf.keys[cur ^ 1], buf.vals[cur ^ 1], n,
                 pd.shift[p], pd.mask[p], buf.hist + p * RS_BINS, buf.tile_state + (size_t) p * tiles * RS_BINS));
         cur ^= 1;
