@@ -176,21 +176,28 @@ MSPB_DEVFN uint64_t ordered_bits(double x)
 // ---------------------------------------------------------------- Poisson (native)
 // mu < 12: inversion by sequential search (one uniform).  Otherwise Hoermann's
 // PTRS transformed rejection (Insurance: Mathematics and Economics 12, 1993).
+constexpr double POISSON_SMALL_MU = 12.0;
+
+// mu < POISSON_SMALL_MU: inversion by sequential search on one uniform
+MSPB_DEVFN uint32_t poisson_small(double u, double mu)
+{
+    double p = exp(-mu), F = p;
+    uint32_t k = 0;
+    while (u > F && k < 200) {
+        k++;
+        p *= mu / (double) k;
+        F += p;
+    }
+    return k;
+}
+
 MSPB_DEVFN uint32_t poisson_native(PhiloxSeq &rng, double mu)
 {
     if (!(mu > 0.0)) {
         return 0;
     }
-    if (mu < 12.0) {
-        const double u = rng.next();
-        double p = exp(-mu), F = p;
-        uint32_t k = 0;
-        while (u > F && k < 200) {
-            k++;
-            p *= mu / (double) k;
-            F += p;
-        }
-        return k;
+    if (mu < POISSON_SMALL_MU) {
+        return poisson_small(rng.next(), mu);
     }
     const double slam = sqrt(mu), loglam = log(mu);
     const double b = 0.931 + 2.53 * slam;

@@ -226,22 +226,45 @@ MSPB_DEVFN void place_one(const Philox &ph, const RateMapView &map, const EdgeDr
     *time = t;
 }
 
+// how many of an edge's n mutations fall inside the call's genome slice
+MSPB_DEVFN uint32_t k1_in_slice(const Philox &ph, const RateMapView &map, const CallView &call, const EdgeDraw &d,
+    uint64_t e, uint32_t n)
+{
+    uint32_t in = 0;
+    if (call.sliced && n > 0 && d.left < call.slice_right && d.right > call.slice_left) {
+        for (uint32_t q = 0; q < n; q++) {
+            double x, t;
+            place_one(ph, map, d, e, q, &x, &t);
+            in += (x >= call.slice_left && x < call.slice_right) ? 1u : 0u;
+        }
+    }
+    return in;
+}
+
 constexpr int K1_ITEMS = 4;
 constexpr int K1_TILE = SCAN_THREADS * K1_ITEMS;
 
 // count[e] = Poisson(branch length x rate mass), and how many of those fall in this
 // call's genome slice.  Both are prefix-summed here (low / high half of one 64-bit sum):
 // goff[e] = mutations of earlier edges (goff[E] = all), loff[e] = in-slice ones.
-__global__ void __launch_bounds__(SCAN_THREADS) k1_count_scan_kernel(TreeSeqView ts, RateMapView map, CallView call,
+__global__ void __launch_bounds__(SCAN_THREADS, 4) k1_count_scan_kernel(TreeSeqView ts, RateMapView map, CallView call,
     Lookback<uint64_t> lb, uint32_t num_tiles, uint32_t *__restrict__ goff, uint32_t *__restrict__ loff,
     uint64_t *total)
 {
     __shared__ uint64_t sm[9];
     __shared__ uint64_t bcast;
     __shared__ uint64_t s_c[K1_TILE];
+    __shared__ uint16_t s_big[K1_TILE]; // edges whose mean needs the rejection sampler
+    __shared__ uint32_t s_nbig;
     const uint64_t tile_base = (uint64_t) blockIdx.x * K1_TILE;
     const Philox ph(call.seed);
-    // striped: consecutive threads take consecutive edges (coalesced column reads)
+    if (threadIdx.x == 0) {
+        s_nbig = 0;
+    }
+    __syncthreads();
+    // striped: consecutive threads take consecutive edges (coalesced column reads).  The
+    // common small means are drawn here by inversion; the rare large ones are set aside
+    // so that their long rejection loop runs on full warps afterwards.
 #pragma unroll
     for (int k = 0; k < K1_ITEMS; k++) {
         const uint32_t j = (uint32_t) k * SCAN_THREADS + threadIdx.x;
@@ -250,19 +273,25 @@ __global__ void __launch_bounds__(SCAN_THREADS) k1_count_scan_kernel(TreeSeqView
         if (e < ts.num_edges) {
             const EdgeDraw d = edge_draw(ts, map, call, e);
             const double mu = (d.branch_end - d.branch_start) * d.mass;
-            PhiloxSeq rng(call.seed, e, TAG_COUNT);
-            const uint32_t n = poisson_native(rng, mu);
-            uint32_t in = 0;
-            if (call.sliced && n > 0 && d.left < call.slice_right && d.right > call.slice_left) {
-                for (uint32_t q = 0; q < n; q++) {
-                    double x, t;
-                    place_one(ph, map, d, e, q, &x, &t);
-                    in += (x >= call.slice_left && x < call.slice_right) ? 1u : 0u;
-                }
+            if (mu >= POISSON_SMALL_MU) {
+                s_big[atomicAdd(&s_nbig, 1u)] = (uint16_t) j;
+            } else if (mu > 0.0) {
+                PhiloxSeq rng(call.seed, e, TAG_COUNT);
+                const uint32_t n = poisson_small(rng.next(), mu);
+                c = (uint64_t) n | ((uint64_t) k1_in_slice(ph, map, call, d, e, n) << 32);
             }
-            c = (uint64_t) n | ((uint64_t) in << 32);
         }
         s_c[j] = c;
+    }
+    __syncthreads();
+    for (uint32_t b = threadIdx.x; b < s_nbig; b += SCAN_THREADS) {
+        const uint32_t j = s_big[b];
+        const uint64_t e = tile_base + j;
+        const EdgeDraw d = edge_draw(ts, map, call, e);
+        const double mu = (d.branch_end - d.branch_start) * d.mass;
+        PhiloxSeq rng(call.seed, e, TAG_COUNT);
+        const uint32_t n = poisson_native(rng, mu);
+        s_c[j] = (uint64_t) n | ((uint64_t) k1_in_slice(ph, map, call, d, e, n) << 32);
     }
     __syncthreads();
     // blocked: thread t scans the K1_ITEMS consecutive edges it owns
@@ -583,7 +612,7 @@ struct Counts3 {
     }
 };
 
-constexpr int P1_ITEMS = 8;
+constexpr int P1_ITEMS = 16;
 constexpr int P1_TILE = SCAN_THREADS * P1_ITEMS;
 
 // Site boundaries and numbering in one pass: site row of every record, mutation rows
@@ -803,8 +832,12 @@ MSPB_DEVFN void resolve_site(const TreeSeqView &ts, const KeptView &kept, const 
         if (j > first) {
             int32_t u = node;
             double tu = node_t;
+            // A strict ancestor of `node` is older than this mutation, so once the walk has left
+            // `node` it can only meet earlier mutations whose node is older than this mutation.
+            // (New mutations only: a kept mutation's time is not checked against its parent node.)
+            const double mut_t = is_new ? sv.rec[r].time : -INFINITY;
             while (u != -1) {
-                if (tu > tmax) {
+                if (tu > tmax || (u != node && tmax <= mut_t)) {
                     break;
                 }
                 for (uint64_t q = j; q-- > first;) {
@@ -847,21 +880,44 @@ MSPB_DEVFN void resolve_site(const TreeSeqView &ts, const KeptView &kept, const 
 }
 
 // ---------------------------------------------------------------- K5
+// decimal length of v (snprintf "%" PRIu64, lib/mutgen.c:431-447); allele numbers are
+// almost always below 2^32, where 32-bit compares and divisions are much cheaper
+MSPB_DEVFN uint32_t num_digits32(uint32_t v)
+{
+    return v < 100000u ? (v < 100u ? (v < 10u ? 1u : 2u) : (v < 1000u ? 3u : (v < 10000u ? 4u : 5u)))
+                       : (v < 10000000u ? (v < 1000000u ? 6u : 7u)
+                                        : (v < 100000000u ? 8u : (v < 1000000000u ? 9u : 10u)));
+}
+
 MSPB_DEVFN uint32_t num_digits(uint64_t v)
 {
-    uint32_t n = 1;
-    while (v >= 10) {
-        v /= 10;
-        n++;
+    if (v <= 0xffffffffull) {
+        return num_digits32((uint32_t) v);
     }
-    return n;
+    uint32_t n = 9; // v >= 2^32 > 10^9: the low nine digits are full
+    v /= 1000000000ull;
+    while (v > 0xffffffffull) {
+        v /= 1000000000ull;
+        n += 9;
+    }
+    return n + num_digits32((uint32_t) v);
 }
 
 MSPB_DEVFN void write_digits(char *dst, uint64_t v, uint32_t n)
 {
-    for (uint32_t k = n; k-- > 0;) {
-        dst[k] = (char) ('0' + (v % 10));
-        v /= 10;
+    uint32_t k = n;
+    while (v > 0xffffffffull) {
+        uint32_t low = (uint32_t) (v % 1000000000ull);
+        v /= 1000000000ull;
+        for (int d = 0; d < 9; d++) {
+            dst[--k] = (char) ('0' + (low % 10u));
+            low /= 10u;
+        }
+    }
+    uint32_t w = (uint32_t) v;
+    while (k > 0) {
+        dst[--k] = (char) ('0' + (w % 10u));
+        w /= 10u;
     }
 }
 
