@@ -59,6 +59,7 @@ extern "C" {
 #define MSPB_ERR_TOO_MANY_ROWS (-1005) /* more than 2^31 - 1 sites or mutations */
 #define MSPB_ERR_UNSORTED_MUTATIONS (-1006) /* kept mutations not grouped by site */
 #define MSPB_ERR_NOT_GENERATED (-1007)
+#define MSPB_ERR_UNSORTED_SITES (-1009) /* sliced call: kept sites must be sorted by position */
 #define MSPB_ERR_OFFSET_OVERFLOW (-1008) /* offsets32 asked for, but a column may reach 4 GiB */
 
 enum { MSPB_MODEL_MATRIX = 0, MSPB_MODEL_INFINITE_ALLELES = 1 };
@@ -172,6 +173,17 @@ void mspb_ctx_destroy(mspb_ctx_t *ctx);
 int mspb_ctx_load_tables(mspb_ctx_t *ctx, const mspb_tables_t *tables);
 /* Runs the overlay on the device; the result stays resident until the next call. */
 int mspb_generate(mspb_ctx_t *ctx, const mspb_params_t *params, mspb_counts_t *counts);
+/* Two-phase form for genome-sharded calls (one context per GPU, params.slice_left/right
+ * set): _begin runs everything up to the row numbering and reports this slice's
+ * num_sites, num_mutations and next_allele - start_allele (allele numbers used); the
+ * caller exchanges those between ranks; _end writes the tables with the slice's global
+ * site-id, mutation-id and allele-number bases.  Byte offsets stay slice-local until
+ * mspb_shift_offsets adds the bases obtained from a second exchange of the byte counts. */
+int mspb_generate_begin(mspb_ctx_t *ctx, const mspb_params_t *params, mspb_counts_t *counts);
+int mspb_generate_end(mspb_ctx_t *ctx, uint64_t site_base, uint64_t mutation_base, uint64_t allele_base,
+    mspb_counts_t *counts);
+int mspb_shift_offsets(mspb_ctx_t *ctx, uint64_t ancestral_state_base, uint64_t site_metadata_base,
+    uint64_t derived_state_base, uint64_t mutation_metadata_base);
 /* Copies the resident result to host buffers. */
 int mspb_fetch(mspb_ctx_t *ctx, const mspb_columns_t *host_columns);
 /* Device pointers of the resident result (valid until the next mspb_generate). */

@@ -102,6 +102,7 @@ EXPORTED_SYMBOLS = [
     "mspb_device_columns", "mspb_kernel_launches", "mspb_phase_ms", "mspb_phase_name",
     "mspb_sim_mutations", "mspb_columns_free", "mspb_strerror", "mspb_version",
     "mspb_ctx_stream", "mspb_kernel_timing", "mspb_kernel_time", "mspb_selftest_sort",
+    "mspb_generate_begin", "mspb_generate_end", "mspb_shift_offsets",
 ]
 
 _lib = None
@@ -121,6 +122,9 @@ def lib():
         L.mspb_ctx_destroy.restype = None
         L.mspb_ctx_load_tables.argtypes = [C.c_void_p, C.POINTER(_Tables)]
         L.mspb_generate.argtypes = [C.c_void_p, C.POINTER(_Params), C.POINTER(_Counts)]
+        L.mspb_generate_begin.argtypes = [C.c_void_p, C.POINTER(_Params), C.POINTER(_Counts)]
+        L.mspb_generate_end.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64, C.POINTER(_Counts)]
+        L.mspb_shift_offsets.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64]
         L.mspb_fetch.argtypes = [C.c_void_p, C.POINTER(_Columns)]
         L.mspb_device_columns.argtypes = [C.c_void_p, C.POINTER(_Columns)]
         L.mspb_kernel_launches.argtypes = [C.c_void_p]
@@ -268,6 +272,25 @@ class Context:
         check(lib().mspb_generate(self._h, C.byref(params.struct), C.byref(c)))
         self.counts = {name: getattr(c, name) for name, _ in _Counts._fields_}
         return self.counts
+
+    def generate_begin(self, params: Params):
+        """First phase of a genome-sharded call: counts of this slice (no tables yet)."""
+        c = _Counts()
+        check(lib().mspb_generate_begin(self._h, C.byref(params.struct), C.byref(c)))
+        self.counts = {name: getattr(c, name) for name, _ in _Counts._fields_}
+        return self.counts
+
+    def generate_end(self, site_base=0, mutation_base=0, allele_base=0):
+        """Second phase: writes the tables with global site / mutation / allele numbering."""
+        c = _Counts()
+        check(lib().mspb_generate_end(self._h, int(site_base), int(mutation_base),
+                                      int(allele_base) & 0xFFFFFFFFFFFFFFFF, C.byref(c)))
+        self.counts = {name: getattr(c, name) for name, _ in _Counts._fields_}
+        return self.counts
+
+    def shift_offsets(self, ancestral_state=0, site_metadata=0, derived_state=0, mutation_metadata=0):
+        check(lib().mspb_shift_offsets(self._h, int(ancestral_state), int(site_metadata), int(derived_state),
+                                       int(mutation_metadata)))
 
     def result_sizes(self):
         """Element counts of the output columns of the last ``generate``."""

@@ -50,6 +50,7 @@ struct __align__(32) ChildIv {
 
 struct KeptView {
     uint64_t num_sites, num_mutations; // 0 when keep is off
+    int32_t site_id_offset; // input id of site 0 of this view (genome-sliced calls see a sub-range)
     const double *site_position;
     const uint64_t *site_anc_off, *site_md_off;
     const char *site_anc, *site_md;
@@ -529,7 +530,7 @@ __global__ void __launch_bounds__(256) fill_kept_kernel(KeptView kept, CallView 
         x = kept.site_position[r];
     } else {
         const uint64_t m = r - S0;
-        x = kept.site_position[kept.mut_site[m]];
+        x = kept.site_position[kept.mut_site[m] - kept.site_id_offset];
         t = kept.mut_time == nullptr ? nan("") : kept.mut_time[m];
         node = kept.mut_node[m];
         if (isnan(t)) {
@@ -940,6 +941,7 @@ struct OutView {
     void *mut_der_off;
     char *mut_md;
     void *mut_md_off;
+    uint32_t site_base, mut_base; // added to site ids / parent ids (genome slices of a sharded call)
     int off32; // offset columns are uint32 (else uint64)
     int write_md_off; // 0: the metadata offset columns are known to be all zero already
     MSPB_DEVFN void store_off(void *col, uint64_t row, uint64_t v) const
@@ -1172,10 +1174,10 @@ __global__ void __launch_bounds__(SCAN_THREADS) k5_emit_kernel(SortedView sv, Re
             int32_t par = -1;
             if (!e.single) {
                 const int32_t p = rv.parent[i];
-                par = p < 0 ? -1 : (int32_t) sv.mut_row((uint64_t) p);
+                par = p < 0 ? -1 : (int32_t) (sv.mut_row((uint64_t) p) + out.mut_base);
             }
             char *der_dst = der_base + s_der[j];
-            out.mut_site[row] = (int32_t) site_row;
+            out.mut_site[row] = (int32_t) (site_row + out.site_base);
             out.mut_node[row] = rc.node;
             out.mut_time[row] = rc.time;
             out.mut_parent[row] = par;

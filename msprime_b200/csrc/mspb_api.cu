@@ -60,6 +60,8 @@ struct HostTotals {
     unsigned long long first_bad; // validation: (row << 16 | code index), min wins
     int err;
     uint32_t fractional_sites; // kept site positions that are not integers < 2^32
+    uint32_t kslice[4]; // kept sites [0], [1]) and kept mutations [2], [3]) inside the genome slice
+    uint32_t kept_unsorted; // kept site positions are not increasing (sliced calls need that)
     ReplayTotals replay;
 };
 
@@ -112,6 +114,19 @@ struct mspb_ctx {
     DBuf<int32_t> o_mut_site, o_mut_node, o_mut_parent;
     mspb_counts_t counts = {};
     SortedView last_sv = {};
+    // two-phase calls (multi-GPU): everything K5 needs, kept between _begin and _end
+    struct {
+        bool valid = false, defer = false;
+        SortedView sv;
+        ResolveView rv;
+        KeptView kept;
+        ModelView model;
+        CallView call;
+        OutView out;
+        uint64_t R = 0, S0 = 0, Mnew = 0, M = 0, replay_draws = 0, start_allele = 0, replay_len = 0;
+        int model_kind = 0;
+        bool replay = false;
+    } pending;
     // leading bytes of the metadata offset columns known to be zero (and for which buffer)
     const void *md_zero_site_ptr = nullptr, *md_zero_mut_ptr = nullptr;
     uint64_t md_zero_site_bytes = 0, md_zero_mut_bytes = 0;
@@ -180,6 +195,8 @@ extern "C" const char *mspb_strerror(int err)
             return "Too many rows for 32-bit ids";
         case MSPB_ERR_UNSORTED_MUTATIONS:
             return "Kept mutations must be grouped by site in site order";
+        case MSPB_ERR_UNSORTED_SITES:
+            return "A genome-sliced call needs the kept sites sorted by position and the kept mutations by site";
         case MSPB_ERR_OFFSET_OVERFLOW:
             return "A ragged column may exceed 4 GiB: 32-bit offsets cannot be used";
         case MSPB_ERR_NOT_GENERATED:
@@ -782,30 +799,98 @@ int upload_params(mspb_ctx *ctx, const mspb_params_t *p, RateMapView *map, Model
     return 0;
 }
 
-KeptView make_kept_view(const mspb_ctx *ctx, bool keep)
+// View of the kept rows [site_lo, site_lo + S0) and [mut_lo, mut_lo + M0) (the whole tables
+// unless the call owns a genome slice).  Offset columns keep indexing the full byte arrays.
+KeptView make_kept_view(const mspb_ctx *ctx, bool keep, uint64_t site_lo, uint64_t S0, uint64_t mut_lo, uint64_t M0)
 {
     KeptView k;
     memset(&k, 0, sizeof(k));
     if (!keep) {
         return k;
     }
-    k.num_sites = ctx->S0;
-    k.num_mutations = ctx->M0;
-    k.site_position = ctx->k_site_pos.p;
-    k.site_anc_off = ctx->k_site_anc_off.p;
-    k.site_md_off = ctx->k_site_md_off.p;
+    k.num_sites = S0;
+    k.num_mutations = M0;
+    k.site_id_offset = (int32_t) site_lo;
+    k.site_position = ctx->k_site_pos.p + site_lo;
+    k.site_anc_off = ctx->k_site_anc_off.p + site_lo;
+    k.site_md_off = ctx->k_site_md_off.p + site_lo;
     k.site_anc = ctx->k_site_anc.p;
     k.site_md = ctx->k_site_md.p;
-    k.mut_site = ctx->k_mut_site.p;
-    k.mut_node = ctx->k_mut_node.p;
-    k.mut_time = ctx->have_mut_time ? ctx->k_mut_time.p : nullptr;
-    k.mut_der_off = ctx->k_mut_der_off.p;
-    k.mut_md_off = ctx->k_mut_md_off.p;
+    k.mut_site = ctx->k_mut_site.p + mut_lo;
+    k.mut_node = ctx->k_mut_node.p + mut_lo;
+    k.mut_time = ctx->have_mut_time ? ctx->k_mut_time.p + mut_lo : nullptr;
+    k.mut_der_off = ctx->k_mut_der_off.p + mut_lo;
+    k.mut_md_off = ctx->k_mut_md_off.p + mut_lo;
     k.mut_der = ctx->k_mut_der.p;
     k.mut_md = ctx->k_mut_md.p;
     k.site_allele = ctx->k_site_allele.p;
     k.mut_allele = ctx->k_mut_allele.p;
     return k;
+}
+
+// Sliced calls with kept rows: the rows inside [lo, hi) form one contiguous range when the
+// site table is sorted by position (tskit's own requirement for a tree sequence).
+__global__ void kept_slice_kernel(uint64_t S0, const double *pos, uint64_t M0, const int32_t *mut_site, double lo,
+    double hi, uint32_t *out4)
+{
+    if (blockIdx.x != 0 || threadIdx.x != 0) {
+        return;
+    }
+    uint64_t a = 0, b = S0;
+    while (a < b) { // first site with position >= lo
+        const uint64_t m = (a + b) >> 1;
+        if (pos[m] < lo) {
+            a = m + 1;
+        } else {
+            b = m;
+        }
+    }
+    const uint64_t site_lo = a;
+    b = S0;
+    while (a < b) { // first site with position >= hi
+        const uint64_t m = (a + b) >> 1;
+        if (pos[m] < hi) {
+            a = m + 1;
+        } else {
+            b = m;
+        }
+    }
+    const uint64_t site_hi = a;
+    uint64_t c = 0, d = M0;
+    while (c < d) {
+        const uint64_t m = (c + d) >> 1;
+        if ((uint64_t) mut_site[m] < site_lo) {
+            c = m + 1;
+        } else {
+            d = m;
+        }
+    }
+    const uint64_t mut_lo = c;
+    d = M0;
+    while (c < d) {
+        const uint64_t m = (c + d) >> 1;
+        if ((uint64_t) mut_site[m] < site_hi) {
+            c = m + 1;
+        } else {
+            d = m;
+        }
+    }
+    out4[0] = (uint32_t) site_lo;
+    out4[1] = (uint32_t) site_hi;
+    out4[2] = (uint32_t) mut_lo;
+    out4[3] = (uint32_t) c;
+}
+
+__global__ void kept_sorted_check_kernel(uint64_t S0, const double *pos, uint64_t M0, const int32_t *mut_site,
+    uint32_t *unsorted)
+{
+    const uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i + 1 < S0 && !(pos[i] < pos[i + 1])) {
+        *unsorted = 1u;
+    }
+    if (i + 1 < M0 && mut_site[i] > mut_site[i + 1]) {
+        *unsorted = 1u;
+    }
 }
 
 } // namespace
@@ -841,6 +926,22 @@ struct StageB {
     SortedView sv;
     ResolveView rv;
 };
+
+// K5 on the state saved by run_sorted_stages
+int launch_emit(mspb_ctx *ctx)
+{
+    cudaStream_t st = ctx->stream;
+    HostTotals *dt = (HostTotals *) ctx->dev_totals.p;
+    const uint64_t R = ctx->pending.R;
+    const uint32_t k5_tiles = (uint32_t) ((R + K5_TILE - 1) / K5_TILE);
+    Lookback<Bytes4> lb4;
+    TRY(lookback_state<Bytes4>(ctx, k5_tiles, &lb4));
+    MSPB_LAUNCH(ctx->log, "k5_emit",
+        k5_emit_kernel<<<k5_tiles, SCAN_THREADS, 0, st>>>(ctx->pending.sv, ctx->pending.rv, ctx->pending.kept,
+            ctx->pending.model, ctx->pending.call, ctx->pending.out, lb4, k5_tiles, &dt->p1, &dt->bytes, &dt->dense,
+            &dt->err));
+    return 0;
+}
 
 // sort -> P1 -> K4 -> K5 for one key mode; everything is enqueued, nothing is awaited
 int run_sorted_stages(mspb_ctx *ctx, const mspb_params_t *p, const TreeSeqView &ts, const KeptView &kept,
@@ -920,12 +1021,16 @@ int run_sorted_stages(mspb_ctx *ctx, const mspb_params_t *p, const TreeSeqView &
     if (first_sort) {
         CUDA_OK(cudaEventRecord(ctx->ev[6], st));
     }
-    const uint32_t k5_tiles = (uint32_t) ((R + K5_TILE - 1) / K5_TILE);
-    Lookback<Bytes4> lb4;
-    TRY(lookback_state<Bytes4>(ctx, k5_tiles, &lb4));
-    MSPB_LAUNCH(ctx->log, "k5_emit",
-        k5_emit_kernel<<<k5_tiles, SCAN_THREADS, 0, st>>>(sv, rv, kept, model, call, out, lb4, k5_tiles, &dt->p1,
-            &dt->bytes, &dt->dense, &dt->err));
+    ctx->pending.sv = sv;
+    ctx->pending.rv = rv;
+    ctx->pending.kept = kept;
+    ctx->pending.model = model;
+    ctx->pending.call = call;
+    ctx->pending.out = out;
+    ctx->pending.R = R;
+    if (!ctx->pending.defer) {
+        TRY(launch_emit(ctx));
+    }
     if (first_sort) {
         CUDA_OK(cudaEventRecord(ctx->ev[7], st));
     }
@@ -935,11 +1040,14 @@ int run_sorted_stages(mspb_ctx *ctx, const mspb_params_t *p, const TreeSeqView &
 
 } // namespace
 
-extern "C" int mspb_generate(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t *counts_out)
+static int generate_impl(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t *counts_out, bool defer)
 {
     if (ctx == nullptr || p == nullptr) {
         return MSPB_ERR_BAD_PARAM_VALUE;
     }
+    ctx->pending.valid = false;
+    ctx->pending.defer = defer;
+    ctx->pending.R = 0;
     if (!ctx->tables_loaded) {
         return MSPB_ERR_TABLES_NOT_LOADED;
     }
@@ -959,7 +1067,7 @@ extern "C" int mspb_generate(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_count
     }
     const bool keep = p->keep != 0;
     const bool discrete = p->discrete_genome != 0;
-    const uint64_t S0 = keep ? ctx->S0 : 0, M0 = keep ? ctx->M0 : 0;
+    uint64_t S0 = keep ? ctx->S0 : 0, M0 = keep ? ctx->M0 : 0, site_lo = 0, mut_lo = 0;
     HostTotals *dt = (HostTotals *) ctx->dev_totals.p;
     HostTotals *ht = ctx->host;
 
@@ -978,21 +1086,16 @@ extern "C" int mspb_generate(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_count
     call.sliced = sliced ? 1 : 0;
     call.seed = p->seed;
     call.key_mode = (discrete && ctx->L <= 4294967296.0 && !(keep && ctx->kept_fractional)) ? KEY32_POS : KEY64_POS;
-    if (keep && p->model_kind == MSPB_MODEL_MATRIX) {
-        TRY(ctx->k_site_allele.ensure(S0 + 1));
-        TRY(ctx->k_mut_allele.ensure(M0 + 1));
-        if (S0 > 0) {
-            MSPB_LAUNCH(ctx->log, "kept_allele_index",
-                kept_allele_index_kernel<<<grid_for(S0, 256), 256, 0, st>>>(
-                    model, S0, ctx->k_site_anc.p, ctx->k_site_anc_off.p, ctx->k_site_allele.p));
-        }
-        if (M0 > 0) {
-            MSPB_LAUNCH(ctx->log, "kept_allele_index",
-                kept_allele_index_kernel<<<grid_for(M0, 256), 256, 0, st>>>(
-                    model, M0, ctx->k_mut_der.p, ctx->k_mut_der_off.p, ctx->k_mut_allele.p));
-        }
+    if (sliced && S0 + M0 > 0) {
+        // which kept rows this slice owns (read back with the K1 totals)
+        const uint64_t mx = S0 > M0 ? S0 : M0;
+        MSPB_LAUNCH(ctx->log, "kept_sorted_check",
+            kept_sorted_check_kernel<<<grid_for(mx, 256), 256, 0, st>>>(
+                S0, ctx->k_site_pos.p, M0, ctx->k_mut_site.p, &dt->kept_unsorted));
+        MSPB_LAUNCH(ctx->log, "kept_slice",
+            kept_slice_kernel<<<1, 32, 0, st>>>(S0, ctx->k_site_pos.p, M0, ctx->k_mut_site.p, call.slice_left,
+                call.slice_right, dt->kslice));
     }
-    KeptView kept = make_kept_view(ctx, keep);
 
     // ---- K1: how many new mutations, and where they go
     CUDA_OK(cudaEventRecord(ctx->ev[1], st));
@@ -1043,6 +1146,30 @@ extern "C" int mspb_generate(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_count
         Mnew = ht->replay.num_mutations;
         num_pairs = ht->replay.num_pairs;
     }
+    if (sliced && S0 + M0 > 0) {
+        if (ht->kept_unsorted != 0) {
+            return MSPB_ERR_UNSORTED_SITES;
+        }
+        site_lo = ht->kslice[0];
+        S0 = ht->kslice[1] - ht->kslice[0];
+        mut_lo = ht->kslice[2];
+        M0 = ht->kslice[3] - ht->kslice[2];
+    }
+    if (keep && p->model_kind == MSPB_MODEL_MATRIX) {
+        TRY(ctx->k_site_allele.ensure(S0 + 1));
+        TRY(ctx->k_mut_allele.ensure(M0 + 1));
+        if (S0 > 0) {
+            MSPB_LAUNCH(ctx->log, "kept_allele_index",
+                kept_allele_index_kernel<<<grid_for(S0, 256), 256, 0, st>>>(
+                    model, S0, ctx->k_site_anc.p, ctx->k_site_anc_off.p + site_lo, ctx->k_site_allele.p));
+        }
+        if (M0 > 0) {
+            MSPB_LAUNCH(ctx->log, "kept_allele_index",
+                kept_allele_index_kernel<<<grid_for(M0, 256), 256, 0, st>>>(
+                    model, M0, ctx->k_mut_der.p, ctx->k_mut_der_off.p + mut_lo, ctx->k_mut_allele.p));
+        }
+    }
+    KeptView kept = make_kept_view(ctx, keep, site_lo, S0, mut_lo, M0);
     const uint64_t R = S0 + M0 + Mnew;
     if (R > RS_MAX_N) {
         return MSPB_ERR_TOO_MANY_ROWS;
@@ -1051,7 +1178,9 @@ extern "C" int mspb_generate(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_count
     // ---- buffers: rows are bounded before the sort (M is exact, S <= S0 + Mnew)
     CUDA_OK(cudaEventRecord(ctx->ev[2], st));
     const uint64_t M = M0 + Mnew, Scap = S0 + Mnew;
-    const uint64_t maxlen = max_new_state_len(p, Mnew);
+    // (two-phase calls learn their allele-number base only later: size for any uint64)
+    const uint64_t maxlen
+        = (defer && p->model_kind == MSPB_MODEL_INFINITE_ALLELES) ? 20 : max_new_state_len(p, Mnew);
     const uint64_t der_cap = (keep ? ctx->kept_der_bytes : 0) + Mnew * maxlen;
     const uint64_t anc_cap = (keep ? ctx->kept_anc_bytes : 0) + Mnew * maxlen;
     const uint64_t smd_cap = keep ? ctx->kept_smd_bytes : 0, mmd_cap = keep ? ctx->kept_mmd_bytes : 0;
@@ -1116,6 +1245,8 @@ extern "C" int mspb_generate(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_count
     out.mut_der_off = ctx->o_mut_der_off.p;
     out.mut_md = ctx->o_mut_md.p;
     out.mut_md_off = ctx->o_mut_md_off.p;
+    out.site_base = 0;
+    out.mut_base = 0;
 
     // ---- K2: records (kept markers, kept mutations, new mutations) and their sort keys
     KeyView keys;
@@ -1206,10 +1337,139 @@ extern "C" int mspb_generate(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_count
     c.draws = replay ? ht->replay.draws + (p->model_kind == MSPB_MODEL_MATRIX ? draws : 0) : 0;
     c.device_ms = total;
     c.offset_bytes = ow;
+    ctx->generated = !defer;
+    if (defer) {
+        ctx->pending.valid = true;
+        ctx->pending.S0 = S0;
+        ctx->pending.Mnew = Mnew;
+        ctx->pending.M = M;
+        ctx->pending.start_allele = p->start_allele;
+        ctx->pending.model_kind = p->model_kind;
+    }
+    if (counts_out != nullptr) {
+        *counts_out = c;
+    }
+    return 0;
+}
+
+extern "C" int mspb_generate(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t *counts_out)
+{
+    return generate_impl(ctx, p, counts_out, false);
+}
+
+extern "C" int mspb_generate_begin(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t *counts_out)
+{
+    return generate_impl(ctx, p, counts_out, true);
+}
+
+extern "C" int mspb_generate_end(mspb_ctx_t *ctx, uint64_t site_base, uint64_t mutation_base, uint64_t allele_base,
+    mspb_counts_t *counts_out)
+{
+    if (ctx == nullptr) {
+        return MSPB_ERR_BAD_PARAM_VALUE;
+    }
+    if (!ctx->pending.valid) {
+        return MSPB_ERR_NOT_GENERATED;
+    }
+    CUDA_OK(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    HostTotals *dt = (HostTotals *) ctx->dev_totals.p;
+    HostTotals *ht = ctx->host;
+    mspb_counts_t &c = ctx->counts;
+    if (site_base + c.num_sites > 0x7fffffffull || mutation_base + c.num_mutations > 0x7fffffffull) {
+        return MSPB_ERR_TOO_MANY_ROWS;
+    }
+    ctx->pending.valid = false;
+    ctx->pending.out.site_base = (uint32_t) site_base;
+    ctx->pending.out.mut_base = (uint32_t) mutation_base;
+    ctx->pending.model.start_allele = allele_base;
+    cudaEvent_t e0 = ctx->ev[0], e1 = ctx->ev[1];
+    CUDA_OK(cudaEventRecord(e0, st));
+    if (ctx->pending.R > 0) {
+        TRY(launch_emit(ctx));
+    }
+    CUDA_OK(cudaMemcpyAsync(ht, dt, sizeof(HostTotals), cudaMemcpyDeviceToHost, st));
+    CUDA_OK(cudaEventRecord(e1, st));
+    CUDA_OK(cudaStreamSynchronize(st));
+    CUDA_OK(cudaGetLastError());
+    ctx->log.collect();
+    if (ht->err != 0) {
+        return ht->err;
+    }
+    float ms = 0;
+    cudaEventElapsedTime(&ms, e0, e1);
+    c.ancestral_state_bytes = ht->bytes.anc;
+    c.site_metadata_bytes = ht->bytes.smd;
+    c.derived_state_bytes = ht->bytes.der;
+    c.mutation_metadata_bytes = ht->bytes.mmd;
+    if (ctx->pending.model_kind == MSPB_MODEL_INFINITE_ALLELES) {
+        c.next_allele = allele_base + (c.next_allele - ctx->pending.start_allele);
+    }
+    c.device_ms += ms;
     ctx->generated = true;
     if (counts_out != nullptr) {
         *counts_out = c;
     }
+    return 0;
+}
+
+// adds a constant to every entry of an offset column (uint32 or uint64)
+namespace {
+__global__ void shift_offsets_kernel(void *col, uint64_t n, uint64_t delta, int off32)
+{
+    const uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) {
+        if (off32) {
+            static_cast<uint32_t *>(col)[i] += (uint32_t) delta;
+        } else {
+            static_cast<uint64_t *>(col)[i] += delta;
+        }
+    }
+}
+} // namespace
+
+extern "C" int mspb_shift_offsets(mspb_ctx_t *ctx, uint64_t ancestral_state_base, uint64_t site_metadata_base,
+    uint64_t derived_state_base, uint64_t mutation_metadata_base)
+{
+    if (ctx == nullptr) {
+        return MSPB_ERR_BAD_PARAM_VALUE;
+    }
+    if (!ctx->generated) {
+        return MSPB_ERR_NOT_GENERATED;
+    }
+    CUDA_OK(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    const mspb_counts_t &c = ctx->counts;
+    const int off32 = c.offset_bytes == 4;
+    const uint64_t S1 = c.num_sites + 1, M1 = c.num_mutations + 1;
+    if (off32
+        && (ancestral_state_base + c.ancestral_state_bytes > 0xffffffffull
+               || site_metadata_base + c.site_metadata_bytes > 0xffffffffull
+               || derived_state_base + c.derived_state_bytes > 0xffffffffull
+               || mutation_metadata_base + c.mutation_metadata_bytes > 0xffffffffull)) {
+        return MSPB_ERR_OFFSET_OVERFLOW;
+    }
+    if (ancestral_state_base != 0) {
+        MSPB_LAUNCH(ctx->log, "shift_offsets",
+            shift_offsets_kernel<<<grid_for(S1, 256), 256, 0, st>>>(ctx->o_site_anc_off.p, S1, ancestral_state_base, off32));
+    }
+    if (site_metadata_base != 0) {
+        MSPB_LAUNCH(ctx->log, "shift_offsets",
+            shift_offsets_kernel<<<grid_for(S1, 256), 256, 0, st>>>(ctx->o_site_md_off.p, S1, site_metadata_base, off32));
+        ctx->md_zero_site_bytes = 0;
+    }
+    if (derived_state_base != 0) {
+        MSPB_LAUNCH(ctx->log, "shift_offsets",
+            shift_offsets_kernel<<<grid_for(M1, 256), 256, 0, st>>>(ctx->o_mut_der_off.p, M1, derived_state_base, off32));
+    }
+    if (mutation_metadata_base != 0) {
+        MSPB_LAUNCH(ctx->log, "shift_offsets",
+            shift_offsets_kernel<<<grid_for(M1, 256), 256, 0, st>>>(ctx->o_mut_md_off.p, M1, mutation_metadata_base, off32));
+        ctx->md_zero_mut_bytes = 0;
+    }
+    CUDA_OK(cudaStreamSynchronize(st));
+    CUDA_OK(cudaGetLastError());
+    ctx->log.collect();
     return 0;
 }
 

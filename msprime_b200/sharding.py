@@ -1,0 +1,115 @@
+"""Genome-sharded overlays: one GPU context per rank, each owning a position slice.
+
+The path shards by genome position: edges, nodes and the rate map
+are replicated, a site never straddles two slices, and the native stream is keyed by
+(seed, edge, ordinal) rather than by rank, so the union of the slices' tables is identical
+to the single-GPU tables.  What has to be exchanged is tiny: per-rank counts, to turn
+rank-local site ids, parent ids, allele numbers and byte offsets into global ones.
+
+Two small all-gathers per call (``allgather`` is any callable that maps this rank's list
+of ints to the list of every rank's lists, e.g. :func:`dist_allgather`):
+
+1. after ``generate_begin``: (sites, mutations, allele numbers used)  -> id / allele bases;
+2. after ``generate_end``:   (ancestral, site-metadata, derived, mutation-metadata bytes)
+   -> byte-offset bases, applied on the device by ``shift_offsets``.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+SITE_COLUMNS = ("position", "ancestral_state", "ancestral_state_offset", "metadata", "metadata_offset")
+MUTATION_COLUMNS = ("site", "node", "parent", "time", "derived_state", "derived_state_offset", "metadata",
+                    "metadata_offset")
+
+
+def slice_cuts(sequence_length, world, discrete_genome=True):
+    """``world + 1`` increasing cut points from 0 to L; integers when the genome is discrete
+    (a site must belong to exactly one slice)."""
+    L = float(sequence_length)
+    cuts = [L * r / world for r in range(world + 1)]
+    if discrete_genome:
+        cuts = [float(np.floor(c)) for c in cuts]
+    cuts[0], cuts[-1] = 0.0, L
+    for a, b in zip(cuts[:-1], cuts[1:]):
+        if not a < b:
+            raise ValueError("sequence too short to cut into that many slices")
+    return cuts
+
+
+def exclusive_bases(all_values, rank):
+    """Sum over ranks before ``rank`` of each column of ``all_values`` (world x k ints)."""
+    a = np.asarray(all_values, dtype=object)
+    k = a.shape[1]
+    return [int(sum(int(a[r][j]) for r in range(rank))) for j in range(k)]
+
+
+def dist_allgather(group=None, device=None):
+    """An ``allgather`` callable on top of ``torch.distributed`` (gloo on CPU tensors, nccl on
+    ``device``).  Values travel as int64."""
+    import torch
+    import torch.distributed as dist
+
+    def allgather(values):
+        world = dist.get_world_size(group)
+        t = torch.tensor([int(v) for v in values], dtype=torch.int64, device=device)
+        out = [torch.empty_like(t) for _ in range(world)]
+        dist.all_gather(out, t, group=group)
+        return [[int(x) for x in o.cpu().tolist()] for o in out]
+
+    return allgather
+
+
+def run_slice(engine, params, *, rank, world, allgather, start_allele=0):
+    """Runs this rank's slice on ``engine`` (a ``_native.Context`` with tables loaded, or
+    anything with the same four methods) and returns ``(local_result, info)``.
+
+    ``params`` must already carry this rank's ``slice_left/right``.  The local result has
+    global site ids, parent ids, allele numbers and byte offsets; ``info`` holds the global
+    totals (``num_sites``, ``num_mutations``, ``next_allele``, byte totals)."""
+    c1 = engine.generate_begin(params)
+    used = (int(c1["next_allele"]) - int(start_allele)) & 0xFFFFFFFFFFFFFFFF
+    all1 = allgather([c1["num_sites"], c1["num_mutations"], used, c1["num_new_mutations"]])
+    site_base, mut_base, allele_base, _ = exclusive_bases(all1, rank)
+    c2 = engine.generate_end(site_base, mut_base, (int(start_allele) + allele_base) & 0xFFFFFFFFFFFFFFFF)
+    all2 = allgather([c2["ancestral_state_bytes"], c2["site_metadata_bytes"], c2["derived_state_bytes"],
+                      c2["mutation_metadata_bytes"]])
+    anc, smd, der, mmd = exclusive_bases(all2, rank)
+    engine.shift_offsets(anc, smd, der, mmd)
+    local = engine.fetch()
+    tot1 = [sum(int(r[j]) for r in all1) for j in range(4)]
+    tot2 = [sum(int(r[j]) for r in all2) for j in range(4)]
+    info = {
+        "num_sites": tot1[0], "num_mutations": tot1[1], "num_new_mutations": tot1[3],
+        "next_allele": (int(start_allele) + tot1[2]) & 0xFFFFFFFFFFFFFFFF,
+        "ancestral_state_bytes": tot2[0], "site_metadata_bytes": tot2[1], "derived_state_bytes": tot2[2],
+        "mutation_metadata_bytes": tot2[3], "site_base": site_base, "mutation_base": mut_base,
+    }
+    return local, info
+
+
+def merge_slices(results):
+    """Concatenates the per-slice results (in slice order) into one result.  Offsets are already
+    global: every slice but the last drops its closing offset entry."""
+    out = {"sites": {}, "mutations": {}}
+    last = len(results) - 1
+    for tbl, cols in (("sites", SITE_COLUMNS), ("mutations", MUTATION_COLUMNS)):
+        for col in cols:
+            parts = []
+            for r, res in enumerate(results):
+                a = np.asarray(res[tbl][col])
+                if col.endswith("_offset") and r != last:
+                    a = a[:-1]
+                parts.append(a)
+            out[tbl][col] = np.concatenate(parts) if parts else np.zeros(0)
+    return out
+
+
+def gather_results(local, *, rank, world, group=None):
+    """Final table gather to rank 0 (returns the merged result there, None elsewhere)."""
+    import torch.distributed as dist
+
+    gathered = [None] * world if rank == 0 else None
+    dist.gather_object(local, gathered, dst=0, group=group)
+    if rank != 0:
+        return None
+    return merge_slices(gathered)

@@ -1,0 +1,158 @@
+"""GPU, native Philox stream: structural validity of the tables, determinism per seed,
+slice invariance (the union of genome slices equals the unsliced result, bit for bit),
+model bookkeeping (infinite-alleles numbering) and the Python surface end to end."""
+import numpy as np
+import pytest
+
+import cases
+import table_checks
+import msprime_b200 as msp
+from msprime_b200 import _native, sharding, synth, tables as mtables
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ts_small():
+    return synth.native_treeseq(200, 2e5, 1e-8, 1e4, 3)
+
+
+def run(ctx, ts, *, model, rate, discrete=True, keep=False, seed=1, load=True, **kw):
+    if load:
+        ctx.load_tables(ts)
+    L = ts["sequence_length"]
+    p = _native.Params(map_position=kw.pop("map_position", [0, L]), map_rate=kw.pop("map_rate", [rate]),
+                       model=cases.native_model(model), discrete_genome=discrete, keep=keep,
+                       start_time=kw.pop("start_time", -cases.FMAX), end_time=kw.pop("end_time", cases.FMAX),
+                       seed=seed, **kw)
+    c = ctx.generate(p)
+    return ctx.fetch(), c
+
+
+@pytest.fixture(scope="module")
+def ctx(native_built):
+    c = _native.Context(0)
+    yield c
+    c.close()
+
+
+@pytest.mark.parametrize("model", ["jc69", "binary", "infinite_alleles", "multichar"])
+@pytest.mark.parametrize("discrete", [True, False])
+@pytest.mark.parametrize("rate", [1e-8, 3e-7, 2e-5])
+def test_tables_are_valid(ctx, ts_small, model, discrete, rate):
+    res, c = run(ctx, ts_small, model=cases.MODELS[model], rate=rate, discrete=discrete, seed=11)
+    assert c["num_mutations"] == len(res["mutations"]["site"]) == c["num_new_mutations"]
+    table_checks.check_result(ts_small, res, discrete=discrete)
+    if rate >= 3e-7:
+        assert c["num_mutations"] > 100
+
+
+def test_time_window(ctx, ts_small):
+    res, _ = run(ctx, ts_small, model=cases.JC69, rate=1e-6, start_time=500.0, end_time=5000.0, seed=5)
+    t = res["mutations"]["time"]
+    assert len(t) > 100 and t.min() >= 500.0 and t.max() < 5000.0
+    table_checks.check_result(ts_small, res, discrete=True, start_time=500.0, end_time=5000.0)
+
+
+def test_seed_determinism(ctx, ts_small):
+    a, _ = run(ctx, ts_small, model=cases.JC69, rate=1e-6, seed=7)
+    b, _ = run(ctx, ts_small, model=cases.JC69, rate=1e-6, seed=7, load=False)
+    c, _ = run(ctx, ts_small, model=cases.JC69, rate=1e-6, seed=8, load=False)
+    for tbl in a:
+        for col in a[tbl]:
+            assert np.array_equal(a[tbl][col], b[tbl][col])
+    assert not np.array_equal(a["sites"]["position"], c["sites"]["position"])
+
+
+def test_infinite_alleles_numbering_and_counter(ctx, ts_small):
+    m = dict(cases.INF_ALLELES, start_allele=123456789012)
+    res, c = run(ctx, ts_small, model=m, rate=1e-6, seed=3)
+    anc = [int(x) for x in table_checks.ragged(res["sites"]["ancestral_state"], res["sites"]["ancestral_state_offset"])]
+    der = [int(x) for x in table_checks.ragged(res["mutations"]["derived_state"],
+                                               res["mutations"]["derived_state_offset"])]
+    nxt, mi, site = 123456789012, 0, res["mutations"]["site"]
+    for s, a in enumerate(anc):
+        assert a == nxt
+        nxt += 1
+        while mi < len(der) and site[mi] == s:
+            assert der[mi] == nxt
+            nxt += 1
+            mi += 1
+    assert c["next_allele"] == nxt
+
+
+def test_counter_wraps(ctx):
+    # tests/test_mutations.py:1774-1794: the uint64 counter wraps around
+    ts = cases.four_leaf_tree()
+    m = dict(cases.INF_ALLELES, start_allele=2**64 - 3)
+    res, c = run(ctx, ts, model=m, rate=1.0, seed=2)
+    anc = [int(x) for x in table_checks.ragged(res["sites"]["ancestral_state"], res["sites"]["ancestral_state_offset"])]
+    assert anc[0] == 2**64 - 3 and c["next_allele"] < 2**63 and 0 in anc + [int(x) for x in table_checks.ragged(
+        res["mutations"]["derived_state"], res["mutations"]["derived_state_offset"])]
+
+
+@pytest.mark.parametrize("world", [2, 3, 8])
+@pytest.mark.parametrize("model,keep", [("infinite_alleles", False), ("jc69", False), ("jc69", True),
+                                        ("infinite_alleles", True)])
+def test_union_of_slices_equals_whole(native_built, ts_small, world, model, keep):
+    """Every rank of a sharded call is emulated by its own context on this GPU."""
+    ts = ts_small
+    L = ts["sequence_length"]
+    mdl = cases.MODELS[model]
+    whole_ctx = _native.Context(0)
+    if keep:
+        first, _ = run(whole_ctx, ts, model=mdl, rate=5e-7, seed=21)
+        ts = cases.with_kept(ts, first)
+    start = 1000 if model == "infinite_alleles" else 0
+    mdl = dict(mdl, start_allele=start) if model == "infinite_alleles" else mdl
+    whole, cw = run(whole_ctx, ts, model=mdl, rate=5e-7, keep=keep, seed=22)
+    whole_ctx.close()
+    cuts = sharding.slice_cuts(L, world)
+    ctxs = [_native.Context(0) for _ in range(world)]
+    try:
+        params = []
+        for r, c in enumerate(ctxs):
+            c.load_tables(ts)
+            params.append(_native.Params(map_position=[0, L], map_rate=[5e-7], model=cases.native_model(mdl),
+                                         discrete_genome=True, keep=keep, start_time=-cases.FMAX,
+                                         end_time=cases.FMAX, seed=22, slice_left=cuts[r], slice_right=cuts[r + 1]))
+        # the all-gathers of a real run, played back serially
+        first_phase = [c.generate_begin(p) for c, p in zip(ctxs, params)]
+        all1 = [[f["num_sites"], f["num_mutations"], (f["next_allele"] - start) % 2**64, f["num_new_mutations"]]
+                for f in first_phase]
+        second = []
+        for r, c in enumerate(ctxs):
+            sb, mb, ab, _ = sharding.exclusive_bases(all1, r)
+            second.append(c.generate_end(sb, mb, start + ab))
+        all2 = [[f["ancestral_state_bytes"], f["site_metadata_bytes"], f["derived_state_bytes"],
+                 f["mutation_metadata_bytes"]] for f in second]
+        parts = []
+        for r, c in enumerate(ctxs):
+            c.shift_offsets(*sharding.exclusive_bases(all2, r))
+            parts.append(c.fetch())
+        merged = sharding.merge_slices(parts)
+    finally:
+        for c in ctxs:
+            c.close()
+    for tbl in whole:
+        for col in whole[tbl]:
+            assert np.array_equal(np.asarray(whole[tbl][col]), np.asarray(merged[tbl][col])), (tbl, col)
+    assert sum(a[3] for a in all1) == cw["num_new_mutations"]
+
+
+def test_python_surface_layers_and_provenance(native_built, ts_small):
+    ts = mtables.TableCollection.fromdict(ts_small).tree_sequence()
+    a = msp.sim_mutations(ts, rate=2e-7, random_seed=3, model="jc69")
+    assert a.num_mutations > 0 and a.num_provenances == ts.num_provenances + 1
+    b = msp.sim_mutations(a, rate=2e-7, random_seed=4, model=msp.HKY(kappa=2.0))  # keep=True by default
+    assert b.num_mutations > a.num_mutations and b.num_sites >= a.num_sites
+    c = msp.sim_mutations(a, rate=0, random_seed=4)
+    assert c.num_mutations == a.num_mutations
+    d = msp.sim_mutations(a, rate=0, random_seed=4, keep=False, record_provenance=False)
+    assert d.num_mutations == 0 and d.num_sites == 0 and d.num_provenances == a.num_provenances
+    assert ts.num_mutations == 0  # the input is never modified
+    ia = msp.InfiniteAlleles()
+    e = msp.sim_mutations(ts, rate=2e-7, random_seed=5, model=ia)
+    assert ia.next_allele == e.num_sites + e.num_mutations
+    f = msp.mutate(ts, rate=2e-7, random_seed=6)
+    assert set(f.alleles()[0]) == {"0"} and set(f.alleles()[1]) <= {"0", "1"}
