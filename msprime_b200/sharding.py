@@ -51,10 +51,12 @@ def dist_allgather(group=None, device=None):
 
     def allgather(values):
         world = dist.get_world_size(group)
-        t = torch.tensor([int(v) for v in values], dtype=torch.int64, device=device)
+        # uint64 values (allele counters) travel as their two's-complement int64 image
+        signed = [((int(v) & 0xFFFFFFFFFFFFFFFF) ^ (1 << 63)) - (1 << 63) for v in values]
+        t = torch.tensor(signed, dtype=torch.int64, device=device)
         out = [torch.empty_like(t) for _ in range(world)]
         dist.all_gather(out, t, group=group)
-        return [[int(x) for x in o.cpu().tolist()] for o in out]
+        return [[int(x) & 0xFFFFFFFFFFFFFFFF for x in o.cpu().tolist()] for o in out]
 
     return allgather
 
