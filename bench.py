@@ -286,7 +286,7 @@ def run_b200_arm(args, rank, local_rank, world):
     import torch
     import torch.distributed as dist
 
-    from msprime_b200 import _native, build
+    from msprime_b200 import _native, build, sharding
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the B200 arm has no CPU fallback "
@@ -321,7 +321,8 @@ def run_b200_arm(args, rank, local_rank, world):
     def params(step):
         return _native.Params(map_position=[0, L], map_rate=[w["rate"]], model=native_model(w["model"]),
                               discrete_genome=w["discrete"], keep=False, start_time=-FMAX, end_time=FMAX,
-                              seed=1000 + step, slice_left=sl, slice_right=sr, offsets32=True)
+                              seed=1000 + step, slice_left=sl, slice_right=sr, offsets32=True,
+                              slice_stream=0 if world == 1 else rank + 1)
 
     def sync_all():
         torch.cuda.synchronize()
@@ -336,10 +337,23 @@ def run_b200_arm(args, rank, local_rank, world):
         dist.all_reduce(t, op=op)
         return float(t.item())
 
+    allgather = sharding.dist_allgather(device=f"cuda:{local_rank}") if world > 1 else None
+
+    def overlay(step, fetch_into=None):
+        """One overlay of this rank's slice; returns the number of new mutations it holds."""
+        if world == 1:
+            c = ctx.generate(params(step))
+            if fetch_into is not None:
+                ctx.fetch(fetch_into)
+            return c["num_new_mutations"]
+        sharding.run_slice(ctx, params(step), rank=rank, world=world, allgather=allgather,
+                           fetch=fetch_into is not None, out=fetch_into)
+        return ctx.counts["num_new_mutations"]
+
     ctx.load_tables(host_ts)
     # ---- device-resident throughput
     for i in range(args.warmup):
-        ctx.generate(params(i))
+        overlay(i)
     c = ctx.counts
     sizes = ctx.result_sizes()
     out_bufs = {}
@@ -358,9 +372,8 @@ def run_b200_arm(args, rank, local_rank, world):
     muts = 0
     lib_ms = 0.0
     for i in range(args.steps):
-        c = ctx.generate(params(100 + i))
-        muts += c["num_new_mutations"]
-        lib_ms += c["device_ms"]
+        muts += overlay(100 + i)
+        lib_ms += ctx.counts["device_ms"]
     ev1.record(stream)
     sync_all()
     clocks = sampler.stop()
@@ -376,8 +389,7 @@ def run_b200_arm(args, rank, local_rank, world):
     d2h_bytes = 0
     for i in range(min(2, args.warmup)):
         ctx.load_tables(host_ts)
-        ctx.generate(params(200 + i))
-        ctx.fetch(out_bufs)
+        overlay(200 + i, out_bufs)
     sync_all()
     ev2, ev3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     wall0 = time.perf_counter()
@@ -385,10 +397,9 @@ def run_b200_arm(args, rank, local_rank, world):
     e2e_muts = 0
     for i in range(args.steps):
         ctx.load_tables(host_ts)
-        c = ctx.generate(params(300 + i))
-        res = ctx.fetch(out_bufs)
-        e2e_muts += c["num_new_mutations"]
-        d2h_bytes = sum(int(a.nbytes) for tbl in res.values() for a in tbl.values())
+        e2e_muts += overlay(300 + i, out_bufs)
+        sizes = ctx.result_sizes()
+        d2h_bytes = sum(int(sizes[name]) * np.dtype(out_bufs[name].dtype).itemsize for name in sizes)
     ev3.record(stream)
     sync_all()
     wall = time.perf_counter() - wall0
@@ -453,10 +464,14 @@ def run_b200_arm(args, rank, local_rank, world):
                    "edges": E, "nodes": N, "mutations_per_step": total_muts / args.steps,
                    "l2": "inputs larger than L2 (edge columns + records > 126 MB), no flush",
                    "sharding": "whole genome on one GPU" if world == 1 else
-                   f"{world} genome position slices, edges replicated, no data-path collective"},
+                   f"{world} genome position slices (edges cut to the slice, Philox stream per rank), edges replicated; "
+                   "two 4-integer NCCL all-gathers per overlay "
+                   "(row / allele / byte bases), each rank copies its slice to the host"},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d_total, "d2h_bytes_per_step": d2h_total,
-                "ms_per_step": e2e_ms / args.steps, "path": "mspb_ctx_load_tables + mspb_generate + mspb_fetch, "
-                "pinned host buffers"},
+                "ms_per_step": e2e_ms / args.steps,
+                "path": "mspb_ctx_load_tables + mspb_generate + mspb_fetch, pinned host buffers" if world == 1 else
+                "per rank: mspb_ctx_load_tables + mspb_generate_begin / count all-gather (NCCL) / mspb_generate_end / "
+                "byte all-gather / mspb_shift_offsets + mspb_fetch of the rank's slice into pinned host buffers"},
         "gpu_launches": launches,
         "clocks": clocks,
         "roofline": roofline,

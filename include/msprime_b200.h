@@ -124,6 +124,12 @@ typedef struct {
     /* nonzero: the offset columns of the result are uint32 instead of uint64, as tskit's
      * dict protocol exports them when they fit (tskit_lwt_interface.h:1634-1635) */
     int32_t offsets32;
+    /* How a genome slice is drawn.  0: every edge is drawn whole and the mutations outside
+     * the slice are dropped, so the union of the slices is bit-identical to the unsliced
+     * call (every rank pays for all edges).  Nonzero: edges are cut to the slice and drawn on
+     * this Philox stream (use rank + 1), so work scales with the slice; the result then
+     * depends on the cuts, with the same distribution. */
+    uint32_t slice_stream;
 } mspb_params_t;
 
 /* Row and byte counts of the result of the last mspb_generate. */

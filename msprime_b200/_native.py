@@ -69,7 +69,7 @@ class _Params(C.Structure):
         ("start_time", C.c_double), ("end_time", C.c_double),
         ("seed", C.c_uint64), ("replay_stream", C.c_void_p), ("replay_len", C.c_uint64),
         ("slice_left", C.c_double), ("slice_right", C.c_double),
-        ("offsets32", C.c_int32),
+        ("offsets32", C.c_int32), ("slice_stream", C.c_uint32),
     ]
 
 
@@ -171,7 +171,8 @@ class Params:
     """Keeps the numpy arrays behind a ``mspb_params_t`` alive."""
 
     def __init__(self, *, map_position, map_rate, model, discrete_genome, keep, start_time, end_time,
-                 seed=0, replay_stream=None, slice_left=0.0, slice_right=0.0, offsets32=False):
+                 seed=0, replay_stream=None, slice_left=0.0, slice_right=0.0, offsets32=False,
+                 slice_stream=0):
         self._hold = []
         p = _Params()
         pos, rate = _c(map_position, np.float64), _c(map_rate, np.float64)
@@ -200,6 +201,7 @@ class Params:
             p.replay_stream, p.replay_len = _p(st), len(st)
         p.slice_left, p.slice_right = float(slice_left), float(slice_right)
         p.offsets32 = int(bool(offsets32))
+        p.slice_stream = int(slice_stream)
         self.struct = p
 
 

@@ -178,6 +178,15 @@ MSPB_DEVFN uint64_t ordered_bits(double x)
 // PTRS transformed rejection (Insurance: Mathematics and Economics 12, 1993).
 constexpr double POISSON_SMALL_MU = 12.0;
 
+// 1 / k for the inversion loop (a double division costs ~30 instructions, and the warp
+// iterates as long as its slowest lane)
+__constant__ double POISSON_RCP[64] = { 0.0, 1.0 / 1, 1.0 / 2, 1.0 / 3, 1.0 / 4, 1.0 / 5, 1.0 / 6, 1.0 / 7, 1.0 / 8,
+    1.0 / 9, 1.0 / 10, 1.0 / 11, 1.0 / 12, 1.0 / 13, 1.0 / 14, 1.0 / 15, 1.0 / 16, 1.0 / 17, 1.0 / 18, 1.0 / 19,
+    1.0 / 20, 1.0 / 21, 1.0 / 22, 1.0 / 23, 1.0 / 24, 1.0 / 25, 1.0 / 26, 1.0 / 27, 1.0 / 28, 1.0 / 29, 1.0 / 30,
+    1.0 / 31, 1.0 / 32, 1.0 / 33, 1.0 / 34, 1.0 / 35, 1.0 / 36, 1.0 / 37, 1.0 / 38, 1.0 / 39, 1.0 / 40, 1.0 / 41,
+    1.0 / 42, 1.0 / 43, 1.0 / 44, 1.0 / 45, 1.0 / 46, 1.0 / 47, 1.0 / 48, 1.0 / 49, 1.0 / 50, 1.0 / 51, 1.0 / 52,
+    1.0 / 53, 1.0 / 54, 1.0 / 55, 1.0 / 56, 1.0 / 57, 1.0 / 58, 1.0 / 59, 1.0 / 60, 1.0 / 61, 1.0 / 62, 1.0 / 63 };
+
 // mu < POISSON_SMALL_MU: inversion by sequential search on one uniform
 MSPB_DEVFN uint32_t poisson_small(double u, double mu)
 {
@@ -185,7 +194,7 @@ MSPB_DEVFN uint32_t poisson_small(double u, double mu)
     uint32_t k = 0;
     while (u > F && k < 200) {
         k++;
-        p *= mu / (double) k;
+        p *= mu * (k < 64 ? POISSON_RCP[k] : 1.0 / (double) k);
         F += p;
     }
     return k;
@@ -304,109 +313,179 @@ namespace mspb {
 // ---------------------------------------------------------------- decoupled look-back
 // Single-pass prefix sums over tiles (Merrill & Garland): a tile publishes its
 // aggregate, then sums the aggregates of the tiles before it until it meets one
-// whose inclusive prefix is already known.  T is a small POD with operator+ and a
-// multiple of 4 bytes in size.  Flags: 0 = nothing yet, 1 = aggregate, 2 = inclusive.
-template <typename T>
-struct Lookback {
-    uint32_t *flag;
-    T *agg;
-    T *incl;
+// whose inclusive prefix is already known.
+//
+// A tile's state is HALVES 16-byte words, each written and read with ONE 128-bit
+// access, with the status in the top two bits of its last 32-bit lane (0 = nothing yet,
+// 1 = aggregate, 2 = inclusive prefix), so value and status always travel together and
+// no fence is needed.  The chain advances by at most one window of tiles per L2 round
+// trip, so the window is wide (LB_WINDOW predecessors per round) -- with a 32-tile
+// window the propagation rate, not the memory system, bounded every scan kernel here.
+struct __align__(16) LbWord {
+    uint32_t w[4];
 };
 
-template <typename T>
-MSPB_DEVFN T ld_cg_pod(const T *p)
+constexpr int LB_PER_LANE = 4;
+constexpr int LB_WINDOW = 32 * LB_PER_LANE;
+constexpr uint32_t LB_AGG = 1u, LB_INCL = 2u;
+
+MSPB_DEVFN LbWord lb_load(const LbWord *p)
 {
-    static_assert(sizeof(T) % 4 == 0, "POD of 32-bit words");
-    T v;
-    uint32_t *w = reinterpret_cast<uint32_t *>(&v);
-    const uint32_t *s = reinterpret_cast<const uint32_t *>(p);
-#pragma unroll
-    for (int i = 0; i < (int) (sizeof(T) / 4); i++) {
-        w[i] = __ldcg(s + i);
-    }
+    LbWord v;
+    asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(v.w[0]), "=r"(v.w[1]), "=r"(v.w[2]), "=r"(v.w[3])
+                 : "l"(p)
+                 : "memory");
     return v;
 }
 
-template <typename T>
-MSPB_DEVFN void st_cg_pod(T *p, const T &v)
+MSPB_DEVFN void lb_store(LbWord *p, const LbWord &v)
 {
-    const uint32_t *w = reinterpret_cast<const uint32_t *>(&v);
-    uint32_t *d = reinterpret_cast<uint32_t *>(p);
-#pragma unroll
-    for (int i = 0; i < (int) (sizeof(T) / 4); i++) {
-        __stcg(d + i, w[i]);
-    }
+    asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.w[0]), "r"(v.w[1]), "r"(v.w[2]),
+                 "r"(v.w[3])
+                 : "memory");
 }
 
-template <typename T>
-MSPB_DEVFN T shfl_xor_pod(const T &v, int mask)
-{
-    T r;
-    const uint32_t *w = reinterpret_cast<const uint32_t *>(&v);
-    uint32_t *o = reinterpret_cast<uint32_t *>(&r);
+// Payload of a tile: HALVES x 4 lanes of 32 bits, summed lane-wise as 4 x u32 (WIDE64 =
+// false) or 2 x u64 (true).  The last 32-bit lane of every half must stay below 2^30.
+template <int HALVES, bool WIDE64>
+struct LbVal {
+    uint32_t w[HALVES][4];
+    MSPB_DEVFN void clear()
+    {
 #pragma unroll
-    for (int i = 0; i < (int) (sizeof(T) / 4); i++) {
-        o[i] = __shfl_xor_sync(0xffffffffu, w[i], mask);
+        for (int h = 0; h < HALVES; h++) {
+            w[h][0] = w[h][1] = w[h][2] = w[h][3] = 0;
+        }
     }
-    return r;
-}
+    MSPB_DEVFN void add(const LbVal &o)
+    {
+#pragma unroll
+        for (int h = 0; h < HALVES; h++) {
+            if (WIDE64) {
+#pragma unroll
+                for (int q = 0; q < 2; q++) {
+                    const uint64_t a = ((uint64_t) w[h][2 * q + 1] << 32) | w[h][2 * q];
+                    const uint64_t b = ((uint64_t) o.w[h][2 * q + 1] << 32) | o.w[h][2 * q];
+                    const uint64_t c = a + b;
+                    w[h][2 * q] = (uint32_t) c;
+                    w[h][2 * q + 1] = (uint32_t) (c >> 32);
+                }
+            } else {
+#pragma unroll
+                for (int q = 0; q < 4; q++) {
+                    w[h][q] += o.w[h][q];
+                }
+            }
+        }
+    }
+};
 
 // Called by every thread of the block with the block's aggregate (thread 0's value is
-// used); returns the sum over all earlier tiles.  *total (optional, device memory)
-// receives the grand total from the last tile.  `bcast` is one T in shared memory.
-template <typename T>
-MSPB_DEVFN T lookback_exclusive(const Lookback<T> &lb, uint32_t tile, uint32_t num_tiles, const T &aggregate, T *bcast,
-    T *total)
+// used); returns the sum over all earlier tiles.  `state` holds num_tiles x HALVES words,
+// zeroed before the launch.  `bcast` is one LbVal in shared memory.  *inclusive_out
+// (optional, shared or local) receives prefix + aggregate on every thread.
+template <int HALVES, bool WIDE64>
+MSPB_DEVFN LbVal<HALVES, WIDE64> lookback_prefix(LbWord *state, uint32_t tile, const LbVal<HALVES, WIDE64> &aggregate,
+    LbVal<HALVES, WIDE64> *bcast)
 {
+    typedef LbVal<HALVES, WIDE64> V;
     if (threadIdx.x < 32) {
         const int lane = threadIdx.x;
-        T prefix = T();
+        V prefix;
+        prefix.clear();
         if (tile > 0) {
-            if (lane == 0) {
-                st_cg_pod(&lb.agg[tile], aggregate);
-                __threadfence();
-                *((volatile uint32_t *) &lb.flag[tile]) = 1u;
+#pragma unroll
+            for (int h = 0; h < HALVES; h++) {
+                if (lane == h) {
+                    LbWord me;
+                    me.w[0] = aggregate.w[h][0];
+                    me.w[1] = aggregate.w[h][1];
+                    me.w[2] = aggregate.w[h][2];
+                    me.w[3] = aggregate.w[h][3] | (LB_AGG << 30);
+                    lb_store(&state[(uint64_t) tile * HALVES + h], me);
+                }
             }
             int64_t base = (int64_t) tile - 1;
             for (;;) {
-                const int64_t p = base - lane;
-                uint32_t f = 2u;
-                if (p >= 0) {
-                    do {
-                        f = *((volatile uint32_t *) &lb.flag[p]);
-                    } while (f == 0u);
-                }
-                __threadfence();
-                const uint32_t incl_mask = __ballot_sync(0xffffffffu, f == 2u);
-                const int stop = incl_mask != 0u ? (__ffs(incl_mask) - 1) : 32;
-                T v = T();
-                if (p >= 0 && lane <= stop) {
-                    v = f == 2u ? ld_cg_pod(&lb.incl[p]) : ld_cg_pod(&lb.agg[p]);
+                V part;
+                part.clear();
+                int stop = LB_WINDOW; // offset of the nearest predecessor with an inclusive prefix
+#pragma unroll
+                for (int r = 0; r < LB_PER_LANE; r++) {
+                    if (stop != LB_WINDOW) {
+                        break; // (warp-uniform) an inclusive prefix was found among nearer tiles
+                    }
+                    const int64_t p = base - (r * 32 + lane);
+                    V v;
+                    v.clear();
+                    uint32_t flag = LB_INCL; // before the first tile: an inclusive prefix of zero
+                    if (p >= 0) {
+                        for (;;) {
+                            bool ok = true;
+                            flag = 0;
+#pragma unroll
+                            for (int h = 0; h < HALVES; h++) {
+                                const LbWord x = lb_load(&state[(uint64_t) p * HALVES + h]);
+                                const uint32_t f = x.w[3] >> 30;
+                                ok = ok && f != 0 && (h == 0 || f == flag);
+                                flag = f;
+                                v.w[h][0] = x.w[0];
+                                v.w[h][1] = x.w[1];
+                                v.w[h][2] = x.w[2];
+                                v.w[h][3] = x.w[3] & 0x3fffffffu;
+                            }
+                            if (ok) {
+                                break;
+                            }
+                        }
+                    }
+                    const uint32_t incl = __ballot_sync(0xffffffffu, flag == LB_INCL);
+                    if (stop == LB_WINDOW && incl != 0u) {
+                        stop = r * 32 + (__ffs(incl) - 1);
+                    }
+                    if (r * 32 + lane <= stop) {
+                        part.add(v);
+                    }
                 }
 #pragma unroll
-                for (int s = 16; s > 0; s >>= 1) {
-                    v = v + shfl_xor_pod(v, s);
+                for (int sft = 16; sft > 0; sft >>= 1) {
+                    V o;
+#pragma unroll
+                    for (int h = 0; h < HALVES; h++) {
+#pragma unroll
+                        for (int q = 0; q < 4; q++) {
+                            o.w[h][q] = __shfl_xor_sync(0xffffffffu, part.w[h][q], sft);
+                        }
+                    }
+                    part.add(o);
                 }
-                prefix = prefix + v;
-                if (incl_mask != 0u) {
+                prefix.add(part);
+                if (stop < LB_WINDOW) {
                     break;
                 }
-                base -= 32;
+                base -= LB_WINDOW;
+            }
+        }
+        V inclusive = prefix;
+        inclusive.add(aggregate);
+#pragma unroll
+        for (int h = 0; h < HALVES; h++) {
+            if (lane == h) {
+                LbWord me;
+                me.w[0] = inclusive.w[h][0];
+                me.w[1] = inclusive.w[h][1];
+                me.w[2] = inclusive.w[h][2];
+                me.w[3] = inclusive.w[h][3] | (LB_INCL << 30);
+                lb_store(&state[(uint64_t) tile * HALVES + h], me);
             }
         }
         if (lane == 0) {
-            const T inclusive = prefix + aggregate;
-            st_cg_pod(&lb.incl[tile], inclusive);
-            __threadfence();
-            *((volatile uint32_t *) &lb.flag[tile]) = 2u;
             *bcast = prefix;
-            if (total != nullptr && tile + 1 == num_tiles) {
-                *total = inclusive;
-            }
         }
     }
     __syncthreads();
-    const T r = *bcast;
+    const V r = *bcast;
     __syncthreads();
     return r;
 }

@@ -83,7 +83,9 @@ struct CallView {
     double start_time, end_time;
     double slice_left, slice_right;
     int discrete;
-    int sliced;
+    int sliced; // invariant slicing: draw every edge whole, keep what falls inside the slice
+    int clipped; // clipped slicing: edges are cut to the slice and drawn on stream `stream`
+    uint32_t stream; // Philox stream of a clipped slice (0 otherwise)
     uint64_t seed;
     int key_mode;
 };
@@ -204,20 +206,30 @@ MSPB_DEVFN EdgeDraw edge_draw(const TreeSeqView &ts, const RateMapView &map, con
     EdgeDraw d;
     d.left = ts.edge_left[e];
     d.right = ts.edge_right[e];
+    if (call.clipped) {
+        d.left = fmax(d.left, call.slice_left);
+        d.right = fmin(d.right, call.slice_right);
+        if (!(d.left < d.right)) {
+            // outside this call's slice: nothing to draw, skip the node-time gathers
+            d.child = 0;
+            d.branch_start = d.branch_end = d.mass_lo = d.mass = 0.0;
+            return d;
+        }
+    }
     d.child = ts.edge_child[e];
     const double tc = ts.node_time[d.child];
     const double tp = ts.node_time[ts.edge_parent[e]];
     d.branch_start = fmax(call.start_time, tc);
     d.branch_end = fmin(call.end_time, tp);
     d.mass_lo = map.mass_upto(d.left);
-    d.mass = map.mass_upto(d.right) - d.mass_lo;
+    d.mass = d.left < d.right ? map.mass_upto(d.right) - d.mass_lo : 0.0;
     return d;
 }
 
-MSPB_DEVFN void place_one(const Philox &ph, const RateMapView &map, const EdgeDraw &d, uint64_t e, uint32_t k,
-    double *pos, double *time)
+MSPB_DEVFN void place_one(const Philox &ph, const RateMapView &map, const CallView &call, const EdgeDraw &d,
+    uint64_t e, uint32_t k, double *pos, double *time)
 {
-    const uint4 r = ph((uint32_t) e, (uint32_t) (e >> 32), k, TAG_PLACE);
+    const uint4 r = ph((uint32_t) e, call.stream, k, TAG_PLACE);
     const double up = u53(r.x, r.y), ut = u53(r.z, r.w);
     *pos = map.position_at(d.mass_lo + up * d.mass, d.left, d.right);
     double t = d.branch_start + ut * (d.branch_end - d.branch_start);
@@ -235,7 +247,7 @@ MSPB_DEVFN uint32_t k1_in_slice(const Philox &ph, const RateMapView &map, const 
     if (call.sliced && n > 0 && d.left < call.slice_right && d.right > call.slice_left) {
         for (uint32_t q = 0; q < n; q++) {
             double x, t;
-            place_one(ph, map, d, e, q, &x, &t);
+            place_one(ph, map, call, d, e, q, &x, &t);
             in += (x >= call.slice_left && x < call.slice_right) ? 1u : 0u;
         }
     }
@@ -249,11 +261,10 @@ constexpr int K1_TILE = SCAN_THREADS * K1_ITEMS;
 // call's genome slice.  Both are prefix-summed here (low / high half of one 64-bit sum):
 // goff[e] = mutations of earlier edges (goff[E] = all), loff[e] = in-slice ones.
 __global__ void __launch_bounds__(SCAN_THREADS, 4) k1_count_scan_kernel(TreeSeqView ts, RateMapView map, CallView call,
-    Lookback<uint64_t> lb, uint32_t num_tiles, uint32_t *__restrict__ goff, uint32_t *__restrict__ loff,
-    uint64_t *total)
+    LbWord *lb, uint32_t num_tiles, uint32_t *__restrict__ goff, uint32_t *__restrict__ loff, uint64_t *total)
 {
     __shared__ uint64_t sm[9];
-    __shared__ uint64_t bcast;
+    __shared__ LbVal<1, false> bcast;
     __shared__ uint64_t s_c[K1_TILE];
     __shared__ uint16_t s_big[K1_TILE]; // edges whose mean needs the rejection sampler
     __shared__ uint32_t s_nbig;
@@ -277,7 +288,7 @@ __global__ void __launch_bounds__(SCAN_THREADS, 4) k1_count_scan_kernel(TreeSeqV
             if (mu >= POISSON_SMALL_MU) {
                 s_big[atomicAdd(&s_nbig, 1u)] = (uint16_t) j;
             } else if (mu > 0.0) {
-                PhiloxSeq rng(call.seed, e, TAG_COUNT);
+                PhiloxSeq rng(call.seed, e | ((uint64_t) call.stream << 32), TAG_COUNT);
                 const uint32_t n = poisson_small(rng.next(), mu);
                 c = (uint64_t) n | ((uint64_t) k1_in_slice(ph, map, call, d, e, n) << 32);
             }
@@ -290,7 +301,7 @@ __global__ void __launch_bounds__(SCAN_THREADS, 4) k1_count_scan_kernel(TreeSeqV
         const uint64_t e = tile_base + j;
         const EdgeDraw d = edge_draw(ts, map, call, e);
         const double mu = (d.branch_end - d.branch_start) * d.mass;
-        PhiloxSeq rng(call.seed, e, TAG_COUNT);
+        PhiloxSeq rng(call.seed, e | ((uint64_t) call.stream << 32), TAG_COUNT);
         const uint32_t n = poisson_native(rng, mu);
         s_c[j] = (uint64_t) n | ((uint64_t) k1_in_slice(ph, map, call, d, e, n) << 32);
     }
@@ -305,7 +316,16 @@ __global__ void __launch_bounds__(SCAN_THREADS, 4) k1_count_scan_kernel(TreeSeqV
     }
     uint64_t block_total;
     const uint64_t ex = block_exclusive_scan<uint64_t>(acc, sm, &block_total);
-    uint64_t run = lookback_exclusive<uint64_t>(lb, blockIdx.x, num_tiles, block_total, &bcast, total) + ex;
+    LbVal<1, false> agg;
+    agg.clear();
+    agg.w[0][0] = (uint32_t) block_total;
+    agg.w[0][1] = (uint32_t) (block_total >> 32);
+    const LbVal<1, false> pre = lookback_prefix<1, false>(lb, blockIdx.x, agg, &bcast);
+    const uint64_t tile_prefix = (uint64_t) pre.w[0][0] | ((uint64_t) pre.w[0][1] << 32);
+    if (blockIdx.x + 1 == num_tiles && threadIdx.x == 0) {
+        *total = tile_prefix + block_total;
+    }
+    uint64_t run = tile_prefix + ex;
 #pragma unroll
     for (int k = 0; k < K1_ITEMS; k++) {
         s_c[threadIdx.x * K1_ITEMS + k] = run;
@@ -378,7 +398,7 @@ __global__ void __launch_bounds__(K2_EDGES) k2_place_kernel(TreeSeqView ts, Rate
                 }
             }
             const EdgeDraw &d = sd[lo];
-            place_one(ph, map, d, ebase + lo, j - soff[lo], &x, &t);
+            place_one(ph, map, call, d, ebase + lo, j - soff[lo], &x, &t);
             child = d.child;
             in = !call.sliced || (x >= call.slice_left && x < call.slice_right);
         }
@@ -620,28 +640,28 @@ constexpr int P1_TILE = SCAN_THREADS * P1_ITEMS;
 // and allele draws before it, plus the input checks that need the sorted order (two
 // kept sites at one position, lib/mutgen.c:875-879; a new mutation sharing a position
 // in the continuous genome, which the reference redraws, lib/mutgen.c:1127-1134).
-__global__ void __launch_bounds__(SCAN_THREADS) p1_sites_kernel(SortedView sv, int discrete, Lookback<Counts3> lb,
+// Global reads and writes are striped (coalesced); the scan runs on per-record flag
+// bytes transposed through shared memory.
+__global__ void __launch_bounds__(SCAN_THREADS) p1_sites_kernel(SortedView sv, int discrete, LbWord *lb,
     uint32_t num_tiles, Counts3 *total, uint32_t *__restrict__ multi_list, uint32_t *collisions, uint32_t *dense,
     int *err)
 {
     __shared__ uint64_t sm[9];
-    __shared__ Counts3 bcast;
-    const uint64_t i0 = (uint64_t) blockIdx.x * P1_TILE + (uint64_t) threadIdx.x * P1_ITEMS;
-    uint32_t hb = 0, mb = 0, db = 0, ub = 0; // per-item bit flags
-    uint64_t acc = 0; // s | m << 16 | d << 32 | u << 48 (tile-local, each < 2^16)
-#pragma unroll
+    __shared__ LbVal<1, false> bcast;
+    __shared__ __align__(16) uint8_t s_flag[P1_TILE]; // head | mut << 1 | draws << 2 (2 bits) | multi << 4
+    __shared__ uint16_t s_site[P1_TILE], s_mut[P1_TILE], s_draw[P1_TILE], s_multi[P1_TILE];
+    const uint64_t base = (uint64_t) blockIdx.x * P1_TILE;
+#pragma unroll 4
     for (int k = 0; k < P1_ITEMS; k++) {
-        const uint64_t i = i0 + k;
+        const uint32_t j = (uint32_t) k * SCAN_THREADS + threadIdx.x;
+        const uint64_t i = base + j;
+        uint32_t f = 0;
         if (i < sv.n) {
             const bool h = sv.head(i);
             const bool mu = sv.is_mut(i), nw = sv.is_new(i);
             const uint32_t d = (nw ? 1u : 0u) + ((h && mu) ? 1u : 0u);
             const bool multi = h && i + 1 < sv.n && !sv.head(i + 1);
-            hb |= (h ? 1u : 0u) << k;
-            mb |= (mu ? 1u : 0u) << k;
-            db |= d << (2 * k);
-            ub |= (multi ? 1u : 0u) << k;
-            acc += (h ? 1ull : 0ull) | ((mu ? 1ull : 0ull) << 16) | ((uint64_t) d << 32) | ((multi ? 1ull : 0ull) << 48);
+            f = (h ? 1u : 0u) | ((mu ? 1u : 0u) << 1) | (d << 2) | ((multi ? 1u : 0u) << 4);
             if (!h) {
                 if (sv.has_kept && sv.val[i] < sv.S0) {
                     set_error(err, -21); // MSP_ERR_DUPLICATE_SITE_POSITION
@@ -654,33 +674,66 @@ __global__ void __launch_bounds__(SCAN_THREADS) p1_sites_kernel(SortedView sv, i
                 }
             }
         }
+        s_flag[j] = (uint8_t) f;
+    }
+    __syncthreads();
+    // blocked: thread t owns records t * P1_ITEMS ..
+    uint32_t fl[P1_ITEMS];
+    uint64_t acc = 0; // s | m << 16 | d << 32 | u << 48 (tile-local, each < 2^16)
+    {
+        const uint4 w = reinterpret_cast<const uint4 *>(s_flag)[threadIdx.x];
+        const uint32_t ww[4] = { w.x, w.y, w.z, w.w };
+#pragma unroll
+        for (int k = 0; k < P1_ITEMS; k++) {
+            fl[k] = (ww[k >> 2] >> (8 * (k & 3))) & 0xffu;
+            acc += (uint64_t) (fl[k] & 1u) | ((uint64_t) ((fl[k] >> 1) & 1u) << 16)
+                   | ((uint64_t) ((fl[k] >> 2) & 3u) << 32) | ((uint64_t) ((fl[k] >> 4) & 1u) << 48);
+        }
     }
     uint64_t block_total;
-    const uint64_t ex = block_exclusive_scan<uint64_t>(acc, sm, &block_total);
-    Counts3 agg;
-    agg.s = (uint32_t) (block_total & 0xffffull);
-    agg.m = (uint32_t) ((block_total >> 16) & 0xffffull);
-    agg.d = (uint32_t) ((block_total >> 32) & 0xffffull);
-    agg.u = (uint32_t) (block_total >> 48);
-    const Counts3 pre = lookback_exclusive<Counts3>(lb, blockIdx.x, num_tiles, agg, &bcast, total);
-    uint32_t s = pre.s + (uint32_t) (ex & 0xffffull);
-    uint32_t m = pre.m + (uint32_t) ((ex >> 16) & 0xffffull);
-    uint32_t d = pre.d + (uint32_t) ((ex >> 32) & 0xffffull);
-    uint32_t u = pre.u + (uint32_t) (ex >> 48);
+    uint64_t run = block_exclusive_scan<uint64_t>(acc, sm, &block_total);
+    LbVal<1, false> agg;
+    agg.w[0][0] = (uint32_t) (block_total & 0xffffull); // sites
+    agg.w[0][1] = (uint32_t) ((block_total >> 16) & 0xffffull); // mutation rows
+    agg.w[0][2] = (uint32_t) ((block_total >> 32) & 0xffffull); // draws
+    agg.w[0][3] = (uint32_t) (block_total >> 48); // multi-record sites (< 2^30: carries the status bits)
 #pragma unroll
     for (int k = 0; k < P1_ITEMS; k++) {
-        const uint64_t i = i0 + k;
+        const uint32_t j = threadIdx.x * P1_ITEMS + k;
+        // site: inclusive count (the record's own site row is count - 1); others exclusive
+        s_site[j] = (uint16_t) ((run & 0xffffull) + (fl[k] & 1u));
+        s_mut[j] = (uint16_t) ((run >> 16) & 0xffffull);
+        s_draw[j] = (uint16_t) ((run >> 32) & 0xffffull);
+        s_multi[j] = (uint16_t) (run >> 48);
+        run += (uint64_t) (fl[k] & 1u) | ((uint64_t) ((fl[k] >> 1) & 1u) << 16)
+               | ((uint64_t) ((fl[k] >> 2) & 3u) << 32) | ((uint64_t) ((fl[k] >> 4) & 1u) << 48);
+    }
+    const LbVal<1, false> pw = lookback_prefix<1, false>(lb, blockIdx.x, agg, &bcast);
+    Counts3 pre;
+    pre.s = pw.w[0][0];
+    pre.m = pw.w[0][1];
+    pre.d = pw.w[0][2];
+    pre.u = pw.w[0][3];
+    if (blockIdx.x + 1 == num_tiles && threadIdx.x == 0) {
+        Counts3 all;
+        all.s = pre.s + agg.w[0][0];
+        all.m = pre.m + agg.w[0][1];
+        all.d = pre.d + agg.w[0][2];
+        all.u = pre.u + agg.w[0][3];
+        *total = all;
+    }
+#pragma unroll 4
+    for (int k = 0; k < P1_ITEMS; k++) {
+        const uint32_t j = (uint32_t) k * SCAN_THREADS + threadIdx.x;
+        const uint64_t i = base + j;
         if (i < sv.n) {
-            s += (hb >> k) & 1u;
-            sv.site_row[i] = s - 1u;
+            sv.site_row[i] = pre.s + s_site[j] - 1u;
             if (sv.has_kept) {
-                sv.mut_scan[i] = m;
-                sv.draw_scan[i] = d;
+                sv.mut_scan[i] = pre.m + s_mut[j];
+                sv.draw_scan[i] = pre.d + s_draw[j];
             }
-            m += (mb >> k) & 1u;
-            d += (db >> (2 * k)) & 3u;
-            if ((ub >> k) & 1u) {
-                multi_list[u++] = (uint32_t) i;
+            if ((s_flag[j] >> 4) & 1u) {
+                multi_list[pre.u + s_multi[j]] = (uint32_t) i;
             }
         }
     }
@@ -745,9 +798,9 @@ MSPB_DEVFN double phase_b_uniform(const ResolveView &rv, uint64_t idx, int *err)
 
 // uniforms of the allele draws of the new mutation with ordinal `ord`:
 // root (if it opens a new site) and transition
-MSPB_DEVFN void allele_uniforms(const Philox &ph, uint32_t ord, double *u_root, double *u_trans)
+MSPB_DEVFN void allele_uniforms(const Philox &ph, uint32_t stream, uint32_t ord, double *u_root, double *u_trans)
 {
-    const uint4 w = ph(ord, 0u, 0u, TAG_ALLELE);
+    const uint4 w = ph(ord, stream, 0u, TAG_ALLELE);
     *u_trans = u53(w.x, w.y);
     *u_root = u53(w.z, w.w);
 }
@@ -809,7 +862,7 @@ MSPB_DEVFN void resolve_site(const TreeSeqView &ts, const KeptView &kept, const 
             if (rv.replay != nullptr) {
                 u = phase_b_uniform(rv, draw0, err);
             } else {
-                allele_uniforms(ph, sv.rec[r0].ord, &u, &ut);
+                allele_uniforms(ph, call.stream, sv.rec[r0].ord, &u, &ut);
             }
             anc = (int32_t) select_prob(u, model.num_alleles, model.root);
             rv.site_state[i] = anc;
@@ -864,7 +917,7 @@ MSPB_DEVFN void resolve_site(const TreeSeqView &ts, const KeptView &kept, const 
                 if (rv.replay != nullptr) {
                     u = phase_b_uniform(rv, (uint64_t) cur + opens, err);
                 } else {
-                    allele_uniforms(ph, sv.rec[r].ord, &ur, &u);
+                    allele_uniforms(ph, call.stream, sv.rec[r].ord, &ur, &u);
                 }
                 if (pa < 0) {
                     set_error(err, -51); // MSP_ERR_UNKNOWN_ALLELE
@@ -981,7 +1034,7 @@ struct EmitRec {
 };
 
 MSPB_DEVFN EmitRec emit_record(const SortedView &sv, const ResolveView &rv, const KeptView &kept,
-    const ModelView &model, const Philox &ph, uint64_t i, int *err)
+    const ModelView &model, const Philox &ph, uint32_t stream, uint64_t i, int *err)
 {
     EmitRec q;
     q.r = sv.has_kept ? sv.val[i] : 0u;
@@ -1003,7 +1056,7 @@ MSPB_DEVFN EmitRec emit_record(const SortedView &sv, const ResolveView &rv, cons
                     ur = phase_b_uniform(rv, d, err);
                     ut = phase_b_uniform(rv, d + 1, err);
                 } else {
-                    allele_uniforms(ph, sv.rec[sv.val[i]].ord, &ur, &ut);
+                    allele_uniforms(ph, stream, sv.rec[sv.val[i]].ord, &ur, &ut);
                 }
                 q.site_state = (int32_t) select_prob(ur, model.num_alleles, model.root);
                 q.state = (int32_t) select_prob(
@@ -1088,11 +1141,11 @@ MSPB_DEVFN void flush_stage(const char *stage, char *dst_base, uint64_t g0, uint
 // striped (thread t takes t, t + 256, ...) so that row stores are coalesced; state bytes
 // are assembled in shared memory and flushed with 16-byte stores.
 __global__ void __launch_bounds__(SCAN_THREADS) k5_emit_kernel(SortedView sv, ResolveView rv, KeptView kept,
-    ModelView model, CallView call, OutView out, Lookback<Bytes4> lb, uint32_t num_tiles, const Counts3 *p1_total,
+    ModelView model, CallView call, OutView out, LbWord *lb, uint32_t num_tiles, const Counts3 *p1_total,
     Bytes4 *total, const uint32_t *dense, int *err)
 {
     __shared__ uint64_t sm[9];
-    __shared__ Bytes4 bcast;
+    __shared__ LbVal<2, true> bcast;
     __shared__ uint32_t s_der[K5_TILE], s_anc[K5_TILE], s_mmd[K5_TILE], s_smd[K5_TILE];
     __shared__ __align__(16) char st_der[K5_STAGE + 32];
     __shared__ __align__(16) char st_anc[K5_STAGE + 32];
@@ -1108,7 +1161,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) k5_emit_kernel(SortedView sv, Re
         const uint64_t i = base + j;
         uint32_t d = 0, a = 0, md = 0, sd = 0;
         if (i < sv.n) {
-            const EmitRec q = emit_record(sv, rv, kept, model, ph, i, err);
+            const EmitRec q = emit_record(sv, rv, kept, model, ph, call.stream, i, err);
             d = q.der_len;
             a = q.anc_len;
             md = q.mmd_len;
@@ -1130,8 +1183,23 @@ __global__ void __launch_bounds__(SCAN_THREADS) k5_emit_kernel(SortedView sv, Re
         agg.mmd = tile_offsets(s_mmd, sm);
         agg.smd = tile_offsets(s_smd, sm);
     }
-    const Bytes4 pre = lookback_exclusive<Bytes4>(lb, blockIdx.x, num_tiles, agg, &bcast, total);
+    LbVal<2, true> aw; // half 0: derived, mutation metadata; half 1: ancestral, site metadata
+    aw.w[0][0] = (uint32_t) agg.der;
+    aw.w[0][1] = (uint32_t) (agg.der >> 32);
+    aw.w[0][2] = (uint32_t) agg.mmd;
+    aw.w[0][3] = (uint32_t) (agg.mmd >> 32);
+    aw.w[1][0] = (uint32_t) agg.anc;
+    aw.w[1][1] = (uint32_t) (agg.anc >> 32);
+    aw.w[1][2] = (uint32_t) agg.smd;
+    aw.w[1][3] = (uint32_t) (agg.smd >> 32);
+    const LbVal<2, true> pw = lookback_prefix<2, true>(lb, blockIdx.x, aw, &bcast);
+    Bytes4 pre;
+    pre.der = (uint64_t) pw.w[0][0] | ((uint64_t) pw.w[0][1] << 32);
+    pre.mmd = (uint64_t) pw.w[0][2] | ((uint64_t) pw.w[0][3] << 32);
+    pre.anc = (uint64_t) pw.w[1][0] | ((uint64_t) pw.w[1][1] << 32);
+    pre.smd = (uint64_t) pw.w[1][2] | ((uint64_t) pw.w[1][3] << 32);
     if (blockIdx.x + 1 == num_tiles && threadIdx.x == 0) {
+        *total = pre + agg;
         out.store_off(out.site_anc_off, p1_total->s, pre.anc + agg.anc);
         out.store_off(out.mut_der_off, p1_total->m, pre.der + agg.der);
         if (out.write_md_off) {
@@ -1142,7 +1210,16 @@ __global__ void __launch_bounds__(SCAN_THREADS) k5_emit_kernel(SortedView sv, Re
     const bool stage_der = agg.der <= K5_STAGE, stage_anc = agg.anc <= K5_STAGE;
     char *der_base = stage_der ? st_der + (pre.der & 15ull) : out.mut_der + pre.der;
     char *anc_base = stage_anc ? st_anc + (pre.anc & 15ull) : out.site_anc + pre.anc;
-    // ---- rows and bytes
+    // ---- rows and bytes.  The record gathers (one random sector each) are issued for all
+    // of the thread's items before any of them is used.
+    Rec rcs[K5_ITEMS];
+#pragma unroll
+    for (int k = 0; k < K5_ITEMS; k++) {
+        const uint64_t i = base + (uint32_t) k * SCAN_THREADS + threadIdx.x;
+        if (i < sv.n) {
+            rcs[k] = sv.rec[sv.val[i]];
+        }
+    }
 #pragma unroll
     for (int k = 0; k < K5_ITEMS; k++) {
         const uint32_t j = (uint32_t) k * SCAN_THREADS + threadIdx.x;
@@ -1150,7 +1227,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) k5_emit_kernel(SortedView sv, Re
         if (i >= sv.n) {
             continue;
         }
-        const EmitRec e = emit_record(sv, rv, kept, model, ph, i, err);
+        const EmitRec e = emit_record(sv, rv, kept, model, ph, call.stream, i, err);
         const uint32_t site_row = sv.site_row[i];
         if (e.head) {
             char *anc_dst = anc_base + s_anc[j];
@@ -1170,7 +1247,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) k5_emit_kernel(SortedView sv, Re
         }
         if (e.is_mut) {
             const uint32_t row = sv.mut_row(i);
-            const Rec rc = sv.rec[sv.val[i]];
+            const Rec rc = rcs[k];
             int32_t par = -1;
             if (!e.single) {
                 const int32_t p = rv.parent[i];

@@ -98,8 +98,7 @@ struct mspb_ctx {
     DBuf<uint32_t> k32_0, k32_1; // 32-bit keys (ping-pong)
     DBuf<uint32_t> vals0, vals1, tile_hist, rs_scan_tiles;
     DBuf<uint64_t> or_and;
-    DBuf<uint32_t> lb_flag; // look-back scan state, shared by K1, P1 and K5 (stream ordered)
-    DBuf<char> lb_agg, lb_incl;
+    DBuf<LbWord> lb_state; // look-back scan state, shared by K1, P1 and K5 (stream ordered)
     DBuf<uint32_t> site_scan, mut_scan, draw_scan, multi_list;
     DBuf<int32_t> parent, state, site_state;
     DBuf<uint32_t> rp_edge, rp_interval, rp_count, rp_out_off;
@@ -295,7 +294,7 @@ extern "C" void mspb_ctx_destroy(mspb_ctx_t *ctx)
     REL(map_pos); REL(map_rate); REL(map_cum); REL(model_root); REL(model_matrix); REL(replay);
     REL(model_alleles); REL(model_allele_off);
     REL(goff); REL(loff); REL(rec); REL(keys0); REL(keys1); REL(k32_0); REL(k32_1); REL(vals0); REL(vals1);
-    REL(tile_hist); REL(rs_scan_tiles); REL(or_and); REL(lb_flag); REL(lb_agg); REL(lb_incl);
+    REL(tile_hist); REL(rs_scan_tiles); REL(or_and); REL(lb_state);
     REL(site_scan); REL(mut_scan); REL(draw_scan); REL(multi_list); REL(parent); REL(state); REL(site_state);
     REL(rp_edge); REL(rp_interval); REL(rp_count); REL(rp_out_off); REL(rp_stream_off); REL(dev_totals);
     REL(o_site_pos); REL(o_mut_time); REL(o_site_anc); REL(o_site_md); REL(o_mut_der); REL(o_mut_md);
@@ -528,17 +527,12 @@ RadixSortBuffers<uint32_t> sort_buffers32(mspb_ctx *ctx)
     return b;
 }
 
-// look-back state for `tiles` tiles of a scan over T; flags are cleared on the stream
-template <typename T>
-int lookback_state(mspb_ctx *ctx, uint64_t tiles, Lookback<T> *lb)
+// look-back state for `tiles` tiles of `halves` 16-byte words each, cleared on the stream
+int lookback_state(mspb_ctx *ctx, uint64_t tiles, int halves, LbWord **lb)
 {
-    TRY(ctx->lb_flag.ensure(tiles + 1));
-    TRY(ctx->lb_agg.ensure((tiles + 1) * sizeof(T)));
-    TRY(ctx->lb_incl.ensure((tiles + 1) * sizeof(T)));
-    CUDA_OK(cudaMemsetAsync(ctx->lb_flag.p, 0, (tiles + 1) * sizeof(uint32_t), ctx->stream));
-    lb->flag = ctx->lb_flag.p;
-    lb->agg = reinterpret_cast<T *>(ctx->lb_agg.p);
-    lb->incl = reinterpret_cast<T *>(ctx->lb_incl.p);
+    TRY(ctx->lb_state.ensure((tiles + 1) * halves));
+    CUDA_OK(cudaMemsetAsync(ctx->lb_state.p, 0, (tiles + 1) * halves * sizeof(LbWord), ctx->stream));
+    *lb = ctx->lb_state.p;
     return 0;
 }
 
@@ -934,8 +928,8 @@ int launch_emit(mspb_ctx *ctx)
     HostTotals *dt = (HostTotals *) ctx->dev_totals.p;
     const uint64_t R = ctx->pending.R;
     const uint32_t k5_tiles = (uint32_t) ((R + K5_TILE - 1) / K5_TILE);
-    Lookback<Bytes4> lb4;
-    TRY(lookback_state<Bytes4>(ctx, k5_tiles, &lb4));
+    LbWord *lb4 = nullptr;
+    TRY(lookback_state(ctx, k5_tiles, 2, &lb4));
     MSPB_LAUNCH(ctx->log, "k5_emit",
         k5_emit_kernel<<<k5_tiles, SCAN_THREADS, 0, st>>>(ctx->pending.sv, ctx->pending.rv, ctx->pending.kept,
             ctx->pending.model, ctx->pending.call, ctx->pending.out, lb4, k5_tiles, &dt->p1, &dt->bytes, &dt->dense,
@@ -991,8 +985,8 @@ int run_sorted_stages(mspb_ctx *ctx, const mspb_params_t *p, const TreeSeqView &
         CUDA_OK(cudaEventRecord(ctx->ev[4], st));
     }
     const uint32_t p1_tiles = (uint32_t) ((R + P1_TILE - 1) / P1_TILE);
-    Lookback<Counts3> lb3;
-    TRY(lookback_state<Counts3>(ctx, p1_tiles, &lb3));
+    LbWord *lb3 = nullptr;
+    TRY(lookback_state(ctx, p1_tiles, 1, &lb3));
     CUDA_OK(cudaMemsetAsync(&dt->dense, 0, sizeof(uint32_t), st));
     MSPB_LAUNCH(ctx->log, "p1_sites",
         p1_sites_kernel<<<p1_tiles, SCAN_THREADS, 0, st>>>(sv, call.discrete, lb3, p1_tiles, &dt->p1,
@@ -1061,10 +1055,15 @@ static int generate_impl(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t 
         return MSPB_ERR_BAD_PARAM_VALUE; /* lib/mutgen.c:786 */
     }
     const bool replay = p->replay_stream != nullptr;
-    const bool sliced = !(p->slice_left == 0.0 && (p->slice_right == 0.0 || p->slice_right >= ctx->L));
-    if (sliced && (replay || !(p->slice_left < p->slice_right) || p->slice_left < 0)) {
+    const bool in_slice = !(p->slice_left == 0.0 && (p->slice_right == 0.0 || p->slice_right >= ctx->L));
+    if (in_slice && (replay || !(p->slice_left < p->slice_right) || p->slice_left < 0)) {
         return MSPB_ERR_BAD_PARAM_VALUE;
     }
+    // two ways to own a slice: draw whole edges and keep what falls inside (slice_stream == 0:
+    // the union of slices is exactly the unsliced result), or cut the edges to the slice and
+    // draw on the slice's own Philox stream (slice_stream != 0: work scales with the slice)
+    const bool clipped = in_slice && p->slice_stream != 0;
+    const bool sliced = in_slice && !clipped;
     const bool keep = p->keep != 0;
     const bool discrete = p->discrete_genome != 0;
     uint64_t S0 = keep ? ctx->S0 : 0, M0 = keep ? ctx->M0 : 0, site_lo = 0, mut_lo = 0;
@@ -1081,12 +1080,14 @@ static int generate_impl(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t 
     call.start_time = p->start_time;
     call.end_time = p->end_time;
     call.slice_left = p->slice_left;
-    call.slice_right = sliced ? p->slice_right : ctx->L;
+    call.slice_right = in_slice ? p->slice_right : ctx->L;
     call.discrete = discrete ? 1 : 0;
     call.sliced = sliced ? 1 : 0;
+    call.clipped = clipped ? 1 : 0;
+    call.stream = clipped ? p->slice_stream : 0u;
     call.seed = p->seed;
     call.key_mode = (discrete && ctx->L <= 4294967296.0 && !(keep && ctx->kept_fractional)) ? KEY32_POS : KEY64_POS;
-    if (sliced && S0 + M0 > 0) {
+    if (in_slice && S0 + M0 > 0) {
         // which kept rows this slice owns (read back with the K1 totals)
         const uint64_t mx = S0 > M0 ? S0 : M0;
         MSPB_LAUNCH(ctx->log, "kept_sorted_check",
@@ -1109,8 +1110,8 @@ static int generate_impl(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t 
         }
         if (ctx->E > 0) {
             const uint32_t tiles = (uint32_t) ((ctx->E + K1_TILE - 1) / K1_TILE);
-            Lookback<uint64_t> lb;
-            TRY(lookback_state<uint64_t>(ctx, tiles, &lb));
+            LbWord *lb = nullptr;
+            TRY(lookback_state(ctx, tiles, 1, &lb));
             MSPB_LAUNCH(ctx->log, "k1_count_scan",
                 k1_count_scan_kernel<<<tiles, SCAN_THREADS, 0, st>>>(
                     ts, map, call, lb, tiles, ctx->goff.p, sliced ? ctx->loff.p : nullptr, &dt->k1_total));
@@ -1146,7 +1147,7 @@ static int generate_impl(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t 
         Mnew = ht->replay.num_mutations;
         num_pairs = ht->replay.num_pairs;
     }
-    if (sliced && S0 + M0 > 0) {
+    if (in_slice && S0 + M0 > 0) {
         if (ht->kept_unsorted != 0) {
             return MSPB_ERR_UNSORTED_SITES;
         }

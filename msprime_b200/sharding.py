@@ -61,13 +61,14 @@ def dist_allgather(group=None, device=None):
     return allgather
 
 
-def run_slice(engine, params, *, rank, world, allgather, start_allele=0):
+def run_slice(engine, params, *, rank, world, allgather, start_allele=0, fetch=True, out=None):
     """Runs this rank's slice on ``engine`` (a ``_native.Context`` with tables loaded, or
     anything with the same four methods) and returns ``(local_result, info)``.
 
     ``params`` must already carry this rank's ``slice_left/right``.  The local result has
     global site ids, parent ids, allele numbers and byte offsets; ``info`` holds the global
-    totals (``num_sites``, ``num_mutations``, ``next_allele``, byte totals)."""
+    totals (``num_sites``, ``num_mutations``, ``next_allele``, byte totals).  ``fetch=False``
+    leaves the slice resident on the device; ``out`` passes preallocated host buffers."""
     c1 = engine.generate_begin(params)
     used = (int(c1["next_allele"]) - int(start_allele)) & 0xFFFFFFFFFFFFFFFF
     all1 = allgather([c1["num_sites"], c1["num_mutations"], used, c1["num_new_mutations"]])
@@ -77,7 +78,9 @@ def run_slice(engine, params, *, rank, world, allgather, start_allele=0):
                       c2["mutation_metadata_bytes"]])
     anc, smd, der, mmd = exclusive_bases(all2, rank)
     engine.shift_offsets(anc, smd, der, mmd)
-    local = engine.fetch()
+    local = None
+    if fetch:
+        local = engine.fetch(out) if out is not None else engine.fetch()
     tot1 = [sum(int(r[j]) for r in all1) for j in range(4)]
     tot2 = [sum(int(r[j]) for r in all2) for j in range(4)]
     info = {

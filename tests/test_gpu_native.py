@@ -140,6 +140,36 @@ def test_union_of_slices_equals_whole(native_built, ts_small, world, model, keep
     assert sum(a[3] for a in all1) == cw["num_new_mutations"]
 
 
+def test_clipped_slices(native_built, ts_small):
+    """slice_stream != 0: edges are cut to the slice and drawn on the slice's own stream."""
+    ts = ts_small
+    L = ts["sequence_length"]
+    world, rate = 4, 1e-6
+    cuts = sharding.slice_cuts(L, world)
+    e, nt = ts["edges"], ts["nodes"]["time"]
+    expect = ((e["right"] - e["left"]) * (nt[e["parent"]] - nt[e["child"]])).sum() * rate
+    ctx = _native.Context(0)
+    ctx.load_tables(ts)
+    total, parts, streams = 0, [], []
+    try:
+        for r in range(world):
+            p = _native.Params(map_position=[0, L], map_rate=[rate], model=cases.native_model(cases.JC69),
+                               discrete_genome=True, keep=False, start_time=-cases.FMAX, end_time=cases.FMAX,
+                               seed=9, slice_left=cuts[r], slice_right=cuts[r + 1], slice_stream=r + 1)
+            c = ctx.generate(p)
+            res = ctx.fetch()
+            pos = res["sites"]["position"]
+            assert len(pos) > 0 and pos.min() >= cuts[r] and pos.max() < cuts[r + 1]
+            table_checks.check_result(ts, res, discrete=True)
+            total += c["num_new_mutations"]
+            parts.append(res)
+            streams.append(res["mutations"]["time"][:50].copy())
+    finally:
+        ctx.close()
+    assert abs(total - expect) < 5 * np.sqrt(expect)
+    assert not np.array_equal(streams[0], streams[1])
+
+
 def test_python_surface_layers_and_provenance(native_built, ts_small):
     ts = mtables.TableCollection.fromdict(ts_small).tree_sequence()
     a = msp.sim_mutations(ts, rate=2e-7, random_seed=3, model="jc69")
