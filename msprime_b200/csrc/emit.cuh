@@ -1,0 +1,370 @@
+// msprime_b200: K5, the table writer (sm_100a).  Included by kernels.cuh.
+//
+// Replaces mutgen_populate_tables (lib/mutgen.c:1027-1074) and the allele strings of
+// infinite_alleles_make_allele (lib/mutgen.c:431-447) / the matrix model's aliasing of its
+// allele table (lib/mutgen.c:184-237).  One pass over the position-sorted records writes
+// every fixed-width column coalesced and assembles the ragged state bytes in shared memory;
+// byte offsets come from a tile scan chained across tiles by the look-back in common.cuh.
+//
+// The kernel is specialised on <model, kept rows present, offset width>: the common case
+// (no kept rows) carries no trace of the kept-row handling, and every record is classified
+// once, the result carried in registers between the length pass and the write pass.
+#pragma once
+
+namespace mspb {
+
+constexpr int K5_ITEMS = 4;
+constexpr int K5_TILE = SCAN_THREADS * K5_ITEMS;
+constexpr int K5_STAGE = 12 * 1024; // bytes of one ragged column staged per tile
+
+constexpr uint32_t EM_HEAD = 1u, EM_MUT = 2u, EM_NEW = 4u, EM_SINGLE = 8u;
+
+// two ASCII digits of p < 100, tens digit in the low byte
+MSPB_DEVFN uint32_t two_digits(uint32_t p)
+{
+    const uint32_t t = (p * 205u) >> 11; // p / 10 for p < 1029
+    return 0x3030u + t + ((p - t * 10u) << 8);
+}
+
+// the eight decimal digits of v < 10^8, zero padded, most significant digit in byte 0
+MSPB_DEVFN uint64_t eight_digits(uint32_t v)
+{
+    const uint32_t a = v / 10000u, b = v - a * 10000u;
+    const uint32_t a1 = a / 100u, a0 = a - a1 * 100u;
+    const uint32_t b1 = b / 100u, b0 = b - b1 * 100u;
+    const uint32_t lo = two_digits(a1) | (two_digits(a0) << 16);
+    const uint32_t hi = two_digits(b1) | (two_digits(b0) << 16);
+    return (uint64_t) lo | ((uint64_t) hi << 32);
+}
+
+// decimal text of v, n = num_digits(v) bytes (snprintf "%" PRIu64, lib/mutgen.c:431-447)
+MSPB_DEVFN void write_number(char *dst, uint64_t v, uint32_t n)
+{
+    if (v < 100000000ull) {
+        const uint64_t d = eight_digits((uint32_t) v) >> (8u * (8u - n));
+        const uint32_t lo = (uint32_t) d, hi = (uint32_t) (d >> 32);
+#pragma unroll
+        for (uint32_t b = 0; b < 4; b++) {
+            if (b < n) {
+                dst[b] = (char) (lo >> (8u * b));
+            }
+        }
+#pragma unroll
+        for (uint32_t b = 0; b < 4; b++) {
+            if (b + 4 < n) {
+                dst[b + 4] = (char) (hi >> (8u * b));
+            }
+        }
+    } else {
+        write_digits(dst, v, n);
+    }
+}
+
+MSPB_DEVFN void copy_bytes32(char *dst, const char *src, uint32_t n)
+{
+    for (uint32_t k = 0; k < n; k++) {
+        dst[k] = src[k];
+    }
+}
+
+template <bool OFF32>
+MSPB_DEVFN void store_offset(void *col, uint64_t row, uint64_t v)
+{
+    if (OFF32) {
+        static_cast<uint32_t *>(col)[row] = (uint32_t) v;
+    } else {
+        static_cast<uint64_t *>(col)[row] = v;
+    }
+}
+
+// Tile-local exclusive offsets of one length column held in shared memory (striped by
+// record), returning the tile total.  Thread t scans the K5_ITEMS consecutive records it
+// owns in blocked order; lens[] is overwritten with the offsets.
+template <typename SumT>
+MSPB_DEVFN uint64_t tile_offsets(uint32_t *lens, uint64_t *scan_tmp)
+{
+    static_assert(K5_ITEMS == 4, "one 16-byte shared-memory access per thread");
+    uint4 *mine = reinterpret_cast<uint4 *>(lens) + threadIdx.x;
+    const uint4 l = *mine;
+    const SumT sum = (SumT) l.x + l.y + l.z + l.w;
+    SumT total;
+    const SumT run = block_exclusive_scan<SumT>(sum, reinterpret_cast<SumT *>(scan_tmp), &total);
+    uint4 o;
+    o.x = (uint32_t) run;
+    o.y = (uint32_t) (run + l.x);
+    o.z = (uint32_t) (run + l.x + l.y);
+    o.w = (uint32_t) (run + l.x + l.y + l.z);
+    *mine = o;
+    return (uint64_t) total;
+}
+
+// Copies a tile's staged bytes to global memory with 16-byte stores.  The stage is
+// shifted by (global offset mod 16) so that aligned chunks line up on both sides.
+MSPB_DEVFN void flush_stage(const char *stage, char *dst_base, uint64_t g0, uint32_t total)
+{
+    const uint32_t shift = (uint32_t) (g0 & 15ull);
+    const uint32_t span = shift + total;
+    char *aligned = dst_base + (g0 - shift);
+    for (uint32_t lo = threadIdx.x * 16u; lo < span; lo += SCAN_THREADS * 16u) {
+        if (lo >= shift && lo + 16u <= span) {
+            *reinterpret_cast<uint4 *>(aligned + lo) = *reinterpret_cast<const uint4 *>(stage + lo);
+        } else {
+            const uint32_t hi = lo + 16u < span ? lo + 16u : span;
+            for (uint32_t b = lo < shift ? shift : lo; b < hi; b++) {
+                aligned[b] = stage[b];
+            }
+        }
+    }
+}
+
+// Both state columns of a tile in one scan (lengths packed as derived | ancestral << 32);
+// used when there are no kept rows, where a tile's state bytes are far below 2^32.
+MSPB_DEVFN void tile_offsets_pair(uint32_t *der, uint32_t *anc, uint64_t *scan_tmp, uint64_t *der_total,
+    uint64_t *anc_total)
+{
+    static_assert(K5_ITEMS == 4, "one 16-byte shared-memory access per thread");
+    uint4 *md = reinterpret_cast<uint4 *>(der) + threadIdx.x;
+    uint4 *ma = reinterpret_cast<uint4 *>(anc) + threadIdx.x;
+    const uint4 d = *md, a = *ma;
+    const uint64_t p0 = (uint64_t) d.x | ((uint64_t) a.x << 32), p1 = (uint64_t) d.y | ((uint64_t) a.y << 32);
+    const uint64_t p2 = (uint64_t) d.z | ((uint64_t) a.z << 32), p3 = (uint64_t) d.w | ((uint64_t) a.w << 32);
+    uint64_t total;
+    const uint64_t r0 = block_exclusive_scan<uint64_t>(p0 + p1 + p2 + p3, scan_tmp, &total);
+    const uint64_t r1 = r0 + p0, r2 = r1 + p1, r3 = r2 + p2;
+    uint4 od, oa;
+    od.x = (uint32_t) r0;
+    od.y = (uint32_t) r1;
+    od.z = (uint32_t) r2;
+    od.w = (uint32_t) r3;
+    oa.x = (uint32_t) (r0 >> 32);
+    oa.y = (uint32_t) (r1 >> 32);
+    oa.z = (uint32_t) (r2 >> 32);
+    oa.w = (uint32_t) (r3 >> 32);
+    *md = od;
+    *ma = oa;
+    *der_total = total & 0xffffffffull;
+    *anc_total = total >> 32;
+}
+
+struct Bytes4 {
+    uint64_t der, mmd, anc, smd;
+    MSPB_DEVFN Bytes4 operator+(const Bytes4 &o) const
+    {
+        Bytes4 r;
+        r.der = der + o.der;
+        r.mmd = mmd + o.mmd;
+        r.anc = anc + o.anc;
+        r.smd = smd + o.smd;
+        return r;
+    }
+};
+
+// MODEL: 0 matrix, 1 infinite alleles.  KEPT: kept site / mutation rows are present.
+template <int MODEL, bool KEPT, bool OFF32>
+__global__ void __launch_bounds__(SCAN_THREADS, 4) k5_emit_kernel(SortedView sv, ResolveView rv, KeptView kept,
+    ModelView model, CallView call, OutView out, LbWord *lb, uint32_t num_tiles, const Counts3 *p1_total,
+    Bytes4 *total, const uint32_t *dense, int *err)
+{
+    __shared__ uint64_t sm[9];
+    __shared__ LbVal<2, true> bcast;
+    __shared__ __align__(16) uint32_t s_der[K5_TILE];
+    __shared__ __align__(16) uint32_t s_anc[K5_TILE];
+    __shared__ __align__(16) uint32_t s_mmd[KEPT ? K5_TILE : 4];
+    __shared__ __align__(16) uint32_t s_smd[KEPT ? K5_TILE : 4];
+    __shared__ __align__(16) char st_der[K5_STAGE + 32];
+    __shared__ __align__(16) char st_anc[K5_STAGE + 32];
+    if (*dense != 0u && sv.key.mode == KEY32_POS) {
+        return;
+    }
+    const uint64_t base = (uint64_t) blockIdx.x * K5_TILE;
+    // ---- classify every record once; lengths to shared memory
+    uint32_t meta[K5_ITEMS]; // EM_* | derived length << 8 | ancestral length << 16 (infinite alleles)
+    uint32_t va[K5_ITEMS]; // infinite alleles: draws before the record; matrix: derived allele index
+    uint32_t vb[K5_ITEMS]; // matrix: ancestral allele index of a new site
+    uint32_t srow[K5_ITEMS];
+    Rec rcs[K5_ITEMS];
+#pragma unroll
+    for (int k = 0; k < K5_ITEMS; k++) {
+        const uint32_t j = (uint32_t) k * SCAN_THREADS + threadIdx.x;
+        const uint64_t i = base + j;
+        uint32_t m = 0, d = 0, a = 0, md = 0, sd = 0;
+        va[k] = vb[k] = srow[k] = 0;
+        if (i < sv.n) {
+            const uint32_t r = sv.val[i];
+            rcs[k] = sv.rec[r]; // one random sector per record: issued first, used last
+            const bool head = sv.head(i);
+            const bool single = head && (i + 1 >= sv.n || sv.head(i + 1));
+            const bool is_mut = !KEPT || r >= sv.S0;
+            const bool is_new = !KEPT || r >= sv.S0 + sv.M0;
+            const uint32_t sr = sv.site_row[i];
+            srow[k] = sr;
+            m = (head ? EM_HEAD : 0u) | (is_mut ? EM_MUT : 0u) | (is_new ? EM_NEW : 0u) | (single ? EM_SINGLE : 0u);
+            if (is_new) {
+                // a head that is a mutation opens a new site (kept sites start with their marker)
+                if (MODEL == 1) {
+                    const uint32_t db = KEPT ? sv.draw_scan[i] : (uint32_t) i + sr + 1u - (head ? 1u : 0u);
+                    const uint64_t root_number = model.start_allele + db;
+                    va[k] = db;
+                    d = num_digits(root_number + (head ? 1u : 0u));
+                    if (head) {
+                        a = num_digits(root_number);
+                    }
+                } else {
+                    int32_t s, ss = 0;
+                    if (single) {
+                        // a new site with one new mutation: root draw, then one transition
+                        double ur, ut;
+                        if (rv.replay != nullptr) {
+                            const uint64_t db = sv.draws_before(i);
+                            ur = phase_b_uniform(rv, db, err);
+                            ut = phase_b_uniform(rv, db + 1, err);
+                        } else {
+                            allele_uniforms(Philox(call.seed), call.stream, rcs[k].ord, &ur, &ut);
+                        }
+                        ss = (int32_t) select_prob(ur, model.num_alleles, model.root);
+                        s = (int32_t) select_prob(ut, model.num_alleles,
+                            model.matrix + (uint64_t) ss * model.num_alleles);
+                    } else {
+                        s = rv.state[i];
+                        if (head) {
+                            ss = rv.site_state[i];
+                        }
+                    }
+                    va[k] = (uint32_t) s;
+                    vb[k] = (uint32_t) ss;
+                    d = (uint32_t) (model.allele_off[s + 1] - model.allele_off[s]);
+                    if (head) {
+                        a = (uint32_t) (model.allele_off[ss + 1] - model.allele_off[ss]);
+                    }
+                }
+            }
+            if (KEPT) {
+                if (!is_mut) {
+                    a = (uint32_t) (kept.site_anc_off[r + 1] - kept.site_anc_off[r]);
+                    sd = (uint32_t) (kept.site_md_off[r + 1] - kept.site_md_off[r]);
+                } else if (!is_new) {
+                    const uint64_t km = r - sv.S0;
+                    d = (uint32_t) (kept.mut_der_off[km + 1] - kept.mut_der_off[km]);
+                    md = (uint32_t) (kept.mut_md_off[km + 1] - kept.mut_md_off[km]);
+                }
+            }
+            if (MODEL == 1 && is_new) {
+                m |= (d << 8) | (a << 16);
+            }
+        }
+        meta[k] = m;
+        s_der[j] = d;
+        s_anc[j] = a;
+        if (KEPT) {
+            s_mmd[j] = md;
+            s_smd[j] = sd;
+        }
+    }
+    __syncthreads();
+    // ---- offsets: inside the tile, then across tiles
+    Bytes4 agg = Bytes4();
+    if (KEPT) {
+        agg.der = tile_offsets<uint64_t>(s_der, sm);
+        agg.anc = tile_offsets<uint64_t>(s_anc, sm);
+        agg.mmd = tile_offsets<uint64_t>(s_mmd, sm);
+        agg.smd = tile_offsets<uint64_t>(s_smd, sm);
+    } else {
+        tile_offsets_pair(s_der, s_anc, sm, &agg.der, &agg.anc);
+    }
+    LbVal<2, true> aw; // half 0: derived, mutation metadata; half 1: ancestral, site metadata
+    aw.w[0][0] = (uint32_t) agg.der;
+    aw.w[0][1] = (uint32_t) (agg.der >> 32);
+    aw.w[0][2] = (uint32_t) agg.mmd;
+    aw.w[0][3] = (uint32_t) (agg.mmd >> 32);
+    aw.w[1][0] = (uint32_t) agg.anc;
+    aw.w[1][1] = (uint32_t) (agg.anc >> 32);
+    aw.w[1][2] = (uint32_t) agg.smd;
+    aw.w[1][3] = (uint32_t) (agg.smd >> 32);
+    const LbVal<2, true> pw = lookback_prefix<2, true>(lb, blockIdx.x, aw, &bcast);
+    Bytes4 pre;
+    pre.der = (uint64_t) pw.w[0][0] | ((uint64_t) pw.w[0][1] << 32);
+    pre.mmd = (uint64_t) pw.w[0][2] | ((uint64_t) pw.w[0][3] << 32);
+    pre.anc = (uint64_t) pw.w[1][0] | ((uint64_t) pw.w[1][1] << 32);
+    pre.smd = (uint64_t) pw.w[1][2] | ((uint64_t) pw.w[1][3] << 32);
+    if (blockIdx.x + 1 == num_tiles && threadIdx.x == 0) {
+        *total = pre + agg;
+        store_offset<OFF32>(out.site_anc_off, p1_total->s, pre.anc + agg.anc);
+        store_offset<OFF32>(out.mut_der_off, p1_total->m, pre.der + agg.der);
+        if (out.write_md_off) {
+            store_offset<OFF32>(out.site_md_off, p1_total->s, pre.smd + agg.smd);
+            store_offset<OFF32>(out.mut_md_off, p1_total->m, pre.mmd + agg.mmd);
+        }
+    }
+    const bool stage_der = agg.der <= K5_STAGE, stage_anc = agg.anc <= K5_STAGE;
+    char *der_base = stage_der ? st_der + (pre.der & 15ull) : out.mut_der + pre.der;
+    char *anc_base = stage_anc ? st_anc + (pre.anc & 15ull) : out.site_anc + pre.anc;
+    // ---- rows and bytes
+#pragma unroll
+    for (int k = 0; k < K5_ITEMS; k++) {
+        const uint32_t j = (uint32_t) k * SCAN_THREADS + threadIdx.x;
+        const uint64_t i = base + j;
+        if (i >= sv.n) {
+            continue;
+        }
+        const uint32_t m = meta[k];
+        const uint32_t site_row = srow[k];
+        if (m & EM_HEAD) {
+            const uint32_t ao = s_anc[j];
+            char *anc_dst = anc_base + ao;
+            out.site_position[site_row] = sv.key.position(i);
+            store_offset<OFF32>(out.site_anc_off, site_row, pre.anc + ao);
+            if (out.write_md_off) {
+                store_offset<OFF32>(out.site_md_off, site_row, pre.smd + (KEPT ? s_smd[j] : 0u));
+            }
+            if (KEPT && !(m & EM_MUT)) {
+                const uint32_t r = sv.val[i];
+                const uint64_t a0 = kept.site_anc_off[r], m0 = kept.site_md_off[r];
+                copy_bytes(anc_dst, kept.site_anc + a0, kept.site_anc_off[r + 1] - a0);
+                copy_bytes(out.site_md + pre.smd + s_smd[j], kept.site_md + m0, kept.site_md_off[r + 1] - m0);
+            } else if (MODEL == 0) {
+                const uint64_t a0 = model.allele_off[vb[k]];
+                copy_bytes32(anc_dst, model.alleles + a0, (uint32_t) (model.allele_off[vb[k] + 1] - a0));
+            } else {
+                write_number(anc_dst, model.start_allele + va[k], (m >> 16) & 0xffu);
+            }
+        }
+        if (m & EM_MUT) {
+            const uint32_t row = KEPT ? sv.mut_scan[i] : (uint32_t) i;
+            const uint32_t dof = s_der[j];
+            int32_t par = -1;
+            if (!(m & EM_SINGLE)) {
+                const int32_t p = rv.parent[i];
+                par = p < 0 ? -1 : (int32_t) ((KEPT ? sv.mut_scan[p] : (uint32_t) p) + out.mut_base);
+            }
+            char *der_dst = der_base + dof;
+            out.mut_site[row] = (int32_t) (site_row + out.site_base);
+            out.mut_node[row] = rcs[k].node;
+            out.mut_time[row] = rcs[k].time;
+            out.mut_parent[row] = par;
+            store_offset<OFF32>(out.mut_der_off, row, pre.der + dof);
+            if (out.write_md_off) {
+                store_offset<OFF32>(out.mut_md_off, row, pre.mmd + (KEPT ? s_mmd[j] : 0u));
+            }
+            if (KEPT && !(m & EM_NEW)) {
+                const uint64_t km = sv.val[i] - sv.S0;
+                const uint64_t d0 = kept.mut_der_off[km], m0 = kept.mut_md_off[km];
+                copy_bytes(der_dst, kept.mut_der + d0, kept.mut_der_off[km + 1] - d0);
+                copy_bytes(out.mut_md + pre.mmd + s_mmd[j], kept.mut_md + m0, kept.mut_md_off[km + 1] - m0);
+            } else if (MODEL == 0) {
+                const uint64_t d0 = model.allele_off[va[k]];
+                copy_bytes32(der_dst, model.alleles + d0, (uint32_t) (model.allele_off[va[k] + 1] - d0));
+            } else {
+                write_number(der_dst, model.start_allele + va[k] + ((m & EM_HEAD) ? 1u : 0u), (m >> 8) & 0xffu);
+            }
+        }
+    }
+    __syncthreads();
+    if (stage_der) {
+        flush_stage(st_der, out.mut_der, pre.der, (uint32_t) agg.der);
+    }
+    if (stage_anc) {
+        flush_stage(st_anc, out.site_anc, pre.anc, (uint32_t) agg.anc);
+    }
+}
+
+} // namespace mspb

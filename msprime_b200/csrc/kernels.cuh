@@ -1007,280 +1007,11 @@ struct OutView {
     }
 };
 
-struct Bytes4 {
-    uint64_t der, mmd, anc, smd;
-    MSPB_DEVFN Bytes4 operator+(const Bytes4 &o) const
-    {
-        Bytes4 r;
-        r.der = der + o.der;
-        r.mmd = mmd + o.mmd;
-        r.anc = anc + o.anc;
-        r.smd = smd + o.smd;
-        return r;
-    }
-};
+} // namespace mspb
 
-constexpr int K5_ITEMS = 4;
-constexpr int K5_TILE = SCAN_THREADS * K5_ITEMS;
-constexpr int K5_STAGE = 12 * 1024; // bytes of one ragged column staged per tile
+#include "emit.cuh"
 
-// Everything K5 needs to know about one sorted record.
-struct EmitRec {
-    uint32_t r; // slot
-    bool head, is_mut, is_new, new_site, single;
-    int32_t state, site_state; // matrix model allele indexes
-    uint64_t mut_number, root_number; // infinite alleles
-    uint32_t der_len, mmd_len, anc_len, smd_len;
-};
-
-MSPB_DEVFN EmitRec emit_record(const SortedView &sv, const ResolveView &rv, const KeptView &kept,
-    const ModelView &model, const Philox &ph, uint32_t stream, uint64_t i, int *err)
-{
-    EmitRec q;
-    q.r = sv.has_kept ? sv.val[i] : 0u;
-    q.head = sv.head(i);
-    q.is_mut = sv.is_mut(i);
-    q.is_new = sv.is_new(i);
-    q.new_site = q.head && q.is_mut;
-    q.state = q.site_state = -1;
-    q.mut_number = q.root_number = 0;
-    q.der_len = q.mmd_len = q.anc_len = q.smd_len = 0;
-    q.single = q.head && (i + 1 >= sv.n || sv.head(i + 1));
-    if (model.kind == 0) {
-        if (q.is_new) {
-            if (q.single) {
-                // a new site with one new mutation: root draw, then one transition
-                double ur, ut;
-                if (rv.replay != nullptr) {
-                    const uint64_t d = sv.draws_before(i);
-                    ur = phase_b_uniform(rv, d, err);
-                    ut = phase_b_uniform(rv, d + 1, err);
-                } else {
-                    allele_uniforms(ph, stream, sv.rec[sv.val[i]].ord, &ur, &ut);
-                }
-                q.site_state = (int32_t) select_prob(ur, model.num_alleles, model.root);
-                q.state = (int32_t) select_prob(
-                    ut, model.num_alleles, model.matrix + (uint64_t) q.site_state * model.num_alleles);
-            } else {
-                q.state = rv.state[i];
-                if (q.new_site) {
-                    q.site_state = rv.site_state[i];
-                }
-            }
-            q.der_len = (uint32_t) (model.allele_off[q.state + 1] - model.allele_off[q.state]);
-            if (q.new_site) {
-                q.anc_len = (uint32_t) (model.allele_off[q.site_state + 1] - model.allele_off[q.site_state]);
-            }
-        }
-    } else if (q.is_new) {
-        const uint64_t d = model.start_allele + sv.draws_before(i);
-        q.root_number = d;
-        q.mut_number = d + (q.new_site ? 1u : 0u);
-        q.der_len = num_digits(q.mut_number);
-        if (q.new_site) {
-            q.anc_len = num_digits(q.root_number);
-        }
-    }
-    if (sv.has_kept) {
-        if (!q.is_mut) {
-            q.anc_len = (uint32_t) (kept.site_anc_off[q.r + 1] - kept.site_anc_off[q.r]);
-            q.smd_len = (uint32_t) (kept.site_md_off[q.r + 1] - kept.site_md_off[q.r]);
-        } else if (!q.is_new) {
-            const uint64_t m = q.r - sv.S0;
-            q.der_len = (uint32_t) (kept.mut_der_off[m + 1] - kept.mut_der_off[m]);
-            q.mmd_len = (uint32_t) (kept.mut_md_off[m + 1] - kept.mut_md_off[m]);
-        }
-    }
-    return q;
-}
-
-// Tile-local exclusive offsets of one length column held in shared memory (striped by
-// record), returning the tile total.  Thread t scans the K5_ITEMS consecutive records it
-// owns in blocked order; lens[] is overwritten with the offsets.
-MSPB_DEVFN uint64_t tile_offsets(uint32_t *lens, uint64_t *scan_tmp)
-{
-    uint32_t l[K5_ITEMS];
-    uint64_t sum = 0;
-#pragma unroll
-    for (int k = 0; k < K5_ITEMS; k++) {
-        l[k] = lens[threadIdx.x * K5_ITEMS + k];
-        sum += l[k];
-    }
-    uint64_t total;
-    uint64_t run = block_exclusive_scan<uint64_t>(sum, scan_tmp, &total);
-#pragma unroll
-    for (int k = 0; k < K5_ITEMS; k++) {
-        lens[threadIdx.x * K5_ITEMS + k] = (uint32_t) run;
-        run += l[k];
-    }
-    return total;
-}
-
-// Copies a tile's staged bytes to global memory with 16-byte stores.  The stage is
-// shifted by (global offset mod 16) so that aligned chunks line up on both sides.
-MSPB_DEVFN void flush_stage(const char *stage, char *dst_base, uint64_t g0, uint64_t total)
-{
-    const uint32_t shift = (uint32_t) (g0 & 15ull);
-    const uint64_t span = shift + total;
-    char *aligned = dst_base + (g0 - shift);
-    for (uint64_t c = threadIdx.x; c * 16 < span; c += SCAN_THREADS) {
-        const uint64_t lo = c * 16, hi = lo + 16;
-        if (lo >= shift && hi <= span) {
-            *reinterpret_cast<uint4 *>(aligned + lo) = *reinterpret_cast<const uint4 *>(stage + lo);
-        } else {
-            for (uint64_t b = lo < shift ? shift : lo; b < hi && b < span; b++) {
-                aligned[b] = stage[b];
-            }
-        }
-    }
-}
-
-// Byte offsets of the ragged columns by look-back scan, and the table rows, in one pass
-// over the sorted records (lib/mutgen.c:1027-1074).  Single-record sites get their
-// alleles here; sites with several records read what K4 stored.  Records are handled
-// striped (thread t takes t, t + 256, ...) so that row stores are coalesced; state bytes
-// are assembled in shared memory and flushed with 16-byte stores.
-__global__ void __launch_bounds__(SCAN_THREADS) k5_emit_kernel(SortedView sv, ResolveView rv, KeptView kept,
-    ModelView model, CallView call, OutView out, LbWord *lb, uint32_t num_tiles, const Counts3 *p1_total,
-    Bytes4 *total, const uint32_t *dense, int *err)
-{
-    __shared__ uint64_t sm[9];
-    __shared__ LbVal<2, true> bcast;
-    __shared__ uint32_t s_der[K5_TILE], s_anc[K5_TILE], s_mmd[K5_TILE], s_smd[K5_TILE];
-    __shared__ __align__(16) char st_der[K5_STAGE + 32];
-    __shared__ __align__(16) char st_anc[K5_STAGE + 32];
-    if (*dense != 0u && sv.key.mode == KEY32_POS) {
-        return;
-    }
-    const uint64_t base = (uint64_t) blockIdx.x * K5_TILE;
-    const Philox ph(call.seed);
-    // ---- lengths
-#pragma unroll
-    for (int k = 0; k < K5_ITEMS; k++) {
-        const uint32_t j = (uint32_t) k * SCAN_THREADS + threadIdx.x;
-        const uint64_t i = base + j;
-        uint32_t d = 0, a = 0, md = 0, sd = 0;
-        if (i < sv.n) {
-            const EmitRec q = emit_record(sv, rv, kept, model, ph, call.stream, i, err);
-            d = q.der_len;
-            a = q.anc_len;
-            md = q.mmd_len;
-            sd = q.smd_len;
-        }
-        s_der[j] = d;
-        s_anc[j] = a;
-        if (sv.has_kept) {
-            s_mmd[j] = md;
-            s_smd[j] = sd;
-        }
-    }
-    __syncthreads();
-    // ---- offsets: inside the tile, then across tiles
-    Bytes4 agg = Bytes4();
-    agg.der = tile_offsets(s_der, sm);
-    agg.anc = tile_offsets(s_anc, sm);
-    if (sv.has_kept) {
-        agg.mmd = tile_offsets(s_mmd, sm);
-        agg.smd = tile_offsets(s_smd, sm);
-    }
-    LbVal<2, true> aw; // half 0: derived, mutation metadata; half 1: ancestral, site metadata
-    aw.w[0][0] = (uint32_t) agg.der;
-    aw.w[0][1] = (uint32_t) (agg.der >> 32);
-    aw.w[0][2] = (uint32_t) agg.mmd;
-    aw.w[0][3] = (uint32_t) (agg.mmd >> 32);
-    aw.w[1][0] = (uint32_t) agg.anc;
-    aw.w[1][1] = (uint32_t) (agg.anc >> 32);
-    aw.w[1][2] = (uint32_t) agg.smd;
-    aw.w[1][3] = (uint32_t) (agg.smd >> 32);
-    const LbVal<2, true> pw = lookback_prefix<2, true>(lb, blockIdx.x, aw, &bcast);
-    Bytes4 pre;
-    pre.der = (uint64_t) pw.w[0][0] | ((uint64_t) pw.w[0][1] << 32);
-    pre.mmd = (uint64_t) pw.w[0][2] | ((uint64_t) pw.w[0][3] << 32);
-    pre.anc = (uint64_t) pw.w[1][0] | ((uint64_t) pw.w[1][1] << 32);
-    pre.smd = (uint64_t) pw.w[1][2] | ((uint64_t) pw.w[1][3] << 32);
-    if (blockIdx.x + 1 == num_tiles && threadIdx.x == 0) {
-        *total = pre + agg;
-        out.store_off(out.site_anc_off, p1_total->s, pre.anc + agg.anc);
-        out.store_off(out.mut_der_off, p1_total->m, pre.der + agg.der);
-        if (out.write_md_off) {
-            out.store_off(out.site_md_off, p1_total->s, pre.smd + agg.smd);
-            out.store_off(out.mut_md_off, p1_total->m, pre.mmd + agg.mmd);
-        }
-    }
-    const bool stage_der = agg.der <= K5_STAGE, stage_anc = agg.anc <= K5_STAGE;
-    char *der_base = stage_der ? st_der + (pre.der & 15ull) : out.mut_der + pre.der;
-    char *anc_base = stage_anc ? st_anc + (pre.anc & 15ull) : out.site_anc + pre.anc;
-    // ---- rows and bytes.  The record gathers (one random sector each) are issued for all
-    // of the thread's items before any of them is used.
-    Rec rcs[K5_ITEMS];
-#pragma unroll
-    for (int k = 0; k < K5_ITEMS; k++) {
-        const uint64_t i = base + (uint32_t) k * SCAN_THREADS + threadIdx.x;
-        if (i < sv.n) {
-            rcs[k] = sv.rec[sv.val[i]];
-        }
-    }
-#pragma unroll
-    for (int k = 0; k < K5_ITEMS; k++) {
-        const uint32_t j = (uint32_t) k * SCAN_THREADS + threadIdx.x;
-        const uint64_t i = base + j;
-        if (i >= sv.n) {
-            continue;
-        }
-        const EmitRec e = emit_record(sv, rv, kept, model, ph, call.stream, i, err);
-        const uint32_t site_row = sv.site_row[i];
-        if (e.head) {
-            char *anc_dst = anc_base + s_anc[j];
-            out.site_position[site_row] = sv.key.position(i);
-            out.store_off(out.site_anc_off, site_row, pre.anc + s_anc[j]);
-            if (out.write_md_off) {
-                out.store_off(out.site_md_off, site_row, pre.smd + (sv.has_kept ? s_smd[j] : 0u));
-            }
-            if (!e.is_mut) {
-                copy_bytes(anc_dst, kept.site_anc + kept.site_anc_off[e.r], e.anc_len);
-                copy_bytes(out.site_md + pre.smd + s_smd[j], kept.site_md + kept.site_md_off[e.r], e.smd_len);
-            } else if (model.kind == 0) {
-                copy_bytes(anc_dst, model.alleles + model.allele_off[e.site_state], e.anc_len);
-            } else {
-                write_digits(anc_dst, e.root_number, e.anc_len);
-            }
-        }
-        if (e.is_mut) {
-            const uint32_t row = sv.mut_row(i);
-            const Rec rc = rcs[k];
-            int32_t par = -1;
-            if (!e.single) {
-                const int32_t p = rv.parent[i];
-                par = p < 0 ? -1 : (int32_t) (sv.mut_row((uint64_t) p) + out.mut_base);
-            }
-            char *der_dst = der_base + s_der[j];
-            out.mut_site[row] = (int32_t) (site_row + out.site_base);
-            out.mut_node[row] = rc.node;
-            out.mut_time[row] = rc.time;
-            out.mut_parent[row] = par;
-            out.store_off(out.mut_der_off, row, pre.der + s_der[j]);
-            if (out.write_md_off) {
-                out.store_off(out.mut_md_off, row, pre.mmd + (sv.has_kept ? s_mmd[j] : 0u));
-            }
-            if (!e.is_new) {
-                const uint64_t km = e.r - sv.S0;
-                copy_bytes(der_dst, kept.mut_der + kept.mut_der_off[km], e.der_len);
-                copy_bytes(out.mut_md + pre.mmd + s_mmd[j], kept.mut_md + kept.mut_md_off[km], e.mmd_len);
-            } else if (model.kind == 0) {
-                copy_bytes(der_dst, model.alleles + model.allele_off[e.state], e.der_len);
-            } else {
-                write_digits(der_dst, e.mut_number, e.der_len);
-            }
-        }
-    }
-    __syncthreads();
-    if (stage_der) {
-        flush_stage(st_der, out.mut_der, pre.der, agg.der);
-    }
-    if (stage_anc) {
-        flush_stage(st_anc, out.site_anc, pre.anc, agg.anc);
-    }
-}
+namespace mspb {
 
 // Dense-genome fallback: rebuild keys as position << 32 | coarse descending time from the
 // position-sorted records, so that the next sort also orders sites internally.

@@ -930,10 +930,32 @@ int launch_emit(mspb_ctx *ctx)
     const uint32_t k5_tiles = (uint32_t) ((R + K5_TILE - 1) / K5_TILE);
     LbWord *lb4 = nullptr;
     TRY(lookback_state(ctx, k5_tiles, 2, &lb4));
-    MSPB_LAUNCH(ctx->log, "k5_emit",
-        k5_emit_kernel<<<k5_tiles, SCAN_THREADS, 0, st>>>(ctx->pending.sv, ctx->pending.rv, ctx->pending.kept,
-            ctx->pending.model, ctx->pending.call, ctx->pending.out, lb4, k5_tiles, &dt->p1, &dt->bytes, &dt->dense,
-            &dt->err));
+    const bool kept_rows = ctx->pending.sv.has_kept != 0, off32 = ctx->pending.out.off32 != 0;
+    const int model_kind = ctx->pending.model.kind != 0 ? 1 : 0;
+#define MSPB_K5(M, K, O)                                                                                             \
+    MSPB_LAUNCH(ctx->log, "k5_emit",                                                                                 \
+        (k5_emit_kernel<M, K, O><<<k5_tiles, SCAN_THREADS, 0, st>>>(ctx->pending.sv, ctx->pending.rv,                \
+            ctx->pending.kept, ctx->pending.model, ctx->pending.call, ctx->pending.out, lb4, k5_tiles, &dt->p1,      \
+            &dt->bytes, &dt->dense, &dt->err)))
+#define MSPB_K5_MODEL(M)                                                                                             \
+    if (kept_rows) {                                                                                                 \
+        if (off32) {                                                                                                 \
+            MSPB_K5(M, true, true);                                                                                  \
+        } else {                                                                                                     \
+            MSPB_K5(M, true, false);                                                                                 \
+        }                                                                                                            \
+    } else if (off32) {                                                                                              \
+        MSPB_K5(M, false, true);                                                                                     \
+    } else {                                                                                                         \
+        MSPB_K5(M, false, false);                                                                                    \
+    }
+    if (model_kind == 0) {
+        MSPB_K5_MODEL(0)
+    } else {
+        MSPB_K5_MODEL(1)
+    }
+#undef MSPB_K5_MODEL
+#undef MSPB_K5
     return 0;
 }
 
