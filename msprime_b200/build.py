@@ -11,9 +11,8 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 SRC = os.path.join(HERE, "csrc", "mspb_api.cu")
 OUT = os.path.join(HERE, "_mspb.so")
-DEPS = [os.path.join(HERE, "csrc", f) for f in
-        ("mspb_api.cu", "kernels.cuh", "sort.cuh", "common.cuh", "replay.cuh")] + [
-    os.path.join(HERE, "..", "include", "msprime_b200.h")]
+DEPS = sorted(os.path.join(HERE, "csrc", f) for f in os.listdir(os.path.join(HERE, "csrc"))
+              if f.endswith((".cu", ".cuh"))) + [os.path.join(HERE, "..", "include", "msprime_b200.h")]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",

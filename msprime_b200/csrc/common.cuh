@@ -381,106 +381,117 @@ struct LbVal {
     }
 };
 
-// Called by every thread of the block with the block's aggregate (thread 0's value is
-// used); returns the sum over all earlier tiles.  `state` holds num_tiles x HALVES words,
-// zeroed before the launch.  `bcast` is one LbVal in shared memory.  *inclusive_out
-// (optional, shared or local) receives prefix + aggregate on every thread.
+// Look-back by ONE full warp (lane = threadIdx.x & 31) with the tile's aggregate (the same
+// value on every lane); returns the sum over all earlier tiles on every lane.  `state`
+// holds num_tiles x HALVES words, zeroed before the launch.  The rest of the block may do
+// independent work meanwhile.
+template <int HALVES, bool WIDE64>
+MSPB_DEVFN LbVal<HALVES, WIDE64> lookback_warp(LbWord *state, uint32_t tile, const LbVal<HALVES, WIDE64> &aggregate)
+{
+    typedef LbVal<HALVES, WIDE64> V;
+    const int lane = threadIdx.x & 31;
+    V prefix;
+    prefix.clear();
+    if (tile > 0) {
+#pragma unroll
+        for (int h = 0; h < HALVES; h++) {
+            if (lane == h) {
+                LbWord me;
+                me.w[0] = aggregate.w[h][0];
+                me.w[1] = aggregate.w[h][1];
+                me.w[2] = aggregate.w[h][2];
+                me.w[3] = aggregate.w[h][3] | (LB_AGG << 30);
+                lb_store(&state[(uint64_t) tile * HALVES + h], me);
+            }
+        }
+        int64_t base = (int64_t) tile - 1;
+        for (;;) {
+            V part;
+            part.clear();
+            int stop = LB_WINDOW; // offset of the nearest predecessor with an inclusive prefix
+#pragma unroll
+            for (int r = 0; r < LB_PER_LANE; r++) {
+                if (stop != LB_WINDOW) {
+                    break; // (warp-uniform) an inclusive prefix was found among nearer tiles
+                }
+                const int64_t p = base - (r * 32 + lane);
+                V v;
+                v.clear();
+                uint32_t flag = LB_INCL; // before the first tile: an inclusive prefix of zero
+                if (p >= 0) {
+                    for (;;) {
+                        bool ok = true;
+                        flag = 0;
+#pragma unroll
+                        for (int h = 0; h < HALVES; h++) {
+                            const LbWord x = lb_load(&state[(uint64_t) p * HALVES + h]);
+                            const uint32_t f = x.w[3] >> 30;
+                            ok = ok && f != 0 && (h == 0 || f == flag);
+                            flag = f;
+                            v.w[h][0] = x.w[0];
+                            v.w[h][1] = x.w[1];
+                            v.w[h][2] = x.w[2];
+                            v.w[h][3] = x.w[3] & 0x3fffffffu;
+                        }
+                        if (ok) {
+                            break;
+                        }
+                    }
+                }
+                const uint32_t incl = __ballot_sync(0xffffffffu, flag == LB_INCL);
+                if (stop == LB_WINDOW && incl != 0u) {
+                    stop = r * 32 + (__ffs(incl) - 1);
+                }
+                if (r * 32 + lane <= stop) {
+                    part.add(v);
+                }
+            }
+#pragma unroll
+            for (int sft = 16; sft > 0; sft >>= 1) {
+                V o;
+#pragma unroll
+                for (int h = 0; h < HALVES; h++) {
+#pragma unroll
+                    for (int q = 0; q < 4; q++) {
+                        o.w[h][q] = __shfl_xor_sync(0xffffffffu, part.w[h][q], sft);
+                    }
+                }
+                part.add(o);
+            }
+            prefix.add(part);
+            if (stop < LB_WINDOW) {
+                break;
+            }
+            base -= LB_WINDOW;
+        }
+    }
+    V inclusive = prefix;
+    inclusive.add(aggregate);
+#pragma unroll
+    for (int h = 0; h < HALVES; h++) {
+        if (lane == h) {
+            LbWord me;
+            me.w[0] = inclusive.w[h][0];
+            me.w[1] = inclusive.w[h][1];
+            me.w[2] = inclusive.w[h][2];
+            me.w[3] = inclusive.w[h][3] | (LB_INCL << 30);
+            lb_store(&state[(uint64_t) tile * HALVES + h], me);
+        }
+    }
+    return prefix;
+}
+
+// Called by every thread of the block with the block's aggregate; warp 0 looks back and
+// the exclusive prefix is handed to every thread through `bcast` (one LbVal in shared
+// memory).
 template <int HALVES, bool WIDE64>
 MSPB_DEVFN LbVal<HALVES, WIDE64> lookback_prefix(LbWord *state, uint32_t tile, const LbVal<HALVES, WIDE64> &aggregate,
     LbVal<HALVES, WIDE64> *bcast)
 {
     typedef LbVal<HALVES, WIDE64> V;
     if (threadIdx.x < 32) {
-        const int lane = threadIdx.x;
-        V prefix;
-        prefix.clear();
-        if (tile > 0) {
-#pragma unroll
-            for (int h = 0; h < HALVES; h++) {
-                if (lane == h) {
-                    LbWord me;
-                    me.w[0] = aggregate.w[h][0];
-                    me.w[1] = aggregate.w[h][1];
-                    me.w[2] = aggregate.w[h][2];
-                    me.w[3] = aggregate.w[h][3] | (LB_AGG << 30);
-                    lb_store(&state[(uint64_t) tile * HALVES + h], me);
-                }
-            }
-            int64_t base = (int64_t) tile - 1;
-            for (;;) {
-                V part;
-                part.clear();
-                int stop = LB_WINDOW; // offset of the nearest predecessor with an inclusive prefix
-#pragma unroll
-                for (int r = 0; r < LB_PER_LANE; r++) {
-                    if (stop != LB_WINDOW) {
-                        break; // (warp-uniform) an inclusive prefix was found among nearer tiles
-                    }
-                    const int64_t p = base - (r * 32 + lane);
-                    V v;
-                    v.clear();
-                    uint32_t flag = LB_INCL; // before the first tile: an inclusive prefix of zero
-                    if (p >= 0) {
-                        for (;;) {
-                            bool ok = true;
-                            flag = 0;
-#pragma unroll
-                            for (int h = 0; h < HALVES; h++) {
-                                const LbWord x = lb_load(&state[(uint64_t) p * HALVES + h]);
-                                const uint32_t f = x.w[3] >> 30;
-                                ok = ok && f != 0 && (h == 0 || f == flag);
-                                flag = f;
-                                v.w[h][0] = x.w[0];
-                                v.w[h][1] = x.w[1];
-                                v.w[h][2] = x.w[2];
-                                v.w[h][3] = x.w[3] & 0x3fffffffu;
-                            }
-                            if (ok) {
-                                break;
-                            }
-                        }
-                    }
-                    const uint32_t incl = __ballot_sync(0xffffffffu, flag == LB_INCL);
-                    if (stop == LB_WINDOW && incl != 0u) {
-                        stop = r * 32 + (__ffs(incl) - 1);
-                    }
-                    if (r * 32 + lane <= stop) {
-                        part.add(v);
-                    }
-                }
-#pragma unroll
-                for (int sft = 16; sft > 0; sft >>= 1) {
-                    V o;
-#pragma unroll
-                    for (int h = 0; h < HALVES; h++) {
-#pragma unroll
-                        for (int q = 0; q < 4; q++) {
-                            o.w[h][q] = __shfl_xor_sync(0xffffffffu, part.w[h][q], sft);
-                        }
-                    }
-                    part.add(o);
-                }
-                prefix.add(part);
-                if (stop < LB_WINDOW) {
-                    break;
-                }
-                base -= LB_WINDOW;
-            }
-        }
-        V inclusive = prefix;
-        inclusive.add(aggregate);
-#pragma unroll
-        for (int h = 0; h < HALVES; h++) {
-            if (lane == h) {
-                LbWord me;
-                me.w[0] = inclusive.w[h][0];
-                me.w[1] = inclusive.w[h][1];
-                me.w[2] = inclusive.w[h][2];
-                me.w[3] = inclusive.w[h][3] | (LB_INCL << 30);
-                lb_store(&state[(uint64_t) tile * HALVES + h], me);
-            }
-        }
-        if (lane == 0) {
+        const V prefix = lookback_warp<HALVES, WIDE64>(state, tile, aggregate);
+        if (threadIdx.x == 0) {
             *bcast = prefix;
         }
     }

@@ -98,20 +98,32 @@ MSPB_DEVFN uint64_t tile_offsets(uint32_t *lens, uint64_t *scan_tmp)
     return (uint64_t) total;
 }
 
-// Copies a tile's staged bytes to global memory with 16-byte stores.  The stage is
-// shifted by (global offset mod 16) so that aligned chunks line up on both sides.
+// Copies a tile's staged bytes (stage[0 .. total), 16-byte aligned) to global memory
+// at byte offset g0 with aligned 16-byte stores.  Source and destination differ by
+// g0 mod 16, so each 16-byte chunk is assembled from five shared-memory words with funnel
+// shifts; the (at most two) partial chunks at the ends go byte by byte.
 MSPB_DEVFN void flush_stage(const char *stage, char *dst_base, uint64_t g0, uint32_t total)
 {
     const uint32_t shift = (uint32_t) (g0 & 15ull);
     const uint32_t span = shift + total;
     char *aligned = dst_base + (g0 - shift);
+    const uint32_t *words = reinterpret_cast<const uint32_t *>(stage);
+    const uint32_t rot = 8u * ((16u - shift) & 3u); // bit offset of a chunk's first byte in its first word
     for (uint32_t lo = threadIdx.x * 16u; lo < span; lo += SCAN_THREADS * 16u) {
         if (lo >= shift && lo + 16u <= span) {
-            *reinterpret_cast<uint4 *>(aligned + lo) = *reinterpret_cast<const uint4 *>(stage + lo);
+            const uint32_t w0 = (lo - shift) >> 2;
+            const uint32_t x0 = words[w0], x1 = words[w0 + 1], x2 = words[w0 + 2], x3 = words[w0 + 3],
+                           x4 = words[w0 + 4];
+            uint4 o;
+            o.x = __funnelshift_r(x0, x1, rot);
+            o.y = __funnelshift_r(x1, x2, rot);
+            o.z = __funnelshift_r(x2, x3, rot);
+            o.w = __funnelshift_r(x3, x4, rot);
+            *reinterpret_cast<uint4 *>(aligned + lo) = o;
         } else {
             const uint32_t hi = lo + 16u < span ? lo + 16u : span;
             for (uint32_t b = lo < shift ? shift : lo; b < hi; b++) {
-                aligned[b] = stage[b];
+                aligned[b] = stage[b - shift];
             }
         }
     }
@@ -177,82 +189,100 @@ __global__ void __launch_bounds__(SCAN_THREADS, 4) k5_emit_kernel(SortedView sv,
         return;
     }
     const uint64_t base = (uint64_t) blockIdx.x * K5_TILE;
-    // ---- classify every record once; lengths to shared memory
+    const uint64_t last = sv.n - 1;
+    // ---- all loads of the tile up front: slots and the site rows around every record
+    // (P1's site rows give the site boundaries: no key compares here), then the record
+    // gathers, one random sector each
     uint32_t meta[K5_ITEMS]; // EM_* | derived length << 8 | ancestral length << 16 (infinite alleles)
     uint32_t va[K5_ITEMS]; // infinite alleles: draws before the record; matrix: derived allele index
     uint32_t vb[K5_ITEMS]; // matrix: ancestral allele index of a new site
     uint32_t srow[K5_ITEMS];
     Rec rcs[K5_ITEMS];
+    {
+        uint32_t slot[K5_ITEMS], before[K5_ITEMS], after[K5_ITEMS];
+#pragma unroll
+        for (int k = 0; k < K5_ITEMS; k++) {
+            const uint64_t i = base + (uint32_t) k * SCAN_THREADS + threadIdx.x;
+            const uint64_t ic = i < last ? i : last;
+            slot[k] = sv.val[ic];
+            srow[k] = sv.site_row[ic];
+            before[k] = sv.site_row[ic > 0 ? ic - 1 : 0];
+            after[k] = sv.site_row[ic < last ? ic + 1 : last];
+        }
+#pragma unroll
+        for (int k = 0; k < K5_ITEMS; k++) {
+            rcs[k] = sv.rec[slot[k]];
+        }
+#pragma unroll
+        for (int k = 0; k < K5_ITEMS; k++) {
+            const uint64_t i = base + (uint32_t) k * SCAN_THREADS + threadIdx.x;
+            const bool head = i == 0 || before[k] != srow[k];
+            const bool single = head && (i >= last || after[k] != srow[k]);
+            const bool is_mut = !KEPT || slot[k] >= sv.S0;
+            const bool is_new = !KEPT || slot[k] >= sv.S0 + sv.M0;
+            meta[k] = i < sv.n ? (head ? EM_HEAD : 0u) | (is_mut ? EM_MUT : 0u) | (is_new ? EM_NEW : 0u)
+                                     | (single ? EM_SINGLE : 0u)
+                               : 0u;
+            va[k] = slot[k];
+        }
+    }
+    // ---- lengths to shared memory
 #pragma unroll
     for (int k = 0; k < K5_ITEMS; k++) {
         const uint32_t j = (uint32_t) k * SCAN_THREADS + threadIdx.x;
         const uint64_t i = base + j;
-        uint32_t m = 0, d = 0, a = 0, md = 0, sd = 0;
-        va[k] = vb[k] = srow[k] = 0;
-        if (i < sv.n) {
-            const uint32_t r = sv.val[i];
-            rcs[k] = sv.rec[r]; // one random sector per record: issued first, used last
-            const bool head = sv.head(i);
-            const bool single = head && (i + 1 >= sv.n || sv.head(i + 1));
-            const bool is_mut = !KEPT || r >= sv.S0;
-            const bool is_new = !KEPT || r >= sv.S0 + sv.M0;
-            const uint32_t sr = sv.site_row[i];
-            srow[k] = sr;
-            m = (head ? EM_HEAD : 0u) | (is_mut ? EM_MUT : 0u) | (is_new ? EM_NEW : 0u) | (single ? EM_SINGLE : 0u);
-            if (is_new) {
-                // a head that is a mutation opens a new site (kept sites start with their marker)
-                if (MODEL == 1) {
-                    const uint32_t db = KEPT ? sv.draw_scan[i] : (uint32_t) i + sr + 1u - (head ? 1u : 0u);
-                    const uint64_t root_number = model.start_allele + db;
-                    va[k] = db;
-                    d = num_digits(root_number + (head ? 1u : 0u));
-                    if (head) {
-                        a = num_digits(root_number);
-                    }
-                } else {
-                    int32_t s, ss = 0;
-                    if (single) {
-                        // a new site with one new mutation: root draw, then one transition
-                        double ur, ut;
-                        if (rv.replay != nullptr) {
-                            const uint64_t db = sv.draws_before(i);
-                            ur = phase_b_uniform(rv, db, err);
-                            ut = phase_b_uniform(rv, db + 1, err);
-                        } else {
-                            allele_uniforms(Philox(call.seed), call.stream, rcs[k].ord, &ur, &ut);
-                        }
-                        ss = (int32_t) select_prob(ur, model.num_alleles, model.root);
-                        s = (int32_t) select_prob(ut, model.num_alleles,
-                            model.matrix + (uint64_t) ss * model.num_alleles);
+        const uint32_t m = meta[k], r = va[k];
+        const bool head = (m & EM_HEAD) != 0u;
+        uint32_t d = 0, a = 0, md = 0, sd = 0;
+        vb[k] = 0;
+        if (m & EM_NEW) {
+            // a head that is a mutation opens a new site (kept sites start with their marker)
+            if (MODEL == 1) {
+                const uint32_t db = KEPT ? sv.draw_scan[i] : (uint32_t) i + srow[k] + 1u - (head ? 1u : 0u);
+                const uint64_t root_number = model.start_allele + db;
+                va[k] = db;
+                d = num_digits(root_number + (head ? 1u : 0u));
+                if (head) {
+                    a = num_digits(root_number);
+                }
+                meta[k] = m | (d << 8) | (a << 16);
+            } else {
+                int32_t s, ss = 0;
+                if (m & EM_SINGLE) {
+                    // a new site with one new mutation: root draw, then one transition
+                    double ur, ut;
+                    if (rv.replay != nullptr) {
+                        const uint64_t db = sv.draws_before(i);
+                        ur = phase_b_uniform(rv, db, err);
+                        ut = phase_b_uniform(rv, db + 1, err);
                     } else {
-                        s = rv.state[i];
-                        if (head) {
-                            ss = rv.site_state[i];
-                        }
+                        allele_uniforms(Philox(call.seed), call.stream, rcs[k].ord, &ur, &ut);
                     }
-                    va[k] = (uint32_t) s;
-                    vb[k] = (uint32_t) ss;
-                    d = (uint32_t) (model.allele_off[s + 1] - model.allele_off[s]);
+                    ss = (int32_t) select_prob(ur, model.num_alleles, model.root);
+                    s = (int32_t) select_prob(ut, model.num_alleles, model.matrix + (uint64_t) ss * model.num_alleles);
+                } else {
+                    s = rv.state[i];
                     if (head) {
-                        a = (uint32_t) (model.allele_off[ss + 1] - model.allele_off[ss]);
+                        ss = rv.site_state[i];
                     }
                 }
-            }
-            if (KEPT) {
-                if (!is_mut) {
-                    a = (uint32_t) (kept.site_anc_off[r + 1] - kept.site_anc_off[r]);
-                    sd = (uint32_t) (kept.site_md_off[r + 1] - kept.site_md_off[r]);
-                } else if (!is_new) {
-                    const uint64_t km = r - sv.S0;
-                    d = (uint32_t) (kept.mut_der_off[km + 1] - kept.mut_der_off[km]);
-                    md = (uint32_t) (kept.mut_md_off[km + 1] - kept.mut_md_off[km]);
+                va[k] = (uint32_t) s;
+                vb[k] = (uint32_t) ss;
+                d = (uint32_t) (model.allele_off[s + 1] - model.allele_off[s]);
+                if (head) {
+                    a = (uint32_t) (model.allele_off[ss + 1] - model.allele_off[ss]);
                 }
             }
-            if (MODEL == 1 && is_new) {
-                m |= (d << 8) | (a << 16);
+        } else if (KEPT && m != 0u) {
+            if (!(m & EM_MUT)) {
+                a = (uint32_t) (kept.site_anc_off[r + 1] - kept.site_anc_off[r]);
+                sd = (uint32_t) (kept.site_md_off[r + 1] - kept.site_md_off[r]);
+            } else {
+                const uint64_t km = r - sv.S0;
+                d = (uint32_t) (kept.mut_der_off[km + 1] - kept.mut_der_off[km]);
+                md = (uint32_t) (kept.mut_md_off[km + 1] - kept.mut_md_off[km]);
             }
         }
-        meta[k] = m;
         s_der[j] = d;
         s_anc[j] = a;
         if (KEPT) {
@@ -261,7 +291,7 @@ __global__ void __launch_bounds__(SCAN_THREADS, 4) k5_emit_kernel(SortedView sv,
         }
     }
     __syncthreads();
-    // ---- offsets: inside the tile, then across tiles
+    // ---- offsets inside the tile
     Bytes4 agg = Bytes4();
     if (KEPT) {
         agg.der = tile_offsets<uint64_t>(s_der, sm);
@@ -271,6 +301,7 @@ __global__ void __launch_bounds__(SCAN_THREADS, 4) k5_emit_kernel(SortedView sv,
     } else {
         tile_offsets_pair(s_der, s_anc, sm, &agg.der, &agg.anc);
     }
+    __syncthreads(); // the offsets are read striped below, by other threads than wrote them
     LbVal<2, true> aw; // half 0: derived, mutation metadata; half 1: ancestral, site metadata
     aw.w[0][0] = (uint32_t) agg.der;
     aw.w[0][1] = (uint32_t) (agg.der >> 32);
@@ -280,44 +311,37 @@ __global__ void __launch_bounds__(SCAN_THREADS, 4) k5_emit_kernel(SortedView sv,
     aw.w[1][1] = (uint32_t) (agg.anc >> 32);
     aw.w[1][2] = (uint32_t) agg.smd;
     aw.w[1][3] = (uint32_t) (agg.smd >> 32);
-    const LbVal<2, true> pw = lookback_prefix<2, true>(lb, blockIdx.x, aw, &bcast);
-    Bytes4 pre;
-    pre.der = (uint64_t) pw.w[0][0] | ((uint64_t) pw.w[0][1] << 32);
-    pre.mmd = (uint64_t) pw.w[0][2] | ((uint64_t) pw.w[0][3] << 32);
-    pre.anc = (uint64_t) pw.w[1][0] | ((uint64_t) pw.w[1][1] << 32);
-    pre.smd = (uint64_t) pw.w[1][2] | ((uint64_t) pw.w[1][3] << 32);
-    if (blockIdx.x + 1 == num_tiles && threadIdx.x == 0) {
-        *total = pre + agg;
-        store_offset<OFF32>(out.site_anc_off, p1_total->s, pre.anc + agg.anc);
-        store_offset<OFF32>(out.mut_der_off, p1_total->m, pre.der + agg.der);
-        if (out.write_md_off) {
-            store_offset<OFF32>(out.site_md_off, p1_total->s, pre.smd + agg.smd);
-            store_offset<OFF32>(out.mut_md_off, p1_total->m, pre.mmd + agg.mmd);
+    // ---- offsets across tiles.  When the tile's state bytes fit the stage (always, unless
+    // kept rows carry long strings) nothing below needs the prefix until the very end:
+    // warp 0 looks back while the other warps write rows and assemble bytes.
+    const bool staged = !KEPT || (agg.der <= K5_STAGE && agg.anc <= K5_STAGE && agg.mmd == 0 && agg.smd == 0);
+    Bytes4 pre = Bytes4();
+    if (!staged) {
+        const LbVal<2, true> pw = lookback_prefix<2, true>(lb, blockIdx.x, aw, &bcast);
+        pre.der = (uint64_t) pw.w[0][0] | ((uint64_t) pw.w[0][1] << 32);
+        pre.mmd = (uint64_t) pw.w[0][2] | ((uint64_t) pw.w[0][3] << 32);
+        pre.anc = (uint64_t) pw.w[1][0] | ((uint64_t) pw.w[1][1] << 32);
+        pre.smd = (uint64_t) pw.w[1][2] | ((uint64_t) pw.w[1][3] << 32);
+    } else if (threadIdx.x < 32) {
+        const LbVal<2, true> pw = lookback_warp<2, true>(lb, blockIdx.x, aw);
+        if (threadIdx.x == 0) {
+            bcast = pw;
         }
     }
-    const bool stage_der = agg.der <= K5_STAGE, stage_anc = agg.anc <= K5_STAGE;
-    char *der_base = stage_der ? st_der + (pre.der & 15ull) : out.mut_der + pre.der;
-    char *anc_base = stage_anc ? st_anc + (pre.anc & 15ull) : out.site_anc + pre.anc;
+    char *der_base = staged ? st_der : out.mut_der + pre.der;
+    char *anc_base = staged ? st_anc : out.site_anc + pre.anc;
     // ---- rows and bytes
 #pragma unroll
     for (int k = 0; k < K5_ITEMS; k++) {
         const uint32_t j = (uint32_t) k * SCAN_THREADS + threadIdx.x;
         const uint64_t i = base + j;
-        if (i >= sv.n) {
-            continue;
-        }
         const uint32_t m = meta[k];
         const uint32_t site_row = srow[k];
         if (m & EM_HEAD) {
-            const uint32_t ao = s_anc[j];
-            char *anc_dst = anc_base + ao;
+            char *anc_dst = anc_base + s_anc[j];
             out.site_position[site_row] = sv.key.position(i);
-            store_offset<OFF32>(out.site_anc_off, site_row, pre.anc + ao);
-            if (out.write_md_off) {
-                store_offset<OFF32>(out.site_md_off, site_row, pre.smd + (KEPT ? s_smd[j] : 0u));
-            }
             if (KEPT && !(m & EM_MUT)) {
-                const uint32_t r = sv.val[i];
+                const uint32_t r = va[k];
                 const uint64_t a0 = kept.site_anc_off[r], m0 = kept.site_md_off[r];
                 copy_bytes(anc_dst, kept.site_anc + a0, kept.site_anc_off[r + 1] - a0);
                 copy_bytes(out.site_md + pre.smd + s_smd[j], kept.site_md + m0, kept.site_md_off[r + 1] - m0);
@@ -330,23 +354,18 @@ __global__ void __launch_bounds__(SCAN_THREADS, 4) k5_emit_kernel(SortedView sv,
         }
         if (m & EM_MUT) {
             const uint32_t row = KEPT ? sv.mut_scan[i] : (uint32_t) i;
-            const uint32_t dof = s_der[j];
             int32_t par = -1;
             if (!(m & EM_SINGLE)) {
                 const int32_t p = rv.parent[i];
                 par = p < 0 ? -1 : (int32_t) ((KEPT ? sv.mut_scan[p] : (uint32_t) p) + out.mut_base);
             }
-            char *der_dst = der_base + dof;
+            char *der_dst = der_base + s_der[j];
             out.mut_site[row] = (int32_t) (site_row + out.site_base);
             out.mut_node[row] = rcs[k].node;
             out.mut_time[row] = rcs[k].time;
             out.mut_parent[row] = par;
-            store_offset<OFF32>(out.mut_der_off, row, pre.der + dof);
-            if (out.write_md_off) {
-                store_offset<OFF32>(out.mut_md_off, row, pre.mmd + (KEPT ? s_mmd[j] : 0u));
-            }
             if (KEPT && !(m & EM_NEW)) {
-                const uint64_t km = sv.val[i] - sv.S0;
+                const uint64_t km = va[k] - sv.S0;
                 const uint64_t d0 = kept.mut_der_off[km], m0 = kept.mut_md_off[km];
                 copy_bytes(der_dst, kept.mut_der + d0, kept.mut_der_off[km + 1] - d0);
                 copy_bytes(out.mut_md + pre.mmd + s_mmd[j], kept.mut_md + m0, kept.mut_md_off[km + 1] - m0);
@@ -359,10 +378,43 @@ __global__ void __launch_bounds__(SCAN_THREADS, 4) k5_emit_kernel(SortedView sv,
         }
     }
     __syncthreads();
-    if (stage_der) {
-        flush_stage(st_der, out.mut_der, pre.der, (uint32_t) agg.der);
+    if (staged) {
+        const LbVal<2, true> pw = bcast;
+        pre.der = (uint64_t) pw.w[0][0] | ((uint64_t) pw.w[0][1] << 32);
+        pre.mmd = (uint64_t) pw.w[0][2] | ((uint64_t) pw.w[0][3] << 32);
+        pre.anc = (uint64_t) pw.w[1][0] | ((uint64_t) pw.w[1][1] << 32);
+        pre.smd = (uint64_t) pw.w[1][2] | ((uint64_t) pw.w[1][3] << 32);
     }
-    if (stage_anc) {
+    // ---- the offset columns, which are what needed the prefix
+#pragma unroll
+    for (int k = 0; k < K5_ITEMS; k++) {
+        const uint32_t j = (uint32_t) k * SCAN_THREADS + threadIdx.x;
+        const uint32_t m = meta[k];
+        if (m & EM_HEAD) {
+            store_offset<OFF32>(out.site_anc_off, srow[k], pre.anc + s_anc[j]);
+            if (out.write_md_off) {
+                store_offset<OFF32>(out.site_md_off, srow[k], pre.smd + (KEPT ? s_smd[j] : 0u));
+            }
+        }
+        if (m & EM_MUT) {
+            const uint32_t row = KEPT ? sv.mut_scan[base + j] : (uint32_t) (base + j);
+            store_offset<OFF32>(out.mut_der_off, row, pre.der + s_der[j]);
+            if (out.write_md_off) {
+                store_offset<OFF32>(out.mut_md_off, row, pre.mmd + (KEPT ? s_mmd[j] : 0u));
+            }
+        }
+    }
+    if (blockIdx.x + 1 == num_tiles && threadIdx.x == 0) {
+        *total = pre + agg;
+        store_offset<OFF32>(out.site_anc_off, p1_total->s, pre.anc + agg.anc);
+        store_offset<OFF32>(out.mut_der_off, p1_total->m, pre.der + agg.der);
+        if (out.write_md_off) {
+            store_offset<OFF32>(out.site_md_off, p1_total->s, pre.smd + agg.smd);
+            store_offset<OFF32>(out.mut_md_off, p1_total->m, pre.mmd + agg.mmd);
+        }
+    }
+    if (staged) {
+        flush_stage(st_der, out.mut_der, pre.der, (uint32_t) agg.der);
         flush_stage(st_anc, out.site_anc, pre.anc, (uint32_t) agg.anc);
     }
 }

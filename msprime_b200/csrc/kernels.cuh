@@ -636,59 +636,127 @@ struct Counts3 {
 constexpr int P1_ITEMS = 16;
 constexpr int P1_TILE = SCAN_THREADS * P1_ITEMS;
 
+template <int MODE>
+struct P1Key {
+    typedef uint64_t type;
+    static MSPB_DEVFN const uint64_t *ptr(const KeyView &k) { return k.k64; }
+    static MSPB_DEVFN bool same_pos(uint64_t a, uint64_t b)
+    {
+        return MODE == KEY64_POS ? a == b : (a >> 32) == (b >> 32);
+    }
+};
+
+template <>
+struct P1Key<KEY32_POS> {
+    typedef uint32_t type;
+    static MSPB_DEVFN const uint32_t *ptr(const KeyView &k) { return k.k32; }
+    static MSPB_DEVFN bool same_pos(uint32_t a, uint32_t b) { return a == b; }
+};
+
+// 16 consecutive 4- or 8-byte values starting at a 64-byte aligned index, as 16-byte loads
+template <typename T>
+MSPB_DEVFN void load16(const T *__restrict__ src, T *dst)
+{
+    constexpr int PER = 16 / (int) sizeof(T);
+    const uint4 *v = reinterpret_cast<const uint4 *>(src);
+#pragma unroll
+    for (int q = 0; q < P1_ITEMS / PER; q++) {
+        const uint4 w = v[q];
+        if (sizeof(T) == 4) {
+            dst[4 * q] = (T) w.x;
+            dst[4 * q + 1] = (T) w.y;
+            dst[4 * q + 2] = (T) w.z;
+            dst[4 * q + 3] = (T) w.w;
+        } else {
+            dst[2 * q] = (T) ((uint64_t) w.x | ((uint64_t) w.y << 32));
+            dst[2 * q + 1] = (T) ((uint64_t) w.z | ((uint64_t) w.w << 32));
+        }
+    }
+}
+
+MSPB_DEVFN void store16(uint32_t *dst, const uint32_t *v)
+{
+    uint4 *o = reinterpret_cast<uint4 *>(dst);
+#pragma unroll
+    for (int q = 0; q < P1_ITEMS / 4; q++) {
+        o[q] = make_uint4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+    }
+}
+
+// per-record counts packed for one scan: sites | mutation rows << 16 | draws << 32 | multi << 48
+MSPB_DEVFN uint64_t p1_counts(uint32_t f)
+{
+    return (uint64_t) (f & 1u) | ((uint64_t) ((f >> 1) & 1u) << 16) | ((uint64_t) ((f >> 2) & 3u) << 32)
+           | ((uint64_t) ((f >> 4) & 1u) << 48);
+}
+
 // Site boundaries and numbering in one pass: site row of every record, mutation rows
 // and allele draws before it, plus the input checks that need the sorted order (two
 // kept sites at one position, lib/mutgen.c:875-879; a new mutation sharing a position
 // in the continuous genome, which the reference redraws, lib/mutgen.c:1127-1134).
-// Global reads and writes are striped (coalesced); the scan runs on per-record flag
-// bytes transposed through shared memory.
-__global__ void __launch_bounds__(SCAN_THREADS) p1_sites_kernel(SortedView sv, int discrete, LbWord *lb,
+// Thread t owns 16 consecutive records, read and written with 16-byte accesses and kept
+// in registers throughout (no shared-memory transposes); one block scan and one look-back
+// across tiles give the numbering.
+template <int MODE, bool KEPT>
+__global__ void __launch_bounds__(SCAN_THREADS, (MODE == KEY32_POS && !KEPT) ? 4 : 2) p1_sites_kernel(SortedView sv, int discrete, LbWord *lb,
     uint32_t num_tiles, Counts3 *total, uint32_t *__restrict__ multi_list, uint32_t *collisions, uint32_t *dense,
     int *err)
 {
+    typedef typename P1Key<MODE>::type K;
     __shared__ uint64_t sm[9];
     __shared__ LbVal<1, false> bcast;
-    __shared__ __align__(16) uint8_t s_flag[P1_TILE]; // head | mut << 1 | draws << 2 (2 bits) | multi << 4
-    __shared__ uint16_t s_site[P1_TILE], s_mut[P1_TILE], s_draw[P1_TILE], s_multi[P1_TILE];
-    const uint64_t base = (uint64_t) blockIdx.x * P1_TILE;
-#pragma unroll 4
+    const K *__restrict__ keys = P1Key<MODE>::ptr(sv.key);
+    const uint64_t tile_base = (uint64_t) blockIdx.x * P1_TILE;
+    const uint64_t i0 = tile_base + (uint64_t) threadIdx.x * P1_ITEMS;
+    const uint64_t last = sv.n - 1;
+    const bool full = tile_base + P1_TILE <= sv.n;
+    K pk[P1_ITEMS + 2]; // pk[k + 1]: key of record i0 + k
+    uint32_t slot[KEPT ? P1_ITEMS : 1];
+    if (full) {
+        load16<K>(keys + i0, pk + 1);
+        if (KEPT) {
+            load16<uint32_t>(sv.val + i0, slot);
+        }
+    } else {
+#pragma unroll
+        for (int k = 0; k < P1_ITEMS; k++) {
+            const uint64_t ic = i0 + k < last ? i0 + k : last;
+            pk[k + 1] = keys[ic];
+            if (KEPT) {
+                slot[k] = sv.val[ic];
+            }
+        }
+    }
+    pk[0] = keys[i0 > 0 ? (i0 - 1 < last ? i0 - 1 : last) : 0];
+    pk[P1_ITEMS + 1] = keys[i0 + P1_ITEMS < last ? i0 + P1_ITEMS : last];
+    // flags: head | mut << 1 | draws << 2 (2 bits) | multi << 4
+    uint32_t flw[P1_ITEMS / 4] = { 0u, 0u, 0u, 0u }; // one byte per record
+    uint64_t acc = 0;
+#pragma unroll
     for (int k = 0; k < P1_ITEMS; k++) {
-        const uint32_t j = (uint32_t) k * SCAN_THREADS + threadIdx.x;
-        const uint64_t i = base + j;
+        const uint64_t i = i0 + k;
         uint32_t f = 0;
         if (i < sv.n) {
-            const bool h = sv.head(i);
-            const bool mu = sv.is_mut(i), nw = sv.is_new(i);
+            const bool h = i == 0 || !P1Key<MODE>::same_pos(pk[k + 1], pk[k]);
+            const bool mu = !KEPT || slot[KEPT ? k : 0] >= sv.S0;
+            const bool nw = !KEPT || slot[KEPT ? k : 0] >= sv.S0 + sv.M0;
             const uint32_t d = (nw ? 1u : 0u) + ((h && mu) ? 1u : 0u);
-            const bool multi = h && i + 1 < sv.n && !sv.head(i + 1);
+            const bool multi = h && i + 1 < sv.n && P1Key<MODE>::same_pos(pk[k + 2], pk[k + 1]);
             f = (h ? 1u : 0u) | ((mu ? 1u : 0u) << 1) | (d << 2) | ((multi ? 1u : 0u) << 4);
             if (!h) {
-                if (sv.has_kept && sv.val[i] < sv.S0) {
+                if (KEPT && !mu) {
                     set_error(err, -21); // MSP_ERR_DUPLICATE_SITE_POSITION
                 }
                 if (!discrete && (nw || sv.is_new(i - 1))) {
                     atomicAdd(collisions, 1u);
                 }
-                if (sv.key.mode == KEY32_POS && i >= 32 && sv.key.same_pos(i, i - 32)) {
+                if (MODE == KEY32_POS && i >= 32 && sv.key.same_pos(i, i - 32)) {
                     *dense = 1u;
                 }
             }
         }
-        s_flag[j] = (uint8_t) f;
-    }
-    __syncthreads();
-    // blocked: thread t owns records t * P1_ITEMS ..
-    uint32_t fl[P1_ITEMS];
-    uint64_t acc = 0; // s | m << 16 | d << 32 | u << 48 (tile-local, each < 2^16)
-    {
-        const uint4 w = reinterpret_cast<const uint4 *>(s_flag)[threadIdx.x];
-        const uint32_t ww[4] = { w.x, w.y, w.z, w.w };
-#pragma unroll
-        for (int k = 0; k < P1_ITEMS; k++) {
-            fl[k] = (ww[k >> 2] >> (8 * (k & 3))) & 0xffu;
-            acc += (uint64_t) (fl[k] & 1u) | ((uint64_t) ((fl[k] >> 1) & 1u) << 16)
-                   | ((uint64_t) ((fl[k] >> 2) & 3u) << 32) | ((uint64_t) ((fl[k] >> 4) & 1u) << 48);
-        }
+        flw[k >> 2] |= f << (8 * (k & 3));
+        acc += p1_counts(f);
     }
     uint64_t block_total;
     uint64_t run = block_exclusive_scan<uint64_t>(acc, sm, &block_total);
@@ -697,17 +765,6 @@ __global__ void __launch_bounds__(SCAN_THREADS) p1_sites_kernel(SortedView sv, i
     agg.w[0][1] = (uint32_t) ((block_total >> 16) & 0xffffull); // mutation rows
     agg.w[0][2] = (uint32_t) ((block_total >> 32) & 0xffffull); // draws
     agg.w[0][3] = (uint32_t) (block_total >> 48); // multi-record sites (< 2^30: carries the status bits)
-#pragma unroll
-    for (int k = 0; k < P1_ITEMS; k++) {
-        const uint32_t j = threadIdx.x * P1_ITEMS + k;
-        // site: inclusive count (the record's own site row is count - 1); others exclusive
-        s_site[j] = (uint16_t) ((run & 0xffffull) + (fl[k] & 1u));
-        s_mut[j] = (uint16_t) ((run >> 16) & 0xffffull);
-        s_draw[j] = (uint16_t) ((run >> 32) & 0xffffull);
-        s_multi[j] = (uint16_t) (run >> 48);
-        run += (uint64_t) (fl[k] & 1u) | ((uint64_t) ((fl[k] >> 1) & 1u) << 16)
-               | ((uint64_t) ((fl[k] >> 2) & 3u) << 32) | ((uint64_t) ((fl[k] >> 4) & 1u) << 48);
-    }
     const LbVal<1, false> pw = lookback_prefix<1, false>(lb, blockIdx.x, agg, &bcast);
     Counts3 pre;
     pre.s = pw.w[0][0];
@@ -722,18 +779,36 @@ __global__ void __launch_bounds__(SCAN_THREADS) p1_sites_kernel(SortedView sv, i
         all.u = pre.u + agg.w[0][3];
         *total = all;
     }
-#pragma unroll 4
+    uint32_t site[P1_ITEMS], mut[KEPT ? P1_ITEMS : 1], draw[KEPT ? P1_ITEMS : 1];
+#pragma unroll
     for (int k = 0; k < P1_ITEMS; k++) {
-        const uint32_t j = (uint32_t) k * SCAN_THREADS + threadIdx.x;
-        const uint64_t i = base + j;
-        if (i < sv.n) {
-            sv.site_row[i] = pre.s + s_site[j] - 1u;
-            if (sv.has_kept) {
-                sv.mut_scan[i] = pre.m + s_mut[j];
-                sv.draw_scan[i] = pre.d + s_draw[j];
-            }
-            if ((s_flag[j] >> 4) & 1u) {
-                multi_list[pre.u + s_multi[j]] = (uint32_t) i;
+        const uint32_t f = (flw[k >> 2] >> (8 * (k & 3))) & 0xffu;
+        // site: inclusive count (the record's own site row is count - 1); others exclusive
+        site[k] = pre.s + (uint32_t) (run & 0xffffull) + (f & 1u) - 1u;
+        if (KEPT) {
+            mut[k] = pre.m + (uint32_t) ((run >> 16) & 0xffffull);
+            draw[k] = pre.d + (uint32_t) ((run >> 32) & 0xffffull);
+        }
+        if ((f >> 4) & 1u) {
+            multi_list[pre.u + (uint32_t) (run >> 48)] = (uint32_t) (i0 + k);
+        }
+        run += p1_counts(f);
+    }
+    if (full) {
+        store16(sv.site_row + i0, site);
+        if (KEPT) {
+            store16(sv.mut_scan + i0, mut);
+            store16(sv.draw_scan + i0, draw);
+        }
+    } else {
+#pragma unroll
+        for (int k = 0; k < P1_ITEMS; k++) {
+            if (i0 + k < sv.n) {
+                sv.site_row[i0 + k] = site[k];
+                if (KEPT) {
+                    sv.mut_scan[i0 + k] = mut[k];
+                    sv.draw_scan[i0 + k] = draw[k];
+                }
             }
         }
     }

@@ -1010,9 +1010,25 @@ int run_sorted_stages(mspb_ctx *ctx, const mspb_params_t *p, const TreeSeqView &
     LbWord *lb3 = nullptr;
     TRY(lookback_state(ctx, p1_tiles, 1, &lb3));
     CUDA_OK(cudaMemsetAsync(&dt->dense, 0, sizeof(uint32_t), st));
-    MSPB_LAUNCH(ctx->log, "p1_sites",
-        p1_sites_kernel<<<p1_tiles, SCAN_THREADS, 0, st>>>(sv, call.discrete, lb3, p1_tiles, &dt->p1,
-            ctx->multi_list.p, &dt->collisions, &dt->dense, &dt->err));
+#define MSPB_P1(MODE, K)                                                                                             \
+    MSPB_LAUNCH(ctx->log, "p1_sites",                                                                                \
+        (p1_sites_kernel<MODE, K><<<p1_tiles, SCAN_THREADS, 0, st>>>(sv, call.discrete, lb3, p1_tiles, &dt->p1,      \
+            ctx->multi_list.p, &dt->collisions, &dt->dense, &dt->err)))
+#define MSPB_P1_MODE(MODE)                                                                                           \
+    if (sv.has_kept) {                                                                                               \
+        MSPB_P1(MODE, true);                                                                                         \
+    } else {                                                                                                         \
+        MSPB_P1(MODE, false);                                                                                        \
+    }
+    if (call.key_mode == KEY32_POS) {
+        MSPB_P1_MODE(KEY32_POS)
+    } else if (call.key_mode == KEY64_POS) {
+        MSPB_P1_MODE(KEY64_POS)
+    } else {
+        MSPB_P1_MODE(KEY64_POS_TIME)
+    }
+#undef MSPB_P1_MODE
+#undef MSPB_P1
 
     // ---- K4: sites with several records
     if (first_sort) {

@@ -157,7 +157,8 @@ inline uint64_t scan_num_tiles(uint64_t n)
 // ---------------------------------------------------------------- radix sort
 constexpr int RS_THREADS = 256;
 constexpr int RS_WARPS = RS_THREADS / 32;
-constexpr int RS_BINS = 256;
+constexpr int RS_DIGIT_BITS = 8;
+constexpr int RS_BINS = 1 << RS_DIGIT_BITS;
 constexpr int RS_MAX_PASSES = 8;
 // look-back word: 2 flag bits + 30-bit count
 constexpr uint32_t RS_FLAG_AGG = 1u << 30, RS_FLAG_INCL = 2u << 30, RS_COUNT_MASK = (1u << 30) - 1u;
@@ -340,7 +341,15 @@ __global__ void __launch_bounds__(RS_THREADS, 4) rs_onesweep_kernel(const KeyT *
         const uint64_t i = base + (uint64_t) k * 32 + lane;
         const bool valid = i < n;
         const uint32_t d = valid ? rs_digit(key[k], shift, mask) : 0xffffffffu;
-        const uint32_t peers = __match_any_sync(0xffffffffu, d);
+        // lanes holding the same digit, from one ballot per digit bit (MATCH.ANY runs one
+        // round per distinct value on the XU pipe: ~350 cycles here, the whole pass's bound)
+        uint32_t peers = __ballot_sync(0xffffffffu, valid);
+#pragma unroll
+        for (int b = 0; b < RS_DIGIT_BITS; b++) {
+            const bool bit = ((d >> b) & 1u) != 0u;
+            const uint32_t bal = __ballot_sync(0xffffffffu, bit);
+            peers &= bit ? bal : ~bal;
+        }
         const uint32_t before = __popc(peers & lt);
         uint32_t prev = 0;
         if (valid) {
