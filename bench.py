@@ -242,7 +242,7 @@ def algorithmic_bytes(kernel, n):
     E, R, M, S = n["E"], n["R"], n["M"], n["S"]
     table = {
         # left,right f64 + parent,child i32 + two node-time gathers in, goff u32 out
-        "k1_count_scan": E * (8 + 8 + 4 + 4 + 16) + E * 4,
+        "k1_count": E * (8 + 8 + 4 + 4 + 16) + E * 4,
         # goff in, edge columns of edges that mutate (<= E), Rec 16 B + key 4 B out
         "k2_place": E * 4 + min(E, M) * (8 + 8 + 4 + 4 + 16) + M * (16 + 4),
         "rs_global_hist": R * n["KB"],

@@ -256,41 +256,93 @@ MSPB_DEVFN uint32_t k1_in_slice(const Philox &ph, const RateMapView &map, const 
 
 constexpr int K1_ITEMS = 4;
 constexpr int K1_TILE = SCAN_THREADS * K1_ITEMS;
+constexpr int K1_TILE_SHIFT = 10;
+static_assert((1 << K1_TILE_SHIFT) == K1_TILE, "K1 tile size");
+
+// the rest of edge_draw once the edge's columns and node times are in registers
+MSPB_DEVFN EdgeDraw edge_draw_from(const RateMapView &map, const CallView &call, double left, double right,
+    int32_t child, double tc, double tp)
+{
+    EdgeDraw d;
+    d.left = left;
+    d.right = right;
+    d.child = child;
+    d.branch_start = fmax(call.start_time, tc);
+    d.branch_end = fmin(call.end_time, tp);
+    d.mass_lo = map.mass_upto(d.left);
+    d.mass = d.left < d.right ? map.mass_upto(d.right) - d.mass_lo : 0.0;
+    return d;
+}
 
 // count[e] = Poisson(branch length x rate mass), and how many of those fall in this
-// call's genome slice.  Both are prefix-summed here (low / high half of one 64-bit sum):
-// goff[e] = mutations of earlier edges (goff[E] = all), loff[e] = in-slice ones.
-__global__ void __launch_bounds__(SCAN_THREADS, 4) k1_count_scan_kernel(TreeSeqView ts, RateMapView map, CallView call,
-    LbWord *lb, uint32_t num_tiles, uint32_t *__restrict__ goff, uint32_t *__restrict__ loff, uint64_t *total)
+// call's genome slice (low / high half of one 64-bit count).  Written as offsets INSIDE
+// the tile (goff[e], loff[e]) plus one total per tile: tiles are independent, the tile
+// bases come from k1_spine_kernel, and K2 adds them when it reads.
+__global__ void __launch_bounds__(SCAN_THREADS, 4) k1_count_kernel(TreeSeqView ts, RateMapView map, CallView call,
+    uint32_t *__restrict__ goff, uint32_t *__restrict__ loff, uint64_t *__restrict__ tile_tot)
 {
     __shared__ uint64_t sm[9];
-    __shared__ LbVal<1, false> bcast;
     __shared__ uint64_t s_c[K1_TILE];
     __shared__ uint16_t s_big[K1_TILE]; // edges whose mean needs the rejection sampler
     __shared__ uint32_t s_nbig;
     const uint64_t tile_base = (uint64_t) blockIdx.x * K1_TILE;
+    const uint64_t last = ts.num_edges - 1;
     const Philox ph(call.seed);
     if (threadIdx.x == 0) {
         s_nbig = 0;
     }
     __syncthreads();
-    // striped: consecutive threads take consecutive edges (coalesced column reads).  The
-    // common small means are drawn here by inversion; the rare large ones are set aside
-    // so that their long rejection loop runs on full warps afterwards.
+    // striped: consecutive threads take consecutive edges (coalesced column reads).  All
+    // column loads of the thread's edges are issued first, then all node-time gathers.
+    double mu[K1_ITEMS];
+    {
+        double left[K1_ITEMS], right[K1_ITEMS], tc[K1_ITEMS], tp[K1_ITEMS];
+        int32_t child[K1_ITEMS], parent[K1_ITEMS];
+#pragma unroll
+        for (int k = 0; k < K1_ITEMS; k++) {
+            const uint64_t e = tile_base + (uint32_t) k * SCAN_THREADS + threadIdx.x;
+            const uint64_t ec = e < last ? e : last;
+            left[k] = ts.edge_left[ec];
+            right[k] = ts.edge_right[ec];
+            child[k] = ts.edge_child[ec];
+            parent[k] = ts.edge_parent[ec];
+        }
+#pragma unroll
+        for (int k = 0; k < K1_ITEMS; k++) {
+            if (call.clipped) {
+                left[k] = fmax(left[k], call.slice_left);
+                right[k] = fmin(right[k], call.slice_right);
+            }
+            // outside this call's slice: nothing to draw, skip the node-time gathers
+            const bool inside = !call.clipped || left[k] < right[k];
+            tc[k] = inside ? ts.node_time[child[k]] : 0.0;
+            tp[k] = inside ? ts.node_time[parent[k]] : 0.0;
+        }
+#pragma unroll
+        for (int k = 0; k < K1_ITEMS; k++) {
+            const uint64_t e = tile_base + (uint32_t) k * SCAN_THREADS + threadIdx.x;
+            mu[k] = 0.0;
+            if (e <= last && left[k] < right[k]) {
+                const EdgeDraw d = edge_draw_from(map, call, left[k], right[k], child[k], tc[k], tp[k]);
+                mu[k] = (d.branch_end - d.branch_start) * d.mass;
+            }
+        }
+    }
+    // the common small means are drawn here by inversion; the rare large ones are set
+    // aside so that their long rejection loop runs on full warps afterwards
 #pragma unroll
     for (int k = 0; k < K1_ITEMS; k++) {
         const uint32_t j = (uint32_t) k * SCAN_THREADS + threadIdx.x;
         const uint64_t e = tile_base + j;
         uint64_t c = 0;
-        if (e < ts.num_edges) {
-            const EdgeDraw d = edge_draw(ts, map, call, e);
-            const double mu = (d.branch_end - d.branch_start) * d.mass;
-            if (mu >= POISSON_SMALL_MU) {
-                s_big[atomicAdd(&s_nbig, 1u)] = (uint16_t) j;
-            } else if (mu > 0.0) {
-                PhiloxSeq rng(call.seed, e | ((uint64_t) call.stream << 32), TAG_COUNT);
-                const uint32_t n = poisson_small(rng.next(), mu);
-                c = (uint64_t) n | ((uint64_t) k1_in_slice(ph, map, call, d, e, n) << 32);
+        if (mu[k] >= POISSON_SMALL_MU) {
+            s_big[atomicAdd(&s_nbig, 1u)] = (uint16_t) j;
+        } else if (mu[k] > 0.0) {
+            PhiloxSeq rng(call.seed, e | ((uint64_t) call.stream << 32), TAG_COUNT);
+            const uint32_t n = poisson_small(rng.next(), mu[k]);
+            c = n;
+            if (call.sliced && n > 0) {
+                c |= (uint64_t) k1_in_slice(ph, map, call, edge_draw(ts, map, call, e), e, n) << 32;
             }
         }
         s_c[j] = c;
@@ -300,9 +352,9 @@ __global__ void __launch_bounds__(SCAN_THREADS, 4) k1_count_scan_kernel(TreeSeqV
         const uint32_t j = s_big[b];
         const uint64_t e = tile_base + j;
         const EdgeDraw d = edge_draw(ts, map, call, e);
-        const double mu = (d.branch_end - d.branch_start) * d.mass;
+        const double m = (d.branch_end - d.branch_start) * d.mass;
         PhiloxSeq rng(call.seed, e | ((uint64_t) call.stream << 32), TAG_COUNT);
-        const uint32_t n = poisson_native(rng, mu);
+        const uint32_t n = poisson_native(rng, m);
         s_c[j] = (uint64_t) n | ((uint64_t) k1_in_slice(ph, map, call, d, e, n) << 32);
     }
     __syncthreads();
@@ -315,32 +367,21 @@ __global__ void __launch_bounds__(SCAN_THREADS, 4) k1_count_scan_kernel(TreeSeqV
         acc += c[k];
     }
     uint64_t block_total;
-    const uint64_t ex = block_exclusive_scan<uint64_t>(acc, sm, &block_total);
-    LbVal<1, false> agg;
-    agg.clear();
-    agg.w[0][0] = (uint32_t) block_total;
-    agg.w[0][1] = (uint32_t) (block_total >> 32);
-    const LbVal<1, false> pre = lookback_prefix<1, false>(lb, blockIdx.x, agg, &bcast);
-    const uint64_t tile_prefix = (uint64_t) pre.w[0][0] | ((uint64_t) pre.w[0][1] << 32);
-    if (blockIdx.x + 1 == num_tiles && threadIdx.x == 0) {
-        *total = tile_prefix + block_total;
+    uint64_t run = block_exclusive_scan<uint64_t>(acc, sm, &block_total);
+    if (threadIdx.x == 0) {
+        tile_tot[blockIdx.x] = block_total;
     }
-    uint64_t run = tile_prefix + ex;
 #pragma unroll
     for (int k = 0; k < K1_ITEMS; k++) {
         s_c[threadIdx.x * K1_ITEMS + k] = run;
         run += c[k];
-    }
-    if (tile_base + (uint64_t) threadIdx.x * K1_ITEMS + K1_ITEMS >= ts.num_edges
-        && tile_base + (uint64_t) threadIdx.x * K1_ITEMS < ts.num_edges) {
-        goff[ts.num_edges] = (uint32_t) run; // the thread that owns the last edge
     }
     __syncthreads();
 #pragma unroll
     for (int k = 0; k < K1_ITEMS; k++) {
         const uint32_t j = (uint32_t) k * SCAN_THREADS + threadIdx.x;
         const uint64_t e = tile_base + j;
-        if (e < ts.num_edges) {
+        if (e <= last) {
             const uint64_t v = s_c[j];
             goff[e] = (uint32_t) v;
             if (loff != nullptr) {
@@ -350,6 +391,58 @@ __global__ void __launch_bounds__(SCAN_THREADS, 4) k1_count_scan_kernel(TreeSeqV
     }
 }
 
+// tile_tot[t] (count | in-slice << 32) -> exclusive prefix in place, with the grand total
+// appended at tile_tot[num_tiles] and copied to *total.  One block.
+__global__ void __launch_bounds__(1024) k1_spine_kernel(uint64_t *tile_tot, uint32_t num_tiles, uint64_t *total)
+{
+    __shared__ uint64_t warp_sum[32];
+    __shared__ uint64_t carry_s;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) {
+        carry_s = 0;
+    }
+    __syncthreads();
+    for (uint32_t start = 0; start < num_tiles; start += 1024) {
+        const uint32_t i = start + threadIdx.x;
+        const uint64_t v = i < num_tiles ? tile_tot[i] : 0ull;
+        const uint64_t inc = warp_inclusive_scan(v);
+        if (lane == 31) {
+            warp_sum[warp] = inc;
+        }
+        __syncthreads();
+        if (warp == 0) {
+            const uint64_t w = warp_sum[lane];
+            const uint64_t winc = warp_inclusive_scan(w);
+            warp_sum[lane] = winc - w;
+        }
+        __syncthreads();
+        const uint64_t carry = carry_s;
+        const uint64_t ex = carry + warp_sum[warp] + inc - v;
+        if (i < num_tiles) {
+            tile_tot[i] = ex;
+        }
+        __syncthreads();
+        if (threadIdx.x == 1023) {
+            carry_s = ex + v;
+        }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        tile_tot[num_tiles] = carry_s;
+        *total = carry_s;
+    }
+}
+
+// global offset of edge e's first mutation (e == E: the total), from the tile-local
+// offsets and the tile bases; `hi` selects the in-slice counts
+MSPB_DEVFN uint32_t k1_offset(const uint32_t *__restrict__ local, const uint64_t *__restrict__ tile_base, uint64_t e,
+    uint64_t E, bool hi)
+{
+    const uint64_t t = e >> K1_TILE_SHIFT;
+    const uint64_t b = e < E ? tile_base[t] : tile_base[(E + K1_TILE - 1) >> K1_TILE_SHIFT];
+    return (e < E ? local[e] : 0u) + (uint32_t) (hi ? b >> 32 : b);
+}
+
 // ---------------------------------------------------------------- K2 (native)
 // One block per 256 edges: their draw parameters are staged in shared memory, then
 // each thread places one mutation (slot j of the tile's contiguous slot range), so
@@ -357,8 +450,8 @@ __global__ void __launch_bounds__(SCAN_THREADS, 4) k1_count_scan_kernel(TreeSeqV
 constexpr int K2_EDGES = 256;
 
 __global__ void __launch_bounds__(K2_EDGES) k2_place_kernel(TreeSeqView ts, RateMapView map, CallView call,
-    const uint32_t *__restrict__ goff, const uint32_t *__restrict__ loff, uint32_t base, Rec *__restrict__ rec,
-    KeyView keys)
+    const uint32_t *__restrict__ goff, const uint32_t *__restrict__ loff, const uint64_t *__restrict__ tile_base,
+    uint32_t base, Rec *__restrict__ rec, KeyView keys)
 {
     __shared__ EdgeDraw sd[K2_EDGES];
     __shared__ uint32_t soff[K2_EDGES + 1];
@@ -366,9 +459,9 @@ __global__ void __launch_bounds__(K2_EDGES) k2_place_kernel(TreeSeqView ts, Rate
     const uint64_t E = ts.num_edges;
     const uint64_t ebase = (uint64_t) blockIdx.x * K2_EDGES;
     const uint64_t e = ebase + threadIdx.x;
-    soff[threadIdx.x] = goff[e < E ? e : E];
+    soff[threadIdx.x] = k1_offset(goff, tile_base, e < E ? e : E, E, false);
     if (threadIdx.x == 0) {
-        soff[K2_EDGES] = goff[ebase + K2_EDGES < E ? ebase + K2_EDGES : E];
+        soff[K2_EDGES] = k1_offset(goff, tile_base, ebase + K2_EDGES < E ? ebase + K2_EDGES : E, E, false);
     }
     __syncthreads();
     const uint32_t s0 = soff[0], s1 = soff[K2_EDGES];
@@ -380,7 +473,7 @@ __global__ void __launch_bounds__(K2_EDGES) k2_place_kernel(TreeSeqView ts, Rate
     }
     __syncthreads();
     const Philox ph(call.seed);
-    uint32_t out = base + (call.sliced ? loff[ebase] : s0);
+    uint32_t out = base + (call.sliced ? k1_offset(loff, tile_base, ebase, E, true) : s0);
     for (uint32_t j0 = s0; j0 < s1; j0 += K2_EDGES) {
         const uint32_t j = j0 + threadIdx.x;
         const bool valid = j < s1;

@@ -92,7 +92,8 @@ struct mspb_ctx {
     DBuf<uint64_t> model_allele_off;
     uint64_t kept_anc_bytes = 0, kept_smd_bytes = 0, kept_der_bytes = 0, kept_mmd_bytes = 0;
     // work
-    DBuf<uint32_t> goff, loff;
+    DBuf<uint32_t> goff, loff; // K1: offsets of each edge's mutations inside its K1 tile
+    DBuf<uint64_t> k1_tiles; // K1: tile bases (count | in-slice count << 32), total appended
     DBuf<Rec> rec;
     DBuf<uint64_t> keys0, keys1; // 64-bit keys (ping-pong)
     DBuf<uint32_t> k32_0, k32_1; // 32-bit keys (ping-pong)
@@ -293,7 +294,7 @@ extern "C" void mspb_ctx_destroy(mspb_ctx_t *ctx)
     REL(k_mut_site); REL(k_mut_node); REL(k_site_allele); REL(k_mut_allele);
     REL(map_pos); REL(map_rate); REL(map_cum); REL(model_root); REL(model_matrix); REL(replay);
     REL(model_alleles); REL(model_allele_off);
-    REL(goff); REL(loff); REL(rec); REL(keys0); REL(keys1); REL(k32_0); REL(k32_1); REL(vals0); REL(vals1);
+    REL(goff); REL(loff); REL(k1_tiles); REL(rec); REL(keys0); REL(keys1); REL(k32_0); REL(k32_1); REL(vals0); REL(vals1);
     REL(tile_hist); REL(rs_scan_tiles); REL(or_and); REL(lb_state);
     REL(site_scan); REL(mut_scan); REL(draw_scan); REL(multi_list); REL(parent); REL(state); REL(site_state);
     REL(rp_edge); REL(rp_interval); REL(rp_count); REL(rp_out_off); REL(rp_stream_off); REL(dev_totals);
@@ -1148,11 +1149,12 @@ static int generate_impl(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t 
         }
         if (ctx->E > 0) {
             const uint32_t tiles = (uint32_t) ((ctx->E + K1_TILE - 1) / K1_TILE);
-            LbWord *lb = nullptr;
-            TRY(lookback_state(ctx, tiles, 1, &lb));
-            MSPB_LAUNCH(ctx->log, "k1_count_scan",
-                k1_count_scan_kernel<<<tiles, SCAN_THREADS, 0, st>>>(
-                    ts, map, call, lb, tiles, ctx->goff.p, sliced ? ctx->loff.p : nullptr, &dt->k1_total));
+            TRY(ctx->k1_tiles.ensure(tiles + 1));
+            MSPB_LAUNCH(ctx->log, "k1_count",
+                k1_count_kernel<<<tiles, SCAN_THREADS, 0, st>>>(
+                    ts, map, call, ctx->goff.p, sliced ? ctx->loff.p : nullptr, ctx->k1_tiles.p));
+            MSPB_LAUNCH(ctx->log, "k1_spine",
+                k1_spine_kernel<<<1, 1024, 0, st>>>(ctx->k1_tiles.p, tiles, &dt->k1_total));
         }
         CUDA_OK(cudaMemcpyAsync(ht, dt, sizeof(HostTotals), cudaMemcpyDeviceToHost, st));
         CUDA_OK(cudaStreamSynchronize(st));
@@ -1300,7 +1302,7 @@ static int generate_impl(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t 
         if (!replay) {
             MSPB_LAUNCH(ctx->log, "k2_place",
                 k2_place_kernel<<<grid_for(ctx->E, K2_EDGES), K2_EDGES, 0, st>>>(ts, map, call, ctx->goff.p,
-                    sliced ? ctx->loff.p : nullptr, (uint32_t) (S0 + M0), ctx->rec.p, keys));
+                    sliced ? ctx->loff.p : nullptr, ctx->k1_tiles.p, (uint32_t) (S0 + M0), ctx->rec.p, keys));
         } else {
             MSPB_LAUNCH(ctx->log, "replay_place",
                 replay_place_kernel<<<grid_for(num_pairs, 128), 128, 0, st>>>(ts, map, call, ctx->replay.p, pairs,

@@ -324,12 +324,14 @@ __global__ void __launch_bounds__(RS_THREADS, 4) rs_onesweep_kernel(const KeyT *
     const uint64_t tile_base = (uint64_t) tile * TILE;
     const uint64_t base = tile_base + (uint64_t) warp * (32 * ITEMS);
     const uint32_t tile_n = (uint32_t) ((n - tile_base) < (uint64_t) TILE ? (n - tile_base) : (uint64_t) TILE);
+    const bool full = tile_n == (uint32_t) TILE;
+    const int nbits = 32 - __clz(mask);
     KeyT key[ITEMS];
     uint32_t pos2[ITEMS / 2]; // ranks inside the tile (< 4096), two per register
 #pragma unroll
     for (int k = 0; k < ITEMS; k++) {
         const uint64_t i = base + (uint64_t) k * 32 + lane;
-        key[k] = i < n ? keys_in[i] : (KeyT) 0;
+        key[k] = (full || i < n) ? keys_in[i] : (KeyT) 0;
     }
 #pragma unroll
     for (int k = 0; k < ITEMS / 2; k++) {
@@ -338,29 +340,34 @@ __global__ void __launch_bounds__(RS_THREADS, 4) rs_onesweep_kernel(const KeyT *
     const uint32_t lt = (1u << lane) - 1u;
 #pragma unroll
     for (int k = 0; k < ITEMS; k++) {
-        const uint64_t i = base + (uint64_t) k * 32 + lane;
-        const bool valid = i < n;
-        const uint32_t d = valid ? rs_digit(key[k], shift, mask) : 0xffffffffu;
+        const bool valid = full || base + (uint64_t) k * 32 + lane < n;
+        const uint32_t d = rs_digit(key[k], shift, mask);
         // lanes holding the same digit, from one ballot per digit bit (MATCH.ANY runs one
-        // round per distinct value on the XU pipe: ~350 cycles here, the whole pass's bound)
-        uint32_t peers = __ballot_sync(0xffffffffu, valid);
+        // round per distinct value here and is slower)
+        uint32_t peers = full ? 0xffffffffu : __ballot_sync(0xffffffffu, valid);
 #pragma unroll
         for (int b = 0; b < RS_DIGIT_BITS; b++) {
-            const bool bit = ((d >> b) & 1u) != 0u;
-            const uint32_t bal = __ballot_sync(0xffffffffu, bit);
-            peers &= bit ? bal : ~bal;
+            if (b < nbits) {
+                const bool bit = ((d >> b) & 1u) != 0u;
+                const uint32_t bal = __ballot_sync(0xffffffffu, bit);
+                peers &= bit ? bal : ~bal;
+            }
         }
-        const uint32_t before = __popc(peers & lt);
+        // the lowest lane of each group bumps the warp's digit counter for the whole group
+        const int leader = __ffs(peers | (valid ? 0u : (1u << lane))) - 1;
         uint32_t prev = 0;
-        if (valid) {
-            prev = cnt[warp][d];
+        if (valid && lane == leader) {
+            prev = atomicAdd(&cnt[warp][d], (uint32_t) __popc(peers));
         }
-        __syncwarp();
-        if (valid && before == 0) {
-            cnt[warp][d] = prev + (uint32_t) __popc(peers);
-        }
-        __syncwarp();
-        pos2[k >> 1] |= (prev + before) << (16 * (k & 1));
+        prev = __shfl_sync(0xffffffffu, prev, leader);
+        pos2[k >> 1] |= (prev + (uint32_t) __popc(peers & lt)) << (16 * (k & 1));
+    }
+    // payloads: issued here so that their latency hides behind the scans below
+    uint32_t val[ITEMS];
+#pragma unroll
+    for (int k = 0; k < ITEMS; k++) {
+        const uint64_t i = base + (uint64_t) k * 32 + lane;
+        val[k] = vals_in != nullptr ? ((full || i < n) ? vals_in[i] : 0u) : (uint32_t) i;
     }
     __syncthreads();
     // thread b owns digit b
@@ -392,11 +399,11 @@ __global__ void __launch_bounds__(RS_THREADS, 4) rs_onesweep_kernel(const KeyT *
 #pragma unroll
     for (int k = 0; k < ITEMS; k++) {
         const uint64_t i = base + (uint64_t) k * 32 + lane;
-        if (i < n) {
+        if (full || i < n) {
             const uint32_t d = rs_digit(key[k], shift, mask);
             const uint32_t q = ((pos2[k >> 1] >> (16 * (k & 1))) & 0xffffu) + local_start[d] + cnt[warp][d];
             skeys[q] = key[k];
-            svals[q] = vals_in != nullptr ? vals_in[i] : (uint32_t) i;
+            svals[q] = val[k];
         }
     }
     if (tile > 0) {
