@@ -392,44 +392,37 @@ __global__ void __launch_bounds__(SCAN_THREADS, 4) k1_count_kernel(TreeSeqView t
 }
 
 // tile_tot[t] (count | in-slice << 32) -> exclusive prefix in place, with the grand total
-// appended at tile_tot[num_tiles] and copied to *total.  One block.
+// appended at tile_tot[num_tiles] and copied to *total.  One block; each thread owns a
+// contiguous run of tiles, so it is one pass and one block scan.
 __global__ void __launch_bounds__(1024) k1_spine_kernel(uint64_t *tile_tot, uint32_t num_tiles, uint64_t *total)
 {
     __shared__ uint64_t warp_sum[32];
-    __shared__ uint64_t carry_s;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    if (threadIdx.x == 0) {
-        carry_s = 0;
+    const uint32_t per = (num_tiles + 1023u) / 1024u;
+    const uint32_t lo = threadIdx.x * per, hi = lo + per < num_tiles ? lo + per : num_tiles;
+    uint64_t sum = 0;
+    for (uint32_t i = lo; i < hi; i++) {
+        sum += tile_tot[i];
+    }
+    const uint64_t inc = warp_inclusive_scan(sum);
+    if (lane == 31) {
+        warp_sum[warp] = inc;
     }
     __syncthreads();
-    for (uint32_t start = 0; start < num_tiles; start += 1024) {
-        const uint32_t i = start + threadIdx.x;
-        const uint64_t v = i < num_tiles ? tile_tot[i] : 0ull;
-        const uint64_t inc = warp_inclusive_scan(v);
-        if (lane == 31) {
-            warp_sum[warp] = inc;
-        }
-        __syncthreads();
-        if (warp == 0) {
-            const uint64_t w = warp_sum[lane];
-            const uint64_t winc = warp_inclusive_scan(w);
-            warp_sum[lane] = winc - w;
-        }
-        __syncthreads();
-        const uint64_t carry = carry_s;
-        const uint64_t ex = carry + warp_sum[warp] + inc - v;
-        if (i < num_tiles) {
-            tile_tot[i] = ex;
-        }
-        __syncthreads();
-        if (threadIdx.x == 1023) {
-            carry_s = ex + v;
-        }
-        __syncthreads();
+    if (warp == 0) {
+        const uint64_t w = warp_sum[lane];
+        warp_sum[lane] = warp_inclusive_scan(w) - w;
     }
-    if (threadIdx.x == 0) {
-        tile_tot[num_tiles] = carry_s;
-        *total = carry_s;
+    __syncthreads();
+    uint64_t run = warp_sum[warp] + inc - sum;
+    for (uint32_t i = lo; i < hi; i++) {
+        const uint64_t v = tile_tot[i];
+        tile_tot[i] = run;
+        run += v;
+    }
+    if (threadIdx.x == 1023) {
+        tile_tot[num_tiles] = run;
+        *total = run;
     }
 }
 

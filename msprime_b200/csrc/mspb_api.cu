@@ -495,7 +495,7 @@ int ensure_sort_buffers(mspb_ctx *ctx, uint64_t n, bool k32, bool k64)
     }
     TRY(ctx->vals0.ensure(n + 1));
     TRY(ctx->vals1.ensure(n + 1));
-    TRY(ctx->tile_hist.ensure((size_t) RS_MAX_PASSES * RS_BINS));
+    TRY(ctx->tile_hist.ensure((size_t) RS_MAX_PASSES * RS_BINS + 1));
     TRY(ctx->rs_scan_tiles.ensure(rs_state_words(n)));
     return 0;
 }
@@ -1666,7 +1666,7 @@ int selftest_sort_impl(mspb_ctx *ctx, uint64_t n, uint64_t key_mask, uint64_t se
     DBuf<uint32_t> v0, v1, hist, state;
     int ret = 0;
     if (k0.ensure(n + 1) || k1.ensure(n + 1) || v0.ensure(n + 1) || v1.ensure(n + 1)
-        || hist.ensure((size_t) RS_MAX_PASSES * RS_BINS) || state.ensure(rs_state_words(n))) {
+        || hist.ensure((size_t) RS_MAX_PASSES * RS_BINS + 1) || state.ensure(rs_state_words(n))) {
         ret = MSPB_ERR_NO_MEMORY;
     }
     if (ret == 0) {

@@ -250,13 +250,17 @@ __global__ void __launch_bounds__(256) rs_key_bits_kernel(const KeyT *__restrict
     }
 }
 
-// Global digit histograms of every pass in one read of the keys:
-// hist[pass * RS_BINS + digit].
+// Global digit histograms of every pass in one read of the keys, hist[pass * RS_BINS +
+// digit]; the last block to finish turns each pass's histogram into its exclusive prefix
+// (where each digit's run starts in the output).  hist[RS_MAX_PASSES * RS_BINS] is the
+// ticket counter.
 template <typename KeyT>
 __global__ void __launch_bounds__(RS_THREADS) rs_global_hist_kernel(const KeyT *__restrict__ keys, uint64_t n,
     RadixPlanDev plan, uint32_t *__restrict__ hist)
 {
     __shared__ uint32_t sh[RS_MAX_PASSES * RS_BINS];
+    __shared__ uint32_t scan_tmp[9];
+    __shared__ bool is_last;
     for (int i = threadIdx.x; i < plan.passes * RS_BINS; i += RS_THREADS) {
         sh[i] = 0;
     }
@@ -273,6 +277,21 @@ __global__ void __launch_bounds__(RS_THREADS) rs_global_hist_kernel(const KeyT *
         const uint32_t c = sh[i];
         if (c != 0) {
             atomicAdd(&hist[i], c);
+        }
+    }
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        is_last = atomicAdd(&hist[RS_MAX_PASSES * RS_BINS], 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (is_last) {
+        __threadfence();
+        for (int p = 0; p < plan.passes; p++) {
+            volatile uint32_t *h = hist + p * RS_BINS;
+            uint32_t tot;
+            const uint32_t ex = block_exclusive_scan<uint32_t>(h[threadIdx.x], scan_tmp, &tot);
+            h[threadIdx.x] = ex;
         }
     }
 }
@@ -295,19 +314,19 @@ struct RsTraits {
                                    + (size_t) TILE * (sizeof(KeyT) + 4);
 };
 
-// One pass.  Warp w of a tile owns the contiguous chunk [w*32*ITEMS, (w+1)*32*ITEMS) of the
-// tile and iteration k covers 32 consecutive keys, so (warp, iteration, lane) order is
+// One tile of one pass.  Warp w owns the contiguous chunk [w*32*ITEMS, (w+1)*32*ITEMS) of
+// the tile and iteration k covers 32 consecutive keys, so (warp, iteration, lane) order is
 // index order and ranks accumulated in that order make the pass stable.  Keys and
 // payloads are staged in shared memory in sorted order and written as contiguous runs.
-// vals_in == nullptr means the identity payload (first pass).
-template <typename KeyT>
-__global__ void __launch_bounds__(RS_THREADS, 4) rs_onesweep_kernel(const KeyT *__restrict__ keys_in,
-    const uint32_t *__restrict__ vals_in, KeyT *__restrict__ keys_out, uint32_t *__restrict__ vals_out, uint64_t n,
-    int shift, uint32_t mask, const uint32_t *__restrict__ global_hist, volatile uint32_t *tile_state)
+// vals_in == nullptr means the identity payload (first pass).  FULL tiles carry no bounds
+// checks; NBITS >= the digit width (one ballot per bit).
+template <typename KeyT, int NBITS, bool FULL>
+MSPB_DEVFN void rs_onesweep_tile(const KeyT *__restrict__ keys_in, const uint32_t *__restrict__ vals_in,
+    KeyT *__restrict__ keys_out, uint32_t *__restrict__ vals_out, uint64_t n, int shift, uint32_t mask,
+    const uint32_t *__restrict__ global_excl, volatile uint32_t *tile_state, unsigned char *rs_smem)
 {
     constexpr int ITEMS = RsTraits<KeyT>::ITEMS;
     constexpr int TILE = RsTraits<KeyT>::TILE;
-    extern __shared__ __align__(16) unsigned char rs_smem[];
     KeyT *skeys = reinterpret_cast<KeyT *>(rs_smem);
     uint32_t *svals = reinterpret_cast<uint32_t *>(skeys + TILE);
     uint32_t(*cnt)[RS_BINS] = reinterpret_cast<uint32_t(*)[RS_BINS]>(svals + TILE);
@@ -322,16 +341,14 @@ __global__ void __launch_bounds__(RS_THREADS, 4) rs_onesweep_kernel(const KeyT *
     }
     __syncthreads();
     const uint64_t tile_base = (uint64_t) tile * TILE;
-    const uint64_t base = tile_base + (uint64_t) warp * (32 * ITEMS);
-    const uint32_t tile_n = (uint32_t) ((n - tile_base) < (uint64_t) TILE ? (n - tile_base) : (uint64_t) TILE);
-    const bool full = tile_n == (uint32_t) TILE;
-    const int nbits = 32 - __clz(mask);
+    const uint32_t tile_n = FULL ? (uint32_t) TILE : (uint32_t) (n - tile_base);
+    const uint32_t wbase = (uint32_t) warp * (32 * ITEMS) + lane; // this lane's first key inside the tile
+    const KeyT *kin = keys_in + tile_base + wbase;
     KeyT key[ITEMS];
     uint32_t pos2[ITEMS / 2]; // ranks inside the tile (< 4096), two per register
 #pragma unroll
     for (int k = 0; k < ITEMS; k++) {
-        const uint64_t i = base + (uint64_t) k * 32 + lane;
-        key[k] = (full || i < n) ? keys_in[i] : (KeyT) 0;
+        key[k] = (FULL || wbase + k * 32 < tile_n) ? kin[k * 32] : (KeyT) 0;
     }
 #pragma unroll
     for (int k = 0; k < ITEMS / 2; k++) {
@@ -340,21 +357,19 @@ __global__ void __launch_bounds__(RS_THREADS, 4) rs_onesweep_kernel(const KeyT *
     const uint32_t lt = (1u << lane) - 1u;
 #pragma unroll
     for (int k = 0; k < ITEMS; k++) {
-        const bool valid = full || base + (uint64_t) k * 32 + lane < n;
+        const bool valid = FULL || wbase + k * 32 < tile_n;
         const uint32_t d = rs_digit(key[k], shift, mask);
         // lanes holding the same digit, from one ballot per digit bit (MATCH.ANY runs one
         // round per distinct value here and is slower)
-        uint32_t peers = full ? 0xffffffffu : __ballot_sync(0xffffffffu, valid);
+        uint32_t peers = FULL ? 0xffffffffu : __ballot_sync(0xffffffffu, valid);
 #pragma unroll
-        for (int b = 0; b < RS_DIGIT_BITS; b++) {
-            if (b < nbits) {
-                const bool bit = ((d >> b) & 1u) != 0u;
-                const uint32_t bal = __ballot_sync(0xffffffffu, bit);
-                peers &= bit ? bal : ~bal;
-            }
+        for (int b = 0; b < NBITS; b++) {
+            const bool bit = (d & (1u << b)) != 0u;
+            const uint32_t bal = __ballot_sync(0xffffffffu, bit);
+            peers &= bal ^ (bit ? 0u : 0xffffffffu);
         }
         // the lowest lane of each group bumps the warp's digit counter for the whole group
-        const int leader = __ffs(peers | (valid ? 0u : (1u << lane))) - 1;
+        const int leader = __ffs(FULL ? peers : (peers | (valid ? 0u : (1u << lane)))) - 1;
         uint32_t prev = 0;
         if (valid && lane == leader) {
             prev = atomicAdd(&cnt[warp][d], (uint32_t) __popc(peers));
@@ -364,10 +379,17 @@ __global__ void __launch_bounds__(RS_THREADS, 4) rs_onesweep_kernel(const KeyT *
     }
     // payloads: issued here so that their latency hides behind the scans below
     uint32_t val[ITEMS];
+    if (vals_in != nullptr) {
+        const uint32_t *vin = vals_in + tile_base + wbase;
 #pragma unroll
-    for (int k = 0; k < ITEMS; k++) {
-        const uint64_t i = base + (uint64_t) k * 32 + lane;
-        val[k] = vals_in != nullptr ? ((full || i < n) ? vals_in[i] : 0u) : (uint32_t) i;
+        for (int k = 0; k < ITEMS; k++) {
+            val[k] = (FULL || wbase + k * 32 < tile_n) ? vin[k * 32] : 0u;
+        }
+    } else {
+#pragma unroll
+        for (int k = 0; k < ITEMS; k++) {
+            val[k] = (uint32_t) tile_base + wbase + k * 32;
+        }
     }
     __syncthreads();
     // thread b owns digit b
@@ -388,18 +410,16 @@ __global__ void __launch_bounds__(RS_THREADS, 4) rs_onesweep_kernel(const KeyT *
     } else {
         *mine = RS_FLAG_AGG | tile_count;
     }
-    // exclusive scans over the 256 digits: within the tile, and of the global histogram
+    // exclusive scan over the 256 digits within the tile (the global one is precomputed)
     uint32_t tot;
     const uint32_t ls = block_exclusive_scan<uint32_t>(tile_count, scan_tmp, &tot);
-    const uint32_t gh = global_hist[threadIdx.x];
-    const uint32_t gs = block_exclusive_scan<uint32_t>(gh, scan_tmp, &tot);
+    const uint32_t gs = global_excl[threadIdx.x];
     local_start[threadIdx.x] = ls;
     __syncthreads();
     // stage keys and payloads in sorted order (overlaps the look-back latency of other warps)
 #pragma unroll
     for (int k = 0; k < ITEMS; k++) {
-        const uint64_t i = base + (uint64_t) k * 32 + lane;
-        if (full || i < n) {
+        if (FULL || wbase + k * 32 < tile_n) {
             const uint32_t d = rs_digit(key[k], shift, mask);
             const uint32_t q = ((pos2[k >> 1] >> (16 * (k & 1))) & 0xffffu) + local_start[d] + cnt[warp][d];
             skeys[q] = key[k];
@@ -407,8 +427,9 @@ __global__ void __launch_bounds__(RS_THREADS, 4) rs_onesweep_kernel(const KeyT *
         }
     }
     if (tile > 0) {
-        for (int64_t p = (int64_t) tile - 1; p >= 0; p--) {
-            volatile uint32_t *theirs = tile_state + (uint64_t) p * RS_BINS + threadIdx.x;
+        const volatile uint32_t *theirs = mine;
+        for (;;) {
+            theirs -= RS_BINS;
             uint32_t v;
             do {
                 v = *theirs;
@@ -425,12 +446,27 @@ __global__ void __launch_bounds__(RS_THREADS, 4) rs_onesweep_kernel(const KeyT *
 #pragma unroll
     for (int k = 0; k < ITEMS; k++) {
         const uint32_t j = (uint32_t) k * RS_THREADS + threadIdx.x;
-        if (j < tile_n) {
+        if (FULL || j < tile_n) {
             const KeyT kk = skeys[j];
             const uint32_t dst = global_base[rs_digit(kk, shift, mask)] + j;
             keys_out[dst] = kk;
             vals_out[dst] = svals[j];
         }
+    }
+}
+
+template <typename KeyT, int NBITS>
+__global__ void __launch_bounds__(RS_THREADS, 4) rs_onesweep_kernel(const KeyT *__restrict__ keys_in,
+    const uint32_t *__restrict__ vals_in, KeyT *__restrict__ keys_out, uint32_t *__restrict__ vals_out, uint64_t n,
+    int shift, uint32_t mask, const uint32_t *__restrict__ global_excl, volatile uint32_t *tile_state)
+{
+    extern __shared__ __align__(16) unsigned char rs_smem[];
+    if ((uint64_t) (blockIdx.x + 1) * RsTraits<KeyT>::TILE <= n) {
+        rs_onesweep_tile<KeyT, NBITS, true>(keys_in, vals_in, keys_out, vals_out, n, shift, mask, global_excl,
+            tile_state, rs_smem);
+    } else {
+        rs_onesweep_tile<KeyT, NBITS, false>(keys_in, vals_in, keys_out, vals_out, n, shift, mask, global_excl,
+            tile_state, rs_smem);
     }
 }
 
@@ -496,7 +532,7 @@ inline int device_radix_sort(RadixSortBuffers<KeyT> &buf, uint64_t n, uint64_t v
         pd.shift[p] = plan.shift[p];
         pd.mask[p] = (1u << plan.bits[p]) - 1u;
     }
-    cudaMemsetAsync(buf.hist, 0, (size_t) RS_MAX_PASSES * RS_BINS * sizeof(uint32_t), st);
+    cudaMemsetAsync(buf.hist, 0, ((size_t) RS_MAX_PASSES * RS_BINS + 1) * sizeof(uint32_t), st);
     cudaMemsetAsync(buf.tile_state, 0, (size_t) plan.passes * tiles * RS_BINS * sizeof(uint32_t), st);
     const unsigned hist_blocks = tiles < 148u * 8u ? tiles : 148u * 8u;
     MSPB_LAUNCH(log, "rs_global_hist",
@@ -504,15 +540,36 @@ inline int device_radix_sort(RadixSortBuffers<KeyT> &buf, uint64_t n, uint64_t v
     int cur = 0;
     static bool smem_opt_in = false; // per key type (this is a template)
     if (!smem_opt_in) {
-        cudaFuncSetAttribute(
-            rs_onesweep_kernel<KeyT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) RsTraits<KeyT>::SMEM);
+        const int bytes = (int) RsTraits<KeyT>::SMEM;
+        cudaFuncSetAttribute(rs_onesweep_kernel<KeyT, 5>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+        cudaFuncSetAttribute(rs_onesweep_kernel<KeyT, 6>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+        cudaFuncSetAttribute(rs_onesweep_kernel<KeyT, 7>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+        cudaFuncSetAttribute(rs_onesweep_kernel<KeyT, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
         smem_opt_in = true;
     }
     for (int p = 0; p < plan.passes; p++) {
-        MSPB_LAUNCH(log, "rs_onesweep",
-            rs_onesweep_kernel<KeyT><<<tiles, RS_THREADS, RsTraits<KeyT>::SMEM, st>>>(buf.keys[cur],
-                (p == 0 && identity_vals) ? nullptr : buf.vals[cur], buf.keys[cur ^ 1], buf.vals[cur ^ 1], n,
-                pd.shift[p], pd.mask[p], buf.hist + p * RS_BINS, buf.tile_state + (size_t) p * tiles * RS_BINS));
+        const uint32_t *vin = (p == 0 && identity_vals) ? nullptr : buf.vals[cur];
+        uint32_t *state = buf.tile_state + (size_t) p * tiles * RS_BINS;
+#define MSPB_RS_PASS(NB)                                                                                             \
+    MSPB_LAUNCH(log, "rs_onesweep",                                                                                  \
+        (rs_onesweep_kernel<KeyT, NB><<<tiles, RS_THREADS, RsTraits<KeyT>::SMEM, st>>>(buf.keys[cur], vin,           \
+            buf.keys[cur ^ 1], buf.vals[cur ^ 1], n, pd.shift[p], pd.mask[p], buf.hist + p * RS_BINS, state)))
+        // digits narrower than 5 bits run through the 5-ballot instantiation (extra bits are zero)
+        switch (plan.bits[p]) {
+        case 8:
+            MSPB_RS_PASS(8);
+            break;
+        case 7:
+            MSPB_RS_PASS(7);
+            break;
+        case 6:
+            MSPB_RS_PASS(6);
+            break;
+        default:
+            MSPB_RS_PASS(5);
+            break;
+        }
+#undef MSPB_RS_PASS
         cur ^= 1;
     }
     if (passes_out != nullptr) {
