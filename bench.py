@@ -293,7 +293,12 @@ def run_b200_arm(args, rank, local_rank, world):
                          "(use --impl reference for the CPU baseline)")
     if rank == 0:
         build.build()
+    stdout_fd = None
     if world > 1:
+        # NCCL prints its version banner on stdout: park stdout on stderr until the JSON line
+        sys.stdout.flush()
+        stdout_fd = os.dup(1)
+        os.dup2(2, 1)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
         dist.barrier()
     torch.cuda.set_device(local_rank)
@@ -337,7 +342,8 @@ def run_b200_arm(args, rank, local_rank, world):
         dist.all_reduce(t, op=op)
         return float(t.item())
 
-    allgather = sharding.dist_allgather(device=f"cuda:{local_rank}") if world > 1 else None
+    # counts are exchanged on the device: NCCL all-gathers enqueued on the context's stream
+    gather = sharding.nccl_device_allgather(ctx, world) if world > 1 else None
 
     def overlay(step, fetch_into=None):
         """One overlay of this rank's slice; returns the number of new mutations it holds."""
@@ -346,8 +352,8 @@ def run_b200_arm(args, rank, local_rank, world):
             if fetch_into is not None:
                 ctx.fetch(fetch_into)
             return c["num_new_mutations"]
-        sharding.run_slice(ctx, params(step), rank=rank, world=world, allgather=allgather,
-                           fetch=fetch_into is not None, out=fetch_into)
+        sharding.run_slice_device(ctx, params(step), rank=rank, world=world, gather=gather,
+                                  fetch=fetch_into is not None, out=fetch_into)
         return ctx.counts["num_new_mutations"]
 
     ctx.load_tables(host_ts)
@@ -480,6 +486,10 @@ def run_b200_arm(args, rank, local_rank, world):
         "kernels": kernels,
         "library_device_ms_per_step": lib_ms / args.steps,
     }
+    if stdout_fd is not None:
+        sys.stdout.flush()
+        os.dup2(stdout_fd, 1)
+        os.close(stdout_fd)
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

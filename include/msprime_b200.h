@@ -190,6 +190,26 @@ int mspb_generate_end(mspb_ctx_t *ctx, uint64_t site_base, uint64_t mutation_bas
     mspb_counts_t *counts);
 int mspb_shift_offsets(mspb_ctx_t *ctx, uint64_t ancestral_state_base, uint64_t site_metadata_base,
     uint64_t derived_state_base, uint64_t mutation_metadata_base);
+/* The same exchange without host round trips (the two small
+ * all-gathers): the counts stay on the device.  `send` (MSPB_EXCHANGE_WORDS uint64) and
+ * `recv` (world x MSPB_EXCHANGE_WORDS uint64, rank-major) are device buffers owned by the
+ * context; the caller all-gathers send -> recv on the context's stream (NCCL through
+ * torch.distributed, or a device copy) where marked:
+ *     mspb_generate_begin; mspb_exchange_post_counts;      <all-gather>
+ *     mspb_generate_end_device;                             <all-gather>
+ *     mspb_generate_finish_device                           (the only wait)
+ * _end_device derives the slice's site / mutation / allele-number bases from recv on the
+ * device and writes the tables with them; _finish_device shifts the byte offsets the same
+ * way and returns this rank's counts, the global totals[8] and this rank's bases[8], both
+ * ordered (sites, mutations, allele numbers used, new mutations, ancestral-state bytes,
+ * site-metadata bytes, derived-state bytes, mutation-metadata bytes). */
+#define MSPB_EXCHANGE_WORDS 8
+#define MSPB_EXCHANGE_MAX_WORLD 64
+int mspb_exchange_buffers(mspb_ctx_t *ctx, void **send, void **recv);
+int mspb_exchange_post_counts(mspb_ctx_t *ctx);
+int mspb_generate_end_device(mspb_ctx_t *ctx, uint32_t rank, uint32_t world);
+int mspb_generate_finish_device(mspb_ctx_t *ctx, uint32_t rank, uint32_t world, mspb_counts_t *counts,
+    uint64_t *totals, uint64_t *bases);
 /* Copies the resident result to host buffers. */
 int mspb_fetch(mspb_ctx_t *ctx, const mspb_columns_t *host_columns);
 /* Device pointers of the resident result (valid until the next mspb_generate). */

@@ -103,7 +103,22 @@ EXPORTED_SYMBOLS = [
     "mspb_sim_mutations", "mspb_columns_free", "mspb_strerror", "mspb_version",
     "mspb_ctx_stream", "mspb_kernel_timing", "mspb_kernel_time", "mspb_selftest_sort",
     "mspb_generate_begin", "mspb_generate_end", "mspb_shift_offsets",
+    "mspb_exchange_buffers", "mspb_exchange_post_counts", "mspb_generate_end_device",
+    "mspb_generate_finish_device",
 ]
+
+EXCHANGE_WORDS = 8  # MSPB_EXCHANGE_WORDS
+EXCHANGE_MAX_WORLD = 64  # MSPB_EXCHANGE_MAX_WORLD
+EXCHANGE_FIELDS = ("num_sites", "num_mutations", "alleles_used", "num_new_mutations", "ancestral_state_bytes",
+                   "site_metadata_bytes", "derived_state_bytes", "mutation_metadata_bytes")
+
+
+class _DeviceArray:
+    """A device buffer of this library seen through ``__cuda_array_interface__`` (zero copy)."""
+
+    def __init__(self, ptr, n, typestr="<i8"):
+        self.__cuda_array_interface__ = {
+            "shape": (int(n),), "typestr": typestr, "data": (int(ptr), False), "version": 2, "strides": None}
 
 _lib = None
 
@@ -125,6 +140,11 @@ def lib():
         L.mspb_generate_begin.argtypes = [C.c_void_p, C.POINTER(_Params), C.POINTER(_Counts)]
         L.mspb_generate_end.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64, C.POINTER(_Counts)]
         L.mspb_shift_offsets.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64]
+        L.mspb_exchange_buffers.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]
+        L.mspb_exchange_post_counts.argtypes = [C.c_void_p]
+        L.mspb_generate_end_device.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32]
+        L.mspb_generate_finish_device.argtypes = [
+            C.c_void_p, C.c_uint32, C.c_uint32, C.POINTER(_Counts), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
         L.mspb_fetch.argtypes = [C.c_void_p, C.POINTER(_Columns)]
         L.mspb_device_columns.argtypes = [C.c_void_p, C.POINTER(_Columns)]
         L.mspb_kernel_launches.argtypes = [C.c_void_p]
@@ -289,6 +309,37 @@ class Context:
                                       int(allele_base) & 0xFFFFFFFFFFFFFFFF, C.byref(c)))
         self.counts = {name: getattr(c, name) for name, _ in _Counts._fields_}
         return self.counts
+
+    def exchange_tensors(self, world):
+        """(send, recv) of the device-side exchange as int64 torch tensors on this context's
+        device: ``send`` has EXCHANGE_WORDS entries, ``recv`` has ``world`` times as many."""
+        import torch
+
+        if not 0 < world <= EXCHANGE_MAX_WORLD:
+            raise ValueError("world size out of range")
+        send, recv = C.c_void_p(), C.c_void_p()
+        check(lib().mspb_exchange_buffers(self._h, C.byref(send), C.byref(recv)))
+        dev = torch.device("cuda", self.device)
+        return (torch.as_tensor(_DeviceArray(send.value, EXCHANGE_WORDS), device=dev),
+                torch.as_tensor(_DeviceArray(recv.value, EXCHANGE_WORDS * world), device=dev))
+
+    def exchange_post_counts(self):
+        check(lib().mspb_exchange_post_counts(self._h))
+
+    def generate_end_device(self, rank, world):
+        """Second phase with the bases taken from the gathered counts on the device (no wait)."""
+        check(lib().mspb_generate_end_device(self._h, int(rank), int(world)))
+
+    def generate_finish_device(self, rank, world):
+        """Shifts the byte offsets by the gathered byte totals and waits.  Returns
+        ``(counts, totals, bases)``; the last two are dicts over EXCHANGE_FIELDS."""
+        c = _Counts()
+        tot = (C.c_uint64 * EXCHANGE_WORDS)()
+        bas = (C.c_uint64 * EXCHANGE_WORDS)()
+        check(lib().mspb_generate_finish_device(self._h, int(rank), int(world), C.byref(c), tot, bas))
+        self.counts = {name: getattr(c, name) for name, _ in _Counts._fields_}
+        return (self.counts, dict(zip(EXCHANGE_FIELDS, (int(v) for v in tot))),
+                dict(zip(EXCHANGE_FIELDS, (int(v) for v in bas))))
 
     def shift_offsets(self, ancestral_state=0, site_metadata=0, derived_state=0, mutation_metadata=0):
         check(lib().mspb_shift_offsets(self._h, int(ancestral_state), int(site_metadata), int(derived_state),

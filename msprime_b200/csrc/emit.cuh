@@ -188,6 +188,11 @@ __global__ void __launch_bounds__(SCAN_THREADS, 4) k5_emit_kernel(SortedView sv,
     if (*dense != 0u && sv.key.mode == KEY32_POS) {
         return;
     }
+    if (out.dev_bases != nullptr) {
+        out.site_base += (uint32_t) out.dev_bases[0];
+        out.mut_base += (uint32_t) out.dev_bases[1];
+        model.start_allele += out.dev_bases[2];
+    }
     const uint64_t base = (uint64_t) blockIdx.x * K5_TILE;
     const uint64_t last = sv.n - 1;
     // ---- all loads of the tile up front: slots and the site rows around every record

@@ -88,6 +88,10 @@ struct CallView {
     uint32_t stream; // Philox stream of a clipped slice (0 otherwise)
     uint64_t seed;
     int key_mode;
+    // clipped slices: K1 and K2 run over the edges that overlap the slice only
+    // (edge_list[0 .. num_work), ascending edge ids); otherwise over all num_work = E edges
+    const uint32_t *edge_list;
+    uint64_t num_work;
 };
 
 // keys of the records, before or after the sort
@@ -286,7 +290,7 @@ __global__ void __launch_bounds__(SCAN_THREADS, 4) k1_count_kernel(TreeSeqView t
     __shared__ uint16_t s_big[K1_TILE]; // edges whose mean needs the rejection sampler
     __shared__ uint32_t s_nbig;
     const uint64_t tile_base = (uint64_t) blockIdx.x * K1_TILE;
-    const uint64_t last = ts.num_edges - 1;
+    const uint64_t last = call.num_work - 1;
     const Philox ph(call.seed);
     if (threadIdx.x == 0) {
         s_nbig = 0;
@@ -295,13 +299,16 @@ __global__ void __launch_bounds__(SCAN_THREADS, 4) k1_count_kernel(TreeSeqView t
     // striped: consecutive threads take consecutive edges (coalesced column reads).  All
     // column loads of the thread's edges are issued first, then all node-time gathers.
     double mu[K1_ITEMS];
+    uint32_t eid[K1_ITEMS]; // edge ids of the thread's work items
     {
         double left[K1_ITEMS], right[K1_ITEMS], tc[K1_ITEMS], tp[K1_ITEMS];
         int32_t child[K1_ITEMS], parent[K1_ITEMS];
 #pragma unroll
         for (int k = 0; k < K1_ITEMS; k++) {
-            const uint64_t e = tile_base + (uint32_t) k * SCAN_THREADS + threadIdx.x;
-            const uint64_t ec = e < last ? e : last;
+            const uint64_t w = tile_base + (uint32_t) k * SCAN_THREADS + threadIdx.x;
+            const uint64_t wc = w < last ? w : last;
+            const uint64_t ec = call.edge_list != nullptr ? call.edge_list[wc] : wc;
+            eid[k] = (uint32_t) ec;
             left[k] = ts.edge_left[ec];
             right[k] = ts.edge_right[ec];
             child[k] = ts.edge_child[ec];
@@ -320,9 +327,9 @@ __global__ void __launch_bounds__(SCAN_THREADS, 4) k1_count_kernel(TreeSeqView t
         }
 #pragma unroll
         for (int k = 0; k < K1_ITEMS; k++) {
-            const uint64_t e = tile_base + (uint32_t) k * SCAN_THREADS + threadIdx.x;
+            const uint64_t w = tile_base + (uint32_t) k * SCAN_THREADS + threadIdx.x;
             mu[k] = 0.0;
-            if (e <= last && left[k] < right[k]) {
+            if (w <= last && left[k] < right[k]) {
                 const EdgeDraw d = edge_draw_from(map, call, left[k], right[k], child[k], tc[k], tp[k]);
                 mu[k] = (d.branch_end - d.branch_start) * d.mass;
             }
@@ -333,7 +340,7 @@ __global__ void __launch_bounds__(SCAN_THREADS, 4) k1_count_kernel(TreeSeqView t
 #pragma unroll
     for (int k = 0; k < K1_ITEMS; k++) {
         const uint32_t j = (uint32_t) k * SCAN_THREADS + threadIdx.x;
-        const uint64_t e = tile_base + j;
+        const uint64_t e = eid[k];
         uint64_t c = 0;
         if (mu[k] >= POISSON_SMALL_MU) {
             s_big[atomicAdd(&s_nbig, 1u)] = (uint16_t) j;
@@ -350,7 +357,7 @@ __global__ void __launch_bounds__(SCAN_THREADS, 4) k1_count_kernel(TreeSeqView t
     __syncthreads();
     for (uint32_t b = threadIdx.x; b < s_nbig; b += SCAN_THREADS) {
         const uint32_t j = s_big[b];
-        const uint64_t e = tile_base + j;
+        const uint64_t e = call.edge_list != nullptr ? call.edge_list[tile_base + j] : tile_base + j;
         const EdgeDraw d = edge_draw(ts, map, call, e);
         const double m = (d.branch_end - d.branch_start) * d.mass;
         PhiloxSeq rng(call.seed, e | ((uint64_t) call.stream << 32), TAG_COUNT);
@@ -380,12 +387,12 @@ __global__ void __launch_bounds__(SCAN_THREADS, 4) k1_count_kernel(TreeSeqView t
 #pragma unroll
     for (int k = 0; k < K1_ITEMS; k++) {
         const uint32_t j = (uint32_t) k * SCAN_THREADS + threadIdx.x;
-        const uint64_t e = tile_base + j;
-        if (e <= last) {
+        const uint64_t w = tile_base + j;
+        if (w <= last) {
             const uint64_t v = s_c[j];
-            goff[e] = (uint32_t) v;
+            goff[w] = (uint32_t) v;
             if (loff != nullptr) {
-                loff[e] = (uint32_t) (v >> 32);
+                loff[w] = (uint32_t) (v >> 32);
             }
         }
     }
@@ -436,6 +443,27 @@ MSPB_DEVFN uint32_t k1_offset(const uint32_t *__restrict__ local, const uint64_t
     return (e < E ? local[e] : 0u) + (uint32_t) (hi ? b >> 32 : b);
 }
 
+// ---------------------------------------------------------------- slice edge list
+// Edges overlapping [slice_left, slice_right), as an ascending list of edge ids (an index
+// over the loaded tables, rebuilt only when the slice changes).
+struct EdgeInSlice {
+    const double *left, *right;
+    double slice_left, slice_right;
+    MSPB_DEVFN uint32_t operator()(uint64_t e) const
+    {
+        return (left[e] < slice_right && right[e] > slice_left) ? 1u : 0u;
+    }
+};
+
+__global__ void __launch_bounds__(256) slice_edges_scatter_kernel(EdgeInSlice f, uint64_t num_edges,
+    const uint32_t *__restrict__ pos, uint32_t *__restrict__ list)
+{
+    const uint64_t e = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (e < num_edges && f(e) != 0u) {
+        list[pos[e]] = (uint32_t) e;
+    }
+}
+
 // ---------------------------------------------------------------- K2 (native)
 // One block per 256 edges: their draw parameters are staged in shared memory, then
 // each thread places one mutation (slot j of the tile's contiguous slot range), so
@@ -447,9 +475,10 @@ __global__ void __launch_bounds__(K2_EDGES) k2_place_kernel(TreeSeqView ts, Rate
     uint32_t base, Rec *__restrict__ rec, KeyView keys)
 {
     __shared__ EdgeDraw sd[K2_EDGES];
+    __shared__ uint32_t sid[K2_EDGES]; // edge ids (the Philox key of a placement)
     __shared__ uint32_t soff[K2_EDGES + 1];
     __shared__ uint32_t sm[9];
-    const uint64_t E = ts.num_edges;
+    const uint64_t E = call.num_work; // work items: all edges, or the slice's edge list
     const uint64_t ebase = (uint64_t) blockIdx.x * K2_EDGES;
     const uint64_t e = ebase + threadIdx.x;
     soff[threadIdx.x] = k1_offset(goff, tile_base, e < E ? e : E, E, false);
@@ -461,8 +490,12 @@ __global__ void __launch_bounds__(K2_EDGES) k2_place_kernel(TreeSeqView ts, Rate
     if (s0 == s1) {
         return;
     }
-    if (e < E && soff[threadIdx.x + 1] > soff[threadIdx.x]) {
-        sd[threadIdx.x] = edge_draw(ts, map, call, e);
+    if (e < E) {
+        const uint32_t id = call.edge_list != nullptr ? call.edge_list[e] : (uint32_t) e;
+        sid[threadIdx.x] = id;
+        if (soff[threadIdx.x + 1] > soff[threadIdx.x]) {
+            sd[threadIdx.x] = edge_draw(ts, map, call, id);
+        }
     }
     __syncthreads();
     const Philox ph(call.seed);
@@ -484,7 +517,7 @@ __global__ void __launch_bounds__(K2_EDGES) k2_place_kernel(TreeSeqView ts, Rate
                 }
             }
             const EdgeDraw &d = sd[lo];
-            place_one(ph, map, call, d, ebase + lo, j - soff[lo], &x, &t);
+            place_one(ph, map, call, d, sid[lo], j - soff[lo], &x, &t);
             child = d.child;
             in = !call.sliced || (x >= call.slice_left && x < call.slice_right);
         }
@@ -1156,6 +1189,9 @@ struct OutView {
     char *mut_md;
     void *mut_md_off;
     uint32_t site_base, mut_base; // added to site ids / parent ids (genome slices of a sharded call)
+    // sharded calls that exchange their counts on the device: site / mutation / allele-number
+    // bases are read from here (3 words) and added to the values above
+    const uint64_t *dev_bases;
     int off32; // offset columns are uint32 (else uint64)
     int write_md_off; // 0: the metadata offset columns are known to be all zero already
     MSPB_DEVFN void store_off(void *col, uint64_t row, uint64_t v) const

@@ -94,6 +94,14 @@ struct mspb_ctx {
     // work
     DBuf<uint32_t> goff, loff; // K1: offsets of each edge's mutations inside its K1 tile
     DBuf<uint64_t> k1_tiles; // K1: tile bases (count | in-slice count << 32), total appended
+    // edges overlapping the slice of the last clipped call (index over the loaded tables)
+    DBuf<uint32_t> slice_edges, slice_scan_tiles;
+    double slice_cached_left = 0, slice_cached_right = 0;
+    uint64_t slice_num_edges = 0;
+    bool slice_cache_valid = false;
+    // device-side exchange of a sharded call: send[8] | recv[MAX_WORLD][8] | bases1[16] | bases2[16]
+    DBuf<uint64_t> xchg;
+    uint64_t *xchg_host = nullptr; // pinned mirror of send[8] + bases1[16] + bases2[16]
     DBuf<Rec> rec;
     DBuf<uint64_t> keys0, keys1; // 64-bit keys (ping-pong)
     DBuf<uint32_t> k32_0, k32_1; // 32-bit keys (ping-pong)
@@ -117,6 +125,7 @@ struct mspb_ctx {
     // two-phase calls (multi-GPU): everything K5 needs, kept between _begin and _end
     struct {
         bool valid = false, defer = false;
+        int exchange_stage = 0; // 2: mspb_generate_end_device ran, mspb_generate_finish_device is due
         SortedView sv;
         ResolveView rv;
         KeptView kept;
@@ -294,7 +303,7 @@ extern "C" void mspb_ctx_destroy(mspb_ctx_t *ctx)
     REL(k_mut_site); REL(k_mut_node); REL(k_site_allele); REL(k_mut_allele);
     REL(map_pos); REL(map_rate); REL(map_cum); REL(model_root); REL(model_matrix); REL(replay);
     REL(model_alleles); REL(model_allele_off);
-    REL(goff); REL(loff); REL(k1_tiles); REL(rec); REL(keys0); REL(keys1); REL(k32_0); REL(k32_1); REL(vals0); REL(vals1);
+    REL(goff); REL(loff); REL(k1_tiles); REL(xchg); REL(slice_edges); REL(slice_scan_tiles); REL(rec); REL(keys0); REL(keys1); REL(k32_0); REL(k32_1); REL(vals0); REL(vals1);
     REL(tile_hist); REL(rs_scan_tiles); REL(or_and); REL(lb_state);
     REL(site_scan); REL(mut_scan); REL(draw_scan); REL(multi_list); REL(parent); REL(state); REL(site_state);
     REL(rp_edge); REL(rp_interval); REL(rp_count); REL(rp_out_off); REL(rp_stream_off); REL(dev_totals);
@@ -308,6 +317,9 @@ extern "C" void mspb_ctx_destroy(mspb_ctx_t *ctx)
     }
     if (ctx->or_and_host != nullptr) {
         cudaFreeHost(ctx->or_and_host);
+    }
+    if (ctx->xchg_host != nullptr) {
+        cudaFreeHost(ctx->xchg_host);
     }
     for (auto &e : ctx->ev) {
         if (e != nullptr) {
@@ -659,6 +671,7 @@ extern "C" int mspb_ctx_load_tables(mspb_ctx_t *ctx, const mspb_tables_t *t)
     CUDA_OK(cudaGetLastError());
     ctx->log.collect();
     ctx->tables_loaded = true;
+    ctx->slice_cache_valid = false;
     return 0;
 }
 
@@ -1126,6 +1139,36 @@ static int generate_impl(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t 
     call.stream = clipped ? p->slice_stream : 0u;
     call.seed = p->seed;
     call.key_mode = (discrete && ctx->L <= 4294967296.0 && !(keep && ctx->kept_fractional)) ? KEY32_POS : KEY64_POS;
+    call.edge_list = nullptr;
+    call.num_work = ctx->E;
+    if (clipped && ctx->E > 0) {
+        if (!ctx->slice_cache_valid || ctx->slice_cached_left != call.slice_left
+            || ctx->slice_cached_right != call.slice_right) {
+            EdgeInSlice f;
+            f.left = ts.edge_left;
+            f.right = ts.edge_right;
+            f.slice_left = call.slice_left;
+            f.slice_right = call.slice_right;
+            TRY(ctx->goff.ensure(ctx->E + 2));
+            TRY(ctx->slice_edges.ensure(ctx->E + 1));
+            TRY(ctx->slice_scan_tiles.ensure(scan_num_tiles(ctx->E) + 2));
+            uint32_t *total = ctx->slice_scan_tiles.p + scan_num_tiles(ctx->E) + 1;
+            device_exclusive_scan<uint32_t, EdgeInSlice>(
+                ctx->log, ctx->E, f, ctx->goff.p, ctx->slice_scan_tiles.p, total, st);
+            MSPB_LAUNCH(ctx->log, "slice_edges_scatter",
+                slice_edges_scatter_kernel<<<grid_for(ctx->E, 256), 256, 0, st>>>(
+                    f, ctx->E, ctx->goff.p, ctx->slice_edges.p));
+            uint32_t n_in = 0;
+            CUDA_OK(cudaMemcpyAsync(&n_in, total, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+            CUDA_OK(cudaStreamSynchronize(st));
+            ctx->slice_num_edges = n_in;
+            ctx->slice_cached_left = call.slice_left;
+            ctx->slice_cached_right = call.slice_right;
+            ctx->slice_cache_valid = true;
+        }
+        call.edge_list = ctx->slice_edges.p;
+        call.num_work = ctx->slice_num_edges;
+    }
     if (in_slice && S0 + M0 > 0) {
         // which kept rows this slice owns (read back with the K1 totals)
         const uint64_t mx = S0 > M0 ? S0 : M0;
@@ -1147,8 +1190,8 @@ static int generate_impl(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t 
         if (sliced) {
             TRY(ctx->loff.ensure(ctx->E + 2));
         }
-        if (ctx->E > 0) {
-            const uint32_t tiles = (uint32_t) ((ctx->E + K1_TILE - 1) / K1_TILE);
+        if (call.num_work > 0) {
+            const uint32_t tiles = (uint32_t) ((call.num_work + K1_TILE - 1) / K1_TILE);
             TRY(ctx->k1_tiles.ensure(tiles + 1));
             MSPB_LAUNCH(ctx->log, "k1_count",
                 k1_count_kernel<<<tiles, SCAN_THREADS, 0, st>>>(
@@ -1288,6 +1331,7 @@ static int generate_impl(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t 
     out.mut_md_off = ctx->o_mut_md_off.p;
     out.site_base = 0;
     out.mut_base = 0;
+    out.dev_bases = nullptr;
 
     // ---- K2: records (kept markers, kept mutations, new mutations) and their sort keys
     KeyView keys;
@@ -1301,7 +1345,7 @@ static int generate_impl(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t 
     if (Mnew > 0) {
         if (!replay) {
             MSPB_LAUNCH(ctx->log, "k2_place",
-                k2_place_kernel<<<grid_for(ctx->E, K2_EDGES), K2_EDGES, 0, st>>>(ts, map, call, ctx->goff.p,
+                k2_place_kernel<<<grid_for(call.num_work, K2_EDGES), K2_EDGES, 0, st>>>(ts, map, call, ctx->goff.p,
                     sliced ? ctx->loff.p : nullptr, ctx->k1_tiles.p, (uint32_t) (S0 + M0), ctx->rec.p, keys));
         } else {
             MSPB_LAUNCH(ctx->log, "replay_place",
@@ -1511,6 +1555,211 @@ extern "C" int mspb_shift_offsets(mspb_ctx_t *ctx, uint64_t ancestral_state_base
     CUDA_OK(cudaStreamSynchronize(st));
     CUDA_OK(cudaGetLastError());
     ctx->log.collect();
+    return 0;
+}
+
+// ---------------------------------------------------------------- device-side exchange
+// A sharded call whose counts never visit the host between its stages: the caller
+// all-gathers send -> recv on the context's stream (NCCL through torch.distributed, or any
+// device copy), K5 and the offset shift read their bases from device memory.
+namespace {
+constexpr uint64_t XCHG_WORDS = MSPB_EXCHANGE_WORDS, XCHG_MAX_WORLD = MSPB_EXCHANGE_MAX_WORLD;
+constexpr uint64_t XCHG_RECV = XCHG_WORDS, XCHG_B1 = XCHG_RECV + XCHG_MAX_WORLD * XCHG_WORDS,
+                   XCHG_B2 = XCHG_B1 + 2 * XCHG_WORDS, XCHG_TOTAL = XCHG_B2 + 2 * XCHG_WORDS;
+
+int ensure_exchange(mspb_ctx *ctx)
+{
+    if (ctx->xchg.p == nullptr) {
+        TRY(ctx->xchg.ensure(XCHG_TOTAL));
+        CUDA_OK(cudaMemsetAsync(ctx->xchg.p, 0, XCHG_TOTAL * sizeof(uint64_t), ctx->stream));
+    }
+    if (ctx->xchg_host == nullptr) {
+        CUDA_OK(cudaMallocHost((void **) &ctx->xchg_host, 5 * XCHG_WORDS * sizeof(uint64_t)));
+    }
+    return 0;
+}
+
+// bases[j] = sum over ranks below `rank` of recv[r][j]; bases[WORDS + j] = sum over all ranks
+__global__ void xchg_bases_kernel(const uint64_t *recv, uint32_t rank, uint32_t world, uint64_t *bases)
+{
+    const uint32_t j = threadIdx.x;
+    if (j < XCHG_WORDS) {
+        uint64_t ex = 0, tot = 0;
+        for (uint32_t r = 0; r < world; r++) {
+            const uint64_t v = recv[r * XCHG_WORDS + j];
+            ex += r < rank ? v : 0ull;
+            tot += v;
+        }
+        bases[j] = ex;
+        bases[XCHG_WORDS + j] = tot;
+    }
+}
+
+__global__ void xchg_pack_bytes_kernel(const HostTotals *dt, uint64_t *send)
+{
+    send[0] = dt->bytes.anc;
+    send[1] = dt->bytes.smd;
+    send[2] = dt->bytes.der;
+    send[3] = dt->bytes.mmd;
+    send[4] = send[5] = send[6] = send[7] = 0;
+}
+
+__global__ void shift_offsets_dev_kernel(void *col, uint64_t n, const uint64_t *delta, int off32)
+{
+    const uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    const uint64_t d = *delta;
+    if (i < n && d != 0) {
+        if (off32) {
+            static_cast<uint32_t *>(col)[i] += (uint32_t) d;
+        } else {
+            static_cast<uint64_t *>(col)[i] += d;
+        }
+    }
+}
+} // namespace
+
+extern "C" int mspb_exchange_buffers(mspb_ctx_t *ctx, void **send, void **recv)
+{
+    if (ctx == nullptr || send == nullptr || recv == nullptr) {
+        return MSPB_ERR_BAD_PARAM_VALUE;
+    }
+    CUDA_OK(cudaSetDevice(ctx->device));
+    TRY(ensure_exchange(ctx));
+    *send = ctx->xchg.p;
+    *recv = ctx->xchg.p + XCHG_RECV;
+    return 0;
+}
+
+/* after mspb_generate_begin: puts this rank's (sites, mutations, allele numbers used, new
+ * mutations) into the send buffer, on the stream */
+extern "C" int mspb_exchange_post_counts(mspb_ctx_t *ctx)
+{
+    if (ctx == nullptr) {
+        return MSPB_ERR_BAD_PARAM_VALUE;
+    }
+    if (!ctx->pending.valid) {
+        return MSPB_ERR_NOT_GENERATED;
+    }
+    CUDA_OK(cudaSetDevice(ctx->device));
+    TRY(ensure_exchange(ctx));
+    const mspb_counts_t &c = ctx->counts;
+    uint64_t *h = ctx->xchg_host;
+    memset(h, 0, XCHG_WORDS * sizeof(uint64_t));
+    h[0] = c.num_sites;
+    h[1] = c.num_mutations;
+    h[2] = c.next_allele - ctx->pending.start_allele;
+    h[3] = c.num_new_mutations;
+    CUDA_OK(cudaMemcpyAsync(ctx->xchg.p, h, XCHG_WORDS * sizeof(uint64_t), cudaMemcpyHostToDevice, ctx->stream));
+    return 0;
+}
+
+/* recv holds every rank's counts: bases on the device, K5 with them, byte totals into send.
+ * Nothing is awaited. */
+extern "C" int mspb_generate_end_device(mspb_ctx_t *ctx, uint32_t rank, uint32_t world)
+{
+    if (ctx == nullptr || world == 0 || world > XCHG_MAX_WORLD || rank >= world) {
+        return MSPB_ERR_BAD_PARAM_VALUE;
+    }
+    if (!ctx->pending.valid) {
+        return MSPB_ERR_NOT_GENERATED;
+    }
+    CUDA_OK(cudaSetDevice(ctx->device));
+    TRY(ensure_exchange(ctx));
+    cudaStream_t st = ctx->stream;
+    HostTotals *dt = (HostTotals *) ctx->dev_totals.p;
+    uint64_t *x = ctx->xchg.p;
+    ctx->pending.valid = false;
+    CUDA_OK(cudaEventRecord(ctx->ev[0], st));
+    MSPB_LAUNCH(ctx->log, "xchg_bases", xchg_bases_kernel<<<1, 32, 0, st>>>(x + XCHG_RECV, rank, world, x + XCHG_B1));
+    ctx->pending.out.site_base = 0;
+    ctx->pending.out.mut_base = 0;
+    ctx->pending.out.dev_bases = x + XCHG_B1;
+    ctx->pending.model.start_allele = ctx->pending.start_allele;
+    if (ctx->pending.R > 0) {
+        TRY(launch_emit(ctx));
+    }
+    ctx->pending.out.dev_bases = nullptr;
+    MSPB_LAUNCH(ctx->log, "xchg_pack_bytes", xchg_pack_bytes_kernel<<<1, 1, 0, st>>>(dt, x));
+    ctx->pending.exchange_stage = 2;
+    return 0;
+}
+
+/* recv holds every rank's byte totals: offsets shifted on the device, then the one wait
+ * of the exchange.  counts_out: this rank's counts (next_allele is the global one);
+ * totals_out[8]: global sites, mutations, allele numbers used, new mutations, ancestral /
+ * site-metadata / derived / mutation-metadata bytes; bases_out[8]: this rank's bases in
+ * the same order. */
+extern "C" int mspb_generate_finish_device(mspb_ctx_t *ctx, uint32_t rank, uint32_t world, mspb_counts_t *counts_out,
+    uint64_t *totals_out, uint64_t *bases_out)
+{
+    if (ctx == nullptr || world == 0 || world > XCHG_MAX_WORLD || rank >= world) {
+        return MSPB_ERR_BAD_PARAM_VALUE;
+    }
+    if (ctx->pending.exchange_stage != 2) {
+        return MSPB_ERR_NOT_GENERATED;
+    }
+    ctx->pending.exchange_stage = 0;
+    CUDA_OK(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    HostTotals *dt = (HostTotals *) ctx->dev_totals.p;
+    HostTotals *ht = ctx->host;
+    uint64_t *x = ctx->xchg.p;
+    mspb_counts_t &c = ctx->counts;
+    const int off32 = c.offset_bytes == 4;
+    const uint64_t S1 = c.num_sites + 1, M1 = c.num_mutations + 1;
+    MSPB_LAUNCH(ctx->log, "xchg_bases", xchg_bases_kernel<<<1, 32, 0, st>>>(x + XCHG_RECV, rank, world, x + XCHG_B2));
+    MSPB_LAUNCH(ctx->log, "shift_offsets",
+        shift_offsets_dev_kernel<<<grid_for(S1, 256), 256, 0, st>>>(ctx->o_site_anc_off.p, S1, x + XCHG_B2 + 0, off32));
+    MSPB_LAUNCH(ctx->log, "shift_offsets",
+        shift_offsets_dev_kernel<<<grid_for(M1, 256), 256, 0, st>>>(ctx->o_mut_der_off.p, M1, x + XCHG_B2 + 2, off32));
+    if (ctx->pending.out.write_md_off) {
+        MSPB_LAUNCH(ctx->log, "shift_offsets",
+            shift_offsets_dev_kernel<<<grid_for(S1, 256), 256, 0, st>>>(ctx->o_site_md_off.p, S1, x + XCHG_B2 + 1, off32));
+        MSPB_LAUNCH(ctx->log, "shift_offsets",
+            shift_offsets_dev_kernel<<<grid_for(M1, 256), 256, 0, st>>>(ctx->o_mut_md_off.p, M1, x + XCHG_B2 + 3, off32));
+        ctx->md_zero_site_bytes = ctx->md_zero_mut_bytes = 0;
+    }
+    uint64_t *h = ctx->xchg_host;
+    CUDA_OK(cudaMemcpyAsync(h + XCHG_WORDS, x + XCHG_B1, 4 * XCHG_WORDS * sizeof(uint64_t), cudaMemcpyDeviceToHost, st));
+    CUDA_OK(cudaMemcpyAsync(ht, dt, sizeof(HostTotals), cudaMemcpyDeviceToHost, st));
+    CUDA_OK(cudaEventRecord(ctx->ev[1], st));
+    CUDA_OK(cudaStreamSynchronize(st));
+    CUDA_OK(cudaGetLastError());
+    ctx->log.collect();
+    if (ht->err != 0) {
+        return ht->err;
+    }
+    const uint64_t *b1 = h + XCHG_WORDS, *t1 = b1 + XCHG_WORDS, *b2 = t1 + XCHG_WORDS, *t2 = b2 + XCHG_WORDS;
+    if (t1[0] > 0x7fffffffull || t1[1] > 0x7fffffffull) {
+        return MSPB_ERR_TOO_MANY_ROWS;
+    }
+    if (off32 && (t2[0] > 0xffffffffull || t2[1] > 0xffffffffull || t2[2] > 0xffffffffull || t2[3] > 0xffffffffull)) {
+        return MSPB_ERR_OFFSET_OVERFLOW;
+    }
+    float ms = 0;
+    cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]);
+    c.ancestral_state_bytes = ht->bytes.anc;
+    c.site_metadata_bytes = ht->bytes.smd;
+    c.derived_state_bytes = ht->bytes.der;
+    c.mutation_metadata_bytes = ht->bytes.mmd;
+    if (ctx->pending.model_kind == MSPB_MODEL_INFINITE_ALLELES) {
+        c.next_allele = ctx->pending.start_allele + t1[2];
+    }
+    c.device_ms += ms;
+    ctx->generated = true;
+    if (counts_out != nullptr) {
+        *counts_out = c;
+    }
+    for (int j = 0; j < 4; j++) {
+        if (totals_out != nullptr) {
+            totals_out[j] = t1[j];
+            totals_out[4 + j] = t2[j];
+        }
+        if (bases_out != nullptr) {
+            bases_out[j] = b1[j];
+            bases_out[4 + j] = b2[j];
+        }
+    }
     return 0;
 }
 

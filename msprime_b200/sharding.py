@@ -92,6 +92,48 @@ def run_slice(engine, params, *, rank, world, allgather, start_allele=0, fetch=T
     return local, info
 
 
+def nccl_device_allgather(ctx, world, group=None):
+    """``gather()`` for :func:`run_slice_device`: all-gathers the context's send buffer into
+    its recv buffer with NCCL, enqueued on the context's own stream (no host wait)."""
+    import torch
+    import torch.distributed as dist
+
+    send, recv = ctx.exchange_tensors(world)
+    stream = torch.cuda.ExternalStream(ctx.stream(), device=send.device)
+
+    def gather():
+        with torch.cuda.stream(stream):
+            dist.all_gather_into_tensor(recv, send, group=group)
+
+    return gather
+
+
+def run_slice_device(ctx, params, *, rank, world, gather, fetch=True, out=None):
+    """:func:`run_slice` with the exchange kept on the device: ``gather()`` must all-gather the
+    context's send buffer into its recv buffer on the context's stream (see
+    :func:`nccl_device_allgather`).  The host waits once, at the end, instead of after every
+    stage.  ``params.start_allele`` is the global allele counter before the call."""
+    ctx.generate_begin(params)
+    ctx.exchange_post_counts()
+    gather()
+    ctx.generate_end_device(rank, world)
+    gather()
+    _, totals, bases = ctx.generate_finish_device(rank, world)
+    local = None
+    if fetch:
+        local = ctx.fetch(out) if out is not None else ctx.fetch()
+    info = {
+        "num_sites": totals["num_sites"], "num_mutations": totals["num_mutations"],
+        "num_new_mutations": totals["num_new_mutations"], "next_allele": ctx.counts["next_allele"],
+        "ancestral_state_bytes": totals["ancestral_state_bytes"],
+        "site_metadata_bytes": totals["site_metadata_bytes"],
+        "derived_state_bytes": totals["derived_state_bytes"],
+        "mutation_metadata_bytes": totals["mutation_metadata_bytes"],
+        "site_base": bases["num_sites"], "mutation_base": bases["num_mutations"],
+    }
+    return local, info
+
+
 def merge_slices(results):
     """Concatenates the per-slice results (in slice order) into one result.  Offsets are already
     global: every slice but the last drops its closing offset entry."""

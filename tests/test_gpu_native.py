@@ -140,6 +140,68 @@ def test_union_of_slices_equals_whole(native_built, ts_small, world, model, keep
     assert sum(a[3] for a in all1) == cw["num_new_mutations"]
 
 
+@pytest.mark.parametrize("world", [2, 5])
+@pytest.mark.parametrize("model,keep", [("infinite_alleles", False), ("jc69", True), ("multichar", False)])
+def test_device_exchange_equals_whole(native_built, ts_small, world, model, keep):
+    """The exchange kept on the device (mspb_exchange_* / _end_device / _finish_device): every
+    rank is a context on this GPU and the all-gather is a device copy between their buffers."""
+    import torch
+
+    ts = ts_small
+    L = ts["sequence_length"]
+    mdl = cases.MODELS[model]
+    whole_ctx = _native.Context(0)
+    if keep:
+        first, _ = run(whole_ctx, ts, model=mdl, rate=5e-7, seed=31)
+        ts = cases.with_kept(ts, first)
+    start = 77 if model == "infinite_alleles" else 0
+    mdl = dict(mdl, start_allele=start) if model == "infinite_alleles" else mdl
+    whole, cw = run(whole_ctx, ts, model=mdl, rate=5e-7, keep=keep, seed=32)
+    whole_ctx.close()
+    cuts = sharding.slice_cuts(L, world)
+    ctxs = [_native.Context(0) for _ in range(world)]
+    try:
+        bufs = [c.exchange_tensors(world) for c in ctxs]
+
+        def gather_all():
+            # what NCCL does in a real run; here the ranks share the device, so wait and copy
+            torch.cuda.synchronize()
+            sends = torch.cat([b[0] for b in bufs])
+            for b in bufs:
+                b[1].copy_(sends)
+            torch.cuda.synchronize()
+
+        for r, c in enumerate(ctxs):
+            c.load_tables(ts)
+            c.generate_begin(_native.Params(
+                map_position=[0, L], map_rate=[5e-7], model=cases.native_model(mdl), discrete_genome=True,
+                keep=keep, start_time=-cases.FMAX, end_time=cases.FMAX, seed=32, slice_left=cuts[r],
+                slice_right=cuts[r + 1]))
+            c.exchange_post_counts()
+        gather_all()
+        for r, c in enumerate(ctxs):
+            c.generate_end_device(r, world)
+        gather_all()
+        parts, infos = [], []
+        for r, c in enumerate(ctxs):
+            counts, totals, bases = c.generate_finish_device(r, world)
+            infos.append((counts, totals, bases))
+            parts.append(c.fetch())
+        merged = sharding.merge_slices(parts)
+    finally:
+        for c in ctxs:
+            c.close()
+    for tbl in whole:
+        for col in whole[tbl]:
+            assert np.array_equal(np.asarray(whole[tbl][col]), np.asarray(merged[tbl][col])), (tbl, col)
+    counts, totals, bases = infos[-1]
+    assert totals["num_sites"] == cw["num_sites"] and totals["num_mutations"] == cw["num_mutations"]
+    assert totals["num_new_mutations"] == cw["num_new_mutations"]
+    assert totals["derived_state_bytes"] == cw["derived_state_bytes"]
+    assert counts["next_allele"] == cw["next_allele"]
+    assert bases["num_sites"] == sum(i[0]["num_sites"] for i in infos[:-1])
+
+
 def test_clipped_slices(native_built, ts_small):
     """slice_stream != 0: edges are cut to the slice and drawn on the slice's own stream."""
     ts = ts_small
