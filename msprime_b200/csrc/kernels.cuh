@@ -36,7 +36,8 @@ struct TreeSeqView {
     const double *edge_left, *edge_right;
     const int32_t *edge_parent, *edge_child;
     // child-sorted interval index (K0): the edges of child c are ci[child_start[c] .. child_start[c+1]),
-    // one 32-byte entry per edge so that a step of the parent walk costs one sector
+    // one 32-byte entry per edge; an entry also names the range of its parent's entries, so a
+    // step of the parent walk is a binary search of 32-byte entries and nothing else
     const uint32_t *child_start;
     const struct ChildIv *ci;
 };
@@ -44,9 +45,11 @@ struct TreeSeqView {
 struct __align__(32) ChildIv {
     double left, right;
     double parent_time;
-    int32_t parent;
-    int32_t pad;
+    // the parent, named by the range of its own entries [child_start[p], child_start[p + 1]);
+    // a parent that is a child nowhere is (CI_NONE, p).  The pair identifies the node.
+    uint32_t parent_start, parent_end;
 };
+constexpr uint32_t CI_NONE = 0xffffffffu;
 
 struct KeptView {
     uint64_t num_sites, num_mutations; // 0 when keep is off
@@ -160,12 +163,13 @@ __global__ void k0_permute_kernel(TreeSeqView ts, const uint32_t *perm, ChildIv 
         ChildIv iv;
         iv.left = ts.edge_left[e];
         iv.right = ts.edge_right[e];
-        iv.parent = ts.edge_parent[e];
-        iv.parent_time = ts.node_time[iv.parent];
-        iv.pad = 0;
+        const uint32_t c = (uint32_t) ts.edge_child[e];
+        const uint32_t p = (uint32_t) ts.edge_parent[e];
+        iv.parent_time = ts.node_time[p];
+        iv.parent_start = CI_NONE; // k0_link_kernel replaces the pair by the parent's range
+        iv.parent_end = p;
         ci[i] = iv;
         // CSR starts: child c begins at the first i whose child is >= c
-        const uint32_t c = (uint32_t) ts.edge_child[e];
         const uint32_t prev = i == 0 ? 0u : (uint32_t) ts.edge_child[perm[i - 1]] + 1u;
         for (uint32_t k = (i == 0 ? 0u : prev); k <= c; k++) {
             child_start[k] = (uint32_t) i;
@@ -178,11 +182,45 @@ __global__ void k0_permute_kernel(TreeSeqView ts, const uint32_t *perm, ChildIv 
     }
 }
 
-// parent of node u at position x in the local tree (or -1), and that parent's time
-MSPB_DEVFN int32_t parent_at(const TreeSeqView &ts, int32_t u, double x, double *parent_time)
+__global__ void k0_link_kernel(TreeSeqView ts, ChildIv *ci)
 {
-    uint32_t lo = ts.child_start[u], hi = ts.child_start[u + 1];
-    // the interval that contains x, if any (intervals of one child are disjoint and sorted)
+    const uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < ts.num_edges) {
+        const uint32_t p = ci[i].parent_end;
+        const uint32_t a = ts.child_start[p], b = ts.child_start[p + 1];
+        if (a < b) {
+            ci[i].parent_start = a;
+            ci[i].parent_end = b;
+        }
+    }
+}
+
+// a node as the parent walk names it: the range of its entries in the interval index
+struct WalkNode {
+    uint32_t start, end;
+    MSPB_DEVFN bool operator==(const WalkNode &o) const { return start == o.start && end == o.end; }
+};
+
+MSPB_DEVFN WalkNode walk_node(const TreeSeqView &ts, int32_t u)
+{
+    WalkNode w;
+    w.start = ts.child_start[u];
+    w.end = ts.child_start[u + 1];
+    if (w.start >= w.end) {
+        w.start = CI_NONE;
+        w.end = (uint32_t) u;
+    }
+    return w;
+}
+
+// Steps from node w to its parent at position x in the local tree: false when w is a root
+// there.  Intervals of one child are disjoint and sorted.
+MSPB_DEVFN bool parent_at(const TreeSeqView &ts, WalkNode *w, double x, double *time)
+{
+    if (w->start == CI_NONE) {
+        return false;
+    }
+    uint32_t lo = w->start, hi = w->end;
     while (lo < hi) {
         const uint32_t mid = (lo + hi) >> 1;
         const ChildIv iv = ts.ci[mid];
@@ -191,11 +229,13 @@ MSPB_DEVFN int32_t parent_at(const TreeSeqView &ts, int32_t u, double x, double 
         } else if (x >= iv.right) {
             lo = mid + 1;
         } else {
-            *parent_time = iv.parent_time;
-            return iv.parent;
+            *time = iv.parent_time;
+            w->start = iv.parent_start;
+            w->end = iv.parent_end;
+            return true;
         }
     }
-    return -1;
+    return false;
 }
 
 
@@ -407,9 +447,22 @@ __global__ void __launch_bounds__(1024) k1_spine_kernel(uint64_t *tile_tot, uint
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t per = (num_tiles + 1023u) / 1024u;
     const uint32_t lo = threadIdx.x * per, hi = lo + per < num_tiles ? lo + per : num_tiles;
+    // (a thread's few tiles are loaded together: up to 16 independent loads in flight)
+    uint64_t mine[16];
     uint64_t sum = 0;
-    for (uint32_t i = lo; i < hi; i++) {
-        sum += tile_tot[i];
+    if (per <= 16) {
+#pragma unroll
+        for (uint32_t q = 0; q < 16; q++) {
+            mine[q] = lo + q < hi ? tile_tot[lo + q] : 0ull;
+        }
+#pragma unroll
+        for (uint32_t q = 0; q < 16; q++) {
+            sum += mine[q];
+        }
+    } else {
+        for (uint32_t i = lo; i < hi; i++) {
+            sum += tile_tot[i];
+        }
     }
     const uint64_t inc = warp_inclusive_scan(sum);
     if (lane == 31) {
@@ -422,10 +475,20 @@ __global__ void __launch_bounds__(1024) k1_spine_kernel(uint64_t *tile_tot, uint
     }
     __syncthreads();
     uint64_t run = warp_sum[warp] + inc - sum;
-    for (uint32_t i = lo; i < hi; i++) {
-        const uint64_t v = tile_tot[i];
-        tile_tot[i] = run;
-        run += v;
+    if (per <= 16) {
+#pragma unroll
+        for (uint32_t q = 0; q < 16; q++) {
+            if (lo + q < hi) {
+                tile_tot[lo + q] = run;
+            }
+            run += mine[q];
+        }
+    } else {
+        for (uint32_t i = lo; i < hi; i++) {
+            const uint64_t v = tile_tot[i];
+            tile_tot[i] = run;
+            run += v;
+        }
     }
     if (threadIdx.x == 1023) {
         tile_tot[num_tiles] = run;
@@ -1067,6 +1130,12 @@ MSPB_DEVFN void resolve_site(const TreeSeqView &ts, const KeptView &kept, const 
     // draws (matrix: uniforms; infinite alleles: allele numbers) before record j, redone
     // here because the reordering above may have interleaved kept and new mutations
     uint32_t cur = draw0;
+    constexpr int SEEN = 8; // nodes of the site's first records stay in registers
+    WalkNode seen[SEEN];
+#pragma unroll
+    for (int t = 0; t < SEEN; t++) {
+        seen[t].start = seen[t].end = CI_NONE;
+    }
     for (uint64_t j = first; j < end; j++) {
         const uint32_t r = sv.val[j];
         const bool is_new = !sv.has_kept || r >= KM;
@@ -1077,27 +1146,42 @@ MSPB_DEVFN void resolve_site(const TreeSeqView &ts, const KeptView &kept, const 
         const int32_t node = sv.rec[r].node;
         int32_t par = -1;
         const double node_t = ts.node_time[node];
+        const WalkNode self = walk_node(ts, node);
+#pragma unroll
+        for (int t = 0; t < SEEN; t++) {
+            if ((uint64_t) t == j - first) {
+                seen[t] = self;
+            }
+        }
         if (j > first) {
-            int32_t u = node;
+            WalkNode u = self;
             double tu = node_t;
+            bool at_self = true;
             // A strict ancestor of `node` is older than this mutation, so once the walk has left
             // `node` it can only meet earlier mutations whose node is older than this mutation.
             // (New mutations only: a kept mutation's time is not checked against its parent node.)
             const double mut_t = is_new ? sv.rec[r].time : -INFINITY;
-            while (u != -1) {
-                if (tu > tmax || (u != node && tmax <= mut_t)) {
+            for (;;) {
+                if (tu > tmax || (!at_self && tmax <= mut_t)) {
                     break;
                 }
-                for (uint64_t q = j; q-- > first;) {
-                    if (sv.rec[sv.val[q]].node == u) {
+                // the latest earlier record on node u
+#pragma unroll
+                for (int t = 0; t < SEEN; t++) {
+                    if ((uint64_t) t < j - first && seen[t] == u) {
+                        par = (int32_t) (first + t);
+                    }
+                }
+                for (uint64_t q = j; q-- > first + SEEN;) {
+                    if (walk_node(ts, sv.rec[sv.val[q]].node) == u) {
                         par = (int32_t) q;
                         break;
                     }
                 }
-                if (par >= 0) {
+                if (par >= 0 || !parent_at(ts, &u, x, &tu)) {
                     break;
                 }
-                u = parent_at(ts, u, x, &tu);
+                at_self = false;
             }
         }
         rv.parent[j] = par;

@@ -666,6 +666,7 @@ extern "C" int mspb_ctx_load_tables(mspb_ctx_t *ctx, const mspb_tables_t *t)
         cur = device_radix_sort<uint64_t>(sb, ctx->E, 0, false, st, ctx->log, nullptr);
         MSPB_LAUNCH(ctx->log, "k0_permute", k0_permute_kernel<<<grid_for(ctx->E, 256), 256, 0, st>>>(
             ts, sb.vals[cur], ctx->ci.p, ctx->child_start.p));
+        MSPB_LAUNCH(ctx->log, "k0_link", k0_link_kernel<<<grid_for(ctx->E, 256), 256, 0, st>>>(ts, ctx->ci.p));
     }
     CUDA_OK(cudaStreamSynchronize(st));
     CUDA_OK(cudaGetLastError());

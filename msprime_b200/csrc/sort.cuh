@@ -265,11 +265,47 @@ __global__ void __launch_bounds__(RS_THREADS) rs_global_hist_kernel(const KeyT *
         sh[i] = 0;
     }
     __syncthreads();
+    // 16-byte loads, two in flight per thread; the tail (n not a multiple of PER) goes key by key
+    constexpr int PER = 16 / (int) sizeof(KeyT);
+    const uint64_t nvec = n / PER;
+    const uint4 *vec = reinterpret_cast<const uint4 *>(keys);
     const uint64_t stride = (uint64_t) gridDim.x * RS_THREADS;
-    for (uint64_t i = (uint64_t) blockIdx.x * RS_THREADS + threadIdx.x; i < n; i += stride) {
-        const KeyT k = keys[i];
+    for (uint64_t v = (uint64_t) blockIdx.x * RS_THREADS + threadIdx.x; v < nvec; v += 2 * stride) {
+        const bool two = v + stride < nvec;
+        const uint4 a = vec[v];
+        const uint4 b = two ? vec[v + stride] : make_uint4(0u, 0u, 0u, 0u);
+        KeyT k[2 * PER];
+        if (sizeof(KeyT) == 4) {
+            k[0] = (KeyT) a.x, k[1] = (KeyT) a.y, k[2] = (KeyT) a.z, k[3] = (KeyT) a.w;
+            k[4] = (KeyT) b.x, k[5] = (KeyT) b.y, k[6] = (KeyT) b.z, k[7] = (KeyT) b.w;
+        } else {
+            k[0] = (KeyT) ((uint64_t) a.x | ((uint64_t) a.y << 32));
+            k[1] = (KeyT) ((uint64_t) a.z | ((uint64_t) a.w << 32));
+            k[2] = (KeyT) ((uint64_t) b.x | ((uint64_t) b.y << 32));
+            k[3] = (KeyT) ((uint64_t) b.z | ((uint64_t) b.w << 32));
+        }
         for (int p = 0; p < plan.passes; p++) {
-            atomicAdd(&sh[p * RS_BINS + rs_digit(k, plan.shift[p], plan.mask[p])], 1u);
+            const int sft = plan.shift[p];
+            const uint32_t msk = plan.mask[p];
+            uint32_t *h = sh + p * RS_BINS;
+#pragma unroll
+            for (int q = 0; q < PER; q++) {
+                atomicAdd(&h[rs_digit(k[q], sft, msk)], 1u);
+            }
+            if (two) {
+#pragma unroll
+                for (int q = PER; q < 2 * PER; q++) {
+                    atomicAdd(&h[rs_digit(k[q], sft, msk)], 1u);
+                }
+            }
+        }
+    }
+    if (blockIdx.x == 0) {
+        for (uint64_t i = nvec * PER + threadIdx.x; i < n; i += RS_THREADS) {
+            const KeyT k = keys[i];
+            for (int p = 0; p < plan.passes; p++) {
+                atomicAdd(&sh[p * RS_BINS + rs_digit(k, plan.shift[p], plan.mask[p])], 1u);
+            }
         }
     }
     __syncthreads();
