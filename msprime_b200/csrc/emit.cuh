@@ -16,6 +16,9 @@ namespace mspb {
 constexpr int K5_ITEMS = 4;
 constexpr int K5_TILE = SCAN_THREADS * K5_ITEMS;
 constexpr int K5_STAGE = 12 * 1024; // bytes of one ragged column staged per tile
+// 8 worker warps + 1 warp that only chains the tile's byte counts to the earlier tiles'
+// (decoupled look-back), so that no worker ever waits for the chain before the very end
+constexpr int K5_THREADS = SCAN_THREADS + 32;
 
 constexpr uint32_t EM_HEAD = 1u, EM_MUT = 2u, EM_NEW = 4u, EM_SINGLE = 8u;
 
@@ -173,12 +176,12 @@ struct Bytes4 {
 
 // MODEL: 0 matrix, 1 infinite alleles.  KEPT: kept site / mutation rows are present.
 template <int MODEL, bool KEPT, bool OFF32>
-__global__ void __launch_bounds__(SCAN_THREADS, 4) k5_emit_kernel(SortedView sv, ResolveView rv, KeptView kept,
+__global__ void __launch_bounds__(K5_THREADS, 4) k5_emit_kernel(SortedView sv, ResolveView rv, KeptView kept,
     ModelView model, CallView call, OutView out, LbWord *lb, uint32_t num_tiles, const Counts3 *p1_total,
     Bytes4 *total, const uint32_t *dense, int *err)
 {
     __shared__ uint64_t sm[9];
-    __shared__ LbVal<2, true> bcast;
+    __shared__ LbVal<2, true> bcast, s_agg;
     __shared__ __align__(16) uint32_t s_der[K5_TILE];
     __shared__ __align__(16) uint32_t s_anc[K5_TILE];
     __shared__ __align__(16) uint32_t s_mmd[KEPT ? K5_TILE : 4];
@@ -192,6 +195,27 @@ __global__ void __launch_bounds__(SCAN_THREADS, 4) k5_emit_kernel(SortedView sv,
         out.site_base += (uint32_t) out.dev_bases[0];
         out.mut_base += (uint32_t) out.dev_bases[1];
         model.start_allele += out.dev_bases[2];
+    }
+    if (threadIdx.x >= SCAN_THREADS) {
+        // ---- the look-back warp: meets the workers at their barriers, otherwise only chains
+        __syncthreads(); // lengths are in shared memory
+        for (int b = 0; b < (KEPT ? 12 : 3); b++) {
+            __syncthreads(); // the barriers of the tile scans
+        }
+        __syncthreads(); // offsets and the tile's totals are visible
+        const LbVal<2, true> aw = s_agg;
+        const LbVal<2, true> pw = lookback_warp<2, true>(lb, blockIdx.x, aw);
+        if (threadIdx.x == SCAN_THREADS) {
+            bcast = pw;
+        }
+        const uint64_t der = (uint64_t) aw.w[0][0] | ((uint64_t) aw.w[0][1] << 32);
+        const uint64_t anc = (uint64_t) aw.w[1][0] | ((uint64_t) aw.w[1][1] << 32);
+        const bool no_md = (aw.w[0][2] | aw.w[0][3] | aw.w[1][2] | aw.w[1][3]) == 0u;
+        if (KEPT && !(der <= K5_STAGE && anc <= K5_STAGE && no_md)) {
+            __syncthreads(); // unstaged tiles: the workers wait for the prefix before writing
+        }
+        __syncthreads(); // rows and bytes are done
+        return;
     }
     const uint64_t base = (uint64_t) blockIdx.x * K5_TILE;
     const uint64_t last = sv.n - 1;
@@ -306,7 +330,6 @@ __global__ void __launch_bounds__(SCAN_THREADS, 4) k5_emit_kernel(SortedView sv,
     } else {
         tile_offsets_pair(s_der, s_anc, sm, &agg.der, &agg.anc);
     }
-    __syncthreads(); // the offsets are read striped below, by other threads than wrote them
     LbVal<2, true> aw; // half 0: derived, mutation metadata; half 1: ancestral, site metadata
     aw.w[0][0] = (uint32_t) agg.der;
     aw.w[0][1] = (uint32_t) (agg.der >> 32);
@@ -316,22 +339,22 @@ __global__ void __launch_bounds__(SCAN_THREADS, 4) k5_emit_kernel(SortedView sv,
     aw.w[1][1] = (uint32_t) (agg.anc >> 32);
     aw.w[1][2] = (uint32_t) agg.smd;
     aw.w[1][3] = (uint32_t) (agg.smd >> 32);
+    if (threadIdx.x == 0) {
+        s_agg = aw;
+    }
+    __syncthreads(); // offsets are read striped below, by other threads than wrote them; totals out
     // ---- offsets across tiles.  When the tile's state bytes fit the stage (always, unless
     // kept rows carry long strings) nothing below needs the prefix until the very end:
-    // warp 0 looks back while the other warps write rows and assemble bytes.
+    // the look-back warp chains the tiles while the workers write rows and assemble bytes.
     const bool staged = !KEPT || (agg.der <= K5_STAGE && agg.anc <= K5_STAGE && agg.mmd == 0 && agg.smd == 0);
     Bytes4 pre = Bytes4();
     if (!staged) {
-        const LbVal<2, true> pw = lookback_prefix<2, true>(lb, blockIdx.x, aw, &bcast);
+        __syncthreads(); // (the look-back warp has the prefix)
+        const LbVal<2, true> pw = bcast;
         pre.der = (uint64_t) pw.w[0][0] | ((uint64_t) pw.w[0][1] << 32);
         pre.mmd = (uint64_t) pw.w[0][2] | ((uint64_t) pw.w[0][3] << 32);
         pre.anc = (uint64_t) pw.w[1][0] | ((uint64_t) pw.w[1][1] << 32);
         pre.smd = (uint64_t) pw.w[1][2] | ((uint64_t) pw.w[1][3] << 32);
-    } else if (threadIdx.x < 32) {
-        const LbVal<2, true> pw = lookback_warp<2, true>(lb, blockIdx.x, aw);
-        if (threadIdx.x == 0) {
-            bcast = pw;
-        }
     }
     char *der_base = staged ? st_der : out.mut_der + pre.der;
     char *anc_base = staged ? st_anc : out.site_anc + pre.anc;

@@ -949,7 +949,7 @@ int launch_emit(mspb_ctx *ctx)
     const int model_kind = ctx->pending.model.kind != 0 ? 1 : 0;
 #define MSPB_K5(M, K, O)                                                                                             \
     MSPB_LAUNCH(ctx->log, "k5_emit",                                                                                 \
-        (k5_emit_kernel<M, K, O><<<k5_tiles, SCAN_THREADS, 0, st>>>(ctx->pending.sv, ctx->pending.rv,                \
+        (k5_emit_kernel<M, K, O><<<k5_tiles, K5_THREADS, 0, st>>>(ctx->pending.sv, ctx->pending.rv,                \
             ctx->pending.kept, ctx->pending.model, ctx->pending.call, ctx->pending.out, lb4, k5_tiles, &dt->p1,      \
             &dt->bytes, &dt->dense, &dt->err)))
 #define MSPB_K5_MODEL(M)                                                                                             \

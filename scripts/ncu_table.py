@@ -16,6 +16,23 @@ def main():
     def g(r, name, default=""):
         return r[hdr.index(name)] if name in hdr else default
 
+    if len(sys.argv) > 3 and sys.argv[2] == "--traffic":
+        # {"workload": ..., "kernels": {short name: mean dram bytes (read + write) per launch}}
+        import json
+        import re
+
+        unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+        acc = {}
+        for r in rows[2:]:
+            name = re.sub(r"<.*", "", g(r, "Kernel Name").split("(")[0].replace("void ", "")).replace("_kernel", "")
+            tot = 0.0
+            for col in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+                tot += float(g(r, col)) * unit[rows[1][hdr.index(col)]]
+            acc.setdefault(name, []).append(tot)
+        out = {"workload": sys.argv[3], "source": sys.argv[1].split("/")[-1],
+               "kernels": {k: round(sum(v) / len(v)) for k, v in acc.items()}}
+        print(json.dumps(out, indent=1))
+        return
     pipes = [h for h in hdr if h.startswith("sm__inst_executed_pipe_") and h.endswith(".avg.pct_of_peak_sustained_active")]
     print("kernel | us | regs | warps% | dram rd MB | dram wr MB | dram% | L2% | issue% | top pipe | warp inst M")
     for r in rows[2:]:
