@@ -47,9 +47,14 @@ WORKLOADS = {
     "config5": dict(samples=1_000_000, L=2.5e8, recomb=1e-8, ne=1e4, ts_seed=1, rate=1e-7,
                     model="infinite_alleles", discrete=True,
                     text="config5: InfiniteAlleles rate=1e-7 discrete keep=False, 1e6 diploid samples x 2.5e8 bp"),
-    # smaller cases for quick checks (not bench lines)
-    "config3": dict(samples=100_000, L=1e8, recomb=1e-8, ne=1e4, ts_seed=1, rate=1e-8, model="jc69",
-                    discrete=True, text="1e5 samples x 1e8 bp, JC69 rate=1e-8"),
+    # the other BASELINE.json configs: parity-test cases, timed once for BASELINE.md (not bench lines)
+    "config1": dict(samples=1_000, L=1e6, recomb=1e-8, ne=1e4, ts_seed=1, rate=1e-8, model="jc69",
+                    discrete=True, text="config1: JC69 rate=1e-8 discrete, 1e3 diploid samples x 1e6 bp"),
+    "config2": dict(samples=10_000, L=1e7, recomb=1e-8, ne=1e4, ts_seed=1, rate=1e-8, model="binary",
+                    discrete=False, text="config2: Binary rate=1e-8 continuous genome, 1e4 diploid samples x 1e7 bp"),
+    "config3": dict(samples=100_000, L=1e8, recomb=1e-8, ne=1e4, ts_seed=1, rate=1e-8, model="gtr",
+                    discrete=True, ratemap=1000,
+                    text="config3: GTR, 1000-interval lognormal RateMap around 1e-8, 1e5 diploid samples x 1e8 bp"),
     "small": dict(samples=2_000, L=2e6, recomb=1e-8, ne=1e4, ts_seed=1, rate=1e-7, model="infinite_alleles",
                   discrete=True, text="small: 2e3 samples x 2e6 bp, InfiniteAlleles rate=1e-7"),
 }
@@ -76,7 +81,31 @@ def oracle_model(name):
         m = (np.full((4, 4), 1 / 3) - np.eye(4) / 3).tolist()
         return {"kind": "matrix", "alleles": ["A", "C", "G", "T"], "root_distribution": [0.25] * 4,
                 "transition_matrix": m}
+    if name in ("binary", "gtr"):
+        # the host mirror's matrix builders (msprime/mutations.py:179-201, 763-850); BASELINE.md
+        # fixes the GTR parameters that BASELINE.json leaves open
+        from msprime_b200 import mutations
+
+        mm = (mutations.BinaryMutationModel() if name == "binary" else
+              mutations.GTR(relative_rates=[1, 2, 1, 1, 2, 1], equilibrium_frequencies=[0.3, 0.2, 0.2, 0.3]))
+        return {"kind": "matrix", "alleles": list(mm.alleles), "root_distribution": [float(x) for x in mm.root_distribution],
+                "transition_matrix": np.asarray(mm.transition_matrix).tolist()}
     raise ValueError(name)
+
+
+def rate_map(w, L):
+    """(positions, rates) of the workload's mutation rate map over [0, L)."""
+    n = w.get("ratemap")
+    if not n:
+        return [0.0, float(L)], [w["rate"]]
+    full = float(w["L"])
+    pos = np.linspace(0, full, n + 1)
+    rate = np.random.default_rng(3).lognormal(np.log(w["rate"]), 1.0, n)
+    if L < full:  # a genome prefix of the workload (CPU sample)
+        k = int(np.searchsorted(pos, L, side="left"))
+        pos = np.concatenate([pos[:k], [L]])
+        rate = rate[:k]
+    return pos.tolist(), rate.tolist()
 
 
 def native_model(name):
@@ -111,16 +140,16 @@ def _cpu_worker(seed):
 
     j = _CPU_JOB
     t0 = time.perf_counter()
-    r = oracle.sim_mutations(j["ts"], which=j["which"], map_position=[0, j["ts"]["sequence_length"]],
-                             map_rate=[j["rate"]], model=oracle_model(j["model"]), discrete_genome=j["discrete"],
-                             keep=False, seed=seed)
+    mp_, mr_ = rate_map(j["w"], j["ts"]["sequence_length"])
+    r = oracle.sim_mutations(j["ts"], which=j["which"], map_position=mp_, map_rate=mr_,
+                             model=oracle_model(j["model"]), discrete_genome=j["discrete"], keep=False, seed=seed)
     return len(r["mutations"]["site"]), r["seconds"], time.perf_counter() - t0
 
 
 def cpu_reference_pass(ts, w, cores, seed0, which):
     """One pass: ``cores`` independent processes, each overlaying the sample with its own
     seed (the reference is single-threaded, so this is how it uses a whole host)."""
-    _CPU_JOB.update(ts=ts, which=which, rate=w["rate"], model=w["model"], discrete=w["discrete"])
+    _CPU_JOB.update(ts=ts, which=which, w=w, model=w["model"], discrete=w["discrete"])
     t0 = time.perf_counter()
     if cores == 1:
         res = [_cpu_worker(seed0)]
@@ -323,8 +352,10 @@ def run_b200_arm(args, rank, local_rank, world):
     ctx = _native.Context(local_rank)
     stream = torch.cuda.ExternalStream(ctx.stream(), device=torch.device("cuda", local_rank))
 
+    map_pos, map_rate = rate_map(w, L)
+
     def params(step):
-        return _native.Params(map_position=[0, L], map_rate=[w["rate"]], model=native_model(w["model"]),
+        return _native.Params(map_position=map_pos, map_rate=map_rate, model=native_model(w["model"]),
                               discrete_genome=w["discrete"], keep=False, start_time=-FMAX, end_time=FMAX,
                               seed=1000 + step, slice_left=sl, slice_right=sr, offsets32=True,
                               slice_stream=0 if world == 1 else rank + 1)

@@ -1071,7 +1071,7 @@ MSPB_DEVFN void allele_uniforms(const Philox &ph, uint32_t stream, uint32_t ord,
 MSPB_DEVFN void resolve_site(const TreeSeqView &ts, const KeptView &kept, const ModelView &model, const CallView &call,
     const SortedView &sv, const ResolveView &rv, uint64_t i, int *err);
 
-__global__ void __launch_bounds__(128) k4_resolve_kernel(TreeSeqView ts, KeptView kept, ModelView model, CallView call,
+__global__ void __launch_bounds__(128, 12) k4_resolve_kernel(TreeSeqView ts, KeptView kept, ModelView model, CallView call,
     SortedView sv, ResolveView rv, const uint32_t *__restrict__ multi_list, const Counts3 *p1_total,
     const uint32_t *dense, int *err)
 {

@@ -463,17 +463,28 @@ MSPB_DEVFN void rs_onesweep_tile(const KeyT *__restrict__ keys_in, const uint32_
         }
     }
     if (tile > 0) {
-        const volatile uint32_t *theirs = mine;
-        for (;;) {
-            theirs -= RS_BINS;
-            uint32_t v;
-            do {
-                v = *theirs;
-            } while ((v & ~RS_COUNT_MASK) == 0);
-            prefix += v & RS_COUNT_MASK;
-            if (v & RS_FLAG_INCL) {
-                break;
+        // this digit's counts in earlier tiles, nearest first, until one carries its inclusive
+        // prefix.  RS_LOOK predecessors are read at once (independent loads, one L2 round trip)
+        // and consumed in order up to the first that is not published yet.
+        constexpr int RS_LOOK = 4;
+        int64_t p = (int64_t) tile - 1; // nearest predecessor not consumed yet
+        for (bool done = false; !done;) {
+            uint32_t v[RS_LOOK];
+#pragma unroll
+            for (int w = 0; w < RS_LOOK; w++) {
+                // before the first tile: an inclusive prefix of zero
+                v[w] = p - w >= 0 ? (uint32_t) tile_state[(uint64_t) (p - w) * RS_BINS + threadIdx.x] : (2u << 30);
             }
+            int used = 0;
+#pragma unroll
+            for (int w = 0; w < RS_LOOK; w++) {
+                if (!done && used == w && (v[w] & ~RS_COUNT_MASK) != 0u) {
+                    prefix += v[w] & RS_COUNT_MASK;
+                    used = w + 1;
+                    done = (v[w] & RS_FLAG_INCL) != 0u;
+                }
+            }
+            p -= used;
         }
         *mine = RS_FLAG_INCL | (prefix + tile_count);
     }
