@@ -239,7 +239,11 @@ class Context:
             lib().mspb_ctx_destroy(self._h)
             self._h = None
 
-    __del__ = close
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:  # noqa: BLE001  (interpreter shutdown: module globals may be gone)
+            pass
 
     def __enter__(self):
         return self

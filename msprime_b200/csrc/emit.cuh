@@ -358,7 +358,16 @@ __global__ void __launch_bounds__(K5_THREADS, 4) k5_emit_kernel(SortedView sv, R
     }
     char *der_base = staged ? st_der : out.mut_der + pre.der;
     char *anc_base = staged ? st_anc : out.site_anc + pre.anc;
-    // ---- rows and bytes
+    // ---- rows and bytes (the remaining loads, positions and parents, all in flight first)
+    double posv[K5_ITEMS];
+    int32_t parv[K5_ITEMS];
+#pragma unroll
+    for (int k = 0; k < K5_ITEMS; k++) {
+        const uint64_t i = base + (uint32_t) k * SCAN_THREADS + threadIdx.x;
+        const uint32_t m = meta[k];
+        posv[k] = (m & EM_HEAD) ? sv.key.position(i) : 0.0;
+        parv[k] = ((m & EM_MUT) && !(m & EM_SINGLE)) ? rv.parent[i] : -1;
+    }
 #pragma unroll
     for (int k = 0; k < K5_ITEMS; k++) {
         const uint32_t j = (uint32_t) k * SCAN_THREADS + threadIdx.x;
@@ -367,7 +376,7 @@ __global__ void __launch_bounds__(K5_THREADS, 4) k5_emit_kernel(SortedView sv, R
         const uint32_t site_row = srow[k];
         if (m & EM_HEAD) {
             char *anc_dst = anc_base + s_anc[j];
-            out.site_position[site_row] = sv.key.position(i);
+            out.site_position[site_row] = posv[k];
             if (KEPT && !(m & EM_MUT)) {
                 const uint32_t r = va[k];
                 const uint64_t a0 = kept.site_anc_off[r], m0 = kept.site_md_off[r];
@@ -382,11 +391,8 @@ __global__ void __launch_bounds__(K5_THREADS, 4) k5_emit_kernel(SortedView sv, R
         }
         if (m & EM_MUT) {
             const uint32_t row = KEPT ? sv.mut_scan[i] : (uint32_t) i;
-            int32_t par = -1;
-            if (!(m & EM_SINGLE)) {
-                const int32_t p = rv.parent[i];
-                par = p < 0 ? -1 : (int32_t) ((KEPT ? sv.mut_scan[p] : (uint32_t) p) + out.mut_base);
-            }
+            const int32_t p = parv[k];
+            const int32_t par = p < 0 ? -1 : (int32_t) ((KEPT ? sv.mut_scan[p] : (uint32_t) p) + out.mut_base);
             char *der_dst = der_base + s_der[j];
             out.mut_site[row] = (int32_t) (site_row + out.site_base);
             out.mut_node[row] = rcs[k].node;

@@ -539,6 +539,8 @@ __global__ void __launch_bounds__(K2_EDGES) k2_place_kernel(TreeSeqView ts, Rate
 {
     __shared__ EdgeDraw sd[K2_EDGES];
     __shared__ uint32_t sid[K2_EDGES]; // edge ids (the Philox key of a placement)
+    __shared__ uint8_t s_owner[2][K2_EDGES];
+    static_assert(K2_EDGES <= 256, "edge index inside the block fits one byte");
     __shared__ uint32_t soff[K2_EDGES + 1];
     __shared__ uint32_t sm[9];
     const uint64_t E = call.num_work; // work items: all edges, or the slice's edge list
@@ -563,22 +565,25 @@ __global__ void __launch_bounds__(K2_EDGES) k2_place_kernel(TreeSeqView ts, Rate
     __syncthreads();
     const Philox ph(call.seed);
     uint32_t out = base + (call.sliced ? k1_offset(loff, tile_base, ebase, E, true) : s0);
-    for (uint32_t j0 = s0; j0 < s1; j0 += K2_EDGES) {
+    const uint32_t my0 = soff[threadIdx.x], my1 = soff[threadIdx.x + 1];
+    for (uint32_t j0 = s0, round = 0; j0 < s1; j0 += K2_EDGES, round++) {
+        // which edge owns each of this round's 256 slots: every edge writes its own index into
+        // the slots it covers (as many stores as there are slots; double buffered by round)
+        uint8_t *owner = s_owner[round & 1u];
+        {
+            const uint32_t a = my0 > j0 ? my0 : j0, b = my1 < j0 + K2_EDGES ? my1 : j0 + K2_EDGES;
+            for (uint32_t q = a; q < b; q++) {
+                owner[q - j0] = (uint8_t) threadIdx.x;
+            }
+        }
+        __syncthreads();
         const uint32_t j = j0 + threadIdx.x;
         const bool valid = j < s1;
         double x = 0, t = 0;
         int32_t child = 0;
         bool in = false;
         if (valid) {
-            uint32_t lo = 0, hi = K2_EDGES; // largest el with soff[el] <= j
-            while (hi - lo > 1) {
-                const uint32_t mid = (lo + hi) >> 1;
-                if (soff[mid] <= j) {
-                    lo = mid;
-                } else {
-                    hi = mid;
-                }
-            }
+            const uint32_t lo = owner[threadIdx.x];
             const EdgeDraw &d = sd[lo];
             place_one(ph, map, call, d, sid[lo], j - soff[lo], &x, &t);
             child = d.child;
