@@ -141,7 +141,12 @@ MSPB_DEVFN double u53(uint32_t hi, uint32_t lo)
 }
 
 // purpose tags of the native stream: counter = (id_lo, id_hi, index, tag)
-enum : uint32_t { TAG_COUNT = 0x10000000u, TAG_PLACE = 0x20000000u, TAG_ALLELE = 0x30000000u };
+enum : uint32_t {
+    TAG_COUNT = 0x10000000u,
+    TAG_PLACE = 0x20000000u,
+    TAG_ALLELE = 0x30000000u,
+    TAG_REDRAW = 0x40000000u // + round: position redraws after a collision (continuous genome)
+};
 
 // Sequential uniforms for one (id, tag): used by the Poisson rejection loop.
 struct PhiloxSeq {

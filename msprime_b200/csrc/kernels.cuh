@@ -1299,6 +1299,47 @@ struct OutView {
 
 namespace mspb {
 
+// Continuous genome: a new mutation that landed on an occupied position (a kept site, or an
+// earlier new mutation) draws its position again, as the reference does
+// (lib/mutgen.c:1127-1134).  Runs on the position-sorted records: colliders are the new
+// records that are not the first of their position.  The record's edge is found from its
+// ordinal (K2 numbered the mutations edge by edge); the new position comes from the same
+// edge's span on a Philox counter of its own (TAG_REDRAW + round).
+__global__ void __launch_bounds__(256) redraw_positions_kernel(SortedView sv, TreeSeqView ts, RateMapView map,
+    CallView call, const uint32_t *__restrict__ goff, const uint64_t *__restrict__ tile_base, uint32_t round,
+    uint64_t *__restrict__ key_out, uint32_t *__restrict__ val_out)
+{
+    const uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= sv.n) {
+        return;
+    }
+    const uint32_t r = sv.val[i];
+    uint64_t key = sv.key.k64[i];
+    if (i > 0 && sv.is_new(i) && sv.key.same_pos(i, i - 1)) {
+        const uint32_t j = sv.rec[r].ord;
+        // largest work item w with offset(w) <= j and at least one mutation
+        const uint64_t E = call.num_work;
+        uint64_t lo = 0, hi = E;
+        while (hi - lo > 1) {
+            const uint64_t mid = (lo + hi) >> 1;
+            if (k1_offset(goff, tile_base, mid, E, false) <= j) {
+                lo = mid;
+            } else {
+                hi = mid;
+            }
+        }
+        const uint64_t e = call.edge_list != nullptr ? call.edge_list[lo] : lo;
+        const uint32_t k = j - k1_offset(goff, tile_base, lo, E, false);
+        const EdgeDraw d = edge_draw(ts, map, call, e);
+        const Philox ph(call.seed);
+        const uint4 q = ph((uint32_t) e, call.stream, k, TAG_REDRAW + round);
+        const double x = map.position_at(d.mass_lo + u53(q.x, q.y) * d.mass, d.left, d.right);
+        key = ordered_bits(x);
+    }
+    key_out[i] = key;
+    val_out[i] = r;
+}
+
 // Dense-genome fallback: rebuild keys as position << 32 | coarse descending time from the
 // position-sorted records, so that the next sort also orders sites internally.
 __global__ void __launch_bounds__(256) rekey_pos_time_kernel(SortedView sv, uint64_t *__restrict__ key_out,

@@ -1012,7 +1012,9 @@ int run_sorted_stages(mspb_ctx *ctx, const mspb_params_t *p, const TreeSeqView &
         sv.val = sb.vals[cur];
     } else {
         RadixSortBuffers<uint64_t> sb = sort_buffers64(ctx);
-        const int cur = device_radix_sort<uint64_t>(sb, R, 0, call.key_mode == KEY64_POS, st, ctx->log, nullptr);
+        // (identity payload on the first sort only: re-sorts after a redraw carry the slots along)
+        const int cur = device_radix_sort<uint64_t>(
+            sb, R, 0, call.key_mode == KEY64_POS && first_sort, st, ctx->log, nullptr);
         sv.key.k64 = sb.keys[cur];
         sv.val = sb.vals[cur];
     }
@@ -1388,6 +1390,33 @@ static int generate_impl(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t 
         CUDA_OK(cudaMemsetAsync(&dt->collisions, 0, sizeof(uint32_t), st));
         TRY(run_sorted_stages(ctx, p, ts, kept, model, call, R, S0, M0, out, false));
         CUDA_OK(cudaMemcpyAsync(ht, dt, sizeof(HostTotals), cudaMemcpyDeviceToHost, st));
+    }
+    // continuous genome, native stream: new mutations on occupied positions draw again
+    // (lib/mutgen.c:1127-1134) until every position is unique.  (The replay harness and
+    // invariant slices report the collision instead: the former would need the reference's
+    // exact stream order, the latter could move a record out of the slice.)
+    for (uint32_t round = 1; R > 0 && ht->err == 0 && ht->collisions > 0 && !replay && !sliced
+                             && call.key_mode == KEY64_POS && round <= 32;
+         round++) {
+        RadixSortBuffers<uint64_t> sb = sort_buffers64(ctx);
+        uint64_t *key_in = ctx->last_sv.key.k64;
+        uint64_t *key_tmp = key_in == ctx->keys0.p ? ctx->keys1.p : ctx->keys0.p;
+        uint32_t *val_in = ctx->last_sv.val;
+        uint32_t *val_tmp = val_in == ctx->vals0.p ? ctx->vals1.p : ctx->vals0.p;
+        MSPB_LAUNCH(ctx->log, "redraw_positions",
+            redraw_positions_kernel<<<grid_for(R, 256), 256, 0, st>>>(ctx->last_sv, ts, map, call, ctx->goff.p,
+                ctx->k1_tiles.p, round, key_tmp, val_tmp));
+        if (key_tmp != sb.keys[0]) {
+            CUDA_OK(cudaMemcpyAsync(sb.keys[0], key_tmp, R * sizeof(uint64_t), cudaMemcpyDeviceToDevice, st));
+        }
+        if (val_tmp != sb.vals[0]) {
+            CUDA_OK(cudaMemcpyAsync(sb.vals[0], val_tmp, R * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
+        }
+        CUDA_OK(cudaMemsetAsync(&dt->p1, 0, sizeof(Counts3), st));
+        CUDA_OK(cudaMemsetAsync(&dt->collisions, 0, sizeof(uint32_t), st));
+        TRY(run_sorted_stages(ctx, p, ts, kept, model, call, R, S0, M0, out, false));
+        CUDA_OK(cudaMemcpyAsync(ht, dt, sizeof(HostTotals), cudaMemcpyDeviceToHost, st));
+        CUDA_OK(cudaStreamSynchronize(st));
     }
     CUDA_OK(cudaEventRecord(ctx->ev[8], st));
     CUDA_OK(cudaStreamSynchronize(st));

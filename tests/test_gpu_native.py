@@ -64,6 +64,25 @@ def test_seed_determinism(ctx, ts_small):
     assert not np.array_equal(a["sites"]["position"], c["sites"]["position"])
 
 
+@pytest.mark.parametrize("model", ["jc69", "infinite_alleles"])
+def test_continuous_genome_collisions_are_redrawn(ctx, ts_small, model):
+    """lib/mutgen.c:1127-1134, tests/test_mutations.py:1340: a second layer with the SAME seed on
+    a continuous genome draws every position of the first layer again; each such mutation must
+    move to a fresh position instead of sharing (or failing on) the kept site's."""
+    mdl = cases.MODELS[model]
+    first, c1 = run(ctx, ts_small, model=mdl, rate=3e-7, discrete=False, seed=11)
+    assert c1["num_new_mutations"] > 1000
+    ts2 = cases.with_kept(ts_small, first)
+    second, c2 = run(ctx, ts2, model=mdl, rate=3e-7, discrete=False, keep=True, seed=11)
+    assert c2["num_new_mutations"] == c1["num_new_mutations"]  # same seed, same counts
+    assert c2["num_mutations"] == 2 * c1["num_mutations"]
+    pos = second["sites"]["position"]
+    assert np.all(np.diff(pos) > 0)  # sorted, no two sites share a position
+    assert c2["num_sites"] == 2 * c1["num_sites"]  # nothing merged into a kept site
+    assert np.isin(first["sites"]["position"], pos).all()
+    table_checks.check_result(ts2, second, discrete=False)
+
+
 def test_infinite_alleles_numbering_and_counter(ctx, ts_small):
     m = dict(cases.INF_ALLELES, start_allele=123456789012)
     res, c = run(ctx, ts_small, model=m, rate=1e-6, seed=3)
