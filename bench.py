@@ -55,6 +55,10 @@ WORKLOADS = {
     "config3": dict(samples=100_000, L=1e8, recomb=1e-8, ne=1e4, ts_seed=1, rate=1e-8, model="gtr",
                     discrete=True, ratemap=1000,
                     text="config3: GTR, 1000-interval lognormal RateMap around 1e-8, 1e5 diploid samples x 1e8 bp"),
+    "config4": dict(samples=100_000, L=1e8, recomb=1e-8, ne=1e4, ts_seed=1, rate=1e-8, model="hky",
+                    discrete=True, keep_layer=dict(model="hky", rate=1e-8, seed=5), window=(1e3, 2e4),
+                    text="config4: HKY(kappa=2) rate=1e-8 keep=True on an HKY layer (seed 5), time window [1e3, 2e4), "
+                         "1e5 diploid samples x 1e8 bp"),
     "small": dict(samples=2_000, L=2e6, recomb=1e-8, ne=1e4, ts_seed=1, rate=1e-7, model="infinite_alleles",
                   discrete=True, text="small: 2e3 samples x 2e6 bp, InfiniteAlleles rate=1e-7"),
 }
@@ -71,7 +75,26 @@ def make_input(w):
     ts = synth.native_treeseq(w["samples"], w["L"], w["recomb"], w["ne"], w["ts_seed"])
     log(f"[bench] input: N={len(ts['nodes']['time'])} E={len(ts['edges']['left'])} trees={ts['num_trees']} "
         f"({time.time() - t0:.1f} s, synthetic SMC' generator)")
+    kl = w.get("keep_layer")
+    if kl:
+        # the existing mutations of a keep=True workload: one reference overlay (input preparation)
+        from oracle import oracle
+
+        _, which = cpu_kind()
+        t0 = time.time()
+        first = oracle.sim_mutations(ts, which=which, map_position=[0, ts["sequence_length"]], map_rate=[kl["rate"]],
+                                     model=oracle_model(kl["model"]), discrete_genome=w["discrete"], keep=False,
+                                     seed=kl["seed"])
+        ts = dict(ts)
+        ts["sites"], ts["mutations"] = first["sites"], first["mutations"]
+        log(f"[bench] kept layer: {len(first['mutations']['site'])} mutations at {len(first['sites']['position'])} "
+            f"sites ({time.time() - t0:.1f} s, reference overlay)")
     return ts
+
+
+def time_window(w):
+    lo, hi = w.get("window", (-FMAX, FMAX))
+    return float(lo), float(hi)
 
 
 def oracle_model(name):
@@ -81,12 +104,12 @@ def oracle_model(name):
         m = (np.full((4, 4), 1 / 3) - np.eye(4) / 3).tolist()
         return {"kind": "matrix", "alleles": ["A", "C", "G", "T"], "root_distribution": [0.25] * 4,
                 "transition_matrix": m}
-    if name in ("binary", "gtr"):
+    if name in ("binary", "gtr", "hky"):
         # the host mirror's matrix builders (msprime/mutations.py:179-201, 763-850); BASELINE.md
         # fixes the GTR parameters that BASELINE.json leaves open
         from msprime_b200 import mutations
 
-        mm = (mutations.BinaryMutationModel() if name == "binary" else
+        mm = (mutations.BinaryMutationModel() if name == "binary" else mutations.HKY(kappa=2) if name == "hky" else
               mutations.GTR(relative_rates=[1, 2, 1, 1, 2, 1], equilibrium_frequencies=[0.3, 0.2, 0.2, 0.3]))
         return {"kind": "matrix", "alleles": list(mm.alleles), "root_distribution": [float(x) for x in mm.root_distribution],
                 "transition_matrix": np.asarray(mm.transition_matrix).tolist()}
@@ -128,6 +151,22 @@ def genome_prefix(ts, frac):
     out["sequence_length"] = X
     out["edges"] = {"left": e["left"][keep], "right": np.minimum(e["right"][keep], X),
                     "parent": e["parent"][keep], "child": e["child"][keep]}
+    if "sites" in ts and len(ts["sites"]["position"]) > 0:
+        # kept rows of the prefix (sites are sorted by position, mutations grouped by site)
+        sp = np.asarray(ts["sites"]["position"])
+        ns = int(np.searchsorted(sp, X, side="left"))
+        ms = np.asarray(ts["mutations"]["site"])
+        nm = int(np.searchsorted(ms, ns, side="left"))
+
+        def ragged(cols, name, n):
+            off = np.asarray(cols[name + "_offset"])[: n + 1]
+            return {name: np.asarray(cols[name])[: int(off[-1])], name + "_offset": off}
+
+        st, mt = ts["sites"], ts["mutations"]
+        out["sites"] = {"position": sp[:ns], **ragged(st, "ancestral_state", ns), **ragged(st, "metadata", ns)}
+        out["mutations"] = {"site": ms[:nm], "node": np.asarray(mt["node"])[:nm],
+                            "parent": np.asarray(mt["parent"])[:nm], "time": np.asarray(mt["time"])[:nm],
+                            **ragged(mt, "derived_state", nm), **ragged(mt, "metadata", nm)}
     return out, X / L
 
 
@@ -141,9 +180,13 @@ def _cpu_worker(seed):
     j = _CPU_JOB
     t0 = time.perf_counter()
     mp_, mr_ = rate_map(j["w"], j["ts"]["sequence_length"])
+    lo, hi = time_window(j["w"])
+    keep = bool(j["w"].get("keep_layer"))
     r = oracle.sim_mutations(j["ts"], which=j["which"], map_position=mp_, map_rate=mr_,
-                             model=oracle_model(j["model"]), discrete_genome=j["discrete"], keep=False, seed=seed)
-    return len(r["mutations"]["site"]), r["seconds"], time.perf_counter() - t0
+                             model=oracle_model(j["model"]), discrete_genome=j["discrete"], keep=keep, seed=seed,
+                             start_time=lo, end_time=hi)
+    kept = len(j["ts"]["mutations"]["site"]) if keep else 0
+    return len(r["mutations"]["site"]) - kept, r["seconds"], time.perf_counter() - t0
 
 
 def cpu_reference_pass(ts, w, cores, seed0, which):
@@ -348,6 +391,8 @@ def run_b200_arm(args, rank, local_rank, world):
         hold.append(t)
     E, N = len(ts["edges"]["left"]), len(ts["nodes"]["time"])
     h2d_bytes = E * (8 + 8 + 4 + 4) + N * 8
+    for tbl in ("sites", "mutations"):  # kept rows of a keep=True workload
+        h2d_bytes += sum(int(np.asarray(v).nbytes) for v in ts[tbl].values())
 
     ctx = _native.Context(local_rank)
     stream = torch.cuda.ExternalStream(ctx.stream(), device=torch.device("cuda", local_rank))
@@ -356,7 +401,8 @@ def run_b200_arm(args, rank, local_rank, world):
 
     def params(step):
         return _native.Params(map_position=map_pos, map_rate=map_rate, model=native_model(w["model"]),
-                              discrete_genome=w["discrete"], keep=False, start_time=-FMAX, end_time=FMAX,
+                              discrete_genome=w["discrete"], keep=bool(w.get("keep_layer")),
+                              start_time=time_window(w)[0], end_time=time_window(w)[1],
                               seed=1000 + step, slice_left=sl, slice_right=sr, offsets32=True,
                               slice_stream=0 if world == 1 else rank + 1)
 
