@@ -395,6 +395,33 @@ class Context:
         check(lib().mspb_device_columns(self._h, C.byref(cols)))
         return {name: getattr(cols, name) for name, _ in _COLUMNS}
 
+    def device_tensors(self):
+        """The resident result as torch tensors on this context's device, WITHOUT a copy
+        (the table hand-off for consumers that stay on the GPU):
+        ``{"sites": {...}, "mutations": {...}}`` with the column names of :meth:`fetch`.
+        The tensors alias the context's buffers: they are valid until the next ``generate*``
+        call on this context and are written on its stream (:meth:`stream`).  torch has no
+        unsigned 32/64-bit arithmetic, so offset columns come back as int32 / int64 views
+        and byte columns as uint8."""
+        import torch
+
+        ptrs = self.device_columns()
+        sizes = self.result_sizes()
+        dev = torch.device("cuda", self.device)
+        off = "<i4" if self.counts["offset_bytes"] == 4 else "<i8"
+        typestr = {np.float64: "<f8", np.int32: "<i4", np.uint8: "|u1", np.uint64: off}
+        res = {"sites": {}, "mutations": {}}
+        for name, dtype in _COLUMNS:
+            tbl, col = ("sites", name[len("site_"):]) if name.startswith("site_") else (
+                "mutations", name[len("mutation_"):])
+            n = sizes[name]
+            if n == 0 or not ptrs[name]:
+                tdt = {"<f8": torch.float64, "<i4": torch.int32, "|u1": torch.uint8, "<i8": torch.int64}
+                res[tbl][col] = torch.empty(0, dtype=tdt[typestr[dtype]], device=dev)
+            else:
+                res[tbl][col] = torch.as_tensor(_DeviceArray(ptrs[name], n, typestr[dtype]), device=dev)
+        return res
+
     def kernel_launches(self) -> int:
         return int(lib().mspb_kernel_launches(self._h))
 

@@ -221,6 +221,25 @@ def test_device_exchange_equals_whole(native_built, ts_small, world, model, keep
     assert bases["num_sites"] == sum(i[0]["num_sites"] for i in infos[:-1])
 
 
+def test_device_tensors_alias_the_result(ctx, ts_small):
+    """the result handed over as torch tensors on the device, no copy."""
+    import torch
+
+    host, c = run(ctx, ts_small, model=cases.INF_ALLELES, rate=1e-6, seed=5)
+    dev = ctx.device_tensors()
+    torch.cuda.synchronize()
+    for tbl in host:
+        for col in host[tbl]:
+            t = dev[tbl][col]
+            assert t.is_cuda and t.numel() == len(host[tbl][col]), (tbl, col)
+            got = t.cpu().numpy()
+            want = np.asarray(host[tbl][col])
+            assert np.array_equal(got.view(np.uint8), want.astype(got.dtype).view(np.uint8)), (tbl, col)
+    # a consumer on the GPU: per-site mutation counts straight from the resident columns
+    counts = torch.bincount(dev["mutations"]["site"].long(), minlength=c["num_sites"])
+    assert int(counts.sum()) == c["num_mutations"] and int(counts.min()) >= 1
+
+
 def test_clipped_slices(native_built, ts_small):
     """slice_stream != 0: edges are cut to the slice and drawn on the slice's own stream."""
     ts = ts_small
