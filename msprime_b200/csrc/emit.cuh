@@ -226,6 +226,7 @@ __global__ void __launch_bounds__(K5_THREADS, 4) k5_emit_kernel(SortedView sv, R
     uint32_t va[K5_ITEMS]; // infinite alleles: draws before the record; matrix: derived allele index
     uint32_t vb[K5_ITEMS]; // matrix: ancestral allele index of a new site
     uint32_t srow[K5_ITEMS];
+    uint32_t pos32[K5_ITEMS]; // 32-bit position keys are read with everything else (wider ones later)
     Rec rcs[K5_ITEMS];
     {
         uint32_t slot[K5_ITEMS], before[K5_ITEMS], after[K5_ITEMS];
@@ -234,6 +235,7 @@ __global__ void __launch_bounds__(K5_THREADS, 4) k5_emit_kernel(SortedView sv, R
             const uint64_t i = base + (uint32_t) k * SCAN_THREADS + threadIdx.x;
             const uint64_t ic = i < last ? i : last;
             slot[k] = sv.val[ic];
+            pos32[k] = sv.key.mode == KEY32_POS ? sv.key.k32[ic] : 0u;
             srow[k] = sv.site_row[ic];
             before[k] = sv.site_row[ic > 0 ? ic - 1 : 0];
             after[k] = sv.site_row[ic < last ? ic + 1 : last];
@@ -365,7 +367,7 @@ __global__ void __launch_bounds__(K5_THREADS, 4) k5_emit_kernel(SortedView sv, R
     for (int k = 0; k < K5_ITEMS; k++) {
         const uint64_t i = base + (uint32_t) k * SCAN_THREADS + threadIdx.x;
         const uint32_t m = meta[k];
-        posv[k] = (m & EM_HEAD) ? sv.key.position(i) : 0.0;
+        posv[k] = sv.key.mode == KEY32_POS ? (double) pos32[k] : ((m & EM_HEAD) ? sv.key.position(i) : 0.0);
         parv[k] = ((m & EM_MUT) && !(m & EM_SINGLE)) ? rv.parent[i] : -1;
     }
 #pragma unroll
