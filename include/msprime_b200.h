@@ -49,6 +49,8 @@ extern "C" {
 #define MSPB_ERR_INSUFFICIENT_ALLELES (-52)
 #define MSPB_ERR_BAD_ROOT_PROBABILITIES (-53)
 #define MSPB_ERR_BAD_TRANSITION_MATRIX (-54)
+#define MSPB_ERR_BAD_SLIM_PARAMETERS (-56)
+#define MSPB_ERR_MUTATION_ID_OVERFLOW (-57)
 #define MSPB_ERR_UNKNOWN_TIME_NOT_SUPPORTED (-69)
 /* implementation specific */
 #define MSPB_ERR_CUDA (-1000)
@@ -62,7 +64,8 @@ extern "C" {
 #define MSPB_ERR_UNSORTED_SITES (-1009) /* sliced call: kept sites must be sorted by position */
 #define MSPB_ERR_OFFSET_OVERFLOW (-1008) /* offsets32 asked for, but a column may reach 4 GiB */
 
-enum { MSPB_MODEL_MATRIX = 0, MSPB_MODEL_INFINITE_ALLELES = 1 };
+/* the reference's three C models (lib/mutgen.c:184-237, 257-413, 431-481) */
+enum { MSPB_MODEL_MATRIX = 0, MSPB_MODEL_INFINITE_ALLELES = 1, MSPB_MODEL_SLIM = 2 };
 
 /* Input tables (host memory, borrowed for the duration of the call). */
 typedef struct {
@@ -104,7 +107,7 @@ typedef struct {
     const uint64_t *allele_offset; /* num_alleles + 1 */
     const double *root_distribution; /* num_alleles */
     const double *transition_matrix; /* num_alleles^2, row major */
-    uint64_t start_allele; /* infinite alleles: next_allele on entry */
+    uint64_t start_allele; /* infinite alleles: next_allele on entry; SLiM: next_mutation_id (int64 >= 0) */
     /* flags and window (MSP_DISCRETE_SITES / MSP_KEEP_SITES, lib/msprime.h:66-68) */
     int32_t discrete_genome;
     int32_t keep;
@@ -130,6 +133,13 @@ typedef struct {
      * this Philox stream (use rank + 1), so work scales with the slice; the result then
      * depends on the cuts, with the same distribution. */
     uint32_t slice_stream;
+    /* SLiM model (slim_mutation_model_alloc, lib/mutgen.c:552-589): new sites have the empty
+     * ancestral state; a new mutation's derived state is its parent's state, a comma and the
+     * next mutation id, its metadata the parent's metadata plus a 17-byte MutationMetadataRec
+     * with origin generation = slim_generation - (int32) time.  Single-call only (not with
+     * mspb_generate_begin). */
+    int32_t slim_mutation_type_id;
+    int32_t slim_generation;
 } mspb_params_t;
 
 /* Row and byte counts of the result of the last mspb_generate. */

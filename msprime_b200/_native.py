@@ -21,6 +21,7 @@ SO_PATH = os.path.join(HERE, "_mspb.so")
 
 MODEL_MATRIX = 0
 MODEL_INFINITE_ALLELES = 1
+MODEL_SLIM = 2
 NUM_PHASES = 8
 
 ERR_NO_DEVICE = -1001
@@ -70,6 +71,7 @@ class _Params(C.Structure):
         ("seed", C.c_uint64), ("replay_stream", C.c_void_p), ("replay_len", C.c_uint64),
         ("slice_left", C.c_double), ("slice_right", C.c_double),
         ("offsets32", C.c_int32), ("slice_stream", C.c_uint32),
+        ("slim_mutation_type_id", C.c_int32), ("slim_generation", C.c_int32),
     ]
 
 
@@ -210,6 +212,11 @@ class Params:
             p.num_alleles = len(model["alleles"])
             p.alleles, p.allele_offset = _p(data), _p(off)
             p.root_distribution, p.transition_matrix = _p(root), _p(mat)
+        elif model["kind"] == MODEL_SLIM:
+            # {"kind": 2, "type": mutation type id, "next_id": ..., "slim_generation": ...}
+            p.start_allele = int(model.get("next_id", 0)) & 0xFFFFFFFFFFFFFFFF
+            p.slim_mutation_type_id = int(model["type"])
+            p.slim_generation = int(model.get("slim_generation", 1))
         else:
             p.start_allele = int(model["start_allele"]) & 0xFFFFFFFFFFFFFFFF
         p.discrete_genome, p.keep = int(bool(discrete_genome)), int(bool(keep))

@@ -174,7 +174,81 @@ struct Bytes4 {
     }
 };
 
-// MODEL: 0 matrix, 1 infinite alleles.  KEPT: kept site / mutation rows are present.
+// The SLiM model's stacked state of new mutation i (lib/mutgen.c:355-413): the parent's
+// derived state, a comma if that is not empty, the mutation id; and the parent's metadata plus
+// one 17-byte record.  Written back to front along the parent chain: new ancestors contribute
+// their own id / record, the first kept ancestor (or the kept site, when the chain ends without
+// one: lib/mutgen.c:1190-1194) contributes its whole state and metadata.
+MSPB_DEVFN void slim_write_state(const SortedView &sv, const ResolveView &rv, const KeptView &kept,
+    const ModelView &model, uint64_t i, bool single, char *der_end, char *md_end)
+{
+    uint64_t cur = i;
+    for (;;) {
+        const uint32_t r = sv.val[cur];
+        const uint64_t id = model.start_allele + (sv.has_kept ? sv.draw_scan[cur] : (uint32_t) cur);
+        const uint32_t n = num_digits(id);
+        der_end -= n;
+        write_digits(der_end, id, n);
+        {
+            const int32_t type_id = model.slim_type, subpop = -1;
+            const int32_t origin = model.slim_generation - (int32_t) sv.rec[r].time;
+            const float sel = 0.0f;
+            const int8_t nuc = -1;
+            char rec17[SLIM_MD_SIZE];
+            memcpy(rec17, &type_id, 4);
+            memcpy(rec17 + 4, &sel, 4);
+            memcpy(rec17 + 8, &subpop, 4);
+            memcpy(rec17 + 12, &origin, 4);
+            memcpy(rec17 + 16, &nuc, 1);
+            md_end -= SLIM_MD_SIZE;
+            for (int b = 0; b < SLIM_MD_SIZE; b++) {
+                md_end[b] = rec17[b];
+            }
+        }
+        const int32_t p = single ? -1 : rv.parent[cur];
+        const char *bs = nullptr, *bm = nullptr; // the base that ends the chain, if it is reached
+        uint64_t bl = 0, bml = 0;
+        bool ends = false;
+        if (p < 0) {
+            ends = true;
+            if (sv.has_kept) {
+                uint64_t h = cur; // this site's first record: a kept site's marker
+                while (h > 0 && sv.site_row[h - 1] == sv.site_row[h]) {
+                    h--;
+                }
+                const uint32_t r0 = sv.val[h];
+                if (r0 < sv.S0) {
+                    bs = kept.site_anc + kept.site_anc_off[r0];
+                    bl = kept.site_anc_off[r0 + 1] - kept.site_anc_off[r0];
+                    bm = kept.site_md + kept.site_md_off[r0];
+                    bml = kept.site_md_off[r0 + 1] - kept.site_md_off[r0];
+                }
+            }
+        } else {
+            const uint32_t rp = sv.val[p];
+            if (sv.has_kept && rp < sv.S0 + sv.M0) {
+                const uint64_t km = rp - sv.S0;
+                ends = true;
+                bs = kept.mut_der + kept.mut_der_off[km];
+                bl = kept.mut_der_off[km + 1] - kept.mut_der_off[km];
+                bm = kept.mut_md + kept.mut_md_off[km];
+                bml = kept.mut_md_off[km + 1] - kept.mut_md_off[km];
+            }
+        }
+        if (ends) {
+            if (bl > 0) {
+                *--der_end = ',';
+                copy_bytes(der_end - bl, bs, bl);
+            }
+            copy_bytes(md_end - bml, bm, bml);
+            return;
+        }
+        *--der_end = ','; // a new parent's state is never empty
+        cur = (uint64_t) p;
+    }
+}
+
+// MODEL: 0 matrix, 1 infinite alleles, 2 SLiM.  KEPT: kept site / mutation rows are present.
 template <int MODEL, bool KEPT, bool OFF32>
 __global__ void __launch_bounds__(K5_THREADS, 4) k5_emit_kernel(SortedView sv, ResolveView rv, KeptView kept,
     ModelView model, CallView call, OutView out, LbWord *lb, uint32_t num_tiles, const Counts3 *p1_total,
@@ -184,8 +258,10 @@ __global__ void __launch_bounds__(K5_THREADS, 4) k5_emit_kernel(SortedView sv, R
     __shared__ LbVal<2, true> bcast, s_agg;
     __shared__ __align__(16) uint32_t s_der[K5_TILE];
     __shared__ __align__(16) uint32_t s_anc[K5_TILE];
-    __shared__ __align__(16) uint32_t s_mmd[KEPT ? K5_TILE : 4];
-    __shared__ __align__(16) uint32_t s_smd[KEPT ? K5_TILE : 4];
+    // metadata columns carry bytes when rows are kept or the model writes metadata (SLiM)
+    constexpr bool MD = KEPT || MODEL == 2;
+    __shared__ __align__(16) uint32_t s_mmd[MD ? K5_TILE : 4];
+    __shared__ __align__(16) uint32_t s_smd[MD ? K5_TILE : 4];
     __shared__ __align__(16) char st_der[K5_STAGE + 32];
     __shared__ __align__(16) char st_anc[K5_STAGE + 32];
     if (*dense != 0u && sv.key.mode == KEY32_POS) {
@@ -199,7 +275,7 @@ __global__ void __launch_bounds__(K5_THREADS, 4) k5_emit_kernel(SortedView sv, R
     if (threadIdx.x >= SCAN_THREADS) {
         // ---- the look-back warp: meets the workers at their barriers, otherwise only chains
         __syncthreads(); // lengths are in shared memory
-        for (int b = 0; b < (KEPT ? 12 : 3); b++) {
+        for (int b = 0; b < (MD ? 12 : 3); b++) {
             __syncthreads(); // the barriers of the tile scans
         }
         __syncthreads(); // offsets and the tile's totals are visible
@@ -211,7 +287,7 @@ __global__ void __launch_bounds__(K5_THREADS, 4) k5_emit_kernel(SortedView sv, R
         const uint64_t der = (uint64_t) aw.w[0][0] | ((uint64_t) aw.w[0][1] << 32);
         const uint64_t anc = (uint64_t) aw.w[1][0] | ((uint64_t) aw.w[1][1] << 32);
         const bool no_md = (aw.w[0][2] | aw.w[0][3] | aw.w[1][2] | aw.w[1][3]) == 0u;
-        if (KEPT && !(der <= K5_STAGE && anc <= K5_STAGE && no_md)) {
+        if (MD && !out.dry_run && !(der <= K5_STAGE && anc <= K5_STAGE && no_md)) {
             __syncthreads(); // unstaged tiles: the workers wait for the prefix before writing
         }
         __syncthreads(); // rows and bytes are done
@@ -268,7 +344,18 @@ __global__ void __launch_bounds__(K5_THREADS, 4) k5_emit_kernel(SortedView sv, R
         vb[k] = 0;
         if (m & EM_NEW) {
             // a head that is a mutation opens a new site (kept sites start with their marker)
-            if (MODEL == 1) {
+            if (MODEL == 2) {
+                // SLiM: the id counts new mutations only; a new site's ancestral state is empty
+                const uint32_t db = KEPT ? sv.draw_scan[i] : (uint32_t) i;
+                va[k] = db;
+                if (m & EM_SINGLE) {
+                    d = num_digits(model.start_allele + db);
+                    md = SLIM_MD_SIZE;
+                } else {
+                    d = (uint32_t) rv.state[i];
+                    md = (uint32_t) rv.site_state[i];
+                }
+            } else if (MODEL == 1) {
                 const uint32_t db = KEPT ? sv.draw_scan[i] : (uint32_t) i + srow[k] + 1u - (head ? 1u : 0u);
                 const uint64_t root_number = model.start_allele + db;
                 va[k] = db;
@@ -316,7 +403,7 @@ __global__ void __launch_bounds__(K5_THREADS, 4) k5_emit_kernel(SortedView sv, R
         }
         s_der[j] = d;
         s_anc[j] = a;
-        if (KEPT) {
+        if (MD) {
             s_mmd[j] = md;
             s_smd[j] = sd;
         }
@@ -324,7 +411,7 @@ __global__ void __launch_bounds__(K5_THREADS, 4) k5_emit_kernel(SortedView sv, R
     __syncthreads();
     // ---- offsets inside the tile
     Bytes4 agg = Bytes4();
-    if (KEPT) {
+    if (MD) {
         agg.der = tile_offsets<uint64_t>(s_der, sm);
         agg.anc = tile_offsets<uint64_t>(s_anc, sm);
         agg.mmd = tile_offsets<uint64_t>(s_mmd, sm);
@@ -348,8 +435,21 @@ __global__ void __launch_bounds__(K5_THREADS, 4) k5_emit_kernel(SortedView sv, R
     // ---- offsets across tiles.  When the tile's state bytes fit the stage (always, unless
     // kept rows carry long strings) nothing below needs the prefix until the very end:
     // the look-back warp chains the tiles while the workers write rows and assemble bytes.
-    const bool staged = !KEPT || (agg.der <= K5_STAGE && agg.anc <= K5_STAGE && agg.mmd == 0 && agg.smd == 0);
+    const bool staged = !MD || (agg.der <= K5_STAGE && agg.anc <= K5_STAGE && agg.mmd == 0 && agg.smd == 0);
     Bytes4 pre = Bytes4();
+    if (out.dry_run) {
+        // sizing pass (models whose state lengths are not bounded up front): totals only
+        __syncthreads();
+        if (blockIdx.x + 1 == num_tiles && threadIdx.x == 0) {
+            const LbVal<2, true> pw = bcast;
+            pre.der = (uint64_t) pw.w[0][0] | ((uint64_t) pw.w[0][1] << 32);
+            pre.mmd = (uint64_t) pw.w[0][2] | ((uint64_t) pw.w[0][3] << 32);
+            pre.anc = (uint64_t) pw.w[1][0] | ((uint64_t) pw.w[1][1] << 32);
+            pre.smd = (uint64_t) pw.w[1][2] | ((uint64_t) pw.w[1][3] << 32);
+            *total = pre + agg;
+        }
+        return;
+    }
     if (!staged) {
         __syncthreads(); // (the look-back warp has the prefix)
         const LbVal<2, true> pw = bcast;
@@ -387,7 +487,7 @@ __global__ void __launch_bounds__(K5_THREADS, 4) k5_emit_kernel(SortedView sv, R
             } else if (MODEL == 0) {
                 const uint64_t a0 = model.allele_off[vb[k]];
                 copy_bytes32(anc_dst, model.alleles + a0, (uint32_t) (model.allele_off[vb[k] + 1] - a0));
-            } else {
+            } else if (MODEL == 1) {
                 write_number(anc_dst, model.start_allele + va[k], (m >> 16) & 0xffu);
             }
         }
@@ -408,8 +508,13 @@ __global__ void __launch_bounds__(K5_THREADS, 4) k5_emit_kernel(SortedView sv, R
             } else if (MODEL == 0) {
                 const uint64_t d0 = model.allele_off[va[k]];
                 copy_bytes32(der_dst, model.alleles + d0, (uint32_t) (model.allele_off[va[k] + 1] - d0));
-            } else {
+            } else if (MODEL == 1) {
                 write_number(der_dst, model.start_allele + va[k] + ((m & EM_HEAD) ? 1u : 0u), (m >> 8) & 0xffu);
+            } else {
+                const uint32_t dl = (m & EM_SINGLE) ? num_digits(model.start_allele + va[k]) : (uint32_t) rv.state[i];
+                const uint32_t ml = (m & EM_SINGLE) ? (uint32_t) SLIM_MD_SIZE : (uint32_t) rv.site_state[i];
+                slim_write_state(sv, rv, kept, model, i, (m & EM_SINGLE) != 0u, der_dst + dl,
+                    out.mut_md + pre.mmd + s_mmd[j] + ml);
             }
         }
     }
@@ -429,14 +534,14 @@ __global__ void __launch_bounds__(K5_THREADS, 4) k5_emit_kernel(SortedView sv, R
         if (m & EM_HEAD) {
             store_offset<OFF32>(out.site_anc_off, srow[k], pre.anc + s_anc[j]);
             if (out.write_md_off) {
-                store_offset<OFF32>(out.site_md_off, srow[k], pre.smd + (KEPT ? s_smd[j] : 0u));
+                store_offset<OFF32>(out.site_md_off, srow[k], pre.smd + (MD ? s_smd[j] : 0u));
             }
         }
         if (m & EM_MUT) {
             const uint32_t row = KEPT ? sv.mut_scan[base + j] : (uint32_t) (base + j);
             store_offset<OFF32>(out.mut_der_off, row, pre.der + s_der[j]);
             if (out.write_md_off) {
-                store_offset<OFF32>(out.mut_md_off, row, pre.mmd + (KEPT ? s_mmd[j] : 0u));
+                store_offset<OFF32>(out.mut_md_off, row, pre.mmd + (MD ? s_mmd[j] : 0u));
             }
         }
     }

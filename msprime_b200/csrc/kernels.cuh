@@ -72,8 +72,10 @@ struct ModelView {
     const uint64_t *allele_off;
     const double *root; // num_alleles
     const double *matrix; // num_alleles^2
-    uint64_t start_allele;
+    uint64_t start_allele; // infinite alleles: next allele; SLiM: next mutation id
+    int32_t slim_type, slim_generation; // SLiM model (kind 2), lib/mutgen.c:552-589
 };
+constexpr int SLIM_MD_SIZE = 17; // MutationMetadataRec, lib/mutgen.c:262-290
 
 // How positions are packed into sort keys.
 enum KeyMode : int {
@@ -789,6 +791,7 @@ struct SortedView {
     uint32_t *val; // slot of the record at each sorted index (K4 reorders inside sites)
     const Rec *rec;
     int has_kept; // S0 + M0 > 0
+    int root_draw; // a new site takes one draw / allele number for its root state (not the SLiM model)
     // P1 results
     uint32_t *site_row; // row of the site that record i belongs to
     uint32_t *mut_scan; // mutation rows before i (has_kept only; otherwise it is i)
@@ -802,7 +805,10 @@ struct SortedView {
     MSPB_DEVFN uint32_t mut_row(uint64_t i) const { return has_kept ? mut_scan[i] : (uint32_t) i; }
     MSPB_DEVFN uint32_t draws_before(uint64_t i) const
     {
-        return has_kept ? draw_scan[i] : (uint32_t) i + site_row[i] + 1u - (head(i) ? 1u : 0u);
+        if (has_kept) {
+            return draw_scan[i];
+        }
+        return root_draw ? (uint32_t) i + site_row[i] + 1u - (head(i) ? 1u : 0u) : (uint32_t) i;
     }
 };
 
@@ -927,7 +933,7 @@ __global__ void __launch_bounds__(SCAN_THREADS, (MODE == KEY32_POS && !KEPT) ? 4
             const bool h = i == 0 || !P1Key<MODE>::same_pos(pk[k + 1], pk[k]);
             const bool mu = !KEPT || slot[KEPT ? k : 0] >= sv.S0;
             const bool nw = !KEPT || slot[KEPT ? k : 0] >= sv.S0 + sv.M0;
-            const uint32_t d = (nw ? 1u : 0u) + ((h && mu) ? 1u : 0u);
+            const uint32_t d = (nw ? 1u : 0u) + ((h && mu && sv.root_draw) ? 1u : 0u);
             const bool multi = h && i + 1 < sv.n && P1Key<MODE>::same_pos(pk[k + 2], pk[k + 1]);
             f = (h ? 1u : 0u) | ((mu ? 1u : 0u) << 1) | (d << 2) | ((multi ? 1u : 0u) << 4);
             if (!h) {
@@ -998,6 +1004,55 @@ __global__ void __launch_bounds__(SCAN_THREADS, (MODE == KEY32_POS && !KEPT) ? 4
                 }
             }
         }
+    }
+}
+
+// ---------------------------------------------------------------- decimal text
+// decimal length of v (snprintf "%" PRIu64, lib/mutgen.c:431-447); allele numbers are
+// almost always below 2^32, where 32-bit compares and divisions are much cheaper
+MSPB_DEVFN uint32_t num_digits32(uint32_t v)
+{
+    return v < 100000u ? (v < 100u ? (v < 10u ? 1u : 2u) : (v < 1000u ? 3u : (v < 10000u ? 4u : 5u)))
+                       : (v < 10000000u ? (v < 1000000u ? 6u : 7u)
+                                        : (v < 100000000u ? 8u : (v < 1000000000u ? 9u : 10u)));
+}
+
+MSPB_DEVFN uint32_t num_digits(uint64_t v)
+{
+    if (v <= 0xffffffffull) {
+        return num_digits32((uint32_t) v);
+    }
+    uint32_t n = 9; // v >= 2^32 > 10^9: the low nine digits are full
+    v /= 1000000000ull;
+    while (v > 0xffffffffull) {
+        v /= 1000000000ull;
+        n += 9;
+    }
+    return n + num_digits32((uint32_t) v);
+}
+
+MSPB_DEVFN void write_digits(char *dst, uint64_t v, uint32_t n)
+{
+    uint32_t k = n;
+    while (v > 0xffffffffull) {
+        uint32_t low = (uint32_t) (v % 1000000000ull);
+        v /= 1000000000ull;
+        for (int d = 0; d < 9; d++) {
+            dst[--k] = (char) ('0' + (low % 10u));
+            low /= 10u;
+        }
+    }
+    uint32_t w = (uint32_t) v;
+    while (k > 0) {
+        dst[--k] = (char) ('0' + (w % 10u));
+        w /= 10u;
+    }
+}
+
+MSPB_DEVFN void copy_bytes(char *dst, const char *src, uint64_t n)
+{
+    for (uint64_t k = 0; k < n; k++) {
+        dst[k] = src[k];
     }
 }
 
@@ -1144,7 +1199,8 @@ MSPB_DEVFN void resolve_site(const TreeSeqView &ts, const KeptView &kept, const 
     for (uint64_t j = first; j < end; j++) {
         const uint32_t r = sv.val[j];
         const bool is_new = !sv.has_kept || r >= KM;
-        const uint32_t opens = (j == i) ? 1u : 0u; // a new site's first record also takes the root draw
+        // a new site's first record also takes the root draw
+        const uint32_t opens = (j == i && sv.root_draw) ? 1u : 0u;
         if (sv.has_kept) {
             sv.draw_scan[j] = cur;
         }
@@ -1210,6 +1266,28 @@ MSPB_DEVFN void resolve_site(const TreeSeqView &ts, const KeptView &kept, const 
                 }
             }
             rv.state[j] = st;
+        } else if (model.kind == 2) {
+            // SLiM: lengths of the stacked derived state and metadata (lib/mutgen.c:355-413); K5
+            // materialises them by walking the same parent chain
+            int32_t dl, ml;
+            if (!is_new) {
+                const uint64_t km = r - S0;
+                dl = (int32_t) (kept.mut_der_off[km + 1] - kept.mut_der_off[km]);
+                ml = (int32_t) (kept.mut_md_off[km + 1] - kept.mut_md_off[km]);
+            } else {
+                int32_t bl = 0, bm = 0;
+                if (par >= 0) {
+                    bl = rv.state[par];
+                    bm = rv.site_state[par];
+                } else if (kept_site) {
+                    bl = (int32_t) (kept.site_anc_off[r0 + 1] - kept.site_anc_off[r0]);
+                    bm = (int32_t) (kept.site_md_off[r0 + 1] - kept.site_md_off[r0]);
+                }
+                dl = bl + (bl > 0 ? 1 : 0) + (int32_t) num_digits(model.start_allele + cur);
+                ml = bm + SLIM_MD_SIZE;
+            }
+            rv.state[j] = dl;
+            rv.site_state[j] = ml;
         }
         cur += (is_new ? 1u : 0u) + opens;
         tmax = fmax(tmax, node_t);
@@ -1217,53 +1295,6 @@ MSPB_DEVFN void resolve_site(const TreeSeqView &ts, const KeptView &kept, const 
 }
 
 // ---------------------------------------------------------------- K5
-// decimal length of v (snprintf "%" PRIu64, lib/mutgen.c:431-447); allele numbers are
-// almost always below 2^32, where 32-bit compares and divisions are much cheaper
-MSPB_DEVFN uint32_t num_digits32(uint32_t v)
-{
-    return v < 100000u ? (v < 100u ? (v < 10u ? 1u : 2u) : (v < 1000u ? 3u : (v < 10000u ? 4u : 5u)))
-                       : (v < 10000000u ? (v < 1000000u ? 6u : 7u)
-                                        : (v < 100000000u ? 8u : (v < 1000000000u ? 9u : 10u)));
-}
-
-MSPB_DEVFN uint32_t num_digits(uint64_t v)
-{
-    if (v <= 0xffffffffull) {
-        return num_digits32((uint32_t) v);
-    }
-    uint32_t n = 9; // v >= 2^32 > 10^9: the low nine digits are full
-    v /= 1000000000ull;
-    while (v > 0xffffffffull) {
-        v /= 1000000000ull;
-        n += 9;
-    }
-    return n + num_digits32((uint32_t) v);
-}
-
-MSPB_DEVFN void write_digits(char *dst, uint64_t v, uint32_t n)
-{
-    uint32_t k = n;
-    while (v > 0xffffffffull) {
-        uint32_t low = (uint32_t) (v % 1000000000ull);
-        v /= 1000000000ull;
-        for (int d = 0; d < 9; d++) {
-            dst[--k] = (char) ('0' + (low % 10u));
-            low /= 10u;
-        }
-    }
-    uint32_t w = (uint32_t) v;
-    while (k > 0) {
-        dst[--k] = (char) ('0' + (w % 10u));
-        w /= 10u;
-    }
-}
-
-MSPB_DEVFN void copy_bytes(char *dst, const char *src, uint64_t n)
-{
-    for (uint64_t k = 0; k < n; k++) {
-        dst[k] = src[k];
-    }
-}
 
 struct OutView {
     double *site_position;
@@ -1283,6 +1314,7 @@ struct OutView {
     const uint64_t *dev_bases;
     int off32; // offset columns are uint32 (else uint64)
     int write_md_off; // 0: the metadata offset columns are known to be all zero already
+    int dry_run; // K5 computes the byte totals only (sizing pass of the SLiM model)
     MSPB_DEVFN void store_off(void *col, uint64_t row, uint64_t v) const
     {
         if (off32) {

@@ -187,6 +187,10 @@ extern "C" const char *mspb_strerror(int err)
             return "Root probabilities must be nonnegative and sum to one.";
         case MSPB_ERR_BAD_TRANSITION_MATRIX:
             return "Each row of the transition matrix must be nonnegative and sum to one.";
+        case MSPB_ERR_BAD_SLIM_PARAMETERS:
+            return "SLiM mutation IDs and mutation type IDs must be nonnegative.";
+        case MSPB_ERR_MUTATION_ID_OVERFLOW:
+            return "Mutation ID overflow.";
         case MSPB_ERR_UNKNOWN_TIME_NOT_SUPPORTED:
             return "Kept mutations must have known mutation times (which can be added using "
                    "compute_mutation_times).";
@@ -710,6 +714,10 @@ int check_model(const mspb_params_t *p)
     if (p->model_kind == MSPB_MODEL_INFINITE_ALLELES) {
         return 0;
     }
+    if (p->model_kind == MSPB_MODEL_SLIM) {
+        /* slim_mutator_check_validity, lib/mutgen.c:326-343 */
+        return ((int64_t) p->start_allele < 0 || p->slim_mutation_type_id < 0) ? MSPB_ERR_BAD_SLIM_PARAMETERS : 0;
+    }
     if (p->model_kind != MSPB_MODEL_MATRIX) {
         return MSPB_ERR_BAD_PARAM_VALUE;
     }
@@ -788,6 +796,8 @@ int upload_params(mspb_ctx *ctx, const mspb_params_t *p, RateMapView *map, Model
 
     model->kind = p->model_kind;
     model->start_allele = p->start_allele;
+    model->slim_type = p->slim_mutation_type_id;
+    model->slim_generation = p->slim_generation;
     model->num_alleles = 0;
     model->alleles = nullptr;
     model->allele_off = nullptr;
@@ -927,6 +937,9 @@ uint64_t max_new_state_len(const mspb_params_t *p, uint64_t Mnew)
         }
         return m;
     }
+    if (p->model_kind == MSPB_MODEL_SLIM) {
+        return 20; /* first guess only: the sizing pass of K5 gives the exact totals */
+    }
     const uint64_t last = p->start_allele + 2 * Mnew + 1;
     return last < p->start_allele ? 20 : digits_u64(last); /* 20 digits if the counter wraps */
 }
@@ -946,7 +959,7 @@ int launch_emit(mspb_ctx *ctx)
     LbWord *lb4 = nullptr;
     TRY(lookback_state(ctx, k5_tiles, 2, &lb4));
     const bool kept_rows = ctx->pending.sv.has_kept != 0, off32 = ctx->pending.out.off32 != 0;
-    const int model_kind = ctx->pending.model.kind != 0 ? 1 : 0;
+    const int model_kind = ctx->pending.model.kind;
 #define MSPB_K5(M, K, O)                                                                                             \
     MSPB_LAUNCH(ctx->log, "k5_emit",                                                                                 \
         (k5_emit_kernel<M, K, O><<<k5_tiles, K5_THREADS, 0, st>>>(ctx->pending.sv, ctx->pending.rv,                \
@@ -966,8 +979,10 @@ int launch_emit(mspb_ctx *ctx)
     }
     if (model_kind == 0) {
         MSPB_K5_MODEL(0)
-    } else {
+    } else if (model_kind == 1) {
         MSPB_K5_MODEL(1)
+    } else {
+        MSPB_K5_MODEL(2)
     }
 #undef MSPB_K5_MODEL
 #undef MSPB_K5
@@ -988,6 +1003,7 @@ int run_sorted_stages(mspb_ctx *ctx, const mspb_params_t *p, const TreeSeqView &
     sv.M0 = M0;
     sv.rec = ctx->rec.p;
     sv.has_kept = (S0 + M0) > 0 ? 1 : 0;
+    sv.root_draw = p->model_kind != MSPB_MODEL_SLIM ? 1 : 0;
     sv.site_row = ctx->site_scan.p;
     sv.mut_scan = ctx->mut_scan.p;
     sv.draw_scan = ctx->draw_scan.p;
@@ -1270,7 +1286,15 @@ static int generate_impl(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t 
         = (defer && p->model_kind == MSPB_MODEL_INFINITE_ALLELES) ? 20 : max_new_state_len(p, Mnew);
     const uint64_t der_cap = (keep ? ctx->kept_der_bytes : 0) + Mnew * maxlen;
     const uint64_t anc_cap = (keep ? ctx->kept_anc_bytes : 0) + Mnew * maxlen;
-    const uint64_t smd_cap = keep ? ctx->kept_smd_bytes : 0, mmd_cap = keep ? ctx->kept_mmd_bytes : 0;
+    const bool slim = p->model_kind == MSPB_MODEL_SLIM;
+    if (slim && defer) {
+        return MSPB_ERR_BAD_PARAM_VALUE; /* the SLiM model's ids feed its byte counts: single call only */
+    }
+    if (slim && Mnew > 0 && p->start_allele + Mnew - 1 >= (uint64_t) INT64_MAX) {
+        return MSPB_ERR_MUTATION_ID_OVERFLOW; /* lib/mutgen.c:386-389 */
+    }
+    const uint64_t smd_cap = keep ? ctx->kept_smd_bytes : 0,
+                   mmd_cap = (keep ? ctx->kept_mmd_bytes : 0) + (slim ? Mnew * SLIM_MD_SIZE : 0);
     TRY(ctx->rec.ensure(R + 1));
     TRY(ensure_sort_buffers(ctx, R, call.key_mode == KEY32_POS, call.key_mode != KEY32_POS));
     TRY(ctx->site_scan.ensure(R + 1));
@@ -1335,6 +1359,10 @@ static int generate_impl(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t 
     out.site_base = 0;
     out.mut_base = 0;
     out.dev_bases = nullptr;
+    out.dry_run = 0;
+    if (slim) {
+        ctx->pending.defer = true; // K5 runs below, after its sizing pass
+    }
 
     // ---- K2: records (kept markers, kept mutations, new mutations) and their sort keys
     KeyView keys;
@@ -1428,6 +1456,34 @@ static int generate_impl(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t 
     if (ht->collisions > 0) {
         return MSPB_ERR_REPLAY_REDRAW;
     }
+    if (slim && R > 0) {
+        // SLiM: state and metadata stack along parent chains, so their totals are not bounded
+        // up front: K5 first runs as a sizing pass (lengths and scan only), then for real
+        ctx->pending.out.dry_run = 1;
+        TRY(launch_emit(ctx));
+        ctx->pending.out.dry_run = 0;
+        CUDA_OK(cudaMemcpyAsync(ht, dt, sizeof(HostTotals), cudaMemcpyDeviceToHost, st));
+        CUDA_OK(cudaStreamSynchronize(st));
+        if (off32 && (ht->bytes.der >= 0xffffffffull || ht->bytes.mmd >= 0xffffffffull)) {
+            return MSPB_ERR_OFFSET_OVERFLOW;
+        }
+        TRY(ctx->o_mut_der.ensure(ht->bytes.der + 1));
+        TRY(ctx->o_mut_md.ensure(ht->bytes.mmd + 1));
+        ctx->pending.out.mut_der = ctx->o_mut_der.p;
+        ctx->pending.out.mut_md = ctx->o_mut_md.p;
+        TRY(launch_emit(ctx));
+        CUDA_OK(cudaMemcpyAsync(ht, dt, sizeof(HostTotals), cudaMemcpyDeviceToHost, st));
+        CUDA_OK(cudaEventRecord(ctx->ev[8], st));
+        CUDA_OK(cudaStreamSynchronize(st));
+        CUDA_OK(cudaGetLastError());
+        ctx->log.collect();
+        if (ht->err != 0) {
+            return ht->err;
+        }
+    }
+    if (slim) {
+        defer = false;
+    }
     const uint64_t draws = ht->p1.d;
     if (replay && p->model_kind == MSPB_MODEL_MATRIX && ht->replay.draws + draws > p->replay_len) {
         return MSPB_ERR_REPLAY_STREAM_EXHAUSTED;
@@ -1448,7 +1504,7 @@ static int generate_impl(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t 
     c.derived_state_bytes = ht->bytes.der;
     c.mutation_metadata_bytes = ht->bytes.mmd;
     c.num_new_sites = S - S0;
-    c.next_allele = p->start_allele + (p->model_kind == MSPB_MODEL_INFINITE_ALLELES ? draws : 0);
+    c.next_allele = p->start_allele + (p->model_kind != MSPB_MODEL_MATRIX ? draws : 0);
     c.draws = replay ? ht->replay.draws + (p->model_kind == MSPB_MODEL_MATRIX ? draws : 0) : 0;
     c.device_ms = total;
     c.offset_bytes = ow;

@@ -50,6 +50,8 @@
 #define E_UNKNOWN_ALLELE (-51)
 #define E_INSUFFICIENT_ALLELES (-52)
 #define E_BAD_ROOT_PROBABILITIES (-53)
+#define E_BAD_SLIM_PARAMETERS (-56)
+#define E_MUTATION_ID_OVERFLOW (-57)
 #define E_BAD_TRANSITION_MATRIX (-54)
 #define E_UNKNOWN_TIME_NOT_SUPPORTED (-69)
 #define TSK_E(code) ((code) ^ (1 << 13))
@@ -113,6 +115,9 @@ typedef struct {
     uint64_t arena_len, arena_cap;
     uint64_t next_allele;
     uint64_t seq;
+    /* SLiM model: every new state and metadata string is its own allocation */
+    char **slim_strings;
+    uint64_t num_slim_strings, cap_slim_strings;
 } port_t;
 
 static double
@@ -168,6 +173,10 @@ static int
 check_model(const orc_input_t *in)
 {
     size_t i;
+    if (in->model_kind == ORC_MODEL_SLIM) {
+        /* lib/mutgen.c:326-343 */
+        return ((int64_t) in->start_allele < 0 || in->slim_mutation_type_id < 0) ? E_BAD_SLIM_PARAMETERS : 0;
+    }
     if (in->model_kind != ORC_MODEL_MATRIX) {
         return 0;
     }
@@ -580,6 +589,76 @@ make_allele(port_t *self, const char **dest, uint64_t *len)
     return 0;
 }
 
+/* SLiM model (lib/mutgen.c:257-413): the derived state is the parent's state, a comma if
+ * that is not empty, and the next mutation id in decimal; the metadata is the parent's
+ * metadata plus one 17-byte MutationMetadataRec (type id, selection coefficient 0, subpopulation
+ * -1, origin generation = slim_generation - (int32) time, nucleotide -1). */
+#define SLIM_MD_SIZE 17
+
+static char *
+slim_alloc(port_t *self, uint64_t n)
+{
+    char *b;
+    if (self->num_slim_strings == self->cap_slim_strings) {
+        uint64_t cap = self->cap_slim_strings == 0 ? 1024 : 2 * self->cap_slim_strings;
+        char **g = realloc(self->slim_strings, cap * sizeof(*g));
+        if (g == NULL) {
+            return NULL;
+        }
+        self->slim_strings = g;
+        self->cap_slim_strings = cap;
+    }
+    b = malloc(n > 0 ? n : 1);
+    if (b != NULL) {
+        self->slim_strings[self->num_slim_strings++] = b;
+    }
+    return b;
+}
+
+static int
+slim_transition(port_t *self, const char *pa, uint64_t palen, const char *pm, uint64_t pmlen, rec_t *mut)
+{
+    const orc_input_t *in = self->in;
+    char digits[32], *buff;
+    int n = snprintf(digits, sizeof(digits), "%lld", (long long) (int64_t) self->next_allele);
+    uint64_t len = palen + (palen > 0 ? 1 : 0) + (uint64_t) n;
+    int32_t type_id = in->slim_mutation_type_id, subpop = -1;
+    int32_t origin = in->slim_generation - (int32_t) mut->time;
+    float sel = 0;
+    int8_t nuc = -1;
+
+    buff = slim_alloc(self, len);
+    if (buff == NULL) {
+        return E_NO_MEMORY;
+    }
+    if (palen > 0) {
+        memcpy(buff, pa, palen);
+        buff[palen] = ',';
+    }
+    memcpy(buff + len - (uint64_t) n, digits, (size_t) n);
+    if ((int64_t) self->next_allele == INT64_MAX) {
+        return E_MUTATION_ID_OVERFLOW;
+    }
+    self->next_allele++;
+    mut->state = buff;
+    mut->state_len = len;
+    buff = slim_alloc(self, pmlen + SLIM_MD_SIZE);
+    if (buff == NULL) {
+        return E_NO_MEMORY;
+    }
+    if (pmlen > 0) {
+        memcpy(buff, pm, pmlen);
+    }
+    memcpy(buff + pmlen, &type_id, 4);
+    memcpy(buff + pmlen + 4, &sel, 4);
+    memcpy(buff + pmlen + 8, &subpop, 4);
+    memcpy(buff + pmlen + 12, &origin, 4);
+    memcpy(buff + pmlen + 16, &nuc, 1);
+    mut->meta = buff;
+    mut->meta_len = pmlen + SLIM_MD_SIZE;
+    return 0;
+}
+
 static int
 allele_index(const orc_input_t *in, const char *a, uint64_t len)
 {
@@ -610,6 +689,9 @@ resolve_site(port_t *self, srec_t *site, const int32_t *parent, int64_t *bottom)
             size_t j = select_prob(u, in->num_alleles, in->root_distribution);
             site->anc = in->alleles + in->allele_offset[j];
             site->anc_len = in->allele_offset[j + 1] - in->allele_offset[j];
+        } else if (in->model_kind == ORC_MODEL_SLIM) {
+            site->anc = NULL; /* lib/mutgen.c:346-353: the empty string, no draw */
+            site->anc_len = 0;
         } else {
             ret = make_allele(self, &site->anc, &site->anc_len);
             if (ret != 0) {
@@ -619,8 +701,8 @@ resolve_site(port_t *self, srec_t *site, const int32_t *parent, int64_t *bottom)
     }
     for (k = 0; k < site->count; k++) {
         rec_t *mut = &recs[k];
-        const char *pa;
-        uint64_t palen;
+        const char *pa, *pmd;
+        uint64_t palen, pmdlen;
         int32_t u = mut->node;
         while (u != -1 && bottom[u] < 0) {
             u = parent[u];
@@ -628,11 +710,15 @@ resolve_site(port_t *self, srec_t *site, const int32_t *parent, int64_t *bottom)
         if (u == -1) {
             pa = site->anc;
             palen = site->anc_len;
+            pmd = site->meta; /* lib/mutgen.c:1190-1194: the SITE's metadata stands in */
+            pmdlen = site->meta_len;
         } else {
             rec_t *pm = &self->recs[bottom[u]];
             mut->parent = bottom[u];
             pa = pm->state;
             palen = pm->state_len;
+            pmd = pm->meta;
+            pmdlen = pm->meta_len;
         }
         if (mut->kept_id < 0) {
             if (in->model_kind == ORC_MODEL_MATRIX) {
@@ -647,6 +733,11 @@ resolve_site(port_t *self, srec_t *site, const int32_t *parent, int64_t *bottom)
                     in->transition_matrix + (uint64_t) pi * in->num_alleles);
                 mut->state = in->alleles + in->allele_offset[j];
                 mut->state_len = in->allele_offset[j + 1] - in->allele_offset[j];
+            } else if (in->model_kind == ORC_MODEL_SLIM) {
+                ret = slim_transition(self, pa, palen, pmd, pmdlen, mut);
+                if (ret != 0) {
+                    break;
+                }
             } else {
                 ret = make_allele(self, &mut->state, &mut->state_len);
                 if (ret != 0) {
@@ -939,6 +1030,13 @@ out:
     free(self.recs);
     free(self.pos_set);
     free(self.arena);
+    {
+        uint64_t q;
+        for (q = 0; q < self.num_slim_strings; q++) {
+            free(self.slim_strings[q]);
+        }
+        free(self.slim_strings);
+    }
     if (ret != 0) {
         int32_t ex = out->stream_exhausted;
         uint64_t dr = out->draws;

@@ -26,6 +26,7 @@ PORT_SO = os.path.join(HERE, "_build", "libmutgen_port.so")
 
 MODEL_MATRIX = 0
 MODEL_INFINITE_ALLELES = 1
+MODEL_SLIM = 2
 
 _dp = C.POINTER(C.c_double)
 _ip = C.POINTER(C.c_int32)
@@ -75,6 +76,8 @@ class _Input(C.Structure):
         ("seed", C.c_uint32),
         ("stream", C.c_void_p),
         ("stream_len", C.c_uint64),
+        ("slim_mutation_type_id", C.c_int32),
+        ("slim_generation", C.c_int32),
     ]
 
 
@@ -252,6 +255,12 @@ def sim_mutations(
     elif model["kind"] == "infinite_alleles":
         inp.model_kind = MODEL_INFINITE_ALLELES
         inp.start_allele = int(model.get("start_allele", 0)) & 0xFFFFFFFFFFFFFFFF
+    elif model["kind"] == "slim":
+        # {"kind": "slim", "type": mutation type id, "next_id": ..., "slim_generation": ...}
+        inp.model_kind = MODEL_SLIM
+        inp.start_allele = int(model.get("next_id", 0)) & 0xFFFFFFFFFFFFFFFF
+        inp.slim_mutation_type_id = int(model["type"])
+        inp.slim_generation = int(model.get("slim_generation", 1))
     else:
         raise ValueError("unknown model kind")
 

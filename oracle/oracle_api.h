@@ -18,7 +18,7 @@
 extern "C" {
 #endif
 
-enum { ORC_MODEL_MATRIX = 0, ORC_MODEL_INFINITE_ALLELES = 1 };
+enum { ORC_MODEL_MATRIX = 0, ORC_MODEL_INFINITE_ALLELES = 1, ORC_MODEL_SLIM = 2 };
 enum { ORC_RNG_MT19937 = 0, ORC_RNG_REPLAY = 1 };
 
 typedef struct {
@@ -68,13 +68,16 @@ typedef struct {
     uint32_t seed;
     const double *stream;
     uint64_t stream_len;
+    /* SLiM model (lib/mutgen.c:552-589): start_allele is next_mutation_id on entry */
+    int32_t slim_mutation_type_id;
+    int32_t slim_generation;
 } orc_input_t;
 
 typedef struct {
     int32_t status; /* 0 or a negative MSP_ERR_ code (lib/util.h:48-136 numbering) */
     int32_t stream_exhausted;
     uint64_t draws; /* uniforms consumed */
-    uint64_t next_allele; /* infinite alleles: counter after the call */
+    uint64_t next_allele; /* infinite alleles / SLiM: allele or mutation-id counter after the call */
     double seconds; /* wall time of the generate step alone */
     uint64_t num_sites;
     double *site_position;

@@ -85,6 +85,9 @@ build_model(const orc_input_t *in, mutation_model_t *model)
 
     if (in->model_kind == ORC_MODEL_INFINITE_ALLELES) {
         return infinite_alleles_mutation_model_alloc(model, in->start_allele, 0);
+    } else if (in->model_kind == ORC_MODEL_SLIM) {
+        return slim_mutation_model_alloc(model, in->slim_mutation_type_id, (int64_t) in->start_allele,
+            in->slim_generation, 0);
     } else {
         char **alleles = calloc(in->num_alleles + 1, sizeof(*alleles));
         size_t *lengths = calloc(in->num_alleles + 1, sizeof(*lengths));
@@ -204,6 +207,8 @@ orc_sim_mutations(const orc_input_t *in, orc_output_t *out)
     }
     if (in->model_kind == ORC_MODEL_INFINITE_ALLELES) {
         out->next_allele = model.params.infinite_alleles.next_allele;
+    } else if (in->model_kind == ORC_MODEL_SLIM) {
+        out->next_allele = (uint64_t) model.params.slim_mutator.next_mutation_id;
     }
     ret = export_tables(&tables, out);
 out:

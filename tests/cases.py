@@ -55,7 +55,10 @@ MULTICHAR = {"kind": "matrix", "alleles": ["", "AA", "\U0001F4A9", "x" * 17], "r
              "transition_matrix": [[0.1, 0.2, 0.3, 0.4], [0.25, 0.25, 0.25, 0.25], [0.0, 0.5, 0.0, 0.5],
                                    [0.4, 0.3, 0.2, 0.1]]}
 INF_ALLELES = {"kind": "infinite_alleles", "start_allele": 0}
-MODELS = {"jc69": JC69, "jc69_si": JC69_SI, "binary": BINARY, "multichar": MULTICHAR, "infinite_alleles": INF_ALLELES}
+# SLiMMutationModel(type=1, next_id=7, slim_generation=50), msprime/mutations.py:109-151
+SLIM = {"kind": "slim", "type": 1, "next_id": 7, "slim_generation": 50}
+MODELS = {"jc69": JC69, "jc69_si": JC69_SI, "binary": BINARY, "multichar": MULTICHAR, "infinite_alleles": INF_ALLELES,
+          "slim": SLIM}
 
 
 def with_kept(ts, result):
@@ -67,6 +70,9 @@ def with_kept(ts, result):
 
 def native_model(m):
     """oracle-style model dict -> msprime_b200._native model dict"""
+    if m["kind"] == "slim":
+        return {"kind": 2, "type": m["type"], "next_id": m.get("next_id", 0),
+                "slim_generation": m.get("slim_generation", 1)}
     if m["kind"] == "matrix":
         return {"kind": 0, "alleles": m["alleles"], "root_distribution": m["root_distribution"],
                 "transition_matrix": m["transition_matrix"]}

@@ -55,7 +55,7 @@ def all_cases():
     # recombining input: models x genome x window, then a second layer with keep
     smc = ("smc", 20, 2e4, 2)
     L = 2e4
-    for model in ("jc69", "binary", "infinite_alleles", "multichar"):
+    for model in ("jc69", "binary", "infinite_alleles", "multichar", "slim"):
         for discrete in (True, False):
             for window in (None, WINDOW):
                 tag = f"smc-{model}-{'d' if discrete else 'c'}-{'w' if window else 'a'}"

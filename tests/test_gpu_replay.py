@@ -73,7 +73,7 @@ def test_four_leaf_tree(ctx, oracle_mod, model, discrete, rate):
                discrete=discrete)
 
 
-@pytest.mark.parametrize("model", ["jc69", "binary", "infinite_alleles", "multichar"])
+@pytest.mark.parametrize("model", ["jc69", "binary", "infinite_alleles", "multichar", "slim"])
 @pytest.mark.parametrize("discrete", [True, False])
 @pytest.mark.parametrize("rate", [1e-8, 1e-6, 2e-5])
 @pytest.mark.parametrize("window", [None, (1e3, 2e4)])
