@@ -15,6 +15,7 @@ from .mutations import (  # noqa: F401
     LibraryError,
     MatrixMutationModel,
     MutationModel,
+    SLiMMutationModel,
     mutate,
     mutation_model_factory,
     sim_mutations,

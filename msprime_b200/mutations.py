@@ -107,6 +107,7 @@ _MESSAGES = {
     -52: "Must have at least two alleles.",
     -53: "Root probabilities must be nonnegative and sum to one.",
     -54: "Each row of the transition matrix must be nonnegative and sum to one.",
+    -56: "SLiM mutation IDs and mutation type IDs must be nonnegative.",
 }
 
 
@@ -136,6 +137,49 @@ class InfiniteAlleles(MutationModel):
         return (
             f"Infinite alleles mutation model, beginning with allele"
             f" {self.start_allele}\n    next allele: {self.next_allele}\n"
+        )
+
+
+class SLiMMutationModel(MutationModel):
+    """An infinite-alleles model producing "SLiM-style" mutations (``msprime/mutations.py:109-151``,
+    ``lib/mutgen.c:257-413``): a new site's ancestral state is the empty string, a derived
+    state is the parent's state with the next mutation id appended after a comma, and the
+    metadata stacks one 17-byte ``MutationMetadataRec`` per mutation (mutation type ``type``,
+    selection coefficient 0, subpopulation -1, origin generation ``slim_generation -
+    floor(time)``, nucleotide -1).  The id counter lives on the model object and persists
+    across calls (``_msprimemodule.c:748-760``).  ``block_size`` is accepted for
+    compatibility; the device path has no block allocator."""
+
+    def __init__(self, type, next_id=0, slim_generation=1, block_size=0):  # noqa: A002
+        for name, v in (("type", type), ("next_id", next_id), ("slim_generation", slim_generation),
+                        ("block_size", block_size)):
+            if isinstance(v, bool) or not isinstance(v, (int, np.integer)):
+                raise TypeError(f"{name} must be an integer")
+        if not -2**63 <= int(next_id) < 2**63 or not -2**31 <= int(type) < 2**31 \
+                or not -2**31 <= int(slim_generation) < 2**31:
+            raise OverflowError("SLiM model parameter out of range")
+        if int(next_id) < 0 or int(type) < 0:
+            # slim_mutator_check_validity, lib/mutgen.c:326-343 (MSP_ERR_BAD_SLIM_PARAMETERS)
+            raise _native.LibraryError(_native_message(-56))
+        self._type = int(type)
+        self._next_id = int(next_id)
+        self._slim_generation = int(slim_generation)
+
+    type = property(lambda self: self._type)  # noqa: A003
+    next_id = property(lambda self: self._next_id)
+    slim_generation = property(lambda self: self._slim_generation)
+
+    def _native(self):
+        return {"kind": _native.MODEL_SLIM, "type": self._type, "next_id": self._next_id,
+                "slim_generation": self._slim_generation}
+
+    def asdict(self):
+        return {"type": self._type, "next_id": self._next_id, "slim_generation": self._slim_generation}
+
+    def __str__(self):
+        return (
+            f"Mutation model for SLiM mutations of type m{self.type}\n"
+            f"  next ID: {self.next_id}\n"
         )
 
 
@@ -305,6 +349,8 @@ def _overlay(ctx, tables_dict, *, rate_map, model, discrete_genome, keep, start_
     counts = ctx.generate(params)
     if isinstance(model, InfiniteAlleles):
         model._next_allele = counts["next_allele"]
+    elif isinstance(model, SLiMMutationModel):
+        model._next_id = counts["next_allele"]
     return ctx.fetch(), counts
 
 

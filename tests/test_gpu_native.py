@@ -286,3 +286,63 @@ def test_python_surface_layers_and_provenance(native_built, ts_small):
     assert ia.next_allele == e.num_sites + e.num_mutations
     f = msp.mutate(ts, rate=2e-7, random_seed=6)
     assert set(f.alleles()[0]) == {"0"} and set(f.alleles()[1]) <= {"0", "1"}
+
+
+def test_slim_model_native_stream(ctx, ts_small):
+    """SLiMMutationModel on the native stream (tests/test_mutations.py:1554-1696): empty
+    ancestral states, ids numbered in table order, stacked derived states = the chain of ids up
+    to the root, 17 bytes of metadata per stacked id; a second layer stacks onto kept states."""
+    import struct
+
+    L = ts_small["sequence_length"]
+    m1 = {"kind": "slim", "type": 2, "next_id": 100, "slim_generation": 7}
+    first, c1 = run(ctx, ts_small, model=m1, rate=2e-6, seed=41)
+    M = c1["num_mutations"]
+    assert M > 500 and c1["next_allele"] == 100 + M and c1["ancestral_state_bytes"] == 0
+    table_checks.check_result(ts_small, first, discrete=True)
+    ds = table_checks.ragged(first["mutations"]["derived_state"], first["mutations"]["derived_state_offset"])
+    md = table_checks.ragged(first["mutations"]["metadata"], first["mutations"]["metadata_offset"])
+    par = first["mutations"]["parent"]
+    t = first["mutations"]["time"]
+    for j in range(M):
+        ids = [int(x) for x in bytes(ds[j]).decode().split(",")]
+        assert ids[-1] == 100 + j  # own id last, numbered in row order
+        assert len(bytes(md[j])) == 17 * len(ids)
+        if par[j] >= 0:
+            assert bytes(ds[j]).decode().rsplit(",", 1)[0] == bytes(ds[par[j]]).decode()
+            assert bytes(md[j])[:-17] == bytes(md[par[j]])
+        else:
+            assert len(ids) == 1
+        ty, sel, sub, origin, nuc = struct.unpack("<ifiib", bytes(md[j])[-17:])
+        assert (ty, sel, sub, nuc) == (2, 0.0, -1, -1) and origin == 7 - int(t[j])
+    assert (par >= 0).sum() > 0  # the rate stacks some mutations
+    # second layer on top: ids continue, stacked onto kept states where a kept mutation is above
+    ts2 = cases.with_kept(ts_small, first)
+    m2 = dict(m1, next_id=c1["next_allele"], type=5)
+    second, c2 = run(ctx, ts2, model=m2, rate=2e-6, seed=42, keep=True)
+    assert c2["next_allele"] == c1["next_allele"] + c2["num_new_mutations"]
+    ds2 = table_checks.ragged(second["mutations"]["derived_state"], second["mutations"]["derived_state_offset"])
+    md2 = table_checks.ragged(second["mutations"]["metadata"], second["mutations"]["metadata_offset"])
+    par2 = second["mutations"]["parent"]
+    seen_new = 0
+    for j in range(c2["num_mutations"]):
+        ids = bytes(ds2[j]).decode().split(",")
+        assert len(bytes(md2[j])) == 17 * len(ids)
+        if int(ids[-1]) >= c1["next_allele"]:
+            seen_new += 1
+            if par2[j] >= 0:
+                assert ",".join(ids[:-1]) == bytes(ds2[par2[j]]).decode()
+    assert seen_new == c2["num_new_mutations"]
+    # bad parameters surface the reference's error (lib/mutgen.c:326-343)
+    with pytest.raises(_native.LibraryError, match="nonnegative"):
+        run(ctx, ts_small, model=dict(m1, type=-1), rate=1e-6, seed=1)
+
+
+def test_slim_model_python_surface(native_built, ts_small):
+    ts = mtables.TableCollection.fromdict(ts_small).tree_sequence()
+    model = msp.SLiMMutationModel(type=1, next_id=5)
+    a = msp.sim_mutations(ts, rate=2e-7, random_seed=8, model=model)
+    assert a.num_mutations > 0 and model.next_id == 5 + a.num_mutations
+    b = msp.sim_mutations(a, rate=2e-7, random_seed=9, model=model)
+    assert model.next_id == 5 + b.num_mutations
+

@@ -140,3 +140,19 @@ def test_infinite_alleles_start():
     assert m.start_allele == 7 and m.next_allele == 7
     with pytest.raises(OverflowError):
         msp.InfiniteAlleles(start_allele=-1)
+
+
+def test_slim_model_parameters():
+    # msprime/mutations.py:109-151, tests/test_mutations.py:1554-1600
+    m = msp.SLiMMutationModel(type=3, next_id=11, slim_generation=40)
+    assert (m.type, m.next_id, m.slim_generation) == (3, 11, 40)
+    assert "m3" in str(m) and "next ID: 11" in str(m)
+    assert m._native() == {"kind": 2, "type": 3, "next_id": 11, "slim_generation": 40}
+    assert msp.SLiMMutationModel(type=0).next_id == 0
+    for bad in (dict(type=-1), dict(type=1, next_id=-5)):
+        with pytest.raises(msp.LibraryError, match="nonnegative"):
+            msp.SLiMMutationModel(**bad)
+    with pytest.raises(TypeError):
+        msp.SLiMMutationModel(type="m1")
+    with pytest.raises(OverflowError):
+        msp.SLiMMutationModel(type=1, next_id=2**63)
