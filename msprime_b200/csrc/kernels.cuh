@@ -45,11 +45,15 @@ struct TreeSeqView {
 struct __align__(32) ChildIv {
     double left, right;
     double parent_time;
-    // the parent, named by the range of its own entries [child_start[p], child_start[p + 1]);
-    // a parent that is a child nowhere is (CI_NONE, p).  The pair identifies the node.
-    uint32_t parent_start, parent_end;
+    // The parent.  parent_id identifies the node: child_start[p] when p has entries of its own,
+    // CI_NODE | p when it is a child nowhere.  parent_span names the parent's entries that
+    // OVERLAP [left, right) (k0_link_kernel): (first - child_start[p]) << 8 | count, so a step
+    // of the walk usually probes one entry; CI_SPAN_UNKNOWN when that does not fit (the walk
+    // then recovers the parent's full range from child_start).
+    uint32_t parent_id, parent_span;
 };
-constexpr uint32_t CI_NONE = 0xffffffffu;
+constexpr uint32_t CI_NODE = 0x80000000u;
+constexpr uint32_t CI_SPAN_UNKNOWN = 0xffffffffu;
 
 struct KeptView {
     uint64_t num_sites, num_mutations; // 0 when keep is off
@@ -168,8 +172,8 @@ __global__ void k0_permute_kernel(TreeSeqView ts, const uint32_t *perm, ChildIv 
         const uint32_t c = (uint32_t) ts.edge_child[e];
         const uint32_t p = (uint32_t) ts.edge_parent[e];
         iv.parent_time = ts.node_time[p];
-        iv.parent_start = CI_NONE; // k0_link_kernel replaces the pair by the parent's range
-        iv.parent_end = p;
+        iv.parent_id = p; // k0_link_kernel replaces the pair by (identity, overlapping entries)
+        iv.parent_span = 0;
         ci[i] = iv;
         // CSR starts: child c begins at the first i whose child is >= c
         const uint32_t prev = i == 0 ? 0u : (uint32_t) ts.edge_child[perm[i - 1]] + 1u;
@@ -184,34 +188,64 @@ __global__ void k0_permute_kernel(TreeSeqView ts, const uint32_t *perm, ChildIv 
     }
 }
 
-__global__ void k0_link_kernel(TreeSeqView ts, ChildIv *ci)
+// max_count: spans with more overlapping entries are stored as CI_SPAN_UNKNOWN (256 in
+// production; tests lower it to drive the recovery path of the walk)
+__global__ void k0_link_kernel(TreeSeqView ts, ChildIv *ci, uint32_t max_count)
 {
     const uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
     if (i < ts.num_edges) {
-        const uint32_t p = ci[i].parent_end;
+        const uint32_t p = ci[i].parent_id;
         const uint32_t a = ts.child_start[p], b = ts.child_start[p + 1];
-        if (a < b) {
-            ci[i].parent_start = a;
-            ci[i].parent_end = b;
+        if (a >= b) {
+            ci[i].parent_id = CI_NODE | p;
+            return;
         }
+        const double l = ci[i].left, r = ci[i].right;
+        // first entry of p that ends after l, first entry of p that starts at or after r
+        uint32_t lo = a, hi = b;
+        while (lo < hi) {
+            const uint32_t mid = (lo + hi) >> 1;
+            if (ci[mid].right <= l) {
+                lo = mid + 1;
+            } else {
+                hi = mid;
+            }
+        }
+        const uint32_t f = lo;
+        hi = b;
+        while (lo < hi) {
+            const uint32_t mid = (lo + hi) >> 1;
+            if (ci[mid].left < r) {
+                lo = mid + 1;
+            } else {
+                hi = mid;
+            }
+        }
+        const uint32_t count = lo - f;
+        ci[i].parent_id = a;
+        ci[i].parent_span = (f - a < 0xffffffu && count < max_count) ? ((f - a) << 8 | count) : CI_SPAN_UNKNOWN;
     }
 }
 
-// a node as the parent walk names it: the range of its entries in the interval index
+// a node as the parent walk names it: its identity and the range of its entries that can
+// cover the walk's position
 struct WalkNode {
-    uint32_t start, end;
-    MSPB_DEVFN bool operator==(const WalkNode &o) const { return start == o.start && end == o.end; }
+    uint32_t id, lo, hi;
 };
+
+MSPB_DEVFN uint32_t walk_id(const TreeSeqView &ts, int32_t u)
+{
+    const uint32_t a = ts.child_start[u], b = ts.child_start[u + 1];
+    return a < b ? a : (CI_NODE | (uint32_t) u);
+}
 
 MSPB_DEVFN WalkNode walk_node(const TreeSeqView &ts, int32_t u)
 {
     WalkNode w;
-    w.start = ts.child_start[u];
-    w.end = ts.child_start[u + 1];
-    if (w.start >= w.end) {
-        w.start = CI_NONE;
-        w.end = (uint32_t) u;
-    }
+    const uint32_t a = ts.child_start[u], b = ts.child_start[u + 1];
+    w.id = a < b ? a : (CI_NODE | (uint32_t) u);
+    w.lo = a;
+    w.hi = b;
     return w;
 }
 
@@ -219,25 +253,53 @@ MSPB_DEVFN WalkNode walk_node(const TreeSeqView &ts, int32_t u)
 // there.  Intervals of one child are disjoint and sorted.
 MSPB_DEVFN bool parent_at(const TreeSeqView &ts, WalkNode *w, double x, double *time)
 {
-    if (w->start == CI_NONE) {
-        return false;
-    }
-    uint32_t lo = w->start, hi = w->end;
-    while (lo < hi) {
-        const uint32_t mid = (lo + hi) >> 1;
-        const ChildIv iv = ts.ci[mid];
-        if (x < iv.left) {
-            hi = mid;
-        } else if (x >= iv.right) {
-            lo = mid + 1;
-        } else {
-            *time = iv.parent_time;
-            w->start = iv.parent_start;
-            w->end = iv.parent_end;
-            return true;
+    uint32_t lo = w->lo, hi = w->hi;
+    ChildIv iv;
+    bool found = false;
+    if (hi - lo == 2) {
+        // both candidates in one round trip (they share a 64-byte segment or are adjacent)
+        const ChildIv i0 = ts.ci[lo], i1 = ts.ci[lo + 1];
+        iv = x < i0.right ? i0 : i1;
+        found = x >= iv.left && x < iv.right;
+    } else {
+        while (lo < hi) {
+            const uint32_t mid = (lo + hi) >> 1;
+            iv = ts.ci[mid];
+            if (x < iv.left) {
+                hi = mid;
+            } else if (x >= iv.right) {
+                lo = mid + 1;
+            } else {
+                found = true;
+                break;
+            }
         }
     }
-    return false;
+    if (!found) {
+        return false;
+    }
+    *time = iv.parent_time;
+    w->id = iv.parent_id;
+    if (iv.parent_id & CI_NODE) {
+        w->lo = w->hi = 0;
+    } else if (iv.parent_span != CI_SPAN_UNKNOWN) {
+        w->lo = iv.parent_id + (iv.parent_span >> 8);
+        w->hi = w->lo + (iv.parent_span & 0xffu);
+    } else {
+        // the node whose entries start at parent_id: the last u with child_start[u] <= parent_id
+        uint64_t a = 0, b = ts.num_nodes; // invariant: child_start[a] <= id < child_start[b]
+        while (b - a > 1) {
+            const uint64_t mid = (a + b) >> 1;
+            if (ts.child_start[mid] <= iv.parent_id) {
+                a = mid;
+            } else {
+                b = mid;
+            }
+        }
+        w->lo = iv.parent_id;
+        w->hi = ts.child_start[a + 1];
+    }
+    return true;
 }
 
 
@@ -1191,10 +1253,10 @@ MSPB_DEVFN void resolve_site(const TreeSeqView &ts, const KeptView &kept, const 
     // here because the reordering above may have interleaved kept and new mutations
     uint32_t cur = draw0;
     constexpr int SEEN = 8; // nodes of the site's first records stay in registers
-    WalkNode seen[SEEN];
+    uint32_t seen[SEEN];
 #pragma unroll
     for (int t = 0; t < SEEN; t++) {
-        seen[t].start = seen[t].end = CI_NONE;
+        seen[t] = CI_SPAN_UNKNOWN; // no node has this identity
     }
     for (uint64_t j = first; j < end; j++) {
         const uint32_t r = sv.val[j];
@@ -1211,7 +1273,7 @@ MSPB_DEVFN void resolve_site(const TreeSeqView &ts, const KeptView &kept, const 
 #pragma unroll
         for (int t = 0; t < SEEN; t++) {
             if ((uint64_t) t == j - first) {
-                seen[t] = self;
+                seen[t] = self.id;
             }
         }
         if (j > first) {
@@ -1229,12 +1291,12 @@ MSPB_DEVFN void resolve_site(const TreeSeqView &ts, const KeptView &kept, const 
                 // the latest earlier record on node u
 #pragma unroll
                 for (int t = 0; t < SEEN; t++) {
-                    if ((uint64_t) t < j - first && seen[t] == u) {
+                    if ((uint64_t) t < j - first && seen[t] == u.id) {
                         par = (int32_t) (first + t);
                     }
                 }
                 for (uint64_t q = j; q-- > first + SEEN;) {
-                    if (walk_node(ts, sv.rec[sv.val[q]].node) == u) {
+                    if (walk_id(ts, sv.rec[sv.val[q]].node) == u.id) {
                         par = (int32_t) q;
                         break;
                     }

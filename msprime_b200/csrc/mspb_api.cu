@@ -670,7 +670,16 @@ extern "C" int mspb_ctx_load_tables(mspb_ctx_t *ctx, const mspb_tables_t *t)
         cur = device_radix_sort<uint64_t>(sb, ctx->E, 0, false, st, ctx->log, nullptr);
         MSPB_LAUNCH(ctx->log, "k0_permute", k0_permute_kernel<<<grid_for(ctx->E, 256), 256, 0, st>>>(
             ts, sb.vals[cur], ctx->ci.p, ctx->child_start.p));
-        MSPB_LAUNCH(ctx->log, "k0_link", k0_link_kernel<<<grid_for(ctx->E, 256), 256, 0, st>>>(ts, ctx->ci.p));
+        // MSPB_K0_MAX_SPAN (tests only) lowers the span-count limit so that the walk's range
+        // recovery path runs on small inputs
+        uint32_t max_count = 256;
+        if (const char *env = getenv("MSPB_K0_MAX_SPAN")) {
+            const long v = strtol(env, nullptr, 10);
+            if (v >= 1 && v <= 256) {
+                max_count = (uint32_t) v;
+            }
+        }
+        MSPB_LAUNCH(ctx->log, "k0_link", k0_link_kernel<<<grid_for(ctx->E, 256), 256, 0, st>>>(ts, ctx->ci.p, max_count));
     }
     CUDA_OK(cudaStreamSynchronize(st));
     CUDA_OK(cudaGetLastError());

@@ -117,3 +117,18 @@ def test_stream_exhausted(ctx):
         gpu_run(ctx, ts, model=cases.JC69, stream=np.random.default_rng(1).random(5), map_position=[0, 10],
                 map_rate=[1.0])
     assert e.value.status == -1003
+
+
+@pytest.mark.parametrize("max_span", ["1", "2"])
+def test_walk_range_recovery(ctx, oracle_mod, monkeypatch, max_span):
+    # K0 stores, per index entry, the parent's entries overlapping it; spans that do not fit are
+    # marked unknown and the walk recovers the parent's range from child_start.  A tiny limit
+    # makes that path carry most steps of a dense overlay (many multi-record sites).
+    monkeypatch.setenv("MSPB_K0_MAX_SPAN", max_span)
+    ts = cases.smc_ts(50, 1e5, 1)
+    L = ts["sequence_length"]
+    first = check_case(ctx, oracle_mod, ts, model=cases.JC69, map_position=[0, L], map_rate=[2e-5],
+                       n_stream=3_000_000)
+    ts2 = cases.with_kept(ts, first)
+    check_case(ctx, oracle_mod, ts2, model=cases.JC69, map_position=[0, L], map_rate=[2e-5], seed=2,
+               n_stream=3_000_000, keep=True)
