@@ -300,6 +300,11 @@ class Context:
         check(lib().mspb_ctx_load_tables(self._h, C.byref(t)))
         del hold
 
+    def load_native(self, t):
+        """``t`` is an ``mspb_tables_t`` already filled in, e.g. by ``trees_io.Store.native_tables``
+        (columns of a mapped ``.trees`` file go to the device without passing through a dict)."""
+        check(lib().mspb_ctx_load_tables(self._h, C.byref(t)))
+
     def generate(self, params: Params):
         c = _Counts()
         check(lib().mspb_generate(self._h, C.byref(params.struct), C.byref(c)))

@@ -39,6 +39,22 @@ def build_treegen(force: bool = False) -> str:
     return TREEGEN_OUT
 
 
+TREESIO_SRC = os.path.join(HERE, "csrc", "trees_io.c")
+TREESIO_OUT = os.path.join(HERE, "_treesio.so")
+TREESIO_DEPS = [TREESIO_SRC, os.path.join(HERE, "..", "include", "msprime_b200_io.h"),
+                os.path.join(HERE, "..", "include", "msprime_b200.h")]
+
+
+def build_treesio(force: bool = False) -> str:
+    """The `.trees` (kastore) reader / writer: host-only C (include/msprime_b200_io.h)."""
+    if force or not os.path.exists(TREESIO_OUT) or any(
+            os.path.getmtime(d) > os.path.getmtime(TREESIO_OUT) for d in TREESIO_DEPS):
+        cc = os.environ.get("CC", "gcc")
+        subprocess.run([cc, "-O2", "-std=c11", "-Wall", "-Wextra", "-fPIC", "-shared", "-o", TREESIO_OUT,
+                        TREESIO_SRC], check=True)
+    return TREESIO_OUT
+
+
 def build(force: bool = False, verbose: bool = False) -> str:
     if force or needs_build():
         nvcc = os.environ.get("NVCC", "nvcc")
@@ -48,6 +64,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
             print(" ".join(cmd), file=sys.stderr)
         subprocess.run(cmd, check=True)
     build_treegen(force)
+    build_treesio(force)
     return OUT
 
 

@@ -175,35 +175,8 @@ def encode_alleles(alleles):
     return data, off
 
 
-def sim_mutations(
-    tables,
-    *,
-    which="ref",
-    map_position,
-    map_rate,
-    model,
-    discrete_genome=True,
-    keep=True,
-    start_time=-np.finfo(np.float64).max,
-    end_time=np.finfo(np.float64).max,
-    seed=None,
-    stream=None,
-):
-    """Runs one overlay on the CPU checker ``which`` ("ref" or "port").
-
-    ``model`` is a dict: ``{"kind": "matrix", "alleles": [...], "root_distribution": [...],
-    "transition_matrix": [[...]]}`` or ``{"kind": "infinite_alleles", "start_allele": int}``.
-    Exactly one of ``seed`` (MT19937) and ``stream`` (replay) must be given.
-    Returns a dict with ``sites`` and ``mutations`` column dicts plus bookkeeping.
-    """
-    lib = _load(which)
-    keep_refs = []
-
-    def hold(a):
-        keep_refs.append(a)
-        return a
-
-    inp = _Input()
+def _fill_tables(inp, tables, hold):
+    """Points the tree-sequence fields of ``inp`` at the columns of the dict ``tables``."""
     inp.sequence_length = float(tables["sequence_length"])
     nt = hold(_arr(tables["nodes"]["time"], np.float64))
     inp.num_nodes = nt.size
@@ -237,6 +210,68 @@ def sim_mutations(
         mm, mmo = map(hold, _ragged(m, "metadata", nm))
         inp.mutation_derived_state, inp.mutation_derived_state_offset = _ptr(md), _ptr(mdo)
         inp.mutation_metadata, inp.mutation_metadata_offset = _ptr(mm), _ptr(mmo)
+
+
+
+def _export(out):
+    """Copies the site / mutation columns of an ``orc_output_t`` into numpy arrays."""
+    S, M = out.num_sites, out.num_mutations
+    sao = _copy(out.site_ancestral_state_offset, S + 1, np.uint64)
+    smo = _copy(out.site_metadata_offset, S + 1, np.uint64)
+    mdo = _copy(out.mutation_derived_state_offset, M + 1, np.uint64)
+    mmo = _copy(out.mutation_metadata_offset, M + 1, np.uint64)
+    res = {
+        "sites": {
+            "position": _copy(out.site_position, S, np.float64),
+            "ancestral_state": _copy(out.site_ancestral_state, int(sao[-1]), np.uint8),
+            "ancestral_state_offset": sao,
+            "metadata": _copy(out.site_metadata, int(smo[-1]), np.uint8),
+            "metadata_offset": smo,
+        },
+        "mutations": {
+            "site": _copy(out.mutation_site, M, np.int32),
+            "node": _copy(out.mutation_node, M, np.int32),
+            "parent": _copy(out.mutation_parent, M, np.int32),
+            "time": _copy(out.mutation_time, M, np.float64),
+            "derived_state": _copy(out.mutation_derived_state, int(mdo[-1]), np.uint8),
+            "derived_state_offset": mdo,
+            "metadata": _copy(out.mutation_metadata, int(mmo[-1]), np.uint8),
+            "metadata_offset": mmo,
+        }
+    }
+    return res
+
+
+def sim_mutations(
+    tables,
+    *,
+    which="ref",
+    map_position,
+    map_rate,
+    model,
+    discrete_genome=True,
+    keep=True,
+    start_time=-np.finfo(np.float64).max,
+    end_time=np.finfo(np.float64).max,
+    seed=None,
+    stream=None,
+):
+    """Runs one overlay on the CPU checker ``which`` ("ref" or "port").
+
+    ``model`` is a dict: ``{"kind": "matrix", "alleles": [...], "root_distribution": [...],
+    "transition_matrix": [[...]]}`` or ``{"kind": "infinite_alleles", "start_allele": int}``.
+    Exactly one of ``seed`` (MT19937) and ``stream`` (replay) must be given.
+    Returns a dict with ``sites`` and ``mutations`` column dicts plus bookkeeping.
+    """
+    lib = _load(which)
+    keep_refs = []
+
+    def hold(a):
+        keep_refs.append(a)
+        return a
+
+    inp = _Input()
+    _fill_tables(inp, tables, hold)
 
     mpos = hold(_arr(map_position, np.float64))
     mrate = hold(_arr(map_rate, np.float64))
@@ -283,34 +318,13 @@ def sim_mutations(
     try:
         if status != 0:
             raise OracleError(status)
-        S, M = out.num_sites, out.num_mutations
-        sao = _copy(out.site_ancestral_state_offset, S + 1, np.uint64)
-        smo = _copy(out.site_metadata_offset, S + 1, np.uint64)
-        mdo = _copy(out.mutation_derived_state_offset, M + 1, np.uint64)
-        mmo = _copy(out.mutation_metadata_offset, M + 1, np.uint64)
-        res = {
-            "sites": {
-                "position": _copy(out.site_position, S, np.float64),
-                "ancestral_state": _copy(out.site_ancestral_state, int(sao[-1]), np.uint8),
-                "ancestral_state_offset": sao,
-                "metadata": _copy(out.site_metadata, int(smo[-1]), np.uint8),
-                "metadata_offset": smo,
-            },
-            "mutations": {
-                "site": _copy(out.mutation_site, M, np.int32),
-                "node": _copy(out.mutation_node, M, np.int32),
-                "parent": _copy(out.mutation_parent, M, np.int32),
-                "time": _copy(out.mutation_time, M, np.float64),
-                "derived_state": _copy(out.mutation_derived_state, int(mdo[-1]), np.uint8),
-                "derived_state_offset": mdo,
-                "metadata": _copy(out.mutation_metadata, int(mmo[-1]), np.uint8),
-                "metadata_offset": mmo,
-            },
+        res = _export(out)
+        res.update({
             "draws": int(out.draws),
             "stream_exhausted": bool(out.stream_exhausted),
             "next_allele": int(out.next_allele),
             "seconds": float(out.seconds),
-        }
+        })
         return res
     finally:
         lib.orc_free_output(C.byref(out))
@@ -332,3 +346,60 @@ def tables_equal(a, b):
             if not same:
                 diffs.append(f"{tbl}.{col}")
     return diffs
+
+
+# ---- `.trees` files through the reference's own tskit C (reference build only): the checker
+# of the product's file reader / writer
+
+def _trees_lib():
+    lib = _load("ref")
+    if not hasattr(lib, "_trees_ready"):
+        lib.orc_trees_dump.argtypes = [C.POINTER(_Input), C.c_uint64, C.c_char_p, C.c_char_p]
+        lib.orc_trees_load.argtypes = [C.c_char_p, C.POINTER(_Output)]
+        lib.orc_trees_equal.argtypes = [C.c_char_p, C.c_char_p, C.POINTER(C.c_int32)]
+        lib.orc_trees_copy.argtypes = [C.c_char_p, C.c_char_p]
+        lib._trees_ready = True
+    return lib
+
+
+def trees_dump(tables, path, num_samples=0, time_units="generations"):
+    """Writes ``tables`` (nodes, edges, sites, mutations) with ``tsk_table_collection_dump``."""
+    keep_refs = []
+
+    def hold(a):
+        keep_refs.append(a)
+        return a
+
+    inp = _Input()
+    _fill_tables(inp, tables, hold)
+    status = _trees_lib().orc_trees_dump(C.byref(inp), int(num_samples), time_units.encode(), str(path).encode())
+    if status != 0:
+        raise OracleError(status)
+
+
+def trees_load(path):
+    """Site and mutation tables of a file as ``tsk_table_collection_load`` reads them."""
+    lib = _trees_lib()
+    out = _Output()
+    status = lib.orc_trees_load(str(path).encode(), C.byref(out))
+    try:
+        if status != 0:
+            raise OracleError(status)
+        return _export(out)
+    finally:
+        lib.orc_free_output(C.byref(out))
+
+
+def trees_equal(path_a, path_b):
+    """True when the reference loads both files and finds the table collections equal."""
+    which = C.c_int32()
+    r = _trees_lib().orc_trees_equal(str(path_a).encode(), str(path_b).encode(), C.byref(which))
+    if r < 0:
+        raise OracleError(r)
+    return r == 1
+
+
+def trees_copy(path_in, path_out):
+    status = _trees_lib().orc_trees_copy(str(path_in).encode(), str(path_out).encode())
+    if status != 0:
+        raise OracleError(status)

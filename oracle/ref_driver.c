@@ -250,3 +250,124 @@ orc_free_output(orc_output_t *out)
     free(out->mutation_metadata_offset);
     memset(out, 0, sizeof(*out));
 }
+
+/* ---- `.trees` files through the reference's own tskit C (tsk_table_collection_dump /
+ * _load / _equals, git-submodules/tskit/c/tskit/tables.c): the checker for the product's
+ * file reader / writer (msprime_b200/csrc/trees_io.c).  Reference build only. */
+
+/* Writes the tree sequence of `in` (kept sites / mutations included, sample flags on the
+ * first num_samples nodes, indexes built, one provenance row) as a .trees file. */
+int
+orc_trees_dump(const orc_input_t *in, uint64_t num_samples, const char *time_units, const char *path)
+{
+    int ret;
+    uint64_t j;
+    tsk_table_collection_t tables;
+    static const char *TS = "2026-01-01T00:00:00";
+    static const char *REC = "{\"software\": \"oracle\"}";
+
+    ret = tsk_table_collection_init(&tables, 0);
+    if (ret != 0) {
+        return msp_set_tsk_error(ret);
+    }
+    ret = load_tables(in, &tables);
+    if (ret != 0) {
+        goto out;
+    }
+    for (j = 0; j < num_samples && j < tables.nodes.num_rows; j++) {
+        tables.nodes.flags[j] = TSK_NODE_IS_SAMPLE;
+    }
+    ret = tsk_table_collection_set_time_units(&tables, time_units, strlen(time_units));
+    if (ret != 0) {
+        ret = msp_set_tsk_error(ret);
+        goto out;
+    }
+    ret = tsk_provenance_table_add_row(&tables.provenances, TS, strlen(TS), REC, strlen(REC));
+    if (ret < 0) {
+        ret = msp_set_tsk_error(ret);
+        goto out;
+    }
+    ret = tsk_table_collection_build_index(&tables, 0);
+    if (ret != 0) {
+        ret = msp_set_tsk_error(ret);
+        goto out;
+    }
+    ret = tsk_table_collection_dump(&tables, path, 0);
+    if (ret != 0) {
+        ret = msp_set_tsk_error(ret);
+    }
+out:
+    tsk_table_collection_free(&tables);
+    return ret;
+}
+
+/* Loads a .trees file with the reference and hands its site / mutation tables back. */
+int
+orc_trees_load(const char *path, orc_output_t *out)
+{
+    int ret;
+    tsk_table_collection_t tables;
+
+    memset(out, 0, sizeof(*out));
+    ret = tsk_table_collection_load(&tables, path, 0);
+    if (ret != 0) {
+        ret = msp_set_tsk_error(ret);
+        tsk_table_collection_free(&tables);
+        out->status = ret;
+        return ret;
+    }
+    ret = export_tables(&tables, out);
+    tsk_table_collection_free(&tables);
+    out->status = ret;
+    return ret;
+}
+
+/* 1 when the reference finds the two files' table collections equal (every table, the
+ * metadata, time units and provenance; tsk_table_collection_equals with options 0),
+ * 0 when not, negative on a load error (`which` says which file). */
+int
+orc_trees_equal(const char *path_a, const char *path_b, int32_t *which)
+{
+    int ret;
+    tsk_table_collection_t a, b;
+
+    *which = 0;
+    ret = tsk_table_collection_load(&a, path_a, 0);
+    if (ret != 0) {
+        tsk_table_collection_free(&a);
+        return msp_set_tsk_error(ret);
+    }
+    *which = 1;
+    ret = tsk_table_collection_load(&b, path_b, 0);
+    if (ret != 0) {
+        tsk_table_collection_free(&a);
+        tsk_table_collection_free(&b);
+        return msp_set_tsk_error(ret);
+    }
+    /* also require what equals() does not look at: the loaded trees must pass the
+     * reference's integrity check with indexes present */
+    ret = (int) tsk_table_collection_check_integrity(&b, TSK_CHECK_TREES);
+    if (ret < 0) {
+        ret = msp_set_tsk_error(ret);
+    } else {
+        ret = tsk_table_collection_equals(&a, &b, 0) ? 1 : 0;
+    }
+    tsk_table_collection_free(&a);
+    tsk_table_collection_free(&b);
+    return ret;
+}
+
+/* Reference load + dump of a file (what `tskit.load(x).dump(y)` does). */
+int
+orc_trees_copy(const char *path_in, const char *path_out)
+{
+    int ret;
+    tsk_table_collection_t tables;
+
+    ret = tsk_table_collection_load(&tables, path_in, 0);
+    if (ret == 0) {
+        ret = tsk_table_collection_dump(&tables, path_out, 0);
+    }
+    tsk_table_collection_free(&tables);
+    return ret != 0 ? msp_set_tsk_error(ret) : 0;
+}
