@@ -3,7 +3,12 @@ from .core import __version__  # noqa: F401
 from .intervals import RateMap  # noqa: F401
 from .mutations import (  # noqa: F401
     BINARY,
+    BLOSUM62,
+    EL2,
     NUCLEOTIDES,
+    PAM,
+    SMM,
+    TPM,
     F84,
     GTR,
     HKY,
@@ -14,6 +19,7 @@ from .mutations import (  # noqa: F401
     InputError,
     LibraryError,
     MatrixMutationModel,
+    MicrosatMutationModel,
     MutationModel,
     SLiMMutationModel,
     mutate,

@@ -292,6 +292,156 @@ class GTR(MatrixMutationModel):
         super().__init__(_ACGT_ALLELES, root_distribution, q)
 
 
+def general_microsat_rate_matrix(s, u, v, p, m, lo, hi):
+    """Jump-chain transition matrix of the microsatellite model of Sainudiin et al. (2004) on
+    repeat numbers ``lo .. hi`` (``msprime/mutations.py:204-304``).
+
+    From allele ``i`` the chain moves up with weight ``alpha(i)`` and down with ``1 - alpha(i)``,
+    ``alpha(i) = clip(u - v (i - lo), 0, 1)``; the overall rate of ``i`` is ``beta(i) = 1 + s (i - lo)``;
+    a move is a single step with probability ``p`` and otherwise a geometric(``m``) number of steps
+    truncated to stay inside ``[lo, hi]``.  The rates are divided by the largest row sum and the
+    diagonal takes up the rest of each row.  Built here as whole-array numpy expressions in the
+    reference's order of operations, so the entries are the same doubles."""
+    s, u, v, p, m = (float(x) for x in (s, u, v, p, m))
+    lo, hi = int(lo), int(hi)
+    n = hi - lo + 1
+    q = 1.0 - m
+    # (1 - m) ** k twice: the reference raises to a numpy integer in the numerator (numpy's pow)
+    # and to a Python integer in the denominator (libm's pow); the two differ in the last bit
+    powers_np = np.array([q ** np.int64(k) for k in range(n + 1)], dtype=np.float64)
+    powers = np.array([q ** k for k in range(n + 1)], dtype=np.float64)
+    idx = np.arange(n)
+    i, j = np.meshgrid(idx, idx, indexing="ij")
+    dist = np.abs(i - j)
+    up, down = j > i, j < i
+    # truncated geometric step sizes: m (1-m)^(d-1) / (1 - (1-m)^(room)), room = hi-i going up, i-lo going down
+    num = m * powers_np[np.maximum(dist - 1, 0)]
+    room = np.where(up, (n - 1) - i, i)
+    with np.errstate(divide="ignore", invalid="ignore"):
+        gamma = num / (1.0 - powers[room])
+    gamma[~(up | down)] = 0.0  # the diagonal (and its 0 / 0 when m = 1) is not a move
+    alpha = np.array([max(0.0, min(1.0, u - (v * k))) for k in range(n)], dtype=np.float64)
+    beta = np.array([1.0 + (k * s) for k in range(n)], dtype=np.float64)
+    direction = np.where(up, (beta * alpha)[:, None], (beta * (1.0 - alpha))[:, None])
+    single = direction * (p + ((1.0 - p) * gamma))
+    multi = direction * (1.0 - p) * gamma
+    matrix = np.where(dist == 1, single, multi)
+    matrix[~(up | down)] = 0.0
+    matrix = np.ascontiguousarray(matrix, dtype=np.float64)
+    matrix /= np.max(matrix.sum(axis=1, dtype="float64"))
+    row_sums = matrix.sum(axis=1, dtype="float64")
+    np.fill_diagonal(matrix, np.fmax(0.0, 1.0 - row_sums))
+    return matrix
+
+
+class MicrosatMutationModel(MatrixMutationModel):
+    """Microsatellite repeat-number model with the five parameters of Sainudiin et al. (2004):
+    alleles ``"lo" .. "hi"``, transition matrix :func:`general_microsat_rate_matrix`, root
+    distribution = the chain's stationary distribution unless given
+    (``msprime/mutations.py:307-398``; same defaults and argument errors)."""
+
+    def __init__(self, *, s=None, u=None, v=None, p=None, m=None, lo=None, hi=None, root_distribution=None):
+        import numbers
+
+        s = 0.0 if s is None else s
+        u = 0.5 if u is None else u
+        v = 0.0 if v is None else v
+        p = 1.0 if p is None else p
+        m = 1.0 if m is None else m
+        lo = 1 if lo is None else lo
+        hi = 50 if hi is None else hi
+        params = [s, u, v, p, m, lo, hi]
+        if any(not math.isfinite(x) for x in params):
+            raise ValueError("All parameters must be finite")
+        if any(not isinstance(x, numbers.Number) for x in params):
+            raise ValueError("All parameters must be numeric")
+        lo, hi = int(lo), int(hi)
+        if lo > hi:
+            raise ValueError("lo > hi")
+        if lo < 0:
+            raise ValueError("lo must be >= 0")
+        if s <= -1 / (hi - lo + 1):
+            raise ValueError("s must be > -1/(hi-lo+1)")
+        if u <= 0 or u >= 1:
+            raise ValueError("u must be between 0 and 1")
+        alleles = [str(k) for k in range(lo, hi + 1)]
+        matrix = general_microsat_rate_matrix(s, u, v, p, m, lo, hi)
+        if root_distribution is None:
+            # left eigenvector of eigenvalue 1
+            values, vectors = np.linalg.eig(matrix.T)
+            vectors = np.real_if_close(vectors, tol=1)
+            stationary = np.array(vectors[:, np.where(np.abs(values - 1.0) < 1e-8)[0][0]])
+            root_distribution = stationary / np.sum(stationary)
+        self.s, self.u, self.v, self.p, self.m, self.lo, self.hi = s, u, v, p, m, lo, hi
+        super().__init__(alleles, root_distribution, matrix)
+
+
+class SMM(MicrosatMutationModel):
+    """Stepwise mutation model (Ohta & Kimura 1978): repeat number changes by +/- 1 with equal
+    probability, reflecting at ``lo`` and ``hi`` (``msprime/mutations.py:401-425``)."""
+
+    def __init__(self, lo=None, hi=None, *, root_distribution=None):
+        super().__init__(s=0, u=0.5, v=0, p=0, m=1, lo=lo, hi=hi, root_distribution=root_distribution)
+
+
+class TPM(MicrosatMutationModel):
+    """Two-phase model (Di Rienzo et al. 1994): single steps with probability ``p``, otherwise
+    geometric(``m``) multi-steps (``msprime/mutations.py:428-463``)."""
+
+    def __init__(self, *, p, m, lo=None, hi=None, root_distribution=None):
+        if not (0 < p < 1.0):
+            raise ValueError("p must be between 0 and 1")
+        if not (0 < m < 1.0):
+            raise ValueError("m must be between 0 and 1")
+        super().__init__(s=0, u=0.5, v=0, p=p, m=m, lo=lo, hi=hi, root_distribution=root_distribution)
+
+
+class EL2(MicrosatMutationModel):
+    """Equal-rate, linear-bias, two-phase model (Garza et al. 1995 as parameterised by Sainudiin
+    et al. 2004): multi-steps only, bias ``u - v (i - lo)`` (``msprime/mutations.py:466-513``)."""
+
+    def __init__(self, *, m, u, v, lo=None, hi=None, root_distribution=None):
+        if not (0 < m < 1.0):
+            raise ValueError("m must be between 0 and 1")
+        if not (0 < u < 1.0):
+            raise ValueError("u must be between 0 and 1")
+        super().__init__(s=0, u=u, v=v, p=0, m=m, lo=lo, hi=hi, root_distribution=root_distribution)
+
+
+_AA_DATA = None
+
+
+def _amino_acid_model(name):
+    """(alleles, root distribution, transition matrix) of an empirical amino-acid model from
+    ``data/amino_acid_models.npz`` (published tables; ``scripts/make_aa_models.py`` says where
+    the numbers come from)."""
+    global _AA_DATA
+    if _AA_DATA is None:
+        import os
+
+        path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "data", "amino_acid_models.npz")
+        with np.load(path) as z:
+            _AA_DATA = {k: z[k] for k in z.files}
+    return ([str(a) for a in _AA_DATA[f"{name}_alleles"]], _AA_DATA[f"{name}_root_distribution"].copy(),
+            _AA_DATA[f"{name}_transition_matrix"].copy())
+
+
+class BLOSUM62(MatrixMutationModel):
+    """BLOSUM62 amino-acid substitution model (Henikoff & Henikoff 1992), 20 alleles in
+    Seq-Gen's order (``msprime/mutations.py:853-1114``)."""
+
+    def __init__(self):
+        super().__init__(*_amino_acid_model("blosum62"))
+
+
+class PAM(MatrixMutationModel):
+    """Dayhoff PAM amino-acid substitution model (Dayhoff et al. 1978), 20 alleles in Seq-Gen's
+    order (``msprime/mutations.py:1117-1387``)."""
+
+    def __init__(self):
+        super().__init__(*_amino_acid_model("pam"))
+
+
 class InfiniteSites(MatrixMutationModel):
     """Legacy model object accepted by ``mutate`` (``msprime/mutations.py:1390-1400``)."""
 
@@ -308,6 +458,8 @@ MODEL_MAP = {
     "infinite_alleles": InfiniteAlleles,
     "binary": BinaryMutationModel,
     "jc69": JC69,
+    "blosum62": BLOSUM62,
+    "pam": PAM,
 }
 
 

@@ -66,6 +66,7 @@ def main():
             st["write"] = time.perf_counter() - t
             st["total"] = sum(st.values())
             store.close()
+            last_count = int(counts["num_new_mutations"])
             if best is None or st["total"] < best["total"]:
                 best = dict(st, mutations=int(counts["num_new_mutations"]))
     out = {
@@ -78,7 +79,7 @@ def main():
     # the output must load back (container + schema checks) with the right row count
     with trees_io.Store(dst) as s2:
         t2, _ = s2.native_tables()
-        assert t2.num_mutations == best["mutations"], (t2.num_mutations, best["mutations"])
+        assert t2.num_mutations == last_count, (t2.num_mutations, last_count)
     os.unlink(src)
     os.unlink(dst)
     print(json.dumps(out))

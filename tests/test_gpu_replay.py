@@ -132,3 +132,26 @@ def test_walk_range_recovery(ctx, oracle_mod, monkeypatch, max_span):
     ts2 = cases.with_kept(ts, first)
     check_case(ctx, oracle_mod, ts2, model=cases.JC69, map_position=[0, L], map_rate=[2e-5], seed=2,
                n_stream=3_000_000, keep=True)
+
+
+def _class_model(m):
+    return {"kind": "matrix", "alleles": list(m.alleles), "root_distribution": np.asarray(m.root_distribution).tolist(),
+            "transition_matrix": np.asarray(m.transition_matrix).tolist()}
+
+
+@pytest.mark.parametrize("name", ["pam", "blosum62", "smm", "tpm", "el2"])
+def test_large_alphabets(ctx, oracle_mod, name):
+    # 20 amino acids / up to 49 repeat numbers, multi-character alleles ("10", "11", ...):
+    # the allele search of kept states and the O(A) running sums of root and transition draws
+    import msprime_b200 as msp
+
+    model = {"pam": msp.PAM, "blosum62": msp.BLOSUM62, "smm": lambda: msp.SMM(lo=2, hi=50),
+             "tpm": lambda: msp.TPM(p=0.6, m=0.4, lo=8, hi=30),
+             "el2": lambda: msp.EL2(m=0.5, u=0.6, v=0.01, lo=1, hi=15)}[name]()
+    md = _class_model(model)
+    ts = cases.smc_ts(50, 1e5, 1)
+    L = ts["sequence_length"]
+    first = check_case(ctx, oracle_mod, ts, model=md, map_position=[0, L], map_rate=[1e-5], n_stream=3_000_000)
+    ts2 = cases.with_kept(ts, first)
+    check_case(ctx, oracle_mod, ts2, model=md, map_position=[0, L], map_rate=[1e-5], seed=2, n_stream=3_000_000,
+               keep=True)
