@@ -599,8 +599,14 @@ constexpr int K2_EDGES = 256;
 
 __global__ void __launch_bounds__(K2_EDGES) k2_place_kernel(TreeSeqView ts, RateMapView map, CallView call,
     const uint32_t *__restrict__ goff, const uint32_t *__restrict__ loff, const uint64_t *__restrict__ tile_base,
-    uint32_t base, Rec *__restrict__ rec, KeyView keys)
+    uint32_t base, Rec *__restrict__ rec, KeyView keys, const uint64_t *__restrict__ k1_total, uint64_t capacity)
 {
+    // Launched before the host has read the K1 total (so that the read overlaps this kernel):
+    // the buffers then have the capacity of earlier calls, and a total that does not fit makes
+    // the whole grid return; the host launches again after growing them.
+    if (k1_total != nullptr && (*k1_total & 0xffffffffull) + base > capacity) {
+        return;
+    }
     __shared__ EdgeDraw sd[K2_EDGES];
     __shared__ uint32_t sid[K2_EDGES]; // edge ids (the Philox key of a placement)
     __shared__ uint8_t s_owner[2][K2_EDGES];

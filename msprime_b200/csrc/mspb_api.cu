@@ -23,11 +23,13 @@ template <typename T>
 struct DBuf {
     T *p = nullptr;
     size_t cap = 0;
+    uint64_t gen = 0; // bumped whenever the buffer is (re)allocated, i.e. its contents are lost
     int ensure(size_t n)
     {
         if (n <= cap && p != nullptr) {
             return 0;
         }
+        gen++;
         if (p != nullptr) {
             cudaFree(p);
             p = nullptr;
@@ -71,6 +73,7 @@ struct mspb_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev[MSPB_NUM_PHASES + 1] = {};
+    cudaEvent_t ev_k1 = nullptr; // the K1 totals have reached the host (no timing: cheap to wait on)
     float phase_ms[MSPB_NUM_PHASES] = {};
     LaunchLog log;
     bool tables_loaded = false, generated = false;
@@ -279,6 +282,7 @@ extern "C" int mspb_ctx_create(int device, mspb_ctx_t **out)
     for (auto &e : ctx->ev) {
         cudaEventCreate(&e);
     }
+    cudaEventCreateWithFlags(&ctx->ev_k1, cudaEventDisableTiming);
     ctx->log.stream = ctx->stream;
     if (cudaMallocHost((void **) &ctx->host, sizeof(HostTotals)) != cudaSuccess
         || cudaMallocHost((void **) &ctx->or_and_host, 2 * sizeof(uint64_t)) != cudaSuccess
@@ -329,6 +333,9 @@ extern "C" void mspb_ctx_destroy(mspb_ctx_t *ctx)
         if (e != nullptr) {
             cudaEventDestroy(e);
         }
+    }
+    if (ctx->ev_k1 != nullptr) {
+        cudaEventDestroy(ctx->ev_k1);
     }
     if (ctx->stream != nullptr) {
         cudaStreamDestroy(ctx->stream);
@@ -1211,6 +1218,8 @@ static int generate_impl(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t 
     // ---- K1: how many new mutations, and where they go
     CUDA_OK(cudaEventRecord(ctx->ev[1], st));
     uint64_t Mnew = 0, num_pairs = 0;
+    uint64_t spec_rec = 0, spec_key = 0; // generations of the buffers of a K2 launched ahead of the K1 read-back
+    size_t spec_cap = 0;
     ReplayPairs pairs;
     memset(&pairs, 0, sizeof(pairs));
     if (!replay) {
@@ -1228,7 +1237,29 @@ static int generate_impl(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t 
                 k1_spine_kernel<<<1, 1024, 0, st>>>(ctx->k1_tiles.p, tiles, &dt->k1_total));
         }
         CUDA_OK(cudaMemcpyAsync(ht, dt, sizeof(HostTotals), cudaMemcpyDeviceToHost, st));
-        CUDA_OK(cudaStreamSynchronize(st));
+        CUDA_OK(cudaEventRecord(ctx->ev_k1, st));
+        // K2 does not need the total to be launched (its grid follows the edges): when the
+        // record and key buffers of earlier calls are there, it goes out now and the host's
+        // wait for the total overlaps it.  The kernel checks the total against the capacity.
+        if (!in_slice && S0 + M0 == 0 && call.num_work > 0) {
+            spec_rec = ctx->rec.gen;
+            spec_key = call.key_mode == KEY32_POS ? ctx->k32_0.gen : ctx->keys0.gen;
+            const size_t key_cap = call.key_mode == KEY32_POS ? ctx->k32_0.cap : ctx->keys0.cap;
+            spec_cap = ctx->rec.cap < key_cap ? ctx->rec.cap : key_cap;
+            if (ctx->rec.p != nullptr && spec_cap > 1) {
+                spec_cap -= 1;
+                KeyView skeys;
+                skeys.mode = call.key_mode;
+                skeys.k32 = ctx->k32_0.p;
+                skeys.k64 = ctx->keys0.p;
+                MSPB_LAUNCH(ctx->log, "k2_place",
+                    k2_place_kernel<<<grid_for(call.num_work, K2_EDGES), K2_EDGES, 0, st>>>(ts, map, call,
+                        ctx->goff.p, nullptr, ctx->k1_tiles.p, 0u, ctx->rec.p, skeys, &dt->k1_total, spec_cap));
+            } else {
+                spec_cap = 0;
+            }
+        }
+        CUDA_OK(cudaEventSynchronize(ctx->ev_k1)); // the copy, not the kernel launched after it
         Mnew = sliced ? (ht->k1_total >> 32) : (ht->k1_total & 0xffffffffull);
     } else {
         const uint64_t cap = p->replay_len / 2 + 1;
@@ -1383,10 +1414,15 @@ static int generate_impl(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t 
             fill_kept_kernel<<<grid_for(S0 + M0, 256), 256, 0, st>>>(kept, call, ctx->rec.p, keys, &dt->err));
     }
     if (Mnew > 0) {
-        if (!replay) {
+        const bool placed = spec_cap > 0 && Mnew <= spec_cap && spec_rec == ctx->rec.gen
+                            && spec_key == (call.key_mode == KEY32_POS ? ctx->k32_0.gen : ctx->keys0.gen);
+        if (placed) {
+            // the early launch had room and the buffers did not move: the records are in place
+        } else if (!replay) {
             MSPB_LAUNCH(ctx->log, "k2_place",
                 k2_place_kernel<<<grid_for(call.num_work, K2_EDGES), K2_EDGES, 0, st>>>(ts, map, call, ctx->goff.p,
-                    sliced ? ctx->loff.p : nullptr, ctx->k1_tiles.p, (uint32_t) (S0 + M0), ctx->rec.p, keys));
+                    sliced ? ctx->loff.p : nullptr, ctx->k1_tiles.p, (uint32_t) (S0 + M0), ctx->rec.p, keys, nullptr,
+                    0));
         } else {
             MSPB_LAUNCH(ctx->log, "replay_place",
                 replay_place_kernel<<<grid_for(num_pairs, 128), 128, 0, st>>>(ts, map, call, ctx->replay.p, pairs,
