@@ -73,6 +73,11 @@ struct mspb_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev[MSPB_NUM_PHASES + 1] = {};
+    // host copies of the rate map / matrix model whose device copies are current (upload_params)
+    bool cache_map_valid = false, cache_map_discrete = false, cache_model_valid = false;
+    std::vector<double> cache_map_pos, cache_map_rate, cache_model_root, cache_model_matrix;
+    std::vector<uint64_t> cache_model_off;
+    std::vector<char> cache_model_bytes;
     cudaEvent_t ev_k1 = nullptr; // the K1 totals have reached the host (no timing: cheap to wait on)
     float phase_ms[MSPB_NUM_PHASES] = {};
     LaunchLog log;
@@ -788,22 +793,36 @@ int upload_params(mspb_ctx *ctx, const mspb_params_t *p, RateMapView *map, Model
     cudaStream_t st = ctx->stream;
     const uint64_t R = p->map_size;
     const bool discrete = p->discrete_genome != 0;
-    std::vector<double> rate(R + 1), cum(R + 1);
-    double sum = 0;
-    for (uint64_t j = 0; j <= R; j++) {
-        cum[j] = sum;
-        rate[j] = j < R ? p->map_rate[j] : 0.0;
-        if (j < R) {
-            const double a = discrete ? std::ceil(p->map_position[j]) : p->map_position[j];
-            const double b = discrete ? std::ceil(p->map_position[j + 1]) : p->map_position[j + 1];
-            sum += (b - a) * rate[j];
+    // Repeated calls usually come with the same rate map (and model, below): the device copies
+    // of the previous call are reused when the host arrays compare equal, which saves three
+    // small copies and a stream wait per overlay.
+    const bool same_map = ctx->cache_map_valid && ctx->cache_map_discrete == discrete
+                          && ctx->cache_map_pos.size() == R + 1 && ctx->cache_map_rate.size() == R
+                          && memcmp(ctx->cache_map_pos.data(), p->map_position, (R + 1) * sizeof(double)) == 0
+                          && (R == 0 || memcmp(ctx->cache_map_rate.data(), p->map_rate, R * sizeof(double)) == 0);
+    if (!same_map) {
+        ctx->cache_map_valid = false;
+        std::vector<double> rate(R + 1), cum(R + 1);
+        double sum = 0;
+        for (uint64_t j = 0; j <= R; j++) {
+            cum[j] = sum;
+            rate[j] = j < R ? p->map_rate[j] : 0.0;
+            if (j < R) {
+                const double a = discrete ? std::ceil(p->map_position[j]) : p->map_position[j];
+                const double b = discrete ? std::ceil(p->map_position[j + 1]) : p->map_position[j + 1];
+                sum += (b - a) * rate[j];
+            }
         }
+        TRY(upload(ctx->map_pos, p->map_position, R + 1, st));
+        TRY(upload(ctx->map_rate, rate.data(), R + 1, st));
+        TRY(upload(ctx->map_cum, cum.data(), R + 1, st));
+        // the vectors must outlive the async copies
+        CUDA_OK(cudaStreamSynchronize(st));
+        ctx->cache_map_pos.assign(p->map_position, p->map_position + R + 1);
+        ctx->cache_map_rate.assign(p->map_rate, p->map_rate + R);
+        ctx->cache_map_discrete = discrete;
+        ctx->cache_map_valid = true;
     }
-    TRY(upload(ctx->map_pos, p->map_position, R + 1, st));
-    TRY(upload(ctx->map_rate, rate.data(), R + 1, st));
-    TRY(upload(ctx->map_cum, cum.data(), R + 1, st));
-    // the vectors must outlive the async copies
-    CUDA_OK(cudaStreamSynchronize(st));
     map->pos = ctx->map_pos.p;
     map->rate = ctx->map_rate.p;
     map->cum = ctx->map_cum.p;
@@ -821,10 +840,27 @@ int upload_params(mspb_ctx *ctx, const mspb_params_t *p, RateMapView *map, Model
     model->matrix = nullptr;
     if (p->model_kind == MSPB_MODEL_MATRIX) {
         const uint64_t A = p->num_alleles;
-        TRY(upload(ctx->model_alleles, p->alleles, (size_t) p->allele_offset[A], st));
-        TRY(upload(ctx->model_allele_off, p->allele_offset, A + 1, st));
-        TRY(upload(ctx->model_root, p->root_distribution, A, st));
-        TRY(upload(ctx->model_matrix, p->transition_matrix, A * A, st));
+        const size_t nb = (size_t) p->allele_offset[A];
+        const bool same_model = ctx->cache_model_valid && ctx->cache_model_off.size() == A + 1
+                                && ctx->cache_model_bytes.size() == nb
+                                && memcmp(ctx->cache_model_off.data(), p->allele_offset, (A + 1) * sizeof(uint64_t)) == 0
+                                && (nb == 0 || memcmp(ctx->cache_model_bytes.data(), p->alleles, nb) == 0)
+                                && memcmp(ctx->cache_model_root.data(), p->root_distribution, A * sizeof(double)) == 0
+                                && memcmp(ctx->cache_model_matrix.data(), p->transition_matrix, A * A * sizeof(double))
+                                       == 0;
+        if (!same_model) {
+            ctx->cache_model_valid = false;
+            TRY(upload(ctx->model_alleles, p->alleles, nb, st));
+            TRY(upload(ctx->model_allele_off, p->allele_offset, A + 1, st));
+            TRY(upload(ctx->model_root, p->root_distribution, A, st));
+            TRY(upload(ctx->model_matrix, p->transition_matrix, A * A, st));
+            CUDA_OK(cudaStreamSynchronize(st)); // pageable sources: the caller may free them after the call
+            ctx->cache_model_off.assign(p->allele_offset, p->allele_offset + A + 1);
+            ctx->cache_model_bytes.assign(p->alleles, p->alleles + nb);
+            ctx->cache_model_root.assign(p->root_distribution, p->root_distribution + A);
+            ctx->cache_model_matrix.assign(p->transition_matrix, p->transition_matrix + A * A);
+            ctx->cache_model_valid = true;
+        }
         model->num_alleles = (uint32_t) A;
         model->alleles = ctx->model_alleles.p;
         model->allele_off = ctx->model_allele_off.p;
