@@ -1277,7 +1277,7 @@ static int generate_impl(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t 
         // K2 does not need the total to be launched (its grid follows the edges): when the
         // record and key buffers of earlier calls are there, it goes out now and the host's
         // wait for the total overlaps it.  The kernel checks the total against the capacity.
-        if (!in_slice && S0 + M0 == 0 && call.num_work > 0) {
+        if (!sliced && S0 + M0 == 0 && call.num_work > 0) {
             spec_rec = ctx->rec.gen;
             spec_key = call.key_mode == KEY32_POS ? ctx->k32_0.gen : ctx->keys0.gen;
             const size_t key_cap = call.key_mode == KEY32_POS ? ctx->k32_0.cap : ctx->keys0.cap;

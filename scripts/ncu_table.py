@@ -16,6 +16,14 @@ def main():
     def g(r, name, default=""):
         return r[hdr.index(name)] if name in hdr else default
 
+    # the capture may start mid-overlay: keep one whole overlay = the 11 launches from the first
+    # k1_count on (k1_count, k1_spine, k2_place, histogram, 4 sort passes, p1, k4, k5)
+    body = rows[2:]
+    for i, r in enumerate(body):
+        if "k1_count" in g(r, "Kernel Name"):
+            body = body[i:i + 11]
+            break
+    rows = rows[:2] + body
     if len(sys.argv) > 3 and sys.argv[2] == "--traffic":
         # {"workload": ..., "kernels": {short name: mean dram bytes (read + write) per launch}}
         import json
