@@ -222,6 +222,9 @@ int mspb_generate_finish_device(mspb_ctx_t *ctx, uint32_t rank, uint32_t world, 
     uint64_t *totals, uint64_t *bases);
 /* Copies the resident result to host buffers. */
 int mspb_fetch(mspb_ctx_t *ctx, const mspb_columns_t *host_columns);
+/* Bytes the last mspb_fetch moved over the bus (columns known to be all zero, i.e. the metadata
+ * offsets of a result without metadata, are filled in by the host instead of being copied). */
+uint64_t mspb_last_fetch_bytes(const mspb_ctx_t *ctx);
 /* Device pointers of the resident result (valid until the next mspb_generate). */
 int mspb_device_columns(mspb_ctx_t *ctx, mspb_columns_t *device_columns);
 /* Number of kernels this library launched since the context was created. */

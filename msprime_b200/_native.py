@@ -106,7 +106,7 @@ EXPORTED_SYMBOLS = [
     "mspb_ctx_stream", "mspb_kernel_timing", "mspb_kernel_time", "mspb_selftest_sort",
     "mspb_generate_begin", "mspb_generate_end", "mspb_shift_offsets",
     "mspb_exchange_buffers", "mspb_exchange_post_counts", "mspb_generate_end_device",
-    "mspb_generate_finish_device",
+    "mspb_generate_finish_device", "mspb_last_fetch_bytes",
 ]
 
 EXCHANGE_WORDS = 8  # MSPB_EXCHANGE_WORDS
@@ -151,6 +151,8 @@ def lib():
         L.mspb_device_columns.argtypes = [C.c_void_p, C.POINTER(_Columns)]
         L.mspb_kernel_launches.argtypes = [C.c_void_p]
         L.mspb_kernel_launches.restype = C.c_uint64
+        L.mspb_last_fetch_bytes.argtypes = [C.c_void_p]
+        L.mspb_last_fetch_bytes.restype = C.c_uint64
         L.mspb_phase_ms.argtypes = [C.c_void_p, C.POINTER(C.c_float), C.c_int]
         L.mspb_phase_name.argtypes = [C.c_int]
         L.mspb_phase_name.restype = C.c_char_p
@@ -400,6 +402,10 @@ class Context:
         sites = {k[len("site_"):]: v for k, v in arrays.items() if k.startswith("site_")}
         muts = {k[len("mutation_"):]: v for k, v in arrays.items() if k.startswith("mutation_")}
         return {"sites": sites, "mutations": muts}
+
+    def last_fetch_bytes(self) -> int:
+        """Device-to-host bytes of the last :meth:`fetch`."""
+        return int(lib().mspb_last_fetch_bytes(self._h))
 
     def device_columns(self):
         """Raw device pointers (ints) of the resident result, with element counts and dtypes."""

@@ -78,6 +78,8 @@ struct mspb_ctx {
     std::vector<double> cache_map_pos, cache_map_rate, cache_model_root, cache_model_matrix;
     std::vector<uint64_t> cache_model_off;
     std::vector<char> cache_model_bytes;
+    cudaStream_t copy_stream = nullptr; // load_tables: the columns K0's sorts do not read arrive here
+    cudaEvent_t ev_keys = nullptr, ev_copied = nullptr;
     cudaEvent_t ev_k1 = nullptr; // the K1 totals have reached the host (no timing: cheap to wait on)
     float phase_ms[MSPB_NUM_PHASES] = {};
     LaunchLog log;
@@ -147,6 +149,7 @@ struct mspb_ctx {
     // leading bytes of the metadata offset columns known to be zero (and for which buffer)
     const void *md_zero_site_ptr = nullptr, *md_zero_mut_ptr = nullptr;
     uint64_t md_zero_site_bytes = 0, md_zero_mut_bytes = 0;
+    uint64_t last_fetch_bytes = 0; // device-to-host bytes of the last mspb_fetch
 };
 
 static const char *const PHASE_NAMES[MSPB_NUM_PHASES] = { "params+kept", "K1 count+scan", "K2 place", "K3 sort",
@@ -288,6 +291,12 @@ extern "C" int mspb_ctx_create(int device, mspb_ctx_t **out)
         cudaEventCreate(&e);
     }
     cudaEventCreateWithFlags(&ctx->ev_k1, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&ctx->ev_keys, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&ctx->ev_copied, cudaEventDisableTiming);
+    if (cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking) != cudaSuccess) {
+        mspb_ctx_destroy(ctx);
+        return MSPB_ERR_CUDA;
+    }
     ctx->log.stream = ctx->stream;
     if (cudaMallocHost((void **) &ctx->host, sizeof(HostTotals)) != cudaSuccess
         || cudaMallocHost((void **) &ctx->or_and_host, 2 * sizeof(uint64_t)) != cudaSuccess
@@ -339,8 +348,13 @@ extern "C" void mspb_ctx_destroy(mspb_ctx_t *ctx)
             cudaEventDestroy(e);
         }
     }
-    if (ctx->ev_k1 != nullptr) {
-        cudaEventDestroy(ctx->ev_k1);
+    for (cudaEvent_t e : { ctx->ev_k1, ctx->ev_keys, ctx->ev_copied }) {
+        if (e != nullptr) {
+            cudaEventDestroy(e);
+        }
+    }
+    if (ctx->copy_stream != nullptr) {
+        cudaStreamDestroy(ctx->copy_stream);
     }
     if (ctx->stream != nullptr) {
         cudaStreamDestroy(ctx->stream);
@@ -590,52 +604,86 @@ extern "C" int mspb_ctx_load_tables(mspb_ctx_t *ctx, const mspb_tables_t *t)
     ctx->E = t->num_edges;
     ctx->S0 = t->num_sites;
     ctx->M0 = t->num_mutations;
-    TRY(upload(ctx->node_time, t->node_time, ctx->N, st));
+    // whatever way this function returns, no copy from the caller's buffers is left in flight
+    struct Drain {
+        cudaStream_t a, b;
+        ~Drain()
+        {
+            cudaStreamSynchronize(a);
+            cudaStreamSynchronize(b);
+        }
+    } drain { st, ctx->copy_stream };
+    // The two columns K0's sorts read go first, on the main stream; everything else follows on
+    // the copy stream, so that with pinned sources the sorts run under the rest of the upload.
+    cudaStream_t cs = ctx->copy_stream;
     TRY(upload(ctx->edge_left, t->edge_left, ctx->E, st));
-    TRY(upload(ctx->edge_right, t->edge_right, ctx->E, st));
-    TRY(upload(ctx->edge_parent, t->edge_parent, ctx->E, st));
     TRY(upload(ctx->edge_child, t->edge_child, ctx->E, st));
+    CUDA_OK(cudaEventRecord(ctx->ev_keys, st));
+    CUDA_OK(cudaStreamWaitEvent(cs, ctx->ev_keys, 0)); // one copy engine direction: keep the order
+    TRY(upload(ctx->edge_right, t->edge_right, ctx->E, cs));
+    TRY(upload(ctx->edge_parent, t->edge_parent, ctx->E, cs));
+    TRY(upload(ctx->node_time, t->node_time, ctx->N, cs));
     static const uint64_t zero_off[1] = { 0 };
     if (ctx->S0 > 0) {
         const uint64_t *ao = t->site_ancestral_state_offset, *mo = t->site_metadata_offset;
-        TRY(upload(ctx->k_site_pos, t->site_position, ctx->S0, st));
-        TRY(upload(ctx->k_site_anc_off, ao, ctx->S0 + 1, st));
-        TRY(upload(ctx->k_site_anc, t->site_ancestral_state, (size_t) ao[ctx->S0], st));
+        TRY(upload(ctx->k_site_pos, t->site_position, ctx->S0, cs));
+        TRY(upload(ctx->k_site_anc_off, ao, ctx->S0 + 1, cs));
+        TRY(upload(ctx->k_site_anc, t->site_ancestral_state, (size_t) ao[ctx->S0], cs));
         ctx->kept_anc_bytes = ao[ctx->S0];
         ctx->kept_smd_bytes = mo != nullptr ? mo[ctx->S0] : 0;
         if (mo != nullptr) {
-            TRY(upload(ctx->k_site_md_off, mo, ctx->S0 + 1, st));
-            TRY(upload(ctx->k_site_md, t->site_metadata, (size_t) mo[ctx->S0], st));
+            TRY(upload(ctx->k_site_md_off, mo, ctx->S0 + 1, cs));
+            TRY(upload(ctx->k_site_md, t->site_metadata, (size_t) mo[ctx->S0], cs));
         } else {
             TRY(ctx->k_site_md_off.ensure(ctx->S0 + 1));
-            CUDA_OK(cudaMemsetAsync(ctx->k_site_md_off.p, 0, (ctx->S0 + 1) * sizeof(uint64_t), st));
+            CUDA_OK(cudaMemsetAsync(ctx->k_site_md_off.p, 0, (ctx->S0 + 1) * sizeof(uint64_t), cs));
             TRY(ctx->k_site_md.ensure(1));
         }
     }
     if (ctx->M0 > 0) {
         const uint64_t *dof = t->mutation_derived_state_offset, *mo = t->mutation_metadata_offset;
-        TRY(upload(ctx->k_mut_site, t->mutation_site, ctx->M0, st));
-        TRY(upload(ctx->k_mut_node, t->mutation_node, ctx->M0, st));
+        TRY(upload(ctx->k_mut_site, t->mutation_site, ctx->M0, cs));
+        TRY(upload(ctx->k_mut_node, t->mutation_node, ctx->M0, cs));
         ctx->have_mut_time = t->mutation_time != nullptr;
         if (ctx->have_mut_time) {
-            TRY(upload(ctx->k_mut_time, t->mutation_time, ctx->M0, st));
+            TRY(upload(ctx->k_mut_time, t->mutation_time, ctx->M0, cs));
         }
-        TRY(upload(ctx->k_mut_der_off, dof, ctx->M0 + 1, st));
-        TRY(upload(ctx->k_mut_der, t->mutation_derived_state, (size_t) dof[ctx->M0], st));
+        TRY(upload(ctx->k_mut_der_off, dof, ctx->M0 + 1, cs));
+        TRY(upload(ctx->k_mut_der, t->mutation_derived_state, (size_t) dof[ctx->M0], cs));
         ctx->kept_der_bytes = dof[ctx->M0];
         ctx->kept_mmd_bytes = mo != nullptr ? mo[ctx->M0] : 0;
         if (mo != nullptr) {
-            TRY(upload(ctx->k_mut_md_off, mo, ctx->M0 + 1, st));
-            TRY(upload(ctx->k_mut_md, t->mutation_metadata, (size_t) mo[ctx->M0], st));
+            TRY(upload(ctx->k_mut_md_off, mo, ctx->M0 + 1, cs));
+            TRY(upload(ctx->k_mut_md, t->mutation_metadata, (size_t) mo[ctx->M0], cs));
         } else {
             TRY(ctx->k_mut_md_off.ensure(ctx->M0 + 1));
-            CUDA_OK(cudaMemsetAsync(ctx->k_mut_md_off.p, 0, (ctx->M0 + 1) * sizeof(uint64_t), st));
+            CUDA_OK(cudaMemsetAsync(ctx->k_mut_md_off.p, 0, (ctx->M0 + 1) * sizeof(uint64_t), cs));
             TRY(ctx->k_mut_md.ensure(1));
         }
     }
     (void) zero_off;
     TRY(ctx->child_start.ensure(ctx->N + 2));
     TRY(ctx->ci.ensure(ctx->E + 1));
+    CUDA_OK(cudaEventRecord(ctx->ev_copied, cs));
+
+    // K0, first half: the stable sort by left, then by child, reads only the two columns that
+    // are already there (any values sort; the rows are validated before the permutation uses them)
+    int k0_cur = 0;
+    RadixSortBuffers<uint64_t> k0_sb;
+    if (ctx->E > 0) {
+        TreeSeqView tsk = make_ts_view(ctx);
+        TRY(ensure_sort_buffers(ctx, ctx->E, false, true));
+        k0_sb = sort_buffers64(ctx);
+        MSPB_LAUNCH(ctx->log, "k0_child_keys", k0_child_keys_kernel<<<grid_for(ctx->E, 256), 256, 0, st>>>(tsk, k0_sb.keys[0], k0_sb.vals[0]));
+        int cur = device_radix_sort<uint64_t>(k0_sb, ctx->E, 0, false, st, ctx->log, nullptr);
+        if (cur != 0) {
+            std::swap(k0_sb.keys[0], k0_sb.keys[1]);
+            std::swap(k0_sb.vals[0], k0_sb.vals[1]);
+        }
+        MSPB_LAUNCH(ctx->log, "k0_child_keys2", k0_child_keys2_kernel<<<grid_for(ctx->E, 256), 256, 0, st>>>(tsk, k0_sb.vals[0], k0_sb.keys[0]));
+        k0_cur = device_radix_sort<uint64_t>(k0_sb, ctx->E, 0, false, st, ctx->log, nullptr);
+    }
+    CUDA_OK(cudaStreamWaitEvent(st, ctx->ev_copied, 0));
 
     // validation
     HostTotals *dt = (HostTotals *) ctx->dev_totals.p;
@@ -666,22 +714,12 @@ extern "C" int mspb_ctx_load_tables(mspb_ctx_t *ctx, const mspb_tables_t *t)
         return TSK_E(code);
     }
 
-    // K0: child-sorted interval index = stable sort by left, then by child
+    // K0, second half: the 32-byte entries in (child, left) order, then the parent links
     if (ctx->E == 0) {
         CUDA_OK(cudaMemsetAsync(ctx->child_start.p, 0, (ctx->N + 2) * sizeof(uint32_t), st));
     } else {
-        TRY(ensure_sort_buffers(ctx, ctx->E, false, true));
-        RadixSortBuffers<uint64_t> sb = sort_buffers64(ctx);
-        MSPB_LAUNCH(ctx->log, "k0_child_keys", k0_child_keys_kernel<<<grid_for(ctx->E, 256), 256, 0, st>>>(ts, sb.keys[0], sb.vals[0]));
-        int cur = device_radix_sort<uint64_t>(sb, ctx->E, 0, false, st, ctx->log, nullptr);
-        if (cur != 0) {
-            std::swap(sb.keys[0], sb.keys[1]);
-            std::swap(sb.vals[0], sb.vals[1]);
-        }
-        MSPB_LAUNCH(ctx->log, "k0_child_keys2", k0_child_keys2_kernel<<<grid_for(ctx->E, 256), 256, 0, st>>>(ts, sb.vals[0], sb.keys[0]));
-        cur = device_radix_sort<uint64_t>(sb, ctx->E, 0, false, st, ctx->log, nullptr);
         MSPB_LAUNCH(ctx->log, "k0_permute", k0_permute_kernel<<<grid_for(ctx->E, 256), 256, 0, st>>>(
-            ts, sb.vals[cur], ctx->ci.p, ctx->child_start.p));
+            ts, k0_sb.vals[k0_cur], ctx->ci.p, ctx->child_start.p));
         // MSPB_K0_MAX_SPAN (tests only) lowers the span-count limit so that the walk's range
         // recovery path runs on small inputs
         uint32_t max_count = 256;
@@ -1966,17 +2004,18 @@ extern "C" int mspb_fetch(mspb_ctx_t *ctx, const mspb_columns_t *h)
     cudaStream_t st = ctx->stream;
     const mspb_counts_t &c = ctx->counts;
     const uint64_t S = c.num_sites, M = c.num_mutations, ow = c.offset_bytes;
+    ctx->last_fetch_bytes = 0;
 #define D2H(dst, src, bytes)                                                                                           \
     do {                                                                                                               \
         if ((dst) != nullptr && (bytes) > 0) {                                                                         \
             CUDA_OK(cudaMemcpyAsync((dst), (src), (bytes), cudaMemcpyDeviceToHost, st));                               \
+            ctx->last_fetch_bytes += (bytes);                                                                          \
         }                                                                                                              \
     } while (0)
     D2H(h->site_position, ctx->o_site_pos.p, S * sizeof(double));
     D2H(h->site_ancestral_state, ctx->o_site_anc.p, c.ancestral_state_bytes);
     D2H(h->site_ancestral_state_offset, ctx->o_site_anc_off.p, (S + 1) * ow);
     D2H(h->site_metadata, ctx->o_site_md.p, c.site_metadata_bytes);
-    D2H(h->site_metadata_offset, ctx->o_site_md_off.p, (S + 1) * ow);
     D2H(h->mutation_site, ctx->o_mut_site.p, M * sizeof(int32_t));
     D2H(h->mutation_node, ctx->o_mut_node.p, M * sizeof(int32_t));
     D2H(h->mutation_parent, ctx->o_mut_parent.p, M * sizeof(int32_t));
@@ -1984,10 +2023,33 @@ extern "C" int mspb_fetch(mspb_ctx_t *ctx, const mspb_columns_t *h)
     D2H(h->mutation_derived_state, ctx->o_mut_der.p, c.derived_state_bytes);
     D2H(h->mutation_derived_state_offset, ctx->o_mut_der_off.p, (M + 1) * ow);
     D2H(h->mutation_metadata, ctx->o_mut_md.p, c.mutation_metadata_bytes);
-    D2H(h->mutation_metadata_offset, ctx->o_mut_md_off.p, (M + 1) * ow);
+    // The metadata offset columns are all zero unless rows were kept with metadata or the model
+    // writes some (SLiM), and the context tracks that (md_zero_*): such a column is not worth
+    // 8 bytes per row of PCIe traffic.  The host fills it while the other copies are in flight.
+    const bool site_md_zero = ctx->md_zero_site_ptr == ctx->o_site_md_off.p && ctx->md_zero_site_bytes >= (S + 1) * ow
+                              && c.site_metadata_bytes == 0;
+    const bool mut_md_zero = ctx->md_zero_mut_ptr == ctx->o_mut_md_off.p && ctx->md_zero_mut_bytes >= (M + 1) * ow
+                             && c.mutation_metadata_bytes == 0;
+    if (!site_md_zero) {
+        D2H(h->site_metadata_offset, ctx->o_site_md_off.p, (S + 1) * ow);
+    }
+    if (!mut_md_zero) {
+        D2H(h->mutation_metadata_offset, ctx->o_mut_md_off.p, (M + 1) * ow);
+    }
 #undef D2H
+    if (site_md_zero && h->site_metadata_offset != nullptr) {
+        memset(h->site_metadata_offset, 0, (S + 1) * ow);
+    }
+    if (mut_md_zero && h->mutation_metadata_offset != nullptr) {
+        memset(h->mutation_metadata_offset, 0, (M + 1) * ow);
+    }
     CUDA_OK(cudaStreamSynchronize(st));
     return 0;
+}
+
+extern "C" uint64_t mspb_last_fetch_bytes(const mspb_ctx_t *ctx)
+{
+    return ctx != nullptr ? ctx->last_fetch_bytes : 0;
 }
 
 extern "C" void mspb_columns_free(mspb_columns_t *c)
