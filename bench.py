@@ -390,7 +390,9 @@ def run_b200_arm(args, rank, local_rank, world):
         t, host_ts["edges"][k] = pinned_like(ts["edges"][k])
         hold.append(t)
     E, N = len(ts["edges"]["left"]), len(ts["nodes"]["time"])
-    h2d_bytes = E * (8 + 8 + 4 + 4) + N * 8
+    # node and edge columns: the whole of them at one GPU, this rank's 1 / world share otherwise
+    # (sharded upload; the shares are padded to equal sizes); kept rows are copied whole
+    h2d_bytes = sum(-(-n // world) * w for n, w in ((E, 8), (E, 8), (E, 4), (E, 4), (N, 8)))
     for tbl in ("sites", "mutations"):  # kept rows of a keep=True workload
         h2d_bytes += sum(int(np.asarray(v).nbytes) for v in ts[tbl].values())
 
@@ -442,7 +444,15 @@ def run_b200_arm(args, rank, local_rank, world):
                                   fetch=fetch_into is not None, out=fetch_into)
         return ctx.counts["num_new_mutations"]
 
-    ctx.load_tables(host_ts)
+    def load():
+        """This step's input tables, host -> device (+ index build).  With several GPUs the tables
+        are replicated: every rank uploads 1 / world of them and NCCL all-gathers the shares."""
+        if world == 1:
+            ctx.load_tables(host_ts)
+        else:
+            sharding.load_tables_sharded(ctx, host_ts, rank=rank, world=world)
+
+    load()
     # ---- device-resident throughput
     for i in range(args.warmup):
         overlay(i)
@@ -488,7 +498,7 @@ def run_b200_arm(args, rank, local_rank, world):
     # ---- end to end through the host-buffer calls
     d2h_bytes = 0
     for i in range(min(2, args.warmup)):
-        ctx.load_tables(host_ts)
+        load()
         overlay(200 + i, out_bufs)
     sync_all()
     ev2, ev3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -496,7 +506,7 @@ def run_b200_arm(args, rank, local_rank, world):
     ev2.record(stream)
     e2e_muts = 0
     for i in range(args.steps):
-        ctx.load_tables(host_ts)
+        load()
         e2e_muts += overlay(300 + i, out_bufs)
         sizes = ctx.result_sizes()
         d2h_bytes = ctx.last_fetch_bytes()  # what crossed the bus (all-zero metadata offsets are not copied)
@@ -578,8 +588,10 @@ def run_b200_arm(args, rank, local_rank, world):
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d_total, "d2h_bytes_per_step": d2h_total,
                 "ms_per_step": e2e_ms / args.steps,
                 "path": "mspb_ctx_load_tables + mspb_generate + mspb_fetch, pinned host buffers" if world == 1 else
-                "per rank: mspb_ctx_load_tables + mspb_generate_begin / count all-gather (NCCL) / mspb_generate_end / "
-                "byte all-gather / mspb_shift_offsets + mspb_fetch of the rank's slice into pinned host buffers"},
+                "per rank: mspb_ctx_load_tables_begin (1 / world of the replicated tables over PCIe) / in-place NCCL "
+                "all-gather of the shares over NVLink / mspb_ctx_load_tables_end, then mspb_generate_begin / count "
+                "all-gather (NCCL) / mspb_generate_end / byte all-gather / mspb_shift_offsets + mspb_fetch of the "
+                "rank's slice into pinned host buffers"},
         "gpu_launches": launches,
         "clocks": clocks,
         "roofline": roofline,

@@ -187,6 +187,23 @@ void mspb_ctx_destroy(mspb_ctx_t *ctx);
 /* Validates (tskit check_integrity(0) subset, lib/mutgen.c:1316), uploads the tables
  * and builds the child-sorted edge index.  Reusable across mspb_generate calls. */
 int mspb_ctx_load_tables(mspb_ctx_t *ctx, const mspb_tables_t *tables);
+
+/* The same with the upload shared between the `world` GPUs of a genome-sharded job (the tables
+ * are replicated: every rank needs all of them).  _begin copies only this rank's 1 / world
+ * share of the five large columns (node time, edge left / right / parent / child; kept rows
+ * are copied whole) and describes the device buffers: buffer k is world * bytes_per_rank
+ * bytes long and this rank's share sits at rank * bytes_per_rank.  The caller all-gathers
+ * every buffer IN PLACE on the context's stream (ncclAllGather / torch.distributed
+ * .all_gather_into_tensor over NVLink) and then calls _end, which validates the rows and
+ * builds the index.  With world == 1 the pair is equivalent to mspb_ctx_load_tables. */
+typedef struct {
+    void *ptr; /* device memory owned by the context */
+    uint64_t bytes_per_rank;
+} mspb_shard_t;
+#define MSPB_NUM_TABLE_SHARDS 5
+int mspb_ctx_load_tables_begin(mspb_ctx_t *ctx, const mspb_tables_t *tables, uint32_t rank, uint32_t world,
+    mspb_shard_t shards[MSPB_NUM_TABLE_SHARDS]);
+int mspb_ctx_load_tables_end(mspb_ctx_t *ctx);
 /* Runs the overlay on the device; the result stays resident until the next call. */
 int mspb_generate(mspb_ctx_t *ctx, const mspb_params_t *params, mspb_counts_t *counts);
 /* Two-phase form for genome-sharded calls (one context per GPU, params.slice_left/right

@@ -95,6 +95,13 @@ _COLUMNS = [
 ]
 
 
+class _Shard(C.Structure):
+    _fields_ = [("ptr", C.c_void_p), ("bytes_per_rank", C.c_uint64)]
+
+
+NUM_TABLE_SHARDS = 5
+
+
 class _Columns(C.Structure):
     _fields_ = [(name, C.c_void_p) for name, _ in _COLUMNS]
 
@@ -106,7 +113,8 @@ EXPORTED_SYMBOLS = [
     "mspb_ctx_stream", "mspb_kernel_timing", "mspb_kernel_time", "mspb_selftest_sort",
     "mspb_generate_begin", "mspb_generate_end", "mspb_shift_offsets",
     "mspb_exchange_buffers", "mspb_exchange_post_counts", "mspb_generate_end_device",
-    "mspb_generate_finish_device", "mspb_last_fetch_bytes",
+    "mspb_generate_finish_device", "mspb_last_fetch_bytes", "mspb_ctx_load_tables_begin",
+    "mspb_ctx_load_tables_end",
 ]
 
 EXCHANGE_WORDS = 8  # MSPB_EXCHANGE_WORDS
@@ -138,6 +146,9 @@ def lib():
         L.mspb_ctx_destroy.argtypes = [C.c_void_p]
         L.mspb_ctx_destroy.restype = None
         L.mspb_ctx_load_tables.argtypes = [C.c_void_p, C.POINTER(_Tables)]
+        L.mspb_ctx_load_tables_begin.argtypes = [C.c_void_p, C.POINTER(_Tables), C.c_uint32, C.c_uint32,
+                                                 C.POINTER(_Shard)]
+        L.mspb_ctx_load_tables_end.argtypes = [C.c_void_p]
         L.mspb_generate.argtypes = [C.c_void_p, C.POINTER(_Params), C.POINTER(_Counts)]
         L.mspb_generate_begin.argtypes = [C.c_void_p, C.POINTER(_Params), C.POINTER(_Counts)]
         L.mspb_generate_end.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64, C.POINTER(_Counts)]
@@ -260,8 +271,9 @@ class Context:
     def __exit__(self, *exc):
         self.close()
 
-    def load_tables(self, d):
-        """``d`` is a tskit ``asdict()``-style dict of numpy columns."""
+    @staticmethod
+    def _tables_struct(d):
+        """``mspb_tables_t`` for the ``asdict()``-style dict ``d`` plus the arrays it points into."""
         hold = []
         t = _Tables()
         t.sequence_length = float(d["sequence_length"])
@@ -299,8 +311,26 @@ class Context:
                 t.mutation_time = _p(mt)
             t.mutation_derived_state, t.mutation_derived_state_offset = _p(md), _p(mdo)
             t.mutation_metadata, t.mutation_metadata_offset = _p(mm), _p(mmo)
+        return t, hold
+
+    def load_tables(self, d):
+        """``d`` is a tskit ``asdict()``-style dict of numpy columns."""
+        t, hold = self._tables_struct(d)
         check(lib().mspb_ctx_load_tables(self._h, C.byref(t)))
         del hold
+
+    def load_tables_begin(self, d, rank, world):
+        """Sharded upload (``mspb_ctx_load_tables_begin``): copies this rank's share of the large
+        columns and returns ``[(device pointer, bytes per rank)] * 5``: the buffers the caller must
+        all-gather in place on this context's stream before :meth:`load_tables_end`."""
+        t, hold = self._tables_struct(d)
+        shards = (_Shard * NUM_TABLE_SHARDS)()
+        check(lib().mspb_ctx_load_tables_begin(self._h, C.byref(t), int(rank), int(world), shards))
+        del hold  # the call returns after its copies have completed
+        return [(int(sh.ptr or 0), int(sh.bytes_per_rank)) for sh in shards]
+
+    def load_tables_end(self):
+        check(lib().mspb_ctx_load_tables_end(self._h))
 
     def load_native(self, t):
         """``t`` is an ``mspb_tables_t`` already filled in, e.g. by ``trees_io.Store.native_tables``

@@ -78,6 +78,7 @@ struct mspb_ctx {
     std::vector<double> cache_map_pos, cache_map_rate, cache_model_root, cache_model_matrix;
     std::vector<uint64_t> cache_model_off;
     std::vector<char> cache_model_bytes;
+    bool tables_pending = false; // between mspb_ctx_load_tables_begin and _end
     cudaStream_t copy_stream = nullptr; // load_tables: the columns K0's sorts do not read arrive here
     cudaEvent_t ev_keys = nullptr, ev_copied = nullptr;
     cudaEvent_t ev_k1 = nullptr; // the K1 totals have reached the host (no timing: cheap to wait on)
@@ -581,14 +582,22 @@ int lookback_state(mspb_ctx *ctx, uint64_t tiles, int halves, LbWord **lb)
 
 } // namespace
 
-extern "C" int mspb_ctx_load_tables(mspb_ctx_t *ctx, const mspb_tables_t *t)
-{
-    if (ctx == nullptr || t == nullptr) {
-        return MSPB_ERR_BAD_PARAM_VALUE;
+namespace {
+
+struct StreamDrain {
+    // whatever way a loader returns, no copy from the caller's buffers is left in flight
+    cudaStream_t a, b;
+    ~StreamDrain()
+    {
+        cudaStreamSynchronize(a);
+        cudaStreamSynchronize(b);
     }
-    CUDA_OK(cudaSetDevice(ctx->device));
-    cudaStream_t st = ctx->stream;
+};
+
+int tables_prepare(mspb_ctx_t *ctx, const mspb_tables_t *t)
+{
     ctx->tables_loaded = false;
+    ctx->tables_pending = false;
     ctx->generated = false;
     if (!std::isfinite(t->sequence_length) || t->sequence_length <= 0) {
         /* mutgen_alloc rejects L <= 0 before anything else (lib/mutgen.c:760) */
@@ -604,25 +613,12 @@ extern "C" int mspb_ctx_load_tables(mspb_ctx_t *ctx, const mspb_tables_t *t)
     ctx->E = t->num_edges;
     ctx->S0 = t->num_sites;
     ctx->M0 = t->num_mutations;
-    // whatever way this function returns, no copy from the caller's buffers is left in flight
-    struct Drain {
-        cudaStream_t a, b;
-        ~Drain()
-        {
-            cudaStreamSynchronize(a);
-            cudaStreamSynchronize(b);
-        }
-    } drain { st, ctx->copy_stream };
-    // The two columns K0's sorts read go first, on the main stream; everything else follows on
-    // the copy stream, so that with pinned sources the sorts run under the rest of the upload.
-    cudaStream_t cs = ctx->copy_stream;
-    TRY(upload(ctx->edge_left, t->edge_left, ctx->E, st));
-    TRY(upload(ctx->edge_child, t->edge_child, ctx->E, st));
-    CUDA_OK(cudaEventRecord(ctx->ev_keys, st));
-    CUDA_OK(cudaStreamWaitEvent(cs, ctx->ev_keys, 0)); // one copy engine direction: keep the order
-    TRY(upload(ctx->edge_right, t->edge_right, ctx->E, cs));
-    TRY(upload(ctx->edge_parent, t->edge_parent, ctx->E, cs));
-    TRY(upload(ctx->node_time, t->node_time, ctx->N, cs));
+    return 0;
+}
+
+// existing sites and mutations (read by keep=True calls), on stream cs
+int tables_upload_kept(mspb_ctx_t *ctx, const mspb_tables_t *t, cudaStream_t cs)
+{
     static const uint64_t zero_off[1] = { 0 };
     if (ctx->S0 > 0) {
         const uint64_t *ao = t->site_ancestral_state_offset, *mo = t->site_metadata_offset;
@@ -662,14 +658,17 @@ extern "C" int mspb_ctx_load_tables(mspb_ctx_t *ctx, const mspb_tables_t *t)
         }
     }
     (void) zero_off;
-    TRY(ctx->child_start.ensure(ctx->N + 2));
-    TRY(ctx->ci.ensure(ctx->E + 1));
-    CUDA_OK(cudaEventRecord(ctx->ev_copied, cs));
+    return 0;
+}
 
-    // K0, first half: the stable sort by left, then by child, reads only the two columns that
-    // are already there (any values sort; the rows are validated before the permutation uses them)
+// K0, first half: the stable sort by left, then by child, reads only edge_left and edge_child
+// (any values sort; the rows are validated before the permutation uses them)
+int k0_sort(mspb_ctx_t *ctx, RadixSortBuffers<uint64_t> *sb_out, int *cur_out)
+{
+    cudaStream_t st = ctx->stream;
     int k0_cur = 0;
     RadixSortBuffers<uint64_t> k0_sb;
+    memset(&k0_sb, 0, sizeof(k0_sb));
     if (ctx->E > 0) {
         TreeSeqView tsk = make_ts_view(ctx);
         TRY(ensure_sort_buffers(ctx, ctx->E, false, true));
@@ -683,8 +682,15 @@ extern "C" int mspb_ctx_load_tables(mspb_ctx_t *ctx, const mspb_tables_t *t)
         MSPB_LAUNCH(ctx->log, "k0_child_keys2", k0_child_keys2_kernel<<<grid_for(ctx->E, 256), 256, 0, st>>>(tsk, k0_sb.vals[0], k0_sb.keys[0]));
         k0_cur = device_radix_sort<uint64_t>(k0_sb, ctx->E, 0, false, st, ctx->log, nullptr);
     }
-    CUDA_OK(cudaStreamWaitEvent(st, ctx->ev_copied, 0));
+    *sb_out = k0_sb;
+    *cur_out = k0_cur;
+    return 0;
+}
 
+// validation of every row, then K0's second half
+int tables_finish(mspb_ctx_t *ctx, RadixSortBuffers<uint64_t> k0_sb, int k0_cur)
+{
+    cudaStream_t st = ctx->stream;
     // validation
     HostTotals *dt = (HostTotals *) ctx->dev_totals.p;
     CUDA_OK(cudaMemsetAsync(&dt->first_bad, 0xff, sizeof(unsigned long long), st));
@@ -737,6 +743,93 @@ extern "C" int mspb_ctx_load_tables(mspb_ctx_t *ctx, const mspb_tables_t *t)
     ctx->tables_loaded = true;
     ctx->slice_cache_valid = false;
     return 0;
+}
+
+} // namespace
+
+extern "C" int mspb_ctx_load_tables(mspb_ctx_t *ctx, const mspb_tables_t *t)
+{
+    if (ctx == nullptr || t == nullptr) {
+        return MSPB_ERR_BAD_PARAM_VALUE;
+    }
+    CUDA_OK(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    TRY(tables_prepare(ctx, t));
+    StreamDrain drain { st, ctx->copy_stream };
+    // The two columns K0's sorts read go first, on the main stream; everything else follows on
+    // the copy stream, so that with pinned sources the sorts run under the rest of the upload.
+    cudaStream_t cs = ctx->copy_stream;
+    TRY(upload(ctx->edge_left, t->edge_left, ctx->E, st));
+    TRY(upload(ctx->edge_child, t->edge_child, ctx->E, st));
+    CUDA_OK(cudaEventRecord(ctx->ev_keys, st));
+    CUDA_OK(cudaStreamWaitEvent(cs, ctx->ev_keys, 0)); // one copy engine direction: keep the order
+    TRY(upload(ctx->edge_right, t->edge_right, ctx->E, cs));
+    TRY(upload(ctx->edge_parent, t->edge_parent, ctx->E, cs));
+    TRY(upload(ctx->node_time, t->node_time, ctx->N, cs));
+    TRY(tables_upload_kept(ctx, t, cs));
+    TRY(ctx->child_start.ensure(ctx->N + 2));
+    TRY(ctx->ci.ensure(ctx->E + 1));
+    CUDA_OK(cudaEventRecord(ctx->ev_copied, cs));
+    RadixSortBuffers<uint64_t> k0_sb;
+    int k0_cur = 0;
+    TRY(k0_sort(ctx, &k0_sb, &k0_cur));
+    CUDA_OK(cudaStreamWaitEvent(st, ctx->ev_copied, 0));
+    return tables_finish(ctx, k0_sb, k0_cur);
+}
+
+// Sharded upload of the replicated tables (multi-GPU): this rank copies its 1 / world share of
+// the five big columns; the caller all-gathers the shares in place on the context's stream
+// (NVLink instead of `world` copies of everything over PCIe); mspb_ctx_load_tables_end then
+// validates and builds the index.
+extern "C" int mspb_ctx_load_tables_begin(mspb_ctx_t *ctx, const mspb_tables_t *t, uint32_t rank, uint32_t world,
+    mspb_shard_t *shards)
+{
+    if (ctx == nullptr || t == nullptr || shards == nullptr || world == 0 || rank >= world) {
+        return MSPB_ERR_BAD_PARAM_VALUE;
+    }
+    CUDA_OK(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    TRY(tables_prepare(ctx, t));
+    StreamDrain drain { st, ctx->copy_stream };
+#define SHARD(k, buf, src, n, T)                                                                                     \
+    do {                                                                                                             \
+        const uint64_t per = ((uint64_t) (n) + world - 1) / world;                                                   \
+        TRY(ctx->buf.ensure((size_t) (per * world > 0 ? per * world : 1)));                                          \
+        const uint64_t lo = (uint64_t) rank * per;                                                                   \
+        const uint64_t hi = lo + per < (uint64_t) (n) ? lo + per : (uint64_t) (n);                                   \
+        if (hi > lo) {                                                                                               \
+            CUDA_OK(cudaMemcpyAsync(ctx->buf.p + lo, (src) + lo, (hi - lo) * sizeof(T), cudaMemcpyHostToDevice, st)); \
+        }                                                                                                            \
+        shards[k].ptr = ctx->buf.p;                                                                                  \
+        shards[k].bytes_per_rank = per * sizeof(T);                                                                  \
+    } while (0)
+    SHARD(0, node_time, t->node_time, ctx->N, double);
+    SHARD(1, edge_left, t->edge_left, ctx->E, double);
+    SHARD(2, edge_right, t->edge_right, ctx->E, double);
+    SHARD(3, edge_parent, t->edge_parent, ctx->E, int32_t);
+    SHARD(4, edge_child, t->edge_child, ctx->E, int32_t);
+#undef SHARD
+    TRY(tables_upload_kept(ctx, t, st));
+    TRY(ctx->child_start.ensure(ctx->N + 2));
+    TRY(ctx->ci.ensure(ctx->E + 1));
+    ctx->tables_pending = true;
+    return 0;
+}
+
+extern "C" int mspb_ctx_load_tables_end(mspb_ctx_t *ctx)
+{
+    if (ctx == nullptr) {
+        return MSPB_ERR_BAD_PARAM_VALUE;
+    }
+    if (!ctx->tables_pending) {
+        return MSPB_ERR_TABLES_NOT_LOADED;
+    }
+    CUDA_OK(cudaSetDevice(ctx->device));
+    ctx->tables_pending = false;
+    RadixSortBuffers<uint64_t> k0_sb;
+    int k0_cur = 0;
+    TRY(k0_sort(ctx, &k0_sb, &k0_cur));
+    return tables_finish(ctx, k0_sb, k0_cur);
 }
 
 // ---------------------------------------------------------------- generate

@@ -108,6 +108,35 @@ def nccl_device_allgather(ctx, world, group=None):
     return gather
 
 
+def load_tables_sharded(ctx, tables_dict, *, rank, world, group=None, all_gather=None):
+    """Replicates the tree sequence on every rank's GPU with ONE copy of it crossing PCIe in total:
+    each rank uploads its 1 / world share of the node and edge columns
+    (``mspb_ctx_load_tables_begin``), the shares are all-gathered in place over NVLink (NCCL,
+    enqueued on the context's stream), then every rank validates and builds its index
+    (``mspb_ctx_load_tables_end``).  ``all_gather(full, mine)`` replaces the NCCL call in tests."""
+    import torch
+
+    from . import _native
+
+    shards = ctx.load_tables_begin(tables_dict, rank, world)
+    if world > 1:
+        dev = torch.device("cuda", ctx.device)
+        stream = torch.cuda.ExternalStream(ctx.stream(), device=dev)
+        if all_gather is None:
+            import torch.distributed as dist
+
+            def all_gather(full, mine):
+                dist.all_gather_into_tensor(full, mine, group=group)
+
+        with torch.cuda.stream(stream):
+            for ptr, per in shards:
+                if per == 0:
+                    continue
+                full = torch.as_tensor(_native._DeviceArray(ptr, per * world, "|u1"), device=dev)
+                all_gather(full, full[rank * per:(rank + 1) * per])
+    ctx.load_tables_end()
+
+
 def run_slice_device(ctx, params, *, rank, world, gather, fetch=True, out=None):
     """:func:`run_slice` with the exchange kept on the device: ``gather()`` must all-gather the
     context's send buffer into its recv buffer on the context's stream (see

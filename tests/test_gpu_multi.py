@@ -1,4 +1,5 @@
-"""Two real GPUs, two processes, NCCL: the device-side exchange of a genome-sharded call
+"""Two real GPUs, two processes, NCCL: the sharded upload of the replicated tables
+(``sharding.load_tables_sharded``) and the device-side exchange of a genome-sharded call
 (``sharding.run_slice_device``).  Skipped on a single-GPU box (the same C path is covered
 there by ``test_device_exchange_equals_whole`` with a device-copy all-gather)."""
 import os
@@ -27,7 +28,8 @@ L = ts["sequence_length"]
 cuts = sharding.slice_cuts(L, world)
 mdl = dict(cases.INF_ALLELES, start_allele=500)
 ctx = _native.Context(rank)
-ctx.load_tables(ts)
+# the replicated tables: 1 / world of them from this rank's host, the rest over NCCL
+sharding.load_tables_sharded(ctx, ts, rank=rank, world=world)
 gather = sharding.nccl_device_allgather(ctx, world)
 common = dict(map_position=[0, L], map_rate=[2e-6], model=cases.native_model(mdl), discrete_genome=True, keep=False,
               start_time=-cases.FMAX, end_time=cases.FMAX, seed=77)

@@ -346,3 +346,47 @@ def test_slim_model_python_surface(native_built, ts_small):
     b = msp.sim_mutations(a, rate=2e-7, random_seed=9, model=model)
     assert model.next_id == 5 + b.num_mutations
 
+
+
+@pytest.mark.parametrize("world", [1, 2, 3, 8])
+def test_sharded_table_upload(native_built, ts_small, world):
+    """mspb_ctx_load_tables_begin / _end: every "rank" (contexts on one device here) uploads its
+    1 / world share of the node and edge columns, the shares are exchanged with device copies (the
+    stand-in for the in-place NCCL all-gather), and each context then overlays exactly what a
+    context loaded the ordinary way does, kept rows included."""
+    import torch
+
+    first, _ = run(_native.Context(0), ts_small, model=cases.JC69, rate=2e-7, seed=3)
+    ts = cases.with_kept(ts_small, first)
+    ref = _native.Context(0)
+    want, _ = run(ref, ts, model=cases.JC69, rate=3e-7, keep=True, seed=9)
+    dev = torch.device("cuda", 0)
+    ctxs = [_native.Context(0) for _ in range(world)]
+    shards = [c.load_tables_begin(ts, r, world) for r, c in enumerate(ctxs)]
+    views = [[torch.as_tensor(_native._DeviceArray(ptr, per * world, "|u1"), device=dev) if per else None
+              for ptr, per in sh] for sh in shards]
+    torch.cuda.synchronize()
+    for k in range(_native.NUM_TABLE_SHARDS):
+        per = shards[0][k][1]
+        assert all(sh[k][1] == per for sh in shards)
+        for r in range(world):
+            for q in range(world):
+                if q != r and per:
+                    views[r][k][q * per:(q + 1) * per].copy_(views[q][k][q * per:(q + 1) * per])
+    torch.cuda.synchronize()
+    for r, c in enumerate(ctxs):
+        c.load_tables_end()
+        got, _ = run(c, ts, model=cases.JC69, rate=3e-7, keep=True, seed=9, load=False)
+        for tbl in want:
+            for col in want[tbl]:
+                assert np.array_equal(np.asarray(want[tbl][col]), np.asarray(got[tbl][col])), (r, tbl, col)
+    # the hand-off is checked: _end without _begin is refused, and bad rows are still rejected
+    with pytest.raises(_native.LibraryError):
+        ctxs[0].load_tables_end()
+    bad = dict(ts, edges=dict(ts["edges"], child=np.array(ts["edges"]["child"], copy=True)))
+    bad["edges"]["child"][5] = len(ts["nodes"]["time"]) + 7
+    ctxs[0].load_tables_begin(bad, 0, 1)
+    with pytest.raises(_native.LibraryError):
+        ctxs[0].load_tables_end()
+    for c in ctxs + [ref]:
+        c.close()
