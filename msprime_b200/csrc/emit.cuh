@@ -248,6 +248,63 @@ MSPB_DEVFN void slim_write_state(const SortedView &sv, const ResolveView &rv, co
     }
 }
 
+// Fills the ChainFree table for an infinite-alleles call without kept rows: lane k finds the
+// first record whose derived (ancestral) number has more than k digits.  One warp; runs beside
+// K4 on the context's second stream.
+__global__ void k5_prefix_table_kernel(const uint32_t *__restrict__ site_row, const Counts3 *p1_total, uint64_t n,
+    uint64_t start_allele, const uint64_t *dev_bases, uint32_t fixed_len, const uint32_t *dense, ChainFree *cf)
+{
+    const uint32_t k = threadIdx.x;
+    if (dev_bases != nullptr) {
+        start_allele += dev_bases[2];
+    }
+    if (k == 0) {
+        // numbers must not wrap around 2^64 inside the call (they do in the reference, whose
+        // counter is a uint64 too: the look-back path reproduces that)
+        cf->enabled = (*dense == 0u && (fixed_len > 0 || start_allele <= ~0ull - (2 * n + 2))) ? 1u : 0u;
+        cf->fixed_len = fixed_len;
+        cf->der_upto[0] = cf->anc_upto[0] = 0;
+    }
+    if (k < 1 || k > 20 || fixed_len > 0) {
+        return;
+    }
+    uint64_t pw = 1;
+    bool all = false; // 10^k does not fit 64 bits: every number has at most k digits
+    for (uint32_t j = 0; j < k; j++) {
+        if (pw > ~0ull / 10ull) {
+            all = true;
+            break;
+        }
+        pw *= 10ull;
+    }
+    const uint64_t S = p1_total->s;
+    for (int which = 0; which < 2; which++) {
+        // first record i with start + i + site_row[i] + (derived ? 1 : 0) >= 10^k
+        const uint64_t add = which == 0 ? 1ull : 0ull;
+        uint64_t lo = 0, hi = n;
+        while (!all && lo < hi) {
+            const uint64_t mid = (lo + hi) >> 1;
+            if (start_allele + mid + site_row[mid] + add >= pw) {
+                hi = mid;
+            } else {
+                lo = mid + 1;
+            }
+        }
+        const uint64_t i = all ? n : lo;
+        if (which == 0) {
+            cf->der_upto[k] = i;
+        } else {
+            // heads before record i
+            uint64_t h = S;
+            if (i < n) {
+                const bool head = i == 0 || site_row[i - 1] != site_row[i];
+                h = (uint64_t) site_row[i] + (head ? 0u : 1u);
+            }
+            cf->anc_upto[k] = h;
+        }
+    }
+}
+
 // MODEL: 0 matrix, 1 infinite alleles, 2 SLiM.  KEPT: kept site / mutation rows are present.
 template <int MODEL, bool KEPT, bool OFF32>
 __global__ void __launch_bounds__(K5_THREADS, 4) k5_emit_kernel(SortedView sv, ResolveView rv, KeptView kept,
@@ -272,6 +329,8 @@ __global__ void __launch_bounds__(K5_THREADS, 4) k5_emit_kernel(SortedView sv, R
         out.mut_base += (uint32_t) out.dev_bases[1];
         model.start_allele += out.dev_bases[2];
     }
+    // without kept rows the tile's byte prefix may follow from its first record's index alone
+    const bool chain_free = !KEPT && MODEL != 2 && out.chain_free != nullptr && out.chain_free->enabled != 0u;
     if (threadIdx.x >= SCAN_THREADS) {
         // ---- the look-back warp: meets the workers at their barriers, otherwise only chains
         __syncthreads(); // lengths are in shared memory
@@ -280,9 +339,11 @@ __global__ void __launch_bounds__(K5_THREADS, 4) k5_emit_kernel(SortedView sv, R
         }
         __syncthreads(); // offsets and the tile's totals are visible
         const LbVal<2, true> aw = s_agg;
-        const LbVal<2, true> pw = lookback_warp<2, true>(lb, blockIdx.x, aw);
-        if (threadIdx.x == SCAN_THREADS) {
-            bcast = pw;
+        if (!chain_free) {
+            const LbVal<2, true> pw = lookback_warp<2, true>(lb, blockIdx.x, aw);
+            if (threadIdx.x == SCAN_THREADS) {
+                bcast = pw;
+            }
         }
         const uint64_t der = (uint64_t) aw.w[0][0] | ((uint64_t) aw.w[0][1] << 32);
         const uint64_t anc = (uint64_t) aw.w[1][0] | ((uint64_t) aw.w[1][1] << 32);
@@ -304,6 +365,7 @@ __global__ void __launch_bounds__(K5_THREADS, 4) k5_emit_kernel(SortedView sv, R
     uint32_t srow[K5_ITEMS];
     uint32_t pos32[K5_ITEMS]; // 32-bit position keys are read with everything else (wider ones later)
     Rec rcs[K5_ITEMS];
+    uint32_t heads_before = 0; // thread 0: site rows opened before the tile's first record
     {
         uint32_t slot[K5_ITEMS], before[K5_ITEMS], after[K5_ITEMS];
 #pragma unroll
@@ -332,6 +394,7 @@ __global__ void __launch_bounds__(K5_THREADS, 4) k5_emit_kernel(SortedView sv, R
                                : 0u;
             va[k] = slot[k];
         }
+        heads_before = srow[0] + ((base == 0 || before[0] != srow[0]) ? 0u : 1u);
     }
     // ---- lengths to shared memory
 #pragma unroll
@@ -430,6 +493,19 @@ __global__ void __launch_bounds__(K5_THREADS, 4) k5_emit_kernel(SortedView sv, R
     aw.w[1][3] = (uint32_t) (agg.smd >> 32);
     if (threadIdx.x == 0) {
         s_agg = aw;
+        if (chain_free) {
+            // what the look-back warp would hand over at the end is known now
+            uint64_t pd, pa;
+            out.chain_free->prefix(base, heads_before, &pd, &pa);
+            LbVal<2, true> pw;
+            pw.w[0][0] = (uint32_t) pd;
+            pw.w[0][1] = (uint32_t) (pd >> 32);
+            pw.w[0][2] = pw.w[0][3] = 0u;
+            pw.w[1][0] = (uint32_t) pa;
+            pw.w[1][1] = (uint32_t) (pa >> 32);
+            pw.w[1][2] = pw.w[1][3] = 0u;
+            bcast = pw;
+        }
     }
     __syncthreads(); // offsets are read striped below, by other threads than wrote them; totals out
     // ---- offsets across tiles.  When the tile's state bytes fit the stage (always, unless

@@ -1364,6 +1364,38 @@ MSPB_DEVFN void resolve_site(const TreeSeqView &ts, const KeptView &kept, const 
 
 // ---------------------------------------------------------------- K5
 
+// Byte prefixes of K5's tiles without a chain across tiles, for calls without kept rows whose
+// state lengths follow from a record's index alone.  Infinite alleles: record i of site row
+// s (rows count the heads before it) writes the number start + i + s + 1, and its site, if i
+// is the head, start + i + s; both grow with i, so "how many records / heads write at most k
+// digits" is one binary search per k (k5_prefix_table_kernel) and a tile's prefix is a sum over
+// at most 20 digit classes.  Matrix models whose alleles all have one length: rows x length.
+struct ChainFree {
+    uint32_t enabled; // 0: K5 chains its tiles with the look-back as usual
+    uint32_t fixed_len; // > 0: every state is this long (matrix model)
+    uint64_t der_upto[21]; // [k]: records whose derived number has at most k digits
+    uint64_t anc_upto[21]; // [k]: heads whose ancestral number has at most k digits
+    MSPB_DEVFN void prefix(uint64_t records, uint64_t heads, uint64_t *der, uint64_t *anc) const
+    {
+        if (fixed_len > 0) {
+            *der = records * fixed_len;
+            *anc = heads * fixed_len;
+            return;
+        }
+        uint64_t d = 0, a = 0, dp = 0, ap = 0;
+        for (uint32_t k = 1; k <= 20 && (dp < records || ap < heads); k++) {
+            const uint64_t dk = der_upto[k] < records ? der_upto[k] : records;
+            const uint64_t ak = anc_upto[k] < heads ? anc_upto[k] : heads;
+            d += (uint64_t) k * (dk - dp);
+            a += (uint64_t) k * (ak - ap);
+            dp = dk;
+            ap = ak;
+        }
+        *der = d;
+        *anc = a;
+    }
+};
+
 struct OutView {
     double *site_position;
     char *site_anc;
@@ -1383,6 +1415,7 @@ struct OutView {
     int off32; // offset columns are uint32 (else uint64)
     int write_md_off; // 0: the metadata offset columns are known to be all zero already
     int dry_run; // K5 computes the byte totals only (sizing pass of the SLiM model)
+    const ChainFree *chain_free; // tile prefixes without the look-back (nullptr: not applicable)
     MSPB_DEVFN void store_off(void *col, uint64_t row, uint64_t v) const
     {
         if (off32) {

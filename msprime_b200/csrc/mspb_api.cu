@@ -78,6 +78,8 @@ struct mspb_ctx {
     std::vector<double> cache_map_pos, cache_map_rate, cache_model_root, cache_model_matrix;
     std::vector<uint64_t> cache_model_off;
     std::vector<char> cache_model_bytes;
+    DBuf<ChainFree> chain_free; // K5's tile prefixes without a chain (emit.cuh)
+    cudaEvent_t ev_p1 = nullptr, ev_cf = nullptr; // site rows are final / the prefix table is ready
     bool tables_pending = false; // between mspb_ctx_load_tables_begin and _end
     cudaStream_t copy_stream = nullptr; // load_tables: the columns K0's sorts do not read arrive here
     cudaEvent_t ev_keys = nullptr, ev_copied = nullptr;
@@ -136,6 +138,7 @@ struct mspb_ctx {
     // two-phase calls (multi-GPU): everything K5 needs, kept between _begin and _end
     struct {
         bool valid = false, defer = false;
+        uint32_t fixed_len = 0; // matrix model: the common length of all alleles, or 0
         int exchange_stage = 0; // 2: mspb_generate_end_device ran, mspb_generate_finish_device is due
         SortedView sv;
         ResolveView rv;
@@ -293,6 +296,8 @@ extern "C" int mspb_ctx_create(int device, mspb_ctx_t **out)
     }
     cudaEventCreateWithFlags(&ctx->ev_k1, cudaEventDisableTiming);
     cudaEventCreateWithFlags(&ctx->ev_keys, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&ctx->ev_p1, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&ctx->ev_cf, cudaEventDisableTiming);
     cudaEventCreateWithFlags(&ctx->ev_copied, cudaEventDisableTiming);
     if (cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking) != cudaSuccess) {
         mspb_ctx_destroy(ctx);
@@ -349,7 +354,7 @@ extern "C" void mspb_ctx_destroy(mspb_ctx_t *ctx)
             cudaEventDestroy(e);
         }
     }
-    for (cudaEvent_t e : { ctx->ev_k1, ctx->ev_keys, ctx->ev_copied }) {
+    for (cudaEvent_t e : { ctx->ev_k1, ctx->ev_keys, ctx->ev_copied, ctx->ev_p1, ctx->ev_cf }) {
         if (e != nullptr) {
             cudaEventDestroy(e);
         }
@@ -1143,6 +1148,23 @@ int launch_emit(mspb_ctx *ctx)
     TRY(lookback_state(ctx, k5_tiles, 2, &lb4));
     const bool kept_rows = ctx->pending.sv.has_kept != 0, off32 = ctx->pending.out.off32 != 0;
     const int model_kind = ctx->pending.model.kind;
+    // Without kept rows, infinite-alleles and equal-length matrix states let every tile compute
+    // its byte prefix on its own (ChainFree): the table is filled on the second stream, beside
+    // K4, from the site rows P1 left.
+    ctx->pending.out.chain_free = nullptr;
+    if (!kept_rows && !ctx->pending.out.dry_run && R > 0
+        && (model_kind == MSPB_MODEL_INFINITE_ALLELES || (model_kind == MSPB_MODEL_MATRIX && ctx->pending.fixed_len > 0))) {
+        TRY(ctx->chain_free.ensure(1));
+        cudaStream_t cs = ctx->copy_stream;
+        CUDA_OK(cudaStreamWaitEvent(cs, ctx->ev_p1, 0));
+        k5_prefix_table_kernel<<<1, 32, 0, cs>>>(ctx->pending.sv.site_row, &dt->p1, R, ctx->pending.model.start_allele,
+            ctx->pending.out.dev_bases, model_kind == MSPB_MODEL_MATRIX ? ctx->pending.fixed_len : 0u, &dt->dense,
+            ctx->chain_free.p);
+        ctx->log.count++;
+        CUDA_OK(cudaEventRecord(ctx->ev_cf, cs));
+        CUDA_OK(cudaStreamWaitEvent(st, ctx->ev_cf, 0));
+        ctx->pending.out.chain_free = ctx->chain_free.p;
+    }
 #define MSPB_K5(M, K, O)                                                                                             \
     MSPB_LAUNCH(ctx->log, "k5_emit",                                                                                 \
         (k5_emit_kernel<M, K, O><<<k5_tiles, K5_THREADS, 0, st>>>(ctx->pending.sv, ctx->pending.rv,                \
@@ -1246,6 +1268,7 @@ int run_sorted_stages(mspb_ctx *ctx, const mspb_params_t *p, const TreeSeqView &
 #undef MSPB_P1_MODE
 #undef MSPB_P1
 
+    CUDA_OK(cudaEventRecord(ctx->ev_p1, st)); // the site rows are final from here on
     // ---- K4: sites with several records
     if (first_sort) {
         CUDA_OK(cudaEventRecord(ctx->ev[5], st));
@@ -1567,6 +1590,17 @@ static int generate_impl(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t 
     out.mut_base = 0;
     out.dev_bases = nullptr;
     out.dry_run = 0;
+    out.chain_free = nullptr;
+    // matrix models whose alleles all have one (non-zero) length: state bytes = rows x length
+    ctx->pending.fixed_len = 0;
+    if (p->model_kind == MSPB_MODEL_MATRIX && p->num_alleles > 0) {
+        const uint64_t len0 = p->allele_offset[1] - p->allele_offset[0];
+        bool same = len0 > 0 && len0 < 256;
+        for (uint64_t a = 1; a < p->num_alleles && same; a++) {
+            same = p->allele_offset[a + 1] - p->allele_offset[a] == len0;
+        }
+        ctx->pending.fixed_len = same ? (uint32_t) len0 : 0u;
+    }
     if (slim) {
         ctx->pending.defer = true; // K5 runs below, after its sizing pass
     }

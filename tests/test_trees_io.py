@@ -243,3 +243,36 @@ def test_wide_offsets_round_trip(tmp_path):
     with trees_io.Store(p) as st:
         t, _ = st.native_tables()
         assert t.site_ancestral_state_offset == st.get("sites/ancestral_state_offset").ctypes.data
+
+
+def test_cli_parser_mirrors_msp_mutations():
+    """Arguments and defaults of `msp mutations` (msprime/cli.py:1132-1173)."""
+    from msprime_b200 import cli
+
+    p = cli.get_parser()
+    a = p.parse_args(["mutations", "1e-8", "in.trees", "-o", "out.trees"])
+    assert a.mutation_rate == 1e-8 and a.input == "in.trees" and a.output == "out.trees"
+    assert a.random_seed is None and a.start_time is None and a.end_time is None and a.model == "jc69"
+    a = p.parse_args(["mutations", "0.5", "-s", "7", "--start-time", "1", "--end-time", "2.5", "-m", "pam"])
+    assert a.input is None and a.output is None and a.random_seed == 7
+    assert (a.start_time, a.end_time, a.model) == (1.0, 2.5, "pam")
+    with pytest.raises(SystemExit):
+        p.parse_args(["mutations", "1e-8", "-m", "hky"])  # needs arguments: not a name (mutations.py:1515-1518)
+    with pytest.raises(SystemExit):
+        p.parse_args([])
+
+
+def test_cli_fails_loudly_without_a_gpu(tmp_path):
+    """No CPU fallback: without a device the command stops with the library's error."""
+    import subprocess
+    import sys
+
+    import torch
+
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-m", "msprime_b200", "mutations", "1e-6", GOLDEN, "-o",
+                        str(tmp_path / "o.trees"), "-s", "1"], cwd=root, capture_output=True)
+    assert r.returncode != 0 and b"no CPU fallback" in r.stderr
+    assert not os.path.exists(tmp_path / "o.trees")
