@@ -244,6 +244,7 @@ struct RateMapView {
     const double *pos; // size + 1
     const double *rate; // size + 1 (rate[size] = 0)
     const double *cum; // size + 1
+    const double *inv_rate; // size + 1: 1 / rate, 0 where the rate is 0 (no mass: never selected)
     uint32_t size;
     int discrete;
 
@@ -290,7 +291,7 @@ struct RateMapView {
         }
         const double a = coord(fmax(left, pos[i]));
         const double b = coord(fmin(right, pos[i + 1]));
-        double x = coord(pos[i]) + (m - cum[i]) / rate[i];
+        double x = coord(pos[i]) + (m - cum[i]) * inv_rate[i]; // (the clamps below absorb the rounding)
         if (discrete) {
             x = floor(x);
             if (x > b - 1.0) {

@@ -100,7 +100,7 @@ struct mspb_ctx {
     DBuf<char> k_site_anc, k_site_md, k_mut_der, k_mut_md;
     DBuf<int32_t> k_mut_site, k_mut_node, k_site_allele, k_mut_allele;
     // call parameters on the device
-    DBuf<double> map_pos, map_rate, map_cum, model_root, model_matrix, replay;
+    DBuf<double> map_pos, map_rate, map_cum, map_inv, model_root, model_matrix, replay;
     DBuf<char> model_alleles;
     DBuf<uint64_t> model_allele_off;
     uint64_t kept_anc_bytes = 0, kept_smd_bytes = 0, kept_der_bytes = 0, kept_mmd_bytes = 0;
@@ -329,7 +329,7 @@ extern "C" void mspb_ctx_destroy(mspb_ctx_t *ctx)
     REL(k_site_pos); REL(k_mut_time); REL(k_site_anc_off); REL(k_site_md_off); REL(k_mut_der_off);
     REL(k_mut_md_off); REL(k_site_anc); REL(k_site_md); REL(k_mut_der); REL(k_mut_md);
     REL(k_mut_site); REL(k_mut_node); REL(k_site_allele); REL(k_mut_allele);
-    REL(map_pos); REL(map_rate); REL(map_cum); REL(model_root); REL(model_matrix); REL(replay);
+    REL(map_pos); REL(map_rate); REL(map_cum); REL(map_inv); REL(model_root); REL(model_matrix); REL(replay);
     REL(model_alleles); REL(model_allele_off);
     REL(goff); REL(loff); REL(k1_tiles); REL(xchg); REL(slice_edges); REL(slice_scan_tiles); REL(rec); REL(keys0); REL(keys1); REL(k32_0); REL(k32_1); REL(vals0); REL(vals1);
     REL(tile_hist); REL(rs_scan_tiles); REL(or_and); REL(lb_state);
@@ -938,11 +938,12 @@ int upload_params(mspb_ctx *ctx, const mspb_params_t *p, RateMapView *map, Model
                           && (R == 0 || memcmp(ctx->cache_map_rate.data(), p->map_rate, R * sizeof(double)) == 0);
     if (!same_map) {
         ctx->cache_map_valid = false;
-        std::vector<double> rate(R + 1), cum(R + 1);
+        std::vector<double> rate(R + 1), cum(R + 1), inv(R + 1);
         double sum = 0;
         for (uint64_t j = 0; j <= R; j++) {
             cum[j] = sum;
             rate[j] = j < R ? p->map_rate[j] : 0.0;
+            inv[j] = rate[j] > 0 ? 1.0 / rate[j] : 0.0;
             if (j < R) {
                 const double a = discrete ? std::ceil(p->map_position[j]) : p->map_position[j];
                 const double b = discrete ? std::ceil(p->map_position[j + 1]) : p->map_position[j + 1];
@@ -952,6 +953,7 @@ int upload_params(mspb_ctx *ctx, const mspb_params_t *p, RateMapView *map, Model
         TRY(upload(ctx->map_pos, p->map_position, R + 1, st));
         TRY(upload(ctx->map_rate, rate.data(), R + 1, st));
         TRY(upload(ctx->map_cum, cum.data(), R + 1, st));
+        TRY(upload(ctx->map_inv, inv.data(), R + 1, st));
         // the vectors must outlive the async copies
         CUDA_OK(cudaStreamSynchronize(st));
         ctx->cache_map_pos.assign(p->map_position, p->map_position + R + 1);
@@ -962,6 +964,7 @@ int upload_params(mspb_ctx *ctx, const mspb_params_t *p, RateMapView *map, Model
     map->pos = ctx->map_pos.p;
     map->rate = ctx->map_rate.p;
     map->cum = ctx->map_cum.p;
+    map->inv_rate = ctx->map_inv.p;
     map->size = (uint32_t) R;
     map->discrete = discrete ? 1 : 0;
 
