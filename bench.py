@@ -354,6 +354,28 @@ def slice_cuts(L, world):
     return [float(np.floor(L * r / world)) for r in range(world)] + [float(L)]
 
 
+def bind_near_gpu(index):
+    """Best effort: run this process on the CPUs of the NUMA node its GPU hangs off, so that the
+    pinned host buffers (first touched below) sit on that node and the DMA does not cross sockets.
+    Returns (original affinity, description); changes nothing when NVML or the cgroup says no."""
+    original = None
+    try:
+        original = os.sched_getaffinity(0)
+        import pynvml
+
+        pynvml.nvmlInit()
+        handle = pynvml.nvmlDeviceGetHandleByIndex(index)
+        words = pynvml.nvmlDeviceGetCpuAffinity(handle, (os.cpu_count() + 63) // 64)
+        cpus = {64 * i + b for i, word in enumerate(words) for b in range(64) if (word >> b) & 1}
+        cpus &= original
+        if cpus and cpus != original:
+            os.sched_setaffinity(0, cpus)
+            return original, f"{len(cpus)} of {len(original)} cpus (NVML affinity of GPU {index})"
+        return original, "unchanged (the GPU's CPUs are all of this process's CPUs)"
+    except Exception as e:  # noqa: BLE001
+        return original, f"unchanged ({type(e).__name__})"
+
+
 def run_b200_arm(args, rank, local_rank, world):
     import torch
     import torch.distributed as dist
@@ -376,6 +398,8 @@ def run_b200_arm(args, rank, local_rank, world):
     torch.cuda.set_device(local_rank)
     w = WORKLOADS[args.workload]
     ts = make_input(w)
+    affinity0, binding = bind_near_gpu(local_rank)
+    log(f"[bench] rank {rank}: cpu binding {binding}")
     L = float(ts["sequence_length"])
     cuts = slice_cuts(L, world)
     sl, sr = (0.0, 0.0) if world == 1 else (cuts[rank], cuts[rank + 1])
@@ -562,6 +586,11 @@ def run_b200_arm(args, rank, local_rank, world):
 
     # ---- CPU baseline (N = 1 only): the compiled reference on all host cores
     cpu = None
+    if affinity0 is not None:
+        try:
+            os.sched_setaffinity(0, affinity0)  # the CPU baseline below uses every core
+        except OSError:
+            pass
     if world == 1 and not args.no_cpu_baseline:
         kind, which = cpu_kind()
         cores = os.cpu_count() or 1
