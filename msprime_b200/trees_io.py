@@ -196,9 +196,10 @@ def load_tables_dict(path):
         ts = _tables.decode_ragged(prov["timestamp"], prov["timestamp_offset"])
         rec = _tables.decode_ragged(prov["record"], prov["record_offset"])
         d["provenances"] = [{"timestamp": t, "record": r} for t, r in zip(ts, rec)]
-    for tbl in ("sites", "mutations"):
-        for col in _SCHEMA[tbl][1]:
-            d[tbl][col[0]] = d[tbl][col[0]].view(np.int8)  # the dict protocol's dtype for state bytes
+    for tbl, (_, ragged) in _SCHEMA.items():
+        for name, kas in ragged:
+            if kas == U8 and isinstance(d.get(tbl), dict) and isinstance(d[tbl].get(name), np.ndarray):
+                d[tbl][name] = d[tbl][name].view(np.int8)  # the dict protocol's dtype for state and metadata bytes
     return d
 
 
@@ -210,11 +211,9 @@ def load(path):
 
         d2 = dict(d)
         d2.pop("file_uuid", None)
-        prov = d2.pop("provenances", [])
-        tc = tskit.TableCollection.fromdict(d2)
-        for p in prov:
-            tc.provenances.add_row(record=p["record"], timestamp=p["timestamp"])
-        return tc.tree_sequence()
+        prov = _provenance_columns(d2.pop("provenances", []))
+        d2["provenances"] = {k: (v if k.endswith("_offset") else v.view(np.int8)) for k, v in prov.items()}
+        return tskit.TableCollection.fromdict(d2).tree_sequence()
     return _tables.TableCollection.fromdict(d).tree_sequence()
 
 

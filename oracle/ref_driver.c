@@ -292,6 +292,13 @@ orc_trees_dump(const orc_input_t *in, uint64_t num_samples, const char *time_uni
         ret = msp_set_tsk_error(ret);
         goto out;
     }
+    /* the input columns carry no parents (mutgen recomputes them): make the file a valid
+     * tree sequence, as a file written by tskit after sim_mutations would be */
+    ret = tsk_table_collection_compute_mutation_parents(&tables, 0);
+    if (ret != 0) {
+        ret = msp_set_tsk_error(ret);
+        goto out;
+    }
     ret = tsk_table_collection_dump(&tables, path, 0);
     if (ret != 0) {
         ret = msp_set_tsk_error(ret);
