@@ -1,6 +1,11 @@
-"""``RateMap``: the part of ``msprime/intervals.py:35-97,292,447`` that the mutation
-path needs (constructor validation, ``uniform``, ``asdict`` and the basic read-only
-properties).  Slicing, hapmap I/O and ``RecombinationMap`` are out of scope."""
+"""``RateMap`` for the mutation path.
+
+The surface the overlay needs from ``msprime/intervals.py`` (:35-97 constructor contract, :292
+``uniform``, :447 ``asdict``, the read-only interval properties and the two point queries):
+keyword-only ``position`` (n + 1 break points, first one 0, strictly increasing) and ``rate``
+(n non-negative values, NaN = missing data).  Slicing, hapmap I/O and ``RecombinationMap`` are
+out of scope.  All derived arrays are computed once, in the constructor, and frozen.
+"""
 from __future__ import annotations
 
 import collections.abc
@@ -8,115 +13,98 @@ import collections.abc
 import numpy as np
 
 
-class RateMap(collections.abc.Mapping):
-    """Non-negative rates on consecutive half-open intervals ``[position[i], position[i+1])``.
+def _frozen(values) -> np.ndarray:
+    a = np.array(values, dtype=np.float64)
+    a.setflags(write=False)
+    return a
 
-    Same constructor contract as the reference: keyword-only ``position`` (n + 1
-    values starting at 0, strictly increasing) and ``rate`` (n values, NaN = missing).
-    """
+
+def _indexes(mask, shift=0):
+    return np.flatnonzero(mask) + shift
+
+
+class RateMap(collections.abc.Mapping):
+    """Piecewise-constant non-negative rate over ``[0, sequence_length)``: interval ``i`` is
+    ``[position[i], position[i + 1])`` with rate ``rate[i]``."""
 
     def __init__(self, *, position, rate):
-        self._position = np.array(position, dtype=float)
-        self._position.flags.writeable = False
-        self._rate = np.array(rate, dtype=float)
-        self._rate.flags.writeable = False
-        size = len(self._position)
-        if size < 2:
+        pos, r = _frozen(position), _frozen(rate)
+        if pos.size < 2:
             raise ValueError("Must have at least two positions")
-        if len(self._rate) != size - 1:
+        if r.size + 1 != pos.size:
             raise ValueError("Rate array must have one less entry than the position array")
-        if self._position[0] != 0:
+        if pos[0] != 0:
             raise ValueError("First position must be zero")
-        span = self.span
-        if np.any(span <= 0):
-            bad = np.where(span <= 0)[0] + 1
-            raise ValueError(f"Position values not strictly increasing at indexes {bad}")
-        if np.any(self._rate < 0):
-            bad = np.where(self._rate < 0)[0]
-            raise ValueError(f"Rate values negative at indexes {bad}")
-        self._missing = np.isnan(self._rate)
-        if int(np.sum(self._missing)) == len(self._rate):
+        widths = np.diff(pos)
+        if (widths <= 0).any():
+            raise ValueError(f"Position values not strictly increasing at indexes {_indexes(widths <= 0, 1)}")
+        if (r < 0).any():
+            raise ValueError(f"Rate values negative at indexes {_indexes(r < 0)}")
+        gaps = np.isnan(r)
+        if gaps.all():
             raise ValueError("All intervals are missing data")
-        self._cumulative_mass = np.insert(np.nancumsum(self.mass), 0, 0)
-        self._cumulative_mass.flags.writeable = False
+        self._cols = {
+            "position": pos,
+            "rate": r,
+            "left": pos[:-1],
+            "right": pos[1:],
+            "span": _frozen(widths),
+            "mid": _frozen(pos[:-1] + widths / 2),
+            "mass": _frozen(r * widths),
+            "missing": gaps,
+        }
+        self._cumulative_mass = _frozen(np.concatenate([[0.0], np.nancumsum(r * widths)]))
 
     @staticmethod
     def uniform(sequence_length, rate) -> "RateMap":
+        """One interval covering the whole sequence."""
         return RateMap(position=[0, sequence_length], rate=[rate])
 
-    @property
-    def position(self):
-        return self._position
+    # read-only columns
+    position = property(lambda self: self._cols["position"])
+    rate = property(lambda self: self._cols["rate"])
+    left = property(lambda self: self._cols["left"])
+    right = property(lambda self: self._cols["right"])
+    span = property(lambda self: self._cols["span"])
+    mid = property(lambda self: self._cols["mid"])
+    mass = property(lambda self: self._cols["mass"])
+    missing = property(lambda self: self._cols["missing"])
+    num_intervals = property(lambda self: int(self._cols["rate"].size))
+    sequence_length = property(lambda self: self._cols["position"][-1])
+    total_mass = property(lambda self: self._cumulative_mass[-1])
 
     @property
-    def rate(self):
-        return self._rate
-
-    @property
-    def left(self):
-        return self._position[:-1]
-
-    @property
-    def right(self):
-        return self._position[1:]
-
-    @property
-    def mid(self):
-        return self.left + self.span / 2
-
-    @property
-    def span(self):
-        return self.right - self.left
-
-    @property
-    def mass(self):
-        return self._rate * self.span
-
-    @property
-    def missing(self):
-        return self._missing
-
-    @property
-    def num_intervals(self) -> int:
-        return len(self._rate)
-
-    @property
-    def sequence_length(self):
-        return self._position[-1]
-
-    @property
-    def total_mass(self):
-        return self._cumulative_mass[-1]
-
-    @property
-    def mean_rate(self):
-        span = self.span[~self._missing]
-        return float(np.sum(self.mass[~self._missing]) / np.sum(span))
+    def mean_rate(self) -> float:
+        known = ~self.missing
+        return float(self.mass[known].sum() / self.span[known].sum())
 
     def get_cumulative_mass(self, x):
-        x = np.array(x)
-        if np.any(x < 0) or np.any(x > self.sequence_length):
+        """Mass of ``[0, x)``, linear inside an interval."""
+        q = np.asarray(x, dtype=np.float64)
+        if ((q < 0) | (q > self.sequence_length)).any():
             raise ValueError(f"Cannot have positions < 0 or > {self.sequence_length}")
-        return np.interp(x, self._position, self._cumulative_mass)
+        return np.interp(q, self.position, self._cumulative_mass)
 
     def get_rate(self, x):
-        x = np.array(x)
-        if np.any(x < 0) or np.any(x >= self.sequence_length):
+        """Rate of the interval that contains ``x``."""
+        q = np.asarray(x, dtype=np.float64)
+        if ((q < 0) | (q >= self.sequence_length)).any():
             raise ValueError("Rate only defined for 0 <= x < sequence_length")
-        return self._rate[np.searchsorted(self._position, x, side="right") - 1]
+        return self.rate[np.searchsorted(self.position, q, side="right") - 1]
 
     def asdict(self):
-        return {"position": self.position, "rate": self.rate}
+        """The two arrays the C call takes (``{"position": ..., "rate": ...}``)."""
+        return {name: self._cols[name] for name in ("position", "rate")}
 
     def copy(self) -> "RateMap":
-        return RateMap(position=self.position.copy(), rate=self.rate.copy())
+        return RateMap(position=np.array(self.position), rate=np.array(self.rate))
 
-    # Mapping protocol over interval midpoints, like the reference
+    # Mapping protocol: keys are the midpoints of the intervals that have data
     def __iter__(self):
-        yield from self.mid[~self._missing]
+        return iter(self.mid[~self.missing])
 
     def __len__(self):
-        return int(self.num_intervals - np.sum(self._missing))
+        return int((~self.missing).sum())
 
     def __getitem__(self, key):
         if isinstance(key, slice):
