@@ -1200,16 +1200,30 @@ MSPB_DEVFN void resolve_site(const TreeSeqView &ts, const KeptView &kept, const 
     const SortedView &sv, const ResolveView &rv, uint64_t i, int *err);
 
 __global__ void __launch_bounds__(128, 12) k4_resolve_kernel(TreeSeqView ts, KeptView kept, ModelView model, CallView call,
-    SortedView sv, ResolveView rv, const uint32_t *__restrict__ multi_list, const Counts3 *p1_total,
+    SortedView sv, ResolveView rv, const uint32_t *__restrict__ multi_list, uint32_t *next, const Counts3 *p1_total,
     const uint32_t *dense, int *err)
 {
     if (*dense != 0u && sv.key.mode == KEY32_POS) {
         return; // the host re-sorts with time in the key and runs this step again
     }
+    // The walks differ a lot in length, so the work list is handed out dynamically: the grid is
+    // as large as the device holds at once, and a warp claims the next 32 sites whenever it is
+    // through with its last (`next` is zeroed with the call's totals).
     const uint32_t n_multi = p1_total->u;
-    for (uint64_t w = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; w < n_multi;
-         w += (uint64_t) gridDim.x * blockDim.x) {
-        resolve_site(ts, kept, model, call, sv, rv, multi_list[w], err);
+    const uint32_t lane = threadIdx.x & 31u;
+    for (;;) {
+        uint32_t first = 0;
+        if (lane == 0) {
+            first = atomicAdd(next, 32u);
+        }
+        first = __shfl_sync(0xffffffffu, first, 0);
+        if (first >= n_multi) {
+            break;
+        }
+        if (first + lane < n_multi) {
+            resolve_site(ts, kept, model, call, sv, rv, multi_list[first + lane], err);
+        }
+        __syncwarp();
     }
 }
 

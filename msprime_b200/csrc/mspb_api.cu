@@ -58,6 +58,7 @@ struct HostTotals {
     uint64_t k1_total; // new mutations (low half) | those inside the slice (high half)
     Counts3 p1; // sites, mutation rows, allele draws
     uint32_t collisions, dense;
+    uint32_t k4_next, k4_pad; // K4's work counter: warps claim 32 sites of the work list at a time
     Bytes4 bytes; // ragged column sizes
     unsigned long long first_bad; // validation: (row << 16 | code index), min wins
     int err;
@@ -1288,7 +1289,7 @@ int run_sorted_stages(mspb_ctx *ctx, const mspb_params_t *p, const TreeSeqView &
         rv.replay_len = p->replay_len - used;
     }
     MSPB_LAUNCH(ctx->log, "k4_resolve",
-        k4_resolve_kernel<<<148 * 16, 128, 0, st>>>(ts, kept, model, call, sv, rv, ctx->multi_list.p, &dt->p1,
+        k4_resolve_kernel<<<148 * 12, 128, 0, st>>>(ts, kept, model, call, sv, rv, ctx->multi_list.p, &dt->k4_next, &dt->p1,
             &dt->dense, &dt->err));
 
     // ---- K5: byte offsets + rows
@@ -1664,6 +1665,7 @@ static int generate_impl(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t 
         }
         call.key_mode = KEY64_POS_TIME;
         CUDA_OK(cudaMemsetAsync(&dt->p1, 0, sizeof(Counts3), st));
+        CUDA_OK(cudaMemsetAsync(&dt->k4_next, 0, sizeof(uint32_t), st));
         CUDA_OK(cudaMemsetAsync(&dt->collisions, 0, sizeof(uint32_t), st));
         TRY(run_sorted_stages(ctx, p, ts, kept, model, call, R, S0, M0, out, false));
         CUDA_OK(cudaMemcpyAsync(ht, dt, sizeof(HostTotals), cudaMemcpyDeviceToHost, st));
@@ -1690,6 +1692,7 @@ static int generate_impl(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t 
             CUDA_OK(cudaMemcpyAsync(sb.vals[0], val_tmp, R * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
         }
         CUDA_OK(cudaMemsetAsync(&dt->p1, 0, sizeof(Counts3), st));
+        CUDA_OK(cudaMemsetAsync(&dt->k4_next, 0, sizeof(uint32_t), st));
         CUDA_OK(cudaMemsetAsync(&dt->collisions, 0, sizeof(uint32_t), st));
         TRY(run_sorted_stages(ctx, p, ts, kept, model, call, R, S0, M0, out, false));
         CUDA_OK(cudaMemcpyAsync(ht, dt, sizeof(HostTotals), cudaMemcpyDeviceToHost, st));
