@@ -4,9 +4,11 @@
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--workload NAME]
 
 One "step" is one overlay of the whole workload.  At N > 1 (torchrun, one rank per
-GPU) the genome is cut into N position slices, edges are replicated, and the only
-collective is an all-reduce of the per-rank counts/times (strong scaling of a fixed
-workload).  Rank 0 prints ONE JSON line:
+GPU) the genome is cut into N position slices and the edges are replicated (strong
+scaling of a fixed workload).  The collectives are NCCL calls on the library's stream:
+two 8-integer all-gathers per overlay (row / allele / byte bases) and, end to end, the
+in-place all-gather that replicates the tables after every rank has uploaded 1 / N of
+them.  Rank 0 prints ONE JSON line:
 
 * ``value``        new mutations per second with the tree sequence resident in HBM
                    (CUDA events on the library's stream, max over ranks);
@@ -20,7 +22,9 @@ workload).  Rank 0 prints ONE JSON line:
 ``--impl reference`` times only the CPU reference (all host cores) and prints the
 same line with ``"impl": "reference"``.
 
-The oracle is used here only as the CPU baseline, never as the measured product path.
+The oracle is used here only as the CPU baseline (and, for the keep=True workload, to prepare
+the existing mutations of the INPUT with the reference itself, identically for both arms), never
+as the measured product path.  Per-kernel times come from a second pass over the same steps.
 """
 from __future__ import annotations
 
