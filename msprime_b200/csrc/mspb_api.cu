@@ -1156,7 +1156,10 @@ int launch_emit(mspb_ctx *ctx)
     // its byte prefix on its own (ChainFree): the table is filled on the second stream, beside
     // K4, from the site rows P1 left.
     ctx->pending.out.chain_free = nullptr;
-    if (!kept_rows && !ctx->pending.out.dry_run && R > 0
+    // (Single calls only: there the table is built beside K4.  A two-phase call learns its allele
+    // base after K4 has finished, so the table's ~30 us would sit on the critical path, which is
+    // more than the chain costs for a slice's tile count.)
+    if (!kept_rows && !ctx->pending.out.dry_run && R > 0 && !ctx->pending.defer
         && (model_kind == MSPB_MODEL_INFINITE_ALLELES || (model_kind == MSPB_MODEL_MATRIX && ctx->pending.fixed_len > 0))) {
         TRY(ctx->chain_free.ensure(1));
         cudaStream_t cs = ctx->copy_stream;
