@@ -16,6 +16,9 @@
  * They could not be checked against a real libgsl on this box: PARITY UNPINNED
  * at the GSL boundary for the mu > 10 branch.  Bit-exactness claims elsewhere
  * in this repository are therefore "reference mutgen.c + this shim".
+ * tests/test_gsl_shim.py holds what can be held without libgsl: MT19937 bit for
+ * bit against numpy's and its published check value, the distributions against
+ * scipy's exact ones.
  */
 #include <math.h>
 #include <stdlib.h>
