@@ -156,3 +156,38 @@ def test_slim_model_parameters():
         msp.SLiMMutationModel(type="m1")
     with pytest.raises(OverflowError):
         msp.SLiMMutationModel(type=1, next_id=2**63)
+
+
+# The argument errors the reference's suite asserts of sim_mutations (tests/test_mutations.py:756-835,
+# TestSimMutations.test_bad_rates / test_bad_models / test_bad_tree_sequence / test_boolean_inputs):
+# each must be raised on the host, before any device is touched (there is none here).
+@pytest.mark.parametrize("kwargs, err", [
+    (dict(rate={}), TypeError), (dict(rate=[]), TypeError), (dict(rate="self"), TypeError),
+    (dict(rate="abc"), ValueError), (dict(rate="xxx"), ValueError),
+    (dict(rate=-1), ValueError), (dict(rate=-1e-6), ValueError), (dict(rate=-1e7), ValueError),
+    (dict(rate=0, model={}), TypeError), (dict(rate=0, model=True), TypeError), (dict(rate=0, model=123), TypeError),
+    (dict(rate=0, model=""), ValueError), (dict(rate=0, model="coffee"), ValueError),
+    (dict(rate=10, discrete_genome=[]), TypeError), (dict(rate=10, keep=[]), TypeError),
+])
+def test_sim_mutations_rejects_what_the_reference_rejects(kwargs, err):
+    ts = light_ts(cases.four_leaf_tree())
+    if kwargs.get("rate") == "self":
+        kwargs = dict(kwargs, rate=ts)
+    with pytest.raises(err):
+        msp.sim_mutations(ts, **kwargs)
+
+
+@pytest.mark.parametrize("bad", [None, {}, "sdrf"])
+def test_sim_mutations_wants_a_tree_sequence(bad):
+    with pytest.raises(ValueError, match="TreeSequence"):
+        msp.sim_mutations(bad)
+
+
+@pytest.mark.parametrize("rate", [0, 1])
+def test_uncalibrated_time_units_both_interfaces(rate):
+    # tests/test_mutations.py:703-713
+    d = cases.four_leaf_tree()
+    d["time_units"] = "uncalibrated"
+    for call in (msp.sim_mutations, msp.mutate):
+        with pytest.raises(ValueError, match="uncalibrated"):
+            call(light_ts(d), rate=rate, random_seed=1)
