@@ -191,3 +191,31 @@ def test_uncalibrated_time_units_both_interfaces(rate):
     for call in (msp.sim_mutations, msp.mutate):
         with pytest.raises(ValueError, match="uncalibrated"):
             call(light_ts(d), rate=rate, random_seed=1)
+
+
+def test_provenance_record_contents():
+    # msprime/provenance.py:52-140; what tests/test_mutations.py:114-171 reads back from the record
+    import json
+
+    from msprime_b200 import provenance
+
+    ts = light_ts(cases.four_leaf_tree())
+    rate_map = msp.RateMap(position=[0, 0.25, 1.0], rate=[1e-3, 0])
+    params = dict(command="sim_mutations", tree_sequence=ts, rate=rate_map, model=msp.HKY(kappa=2.0),
+                  start_time=np.float64(-1), end_time=None, discrete_genome=None, keep=np.bool_(False),
+                  random_seed=np.int64(42))
+    record = json.loads(provenance.json_encode_provenance(provenance.get_provenance_dict(params)))
+    assert record["schema_version"] == "1.0.0"
+    assert record["software"]["name"] == "msprime_b200"
+    assert {"os", "python", "libraries"} <= set(record["environment"])
+    p = record["parameters"]
+    assert p["command"] == "sim_mutations"
+    assert p["tree_sequence"] == {"__constant__": "__current_ts__"}  # the input is referenced, not embedded
+    assert p["random_seed"] == 42 and p["start_time"] == -1 and p["keep"] is False
+    assert p["end_time"] is None and p["discrete_genome"] is None
+    assert p["rate"]["position"] == [0, 0.25, 1.0] and p["rate"]["rate"] == [1e-3, 0]
+    assert p["rate"]["__class__"].endswith("RateMap")
+    assert p["model"]["__class__"].endswith("HKY") and p["model"]["kappa"] == 2.0
+    # the parameters are enough to build the model again
+    again = msp.HKY(**{k: v for k, v in p["model"].items() if k != "__class__"})
+    assert np.array_equal(again.transition_matrix, msp.HKY(kappa=2.0).transition_matrix)
