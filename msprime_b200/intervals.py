@@ -1,14 +1,17 @@
 """``RateMap`` for the mutation path.
 
-The surface the overlay needs from ``msprime/intervals.py`` (:35-97 constructor contract, :292
-``uniform``, :447 ``asdict``, the read-only interval properties and the two point queries):
-keyword-only ``position`` (n + 1 break points, first one 0, strictly increasing) and ``rate``
-(n non-negative values, NaN = missing data).  Slicing, hapmap I/O and ``RecombinationMap`` are
-out of scope.  All derived arrays are computed once, in the constructor, and frozen.
+The in-memory surface of ``msprime/intervals.py:35-430``: keyword-only ``position`` (n + 1 break
+points, first one 0, strictly increasing) and ``rate`` (n non-negative values, NaN = missing
+data); read-only interval columns; point queries (``get_rate``, ``get_cumulative_mass``,
+``find_index``); the Mapping protocol over the midpoints of the known intervals, with interval
+slices (``rate_map[a:b]``, ``slice``); ``uniform``, ``copy``, ``asdict``; the text / HTML table.
+Hapmap file reading and ``RecombinationMap`` are out of scope (recombination-side I/O).  All
+derived arrays are computed once, in the constructor, and frozen.
 """
 from __future__ import annotations
 
 import collections.abc
+import numbers
 
 import numpy as np
 
@@ -21,6 +24,10 @@ def _frozen(values) -> np.ndarray:
 
 def _indexes(mask, shift=0):
     return np.flatnonzero(mask) + shift
+
+
+def _rebuild(position, rate):
+    return RateMap(position=position, rate=rate)
 
 
 class RateMap(collections.abc.Mapping):
@@ -52,6 +59,7 @@ class RateMap(collections.abc.Mapping):
             "mid": _frozen(pos[:-1] + widths / 2),
             "mass": _frozen(r * widths),
             "missing": gaps,
+            "non_missing": ~gaps,
         }
         self._cumulative_mass = _frozen(np.concatenate([[0.0], np.nancumsum(r * widths)]))
 
@@ -69,14 +77,17 @@ class RateMap(collections.abc.Mapping):
     mid = property(lambda self: self._cols["mid"])
     mass = property(lambda self: self._cols["mass"])
     missing = property(lambda self: self._cols["missing"])
+    non_missing = property(lambda self: self._cols["non_missing"])
     num_intervals = property(lambda self: int(self._cols["rate"].size))
+    num_missing_intervals = property(lambda self: int(self._cols["missing"].sum()))
+    num_non_missing_intervals = property(lambda self: int(self._cols["non_missing"].sum()))
     sequence_length = property(lambda self: self._cols["position"][-1])
     total_mass = property(lambda self: self._cumulative_mass[-1])
 
     @property
-    def mean_rate(self) -> float:
-        known = ~self.missing
-        return float(self.mass[known].sum() / self.span[known].sum())
+    def mean_rate(self):
+        """Total mass over the span of the intervals that have data."""
+        return self.total_mass / np.sum(self.span[self.non_missing])
 
     def get_cumulative_mass(self, x):
         """Mass of ``[0, x)``, linear inside an interval."""
@@ -89,8 +100,19 @@ class RateMap(collections.abc.Mapping):
         """Rate of the interval that contains ``x``."""
         q = np.asarray(x, dtype=np.float64)
         if ((q < 0) | (q >= self.sequence_length)).any():
-            raise ValueError("Rate only defined for 0 <= x < sequence_length")
+            raise ValueError("position out of bounds")
         return self.rate[np.searchsorted(self.position, q, side="right") - 1]
+
+    def find_index(self, x) -> int:
+        """Index ``i`` with ``left[i] <= x < right[i]``; KeyError outside ``[0, sequence_length)``."""
+        if not 0 <= x < self.sequence_length:
+            raise KeyError(f"Position {x} out of bounds")
+        return int(np.searchsorted(self.position, x, side="right")) - 1
+
+    def missing_intervals(self):
+        """``(num_missing_intervals, 2)`` array of the ``[left, right)`` without data."""
+        gaps = self.missing
+        return np.column_stack([self.left[gaps], self.right[gaps]])
 
     def asdict(self):
         """The two arrays the C call takes (``{"position": ..., "rate": ...}``)."""
@@ -98,6 +120,36 @@ class RateMap(collections.abc.Mapping):
 
     def copy(self) -> "RateMap":
         return RateMap(position=np.array(self.position), rate=np.array(self.rate))
+
+    def __reduce__(self):  # pickling goes back through the constructor, so the copy is frozen too
+        return _rebuild, (np.array(self.position), np.array(self.rate))
+
+    def slice(self, left=None, right=None, *, trim=False) -> "RateMap":  # noqa: A003
+        """The part of the map inside ``[left, right)``.  With ``trim`` the result is shifted to
+        start at 0 and is ``right - left`` long; otherwise coordinates stay and everything outside
+        the window becomes missing data."""
+        L = self.sequence_length
+        lo = 0 if left is None else left
+        hi = L if right is None else right
+        if not 0 <= lo < hi <= L:
+            raise KeyError(f"Invalid slice: left={lo}, right={hi}")
+        first = self.find_index(lo)
+        last = int(np.searchsorted(self.position, hi, side="left")) - 1  # interval that ends the window
+        breaks = np.concatenate([[lo], self.position[first + 1:last + 1], [hi]]).astype(np.float64)
+        rates = np.array(self.rate[first:last + 1])
+        if trim:
+            return RateMap(position=breaks - lo, rate=rates)
+        if lo != 0:  # flank on the left: widen a missing first interval, else add one
+            if np.isnan(rates[0]):
+                breaks[0] = 0
+            else:
+                breaks, rates = np.concatenate([[0], breaks]), np.concatenate([[np.nan], rates])
+        if hi != L:
+            if np.isnan(rates[-1]):
+                breaks[-1] = L
+            else:
+                breaks, rates = np.concatenate([breaks, [L]]), np.concatenate([rates, [np.nan]])
+        return RateMap(position=breaks, rate=rates)
 
     # Mapping protocol: keys are the midpoints of the intervals that have data
     def __iter__(self):
@@ -108,8 +160,45 @@ class RateMap(collections.abc.Mapping):
 
     def __getitem__(self, key):
         if isinstance(key, slice):
-            raise TypeError("RateMap slicing is out of scope for msprime_b200")
-        return self.get_rate(key)
+            if key.step is not None:
+                raise TypeError("Only interval slicing is supported")
+            return self.slice(key.start, key.stop)
+        if not isinstance(key, numbers.Number):
+            raise KeyError(f"Key {key} not in map")
+        value = self.rate[self.find_index(key)]
+        if np.isnan(value):  # consistent with __iter__: positions without data are not "in" the map
+            raise KeyError(f"Position {key} is within a missing interval")
+        return value
 
     def __repr__(self):
         return f"RateMap(position={self.position!r}, rate={self.rate!r})"
+
+    # display: every interval up to 39 of them, else the first and last ten around an ellipsis row
+    def _display_table(self):
+        def rows(sel):
+            return [[f"{l:.10g}", f"{r:.10g}", f"{m:.10g}", f"{w:.10g}", f"{v:.2g}"] for l, r, m, w, v in zip(
+                self.left[sel], self.right[sel], self.mid[sel], self.span[sel], self.rate[sel])]
+
+        if self.num_intervals < 40:
+            body = rows(slice(None))
+        else:
+            body = rows(slice(0, 10)) + [["⋯"] * 5] + rows(slice(-10, None))
+        return ["left", "right", "mid", "span", "rate"], body
+
+    def __str__(self):
+        titles, body = self._display_table()
+        inner = [max(len(t), *(len(row[j]) for row in body)) + 2 for j, t in enumerate(titles)]
+        rule = "─" * (sum(inner) + len(inner) - 1)
+
+        def line(cells):
+            aligned = [f"{c:<{w}}" if j < 2 else f"{c:>{w}}" for j, (c, w) in enumerate(zip(cells, inner))]
+            return "│" + "│".join(aligned) + "│\n"
+
+        return f"\n┌{rule}┐\n{line(titles)}├{rule}┤\n" + "".join(line(r) for r in body) + f"└{rule}┘\n"
+
+    def _repr_html_(self):
+        titles, body = self._display_table()
+        head = "".join(f"<th>{t}</th>" for t in titles)
+        rows = "".join("<tr>" + "".join(f"<td>{c}</td>" for c in r) + "</tr>" for r in body)
+        return ('<div><table border="1" class="tskit-table"><thead><tr>' + head + "</tr></thead><tbody>" + rows
+                + "</tbody></table></div>")
