@@ -8,6 +8,7 @@
 #include <cstring>
 #include <cmath>
 #include <cfloat>
+#include <new>
 #include <vector>
 
 #include "../../include/msprime_b200.h"
@@ -286,21 +287,24 @@ extern "C" int mspb_ctx_create(int device, mspb_ctx_t **out)
         cudaGetLastError();
         return MSPB_ERR_NO_DEVICE;
     }
-    mspb_ctx *ctx = new mspb_ctx();
+    mspb_ctx *ctx = new (std::nothrow) mspb_ctx();
+    if (ctx == nullptr) {
+        return MSPB_ERR_NO_MEMORY;
+    }
     ctx->device = device;
     if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) {
         delete ctx;
         return MSPB_ERR_CUDA;
     }
+    bool events_ok = true;
     for (auto &e : ctx->ev) {
-        cudaEventCreate(&e);
+        events_ok = events_ok && cudaEventCreate(&e) == cudaSuccess;
     }
-    cudaEventCreateWithFlags(&ctx->ev_k1, cudaEventDisableTiming);
-    cudaEventCreateWithFlags(&ctx->ev_keys, cudaEventDisableTiming);
-    cudaEventCreateWithFlags(&ctx->ev_p1, cudaEventDisableTiming);
-    cudaEventCreateWithFlags(&ctx->ev_cf, cudaEventDisableTiming);
-    cudaEventCreateWithFlags(&ctx->ev_copied, cudaEventDisableTiming);
-    if (cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking) != cudaSuccess) {
+    for (cudaEvent_t *e : { &ctx->ev_k1, &ctx->ev_keys, &ctx->ev_p1, &ctx->ev_cf, &ctx->ev_copied }) {
+        events_ok = events_ok && cudaEventCreateWithFlags(e, cudaEventDisableTiming) == cudaSuccess;
+    }
+    if (!events_ok || cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking) != cudaSuccess) {
+        cudaGetLastError();
         mspb_ctx_destroy(ctx);
         return MSPB_ERR_CUDA;
     }
@@ -324,6 +328,9 @@ extern "C" void mspb_ctx_destroy(mspb_ctx_t *ctx)
     if (ctx->stream != nullptr) {
         cudaStreamSynchronize(ctx->stream);
     }
+    if (ctx->copy_stream != nullptr) {
+        cudaStreamSynchronize(ctx->copy_stream);
+    }
 #define REL(b) ctx->b.release()
     REL(node_time); REL(edge_left); REL(edge_right); REL(ci);
     REL(edge_parent); REL(edge_child); REL(child_start);
@@ -331,7 +338,7 @@ extern "C" void mspb_ctx_destroy(mspb_ctx_t *ctx)
     REL(k_mut_md_off); REL(k_site_anc); REL(k_site_md); REL(k_mut_der); REL(k_mut_md);
     REL(k_mut_site); REL(k_mut_node); REL(k_site_allele); REL(k_mut_allele);
     REL(map_pos); REL(map_rate); REL(map_cum); REL(map_inv); REL(model_root); REL(model_matrix); REL(replay);
-    REL(model_alleles); REL(model_allele_off);
+    REL(model_alleles); REL(model_allele_off); REL(chain_free);
     REL(goff); REL(loff); REL(k1_tiles); REL(xchg); REL(slice_edges); REL(slice_scan_tiles); REL(rec); REL(keys0); REL(keys1); REL(k32_0); REL(k32_1); REL(vals0); REL(vals1);
     REL(tile_hist); REL(rs_scan_tiles); REL(or_and); REL(lb_state);
     REL(site_scan); REL(mut_scan); REL(draw_scan); REL(multi_list); REL(parent); REL(state); REL(site_state);
