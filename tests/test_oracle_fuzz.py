@@ -1,0 +1,99 @@
+"""CPU: the oracle's C restatement (oracle/mutgen_port.c, the checker that travels to the GPU box)
+against the compiled, unmodified reference mutgen (oracle/_ref) on RANDOM inputs: trees, rate maps
+with zero stretches, stochastic matrices with structural zeros and alleles of ragged length, time
+windows, both genome kinds, two layers with keep=True (sometimes under a model that cannot read
+the first layer's alleles), free-running MT19937 as well as replay.
+Bit-exact tables, the same number of draws, or the same error code.  Skipped where the compiled
+reference is absent (it is only built where /root/reference exists)."""
+import numpy as np
+import pytest
+
+import cases
+import golden_util
+
+N_CASES = 150
+
+
+def random_model(rng):
+    kind = rng.integers(0, 5)
+    if kind == 0:
+        return dict(cases.INF_ALLELES, start_allele=int(rng.integers(0, 10**6)))
+    if kind == 1:
+        return dict(cases.SLIM, type=int(rng.integers(0, 5)), next_id=int(rng.integers(0, 1000)))
+    n = int(rng.integers(2, 9))
+    pool = ["A", "C", "G", "T", "", "AA", "x" * 17, "é", "0", "1", "long-allele-name", "b", "\U0001F333"]
+    alleles = [pool[i] for i in rng.permutation(len(pool))[:n]]
+    root = rng.random(n) * (rng.random(n) < 0.8)
+    if root.sum() == 0:
+        root[0] = 1
+    root /= root.sum()
+    matrix = rng.random((n, n)) * (rng.random((n, n)) < 0.7)
+    for i in range(n):
+        if matrix[i].sum() == 0:
+            matrix[i, (i + 1) % n] = 1
+        matrix[i] /= matrix[i].sum()
+    # renormalise until numerically tight (the library checks sums with a relative tolerance)
+    root[-1] = 1 - root[:-1].sum() if root[-1] > 0.1 else root[-1]
+    return {"kind": "matrix", "alleles": alleles, "root_distribution": root.tolist(),
+            "transition_matrix": matrix.tolist()}
+
+
+def random_map(rng, L, scale):
+    k = int(rng.integers(1, 8))
+    inner = np.sort(rng.choice(np.arange(1, int(L)), size=k - 1, replace=False)).astype(float) if k > 1 else []
+    if k > 1 and rng.random() < 0.5:
+        inner = inner + rng.random(k - 1) * 0.5  # break points need not be integers
+    position = np.concatenate([[0.0], inner, [L]])
+    rate = rng.random(k) * scale * (rng.random(k) < 0.75)
+    return position.tolist(), rate.tolist()
+
+
+def run(oracle_mod, which, ts, kw):
+    try:
+        return oracle_mod.sim_mutations(ts, which=which, **kw)
+    except oracle_mod.OracleError as e:
+        return e.status
+
+
+@pytest.mark.parametrize("case", range(N_CASES))
+def test_port_equals_compiled_reference(oracle_mod, case):
+    if not oracle_mod.have("ref"):
+        pytest.skip("compiled reference absent")
+    rng = np.random.default_rng(1000 + case)
+    shape = rng.integers(0, 3)
+    if shape == 0:
+        ts, L = cases.four_leaf_tree(), 10.0
+    elif shape == 1:
+        ts, L = cases.stick_tree(int(rng.integers(2, 8)), 20.0), 20.0
+    else:
+        L = float(rng.choice([2e3, 2e4, 1e5]))
+        ts = cases.smc_ts(int(rng.integers(2, 40)), L, int(rng.integers(1, 5)))
+    height = float(np.max(ts["nodes"]["time"]))
+    branch = float(np.sum((ts["edges"]["right"] - ts["edges"]["left"])
+                          * (ts["nodes"]["time"][ts["edges"]["parent"]] - ts["nodes"]["time"][ts["edges"]["child"]])))
+    target = float(rng.choice([5, 50, 400, 3000]))  # expected mutations per layer
+    layers = []
+    for layer in range(2):
+        position, rate = random_map(rng, L, 2 * target / branch)
+        kw = dict(map_position=position, map_rate=rate, model=random_model(rng) if layer == 0 else None,
+                  discrete_genome=bool(rng.random() < 0.7), keep=bool(layer == 1 or rng.random() < 0.3))
+        if rng.random() < 0.4:
+            a, b = sorted(rng.random(2) * height * 1.2)
+            kw.update(start_time=float(a), end_time=float(b))
+        if rng.random() < 0.25:
+            kw["seed"] = int(rng.integers(1, 2**32))
+        else:
+            kw["stream"] = rng.random(int(40 * target) + 10_000)
+        layers.append(kw)
+    if rng.random() < 0.85:  # else: a foreign model over the first layer's alleles, usually an error (same code)
+        layers[1]["model"] = layers[0]["model"]
+    else:
+        layers[1]["model"] = random_model(rng)
+    for kw in layers:
+        want, got = run(oracle_mod, "ref", ts, kw), run(oracle_mod, "port", ts, kw)
+        if isinstance(want, int) or isinstance(got, int):
+            assert want == got, (want, got)
+            return
+        assert not golden_util.diff_tables(want, got)
+        assert (got["draws"], got["next_allele"]) == (want["draws"], want["next_allele"])
+        ts = cases.with_kept(ts, want)
