@@ -19,7 +19,7 @@ def oracle_mod():
 
     oracle.build(("port",))
     if os.path.isdir("/root/reference/lib"):
-        oracle.build(("ref",))
+        oracle.build(("ref", "tskit"))
     return oracle
 
 

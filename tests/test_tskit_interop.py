@@ -1,21 +1,25 @@
-"""CPU, optional: the file hand-off against the reference's REAL tskit Python package, where one
-is importable.  tskit is not installed in this image; the vendored package builds in half a minute
-from the reference tree (nothing is copied into this repository):
-
-    cp -rL /root/reference/git-submodules/tskit/python /tmp/tskit_build/python   # (one cyclic link is skipped)
-    (cd /tmp/tskit_build/python && python setup.py build_ext --inplace)
-
-The tests pick it up from MSPB_TSKIT_PATH or /tmp/tskit_build/python and are skipped elsewhere."""
+"""CPU, optional: the file hand-off against the reference's REAL tskit Python package, where it can be
+had.  tskit is not installed in this image, but the reference vendors it: `make -C oracle tskit`
+(run by `__graft_entry__.build()` where /root/reference exists) compiles its C extension from the
+sources where they lie into oracle/_ref/tskit_py/, and the pure-Python part is imported from the
+reference tree itself (nothing is copied into this repository).  MSPB_TSKIT_PATH may point at another
+tskit checkout.  Skipped wherever neither is there (the GPU box: the reference tree does not travel)."""
 import os
 import sys
 
 import numpy as np
 import pytest
 
-for _p in (os.environ.get("MSPB_TSKIT_PATH"), "/tmp/tskit_build/python"):
-    if _p and os.path.isdir(os.path.join(_p, "tskit")) and _p not in sys.path:
-        sys.path.append(_p)
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+_EXT = os.path.join(ROOT, "oracle", "_ref", "tskit_py")
+_PKG = "/root/reference/git-submodules/tskit/python"
+sys.dont_write_bytecode = True  # the reference tree is read-only: no __pycache__ attempts in it
+if os.environ.get("MSPB_TSKIT_PATH"):
+    sys.path.append(os.environ["MSPB_TSKIT_PATH"])
+elif os.path.isdir(_EXT) and os.path.isdir(os.path.join(_PKG, "tskit")):
+    sys.path.extend([_EXT, _PKG])
 tskit = pytest.importorskip("tskit")
+sys.dont_write_bytecode = False
 
 import cases  # noqa: E402
 from msprime_b200 import build, tables, trees_io  # noqa: E402
