@@ -5,21 +5,15 @@ sources where they lie into oracle/_ref/tskit_py/, and the pure-Python part is i
 reference tree itself (nothing is copied into this repository).  MSPB_TSKIT_PATH may point at another
 tskit checkout.  Skipped wherever neither is there (the GPU box: the reference tree does not travel)."""
 import os
-import sys
 
 import numpy as np
 import pytest
 
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-_EXT = os.path.join(ROOT, "oracle", "_ref", "tskit_py")
-_PKG = "/root/reference/git-submodules/tskit/python"
-sys.dont_write_bytecode = True  # the reference tree is read-only: no __pycache__ attempts in it
-if os.environ.get("MSPB_TSKIT_PATH"):
-    sys.path.append(os.environ["MSPB_TSKIT_PATH"])
-elif os.path.isdir(_EXT) and os.path.isdir(os.path.join(_PKG, "tskit")):
-    sys.path.extend([_EXT, _PKG])
-tskit = pytest.importorskip("tskit")
-sys.dont_write_bytecode = False
+import tskit_path
+
+tskit = tskit_path.load()
+if tskit is None:
+    pytest.skip("the reference's tskit package is not available here", allow_module_level=True)
 
 import cases  # noqa: E402
 from msprime_b200 import build, tables, trees_io  # noqa: E402
