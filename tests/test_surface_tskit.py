@@ -263,3 +263,35 @@ def test_one_device_call_per_overlay(engine):
     msp.sim_mutations(ts, rate=1e-5, random_seed=1)
     msp.sim_mutations(ts, rate=1e-5, random_seed=2)
     assert engine.calls == 2
+
+
+def test_command_line_on_tskit_files(tmp_path):
+    """tests/test_cli.py:1522-1628 (msp mutations output): a file written by tskit goes through our
+    reader, the overlay and our writer; tskit loads the result; keep=True and a discrete genome are
+    what the command line means; the time window and the model option are honoured."""
+    from msprime_b200 import cli
+
+    first = msp.sim_mutations(base_ts(), rate=1e-5, random_seed=2)
+    src, dst = tmp_path / "in.trees", tmp_path / "out.trees"
+    first.dump(str(src))
+    cli.main(["mutations", "1e-5", str(src), "-o", str(dst), "-s", "3"])
+    out = tskit.load(str(dst))
+    assert out.num_mutations > first.num_mutations  # the existing ones are kept
+    assert set(first.tables.sites.position) <= set(out.tables.sites.position)
+    assert_rest_untouched(first, out)
+    p = last_record(out)["parameters"]
+    assert p["keep"] is True and p["discrete_genome"] is True and p["random_seed"] == 3 and p["model"] == "jc69"
+    assert np.all(np.floor(out.tables.sites.position) == out.tables.sites.position)
+    assert {m.derived_state for m in out.mutations()} <= set("ACGT")
+
+    bare = tmp_path / "bare.trees"
+    base_ts().dump(str(bare))
+    cli.main(["mutations", "1e-4", str(bare), "-o", str(dst), "-s", "4", "--start-time", "0", "--end-time", "200",
+              "-m", "binary"])
+    out = tskit.load(str(dst))
+    t = out.tables.mutations.time
+    assert len(t) > 0 and (t >= 0).all() and (t < 200).all()
+    assert {m.derived_state for m in out.mutations()} <= {"0", "1"}
+    # the same seed through the in-memory call gives the same tables
+    again = msp.sim_mutations(base_ts(), rate=1e-4, random_seed=4, start_time=0, end_time=200, model="binary")
+    assert again.tables.sites == out.tables.sites and again.tables.mutations == out.tables.mutations
