@@ -3,7 +3,8 @@
 possible under the matrix, one-way / flip-flop / silent / circular models, integer sites, windows.
 These are invariants of any correct stream, so the same bodies run twice through the public
 `sim_mutations`: on the CPU with the device call answered by the oracle stand-in
-(tests/oracle_engine.py; `-m "not gpu"`), and on the B200 with the native Philox stream (`-m gpu`)."""
+(tests/oracle_engine.py; `-m "not gpu"`), and on the B200 with the native Philox stream (`-m gpu`).
+The second half does the same for keep=True over hand-made existing tables (the reference's TestKeep)."""
 import numpy as np
 import pytest
 
@@ -14,8 +15,7 @@ from msprime_b200 import mutations, tables as mtables
 NUC = ["A", "C", "G", "T"]
 
 
-@pytest.fixture(params=["oracle", pytest.param("device", marks=pytest.mark.gpu)])
-def engine(request, monkeypatch):
+def _engine(request, monkeypatch):
     if request.param == "oracle":
         import oracle_engine
 
@@ -25,6 +25,11 @@ def engine(request, monkeypatch):
         request.getfixturevalue("native_built")
     monkeypatch.setattr(mutations, "_tables", mtables)
     return request.param
+
+
+@pytest.fixture(params=["oracle", pytest.param("device", marks=pytest.mark.gpu)])
+def engine(request, monkeypatch):
+    return _engine(request, monkeypatch)
 
 
 def small_ts(seed=1, samples=10, L=10.0):
@@ -220,3 +225,266 @@ def test_coalescent_trees_windows(engine):
         assert len(time) > 0 and (time >= lo).all() and (time < hi).all()
         verify_mutations(d, out, True)
     assert overlay(d, "jc69", 1.0, True, start_time=-10.0, end_time=-1.0).num_mutations == 0
+
+
+# ---------------------------------------------------------------------------------------------
+# keep=True over inputs that did not come out of an overlay (TestKeep, tests/test_mutations.py:1231-1520):
+# hand-placed mutations on every branch, unique metadata on the existing rows, multi-character alleles,
+# a site without mutations, rows whose parent column has to be worked out again.
+# On the device these inputs have not run yet (this file was written with no GPU time left in round 1):
+# until they have, a device failure here is reported as xfail rather than stopping the suite.
+pending_on_device = pytest.mark.xfail(reason="first device run pending (written after the round's GPU time was spent)",
+                                      strict=False)
+
+
+@pytest.fixture(params=["oracle", pytest.param("device", marks=[pytest.mark.gpu, pending_on_device])])
+def keep_engine(request, monkeypatch):
+    return _engine(request, monkeypatch)
+
+
+def pack(strings):
+    data, off = mtables.encode_ragged(strings)
+    return data.view(np.int8), off
+
+
+def with_existing(d, sites, muts):
+    """`d` with hand-made site / mutation tables: sites = [(position, ancestral_state, metadata)],
+    muts = [dict(site, node, derived, time, parent, metadata)], already in table order."""
+    out = dict(d)
+    anc, anc_off = pack([s[1] for s in sites])
+    smd, smd_off = pack([s[2] for s in sites])
+    out["sites"] = {"position": np.array([s[0] for s in sites], dtype=np.float64), "ancestral_state": anc,
+                    "ancestral_state_offset": anc_off, "metadata": smd, "metadata_offset": smd_off}
+    der, der_off = pack([m["derived"] for m in muts])
+    mmd, mmd_off = pack([m["metadata"] for m in muts])
+    out["mutations"] = {
+        "site": np.array([m["site"] for m in muts], dtype=np.int32),
+        "node": np.array([m["node"] for m in muts], dtype=np.int32),
+        "parent": np.array([m["parent"] for m in muts], dtype=np.int32),
+        "time": np.array([m["time"] for m in muts], dtype=np.float64),
+        "derived_state": der, "derived_state_offset": der_off, "metadata": mmd, "metadata_offset": mmd_off}
+    return out
+
+
+def tag(k):
+    return int(k).to_bytes(4, "little")
+
+
+def branch_mutations(d, oldest_first=False):
+    """tsutil.insert_branch_mutations (tests/tsutil.py:52-84): one site per tree at its left end, a
+    mutation above every non-root node flipping 0 <-> 1 along each lineage, parents before children;
+    times at the middle of the branch; unique metadata on every row.  ``oldest_first`` lists each
+    site's rows by decreasing time, the order an overlay writes (needed where new rows are merged
+    into the site: the reference orders existing rows by id and new ones by time)."""
+    lefts = np.unique(d["edges"]["left"])
+    node_time = d["nodes"]["time"]
+    sites, muts = [], []
+    for j, x in enumerate(lefts):
+        parent = parent_array(d, x)
+        sites.append((float(x), "0", b"site%d" % j))
+        children = {}
+        for c in np.flatnonzero(parent >= 0):
+            children.setdefault(int(parent[c]), []).append(int(c))
+        roots = [u for u in children if parent[u] == -1]
+        for root in roots:
+            state, above, stack = {root: 0}, {root: -1}, [root]
+            while stack:
+                u = stack.pop()
+                stack.extend(children.get(u, []))
+                v = parent[u]
+                if v != -1:
+                    state[u] = (state[v] + 1) % 2
+                    above[u] = len(muts)
+                    muts.append(dict(site=j, node=u, derived=str(state[u]), parent=above[v],
+                                     time=(node_time[u] + node_time[v]) / 2, metadata=tag(len(muts))))
+    if oldest_first:
+        order = sorted(range(len(muts)), key=lambda k: (muts[k]["site"], -muts[k]["time"]))
+        new_id = {old: new for new, old in enumerate(order)}
+        muts = [dict(muts[k], parent=new_id.get(muts[k]["parent"], -1)) for k in order]
+    return with_existing(d, sites, muts)
+
+
+def table_rows(ts_or_dict):
+    ts = ts_or_dict if hasattr(ts_or_dict, "tables") else mtables.TableCollection.fromdict(ts_or_dict).tree_sequence()
+    t = ts.tables
+    pos, anc, site, node, par, time, der = rows(ts)
+    md = [bytes(x) for x in table_bytes(t.mutations.metadata, t.mutations.metadata_offset)]
+    smd = [bytes(x) for x in table_bytes(t.sites.metadata, t.sites.metadata_offset)]
+    return dict(pos=pos, anc=anc, site=site, node=node, par=par, time=time, der=der, md=md, smd=smd)
+
+
+def table_bytes(data, offset):
+    raw = np.asarray(data).astype(np.int8).view(np.uint8).tobytes()
+    off = np.asarray(offset).astype(np.int64)
+    return [raw[off[i]:off[i + 1]] for i in range(len(off) - 1)]
+
+
+def verify_sites(original, updated, discrete):
+    """TestKeep.verify_sites (tests/test_mutations.py:1258-1298): every existing site and row is still
+    there with its node, state and metadata, and the parent of an existing row, followed up through
+    any new rows in between, is the existing row it had before."""
+    o, u = table_rows(original), table_rows(updated)
+    old_site = {p: j for j, p in enumerate(o["pos"])}
+    old_row = {m: k for k, m in enumerate(o["md"])}
+    assert len(old_row) == len(o["md"])  # the metadata identifies the rows
+    found = 0
+    for j, p in enumerate(u["pos"]):
+        if p not in old_site:
+            continue
+        found += 1
+        oj = old_site[p]
+        assert u["anc"][j] == o["anc"][oj] and u["smd"][j] == o["smd"][oj]
+        mine = np.flatnonzero(u["site"] == j)
+        if not discrete:
+            assert len(mine) == int(np.sum(o["site"] == oj))
+        for k in mine:
+            if u["md"][k] not in old_row:
+                continue
+            ok = old_row[u["md"][k]]
+            assert o["site"][ok] == oj and u["node"][k] == o["node"][ok] and u["der"][k] == o["der"][ok]
+            assert u["time"][k] == o["time"][ok]
+            q = u["par"][k]
+            while q != -1 and u["md"][q] not in old_row:
+                q = u["par"][q]
+            assert (o["par"][ok] == -1) if q == -1 else (old_row[u["md"][q]] == o["par"][ok])
+    assert found == len(o["pos"])
+    kept = [m for m in u["md"] if m in old_row]
+    assert sorted(kept) == sorted(o["md"])
+
+
+def check_keep(d_existing, rate, seed):
+    """TestKeep.verify (:1237-1256): on a continuous genome keep=True gives exactly the existing rows
+    plus what keep=False would have drawn."""
+    ts = mtables.TableCollection.fromdict(d_existing).tree_sequence()
+    fresh = msp.sim_mutations(ts, rate=rate, random_seed=seed, discrete_genome=False, keep=False)
+    both = msp.sim_mutations(ts, rate=rate, random_seed=seed, discrete_genome=False, keep=True)
+    assert fresh.num_sites > 0
+    assert ts.num_sites + fresh.num_sites == both.num_sites
+    assert ts.num_mutations + fresh.num_mutations == both.num_mutations
+    old, new, union = (set(rows(x)[0].tolist()) for x in (ts, fresh, both))
+    assert old | new == union
+    verify_sites(ts, both, discrete=False)
+    return both
+
+
+def test_keep_adds_to_a_first_layer(keep_engine):
+    d = small_ts(seed=2)
+    first = overlay(d, "binary", 1.0, False, seed=11)
+    r = table_rows(first)
+    existing = with_existing(
+        d, [(p, a, b"") for p, a in zip(r["pos"], r["anc"])],
+        [dict(site=int(s), node=int(n), derived=x, time=float(t), parent=int(p), metadata=tag(k))
+         for k, (s, n, x, t, p) in enumerate(zip(r["site"], r["node"], r["der"], r["time"], r["par"]))])
+    assert len(r["pos"]) > 5
+    check_keep(existing, 1.0, 2)
+
+
+def test_keep_over_a_mutation_on_every_branch(keep_engine):
+    d = small_ts(seed=2, samples=5)
+    existing = branch_mutations(d)
+    assert len(existing["sites"]["position"]) > 1
+    both = check_keep(existing, 3.0, 7)
+    assert both.num_sites > len(existing["sites"]["position"])
+    # with no new mutations at all the tables come back exactly, parents included
+    ts = mtables.TableCollection.fromdict(existing).tree_sequence()
+    same = msp.sim_mutations(ts, rate=0, random_seed=1, keep=True, discrete_genome=False)
+    a, b = table_rows(ts), table_rows(same)
+    for key in a:
+        assert np.array_equal(np.asarray(a[key]), np.asarray(b[key])), key
+
+
+def test_keep_parents_are_worked_out_again_on_a_discrete_genome(keep_engine):
+    # new mutations land ON the existing sites (integer positions 0 .. 9), above and below existing rows
+    d = small_ts(seed=3, samples=6)
+    existing = branch_mutations(d, oldest_first=True)
+    ts = mtables.TableCollection.fromdict(existing).tree_sequence()
+    model = matrix_model(["0", "1"], [[0, 1], [1, 0]], [1, 0])
+    both = msp.sim_mutations(ts, rate=1.0, random_seed=5, keep=True, discrete_genome=True, model=model)
+    assert both.num_mutations > ts.num_mutations
+    verify_sites(ts, both, discrete=True)
+    u = table_rows(both)
+    new_on_old = [k for k in range(len(u["md"])) if u["md"][k] == b"" and u["pos"][u["site"][k]] in
+                  set(existing["sites"]["position"].tolist())]
+    assert len(new_on_old) > 0
+    # every row's state differs from the state it inherits (flip model), new and existing alike at new rows
+    for k in new_on_old:
+        inherited = u["anc"][u["site"][k]] if u["par"][k] == -1 else u["der"][u["par"][k]]
+        assert u["der"][k] != inherited
+
+
+def test_keep_multichar_alleles_under_a_nucleotide_layer(keep_engine):
+    # tests/test_mutations.py:1356-1374: existing alleles the model does not know are fine as long as
+    # no new mutation has to read them (continuous genome: new sites only)
+    d = small_ts(seed=3, samples=12)
+    first = table_rows(overlay(d, "binary", 1.0, False, seed=1))
+    assert len(first["pos"]) > 2
+    existing = with_existing(
+        d, [(p, "A" * j, b"") for j, p in enumerate(first["pos"])],
+        [dict(site=int(s), node=int(n), derived="T" * int(s), time=float(t), parent=int(p), metadata=tag(k))
+         for k, (s, n, t, p) in enumerate(zip(first["site"], first["node"], first["time"], first["par"]))])
+    ts = mtables.TableCollection.fromdict(existing).tree_sequence()
+    both = msp.sim_mutations(ts, rate=1.0, random_seed=1, keep=True, discrete_genome=False)
+    verify_sites(ts, both, discrete=False)
+    assert both.num_sites > ts.num_sites
+
+
+def test_keep_a_site_without_mutations(keep_engine):
+    # tests/test_mutations.py:1335-1338 (tsutil.insert_site): the empty site stays
+    d = small_ts(seed=3, samples=12)
+    existing = with_existing(d, [(0.5, "XY", b"meta")], [])
+    ts = mtables.TableCollection.fromdict(existing).tree_sequence()
+    both = msp.sim_mutations(ts, rate=3.0, random_seed=7, keep=True, discrete_genome=False)
+    u = table_rows(both)
+    j = int(np.flatnonzero(u["pos"] == 0.5)[0])
+    assert u["anc"][j] == "XY" and u["smd"][j] == b"meta" and not np.any(u["site"] == j)
+    assert both.num_sites > 1 and both.num_mutations == both.num_sites - 1
+    gone = msp.sim_mutations(ts, rate=3.0, random_seed=7, keep=False, discrete_genome=False)
+    assert 0.5 not in rows(gone)[0]
+
+
+def test_same_seed_twice_does_not_repeat_sites(keep_engine):
+    # tests/test_mutations.py:1340-1354: the second layer redraws positions that are taken
+    d = small_ts(seed=3, samples=12)
+    first = overlay(d, "jc69", 1.0, False, seed=1)
+    second = msp.sim_mutations(first, rate=1.0, random_seed=1, keep=True, discrete_genome=False)
+    pos = rows(second)[0]
+    assert len(set(pos.tolist())) == len(pos) and set(rows(first)[0].tolist()) < set(pos.tolist())
+
+
+def test_layers_in_overlapping_windows(keep_engine):
+    # tests/test_mutations.py:1434-1454
+    d = small_ts(seed=3, samples=12)
+    one = overlay(d, "jc69", 1.0, True, seed=1, start_time=1.0, end_time=2.0)
+    two = msp.sim_mutations(one, rate=1.0, random_seed=3, discrete_genome=True, start_time=0.0, end_time=1.5)
+    assert two.num_mutations > one.num_mutations > 0
+    verify_mutations(d, two, True)
+
+
+def test_layering_a_model_with_other_alleles(keep_engine):
+    # tests/test_mutations.py:1478-1520: a second model that turns everything into one of two identical
+    # multi-byte alleles, over binary rows; new rows at old sites must read the old states
+    d = small_ts(seed=3, samples=5, L=100.0)
+    tree = "\U0001F384"
+    model = msp.MatrixMutationModel(["0", "1", tree, tree], [0, 0, 0.5, 0.5],
+                                    [[0, 0, 1, 0], [0, 0, 0, 1], [0, 0, 0.5, 0.5], [0, 0, 0.5, 0.5]])
+    r = table_rows(overlay(d, "binary", 0.05, True, seed=1))
+    assert set(r["anc"]) | set(r["der"]) <= {"0", "1"} and len(r["pos"]) > 3
+    existing = with_existing(
+        d, [(p, a, b"") for p, a in zip(r["pos"], r["anc"])],
+        [dict(site=int(s), node=int(n), derived=x, time=float(t), parent=int(p), metadata=tag(k))
+         for k, (s, n, x, t, p) in enumerate(zip(r["site"], r["node"], r["der"], r["time"], r["par"]))])
+    ts = mtables.TableCollection.fromdict(existing).tree_sequence()
+    both = msp.sim_mutations(ts, rate=0.2, random_seed=2, keep=True, model=model)
+    verify_sites(ts, both, discrete=True)
+    u = table_rows(both)
+    old_positions = set(r["pos"].tolist())
+    assert old_positions < set(u["pos"].tolist())
+    new_at_old = 0
+    for k in range(len(u["md"])):
+        at_old = u["pos"][u["site"][k]] in old_positions
+        if not at_old:
+            assert u["anc"][u["site"][k]] == tree and u["der"][k] == tree
+        elif u["md"][k] == b"":
+            assert u["der"][k] == tree
+            new_at_old += 1
+    assert new_at_old > 0
