@@ -97,3 +97,30 @@ def test_port_equals_compiled_reference(oracle_mod, case):
         assert not golden_util.diff_tables(want, got)
         assert (got["draws"], got["next_allele"]) == (want["draws"], want["next_allele"])
         ts = cases.with_kept(ts, want)
+
+
+@pytest.mark.parametrize("case", range(40))
+def test_port_equals_reference_over_hand_made_existing_tables(oracle_mod, case):
+    """keep=True over existing rows that no overlay wrote: a mutation on every branch of every tree
+    (rows in tree order, which is NOT time order, or oldest first), unique metadata, and new mutations
+    landing on the same integer positions.  New rows are merged into a site of existing rows only
+    where those are oldest first: otherwise the reference's comparator (existing rows by id, the rest
+    by time, lib/mutgen.c:36-49) is not a total order and its own assertion `mut->time <=
+    parent_mut->time` (lib/mutgen.c:1200) fires; rows in tree order get a continuous genome."""
+    if not oracle_mod.have("ref"):
+        pytest.skip("compiled reference absent")
+    import test_surface_semantics as sem
+
+    rng = np.random.default_rng(5000 + case)
+    d = sem.small_ts(seed=int(rng.integers(1, 6)), samples=int(rng.integers(2, 9)), L=float(rng.choice([5, 10, 30])))
+    oldest_first = bool(case % 2)
+    existing = sem.branch_mutations(d, oldest_first=oldest_first)
+    model = cases.BINARY if rng.random() < 0.7 else cases.JC69  # JC69 cannot read "0" / "1": same error on both sides
+    kw = dict(map_position=[0, d["sequence_length"]], map_rate=[float(rng.choice([0.0, 0.2, 1.0, 4.0]))], model=model,
+              discrete_genome=oldest_first and bool(rng.random() < 0.8), keep=True, stream=rng.random(200_000))
+    want, got = run(oracle_mod, "ref", existing, kw), run(oracle_mod, "port", existing, kw)
+    if isinstance(want, int) or isinstance(got, int):
+        assert want == got, (want, got)
+        return
+    assert not golden_util.diff_tables(want, got)
+    assert got["draws"] == want["draws"]
