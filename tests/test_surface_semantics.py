@@ -488,3 +488,42 @@ def test_layering_a_model_with_other_alleles(keep_engine):
             assert u["der"][k] == tree
             new_at_old += 1
     assert new_at_old > 0
+
+
+# ---------------------------------------------------------------------------------------------
+# The same hand-made existing tables through the replay harness, bit for bit against the oracle (the
+# inputs of tests/test_oracle_fuzz.py::test_port_equals_reference_over_hand_made_existing_tables, where
+# the oracle's restatement is held to the compiled reference).  Device runs pending, as above.
+@pytest.mark.gpu
+@pending_on_device
+@pytest.mark.parametrize("case", range(12))
+def test_replay_parity_over_hand_made_existing_tables(native_built, oracle_mod, case):
+    import test_gpu_replay as replay
+    from msprime_b200 import _native
+
+    rng = np.random.default_rng(7000 + case)
+    d = small_ts(seed=int(rng.integers(1, 6)), samples=int(rng.integers(2, 9)), L=float(rng.choice([5, 10, 30])))
+    oldest_first = bool(case % 2)
+    existing = branch_mutations(d, oldest_first=oldest_first)
+    if case in (4, 5):  # plus a site without mutations, between the others
+        x = float(np.setdiff1d(np.arange(d["sequence_length"]) + 0.5, existing["sites"]["position"])[0])
+        t = table_rows(existing)
+        j = int(np.searchsorted(t["pos"], x))
+        sites = [(p, a, m) for p, a, m in zip(t["pos"], t["anc"], t["smd"])]
+        sites.insert(j, (x, "empty", b"no mutations here"))
+        muts = [dict(site=int(s) + (1 if s >= j else 0), node=int(n), derived=x_, time=float(tm), parent=int(p),
+                     metadata=m) for s, n, x_, tm, p, m in zip(t["site"], t["node"], t["der"], t["time"], t["par"],
+                                                               t["md"])]
+        existing = with_existing(d, sites, muts)
+    model = cases.BINARY if case % 3 else cases.JC69_SI  # JC69 cannot read "0" / "1": an error, the same one
+    with _native.Context(0) as ctx:
+        kw = dict(model=model, map_position=[0, d["sequence_length"]], map_rate=[float(rng.choice([0.0, 0.2, 1.0, 4.0]))],
+                  discrete=oldest_first and case % 4 != 3, keep=True, seed=case + 1)
+        try:
+            replay.check_case(ctx, oracle_mod, existing, **kw)
+        except oracle_mod.OracleError as e:
+            with pytest.raises(_native.LibraryError) as got:
+                replay.gpu_run(ctx, existing, model=model, stream=np.random.default_rng(case + 1).random(200_000),
+                               map_position=kw["map_position"], map_rate=kw["map_rate"], discrete=kw["discrete"],
+                               keep=True)
+            assert got.value.status == e.status
