@@ -14,6 +14,12 @@ from msprime_b200 import mutations, tables as mtables
 
 NUC = ["A", "C", "G", "T"]
 
+# None of the device runs in this file has happened yet: the file was written after round 1's GPU time was
+# spent.  The bodies are verified on the CPU (oracle stand-in); until the first device run a device failure is
+# reported as xfail instead of stopping the suite, a pass as XPASS (then the marker goes).
+pending_on_device = pytest.mark.xfail(reason="first device run pending (written after the round's GPU time was spent)",
+                                      strict=False)
+
 
 def _engine(request, monkeypatch):
     if request.param == "oracle":
@@ -27,7 +33,7 @@ def _engine(request, monkeypatch):
     return request.param
 
 
-@pytest.fixture(params=["oracle", pytest.param("device", marks=pytest.mark.gpu)])
+@pytest.fixture(params=["oracle", pytest.param("device", marks=[pytest.mark.gpu, pending_on_device])])
 def engine(request, monkeypatch):
     return _engine(request, monkeypatch)
 
@@ -231,10 +237,7 @@ def test_coalescent_trees_windows(engine):
 # keep=True over inputs that did not come out of an overlay (TestKeep, tests/test_mutations.py:1231-1520):
 # hand-placed mutations on every branch, unique metadata on the existing rows, multi-character alleles,
 # a site without mutations, rows whose parent column has to be worked out again.
-# On the device these inputs have not run yet (this file was written with no GPU time left in round 1):
-# until they have, a device failure here is reported as xfail rather than stopping the suite.
-pending_on_device = pytest.mark.xfail(reason="first device run pending (written after the round's GPU time was spent)",
-                                      strict=False)
+# (The parity tests on the device layer only over overlay output so far, so these are new ground there.)
 
 
 @pytest.fixture(params=["oracle", pytest.param("device", marks=[pytest.mark.gpu, pending_on_device])])
