@@ -234,6 +234,9 @@ extern "C" const char *mspb_strerror(int err)
         default:
             break;
     }
+    if (err == TSK_E(-200)) {
+        return "Bad offset provided in input array. (TSK_ERR_BAD_OFFSET)";
+    }
     if (err < 0 && !(err & (1 << 13))) {
         return "tskit table integrity error (code = err ^ 8192)";
     }
@@ -629,10 +632,42 @@ int tables_prepare(mspb_ctx_t *ctx, const mspb_tables_t *t)
     return 0;
 }
 
+// A ragged column's offsets must start at 0 and never decrease (tskit's check_offsets, tables.c:
+// TSK_ERR_BAD_OFFSET, applied by tsk_*_table_set_columns before the reference's mutgen ever sees a table):
+// the kernels take lengths as differences of neighbours and would read past the column otherwise.
+bool offsets_ok(const uint64_t *off, uint64_t rows)
+{
+    if (off == nullptr) {
+        return true; // absent metadata column: all rows empty
+    }
+    uint64_t bad = off[0] != 0 ? 1 : 0;
+    for (uint64_t j = 0; j < rows; j++) {
+        bad |= off[j + 1] < off[j] ? 1 : 0;
+    }
+    return bad == 0;
+}
+
 // existing sites and mutations (read by keep=True calls), on stream cs
 int tables_upload_kept(mspb_ctx_t *ctx, const mspb_tables_t *t, cudaStream_t cs)
 {
     static const uint64_t zero_off[1] = { 0 };
+    if (ctx->S0 > 0
+        && (t->site_position == nullptr || t->site_ancestral_state_offset == nullptr
+            || (t->site_ancestral_state == nullptr && t->site_ancestral_state_offset[ctx->S0] != 0))) {
+        return MSPB_ERR_BAD_PARAM_VALUE;
+    }
+    if (ctx->M0 > 0
+        && (t->mutation_site == nullptr || t->mutation_node == nullptr || t->mutation_derived_state_offset == nullptr
+            || (t->mutation_derived_state == nullptr && t->mutation_derived_state_offset[ctx->M0] != 0))) {
+        return MSPB_ERR_BAD_PARAM_VALUE;
+    }
+    if ((ctx->S0 > 0
+            && !(offsets_ok(t->site_ancestral_state_offset, ctx->S0) && offsets_ok(t->site_metadata_offset, ctx->S0)))
+        || (ctx->M0 > 0
+            && !(offsets_ok(t->mutation_derived_state_offset, ctx->M0)
+                && offsets_ok(t->mutation_metadata_offset, ctx->M0)))) {
+        return TSK_E(-200); // TSK_ERR_BAD_OFFSET
+    }
     if (ctx->S0 > 0) {
         const uint64_t *ao = t->site_ancestral_state_offset, *mo = t->site_metadata_offset;
         TRY(upload(ctx->k_site_pos, t->site_position, ctx->S0, cs));

@@ -141,7 +141,8 @@ class Store:
         it = _Item()
         for j in range(len(self)):
             _check(lib().mspb_store_item(self._h, j, C.byref(it)), "item")
-            yield C.string_at(it.key, it.key_len).decode(), self._view(it)
+            # keys are bytes to kastore; one that is not UTF-8 is simply not a key the schema knows
+            yield C.string_at(it.key, it.key_len).decode("utf8", "surrogateescape"), self._view(it)
 
     def get(self, key):
         it = _Item()
@@ -158,12 +159,77 @@ class Store:
         _check(lib().mspb_store_tables(self._h, C.byref(t), C.byref(tu), C.byref(tu_len)),
                f"Cannot load '{self.path}'")
         t._store = self
-        units = C.string_at(tu, tu_len.value).decode() if tu.value else "unknown"
+        units = _text(np.frombuffer(C.string_at(tu, tu_len.value), dtype=np.uint8)) if tu.value else "unknown"
         return t, units
 
 
 def _text(a) -> str:
-    return bytes(np.asarray(a).view(np.uint8)).decode("utf8")
+    """A text item (time units, schemas, uuid).  The C layers do not look inside; tskit's Python layer
+    fails on bytes that are not UTF-8 when the value is read, here that is at load time."""
+    try:
+        return bytes(np.asarray(a).view(np.uint8)).decode("utf8")
+    except UnicodeDecodeError as e:
+        raise FileFormatError(f"A text item of the file is not valid UTF-8 ({e})", -100 ^ (1 << 13)) from None
+
+
+def _fail(path, code, what):
+    _check(code ^ (1 << 13), f"Cannot load '{os.fspath(path)}' ({what})")
+
+
+_OPTIONAL_COLUMNS = {("individuals", "parents"), ("edges", "metadata"), ("migrations", "metadata"), ("mutations", "time")}
+
+
+def _check_columns(d, path):
+    """The column rules of ``read_table_cols`` / ``read_table_ragged_cols`` and ``check_offsets``
+    (tables.c:100-262) for EVERY table, as ``tsk_table_collection_load`` applies them (the C entry point
+    looks only at what the overlay reads): required columns present (-103), data and offset columns
+    together (-104), element types (-105), equal row counts (-100), offsets starting at 0, never
+    decreasing and ending at the data length (-200)."""
+    if "file_uuid" not in d:  # tables.c: "uuid" is a required item, 36 characters
+        _fail(path, -103, "uuid")
+    if len(d["file_uuid"]) != 36:
+        _fail(path, -100, "uuid")
+    idx = d.get("indexes") or {}
+    ins, rem = idx.get("edge_insertion_order"), idx.get("edge_removal_order")
+    if (ins is None) != (rem is None):  # tables.c:11751-11770: the two index columns come together
+        _fail(path, -104, "indexes")
+    if ins is not None:
+        if ins.dtype != np.int32 or rem.dtype != np.int32:
+            _fail(path, -105, "indexes")
+        if not len(ins) == len(rem) == len(d.get("edges", {}).get("left", ())):
+            _fail(path, -100, "indexes")
+    for tbl, (fixed, ragged) in _SCHEMA.items():
+        cols = d.get(tbl)
+        if not isinstance(cols, dict):
+            _fail(path, -103, tbl)
+        rows = None
+        for name, kas, _ in fixed:
+            a = cols.get(name)
+            if a is None:
+                if (tbl, name) in _OPTIONAL_COLUMNS:
+                    continue
+                _fail(path, -103, f"{tbl}/{name}")
+            if _KAS_OF.get(np.asarray(a).dtype) != kas:
+                _fail(path, -105, f"{tbl}/{name}")
+            if rows is not None and len(a) != rows:
+                _fail(path, -100, f"{tbl}/{name}")
+            rows = len(a)
+        for name, kas in ragged:
+            data, off = cols.get(name), cols.get(name + "_offset")
+            if data is None and off is None:
+                if (tbl, name) in _OPTIONAL_COLUMNS:
+                    continue
+                _fail(path, -103, f"{tbl}/{name}")
+            if data is None or off is None:
+                _fail(path, -104, f"{tbl}/{name}")
+            data, off = np.asarray(data), np.asarray(off)
+            if _KAS_OF.get(data.dtype) != kas or off.dtype not in (np.uint32, np.uint64):
+                _fail(path, -105, f"{tbl}/{name}")
+            if len(off) == 0 or (rows is not None and len(off) != rows + 1):
+                _fail(path, -100, f"{tbl}/{name}_offset")
+            rows = len(off) - 1
+            if off[0] != 0 or int(off[-1]) != len(data) or np.any(off[1:] < off[:-1]):
+                _fail(path, -200, f"{tbl}/{name}_offset")
 
 
 def load_tables_dict(path):
@@ -177,24 +243,31 @@ def load_tables_dict(path):
             if tbl == "format":
                 continue
             if col == "metadata_schema" or (tbl == "reference_sequence" and col in ("data", "url")):
+                if tbl in _SCHEMA and _KAS_OF.get(arr.dtype) != U8:  # a table's schema is a uint8 column to tskit
+                    _fail(path, -105, key)
                 arr = _text(arr)
             elif tbl == "reference_sequence" and col == "metadata":
                 arr = bytes(arr.view(np.uint8))
             d.setdefault(tbl, {})[col] = arr
         elif key == "sequence_length":
             d[key] = float(arr[0])
-        elif key in ("time_units", "metadata_schema"):
-            d[key] = _text(arr)
-        elif key == "metadata":
-            d[key] = bytes(arr.view(np.uint8))
-        elif key == "uuid":
-            d["file_uuid"] = _text(arr)
+        elif key in ("time_units", "metadata_schema", "metadata", "uuid"):
+            if arr.dtype != np.int8:  # kastore_gets_int8 (tables.c:11636-11700): KAS_ERR_TYPE_MISMATCH
+                _check((-13 ^ (1 << 14)) ^ (1 << 13), f"Cannot load '{os.fspath(path)}' ({key})")
+            if key == "metadata":
+                d[key] = bytes(arr.view(np.uint8))
+            else:
+                d["file_uuid" if key == "uuid" else key] = _text(arr)
         else:
             d[key] = arr
+    _check_columns(d, path)
     prov = d.pop("provenances", None)
     if prov is not None:
-        ts = _tables.decode_ragged(prov["timestamp"], prov["timestamp_offset"])
-        rec = _tables.decode_ragged(prov["record"], prov["record_offset"])
+        try:
+            ts = _tables.decode_ragged(prov["timestamp"], prov["timestamp_offset"])
+            rec = _tables.decode_ragged(prov["record"], prov["record_offset"])
+        except UnicodeDecodeError as e:
+            raise FileFormatError(f"A provenance row is not valid UTF-8 ({e})", -100 ^ (1 << 13)) from None
         d["provenances"] = [{"timestamp": t, "record": r} for t, r in zip(ts, rec)]
     for tbl, (_, ragged) in _SCHEMA.items():
         for name, kas in ragged:
