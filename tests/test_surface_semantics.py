@@ -530,3 +530,34 @@ def test_replay_parity_over_hand_made_existing_tables(native_built, oracle_mod, 
                                map_position=kw["map_position"], map_rate=kw["map_rate"], discrete=kw["discrete"],
                                keep=True)
             assert got.value.status == e.status
+
+
+@pytest.mark.gpu
+@pending_on_device
+def test_existing_offset_columns_are_checked_at_the_boundary(native_built):
+    """tskit refuses offset columns that do not start at 0 or that decrease (TSK_ERR_BAD_OFFSET, when the
+    columns are set); the C boundary does the same before anything is uploaded, because the kernels take
+    lengths as differences of neighbouring offsets."""
+    from msprime_b200 import _native
+
+    d = small_ts(seed=2, samples=5)
+    good = branch_mutations(d)
+    with _native.Context(0) as ctx:
+        ctx.load_tables(good)
+        for table, column in (("sites", "ancestral_state_offset"), ("sites", "metadata_offset"),
+                              ("mutations", "derived_state_offset"), ("mutations", "metadata_offset")):
+            for damage in ("start", "order"):
+                bad = dict(good)
+                bad[table] = dict(good[table])
+                off = np.array(good[table][column], dtype=np.uint64)
+                if damage == "start":
+                    off[0] = 1
+                else:
+                    off[1], off[2] = max(off[1], off[2]) + 1, min(off[1], off[2])
+                    if off[1] <= off[2]:
+                        continue
+                bad[table][column] = off
+                with pytest.raises(_native.LibraryError) as e:
+                    ctx.load_tables(bad)
+                assert e.value.status == (-200 ^ (1 << 13)), (table, column, damage)
+        ctx.load_tables(good)  # the context is still usable
