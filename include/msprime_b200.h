@@ -184,8 +184,10 @@ typedef struct mspb_ctx mspb_ctx_t;
  * usable GPU (there is no CPU fallback). */
 int mspb_ctx_create(int device, mspb_ctx_t **ctx);
 void mspb_ctx_destroy(mspb_ctx_t *ctx);
-/* Validates (tskit check_integrity(0) subset, lib/mutgen.c:1316), uploads the tables
- * and builds the child-sorted edge index.  Reusable across mspb_generate calls. */
+/* Validates (tskit check_integrity(0) subset, lib/mutgen.c:1316; and, for the existing site and
+ * mutation rows, what tsk_*_table_set_columns checks before the reference ever sees them: offset
+ * columns start at 0 and never decrease, else TSK_ERR_BAD_OFFSET with bit 13 flipped), uploads the
+ * tables and builds the child-sorted edge index.  Reusable across mspb_generate calls. */
 int mspb_ctx_load_tables(mspb_ctx_t *ctx, const mspb_tables_t *tables);
 
 /* The same with the upload shared between the `world` GPUs of a genome-sharded job (the tables
