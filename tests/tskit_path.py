@@ -12,6 +12,12 @@ _PKG = "/root/reference/git-submodules/tskit/python"
 
 
 def load():
+    if not os.environ.get("MSPB_TSKIT_PATH") and os.path.isdir(os.path.join(_PKG, "tskit")) \
+            and not os.path.exists(os.path.join(_EXT, ".stamp")):
+        # the reference tree is here but its extension has not been compiled yet (build() does this too)
+        import subprocess
+
+        subprocess.run(["make", "-s", "-C", os.path.join(ROOT, "oracle"), "tskit"], check=False)
     if os.environ.get("MSPB_TSKIT_PATH"):
         extra = [os.environ["MSPB_TSKIT_PATH"]]
     elif os.path.isdir(_EXT) and os.path.isdir(os.path.join(_PKG, "tskit")):
