@@ -27,9 +27,7 @@ def node_levels(num_nodes, parent, child):
     in tskit order, i.e. by parent time: a parent's children were all seen as parents earlier,
     so one pass over the edges in order is enough)."""
     level = np.zeros(num_nodes, dtype=np.int64)
-    order = np.arange(len(parent))
-    for j in order:  # plain loop: prototype; the device version is a scatter-max per level sweep
-        p, c = parent[j], child[j]
+    for p, c in zip(parent, child):  # plain loop: prototype; the device version relaxes with scatter-max
         if level[p] < level[c] + 1:
             level[p] = level[c] + 1
     return level
@@ -40,7 +38,6 @@ class StepFunctions:
         self.start = np.zeros(num_nodes + 1, dtype=np.int64)
         self.breaks = np.zeros(0, dtype=np.float64)
         self.values = np.zeros(0, dtype=np.int64)
-        self._pending = []  # (node ids, breaks, values) per level, concatenated at the end
 
     def value_at(self, nodes, x):
         """f_node(x) for arrays of queries."""
@@ -55,12 +52,11 @@ class StepFunctions:
 
 def build(tables):
     """Step functions of every node of the tree sequence (``asdict()``-style numpy columns)."""
-    time = np.asarray(tables["nodes"]["time"], dtype=np.float64)
     flags = np.asarray(tables["nodes"]["flags"])
     e = tables["edges"]
     left, right = np.asarray(e["left"], dtype=np.float64), np.asarray(e["right"], dtype=np.float64)
     parent, child = np.asarray(e["parent"], dtype=np.int64), np.asarray(e["child"], dtype=np.int64)
-    N, L = len(time), float(tables["sequence_length"])
+    N, L = len(flags), float(tables["sequence_length"])
     level = node_levels(N, parent, child)
     is_sample = (flags & 1) != 0
 

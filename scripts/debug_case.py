@@ -4,7 +4,6 @@ sys.path.insert(0, "tests")
 import cases
 import test_gpu_replay as T
 from msprime_b200 import _native
-import importlib
 sys.path.insert(0, ".")
 from oracle import oracle as oracle_mod  # noqa
 oracle_mod.build(("port",))

@@ -8,7 +8,6 @@ import sys
 import numpy as np
 import pytest
 
-import cases
 import table_checks
 from msprime_b200 import mutations, trees_io
 

@@ -9,7 +9,7 @@ import numpy as np
 import pytest
 
 import cases
-from msprime_b200 import _native, build, tables, trees_io
+from msprime_b200 import build, trees_io
 
 GOLDEN = os.path.join(os.path.dirname(__file__), "golden", "ref_overlay.trees")
 GOLDEN_COLUMNS = os.path.join(os.path.dirname(__file__), "golden", "ref_overlay_columns.npz")
