@@ -4,9 +4,9 @@ The in-memory surface of ``msprime/intervals.py:35-430``: keyword-only ``positio
 points, first one 0, strictly increasing) and ``rate`` (n non-negative values, NaN = missing
 data); read-only interval columns; point queries (``get_rate``, ``get_cumulative_mass``,
 ``find_index``); the Mapping protocol over the midpoints of the known intervals, with interval
-slices (``rate_map[a:b]``, ``slice``); ``uniform``, ``copy``, ``asdict``; the text / HTML table.
-Hapmap file reading and ``RecombinationMap`` are out of scope (recombination-side I/O).  All
-derived arrays are computed once, in the constructor, and frozen.
+slices (``rate_map[a:b]``, ``slice``); ``uniform``, ``copy``, ``asdict``, ``read_hapmap``; the text /
+HTML table.  The deprecated ``RecombinationMap`` is out of scope.  All derived arrays are computed
+once, in the constructor, and frozen.
 """
 from __future__ import annotations
 
@@ -67,6 +67,55 @@ class RateMap(collections.abc.Mapping):
     def uniform(sequence_length, rate) -> "RateMap":
         """One interval covering the whole sequence."""
         return RateMap(position=[0, sequence_length], rate=[rate])
+
+    @staticmethod
+    def read_hapmap(fileobj, sequence_length=None, *, has_header=True, position_col=None, rate_col=None,
+                    map_col=None) -> "RateMap":
+        """A rate map from a white-space separated HapMap-style table (``msprime/intervals.py:452-609``):
+        one column of physical positions in bp (default: the second) and either a column of cumulative
+        map positions in cM (``map_col``, default: the fourth) or one of rates in cM/Mb (``rate_col``), each
+        row's rate holding up to the next row's position.  The stretch before the first row is missing
+        data unless the map there is already above 0 (then the first rate extends back to 0); a
+        ``sequence_length`` beyond the last row adds a stretch of missing data, one short of it is an error.
+        ``fileobj`` goes to :func:`numpy.loadtxt` (file names ending in .gz / .bz2 are decompressed)."""
+        if rate_col is not None and map_col is not None:
+            raise ValueError("Cannot specify both rate_col and map_col")
+        by_rate = rate_col is not None
+        value_col = rate_col if by_rate else (3 if map_col is None else map_col)
+        position_col = 1 if position_col is None else position_col
+        if position_col == value_col:
+            raise ValueError("Cannot specify the same columns for position_col and rate_col or map_col")
+        value, pos = np.loadtxt(fileobj, skiprows=1 if has_header else 0, usecols=[value_col, position_col],
+                                dtype=[("value", float), ("pos", int)], unpack=True)
+        value, pos = np.atleast_1d(value), np.atleast_1d(pos)
+        if by_rate:
+            if len(value) and value[-1] != 0:
+                raise ValueError("The last entry in the 'rate' column must be zero")
+            # cM/Mb times Mb, accumulated, then cM -> Morgans
+            morgans = np.insert(np.cumsum(value[:-1] * np.diff(pos / 1e6)), 0, 0) / 100
+        else:
+            morgans = value / 100
+        if len(morgans) == 0:
+            raise ValueError("Empty hapmap file")
+        first, last = pos[0], pos[-1]
+        if morgans[0] > 0 and first == 0:
+            raise ValueError("The map distance at the start of the chromosome must be zero")
+        known_from = first
+        if first > 0:
+            if morgans[0] > 0:
+                known_from = 0  # the map is already above zero at the first row: its rate reaches back to 0
+            pos, morgans = np.insert(pos, 0, 0), np.insert(morgans, 0, 0)
+        if sequence_length is not None:
+            if sequence_length < last:
+                raise ValueError(f"The sequence_length cannot be less than the last physical position  ({pos[-1]})")
+            if sequence_length > last:
+                pos, morgans = np.append(pos, sequence_length), np.append(morgans, morgans[-1])
+        rate = np.diff(morgans) / np.diff(pos)
+        if known_from != 0:
+            rate[0] = np.nan
+        if last != pos[-1]:
+            rate[-1] = np.nan
+        return RateMap(position=pos, rate=rate)
 
     # read-only columns
     position = property(lambda self: self._cols["position"])

@@ -177,3 +177,52 @@ def test_tables_for_display():
     assert len(rows) == 10 and int(rows[-1][0]) == 9
     root = xml.etree.ElementTree.fromstring(msp.RateMap(position=[0, 10], rate=[0.1])._repr_html_())
     assert root.tag == "div" and len(list(root.find("table").find("tbody"))) == 1
+
+
+# ---- RateMap.read_hapmap against the reference's own reader (tests/golden/make_hapmap_golden.py)
+import gzip  # noqa: E402
+import io  # noqa: E402
+import warnings  # noqa: E402
+
+import hapmap_cases  # noqa: E402
+
+with open(os.path.join(HERE, "golden", "hapmap_ref.json")) as f:
+    HAPMAP_REF = json.load(f)
+
+
+@pytest.mark.parametrize("name", sorted(hapmap_cases.CASES))
+def test_read_hapmap(name):
+    text, kwargs = hapmap_cases.CASES[name]
+    want = HAPMAP_REF[name]
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")  # numpy warns about the empty / ragged inputs of the error cases
+        if "error" in want:
+            with pytest.raises(ValueError) as e:
+                msp.RateMap.read_hapmap(io.StringIO(text), **kwargs)
+            if want["message"].split()[0] in ("Cannot", "The", "Empty"):  # our own messages, not numpy's
+                assert str(e.value) == want["message"]
+            return
+        m = msp.RateMap.read_hapmap(io.StringIO(text), **kwargs)
+    assert same(m.position, want["position"]) and same(m.rate, want["rate"])
+
+
+def test_read_hapmap_from_files(tmp_path):
+    text, _ = hapmap_cases.CASES["simple"]
+    plain = tmp_path / "hapfile.txt"
+    plain.write_text(text)
+    m = msp.RateMap.read_hapmap(plain)
+    assert same(m.position, [0, 1, 2, 3]) and same(m.rate, HAPMAP_REF["simple"]["rate"])
+    packed = str(tmp_path / "hapmap.txt.gz")
+    with gzip.GzipFile(packed, "wb") as gz:
+        gz.write(b"HEADER\nchr1 0 1\nchr1 1 5.5\nchr1 2 0\n")
+    m = msp.RateMap.read_hapmap(packed, rate_col=2)
+    assert same(m.position, [0, 1, 2]) and same(m.rate, [1e-8, 5.5e-8])
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        with pytest.raises(ValueError, match="Empty"):
+            msp.RateMap.read_hapmap(io.StringIO("HEADER"))
+    # a single row (the reference's reader does not get this far: len() of a 0-d array)
+    one = msp.RateMap.read_hapmap(io.StringIO("HEADER\nchr1 5 x 0.000001\n"), sequence_length=9)
+    assert same(one.position, [0, 5, 9]) and same(one.rate, [1e-8 / 5, np.nan])
+    with pytest.raises(ValueError, match="missing data"):
+        msp.RateMap.read_hapmap(io.StringIO("HEADER\nchr1 5 x 0\n"), sequence_length=9)
