@@ -928,6 +928,14 @@ int check_model(const mspb_params_t *p)
         || p->transition_matrix == nullptr) {
         return MSPB_ERR_BAD_PARAM_VALUE;
     }
+    if (p->allele_offset[0] != 0) {
+        return MSPB_ERR_BAD_PARAM_VALUE;
+    }
+    for (uint64_t i = 0; i < p->num_alleles; i++) {
+        if (p->allele_offset[i + 1] < p->allele_offset[i]) {
+            return MSPB_ERR_BAD_PARAM_VALUE; // allele lengths are differences of neighbouring offsets
+        }
+    }
     if (!valid_probabilities(p->num_alleles, p->root_distribution)) {
         return MSPB_ERR_BAD_ROOT_PROBABILITIES;
     }
