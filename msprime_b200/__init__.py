@@ -26,3 +26,10 @@ from .mutations import (  # noqa: F401
     mutation_model_factory,
     sim_mutations,
 )
+
+# the names of the reference's ``msprime.__all__`` that belong to this path, plus the two error types
+__all__ = [
+    "BINARY", "BLOSUM62", "BinaryMutationModel", "EL2", "F84", "GTR", "HKY", "InfiniteAlleles", "InfiniteSites",
+    "InputError", "JC69", "LibraryError", "MatrixMutationModel", "MicrosatMutationModel", "MutationModel",
+    "NUCLEOTIDES", "PAM", "RateMap", "SLiMMutationModel", "SMM", "TPM", "mutate", "sim_mutations",
+]

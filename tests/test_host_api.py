@@ -219,3 +219,15 @@ def test_provenance_record_contents():
     # the parameters are enough to build the model again
     again = msp.HKY(**{k: v for k, v in p["model"].items() if k != "__class__"})
     assert np.array_equal(again.transition_matrix, msp.HKY(kappa=2.0).transition_matrix)
+
+
+def test_star_import_gives_the_paths_names():
+    # tests/test_imports_star.py: `from msprime import *` must work and export the documented names
+    ns = {}
+    exec("from msprime_b200 import *", ns)
+    wanted = {"BinaryMutationModel", "BLOSUM62", "F84", "GTR", "HKY", "InfiniteAlleles", "JC69", "MatrixMutationModel",
+              "MicrosatMutationModel", "MutationModel", "SMM", "TPM", "EL2", "NUCLEOTIDES", "PAM", "SLiMMutationModel",
+              "sim_mutations", "BINARY", "mutate", "InfiniteSites", "RateMap"}  # msprime/__init__.py, this path's share
+    assert wanted <= set(ns)
+    assert set(msp.__all__) == wanted | {"LibraryError", "InputError"}
+    assert "np" not in ns and "core" not in ns
