@@ -295,3 +295,28 @@ def test_command_line_on_tskit_files(tmp_path):
     # the same seed through the in-memory call gives the same tables
     again = msp.sim_mutations(base_ts(), rate=1e-4, random_seed=4, start_time=0, end_time=200, model="binary")
     assert again.tables.sites == out.tables.sites and again.tables.mutations == out.tables.mutations
+
+
+def test_legacy_alphabets():
+    """TestMutate, tests/test_mutations.py:618-684."""
+    ts = base_ts()
+    default = msp.mutate(ts, rate=1e-5, random_seed=2)
+    binary = msp.mutate(ts, rate=1e-5, random_seed=2, model=msp.InfiniteSites(msp.BINARY))
+    nucs = msp.mutate(ts, rate=1e-5, random_seed=2, model=msp.InfiniteSites(msp.NUCLEOTIDES))
+    assert default.tables.sites == binary.tables.sites and default.tables.mutations == binary.tables.mutations
+    assert {s.ancestral_state for s in binary.sites()} == {"0"}
+    assert {m.derived_state for m in binary.mutations()} == {"1"}
+    assert {s.ancestral_state for s in nucs.sites()} <= set("ACGT") and len({s.ancestral_state for s in nucs.sites()}) > 1
+    assert {m.derived_state for m in nucs.mutations()} <= set("ACGT")
+    # the alphabet does not move the mutations: same seed, same places, same branches
+    assert binary.num_sites == nucs.num_sites > 0 and binary.num_mutations == nucs.num_mutations
+    for a, b in zip(binary.sites(), nucs.sites()):
+        assert a.position == b.position and a.mutations[0].node == b.mutations[0].node
+    plain = msp.sim_mutations(ts, rate=1e-5, random_seed=2)  # the default here is nucleotides
+    assert {m.derived_state for m in plain.mutations()} <= set("ACGT")
+    for bad in (-1, 3, "binary"):
+        with pytest.raises(ValueError, match="alphabet"):
+            msp.InfiniteSites(bad)
+    for model in (msp.PAM(), "jc69", msp.BinaryMutationModel()):
+        with pytest.raises(ValueError, match="legacy"):
+            msp.mutate(ts, rate=1, random_seed=2, model=model)
