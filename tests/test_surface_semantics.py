@@ -233,6 +233,29 @@ def test_coalescent_trees_windows(engine):
     assert overlay(d, "jc69", 1.0, True, start_time=-10.0, end_time=-1.0).num_mutations == 0
 
 
+def rate_map_overlay(d, position, rate, discrete, seed=1):
+    ts = mtables.TableCollection.fromdict(d).tree_sequence()
+    return msp.sim_mutations(ts, rate=msp.RateMap(position=position, rate=rate), random_seed=seed,
+                             discrete_genome=discrete)
+
+
+def test_rate_map_zero_stretches_and_integer_sites(engine):
+    """TestMutateRateMap, tests/test_mutations.py:527-590: on a discrete genome an interval of the map
+    covers the INTEGERS inside it, whatever its break points; a stretch of rate 0 stays empty."""
+    d = small_ts(seed=6)  # ten positions, several trees
+    assert np.array_equal(rows(rate_map_overlay(d, [0, 3, 7, 10], [4.0, 0.0, 4.0], True))[0], [0, 1, 2, 7, 8, 9])
+    # [0, 2.9) holds 0, 1, 2; [4.3, 4.9) and [9.5, 10) hold no integer at all, however high their rates
+    out = rate_map_overlay(d, [0, 2.9, 4.3, 4.9, 9.5, 10], [4.0, 0.0, 10.0, 0.0, 10.0], True, seed=2)
+    assert np.array_equal(rows(out)[0], [0, 1, 2])
+    out = rate_map_overlay(d, [0, 0.5, 1.0, 4.5, 5.0, 9.5, 10], [0, 10, 0, 10, 0, 10], True, seed=2)
+    assert out.num_mutations == 0 and out.num_sites == 0
+    # continuous genome: every stretch with a rate gets mutations, the others none
+    position, rate = [0, 3, 4.3, 4.9, 10], [5.0, 0.0, 5.0, 0.0]
+    pos = rows(rate_map_overlay(d, position, rate, False, seed=2))[0]
+    for left, right, r in zip(position[:-1], position[1:], rate):
+        assert (np.sum((pos >= left) & (pos < right)) > 0) == (r > 0)
+
+
 # ---------------------------------------------------------------------------------------------
 # keep=True over inputs that did not come out of an overlay (TestKeep, tests/test_mutations.py:1231-1520):
 # hand-placed mutations on every branch, unique metadata on the existing rows, multi-character alleles,
