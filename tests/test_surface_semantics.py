@@ -256,6 +256,47 @@ def test_rate_map_zero_stretches_and_integer_sites(engine):
         assert (np.sum((pos >= left) & (pos < right)) > 0) == (r > 0)
 
 
+def cut_above(d, t):
+    """The tree sequence with every edge into a node older than `t` removed: trees with several roots,
+    as `sim_ancestry(..., end_time=t)` leaves them (tests/test_mutations.py:1678, 1758)."""
+    e = d["edges"]
+    keep = d["nodes"]["time"][e["parent"]] <= t
+    out = dict(d)
+    out["edges"] = {k: v[keep] for k, v in e.items()}
+    return out
+
+
+@pytest.mark.parametrize("model", ["jc69", "infinite_alleles", "slim"])
+def test_incomplete_trees(engine, model):
+    full = small_ts(seed=4, samples=8)
+    d = cut_above(full, float(np.quantile(full["nodes"]["time"], 0.7)))
+    e = d["edges"]
+    cover = (e["left"] <= 0.0) & (0.0 < e["right"])
+    in_tree = np.union1d(e["parent"][cover], e["child"][cover])
+    assert np.sum(parent_array(d, 0.0)[in_tree] == -1) > 1  # several roots in the first tree
+    m = {"jc69": "jc69", "infinite_alleles": msp.InfiniteAlleles(start_allele=3),
+         "slim": msp.SLiMMutationModel(type=1, next_id=10)}[model]
+    out = overlay(d, m, 2.0, True, seed=23)
+    assert out.num_mutations > 10
+    verify_mutations(d, out, True)
+    pos, anc, site, node, par, time, der = rows(out)
+    if model == "infinite_alleles":
+        expect = 3
+        for j in range(len(pos)):
+            assert int(anc[j]) == expect
+            expect += 1
+            for k in np.flatnonzero(site == j):
+                assert int(der[k]) == expect
+                expect += 1
+        assert m.next_allele == expect
+    if model == "slim":
+        assert set(anc) == {""} and m.next_id == 10 + len(der)
+        for k in range(len(der)):
+            ids = der[k].split(",")
+            assert int(ids[-1]) == 10 + k
+            assert (",".join(ids[:-1]) == der[par[k]]) if par[k] >= 0 else len(ids) == 1
+
+
 # ---------------------------------------------------------------------------------------------
 # keep=True over inputs that did not come out of an overlay (TestKeep, tests/test_mutations.py:1231-1520):
 # hand-placed mutations on every branch, unique metadata on the existing rows, multi-character alleles,
