@@ -124,3 +124,29 @@ def test_port_equals_reference_over_hand_made_existing_tables(oracle_mod, case):
         return
     assert not golden_util.diff_tables(want, got)
     assert got["draws"] == want["draws"]
+
+
+@pytest.mark.parametrize("case", range(24))
+def test_port_equals_reference_on_trees_with_several_roots(oracle_mod, case):
+    """Tree sequences cut at a time (what `sim_ancestry(end_time=...)` leaves): unary stretches, isolated
+    samples, several roots per tree; all three model kinds, both genome kinds, a second layer with keep."""
+    if not oracle_mod.have("ref"):
+        pytest.skip("compiled reference absent")
+    import test_surface_semantics as sem
+
+    rng = np.random.default_rng(9000 + case)
+    full = sem.small_ts(seed=int(rng.integers(1, 8)), samples=int(rng.integers(2, 12)), L=float(rng.choice([5, 20])))
+    ts = sem.cut_above(full, float(np.quantile(full["nodes"]["time"], rng.choice([0.55, 0.7, 0.9]))))
+    if len(ts["edges"]["left"]) == 0:  # nothing left below the cut (two samples): the uncut input then
+        ts = full
+    model = [cases.JC69, cases.BINARY, cases.INF_ALLELES, cases.SLIM, cases.MULTICHAR][case % 5]
+    for layer in range(2):
+        kw = dict(map_position=[0, ts["sequence_length"]], map_rate=[float(rng.choice([0.3, 2.0]))], model=model,
+                  discrete_genome=bool(case % 3), keep=bool(layer), stream=rng.random(100_000))
+        want, got = run(oracle_mod, "ref", ts, kw), run(oracle_mod, "port", ts, kw)
+        if isinstance(want, int) or isinstance(got, int):
+            assert want == got, (want, got)
+            return
+        assert not golden_util.diff_tables(want, got)
+        assert (got["draws"], got["next_allele"]) == (want["draws"], want["next_allele"])
+        ts = cases.with_kept(ts, want)
