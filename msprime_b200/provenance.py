@@ -37,22 +37,63 @@ def get_provenance_dict(parameters=None):
     }
 
 
+CURRENT_TREE_SEQUENCE = object()  # what the placeholder for "the input tree sequence" decodes to
+
+
 class _Encoder(json.JSONEncoder):
+    """The reference's encoding (``msprime/provenance.py:97-176``): the input tree sequence is a
+    placeholder, arrays and numpy scalars carry their dtype, objects with ``asdict`` carry their class."""
+
     def default(self, obj):
         if hasattr(obj, "tables") and hasattr(obj, "sequence_length"):
-            # tree sequences are not serialised (msprime/provenance.py:131-140)
+            # tree sequences are not serialised: the provenance row before this one describes them
             return {"__constant__": "__current_ts__"}
         if isinstance(obj, np.ndarray):
-            return obj.tolist()
+            return {"__ndarray__": obj.tolist(), "dtype": obj.dtype.str}
         if isinstance(obj, np.generic):
-            return obj.item()
+            return {"__npgeneric__": str(obj), "dtype": obj.dtype.str}
         if hasattr(obj, "asdict"):
-            d = obj.asdict()
-            d = {k: v for k, v in d.items()}
+            d = dict(obj.asdict())
             d["__class__"] = f"{obj.__class__.__module__}.{obj.__class__.__name__}"
             return d
-        return super().default(obj)
+        raise TypeError(f"Object of type {obj.__class__.__name__} is not JSON serialisable. Please provide an "
+                        "`asdict` method that returns the object's constructor arguments.")
 
 
 def json_encode_provenance(provenance_dict, num_replicates=1):
     return json.dumps(provenance_dict, cls=_Encoder)
+
+
+def json_decode_provenance(record: str):
+    """Inverse of :func:`json_encode_provenance`: arrays, numpy scalars and model / rate map objects
+    come back as such (classes are looked up in the module named in the record)."""
+    import importlib
+
+    def hook(obj):
+        if "__constant__" in obj:
+            return {"__current_ts__": CURRENT_TREE_SEQUENCE}[obj["__constant__"]]
+        if "__ndarray__" in obj:
+            return np.asarray(obj["__ndarray__"], dtype=obj["dtype"])
+        if "__npgeneric__" in obj:
+            return np.array([obj["__npgeneric__"]]).astype(obj["dtype"])[0]
+        if "__class__" in obj:
+            module, name = obj.pop("__class__").rsplit(".", 1)
+            return getattr(importlib.import_module(module), name)(**obj)
+        return obj
+
+    return json.JSONDecoder(object_hook=hook).decode(record)
+
+
+def parse_provenance(provenance, current_ts):
+    """``(command, parameters)`` of a provenance row written by this package, ready to run again:
+    ``getattr(msprime_b200, command)(**parameters)`` (``msprime/provenance.py:202-220``).  ``provenance``
+    is a row with a ``record`` attribute (tskit) or the JSON text itself."""
+    record = getattr(provenance, "record", provenance)
+    if isinstance(record, dict):
+        record = record["record"]
+    decoded = json_decode_provenance(record)
+    if decoded["software"]["name"] != "msprime_b200":
+        raise ValueError(f"Only msprime_b200 provenances can be parsed, found {decoded['software']['name']}")
+    parameters = decoded["parameters"]
+    command = parameters.pop("command")
+    return command, {k: (current_ts if v is CURRENT_TREE_SEQUENCE else v) for k, v in parameters.items()}

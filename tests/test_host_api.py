@@ -194,7 +194,8 @@ def test_uncalibrated_time_units_both_interfaces(rate):
 
 
 def test_provenance_record_contents():
-    # msprime/provenance.py:52-140; what tests/test_mutations.py:114-171 reads back from the record
+    # msprime/provenance.py:52-220; what tests/test_mutations.py:114-171 and tests/test_provenance.py:170-245
+    # read back from the record
     import json
 
     from msprime_b200 import provenance
@@ -202,23 +203,32 @@ def test_provenance_record_contents():
     ts = light_ts(cases.four_leaf_tree())
     rate_map = msp.RateMap(position=[0, 0.25, 1.0], rate=[1e-3, 0])
     params = dict(command="sim_mutations", tree_sequence=ts, rate=rate_map, model=msp.HKY(kappa=2.0),
-                  start_time=np.float64(-1), end_time=None, discrete_genome=None, keep=np.bool_(False),
-                  random_seed=np.int64(42))
-    record = json.loads(provenance.json_encode_provenance(provenance.get_provenance_dict(params)))
+                  start_time=np.int64(-1), end_time=np.array(100), discrete_genome=None, keep=False, random_seed=42)
+    text = provenance.json_encode_provenance(provenance.get_provenance_dict(params))
+    record = json.loads(text)
     assert record["schema_version"] == "1.0.0"
     assert record["software"]["name"] == "msprime_b200"
     assert {"os", "python", "libraries"} <= set(record["environment"])
     p = record["parameters"]
     assert p["command"] == "sim_mutations"
     assert p["tree_sequence"] == {"__constant__": "__current_ts__"}  # the input is referenced, not embedded
-    assert p["random_seed"] == 42 and p["start_time"] == -1 and p["keep"] is False
-    assert p["end_time"] is None and p["discrete_genome"] is None
-    assert p["rate"]["position"] == [0, 0.25, 1.0] and p["rate"]["rate"] == [1e-3, 0]
-    assert p["rate"]["__class__"].endswith("RateMap")
-    assert p["model"]["__class__"].endswith("HKY") and p["model"]["kappa"] == 2.0
-    # the parameters are enough to build the model again
-    again = msp.HKY(**{k: v for k, v in p["model"].items() if k != "__class__"})
-    assert np.array_equal(again.transition_matrix, msp.HKY(kappa=2.0).transition_matrix)
+    assert p["random_seed"] == 42 and p["keep"] is False and p["discrete_genome"] is None
+    assert p["start_time"]["__npgeneric__"] == "-1" and p["end_time"]["__ndarray__"] == 100
+    assert p["rate"]["__class__"] == "msprime_b200.intervals.RateMap"
+    assert p["rate"]["position"]["__ndarray__"] == [0, 0.25, 1.0] and p["rate"]["rate"]["__ndarray__"] == [1e-3, 0]
+    assert p["model"]["__class__"] == "msprime_b200.mutations.HKY" and p["model"]["kappa"] == 2.0
+    # and back: the call can be made again from the record
+    command, again = provenance.parse_provenance(text, ts)
+    assert command == "sim_mutations" and again["tree_sequence"] is ts
+    assert isinstance(again["rate"], msp.RateMap) and again["rate"] == rate_map
+    assert isinstance(again["model"], msp.HKY)
+    assert np.array_equal(again["model"].transition_matrix, msp.HKY(kappa=2.0).transition_matrix)
+    assert again["start_time"] == -1 and again["end_time"] == 100 and again["random_seed"] == 42
+    foreign = json.dumps(dict(record, software={"name": "skynet", "version": "1"}))
+    with pytest.raises(ValueError, match="Only msprime_b200"):
+        provenance.parse_provenance(foreign, None)
+    with pytest.raises(TypeError, match="asdict"):
+        provenance.json_encode_provenance({"x": object()})
 
 
 def test_star_import_gives_the_paths_names():

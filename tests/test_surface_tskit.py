@@ -211,7 +211,14 @@ def test_rate_map_confines_mutations():
     pos = out.tables.sites.position
     assert len(pos) > 0 and (pos >= 5000).all() and (pos <= 7000).all()
     p = last_record(out)["parameters"]["rate"]
-    assert p["position"] == [0, 5000, 7000.5, L] and p["__class__"].endswith("RateMap")
+    assert p["position"]["__ndarray__"] == [0, 5000, 7000.5, L] and p["__class__"].endswith("RateMap")
+    # the record is enough to make the call again (tests/test_provenance.py:240-245, 340-352)
+    from msprime_b200 import provenance
+
+    command, params = provenance.parse_provenance(out.provenance(out.num_provenances - 1), ts)
+    assert command == "sim_mutations" and params["tree_sequence"] is ts and params["rate"] == rate_map
+    again = getattr(msp, command)(**params)
+    assert again.tables.sites == out.tables.sites and again.tables.mutations == out.tables.mutations
     with pytest.raises(msp.InputError, match="rate map"):
         msp.sim_mutations(ts, rate=msp.RateMap(position=[0, L / 2], rate=[1e-5]))
 
