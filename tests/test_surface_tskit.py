@@ -70,6 +70,13 @@ def assert_rest_untouched(before, after):
         assert a.provenances[j] == b.provenances[j]
 
 
+def test_provenance_record_passes_tskits_schema():
+    # tests/test_provenance.py:55-64: tskit.validate_provenance on what the call writes
+    out = msp.sim_mutations(base_ts(), rate=msp.RateMap(position=[0, 1e4, 2e4], rate=[1e-6, 0]), random_seed=3,
+                            model=msp.GTR([1, 2, 1, 1, 2, 1]))
+    tskit.validate_provenance(last_record(out))
+
+
 def test_defaults_add_nothing_but_a_provenance_record():
     ts = base_ts()
     out = msp.sim_mutations(ts)
