@@ -275,6 +275,10 @@ void mspb_columns_free(mspb_columns_t *cols);
 
 const char *mspb_strerror(int err);
 const char *mspb_version(void);
+/* CUDA runtime the library was built against, as cudaRuntimeGetVersion reports it (12090 = 12.9); works
+ * without a device.  Recorded in provenance where the reference records its GSL version
+ * (msprime/provenance.py:66-69). */
+int mspb_cuda_runtime_version(void);
 
 #ifdef __cplusplus
 }

@@ -109,7 +109,7 @@ class _Columns(C.Structure):
 EXPORTED_SYMBOLS = [
     "mspb_ctx_create", "mspb_ctx_destroy", "mspb_ctx_load_tables", "mspb_generate", "mspb_fetch",
     "mspb_device_columns", "mspb_kernel_launches", "mspb_phase_ms", "mspb_phase_name",
-    "mspb_sim_mutations", "mspb_columns_free", "mspb_strerror", "mspb_version",
+    "mspb_sim_mutations", "mspb_columns_free", "mspb_strerror", "mspb_version", "mspb_cuda_runtime_version",
     "mspb_ctx_stream", "mspb_kernel_timing", "mspb_kernel_time", "mspb_selftest_sort",
     "mspb_generate_begin", "mspb_generate_end", "mspb_shift_offsets",
     "mspb_exchange_buffers", "mspb_exchange_post_counts", "mspb_generate_end_device",
@@ -170,6 +170,7 @@ def lib():
         L.mspb_strerror.argtypes = [C.c_int]
         L.mspb_strerror.restype = C.c_char_p
         L.mspb_version.restype = C.c_char_p
+        L.mspb_cuda_runtime_version.restype = C.c_int
         L.mspb_selftest_sort.argtypes = [C.c_void_p, C.c_uint64, C.c_int, C.c_uint64, C.c_uint64, C.c_int,
                                          C.POINTER(C.c_int)]
         L.mspb_ctx_stream.argtypes = [C.c_void_p]

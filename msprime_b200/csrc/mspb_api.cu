@@ -171,6 +171,16 @@ extern "C" const char *mspb_version(void)
     return MSPB_VERSION;
 }
 
+extern "C" int mspb_cuda_runtime_version(void)
+{
+    int v = 0;
+    if (cudaRuntimeGetVersion(&v) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return v;
+}
+
 extern "C" const char *mspb_strerror(int err)
 {
     switch (err) {

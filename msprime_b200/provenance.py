@@ -25,6 +25,15 @@ def get_environment():
         },
         "libraries": {"numpy": {"version": np.__version__}},
     }
+    try:  # the native library and the CUDA runtime it was built against, where the reference names GSL
+        from . import _native
+
+        lib = _native.lib()
+        cuda = int(lib.mspb_cuda_runtime_version())
+        env["libraries"]["msprime_b200_native"] = {"version": lib.mspb_version().decode()}
+        env["libraries"]["cuda_runtime"] = {"version": f"{cuda // 1000}.{cuda % 1000 // 10}"}
+    except Exception:  # noqa: BLE001 - a provenance record must not fail for want of a version string
+        pass
     return env
 
 
