@@ -178,6 +178,10 @@ def lib():
         L.mspb_kernel_timing.argtypes = [C.c_void_p, C.c_int]
         L.mspb_kernel_time.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_uint64),
                                        C.POINTER(C.c_double)]
+        L.mspb_sim_mutations.argtypes = [C.c_int, C.POINTER(_Tables), C.POINTER(_Params), C.POINTER(_Counts),
+                                         C.POINTER(_Columns)]
+        L.mspb_columns_free.argtypes = [C.POINTER(_Columns)]
+        L.mspb_columns_free.restype = None
         _lib = L
     return _lib
 
@@ -502,3 +506,41 @@ class Context:
         buf = (C.c_float * NUM_PHASES)()
         check(lib().mspb_phase_ms(self._h, buf, NUM_PHASES))
         return {lib().mspb_phase_name(i).decode(): float(buf[i]) for i in range(NUM_PHASES)}
+
+
+def sim_mutations_oneshot(tables_dict, params: Params, device: int = 0):
+    """The one-shot entry point ``mspb_sim_mutations`` (the call INTEGRATION.md's stub binds where the
+    reference calls ``mutgen_alloc`` .. ``mutgen_generate``, ``msprime/_msprimemodule.c:3084-3109``):
+    host tables in, malloc'd host columns out.  Returns ``(result, counts)`` with the columns copied
+    into numpy arrays and the library's buffers released (``mspb_columns_free``)."""
+    t, hold = Context._tables_struct(tables_dict)
+    c, cols = _Counts(), _Columns()
+    check(lib().mspb_sim_mutations(int(device), C.byref(t), C.byref(params.struct), C.byref(c), C.byref(cols)))
+    del hold
+    try:
+        counts = {name: getattr(c, name) for name, _ in _Counts._fields_}
+        S, M = counts["num_sites"], counts["num_mutations"]
+        sizes = {
+            "site_position": S, "site_ancestral_state": counts["ancestral_state_bytes"],
+            "site_ancestral_state_offset": S + 1, "site_metadata": counts["site_metadata_bytes"],
+            "site_metadata_offset": S + 1, "mutation_site": M, "mutation_node": M, "mutation_parent": M,
+            "mutation_time": M, "mutation_derived_state": counts["derived_state_bytes"],
+            "mutation_derived_state_offset": M + 1, "mutation_metadata": counts["mutation_metadata_bytes"],
+            "mutation_metadata_offset": M + 1,
+        }
+        off_dtype = np.uint32 if counts["offset_bytes"] == 4 else np.uint64
+        arrays = {}
+        for name, dtype in _COLUMNS:
+            if name.endswith("_offset"):
+                dtype = off_dtype
+            n = int(sizes[name])
+            ptr = getattr(cols, name)
+            if n == 0 or not ptr:
+                arrays[name] = np.zeros(0, dtype=dtype)
+            else:
+                arrays[name] = np.frombuffer(C.string_at(ptr, n * np.dtype(dtype).itemsize), dtype=dtype).copy()
+    finally:
+        lib().mspb_columns_free(C.byref(cols))
+    sites = {k[len("site_"):]: v for k, v in arrays.items() if k.startswith("site_")}
+    muts = {k[len("mutation_"):]: v for k, v in arrays.items() if k.startswith("mutation_")}
+    return {"sites": sites, "mutations": muts}, counts

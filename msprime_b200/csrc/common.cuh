@@ -224,16 +224,16 @@ MSPB_DEVFN uint32_t poisson_native(PhiloxSeq &rng, double mu)
         const double us = 0.5 - fabs(U);
         const double kf = floor((2.0 * a / us + b) * U + mu + 0.43);
         if (us >= 0.07 && V <= vr) {
-            return (uint32_t) kf;
+            return kf < 4294967295.0 ? (uint32_t) kf : 0xffffffffu; // (K1 rejects totals beyond 31 bits)
         }
         if (kf < 0.0 || (us < 0.013 && V > us)) {
             continue;
         }
         if (log(V) + log(invalpha) - log(a / (us * us) + b) <= -mu + kf * loglam - lgamma(kf + 1.0)) {
-            return (uint32_t) kf;
+            return kf < 4294967295.0 ? (uint32_t) kf : 0xffffffffu;
         }
     }
-    return (uint32_t) mu;
+    return mu < 4294967295.0 ? (uint32_t) mu : 0xffffffffu;
 }
 
 // ---------------------------------------------------------------- rate map

@@ -309,7 +309,7 @@ __global__ void k5_prefix_table_kernel(const uint32_t *__restrict__ site_row, co
 template <int MODEL, bool KEPT, bool OFF32>
 __global__ void __launch_bounds__(K5_THREADS, 4) k5_emit_kernel(SortedView sv, ResolveView rv, KeptView kept,
     ModelView model, CallView call, OutView out, LbWord *lb, uint32_t num_tiles, const Counts3 *p1_total,
-    Bytes4 *total, const uint32_t *dense, int *err)
+    Bytes4 *total, const uint32_t *dense, const uint32_t *collisions, int *err)
 {
     __shared__ uint64_t sm[9];
     __shared__ LbVal<2, true> bcast, s_agg;
@@ -321,8 +321,8 @@ __global__ void __launch_bounds__(K5_THREADS, 4) k5_emit_kernel(SortedView sv, R
     __shared__ __align__(16) uint32_t s_smd[MD ? K5_TILE : 4];
     __shared__ __align__(16) char st_der[K5_STAGE + 32];
     __shared__ __align__(16) char st_anc[K5_STAGE + 32];
-    if (*dense != 0u && sv.key.mode == KEY32_POS) {
-        return;
+    if ((*dense != 0u && sv.key.mode == KEY32_POS) || *collisions != 0u) {
+        return; // the host sorts again (dense genome) or redraws the colliding positions first
     }
     if (out.dev_bases != nullptr) {
         out.site_base += (uint32_t) out.dev_bases[0];

@@ -387,17 +387,19 @@ MSPB_DEVFN EdgeDraw edge_draw_from(const RateMapView &map, const CallView &call,
 // the tile (goff[e], loff[e]) plus one total per tile: tiles are independent, the tile
 // bases come from k1_spine_kernel, and K2 adds them when it reads.
 __global__ void __launch_bounds__(SCAN_THREADS, 4) k1_count_kernel(TreeSeqView ts, RateMapView map, CallView call,
-    uint32_t *__restrict__ goff, uint32_t *__restrict__ loff, uint64_t *__restrict__ tile_tot)
+    uint32_t *__restrict__ goff, uint32_t *__restrict__ loff, uint64_t *__restrict__ tile_tot, int *err)
 {
     __shared__ uint64_t sm[9];
     __shared__ uint64_t s_c[K1_TILE];
     __shared__ uint16_t s_big[K1_TILE]; // edges whose mean needs the rejection sampler
     __shared__ uint32_t s_nbig;
+    __shared__ unsigned long long s_exact; // the tile's count in 64 bits (only summed when it may be huge)
     const uint64_t tile_base = (uint64_t) blockIdx.x * K1_TILE;
     const uint64_t last = call.num_work - 1;
     const Philox ph(call.seed);
     if (threadIdx.x == 0) {
         s_nbig = 0;
+        s_exact = 0ull;
     }
     __syncthreads();
     // striped: consecutive threads take consecutive edges (coalesced column reads).  All
@@ -471,11 +473,30 @@ __global__ void __launch_bounds__(SCAN_THREADS, 4) k1_count_kernel(TreeSeqView t
     __syncthreads();
     // blocked: thread t scans the K1_ITEMS consecutive edges it owns
     uint64_t c[K1_ITEMS];
-    uint64_t acc = 0;
+    uint64_t acc = 0, low = 0;
 #pragma unroll
     for (int k = 0; k < K1_ITEMS; k++) {
         c[k] = s_c[threadIdx.x * K1_ITEMS + k];
         acc += c[k];
+        low += c[k] & 0xffffffffull;
+    }
+    // Counts are packed (new mutations | those inside the slice << 32) and ids are int32: a tile
+    // whose count does not fit 31 bits would carry into the upper half and cannot belong to a
+    // valid result anyway (MSPB_ERR_TOO_MANY_ROWS).  Every thread below 2^21 means the tile is
+    // below 2^29; otherwise the tile is summed exactly.
+    if (__syncthreads_or(low >= (1ull << 21) ? 1 : 0)) {
+        atomicAdd(&s_exact, (unsigned long long) low);
+        __syncthreads();
+        if (s_exact > 0x7fffffffull) {
+            if (threadIdx.x == 0) {
+                set_error(err, -1005);
+            }
+            acc = 0; // keep the packed sums in range; the call fails
+#pragma unroll
+            for (int k = 0; k < K1_ITEMS; k++) {
+                c[k] = 0;
+            }
+        }
     }
     uint64_t block_total;
     uint64_t run = block_exclusive_scan<uint64_t>(acc, sm, &block_total);
@@ -505,15 +526,20 @@ __global__ void __launch_bounds__(SCAN_THREADS, 4) k1_count_kernel(TreeSeqView t
 // tile_tot[t] (count | in-slice << 32) -> exclusive prefix in place, with the grand total
 // appended at tile_tot[num_tiles] and copied to *total.  One block; each thread owns a
 // contiguous run of tiles, so it is one pass and one block scan.
-__global__ void __launch_bounds__(1024) k1_spine_kernel(uint64_t *tile_tot, uint32_t num_tiles, uint64_t *total)
+__global__ void __launch_bounds__(1024) k1_spine_kernel(uint64_t *tile_tot, uint32_t num_tiles, uint64_t *total,
+    int *err)
 {
     __shared__ uint64_t warp_sum[32];
+    __shared__ unsigned long long s_exact;
+    if (threadIdx.x == 0) {
+        s_exact = 0ull;
+    }
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t per = (num_tiles + 1023u) / 1024u;
     const uint32_t lo = threadIdx.x * per, hi = lo + per < num_tiles ? lo + per : num_tiles;
     // (a thread's few tiles are loaded together: up to 16 independent loads in flight)
     uint64_t mine[16];
-    uint64_t sum = 0;
+    uint64_t sum = 0, low = 0;
     if (per <= 16) {
 #pragma unroll
         for (uint32_t q = 0; q < 16; q++) {
@@ -522,10 +548,29 @@ __global__ void __launch_bounds__(1024) k1_spine_kernel(uint64_t *tile_tot, uint
 #pragma unroll
         for (uint32_t q = 0; q < 16; q++) {
             sum += mine[q];
+            low += mine[q] & 0xffffffffull;
         }
     } else {
         for (uint32_t i = lo; i < hi; i++) {
-            sum += tile_tot[i];
+            const uint64_t v = tile_tot[i];
+            sum += v;
+            low += v & 0xffffffffull;
+        }
+    }
+    // the grand total must fit 31 bits (ids are int32; the packed halves must not carry): 1024
+    // threads below 2^21 each are safe, otherwise sum exactly
+    if (__syncthreads_or(low >= (1ull << 21) ? 1 : 0)) {
+        atomicAdd(&s_exact, (unsigned long long) low);
+        __syncthreads();
+        if (s_exact > 0x7fffffffull) {
+            if (threadIdx.x == 0) {
+                set_error(err, -1005);
+            }
+            sum = 0; // the call fails; keep what K2's guard reads in range
+#pragma unroll
+            for (uint32_t q = 0; q < 16; q++) {
+                mine[q] = 0;
+            }
         }
     }
     const uint64_t inc = warp_inclusive_scan(sum);
@@ -599,12 +644,13 @@ constexpr int K2_EDGES = 256;
 
 __global__ void __launch_bounds__(K2_EDGES) k2_place_kernel(TreeSeqView ts, RateMapView map, CallView call,
     const uint32_t *__restrict__ goff, const uint32_t *__restrict__ loff, const uint64_t *__restrict__ tile_base,
-    uint32_t base, Rec *__restrict__ rec, KeyView keys, const uint64_t *__restrict__ k1_total, uint64_t capacity)
+    uint32_t base, Rec *__restrict__ rec, KeyView keys, const uint64_t *__restrict__ k1_total, uint64_t capacity,
+    const int *err)
 {
     // Launched before the host has read the K1 total (so that the read overlaps this kernel):
-    // the buffers then have the capacity of earlier calls, and a total that does not fit makes
-    // the whole grid return; the host launches again after growing them.
-    if (k1_total != nullptr && (*k1_total & 0xffffffffull) + base > capacity) {
+    // the buffers then have the capacity of earlier calls, and a total that does not fit (or a
+    // count that K1 refused) makes the whole grid return; the host launches again after growing them.
+    if (k1_total != nullptr && ((*k1_total & 0xffffffffull) + base > capacity || *err != 0)) {
         return;
     }
     __shared__ EdgeDraw sd[K2_EDGES];
@@ -695,20 +741,103 @@ struct ReplayTotals {
     int exhausted;
 };
 
+// Continuous genome under the replay harness: a position that is already taken (by a kept site
+// or by an earlier new mutation) is drawn again from the NEXT uniform of the stream, exactly as
+// the reference's loop does (lib/mutgen.c:1127-1134), and so is a flat() value that rounds up to
+// its upper bound (lib/util.c:717-735).  Either makes the number of uniforms a mutation consumes
+// depend on everything placed before it, so the sequential walker places the mutations itself:
+// it keeps the taken positions in an open-addressing hash set in device memory (`set`, zeroed by
+// the host, capacity a power of two at least twice the number of positions it can hold) and
+// writes records and keys directly.  set == nullptr: discrete genome, placement stays parallel.
+struct ReplaySerial {
+    uint64_t *set;
+    uint64_t mask; // capacity - 1
+    const double *kept_position; // positions of the kept sites (taken from the start)
+    uint64_t num_kept_sites;
+    Rec *rec;
+    uint64_t *k64;
+    uint32_t base; // slot of the first new mutation
+    uint64_t max_new; // room for new mutations in rec / k64
+};
+
+MSPB_DEVFN uint64_t replay_hash(uint64_t k)
+{
+    k ^= k >> 33;
+    k *= 0xff51afd7ed558ccdull;
+    k ^= k >> 33;
+    k *= 0xc4ceb9fe1a85ec53ull;
+    k ^= k >> 33;
+    return k;
+}
+
+// true when key was already in the set; inserts it otherwise (keys are never 0: positions are >= 0)
+MSPB_DEVFN bool replay_set_test_and_insert(const ReplaySerial &sp, uint64_t key)
+{
+    uint64_t h = replay_hash(key) & sp.mask;
+    for (;;) {
+        const uint64_t v = sp.set[h];
+        if (v == key) {
+            return true;
+        }
+        if (v == 0ull) {
+            sp.set[h] = key;
+            return false;
+        }
+        h = (h + 1) & sp.mask;
+    }
+}
+
+MSPB_DEVFN bool replay_set_contains(const ReplaySerial &sp, uint64_t key)
+{
+    uint64_t h = replay_hash(key) & sp.mask;
+    for (;;) {
+        const uint64_t v = sp.set[h];
+        if (v == key) {
+            return true;
+        }
+        if (v == 0ull) {
+            return false;
+        }
+        h = (h + 1) & sp.mask;
+    }
+}
+
+// msp_gsl_ran_flat (lib/util.c:717-735) on the stream: no draw when lo == hi, again while x >= hi
+MSPB_DEVFN double replay_flat_serial(ReplayStream &s, double lo, double hi)
+{
+    if (lo == hi) {
+        return lo;
+    }
+    double x;
+    do {
+        const double u = s.next();
+        x = lo * (1 - u) + hi * u;
+    } while (x >= hi && !s.exhausted);
+    return x;
+}
+
 // One thread walks the stream in the reference's order: edges in table order, rate
 // intervals left to right, Poisson first, then two uniforms per mutation.
 __global__ void replay_resolve_kernel(TreeSeqView ts, RateMapView map, CallView call, const double *stream,
-    uint64_t stream_len, ReplayPairs pairs, ReplayTotals *totals, int *err)
+    uint64_t stream_len, ReplayPairs pairs, ReplaySerial sp, ReplayTotals *totals, int *err)
 {
     if (blockIdx.x != 0 || threadIdx.x != 0) {
         return;
     }
     ReplayStream s { stream, stream_len, 0, 0 };
     uint64_t np = 0, nm = 0;
+    const bool serial = sp.set != nullptr;
+    if (serial) {
+        // two kept sites at one position are P1's to report (MSP_ERR_DUPLICATE_SITE_POSITION)
+        for (uint64_t j = 0; j < sp.num_kept_sites; j++) {
+            replay_set_test_and_insert(sp, ordered_bits(sp.kept_position[j]));
+        }
+    }
     for (uint64_t e = 0; e < ts.num_edges && !s.exhausted; e++) {
         double left = ts.edge_left[e];
         const double edge_right = ts.edge_right[e];
-        const double branch_start = fmax(call.start_time, ts.node_time[ts.edge_child[e]]);
+        const int32_t child = ts.edge_child[e];
+        const double branch_start = fmax(call.start_time, ts.node_time[child]);
         const double branch_end = fmin(call.end_time, ts.node_time[ts.edge_parent[e]]);
         const double branch_length = branch_end - branch_start;
         uint32_t idx = map.index(left);
@@ -719,7 +848,11 @@ __global__ void replay_resolve_kernel(TreeSeqView ts, RateMapView map, CallView 
             const double mu = branch_length * (site_right - site_left) * map.rate[idx];
             const unsigned int n = replay_poisson(s, mu);
             if (n > 0) {
-                if (np >= pairs.capacity || nm + n > 0x7fffffffull) {
+                if (np >= pairs.capacity || nm + n > 0x7fffffffull || (serial && nm + n > sp.max_new)) {
+                    if (serial && nm + n > sp.max_new && nm + n <= 0x7fffffffull) {
+                        s.exhausted = 1; // every mutation takes two uniforms or more: the stream cannot cover them
+                        break;
+                    }
                     set_error(err, -1005);
                     s.exhausted = 1;
                     break;
@@ -730,10 +863,29 @@ __global__ void replay_resolve_kernel(TreeSeqView ts, RateMapView map, CallView 
                 pairs.out_off[np] = (uint32_t) nm;
                 pairs.stream_off[np] = s.pos;
                 np++;
-                nm += n;
-                s.pos += 2ull * n;
-                if (s.pos > s.len) {
-                    s.exhausted = 1;
+                if (!serial) {
+                    nm += n;
+                    s.pos += 2ull * n;
+                    if (s.pos > s.len) {
+                        s.exhausted = 1;
+                    }
+                } else {
+                    for (unsigned int k = 0; k < n && !s.exhausted; k++, nm++) {
+                        double x;
+                        uint64_t key;
+                        do {
+                            x = replay_flat_serial(s, site_left, site_right);
+                            key = ordered_bits(x);
+                        } while (replay_set_contains(sp, key) && !s.exhausted);
+                        const double t = replay_flat_serial(s, branch_start, branch_end);
+                        replay_set_test_and_insert(sp, key);
+                        Rec r;
+                        r.time = t;
+                        r.node = child;
+                        r.ord = (uint32_t) nm;
+                        sp.rec[sp.base + nm] = r;
+                        sp.k64[sp.base + nm] = key;
+                    }
                 }
             }
             left = right;
@@ -1201,10 +1353,17 @@ MSPB_DEVFN void resolve_site(const TreeSeqView &ts, const KeptView &kept, const 
 
 __global__ void __launch_bounds__(128, 12) k4_resolve_kernel(TreeSeqView ts, KeptView kept, ModelView model, CallView call,
     SortedView sv, ResolveView rv, const uint32_t *__restrict__ multi_list, uint32_t *next, const Counts3 *p1_total,
-    const uint32_t *dense, int *err)
+    const uint32_t *dense, const uint32_t *collisions, int *err)
 {
     if (*dense != 0u && sv.key.mode == KEY32_POS) {
         return; // the host re-sorts with time in the key and runs this step again
+    }
+    if (*collisions != 0u) {
+        // continuous genome: some new mutation sits on an occupied position.  The reference draws
+        // such a position again BEFORE any allele is read (lib/mutgen.c:1127-1134), so nothing
+        // may be resolved (or fail on an allele the model does not know) until positions are
+        // unique: the host redraws and runs this step again, or reports the collision.
+        return;
     }
     // The walks differ a lot in length, so the work list is handed out dynamically: the grid is
     // as large as the device holds at once, and a warp claims the next 32 sites whenever it is

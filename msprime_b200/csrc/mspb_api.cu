@@ -127,6 +127,7 @@ struct mspb_ctx {
     DBuf<int32_t> parent, state, site_state;
     DBuf<uint32_t> rp_edge, rp_interval, rp_count, rp_out_off;
     DBuf<uint64_t> rp_stream_off;
+    DBuf<uint64_t> replay_set; // replay harness, continuous genome: the positions taken so far (hash set)
     DBuf<char> dev_totals; // HostTotals mirror
     HostTotals *host = nullptr; // pinned
     uint64_t *or_and_host = nullptr; // pinned
@@ -355,7 +356,7 @@ extern "C" void mspb_ctx_destroy(mspb_ctx_t *ctx)
     REL(goff); REL(loff); REL(k1_tiles); REL(xchg); REL(slice_edges); REL(slice_scan_tiles); REL(rec); REL(keys0); REL(keys1); REL(k32_0); REL(k32_1); REL(vals0); REL(vals1);
     REL(tile_hist); REL(rs_scan_tiles); REL(or_and); REL(lb_state);
     REL(site_scan); REL(mut_scan); REL(draw_scan); REL(multi_list); REL(parent); REL(state); REL(site_state);
-    REL(rp_edge); REL(rp_interval); REL(rp_count); REL(rp_out_off); REL(rp_stream_off); REL(dev_totals);
+    REL(rp_edge); REL(rp_interval); REL(rp_count); REL(rp_out_off); REL(rp_stream_off); REL(replay_set); REL(dev_totals);
     REL(o_site_pos); REL(o_mut_time); REL(o_site_anc); REL(o_site_md); REL(o_mut_der); REL(o_mut_md);
     REL(o_site_anc_off); REL(o_site_md_off); REL(o_mut_der_off); REL(o_mut_md_off);
     REL(o_mut_site); REL(o_mut_node); REL(o_mut_parent);
@@ -1236,7 +1237,7 @@ int launch_emit(mspb_ctx *ctx)
     MSPB_LAUNCH(ctx->log, "k5_emit",                                                                                 \
         (k5_emit_kernel<M, K, O><<<k5_tiles, K5_THREADS, 0, st>>>(ctx->pending.sv, ctx->pending.rv,                \
             ctx->pending.kept, ctx->pending.model, ctx->pending.call, ctx->pending.out, lb4, k5_tiles, &dt->p1,      \
-            &dt->bytes, &dt->dense, &dt->err)))
+            &dt->bytes, &dt->dense, &dt->collisions, &dt->err)))
 #define MSPB_K5_MODEL(M)                                                                                             \
     if (kept_rows) {                                                                                                 \
         if (off32) {                                                                                                 \
@@ -1353,7 +1354,7 @@ int run_sorted_stages(mspb_ctx *ctx, const mspb_params_t *p, const TreeSeqView &
     }
     MSPB_LAUNCH(ctx->log, "k4_resolve",
         k4_resolve_kernel<<<148 * 12, 128, 0, st>>>(ts, kept, model, call, sv, rv, ctx->multi_list.p, &dt->k4_next, &dt->p1,
-            &dt->dense, &dt->err));
+            &dt->dense, &dt->collisions, &dt->err));
 
     // ---- K5: byte offsets + rows
     if (first_sort) {
@@ -1479,6 +1480,7 @@ static int generate_impl(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t 
     size_t spec_cap = 0;
     ReplayPairs pairs;
     memset(&pairs, 0, sizeof(pairs));
+    bool serial_placed = false; // replay harness, continuous genome: replay_resolve wrote the records itself
     if (!replay) {
         TRY(ctx->goff.ensure(ctx->E + 2));
         if (sliced) {
@@ -1489,9 +1491,9 @@ static int generate_impl(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t 
             TRY(ctx->k1_tiles.ensure(tiles + 1));
             MSPB_LAUNCH(ctx->log, "k1_count",
                 k1_count_kernel<<<tiles, SCAN_THREADS, 0, st>>>(
-                    ts, map, call, ctx->goff.p, sliced ? ctx->loff.p : nullptr, ctx->k1_tiles.p));
+                    ts, map, call, ctx->goff.p, sliced ? ctx->loff.p : nullptr, ctx->k1_tiles.p, &dt->err));
             MSPB_LAUNCH(ctx->log, "k1_spine",
-                k1_spine_kernel<<<1, 1024, 0, st>>>(ctx->k1_tiles.p, tiles, &dt->k1_total));
+                k1_spine_kernel<<<1, 1024, 0, st>>>(ctx->k1_tiles.p, tiles, &dt->k1_total, &dt->err));
         }
         CUDA_OK(cudaMemcpyAsync(ht, dt, sizeof(HostTotals), cudaMemcpyDeviceToHost, st));
         CUDA_OK(cudaEventRecord(ctx->ev_k1, st));
@@ -1511,12 +1513,19 @@ static int generate_impl(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t 
                 skeys.k64 = ctx->keys0.p;
                 MSPB_LAUNCH(ctx->log, "k2_place",
                     k2_place_kernel<<<grid_for(call.num_work, K2_EDGES), K2_EDGES, 0, st>>>(ts, map, call,
-                        ctx->goff.p, nullptr, ctx->k1_tiles.p, 0u, ctx->rec.p, skeys, &dt->k1_total, spec_cap));
+                        ctx->goff.p, nullptr, ctx->k1_tiles.p, 0u, ctx->rec.p, skeys, &dt->k1_total, spec_cap,
+                        &dt->err));
             } else {
                 spec_cap = 0;
             }
         }
         CUDA_OK(cudaEventSynchronize(ctx->ev_k1)); // the copy, not the kernel launched after it
+        if (ht->err != 0) {
+            // more new mutations than 31-bit ids can name (K1 / the spine refused the count)
+            CUDA_OK(cudaStreamSynchronize(st));
+            ctx->log.collect();
+            return ht->err;
+        }
         Mnew = sliced ? (ht->k1_total >> 32) : (ht->k1_total & 0xffffffffull);
     } else {
         const uint64_t cap = p->replay_len / 2 + 1;
@@ -1532,9 +1541,37 @@ static int generate_impl(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t 
         pairs.out_off = ctx->rp_out_off.p;
         pairs.stream_off = ctx->rp_stream_off.p;
         pairs.capacity = cap;
+        // Continuous genome: the walker places the mutations itself, because a position that is
+        // taken is drawn again from the stream (lib/mutgen.c:1127-1134).  Records and keys are
+        // sized from the stream length here (a mutation takes at least two uniforms).
+        ReplaySerial sp;
+        memset(&sp, 0, sizeof(sp));
+        if (!discrete) {
+            const uint64_t bound = S0 + M0 + cap;
+            if (bound > RS_MAX_N) {
+                return MSPB_ERR_TOO_MANY_ROWS;
+            }
+            uint64_t hcap = 1024;
+            while (hcap < 2 * (S0 + cap) + 2) {
+                hcap <<= 1;
+            }
+            TRY(ctx->rec.ensure(bound + 1));
+            TRY(ensure_sort_buffers(ctx, bound, false, true));
+            TRY(ctx->replay_set.ensure(hcap));
+            CUDA_OK(cudaMemsetAsync(ctx->replay_set.p, 0, hcap * sizeof(uint64_t), st));
+            sp.set = ctx->replay_set.p;
+            sp.mask = hcap - 1;
+            sp.kept_position = ctx->k_site_pos.p;
+            sp.num_kept_sites = S0;
+            sp.rec = ctx->rec.p;
+            sp.k64 = ctx->keys0.p;
+            sp.base = (uint32_t) (S0 + M0);
+            sp.max_new = cap;
+            serial_placed = true;
+        }
         MSPB_LAUNCH(ctx->log, "replay_resolve",
-            replay_resolve_kernel<<<1, 32, 0, st>>>(ts, map, call, ctx->replay.p, p->replay_len, pairs, &dt->replay,
-                &dt->err));
+            replay_resolve_kernel<<<1, 32, 0, st>>>(ts, map, call, ctx->replay.p, p->replay_len, pairs, sp,
+                &dt->replay, &dt->err));
         CUDA_OK(cudaMemcpyAsync(ht, dt, sizeof(HostTotals), cudaMemcpyDeviceToHost, st));
         CUDA_OK(cudaStreamSynchronize(st));
         if (ht->err != 0) {
@@ -1684,13 +1721,14 @@ static int generate_impl(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t 
     if (Mnew > 0) {
         const bool placed = spec_cap > 0 && Mnew <= spec_cap && spec_rec == ctx->rec.gen
                             && spec_key == (call.key_mode == KEY32_POS ? ctx->k32_0.gen : ctx->keys0.gen);
-        if (placed) {
-            // the early launch had room and the buffers did not move: the records are in place
+        if (placed || serial_placed) {
+            // the early launch had room and the buffers did not move (or the replay walker placed
+            // the mutations itself): the records are in place
         } else if (!replay) {
             MSPB_LAUNCH(ctx->log, "k2_place",
                 k2_place_kernel<<<grid_for(call.num_work, K2_EDGES), K2_EDGES, 0, st>>>(ts, map, call, ctx->goff.p,
                     sliced ? ctx->loff.p : nullptr, ctx->k1_tiles.p, (uint32_t) (S0 + M0), ctx->rec.p, keys, nullptr,
-                    0));
+                    0, nullptr));
         } else {
             MSPB_LAUNCH(ctx->log, "replay_place",
                 replay_place_kernel<<<grid_for(num_pairs, 128), 128, 0, st>>>(ts, map, call, ctx->replay.p, pairs,

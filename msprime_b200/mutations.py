@@ -11,6 +11,7 @@ from __future__ import annotations
 import inspect
 import math
 import sys
+import threading
 
 import numpy as np
 
@@ -479,13 +480,28 @@ def mutation_model_factory(model):
 
 
 _contexts: dict[int, _native.Context] = {}
+# One context per device is shared by every caller, and load_tables / generate / fetch are three
+# ctypes calls that release the GIL: the sequence runs under the device's lock, so that two threads
+# calling sim_mutations on one device cannot generate over, or fetch, each other's tables (the
+# reference keeps all state per call, msprime/_msprimemodule.c:3047-3120).
+_contexts_guard = threading.Lock()
+_device_locks: dict[int, threading.Lock] = {}
+
+
+def _device_lock(device: int) -> threading.Lock:
+    with _contexts_guard:
+        lock = _device_locks.get(device)
+        if lock is None:
+            lock = _device_locks[device] = threading.Lock()
+        return lock
 
 
 def _context(device: int) -> _native.Context:
-    ctx = _contexts.get(device)
-    if ctx is None:
-        ctx = _contexts[device] = _native.Context(device)
-    return ctx
+    with _contexts_guard:
+        ctx = _contexts.get(device)
+        if ctx is None:
+            ctx = _contexts[device] = _native.Context(device)
+        return ctx
 
 
 def _overlay(ctx, tables_dict, *, rate_map, model, discrete_genome, keep, start_time, end_time,
@@ -599,10 +615,11 @@ def sim_mutations(
     model = mutation_model_factory(model)
     seed = core.check_seed(seed)
 
-    result, _ = _overlay(
-        _context(device), tables_dict, rate_map=rate_map.asdict(), model=model,
-        discrete_genome=discrete_genome, keep=keep, start_time=start_time, end_time=end_time,
-        seed=seed)
+    with _device_lock(device):
+        result, _ = _overlay(
+            _context(device), tables_dict, rate_map=rate_map.asdict(), model=model,
+            discrete_genome=discrete_genome, keep=keep, start_time=start_time, end_time=end_time,
+            seed=seed)
     out = _merge_result(tables_dict, result)
     record = None
     if provenance_dict is not None:

@@ -76,7 +76,21 @@ def json_encode_provenance(provenance_dict, num_replicates=1):
 def json_decode_provenance(record: str):
     """Inverse of :func:`json_encode_provenance`: arrays, numpy scalars and model / rate map objects
     come back as such (classes are looked up in the module named in the record)."""
-    import importlib
+    def resolve(qualified):
+        # Only this package's own model and rate-map classes are ever built from a record: a row in an
+        # untrusted .trees file must not be able to name an arbitrary callable.
+        from . import intervals, mutations
+
+        module, _, name = qualified.rpartition(".")
+        allowed = {"msprime_b200.mutations": (mutations, mutations.MutationModel),
+                   "msprime_b200.intervals": (intervals, intervals.RateMap)}
+        if module not in allowed:
+            raise ValueError(f"provenance record names a class outside this package: {qualified}")
+        mod, base = allowed[module]
+        cls = getattr(mod, name, None)
+        if not (isinstance(cls, type) and issubclass(cls, base)):
+            raise ValueError(f"provenance record names an unknown class: {qualified}")
+        return cls
 
     def hook(obj):
         if "__constant__" in obj:
@@ -86,8 +100,7 @@ def json_decode_provenance(record: str):
         if "__npgeneric__" in obj:
             return np.array([obj["__npgeneric__"]]).astype(obj["dtype"])[0]
         if "__class__" in obj:
-            module, name = obj.pop("__class__").rsplit(".", 1)
-            return getattr(importlib.import_module(module), name)(**obj)
+            return resolve(obj.pop("__class__"))(**obj)
         return obj
 
     return json.JSONDecoder(object_hook=hook).decode(record)
@@ -100,9 +113,10 @@ def parse_provenance(provenance, current_ts):
     record = getattr(provenance, "record", provenance)
     if isinstance(record, dict):
         record = record["record"]
+    name = json.loads(record).get("software", {}).get("name")  # checked before any object is rebuilt
+    if name != "msprime_b200":
+        raise ValueError(f"Only msprime_b200 provenances can be parsed, found {name}")
     decoded = json_decode_provenance(record)
-    if decoded["software"]["name"] != "msprime_b200":
-        raise ValueError(f"Only msprime_b200 provenances can be parsed, found {decoded['software']['name']}")
     parameters = decoded["parameters"]
     command = parameters.pop("command")
     return command, {k: (current_ts if v is CURRENT_TREE_SEQUENCE else v) for k, v in parameters.items()}

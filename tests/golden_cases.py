@@ -65,6 +65,16 @@ def all_cases():
     pos, rate = _ratemap(L)
     for discrete in (True, False):
         add(f"smc-ratemap-{'d' if discrete else 'c'}", smc, "jc69", pos, rate, discrete=discrete, n=100_000)
+    # continuous genome, second layer drawn from the SAME stream as the first: every first draw of a
+    # position lands on a site that is taken and is drawn again from the next uniform
+    # (lib/mutgen.c:1127-1134; the reference forces this with equal seeds, tests/test_mutations.py:1340-1354)
+    for model in ("jc69", "binary", "infinite_alleles", "slim"):
+        add(f"smc-{model}-c-a-sameseed", smc, model, [0, L], [7e-7], discrete=False, keep=True,
+            base=f"smc-{model}-c-a", seed=1, n=100_000)
+    add("four_leaf-jc69-c-4.0-sameseed", ("four_leaf",), "jc69", [0, 10], [4.0], discrete=False, keep=True,
+        base="four_leaf-jc69-c-4.0", seed=1)
+    add("four_leaf-multichar-c-0.3-sameseed", ("four_leaf",), "multichar", [0, 10], [0.3], discrete=False, keep=True,
+        base="four_leaf-multichar-c-0.3", seed=1)
     # big mu per edge: exercises the gamma / binomial branch of gsl_ran_poisson
     add("four_leaf-bigmu", ("four_leaf",), "jc69", [0, 10], [12.0], n=60_000)
     return out

@@ -14,13 +14,6 @@ from msprime_b200 import mutations, tables as mtables
 
 NUC = ["A", "C", "G", "T"]
 
-# None of the device runs in this file has happened yet: the file was written after round 1's GPU time was
-# spent.  The bodies are verified on the CPU (oracle stand-in); until the first device run a device failure is
-# reported as xfail instead of stopping the suite, a pass as XPASS (then the marker goes).
-pending_on_device = pytest.mark.xfail(reason="first device run pending (written after the round's GPU time was spent)",
-                                      strict=False)
-
-
 def _engine(request, monkeypatch):
     if request.param == "oracle":
         import oracle_engine
@@ -33,7 +26,7 @@ def _engine(request, monkeypatch):
     return request.param
 
 
-@pytest.fixture(params=["oracle", pytest.param("device", marks=[pytest.mark.gpu, pending_on_device])])
+@pytest.fixture(params=["oracle", pytest.param("device", marks=[pytest.mark.gpu])])
 def engine(request, monkeypatch):
     return _engine(request, monkeypatch)
 
@@ -304,7 +297,7 @@ def test_incomplete_trees(engine, model):
 # (The parity tests on the device layer only over overlay output so far, so these are new ground there.)
 
 
-@pytest.fixture(params=["oracle", pytest.param("device", marks=[pytest.mark.gpu, pending_on_device])])
+@pytest.fixture(params=["oracle", pytest.param("device", marks=[pytest.mark.gpu])])
 def keep_engine(request, monkeypatch):
     return _engine(request, monkeypatch)
 
@@ -560,9 +553,8 @@ def test_layering_a_model_with_other_alleles(keep_engine):
 # ---------------------------------------------------------------------------------------------
 # The same hand-made existing tables through the replay harness, bit for bit against the oracle (the
 # inputs of tests/test_oracle_fuzz.py::test_port_equals_reference_over_hand_made_existing_tables, where
-# the oracle's restatement is held to the compiled reference).  Device runs pending, as above.
+# the oracle's restatement is held to the compiled reference).
 @pytest.mark.gpu
-@pending_on_device
 @pytest.mark.parametrize("case", range(12))
 def test_replay_parity_over_hand_made_existing_tables(native_built, oracle_mod, case):
     import test_gpu_replay as replay
@@ -597,7 +589,6 @@ def test_replay_parity_over_hand_made_existing_tables(native_built, oracle_mod, 
 
 
 @pytest.mark.gpu
-@pending_on_device
 def test_existing_offset_columns_are_checked_at_the_boundary(native_built):
     """tskit refuses offset columns that do not start at 0 or that decrease (TSK_ERR_BAD_OFFSET, when the
     columns are set); the C boundary does the same before anything is uploaded, because the kernels take
