@@ -63,6 +63,7 @@ extern "C" {
 #define MSPB_ERR_NOT_GENERATED (-1007)
 #define MSPB_ERR_UNSORTED_SITES (-1009) /* sliced call: kept sites must be sorted by position */
 #define MSPB_ERR_OFFSET_OVERFLOW (-1008) /* offsets32 asked for, but a column may reach 4 GiB */
+#define MSPB_ERR_NOALLOC_TOO_LARGE (-1010) /* mspb_site_rows_noalloc: more than MSPB_NOALLOC_MAX_RECORDS records */
 
 /* the reference's three C models (lib/mutgen.c:184-237, 257-413, 431-481) */
 enum { MSPB_MODEL_MATRIX = 0, MSPB_MODEL_INFINITE_ALLELES = 1, MSPB_MODEL_SLIM = 2 };
@@ -272,6 +273,25 @@ int mspb_selftest_sort(mspb_ctx_t *ctx, uint64_t n, int key_bytes, uint64_t key_
 int mspb_sim_mutations(int device, const mspb_tables_t *tables, const mspb_params_t *params,
     mspb_counts_t *counts, mspb_columns_t *out);
 void mspb_columns_free(mspb_columns_t *cols);
+
+/* Allocation-free site numbering.  This entry point has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid it).  It is the site-numbering step of the overlay
+ * (the kernel behind mspb_generate that turns position-sorted records into site rows) on caller-owned
+ * device memory: sorted_positions[n] (uint32 integer positions in non-decreasing order) in, site_row[n]
+ * (the number of distinct positions before each record = the `site` column of the mutation table) and
+ * *num_sites out; all three are DEVICE pointers, the arrays 16-byte aligned.  The work is enqueued on
+ * `stream` (a cudaStream_t, NULL = the default stream) of CUDA device `device` and the call returns
+ * without waiting.  It calls no cudaMalloc / cudaFree / cudaMallocHost and no allocating library routine:
+ * the kernel's cross-tile scratch is a file-scope __device__ array of 256.3 KB that every GPU loading the
+ * library holds until exit, which bounds the input: n > MSPB_NOALLOC_MAX_RECORDS (2^26) is refused with
+ * MSPB_ERR_NOALLOC_TOO_LARGE.  All calls on a device share that array and it keeps the last call's
+ * contents (the call clears what it uses, on `stream`, first): calls that overlap on one GPU race; order
+ * them on one stream or with events.  The first call on a device looks the array's address up
+ * (cudaGetSymbolAddress) and should be made outside stream capture. */
+#define MSPB_NOALLOC_MAX_RECORDS (1ull << 26)
+int mspb_site_rows_noalloc(int device, void *stream, const uint32_t *sorted_positions, uint64_t n,
+    uint32_t *site_row, uint64_t *num_sites);
 
 const char *mspb_strerror(int err);
 const char *mspb_version(void);

@@ -114,7 +114,7 @@ EXPORTED_SYMBOLS = [
     "mspb_generate_begin", "mspb_generate_end", "mspb_shift_offsets",
     "mspb_exchange_buffers", "mspb_exchange_post_counts", "mspb_generate_end_device",
     "mspb_generate_finish_device", "mspb_last_fetch_bytes", "mspb_ctx_load_tables_begin",
-    "mspb_ctx_load_tables_end",
+    "mspb_ctx_load_tables_end", "mspb_site_rows_noalloc",
 ]
 
 EXCHANGE_WORDS = 8  # MSPB_EXCHANGE_WORDS
@@ -182,6 +182,7 @@ def lib():
                                          C.POINTER(_Columns)]
         L.mspb_columns_free.argtypes = [C.POINTER(_Columns)]
         L.mspb_columns_free.restype = None
+        L.mspb_site_rows_noalloc.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]
         _lib = L
     return _lib
 
@@ -544,3 +545,15 @@ def sim_mutations_oneshot(tables_dict, params: Params, device: int = 0):
     sites = {k[len("site_"):]: v for k, v in arrays.items() if k.startswith("site_")}
     muts = {k[len("mutation_"):]: v for k, v in arrays.items() if k.startswith("mutation_")}
     return {"sites": sites, "mutations": muts}, counts
+
+
+NOALLOC_MAX_RECORDS = 1 << 26  # MSPB_NOALLOC_MAX_RECORDS
+ERR_NOALLOC_TOO_LARGE = -1010
+
+
+def site_rows_noalloc(device, stream, sorted_positions_ptr, n, site_row_ptr, num_sites_ptr):
+    """``mspb_site_rows_noalloc``: raw device pointers in, work enqueued on ``stream`` (an integer
+    ``cudaStream_t``, 0 = default stream); nothing is allocated.  Raises on a non-zero status."""
+    check(lib().mspb_site_rows_noalloc(int(device), C.c_void_p(int(stream) or None),
+                                       C.c_void_p(int(sorted_positions_ptr) or None), int(n),
+                                       C.c_void_p(int(site_row_ptr) or None), C.c_void_p(int(num_sites_ptr) or None)))

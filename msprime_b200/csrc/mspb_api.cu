@@ -242,6 +242,9 @@ extern "C" const char *mspb_strerror(int err)
             return "A ragged column may exceed 4 GiB: 32-bit offsets cannot be used";
         case MSPB_ERR_NOT_GENERATED:
             return "No result is resident: call mspb_generate first";
+        case MSPB_ERR_NOALLOC_TOO_LARGE:
+            return "Input exceeds the fixed scratch of the allocation-free entry point "
+                   "(more than MSPB_NOALLOC_MAX_RECORDS records)";
         default:
             break;
     }
@@ -2432,4 +2435,158 @@ extern "C" int mspb_selftest_sort(mspb_ctx_t *ctx, uint64_t n, int key_bytes, ui
         return selftest_sort_impl<uint32_t>(ctx, n, key_mask & 0xffffffffull, seed, measure_bits != 0, passes);
     }
     return selftest_sort_impl<uint64_t>(ctx, n, key_mask, seed, measure_bits != 0, passes);
+}
+
+// ---------------------------------------------------------------- allocation-free entry point
+// mspb_site_rows_noalloc (include/msprime_b200.h): the site numbering step (a variant of
+// p1_sites_kernel for 32-bit position keys without kept rows) for callers that cannot call
+// cudaMalloc: code under CUDA graph capture, tight serving loops, harnesses that forbid it.
+// The cross-tile look-back state, which the regular path keeps in a context buffer from
+// cudaMalloc, lives here in a file-scope device array of fixed size: every GPU that loads the
+// library holds these 256.3 KB until the process exits.  Every call on a device shares the
+// array and finds the previous call's contents in it, so the part a call uses is cleared on
+// the caller's stream before the kernel; two calls that overlap on one GPU (different
+// streams, no ordering between them) race on it.  No cudaMalloc, cudaFree, cudaMallocHost or
+// other allocating routine is called on this path.
+namespace {
+
+constexpr uint64_t NOALLOC_MAX_RECORDS = MSPB_NOALLOC_MAX_RECORDS;
+constexpr uint64_t NOALLOC_MAX_TILES = (NOALLOC_MAX_RECORDS + P1_TILE - 1) / P1_TILE; // 16384
+constexpr size_t NOALLOC_HEADER_BYTES = 256; // word 0: number of sites
+constexpr size_t NOALLOC_SCRATCH_BYTES = NOALLOC_HEADER_BYTES + (NOALLOC_MAX_TILES + 1) * sizeof(LbWord);
+
+// In HOST code this name is only a stand-in for the symbol, not a device address: the address
+// each device gives it comes from cudaGetSymbolAddress (noalloc_scratch_address below).
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NOALLOC_SCRATCH_BYTES];
+
+constexpr int NOALLOC_MAX_DEVICES = 64;
+void *g_noalloc_ptr[NOALLOC_MAX_DEVICES] = {};
+
+// device address of the scratch array on the CURRENT device, looked up once per device
+int noalloc_scratch_address(int device, unsigned char **out)
+{
+    if (device < 0 || device >= NOALLOC_MAX_DEVICES) {
+        return MSPB_ERR_BAD_PARAM_VALUE;
+    }
+    void *p = __atomic_load_n(&g_noalloc_ptr[device], __ATOMIC_ACQUIRE);
+    if (p == nullptr) {
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (e != cudaSuccess || p == nullptr) {
+            fprintf(stderr, "msprime_b200: cudaGetSymbolAddress failed on device %d: %s\n", device,
+                cudaGetErrorString(e));
+            cudaGetLastError();
+            return MSPB_ERR_CUDA;
+        }
+        // (two threads racing here store the same address)
+        __atomic_store_n(&g_noalloc_ptr[device], p, __ATOMIC_RELEASE);
+    }
+    *out = static_cast<unsigned char *>(p);
+    return 0;
+}
+
+// Site row of every record of a position-sorted array of 32-bit keys: the number of distinct
+// positions before it (p1_sites_kernel<KEY32_POS, false> without the work list, the draw
+// numbering and the input checks).  Thread t owns 16 consecutive records; one block scan and
+// one decoupled look-back across tiles whose state is `lb` (zeroed before the launch).
+__global__ void __launch_bounds__(SCAN_THREADS, 4) site_rows_noalloc_kernel(const uint32_t *__restrict__ keys,
+    uint64_t n, uint32_t *__restrict__ site_row, LbWord *lb, uint32_t num_tiles, uint64_t *num_sites)
+{
+    __shared__ uint32_t sm[9];
+    __shared__ LbVal<1, false> bcast;
+    const uint64_t tile_base = (uint64_t) blockIdx.x * P1_TILE;
+    const uint64_t i0 = tile_base + (uint64_t) threadIdx.x * P1_ITEMS;
+    const uint64_t last = n - 1;
+    const bool full = tile_base + P1_TILE <= n;
+    uint32_t pk[P1_ITEMS + 1]; // pk[k + 1]: key of record i0 + k
+    if (full) {
+        load16<uint32_t>(keys + i0, pk + 1);
+    } else {
+#pragma unroll
+        for (int k = 0; k < P1_ITEMS; k++) {
+            pk[k + 1] = keys[i0 + k < last ? i0 + k : last];
+        }
+    }
+    pk[0] = keys[i0 > 0 ? (i0 - 1 < last ? i0 - 1 : last) : 0];
+    uint32_t heads = 0, acc = 0; // bit k: record i0 + k opens a site
+#pragma unroll
+    for (int k = 0; k < P1_ITEMS; k++) {
+        const uint64_t i = i0 + k;
+        if (i < n && (i == 0 || pk[k + 1] != pk[k])) {
+            heads |= 1u << k;
+            acc++;
+        }
+    }
+    uint32_t block_total;
+    uint32_t run = block_exclusive_scan<uint32_t>(acc, sm, &block_total);
+    LbVal<1, false> agg;
+    agg.w[0][0] = block_total;
+    agg.w[0][1] = agg.w[0][2] = agg.w[0][3] = 0;
+    const LbVal<1, false> pw = lookback_prefix<1, false>(lb, blockIdx.x, agg, &bcast);
+    if (blockIdx.x + 1 == num_tiles && threadIdx.x == 0) {
+        *num_sites = (uint64_t) pw.w[0][0] + block_total;
+    }
+    uint32_t site[P1_ITEMS];
+    run += pw.w[0][0];
+#pragma unroll
+    for (int k = 0; k < P1_ITEMS; k++) {
+        run += (heads >> k) & 1u;
+        site[k] = run - 1u; // inclusive count of heads: the record's own site row is count - 1
+    }
+    if (full) {
+        store16(site_row + i0, site);
+    } else {
+#pragma unroll
+        for (int k = 0; k < P1_ITEMS; k++) {
+            if (i0 + k < n) {
+                site_row[i0 + k] = site[k];
+            }
+        }
+    }
+}
+
+} // namespace
+
+extern "C" int mspb_site_rows_noalloc(int device, void *stream, const uint32_t *sorted_positions, uint64_t n,
+    uint32_t *site_row, uint64_t *num_sites)
+{
+    if (num_sites == nullptr || (n > 0 && (sorted_positions == nullptr || site_row == nullptr))) {
+        return MSPB_ERR_BAD_PARAM_VALUE;
+    }
+    if (n > NOALLOC_MAX_RECORDS) {
+        return MSPB_ERR_NOALLOC_TOO_LARGE; // the scratch array is fixed: no larger input can be served
+    }
+    if (n > 0 && ((reinterpret_cast<uintptr_t>(sorted_positions) | reinterpret_cast<uintptr_t>(site_row)) & 15u) != 0) {
+        return MSPB_ERR_BAD_PARAM_VALUE; // full tiles move 16 bytes at a time
+    }
+    int previous = -1;
+    CUDA_OK(cudaGetDevice(&previous));
+    if (previous != device) {
+        CUDA_OK(cudaSetDevice(device));
+    }
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    unsigned char *scratch = nullptr;
+    int ret = noalloc_scratch_address(device, &scratch); // set-up: once per device, that device current
+    if (ret == 0) {
+        if (n == 0) {
+            ret = cudaMemsetAsync(num_sites, 0, sizeof(uint64_t), st) == cudaSuccess ? 0 : MSPB_ERR_CUDA;
+        } else {
+            const uint32_t tiles = (uint32_t) ((n + P1_TILE - 1) / P1_TILE);
+            LbWord *lb = reinterpret_cast<LbWord *>(scratch + NOALLOC_HEADER_BYTES);
+            // the look-back state must start at zero; the array keeps the last call's contents
+            if (cudaMemsetAsync(lb, 0, ((size_t) tiles + 1) * sizeof(LbWord), st) != cudaSuccess) {
+                ret = MSPB_ERR_CUDA;
+            } else {
+                site_rows_noalloc_kernel<<<tiles, SCAN_THREADS, 0, st>>>(sorted_positions, n, site_row, lb, tiles,
+                    num_sites);
+                ret = cudaPeekAtLastError() == cudaSuccess ? 0 : MSPB_ERR_CUDA;
+            }
+        }
+        if (ret == MSPB_ERR_CUDA) {
+            fprintf(stderr, "msprime_b200: mspb_site_rows_noalloc: %s\n", cudaGetErrorString(cudaGetLastError()));
+        }
+    }
+    if (previous != device) {
+        cudaSetDevice(previous);
+    }
+    return ret;
 }
