@@ -72,6 +72,28 @@ def log(*a):
     print(*a, file=sys.stderr, flush=True)
 
 
+INPUT_TEXT = "synthetic SMC' tree sequence (msprime_b200/csrc/treegen.c)"
+
+
+def config_dict(w, E, N, world):
+    """The ``config`` object of the JSON line: the same for the B200 arm and the reference arm."""
+    return {"workload": w["text"], "input": INPUT_TEXT, "edges": E, "nodes": N,
+            "l2": "inputs larger than L2 (edge columns + records > 126 MB), no flush",
+            "sharding": "whole genome on one GPU" if world == 1 else
+            f"{world} genome position slices (edges cut to the slice, Philox stream per rank), edges replicated; "
+            "two 8-integer NCCL all-gathers per overlay on the library's stream "
+            "(row / allele / byte bases stay on the device), each rank copies its slice to the host"}
+
+
+def overall_bytes(E, M, S, DB, AB, M0=0, kept_bytes=0):
+    """SURVEY.md section 8(d) A_bytes of one overlay (compulsory traffic: every input read once, every
+    output written once), with the offset columns as the survey counts them (two uint64 per row) and as
+    this library writes them (one uint32 per row; metadata offsets of a result without metadata stay zero)."""
+    common = E * (8 + 8 + 4 + 4) + E * (8 + 8) + M0 * (4 + 4 + 8) + kept_bytes + DB + AB
+    return {"survey": common + M * (4 + 4 + 4 + 8 + 8 + 8) + S * (8 + 8 + 8),
+            "as_written": common + M * (4 + 4 + 4 + 8 + 4) + S * (8 + 4)}
+
+
 def make_input(w):
     from msprime_b200 import synth
 
@@ -219,22 +241,39 @@ def cpu_kind():
     return "port", "port"
 
 
+def reference_sample(ts, w, expected, seconds):
+    """The bounded CPU sample both arms use: the genome prefix of the workload that takes one core about
+    ``seconds`` at the reference's measured ~1.7e5 mutations/s/core (config 5)."""
+    frac = min(1.0, max(1e-3, seconds * 1.7e5 / max(expected, 1.0)))
+    return genome_prefix(ts, frac)
+
+
+def expected_mutations(ts, w):
+    from msprime_b200 import validate
+
+    mp_, mr_ = rate_map(w, ts["sequence_length"])
+    lo, hi = time_window(w)
+    return validate.expected_new_mutations(ts, mp_, mr_, discrete=w["discrete"],
+                                           start_time=None if lo == -FMAX else lo, end_time=None if hi == FMAX else hi)
+
+
+CPU_SAMPLE_SECONDS = 9.0  # one-core seconds of reference work per process and pass, both arms
+
+
 def run_reference_arm(args, rank, world):
     """``--impl reference``: the reference's own CPU implementation on the host cores."""
     if rank != 0:
         return
     w = WORKLOADS[args.workload]
     kind, which = cpu_kind()
+    from oracle import oracle
+
+    oracle._load(which)  # in the parent, before any fork: the pool's workers inherit the mapped library
     ts = make_input(w)
+    E, N = len(ts["edges"]["left"]), len(ts["nodes"]["time"])
     cores = os.cpu_count() or 1
-    # bounded sample: about 120 s of single-core reference time spread over all steps
-    # (the reference runs config5 at ~1.7e5 mutations/s per core)
-    expected = float(((ts["edges"]["right"] - ts["edges"]["left"])
-                      * (ts["nodes"]["time"][ts["edges"]["parent"]] - ts["nodes"]["time"][ts["edges"]["child"]])).sum()
-                     ) * w["rate"]
-    per_step = 120.0 / max(1, args.steps + args.warmup)
-    frac = min(1.0, max(1e-3, per_step * 1.7e5 / max(expected, 1.0)))
-    sample, frac = genome_prefix(ts, frac)
+    expected = expected_mutations(ts, w)
+    sample, frac = reference_sample(ts, w, expected, CPU_SAMPLE_SECONDS)
     for i in range(args.warmup):
         cpu_reference_pass(sample, w, cores, 1000 + 100 * i, which)
     muts = 0
@@ -244,14 +283,21 @@ def run_reference_arm(args, rank, world):
         muts += m
         wall += t
     value = muts / wall
+    # the WHOLE workload once, one process (the reference is single-threaded): no extrapolation
+    full = None
+    if not args.no_full_config:
+        m, inner, t = cpu_reference_pass(ts, w, 1, 9000, which)
+        full = {"mutations": m, "seconds_mutgen_generate": inner, "seconds_wall": t, "value": m / t, "unit": UNIT,
+                "cores": 1}
     sample_txt = (f"genome prefix [0, {sample['sequence_length']:.0f}) = {frac:.4f} of the workload, "
                   f"{cores} processes x 1 overlay each per step, MT19937 seeds differ per process")
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * wall / max(1, args.steps),
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": w["text"], "input": "synthetic SMC' tree sequence (msprime_b200/csrc/treegen.c)"},
+        "config": config_dict(w, E, N, max(1, args.gpus)),
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample_txt},
+        "full_config_one_core": full,
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -328,9 +374,10 @@ def algorithmic_bytes(kernel, n):
         "p1_sites": R * (n["KB"] + 4),
         # key in (records of multi-mutation sites are a small fraction)
         "k4_resolve": R * n["KB"],
-        # key, val, site row, one 32 B sector per gathered Rec in; table rows + ragged bytes out
+        # key, slot, site row and the 16-byte record in (the record is gathered through the sorted slot: the
+        # 32-byte DRAM sector it sits in is traffic, not algorithm); table rows + ragged bytes out
         # (offset columns are uint32; all-zero metadata offsets are not rewritten)
-        "k5_emit": R * (n["KB"] + 4 + 4 + 32) + M * (4 + 4 + 4 + 8 + 4) + S * (8 + 4) + n["DB"] + n["AB"],
+        "k5_emit": R * (n["KB"] + 4 + 4 + 16) + M * (4 + 4 + 4 + 8 + 4) + S * (8 + 4) + n["DB"] + n["AB"],
     }
     return table.get(kernel)
 
@@ -503,8 +550,10 @@ def run_b200_arm(args, rank, local_rank, world):
     ev0.record(stream)
     muts = 0
     lib_ms = 0.0
+    last_timed_new = 0
     for i in range(args.steps):
-        muts += overlay(100 + i)
+        last_timed_new = overlay(100 + i)
+        muts += last_timed_new
         lib_ms += ctx.counts["device_ms"]
     ev1.record(stream)
     sync_all()
@@ -546,6 +595,61 @@ def run_b200_arm(args, rank, local_rank, world):
     e2e_value = e2e_total / (e2e_ms * 1e-3)
     h2d_total = reduce(float(h2d_bytes), dist.ReduceOp.SUM if world > 1 else None)
     d2h_total = reduce(float(d2h_bytes), dist.ReduceOp.SUM if world > 1 else None)
+    e2e_serial = {"value": e2e_value, "ms_per_step": e2e_ms / args.steps}
+
+    # ---- the same calls with several overlays in flight (N = 1): PCIe is full duplex and the copy engines
+    # run beside the kernels, so step i + 1 uploads while step i computes and step i - 1 downloads.  Every step
+    # still makes the whole call sequence (mspb_ctx_load_tables + mspb_generate + mspb_fetch, pinned host buffers in
+    # and out); the steps are dealt round-robin to `depth` contexts, each driven by its own host thread
+    # (the C calls release the GIL), and K steps are timed from the first call to the last return.
+    e2e_pipe = None
+    depth = max(1, args.e2e_depth)
+    if world == 1 and depth > 1:
+        ctxs = [ctx] + [_native.Context(local_rank) for _ in range(depth - 1)]
+        bufs = [out_bufs]
+        for _ in range(depth - 1):
+            b = {}
+            for name, dtype in _native._COLUMNS:
+                if name.endswith("_offset"):
+                    dtype = np.uint32
+                t, b[name] = pinned_empty(len(out_bufs[name]), dtype)
+                hold.append(t)
+            bufs.append(b)
+        for i in range(600, 600 + args.steps + depth):
+            params(i)
+        done = [0] * depth
+
+        def pipe_worker(k, first, count, barrier):
+            torch.cuda.set_device(local_rank)
+            barrier.wait()
+            for i in range(first + k, first + count, depth):
+                ctxs[k].load_tables(host_ts)
+                c = ctxs[k].generate(params(i))
+                ctxs[k].fetch(bufs[k])
+                done[k] += c["num_new_mutations"]
+
+        def run_pipe(first, count):
+            barrier = threading.Barrier(depth + 1)
+            ths = [threading.Thread(target=pipe_worker, args=(k, first, count, barrier)) for k in range(depth)]
+            for t in ths:
+                t.start()
+            torch.cuda.synchronize()
+            barrier.wait()
+            t0 = time.perf_counter()
+            for t in ths:
+                t.join()
+            torch.cuda.synchronize()
+            return time.perf_counter() - t0
+
+        run_pipe(600, depth)  # warm-up: every context sizes its buffers
+        for k in range(depth):
+            done[k] = 0
+        wall_p = run_pipe(600 + depth, args.steps)
+        e2e_pipe = {"value": sum(done) / wall_p, "ms_per_step": 1e3 * wall_p / args.steps, "depth": depth}
+        for c in ctxs[1:]:
+            c.close()
+        e2e_ms = 1e3 * wall_p
+        e2e_value = e2e_pipe["value"]
 
     if rank != 0:
         if world > 1:
@@ -587,6 +691,57 @@ def run_b200_arm(args, rank, local_rank, world):
                     "share_of_kernel_time": ms / total_kernel_ms, "algorithmic_bytes_per_launch": ab}
         break
     kernels = {k: {"launches": v[0], "ms_total": round(v[1], 4)} for k, v in kt[:12]}
+    if roofline is not None and roofline["kernel"] == "k5_emit":
+        # SURVEY.md section 8(d) counts K5's OUTPUT terms only; reported beside the figure above, which
+        # also charges the kernel's compulsory inputs (key, slot, site row, 16-byte record)
+        out_only = nn["M"] * (4 + 4 + 4 + 8 + 4) + nn["S"] * (8 + 4) + nn["DB"] + nn["AB"]
+        roofline["frac_output_terms_only"] = out_only / (roofline["avg_launch_ms"] * 1e-3) / 1e9 / peak
+    # whole overlay against the same peak: SURVEY.md section 8(d) A_bytes / device time per overlay (N = 1)
+    roofline_e2e = None
+    if world == 1:
+        kept_bytes = sum(int(np.asarray(ts[t][c]).nbytes) for t, c in (
+            ("sites", "ancestral_state"), ("mutations", "derived_state"))) if w.get("keep_layer") else 0
+        ob = overall_bytes(E, nn["M"], nn["S"], nn["DB"], nn["AB"],
+                           M0=len(ts["mutations"]["site"]) if w.get("keep_layer") else 0, kept_bytes=kept_bytes)
+        step_s = dev_ms / args.steps * 1e-3
+        roofline_e2e = {"bound": "hbm", "unit": "GB/s", "peak": peak,
+                        "a_bytes_survey": ob["survey"], "a_bytes_as_written": ob["as_written"],
+                        "achieved_survey": ob["survey"] / step_s / 1e9, "frac_survey": ob["survey"] / step_s / 1e9 / peak,
+                        "achieved_as_written": ob["as_written"] / step_s / 1e9,
+                        "frac_as_written": ob["as_written"] / step_s / 1e9 / peak}
+
+    # ---- the last timed overlay, checked OUTSIDE the timed region: valid tables, right count, right numbering
+    validated = None
+    if not args.no_validate:
+        from msprime_b200 import validate
+
+        t0 = time.perf_counter()
+        step = 100 + args.steps - 1  # seed of the last timed overlay
+        validated = {"step_seed": 1000 + step, "ok": False}
+        try:
+            if world == 1:
+                cnt = ctx.generate(params(step))
+                res = ctx.fetch()
+                lo, hi = time_window(w)
+                win = dict(start_time=None if lo == -FMAX else lo, end_time=None if hi == FMAX else hi)
+                M0 = len(ts["mutations"]["site"]) if w.get("keep_layer") else 0
+                validated["num_new_mutations"] = int(cnt["num_new_mutations"])
+                validated["same_count_as_timed_step"] = bool(cnt["num_new_mutations"] == last_timed_new)
+                validate.check_result(ts, res, discrete=w["discrete"], kept_mutations=M0, **win)
+                validated["check_result"] = True
+                mean, z = validate.check_count(ts, cnt["num_new_mutations"], map_pos, map_rate, discrete=w["discrete"],
+                                               **win)
+                validated["expected_new_mutations"] = mean
+                validated["count_z"] = z
+                if w["model"] == "infinite_alleles" and M0 == 0:
+                    validate.check_infinite_alleles_numbering(res, 0)
+                    validated["infinite_alleles_numbering"] = True
+                validated["ok"] = bool(validated["same_count_as_timed_step"])
+            else:
+                validated["skipped"] = "N > 1: each rank holds one slice; tests/test_gpu_multi.py checks the merged tables"
+        except AssertionError as e:
+            validated["error"] = f"{type(e).__name__}: {e}"[:300]
+        validated["seconds"] = round(time.perf_counter() - t0, 1)
 
     # ---- CPU baseline (N = 1 only): the compiled reference on all host cores
     cpu = None
@@ -597,10 +752,11 @@ def run_b200_arm(args, rank, local_rank, world):
             pass
     if world == 1 and not args.no_cpu_baseline:
         kind, which = cpu_kind()
+        from oracle import oracle
+
+        oracle._load(which)
         cores = os.cpu_count() or 1
-        expected = float(last["num_new_mutations"])
-        frac = min(1.0, max(1e-3, 12.0 * 1.7e5 / max(expected, 1.0)))
-        sample, frac = genome_prefix(ts, frac)
+        sample, frac = reference_sample(ts, w, expected_mutations(ts, w), CPU_SAMPLE_SECONDS)
         m, inner, wall_cpu = cpu_reference_pass(sample, w, cores, 7000, which)
         cpu = {"value": m / wall_cpu, "unit": UNIT, "cores": cores, "kind": kind,
                "sample": f"genome prefix [0, {sample['sequence_length']:.0f}) = {frac:.4f} of the workload; "
@@ -611,16 +767,16 @@ def run_b200_arm(args, rank, local_rank, world):
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": w["text"], "input": "synthetic SMC' tree sequence (msprime_b200/csrc/treegen.c)",
-                   "edges": E, "nodes": N, "mutations_per_step": total_muts / args.steps,
-                   "l2": "inputs larger than L2 (edge columns + records > 126 MB), no flush",
-                   "sharding": "whole genome on one GPU" if world == 1 else
-                   f"{world} genome position slices (edges cut to the slice, Philox stream per rank), edges replicated; "
-                   "two 8-integer NCCL all-gathers per overlay on the library's stream "
-                   "(row / allele / byte bases stay on the device), each rank copies its slice to the host"},
+        "config": config_dict(w, E, N, world),
+        "mutations_per_step": total_muts / args.steps,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d_total, "d2h_bytes_per_step": d2h_total,
                 "ms_per_step": e2e_ms / args.steps,
-                "path": "mspb_ctx_load_tables + mspb_generate + mspb_fetch, pinned host buffers" if world == 1 else
+                "one_at_a_time": e2e_serial,
+                "in_flight": e2e_pipe["depth"] if e2e_pipe else 1,
+                "path": ("mspb_ctx_load_tables + mspb_generate + mspb_fetch, pinned host buffers"
+                         + (f"; {e2e_pipe['depth']} overlays in flight (one context and host thread each): upload of "
+                            "step i + 1, kernels of step i and download of step i - 1 overlap" if e2e_pipe else ""))
+                if world == 1 else
                 "per rank: mspb_ctx_load_tables_begin (1 / world of the replicated tables over PCIe) / in-place NCCL "
                 "all-gather of the shares over NVLink / mspb_ctx_load_tables_end, then mspb_generate_begin / count "
                 "all-gather (NCCL) / mspb_generate_end / byte all-gather / mspb_shift_offsets + mspb_fetch of the "
@@ -628,6 +784,8 @@ def run_b200_arm(args, rank, local_rank, world):
         "gpu_launches": launches,
         "clocks": clocks,
         "roofline": roofline,
+        "roofline_e2e": roofline_e2e,
+        "validated": validated,
         "cpu_baseline": cpu,
         "phases_ms_last_step": {k: round(v, 4) for k, v in phases.items()},
         "kernels": kernels,
@@ -650,6 +808,11 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="config5", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-validate", action="store_true", help="skip the checks of the last timed overlay")
+    ap.add_argument("--e2e-depth", type=int, default=3,
+                    help="end-to-end overlays in flight at N = 1 (1 = one at a time)")
+    ap.add_argument("--no-full-config", action="store_true",
+                    help="reference arm: skip the single-process overlay of the whole workload")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
