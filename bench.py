@@ -743,6 +743,20 @@ def run_b200_arm(args, rank, local_rank, world):
             validated["error"] = f"{type(e).__name__}: {e}"[:300]
         validated["seconds"] = round(time.perf_counter() - t0, 1)
 
+    # ---- the consumers of the resident tables, outside every timed region: the sample-count
+    # index is built once per loaded tree sequence, the site AFS is one query per overlay
+    consumers_info = None
+    if world == 1 and not args.no_consumers:
+        try:
+            info = ctx.build_sample_index(ts["nodes"]["flags"])
+            cnt = ctx.generate(params(100 + args.steps - 1))
+            afs = ctx.site_afs()
+            consumers_info = {"sample_index": info, "site_afs_ms": round(ctx.afs_ms, 4),
+                              "mutations": int(cnt["num_mutations"]), "afs_total": int(afs.sum()),
+                              "afs_head": [int(v) for v in afs[:6]]}
+        except Exception as e:  # noqa: BLE001
+            consumers_info = {"error": f"{type(e).__name__}: {e}"[:200]}
+
     # ---- CPU baseline (N = 1 only): the compiled reference on all host cores
     cpu = None
     if affinity0 is not None:
@@ -786,6 +800,7 @@ def run_b200_arm(args, rank, local_rank, world):
         "roofline": roofline,
         "roofline_e2e": roofline_e2e,
         "validated": validated,
+        "consumers": consumers_info,
         "cpu_baseline": cpu,
         "phases_ms_last_step": {k: round(v, 4) for k, v in phases.items()},
         "kernels": kernels,
@@ -809,6 +824,7 @@ def main():
     ap.add_argument("--workload", default="config5", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-validate", action="store_true", help="skip the checks of the last timed overlay")
+    ap.add_argument("--no-consumers", action="store_true", help="skip the sample-count index / site AFS figures")
     ap.add_argument("--e2e-depth", type=int, default=3,
                     help="end-to-end overlays in flight at N = 1 (1 = one at a time)")
     ap.add_argument("--no-full-config", action="store_true",

@@ -274,6 +274,24 @@ int mspb_sim_mutations(int device, const mspb_tables_t *tables, const mspb_param
     mspb_counts_t *counts, mspb_columns_t *out);
 void mspb_columns_free(mspb_columns_t *cols);
 
+/* Consumers of the resident tables on the device: what the reference's users compute
+ * next from the tables this path writes (verification.py:6008-6013).
+ *   mspb_ctx_build_sample_index  <- the num_samples bookkeeping of tskit's tree sweep (tsk_tree_t.num_samples,
+ *                                   git-submodules/tskit/c/tskit/trees.c), as per-node step functions over the
+ *                                   genome, built once per loaded tree sequence.  node_flags: tskit nodes.flags
+ *                                   (host, num_nodes entries; bit 0 = TSK_NODE_IS_SAMPLE).
+ *   mspb_samples_below           <- tsk_tree_get_num_samples(tree covering the site, mutation's node) for every
+ *                                   mutation row of the result of the last mspb_generate (host, num_mutations).
+ *   mspb_site_afs                <- tsk_treeseq_allele_frequency_spectrum with TSK_STAT_SITE | TSK_STAT_POLARISED,
+ *                                   one sample set (all samples), no span normalisation (trees.c:3816, 3527-3540):
+ *                                   afs[k] = derived alleles (byte strings other than the site's ancestral state)
+ *                                   carried by exactly k samples, 0 < k < num_samples; afs_len = num_samples + 1.
+ * Results of unsliced calls only (a genome slice of a sharded call carries global row ids). */
+int mspb_ctx_build_sample_index(mspb_ctx_t *ctx, const uint32_t *node_flags, uint64_t *num_samples,
+    uint64_t *num_levels, uint64_t *num_steps, double *build_ms);
+int mspb_samples_below(mspb_ctx_t *ctx, uint32_t *below);
+int mspb_site_afs(mspb_ctx_t *ctx, uint64_t *afs, uint64_t afs_len, double *device_ms);
+
 /* Allocation-free site numbering.  This entry point has NO counterpart in the reference: it was added
  * for callers that cannot call cudaMalloc (code under CUDA graph
  * capture, tight serving loops, harnesses that forbid it).  It is the site-numbering step of the overlay

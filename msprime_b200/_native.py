@@ -114,7 +114,8 @@ EXPORTED_SYMBOLS = [
     "mspb_generate_begin", "mspb_generate_end", "mspb_shift_offsets",
     "mspb_exchange_buffers", "mspb_exchange_post_counts", "mspb_generate_end_device",
     "mspb_generate_finish_device", "mspb_last_fetch_bytes", "mspb_ctx_load_tables_begin",
-    "mspb_ctx_load_tables_end", "mspb_site_rows_noalloc",
+    "mspb_ctx_load_tables_end", "mspb_site_rows_noalloc", "mspb_ctx_build_sample_index", "mspb_samples_below",
+    "mspb_site_afs",
 ]
 
 EXCHANGE_WORDS = 8  # MSPB_EXCHANGE_WORDS
@@ -183,6 +184,10 @@ def lib():
         L.mspb_columns_free.argtypes = [C.POINTER(_Columns)]
         L.mspb_columns_free.restype = None
         L.mspb_site_rows_noalloc.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]
+        L.mspb_ctx_build_sample_index.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64),
+                                                  C.POINTER(C.c_uint64), C.POINTER(C.c_double)]
+        L.mspb_samples_below.argtypes = [C.c_void_p, C.c_void_p]
+        L.mspb_site_afs.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_double)]
         _lib = L
     return _lib
 
@@ -475,6 +480,37 @@ class Context:
             else:
                 res[tbl][col] = torch.as_tensor(_DeviceArray(ptrs[name], n, typestr[dtype]), device=dev)
         return res
+
+    # ---- consumers of the resident result
+    def build_sample_index(self, node_flags):
+        """Builds, for the loaded tree sequence, the step functions below(u, x) = number of samples under
+        node ``u`` in the tree covering ``x`` (``node_flags``: tskit's ``nodes.flags``, bit 0 = sample).
+        Once per ``load_tables``; returns sizes and the device time of the build."""
+        flags = _c(node_flags, np.uint32)
+        ns, nl, nst, ms = C.c_uint64(), C.c_uint64(), C.c_uint64(), C.c_double()
+        check(lib().mspb_ctx_build_sample_index(self._h, C.c_void_p(_p(flags) if flags.size else None), C.byref(ns),
+                                                C.byref(nl), C.byref(nst), C.byref(ms)))
+        self.sample_index = {"num_samples": int(ns.value), "levels": int(nl.value), "steps": int(nst.value),
+                             "build_ms": float(ms.value)}
+        return self.sample_index
+
+    def samples_below(self):
+        """Samples below every mutation row of the resident result (``tsk_tree_get_num_samples`` of the
+        mutation's node in the tree covering its site)."""
+        out = np.empty(self.counts["num_mutations"], dtype=np.uint32)
+        check(lib().mspb_samples_below(self._h, C.c_void_p(_p(out) if out.size else None) if out.size else _p(np.empty(1, np.uint32))))
+        return out
+
+    def site_afs(self):
+        """Polarised, un-normalised site allele frequency spectrum of all samples of the resident result
+        (``tsk_treeseq_allele_frequency_spectrum``, mode "site", polarised, span_normalise=False): a
+        uint64 array of ``num_samples + 1`` counts.  ``self.afs_ms`` is the device time of the query."""
+        n = self.sample_index["num_samples"]
+        out = np.zeros(n + 1, dtype=np.uint64)
+        ms = C.c_double()
+        check(lib().mspb_site_afs(self._h, _p(out), n + 1, C.byref(ms)))
+        self.afs_ms = float(ms.value)
+        return out
 
     def kernel_launches(self) -> int:
         return int(lib().mspb_kernel_launches(self._h))

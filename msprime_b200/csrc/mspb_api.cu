@@ -13,6 +13,7 @@
 
 #include "../../include/msprime_b200.h"
 #include "kernels.cuh"
+#include "consumers.cuh"
 
 using namespace mspb;
 
@@ -157,6 +158,19 @@ struct mspb_ctx {
     const void *md_zero_site_ptr = nullptr, *md_zero_mut_ptr = nullptr;
     uint64_t md_zero_site_bytes = 0, md_zero_mut_bytes = 0;
     uint64_t last_fetch_bytes = 0; // device-to-host bytes of the last mspb_fetch
+    // sample-count step functions of the loaded tree sequence (consumers.cuh), built on request
+    struct {
+        bool valid = false;
+        uint32_t num_samples = 0, num_x = 0, levels = 0;
+        uint64_t steps = 0; // entries of fx / fv in use
+        DBuf<uint32_t> is_sample, foff, fcnt;
+        DBuf<uint64_t> xs;
+        uint32_t *fx = nullptr, *fv = nullptr;
+        size_t fcap = 0;
+        double build_ms = 0;
+    } sidx;
+    DBuf<uint32_t> q_below, q_own; // per mutation row of the resident result
+    DBuf<unsigned long long> q_afs;
 };
 
 static const char *const PHASE_NAMES[MSPB_NUM_PHASES] = { "params+kept", "K1 count+scan", "K2 place", "K3 sort",
@@ -363,7 +377,14 @@ extern "C" void mspb_ctx_destroy(mspb_ctx_t *ctx)
     REL(o_site_pos); REL(o_mut_time); REL(o_site_anc); REL(o_site_md); REL(o_mut_der); REL(o_mut_md);
     REL(o_site_anc_off); REL(o_site_md_off); REL(o_mut_der_off); REL(o_mut_md_off);
     REL(o_mut_site); REL(o_mut_node); REL(o_mut_parent);
+    REL(sidx.is_sample); REL(sidx.foff); REL(sidx.fcnt); REL(sidx.xs); REL(q_below); REL(q_own); REL(q_afs);
 #undef REL
+    if (ctx->sidx.fx != nullptr) {
+        cudaFree(ctx->sidx.fx);
+    }
+    if (ctx->sidx.fv != nullptr) {
+        cudaFree(ctx->sidx.fv);
+    }
     ctx->log.release();
     if (ctx->host != nullptr) {
         cudaFreeHost(ctx->host);
@@ -629,6 +650,7 @@ int tables_prepare(mspb_ctx_t *ctx, const mspb_tables_t *t)
     ctx->tables_loaded = false;
     ctx->tables_pending = false;
     ctx->generated = false;
+    ctx->sidx.valid = false;
     if (!std::isfinite(t->sequence_length) || t->sequence_length <= 0) {
         /* mutgen_alloc rejects L <= 0 before anything else (lib/mutgen.c:760) */
         return MSPB_ERR_BAD_PARAM_VALUE;
@@ -2435,6 +2457,349 @@ extern "C" int mspb_selftest_sort(mspb_ctx_t *ctx, uint64_t n, int key_bytes, ui
         return selftest_sort_impl<uint32_t>(ctx, n, key_mask & 0xffffffffull, seed, measure_bits != 0, passes);
     }
     return selftest_sort_impl<uint64_t>(ctx, n, key_mask, seed, measure_bits != 0, passes);
+}
+
+// ---------------------------------------------------------------- consumers of the tables
+namespace {
+
+// room for `need` steps in fx / fv, keeping what is there
+int sidx_reserve(mspb_ctx *ctx, size_t need)
+{
+    if (need <= ctx->sidx.fcap) {
+        return 0;
+    }
+    const size_t cap = need + need / 2 + 1024;
+    uint32_t *nx = nullptr, *nv = nullptr;
+    if (cudaMalloc((void **) &nx, cap * sizeof(uint32_t)) != cudaSuccess
+        || cudaMalloc((void **) &nv, cap * sizeof(uint32_t)) != cudaSuccess) {
+        cudaGetLastError();
+        if (nx != nullptr) {
+            cudaFree(nx);
+        }
+        return MSPB_ERR_NO_MEMORY;
+    }
+    if (ctx->sidx.steps > 0) {
+        CUDA_OK(cudaMemcpyAsync(nx, ctx->sidx.fx, ctx->sidx.steps * sizeof(uint32_t), cudaMemcpyDeviceToDevice, ctx->stream));
+        CUDA_OK(cudaMemcpyAsync(nv, ctx->sidx.fv, ctx->sidx.steps * sizeof(uint32_t), cudaMemcpyDeviceToDevice, ctx->stream));
+        CUDA_OK(cudaStreamSynchronize(ctx->stream));
+    }
+    if (ctx->sidx.fx != nullptr) {
+        cudaFree(ctx->sidx.fx);
+        cudaFree(ctx->sidx.fv);
+    }
+    ctx->sidx.fx = nx;
+    ctx->sidx.fv = nv;
+    ctx->sidx.fcap = cap;
+    return 0;
+}
+
+SampleFnView sidx_view(const mspb_ctx *ctx)
+{
+    SampleFnView v;
+    v.num_nodes = ctx->N;
+    v.is_sample = ctx->sidx.is_sample.p;
+    v.foff = ctx->sidx.foff.p;
+    v.fcnt = ctx->sidx.fcnt.p;
+    v.fx = ctx->sidx.fx;
+    v.fv = ctx->sidx.fv;
+    v.xs = ctx->sidx.xs.p;
+    v.num_x = ctx->sidx.num_x;
+    return v;
+}
+
+uint64_t bits_mask(uint64_t max_value)
+{
+    uint64_t m = 1;
+    while (m <= max_value && m != 0) {
+        m <<= 1;
+    }
+    return m - 1; // (m == 0 after a wrap: all ones)
+}
+
+struct SidxTemps {
+    DBuf<uint32_t> level, lrank, rrank, eorder, count, first, offset, delta, before, kept_before, tile_sums, small;
+    ~SidxTemps()
+    {
+        level.release(); lrank.release(); rrank.release(); eorder.release(); count.release(); first.release();
+        offset.release(); delta.release(); before.release(); kept_before.release(); tile_sums.release(); small.release();
+    }
+};
+
+int build_sample_index(mspb_ctx *ctx, const uint32_t *node_flags)
+{
+    cudaStream_t st = ctx->stream;
+    const uint64_t N = ctx->N, E = ctx->E;
+    auto &si = ctx->sidx;
+    si.valid = false;
+    si.steps = 0;
+    si.levels = 0;
+    SidxTemps t;
+    cudaEvent_t e0 = ctx->ev[0], e1 = ctx->ev[1];
+    CUDA_OK(cudaEventRecord(e0, st));
+    TRY(si.is_sample.ensure(N + 1));
+    TRY(si.foff.ensure(N + 1));
+    TRY(si.fcnt.ensure(N + 1));
+    TRY(t.small.ensure(8));
+    TRY(t.level.ensure(N + 1));
+    CUDA_OK(cudaMemsetAsync(t.small.p, 0, 8 * sizeof(uint32_t), st));
+    CUDA_OK(cudaMemsetAsync(si.fcnt.p, 0, (N + 1) * sizeof(uint32_t), st));
+    CUDA_OK(cudaMemsetAsync(si.foff.p, 0, (N + 1) * sizeof(uint32_t), st));
+    CUDA_OK(cudaMemsetAsync(t.level.p, 0, (N + 1) * sizeof(uint32_t), st));
+    // node flags arrive in t.level's neighbour (a temporary of N words)
+    TRY(t.lrank.ensure((N > E ? N : E) + 1));
+    if (N > 0) {
+        CUDA_OK(cudaMemcpyAsync(t.lrank.p, node_flags, N * sizeof(uint32_t), cudaMemcpyHostToDevice, st));
+        MSPB_LAUNCH(ctx->log, "sf_flags",
+            sf_flags_kernel<<<grid_for(N, 256), 256, 0, st>>>(N, t.lrank.p, si.is_sample.p, t.small.p));
+    }
+    uint32_t h_small[8] = { 0 };
+    CUDA_OK(cudaMemcpyAsync(h_small, t.small.p, sizeof(h_small), cudaMemcpyDeviceToHost, st));
+    CUDA_OK(cudaStreamSynchronize(st)); // (also: the caller's flags are no longer read)
+    si.num_samples = h_small[0];
+    si.num_x = 0;
+    TRY(si.xs.ensure(2 * E + 2));
+    TRY(sidx_reserve(ctx, 5 * E + 1024));
+    if (E > 0) {
+        const TreeSeqView ts = make_ts_view(ctx);
+        // ---- the distinct edge end points, ascending
+        TRY(ensure_sort_buffers(ctx, 2 * E, false, true));
+        RadixSortBuffers<uint64_t> sb = sort_buffers64(ctx);
+        MSPB_LAUNCH(ctx->log, "sf_endpoint_keys",
+            sf_endpoint_keys_kernel<<<grid_for(E, 256), 256, 0, st>>>(ts, sb.keys[0]));
+        int cur = device_radix_sort<uint64_t>(sb, 2 * E, 0, true, st, ctx->log, nullptr);
+        TRY(t.before.ensure(2 * E + 1));
+        TRY(t.tile_sums.ensure(scan_num_tiles(2 * E) + 2));
+        SfHead head { sb.keys[cur] };
+        device_exclusive_scan<uint32_t, SfHead>(ctx->log, 2 * E, head, t.before.p, t.tile_sums.p, t.small.p + 1, st);
+        MSPB_LAUNCH(ctx->log, "sf_unique",
+            sf_unique_kernel<<<grid_for(2 * E, 256), 256, 0, st>>>(2 * E, sb.keys[cur], t.before.p, si.xs.p));
+        CUDA_OK(cudaMemcpyAsync(h_small, t.small.p, sizeof(h_small), cudaMemcpyDeviceToHost, st));
+        CUDA_OK(cudaStreamSynchronize(st));
+        si.num_x = h_small[1];
+        TRY(t.rrank.ensure(E + 1));
+        MSPB_LAUNCH(ctx->log, "sf_edge_ranks",
+            sf_edge_ranks_kernel<<<grid_for(E, 256), 256, 0, st>>>(ts, si.xs.p, si.num_x, t.lrank.p, t.rrank.p));
+        // ---- levels: relax until nothing changes (one round per level of the deepest node at most)
+        uint32_t rounds = 0;
+        for (;;) {
+            CUDA_OK(cudaMemsetAsync(t.small.p + 2, 0, sizeof(uint32_t), st));
+            // a few rounds per wait: the flag is only ever set
+            for (int k = 0; k < 4; k++) {
+                MSPB_LAUNCH(ctx->log, "sf_relax_levels",
+                    sf_relax_levels_kernel<<<grid_for(E, 256), 256, 0, st>>>(ts, t.level.p, t.small.p + 2));
+            }
+            rounds += 4;
+            CUDA_OK(cudaMemcpyAsync(h_small, t.small.p, sizeof(h_small), cudaMemcpyDeviceToHost, st));
+            CUDA_OK(cudaStreamSynchronize(st));
+            if (h_small[2] == 0u) {
+                break;
+            }
+            if (rounds > N + 8) {
+                return MSPB_ERR_GENERIC; // cannot happen for edges whose parents are older than their children
+            }
+        }
+        // ---- edges by (level of the parent, parent)
+        const uint32_t max_levels = rounds + 2;
+        DBuf<uint32_t> level_count;
+        TRY(level_count.ensure(max_levels + 1));
+        struct Rel {
+            DBuf<uint32_t> &b;
+            ~Rel() { b.release(); }
+        } rel { level_count };
+        CUDA_OK(cudaMemsetAsync(level_count.p, 0, (max_levels + 1) * sizeof(uint32_t), st));
+        TRY(ensure_sort_buffers(ctx, E, false, true));
+        sb = sort_buffers64(ctx);
+        MSPB_LAUNCH(ctx->log, "sf_edge_level_keys",
+            sf_edge_level_keys_kernel<<<grid_for(E, 256), 256, 0, st>>>(ts, t.level.p, sb.keys[0], level_count.p, max_levels));
+        cur = device_radix_sort<uint64_t>(sb, E, ((uint64_t) bits_mask(max_levels) << 32) | bits_mask(N), true, st,
+            ctx->log, nullptr);
+        TRY(t.eorder.ensure(E + 1));
+        CUDA_OK(cudaMemcpyAsync(t.eorder.p, sb.vals[cur], E * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
+        std::vector<uint32_t> h_count(max_levels + 1);
+        CUDA_OK(cudaMemcpyAsync(h_count.data(), level_count.p, (max_levels + 1) * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+        CUDA_OK(cudaStreamSynchronize(st));
+        // ---- one level at a time (level 0 has no child edges: those nodes are constant)
+        const uint64_t key_bits = ((uint64_t) bits_mask(N) << 32) | bits_mask(si.num_x);
+        uint64_t a = h_count[0]; // (no edge has a parent of level 0)
+        for (uint32_t lv = 1; lv <= max_levels; lv++) {
+            const uint64_t n_e = h_count[lv];
+            if (n_e == 0) {
+                continue;
+            }
+            si.levels = lv + 1;
+            SfLevelEdges le { ts, t.eorder.p + a, t.lrank.p, t.rrank.p };
+            a += n_e;
+            TRY(t.count.ensure(n_e + 1));
+            TRY(t.first.ensure(n_e + 1));
+            TRY(t.offset.ensure(n_e + 1));
+            TRY(t.tile_sums.ensure(scan_num_tiles(n_e) + 2));
+            MSPB_LAUNCH(ctx->log, "sf_count_events",
+                sf_count_events_kernel<<<grid_for(n_e, 256), 256, 0, st>>>(le, n_e, sidx_view(ctx), t.count.p, t.first.p));
+            device_exclusive_scan<uint32_t, SfArray>(ctx->log, n_e, SfArray { t.count.p }, t.offset.p, t.tile_sums.p,
+                t.small.p + 3, st);
+            CUDA_OK(cudaMemcpyAsync(h_small, t.small.p, sizeof(h_small), cudaMemcpyDeviceToHost, st));
+            CUDA_OK(cudaStreamSynchronize(st));
+            const uint64_t T = h_small[3];
+            if (T > RS_MAX_N) {
+                return MSPB_ERR_TOO_MANY_ROWS;
+            }
+            TRY(ensure_sort_buffers(ctx, T, false, true));
+            sb = sort_buffers64(ctx);
+            TRY(t.delta.ensure(T + 1));
+            TRY(t.before.ensure(T + 1));
+            TRY(t.kept_before.ensure(T + 1));
+            TRY(t.tile_sums.ensure(scan_num_tiles(T) + 2));
+            MSPB_LAUNCH(ctx->log, "sf_emit_events",
+                sf_emit_events_kernel<<<grid_for(n_e, 256), 256, 0, st>>>(le, n_e, sidx_view(ctx), t.count.p, t.first.p,
+                    t.offset.p, sb.keys[0], t.delta.p));
+            cur = device_radix_sort<uint64_t>(sb, T, key_bits, true, st, ctx->log, nullptr);
+            device_exclusive_scan<uint32_t, SfGather>(ctx->log, T, SfGather { t.delta.p, sb.vals[cur] }, t.before.p,
+                t.tile_sums.p, nullptr, st);
+            device_exclusive_scan<uint32_t, SfKeep>(ctx->log, T, SfKeep { sb.keys[cur], T }, t.kept_before.p,
+                t.tile_sums.p, t.small.p + 4, st);
+            CUDA_OK(cudaMemcpyAsync(h_small, t.small.p, sizeof(h_small), cudaMemcpyDeviceToHost, st));
+            CUDA_OK(cudaStreamSynchronize(st));
+            const uint64_t K = h_small[4];
+            if (si.steps + K > 0xfffffff0ull) {
+                return MSPB_ERR_TOO_MANY_ROWS;
+            }
+            TRY(sidx_reserve(ctx, si.steps + K));
+            MSPB_LAUNCH(ctx->log, "sf_store_steps",
+                sf_store_steps_kernel<<<grid_for(T, 256), 256, 0, st>>>(T, sb.keys[cur], t.delta.p, sb.vals[cur],
+                    t.before.p, t.kept_before.p, si.is_sample.p, (uint32_t) si.steps, si.fx, si.fv, si.foff.p,
+                    si.fcnt.p));
+            si.steps += K;
+        }
+    }
+    CUDA_OK(cudaEventRecord(e1, st));
+    CUDA_OK(cudaStreamSynchronize(st));
+    CUDA_OK(cudaGetLastError());
+    ctx->log.collect();
+    float ms = 0;
+    cudaEventElapsedTime(&ms, e0, e1);
+    si.build_ms = ms;
+    si.valid = true;
+    return 0;
+}
+
+// below / own of every mutation row of the resident result
+int query_below(mspb_ctx *ctx)
+{
+    cudaStream_t st = ctx->stream;
+    if (!ctx->generated) {
+        return MSPB_ERR_NOT_GENERATED;
+    }
+    if (!ctx->sidx.valid) {
+        return MSPB_ERR_TABLES_NOT_LOADED;
+    }
+    if (ctx->pending.out.site_base != 0 || ctx->pending.out.mut_base != 0 || ctx->pending.out.dev_bases != nullptr) {
+        return MSPB_ERR_BAD_PARAM_VALUE; // rows of one genome slice of a sharded call: ids are not local
+    }
+    const uint64_t M = ctx->counts.num_mutations;
+    TRY(ctx->q_below.ensure(M + 1));
+    TRY(ctx->q_own.ensure(M + 1));
+    if (M > 0) {
+        MSPB_LAUNCH(ctx->log, "sf_below",
+            sf_below_kernel<<<grid_for(M, 256), 256, 0, st>>>(M, ctx->o_mut_site.p, ctx->o_mut_node.p, ctx->o_site_pos.p,
+                sidx_view(ctx), ctx->q_below.p, ctx->q_own.p));
+        MSPB_LAUNCH(ctx->log, "sf_own",
+            sf_own_kernel<<<grid_for(M, 256), 256, 0, st>>>(M, ctx->o_mut_parent.p, ctx->q_below.p, ctx->q_own.p));
+    }
+    return 0;
+}
+
+} // namespace
+
+extern "C" int mspb_ctx_build_sample_index(mspb_ctx_t *ctx, const uint32_t *node_flags, uint64_t *num_samples,
+    uint64_t *num_levels, uint64_t *num_steps, double *build_ms)
+{
+    if (ctx == nullptr || (node_flags == nullptr && ctx->N > 0)) {
+        return MSPB_ERR_BAD_PARAM_VALUE;
+    }
+    if (!ctx->tables_loaded) {
+        return MSPB_ERR_TABLES_NOT_LOADED;
+    }
+    if (ctx->pending.valid) {
+        return MSPB_ERR_BAD_PARAM_VALUE; // between mspb_generate_begin and _end: the sort buffers are in use
+    }
+    CUDA_OK(cudaSetDevice(ctx->device));
+    const int ret = build_sample_index(ctx, node_flags);
+    if (ret != 0) {
+        cudaStreamSynchronize(ctx->stream);
+        ctx->log.collect();
+        return ret;
+    }
+    if (num_samples != nullptr) {
+        *num_samples = ctx->sidx.num_samples;
+    }
+    if (num_levels != nullptr) {
+        *num_levels = ctx->sidx.levels;
+    }
+    if (num_steps != nullptr) {
+        *num_steps = ctx->sidx.steps;
+    }
+    if (build_ms != nullptr) {
+        *build_ms = ctx->sidx.build_ms;
+    }
+    return 0;
+}
+
+extern "C" int mspb_samples_below(mspb_ctx_t *ctx, uint32_t *below)
+{
+    if (ctx == nullptr || below == nullptr) {
+        return MSPB_ERR_BAD_PARAM_VALUE;
+    }
+    CUDA_OK(cudaSetDevice(ctx->device));
+    TRY(query_below(ctx));
+    const uint64_t M = ctx->counts.num_mutations;
+    if (M > 0) {
+        CUDA_OK(cudaMemcpyAsync(below, ctx->q_below.p, M * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    CUDA_OK(cudaStreamSynchronize(ctx->stream));
+    CUDA_OK(cudaGetLastError());
+    ctx->log.collect();
+    return 0;
+}
+
+extern "C" int mspb_site_afs(mspb_ctx_t *ctx, uint64_t *afs, uint64_t afs_len, double *device_ms)
+{
+    if (ctx == nullptr || afs == nullptr) {
+        return MSPB_ERR_BAD_PARAM_VALUE;
+    }
+    CUDA_OK(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    if (ctx->sidx.valid && afs_len != (uint64_t) ctx->sidx.num_samples + 1) {
+        return MSPB_ERR_BAD_PARAM_VALUE;
+    }
+    cudaEvent_t e0 = ctx->ev[0], e1 = ctx->ev[1];
+    CUDA_OK(cudaEventRecord(e0, st));
+    TRY(query_below(ctx));
+    const uint64_t M = ctx->counts.num_mutations;
+    TRY(ctx->q_afs.ensure(afs_len + 1));
+    CUDA_OK(cudaMemsetAsync(ctx->q_afs.p, 0, afs_len * sizeof(unsigned long long), st));
+    if (M > 0) {
+        const unsigned afs_grid = grid_for(M, 256) < 148u * 8u ? grid_for(M, 256) : 148u * 8u;
+        if (ctx->counts.offset_bytes == 4) {
+            MSPB_LAUNCH(ctx->log, "sf_afs",
+                sf_afs_kernel<true><<<afs_grid, 256, 0, st>>>(M, ctx->o_mut_site.p, ctx->q_own.p, ctx->o_mut_der.p,
+                    ctx->o_mut_der_off.p, ctx->o_site_anc.p, ctx->o_site_anc_off.p, ctx->sidx.num_samples, ctx->q_afs.p));
+        } else {
+            MSPB_LAUNCH(ctx->log, "sf_afs",
+                sf_afs_kernel<false><<<afs_grid, 256, 0, st>>>(M, ctx->o_mut_site.p, ctx->q_own.p, ctx->o_mut_der.p,
+                    ctx->o_mut_der_off.p, ctx->o_site_anc.p, ctx->o_site_anc_off.p, ctx->sidx.num_samples, ctx->q_afs.p));
+        }
+    }
+    CUDA_OK(cudaEventRecord(e1, st));
+    CUDA_OK(cudaMemcpyAsync(afs, ctx->q_afs.p, afs_len * sizeof(uint64_t), cudaMemcpyDeviceToHost, st));
+    CUDA_OK(cudaStreamSynchronize(st));
+    CUDA_OK(cudaGetLastError());
+    ctx->log.collect();
+    if (device_ms != nullptr) {
+        float ms = 0;
+        cudaEventElapsedTime(&ms, e0, e1);
+        *device_ms = ms;
+    }
+    return 0;
 }
 
 // ---------------------------------------------------------------- allocation-free entry point
