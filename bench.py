@@ -80,7 +80,8 @@ def config_dict(w, E, N, world):
     return {"workload": w["text"], "input": INPUT_TEXT, "edges": E, "nodes": N,
             "l2": "inputs larger than L2 (edge columns + records > 126 MB), no flush",
             "sharding": "whole genome on one GPU" if world == 1 else
-            f"{world} genome position slices (edges cut to the slice, Philox stream per rank), edges replicated; "
+            f"{world} genome position slices of equal expected mutation mass (edges cut to the slice, Philox stream per "
+            "rank), edges replicated; "
             "two 8-integer NCCL all-gathers per overlay on the library's stream "
             "(row / allele / byte bases stay on the device), each rank copies its slice to the host"}
 
@@ -401,10 +402,6 @@ def pinned_empty(n, dtype):
     return t, (a.view(dtype) if dtype in (np.uint64, np.uint32) else a)
 
 
-def slice_cuts(L, world):
-    return [float(np.floor(L * r / world)) for r in range(world)] + [float(L)]
-
-
 def bind_near_gpu(index):
     """Best effort: run this process on the CPUs of the NUMA node its GPU hangs off, so that the
     pinned host buffers (first touched below) sit on that node and the DMA does not cross sockets.
@@ -425,6 +422,58 @@ def bind_near_gpu(index):
         return original, "unchanged (the GPU's CPUs are all of this process's CPUs)"
     except Exception as e:  # noqa: BLE001
         return original, f"unchanged ({type(e).__name__})"
+
+
+def python_call_timing(ts, w, map_pos, map_rate, device):
+    """Wall time of ``msprime_b200.sim_mutations`` on the bench workload (TreeSequence in, TreeSequence out), and of
+    its steps: table dict, upload + index, overlay, download into fresh numpy arrays, result object.  tskit is
+    not installed on the GPU box, so the tree sequence is the package's own stand-in for it (same dict protocol;
+    with real tskit the call adds ``TableCollection.fromdict`` + ``tree_sequence()``, msprime/mutations.py:1699-1702)."""
+    import msprime_b200 as msp
+    from msprime_b200 import intervals, mutations, tables as mtables
+
+    name = w["model"]
+    model = (mutations.InfiniteAlleles() if name == "infinite_alleles" else mutations.JC69() if name == "jc69" else
+             mutations.BinaryMutationModel() if name == "binary" else mutations.HKY(kappa=2) if name == "hky" else
+             mutations.GTR(relative_rates=[1, 2, 1, 1, 2, 1], equilibrium_frequencies=[0.3, 0.2, 0.2, 0.3]))
+    rate = w["rate"] if len(map_rate) == 1 else intervals.RateMap(position=map_pos, rate=map_rate)
+    lo, hi = time_window(w)
+    kw = dict(rate=rate, model=model, discrete_genome=w["discrete"], keep=bool(w.get("keep_layer")),
+              start_time=None if lo == -FMAX else lo, end_time=None if hi == FMAX else hi, device=device)
+    tsobj = mtables.TableCollection.fromdict(ts).tree_sequence()
+    walls = []
+    out = None
+    for i in range(3):  # the first call creates the context and sizes its buffers
+        t0 = time.perf_counter()
+        out = msp.sim_mutations(tsobj, random_seed=11 + i, **kw)
+        walls.append(time.perf_counter() - t0)
+    new = out.num_mutations - (len(ts["mutations"]["site"]) if w.get("keep_layer") else 0)
+    # the same steps by hand on the call's own context
+    ctx = mutations._context(device)
+    steps = {}
+    t0 = time.perf_counter()
+    d, kind = mtables.from_tree_sequence(tsobj)
+    steps["tables_dict"] = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    ctx.load_tables(d)
+    steps["load_tables_pageable"] = time.perf_counter() - t0
+    from msprime_b200 import _native
+
+    prm = _native.Params(map_position=map_pos, map_rate=map_rate, model=model._native(), discrete_genome=w["discrete"],
+                         keep=bool(w.get("keep_layer")), start_time=lo, end_time=hi, seed=99)
+    t0 = time.perf_counter()
+    ctx.generate(prm)
+    steps["generate"] = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    res = ctx.fetch()
+    steps["fetch_pageable"] = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    mtables.to_tree_sequence(mutations._merge_result(d, res), kind, None)
+    steps["result_object"] = time.perf_counter() - t0
+    return {"wall_ms_first_call": round(1e3 * walls[0], 2), "wall_ms": round(1e3 * min(walls[1:]), 2),
+            "value": new / min(walls[1:]), "unit": UNIT,
+            "steps_ms": {k: round(1e3 * v, 2) for k, v in steps.items()},
+            "tree_sequence": "msprime_b200.tables stand-in (tskit is not installed here)"}
 
 
 def run_b200_arm(args, rank, local_rank, world):
@@ -452,7 +501,11 @@ def run_b200_arm(args, rank, local_rank, world):
     affinity0, binding = bind_near_gpu(local_rank)
     log(f"[bench] rank {rank}: cpu binding {binding}")
     L = float(ts["sequence_length"])
-    cuts = slice_cuts(L, world)
+    map_pos, map_rate = rate_map(w, L)
+    # slices of equal expected mutation mass (branch length x rate), not of equal length
+    lo_t, hi_t = time_window(w)
+    cuts = sharding.balanced_cuts(ts, map_pos, map_rate, world, discrete_genome=w["discrete"],
+                                  start_time=None if lo_t == -FMAX else lo_t, end_time=None if hi_t == FMAX else hi_t)
     sl, sr = (0.0, 0.0) if world == 1 else (cuts[rank], cuts[rank + 1])
 
     # host inputs in pinned memory (what a caller hands to the C ABI)
@@ -473,8 +526,6 @@ def run_b200_arm(args, rank, local_rank, world):
 
     ctx = _native.Context(local_rank)
     stream = torch.cuda.ExternalStream(ctx.stream(), device=torch.device("cuda", local_rank))
-
-    map_pos, map_rate = rate_map(w, L)
 
     pcache = {}
 
@@ -757,6 +808,15 @@ def run_b200_arm(args, rank, local_rank, world):
         except Exception as e:  # noqa: BLE001
             consumers_info = {"error": f"{type(e).__name__}: {e}"[:200]}
 
+    # ---- the call the north star names, msprime_b200.sim_mutations(tree_sequence, ...) -> tree sequence, with the
+    # caller's plain (pageable) numpy columns in and fresh numpy columns out; wall time, and the same steps one by one
+    e2e_python = None
+    if world == 1 and not args.no_e2e_python:
+        try:
+            e2e_python = python_call_timing(ts, w, map_pos, map_rate, local_rank)
+        except Exception as e:  # noqa: BLE001
+            e2e_python = {"error": f"{type(e).__name__}: {e}"[:200]}
+
     # ---- CPU baseline (N = 1 only): the compiled reference on all host cores
     cpu = None
     if affinity0 is not None:
@@ -801,6 +861,7 @@ def run_b200_arm(args, rank, local_rank, world):
         "roofline_e2e": roofline_e2e,
         "validated": validated,
         "consumers": consumers_info,
+        "e2e_python": e2e_python,
         "cpu_baseline": cpu,
         "phases_ms_last_step": {k: round(v, 4) for k, v in phases.items()},
         "kernels": kernels,
@@ -825,6 +886,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-validate", action="store_true", help="skip the checks of the last timed overlay")
     ap.add_argument("--no-consumers", action="store_true", help="skip the sample-count index / site AFS figures")
+    ap.add_argument("--no-e2e-python", action="store_true", help="skip the timing of the Python-level call")
     ap.add_argument("--e2e-depth", type=int, default=3,
                     help="end-to-end overlays in flight at N = 1 (1 = one at a time)")
     ap.add_argument("--no-full-config", action="store_true",

@@ -274,6 +274,12 @@ int mspb_sim_mutations(int device, const mspb_tables_t *tables, const mspb_param
     mspb_counts_t *counts, mspb_columns_t *out);
 void mspb_columns_free(mspb_columns_t *cols);
 
+/* Pinned host memory from a pool (no reference counterpart): result columns copied into pinned buffers arrive at
+ * the link's rate, into pageable ones at a fraction of it.  Blocks are pinned once and reused after
+ * mspb_pinned_free; NULL when the allocation fails.  Thread safe. */
+void *mspb_pinned_alloc(uint64_t bytes);
+void mspb_pinned_free(void *block);
+
 /* Consumers of the resident tables on the device: what the reference's users compute
  * next from the tables this path writes (verification.py:6008-6013).
  *   mspb_ctx_build_sample_index  <- the num_samples bookkeeping of tskit's tree sweep (tsk_tree_t.num_samples,

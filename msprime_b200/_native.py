@@ -115,7 +115,7 @@ EXPORTED_SYMBOLS = [
     "mspb_exchange_buffers", "mspb_exchange_post_counts", "mspb_generate_end_device",
     "mspb_generate_finish_device", "mspb_last_fetch_bytes", "mspb_ctx_load_tables_begin",
     "mspb_ctx_load_tables_end", "mspb_site_rows_noalloc", "mspb_ctx_build_sample_index", "mspb_samples_below",
-    "mspb_site_afs",
+    "mspb_site_afs", "mspb_pinned_alloc", "mspb_pinned_free",
 ]
 
 EXCHANGE_WORDS = 8  # MSPB_EXCHANGE_WORDS
@@ -188,6 +188,10 @@ def lib():
                                                   C.POINTER(C.c_uint64), C.POINTER(C.c_double)]
         L.mspb_samples_below.argtypes = [C.c_void_p, C.c_void_p]
         L.mspb_site_afs.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_double)]
+        L.mspb_pinned_alloc.argtypes = [C.c_uint64]
+        L.mspb_pinned_alloc.restype = C.c_void_p
+        L.mspb_pinned_free.argtypes = [C.c_void_p]
+        L.mspb_pinned_free.restype = None
         _lib = L
     return _lib
 
@@ -211,6 +215,36 @@ def _c(a, dtype):
 
 def _p(a):
     return a.ctypes.data
+
+
+class _PinnedBlock:
+    """One block of the library's pinned-memory pool; goes back to the pool when collected."""
+
+    def __init__(self, nbytes):
+        self.ptr = lib().mspb_pinned_alloc(int(nbytes))
+
+    def __del__(self):
+        try:
+            if self.ptr:
+                lib().mspb_pinned_free(self.ptr)
+                self.ptr = None
+        except Exception:  # noqa: BLE001  (interpreter shutdown)
+            pass
+
+
+def pinned_empty(n, dtype):
+    """A numpy array of ``n`` items over pinned host memory from the library's pool (the block returns to the
+    pool when the array and its views are collected); a plain ``np.empty`` when pinning fails."""
+    dtype = np.dtype(dtype)
+    nbytes = int(n) * dtype.itemsize
+    if nbytes == 0:
+        return np.empty(0, dtype=dtype)
+    block = _PinnedBlock(nbytes)
+    if not block.ptr:
+        return np.empty(int(n), dtype=dtype)
+    buf = (C.c_char * nbytes).from_address(block.ptr)
+    buf._block = block  # the array below keeps `buf` alive, and `buf` the block
+    return np.frombuffer(buf, dtype=dtype, count=int(n))
 
 
 class Params:
@@ -436,7 +470,9 @@ class Context:
                     raise ValueError(f"output buffer for {name} is too small or of the wrong dtype")
                 a = buf[:sizes[name]]
             else:
-                a = np.empty(sizes[name], dtype=dtype)
+                # fresh arrays over pinned memory from the library's pool: the DMA runs at the link's rate
+                # (pageable destinations are staged by the driver at a fraction of it)
+                a = pinned_empty(sizes[name], dtype)
             arrays[name] = a
             setattr(cols, name, _p(a) if a.size > 0 else None)
         check(lib().mspb_fetch(self._h, C.byref(cols)))

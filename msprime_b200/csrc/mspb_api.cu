@@ -142,6 +142,7 @@ struct mspb_ctx {
     // two-phase calls (multi-GPU): everything K5 needs, kept between _begin and _end
     struct {
         bool valid = false, defer = false;
+        bool defer_resolve = false; // SLiM in a two-phase call: K4 needs the slice's id base, so it runs in _end
         uint32_t fixed_len = 0; // matrix model: the common length of all alleles, or 0
         int exchange_stage = 0; // 2: mspb_generate_end_device ran, mspb_generate_finish_device is due
         SortedView sv;
@@ -1287,6 +1288,46 @@ int launch_emit(mspb_ctx *ctx)
     return 0;
 }
 
+// K4 on the state saved by run_sorted_stages
+int launch_resolve(mspb_ctx *ctx)
+{
+    HostTotals *dt = (HostTotals *) ctx->dev_totals.p;
+    const TreeSeqView ts = make_ts_view(ctx);
+    MSPB_LAUNCH(ctx->log, "k4_resolve",
+        k4_resolve_kernel<<<148 * 12, 128, 0, ctx->stream>>>(ts, ctx->pending.kept, ctx->pending.model,
+            ctx->pending.call, ctx->pending.sv, ctx->pending.rv, ctx->multi_list.p, &dt->k4_next, &dt->p1, &dt->dense,
+            &dt->collisions, &dt->err));
+    return 0;
+}
+
+// SLiM: state and metadata stack along parent chains, so their totals are not bounded up front:
+// K5 first runs as a sizing pass (lengths and scan only), then for real.  Leaves the totals on
+// the host (waits twice).
+int slim_size_and_emit(mspb_ctx *ctx)
+{
+    cudaStream_t st = ctx->stream;
+    HostTotals *dt = (HostTotals *) ctx->dev_totals.p;
+    HostTotals *ht = ctx->host;
+    ctx->pending.out.dry_run = 1;
+    TRY(launch_emit(ctx));
+    ctx->pending.out.dry_run = 0;
+    CUDA_OK(cudaMemcpyAsync(ht, dt, sizeof(HostTotals), cudaMemcpyDeviceToHost, st));
+    CUDA_OK(cudaStreamSynchronize(st));
+    if (ht->err != 0) {
+        return ht->err;
+    }
+    if (ctx->pending.out.off32 && (ht->bytes.der >= 0xffffffffull || ht->bytes.mmd >= 0xffffffffull)) {
+        return MSPB_ERR_OFFSET_OVERFLOW;
+    }
+    TRY(ctx->o_mut_der.ensure(ht->bytes.der + 1));
+    TRY(ctx->o_mut_md.ensure(ht->bytes.mmd + 1));
+    ctx->pending.out.mut_der = ctx->o_mut_der.p;
+    ctx->pending.out.mut_md = ctx->o_mut_md.p;
+    TRY(launch_emit(ctx));
+    CUDA_OK(cudaMemcpyAsync(ht, dt, sizeof(HostTotals), cudaMemcpyDeviceToHost, st));
+    return 0;
+}
+
 // sort -> P1 -> K4 -> K5 for one key mode; everything is enqueued, nothing is awaited
 int run_sorted_stages(mspb_ctx *ctx, const mspb_params_t *p, const TreeSeqView &ts, const KeptView &kept,
     const ModelView &model, CallView call, uint64_t R, uint64_t S0, uint64_t M0, const OutView &out, bool first_sort)
@@ -1377,14 +1418,6 @@ int run_sorted_stages(mspb_ctx *ctx, const mspb_params_t *p, const TreeSeqView &
         rv.replay = ctx->replay.p + used;
         rv.replay_len = p->replay_len - used;
     }
-    MSPB_LAUNCH(ctx->log, "k4_resolve",
-        k4_resolve_kernel<<<148 * 12, 128, 0, st>>>(ts, kept, model, call, sv, rv, ctx->multi_list.p, &dt->k4_next, &dt->p1,
-            &dt->dense, &dt->collisions, &dt->err));
-
-    // ---- K5: byte offsets + rows
-    if (first_sort) {
-        CUDA_OK(cudaEventRecord(ctx->ev[6], st));
-    }
     ctx->pending.sv = sv;
     ctx->pending.rv = rv;
     ctx->pending.kept = kept;
@@ -1392,6 +1425,14 @@ int run_sorted_stages(mspb_ctx *ctx, const mspb_params_t *p, const TreeSeqView &
     ctx->pending.call = call;
     ctx->pending.out = out;
     ctx->pending.R = R;
+    if (!ctx->pending.defer_resolve) {
+        TRY(launch_resolve(ctx));
+    }
+
+    // ---- K5: byte offsets + rows
+    if (first_sort) {
+        CUDA_OK(cudaEventRecord(ctx->ev[6], st));
+    }
     if (!ctx->pending.defer) {
         TRY(launch_emit(ctx));
     }
@@ -1411,6 +1452,7 @@ static int generate_impl(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t 
     }
     ctx->pending.valid = false;
     ctx->pending.defer = defer;
+    ctx->pending.defer_resolve = false;
     ctx->pending.R = 0;
     if (!ctx->tables_loaded) {
         return MSPB_ERR_TABLES_NOT_LOADED;
@@ -1646,9 +1688,10 @@ static int generate_impl(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t 
     const uint64_t der_cap = (keep ? ctx->kept_der_bytes : 0) + Mnew * maxlen;
     const uint64_t anc_cap = (keep ? ctx->kept_anc_bytes : 0) + Mnew * maxlen;
     const bool slim = p->model_kind == MSPB_MODEL_SLIM;
-    if (slim && defer) {
-        return MSPB_ERR_BAD_PARAM_VALUE; /* the SLiM model's ids feed its byte counts: single call only */
-    }
+    // (a slice of a two-phase call learns the first id it may use from the other ranks, and the SLiM
+    // model's ids feed its state lengths: K4 and K5 then run in mspb_generate_end)
+    const bool slim_two_phase = slim && defer;
+    ctx->pending.defer_resolve = slim_two_phase;
     if (slim && Mnew > 0 && p->start_allele + Mnew - 1 >= (uint64_t) INT64_MAX) {
         return MSPB_ERR_MUTATION_ID_OVERFLOW; /* lib/mutgen.c:386-389 */
     }
@@ -1834,23 +1877,8 @@ static int generate_impl(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t 
     if (ht->collisions > 0) {
         return MSPB_ERR_REPLAY_REDRAW;
     }
-    if (slim && R > 0) {
-        // SLiM: state and metadata stack along parent chains, so their totals are not bounded
-        // up front: K5 first runs as a sizing pass (lengths and scan only), then for real
-        ctx->pending.out.dry_run = 1;
-        TRY(launch_emit(ctx));
-        ctx->pending.out.dry_run = 0;
-        CUDA_OK(cudaMemcpyAsync(ht, dt, sizeof(HostTotals), cudaMemcpyDeviceToHost, st));
-        CUDA_OK(cudaStreamSynchronize(st));
-        if (off32 && (ht->bytes.der >= 0xffffffffull || ht->bytes.mmd >= 0xffffffffull)) {
-            return MSPB_ERR_OFFSET_OVERFLOW;
-        }
-        TRY(ctx->o_mut_der.ensure(ht->bytes.der + 1));
-        TRY(ctx->o_mut_md.ensure(ht->bytes.mmd + 1));
-        ctx->pending.out.mut_der = ctx->o_mut_der.p;
-        ctx->pending.out.mut_md = ctx->o_mut_md.p;
-        TRY(launch_emit(ctx));
-        CUDA_OK(cudaMemcpyAsync(ht, dt, sizeof(HostTotals), cudaMemcpyDeviceToHost, st));
+    if (slim && R > 0 && !slim_two_phase) {
+        TRY(slim_size_and_emit(ctx));
         CUDA_OK(cudaEventRecord(ctx->ev[8], st));
         CUDA_OK(cudaStreamSynchronize(st));
         CUDA_OK(cudaGetLastError());
@@ -1859,7 +1887,7 @@ static int generate_impl(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t 
             return ht->err;
         }
     }
-    if (slim) {
+    if (slim && !slim_two_phase) {
         defer = false;
     }
     const uint64_t draws = ht->p1.d;
@@ -1934,7 +1962,17 @@ extern "C" int mspb_generate_end(mspb_ctx_t *ctx, uint64_t site_base, uint64_t m
     ctx->pending.model.start_allele = allele_base;
     cudaEvent_t e0 = ctx->ev[0], e1 = ctx->ev[1];
     CUDA_OK(cudaEventRecord(e0, st));
-    if (ctx->pending.R > 0) {
+    if (ctx->pending.defer_resolve) {
+        // SLiM: the ids of this slice start at allele_base (lib/mutgen.c:386-389 for the overflow rule)
+        if (ctx->pending.Mnew > 0 && allele_base + ctx->pending.Mnew - 1 >= (uint64_t) INT64_MAX) {
+            return MSPB_ERR_MUTATION_ID_OVERFLOW;
+        }
+        if (ctx->pending.R > 0) {
+            CUDA_OK(cudaMemsetAsync(&dt->k4_next, 0, sizeof(uint32_t), st));
+            TRY(launch_resolve(ctx));
+            TRY(slim_size_and_emit(ctx));
+        }
+    } else if (ctx->pending.R > 0) {
         TRY(launch_emit(ctx));
     }
     CUDA_OK(cudaMemcpyAsync(ht, dt, sizeof(HostTotals), cudaMemcpyDeviceToHost, st));
@@ -1951,8 +1989,8 @@ extern "C" int mspb_generate_end(mspb_ctx_t *ctx, uint64_t site_base, uint64_t m
     c.site_metadata_bytes = ht->bytes.smd;
     c.derived_state_bytes = ht->bytes.der;
     c.mutation_metadata_bytes = ht->bytes.mmd;
-    if (ctx->pending.model_kind == MSPB_MODEL_INFINITE_ALLELES) {
-        c.next_allele = allele_base + (c.next_allele - ctx->pending.start_allele);
+    if (ctx->pending.model_kind != MSPB_MODEL_MATRIX) {
+        c.next_allele = allele_base + (c.next_allele - ctx->pending.start_allele); // allele number / SLiM id counter
     }
     c.device_ms += ms;
     ctx->generated = true;
@@ -2103,6 +2141,10 @@ extern "C" int mspb_exchange_post_counts(mspb_ctx_t *ctx)
     }
     if (!ctx->pending.valid) {
         return MSPB_ERR_NOT_GENERATED;
+    }
+    if (ctx->pending.defer_resolve) {
+        // the SLiM model sizes its columns from the id base, which the host must know: mspb_generate_end
+        return MSPB_ERR_BAD_PARAM_VALUE;
     }
     CUDA_OK(cudaSetDevice(ctx->device));
     TRY(ensure_exchange(ctx));
@@ -2457,6 +2499,71 @@ extern "C" int mspb_selftest_sort(mspb_ctx_t *ctx, uint64_t n, int key_bytes, ui
         return selftest_sort_impl<uint32_t>(ctx, n, key_mask & 0xffffffffull, seed, measure_bits != 0, passes);
     }
     return selftest_sort_impl<uint64_t>(ctx, n, key_mask, seed, measure_bits != 0, passes);
+}
+
+// ---------------------------------------------------------------- pinned host buffers
+// A download into pageable memory is staged by the driver at a few GB/s (0.22 s for the 0.74 GB of a bench-size
+// result, against 13 ms of DMA into pinned memory), and pinning memory per call costs as much.  Callers that
+// want their result columns in buffers of their own lifetime take them from this pool: blocks are pinned once
+// and handed out again after mspb_pinned_free (the Python layer frees a block when the numpy array over it is
+// collected), so a steady caller allocates nothing.
+#include <mutex>
+
+namespace {
+
+std::mutex g_pinned_mutex;
+std::multimap<size_t, void *> g_pinned_free; // capacity -> block
+std::map<void *, size_t> g_pinned_live; // block -> capacity
+size_t g_pinned_cached_bytes = 0;
+constexpr size_t PINNED_CACHE_LIMIT = 16ull << 30; // free blocks kept pinned at most
+
+} // namespace
+
+extern "C" void *mspb_pinned_alloc(uint64_t bytes)
+{
+    const size_t want = ((size_t) (bytes > 0 ? bytes : 1) + 0xfffffull) & ~(size_t) 0xfffffull; // whole MiB
+    {
+        std::lock_guard<std::mutex> lock(g_pinned_mutex);
+        auto it = g_pinned_free.lower_bound(want);
+        if (it != g_pinned_free.end() && it->first <= 2 * want) {
+            void *p = it->second;
+            g_pinned_live[p] = it->first;
+            g_pinned_cached_bytes -= it->first;
+            g_pinned_free.erase(it);
+            return p;
+        }
+    }
+    void *p = nullptr;
+    if (cudaHostAlloc(&p, want, cudaHostAllocPortable) != cudaSuccess) {
+        cudaGetLastError();
+        return nullptr;
+    }
+    std::lock_guard<std::mutex> lock(g_pinned_mutex);
+    g_pinned_live[p] = want;
+    return p;
+}
+
+extern "C" void mspb_pinned_free(void *p)
+{
+    if (p == nullptr) {
+        return;
+    }
+    size_t cap = 0;
+    {
+        std::lock_guard<std::mutex> lock(g_pinned_mutex);
+        auto it = g_pinned_live.find(p);
+        if (it == g_pinned_live.end()) {
+            return; // not one of ours
+        }
+        cap = it->second;
+        g_pinned_live.erase(it);
+        if (g_pinned_cached_bytes + cap <= PINNED_CACHE_LIMIT) {
+            g_pinned_free.emplace(cap, p);
+            g_pinned_cached_bytes += cap;
+            return;
+        }
+    }
+    cudaFreeHost(p);
 }
 
 // ---------------------------------------------------------------- consumers of the tables

@@ -36,6 +36,58 @@ def slice_cuts(sequence_length, world, discrete_genome=True):
     return cuts
 
 
+def balanced_cuts(tables, map_position, map_rate, world, *, discrete_genome=True, start_time=None, end_time=None,
+                  bins=16384):
+    """``world + 1`` cut points such that every slice holds about the same expected number of new mutations
+    ("the cuts are chosen so that the total branch mass is balanced"), where equal-length
+    slices (:func:`slice_cuts`) differ as much as the rate map does.
+
+    The mutation mass of [0, x) is the integral of rate(x) times the total branch length (inside the time
+    window) of the edges covering x.  It is accumulated over ``bins`` equal stretches of the genome: the branch
+    length alive inside a stretch comes from the edges' end points (two weighted histograms), the rate mass
+    of a stretch from the rate map; inside a stretch both are taken as uniform, which is exact for the
+    purpose (cuts only have to balance the slices, any cuts give the same distribution of results)."""
+    L = float(tables["sequence_length"])
+    if world == 1:
+        return [0.0, L]
+    e, nt = tables["edges"], np.asarray(tables["nodes"]["time"], dtype=np.float64)
+    lo, hi = nt[np.asarray(e["child"])], nt[np.asarray(e["parent"])]
+    if start_time is not None:
+        lo = np.maximum(lo, start_time)
+    if end_time is not None:
+        hi = np.minimum(hi, end_time)
+    branch = np.maximum(hi - lo, 0.0)
+    left, right = np.asarray(e["left"], dtype=np.float64), np.asarray(e["right"], dtype=np.float64)
+    w = L / bins
+    edges_ = np.arange(bins + 1) * w
+    # covered(x) = sum over edges of branch * length of (edge intersected with [0, x)) at the bin boundaries
+    #            = sum branch * min(x, right) - sum branch * min(x, left); for a set of points p with weights b,
+    # sum b * min(X_j, p) = X_j * (weight of the points in bins >= j) + (sum of b * p over the bins < j)
+    def capped_sum(points):
+        k = np.minimum((points / w).astype(np.int64), bins - 1)
+        weight = np.bincount(k, weights=branch, minlength=bins)
+        moment = np.bincount(k, weights=branch * points, minlength=bins)
+        beyond = np.concatenate([np.cumsum(weight[::-1])[::-1], [0.0]])
+        before = np.concatenate([[0.0], np.cumsum(moment)])
+        return edges_ * beyond + before
+
+    covered = capped_sum(right) - capped_sum(left)
+    alive = np.diff(covered) / w  # mean branch length alive inside every bin
+    mp, mr = np.asarray(map_position, dtype=np.float64), np.asarray(map_rate, dtype=np.float64)
+    cum_rate = np.concatenate([[0.0], np.cumsum(np.diff(mp) * mr)])
+    rate_mass = np.diff(np.interp(edges_, mp, cum_rate))
+    mass = np.concatenate([[0.0], np.cumsum(alive * rate_mass)])
+    if not mass[-1] > 0:
+        return slice_cuts(L, world, discrete_genome)
+    cuts = np.interp(np.arange(world + 1) * mass[-1] / world, mass, edges_)
+    cuts = [float(np.floor(c)) if discrete_genome else float(c) for c in cuts]
+    cuts[0], cuts[-1] = 0.0, L
+    for a, b in zip(cuts[:-1], cuts[1:]):
+        if not a < b:
+            return slice_cuts(L, world, discrete_genome)
+    return cuts
+
+
 def exclusive_bases(all_values, rank):
     """Sum over ranks before ``rank`` of each column of ``all_values`` (world x k ints)."""
     a = np.asarray(all_values, dtype=object)

@@ -154,3 +154,39 @@ def test_slice_cuts():
     with pytest.raises(ValueError):
         sharding.slice_cuts(2, 4)
     assert sharding.exclusive_bases([[1, 10], [2, 20], [3, 30]], 2) == [3, 30]
+
+
+def test_balanced_cuts_even_out_the_expected_mutations():
+    """Equal-length slices of a genome whose rate map varies a lot hold very different numbers of mutations;
+    the mass-balanced cuts hold the same number each, and are integers on a discrete
+    genome.  The expectation per slice is the exact sum over clipped edges (msprime_b200/validate.py)."""
+    import cases
+    from msprime_b200 import validate
+
+    ts = cases.smc_ts(100, 2e6, 7)
+    L = ts["sequence_length"]
+    rng = np.random.default_rng(3)
+    pos = np.linspace(0, L, 41)
+    rate = rng.lognormal(np.log(1e-8), 1.5, 40)
+
+    def per_slice(cuts, **win):
+        out = []
+        e = ts["edges"]
+        for a, b in zip(cuts[:-1], cuts[1:]):
+            clipped = {"sequence_length": L, "nodes": ts["nodes"],
+                       "edges": {"left": np.clip(e["left"], a, b), "right": np.clip(e["right"], a, b),
+                                 "parent": e["parent"], "child": e["child"]}}
+            out.append(validate.expected_new_mutations(clipped, pos, rate, discrete=True, **win))
+        return np.array(out)
+
+    for world in (2, 4, 8):
+        for win in ({}, {"start_time": 1e3, "end_time": 2e4}):
+            even = per_slice(sharding.slice_cuts(L, world), **win)
+            cuts = sharding.balanced_cuts(ts, pos, rate, world, discrete_genome=True, **win)
+            assert len(cuts) == world + 1 and cuts[0] == 0 and cuts[-1] == L
+            assert all(c == np.floor(c) for c in cuts) and all(a < b for a, b in zip(cuts[:-1], cuts[1:]))
+            bal = per_slice(cuts, **win)
+            assert abs(bal.sum() - even.sum()) < 1e-6 * even.sum()
+            assert bal.max() / bal.mean() < 1.02, (world, bal)
+            assert even.max() / even.mean() > 1.2 or world == 2
+    assert sharding.balanced_cuts(ts, pos, rate, 1) == [0.0, L]
