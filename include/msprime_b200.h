@@ -292,11 +292,19 @@ void mspb_pinned_free(void *block);
  *                                   one sample set (all samples), no span normalisation (trees.c:3816, 3527-3540):
  *                                   afs[k] = derived alleles (byte strings other than the site's ancestral state)
  *                                   carried by exactly k samples, 0 < k < num_samples; afs_len = num_samples + 1.
+ *   mspb_decode_genotypes        <- tsk_variant_decode (git-submodules/tskit/c/tskit/genotypes.c:474) for the sites
+ *                                   [site_begin, site_end) of the result: genotypes[(site - site_begin) * num_samples
+ *                                   + j] = allele index of sample j (sample nodes in increasing order; allele 0 is
+ *                                   the ancestral state, derived states follow in order of first appearance);
+ *                                   host buffer of (site_end - site_begin) * num_samples int32; at most 65535 sites
+ *                                   per call.
  * Results of unsliced calls only (a genome slice of a sharded call carries global row ids). */
 int mspb_ctx_build_sample_index(mspb_ctx_t *ctx, const uint32_t *node_flags, uint64_t *num_samples,
     uint64_t *num_levels, uint64_t *num_steps, double *build_ms);
 int mspb_samples_below(mspb_ctx_t *ctx, uint32_t *below);
 int mspb_site_afs(mspb_ctx_t *ctx, uint64_t *afs, uint64_t afs_len, double *device_ms);
+int mspb_decode_genotypes(mspb_ctx_t *ctx, uint64_t site_begin, uint64_t site_end, int32_t *genotypes,
+    double *device_ms);
 
 /* Allocation-free site numbering.  This entry point has NO counterpart in the reference: it was added
  * for callers that cannot call cudaMalloc (code under CUDA graph

@@ -115,7 +115,7 @@ EXPORTED_SYMBOLS = [
     "mspb_exchange_buffers", "mspb_exchange_post_counts", "mspb_generate_end_device",
     "mspb_generate_finish_device", "mspb_last_fetch_bytes", "mspb_ctx_load_tables_begin",
     "mspb_ctx_load_tables_end", "mspb_site_rows_noalloc", "mspb_ctx_build_sample_index", "mspb_samples_below",
-    "mspb_site_afs", "mspb_pinned_alloc", "mspb_pinned_free",
+    "mspb_site_afs", "mspb_pinned_alloc", "mspb_pinned_free", "mspb_decode_genotypes",
 ]
 
 EXCHANGE_WORDS = 8  # MSPB_EXCHANGE_WORDS
@@ -188,6 +188,7 @@ def lib():
                                                   C.POINTER(C.c_uint64), C.POINTER(C.c_double)]
         L.mspb_samples_below.argtypes = [C.c_void_p, C.c_void_p]
         L.mspb_site_afs.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_double)]
+        L.mspb_decode_genotypes.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p, C.POINTER(C.c_double)]
         L.mspb_pinned_alloc.argtypes = [C.c_uint64]
         L.mspb_pinned_alloc.restype = C.c_void_p
         L.mspb_pinned_free.argtypes = [C.c_void_p]
@@ -546,6 +547,19 @@ class Context:
         ms = C.c_double()
         check(lib().mspb_site_afs(self._h, _p(out), n + 1, C.byref(ms)))
         self.afs_ms = float(ms.value)
+        return out
+
+    def genotypes(self, site_begin=0, site_end=None):
+        """``tsk_variant_decode`` for the sites ``[site_begin, site_end)`` of the resident result: an int32 array of
+        shape (sites, samples), sample nodes in increasing order, allele 0 = the ancestral state."""
+        S = self.counts["num_sites"]
+        site_end = S if site_end is None else int(site_end)
+        n = self.sample_index["num_samples"]
+        out = np.zeros((max(site_end - int(site_begin), 0), n), dtype=np.int32)
+        ms = C.c_double()
+        if out.size > 0:
+            check(lib().mspb_decode_genotypes(self._h, int(site_begin), site_end, _p(out), C.byref(ms)))
+        self.decode_ms = float(ms.value)
         return out
 
     def kernel_launches(self) -> int:

@@ -275,6 +275,29 @@ struct RateMapView {
     // position at cumulative mass m, restricted to the edge [left, right)
     MSPB_DEVFN double position_at(double m, double left, double right) const
     {
+        if (size == 1) {
+            // one interval [0, L): the general path below with i = 0, cum[0] = 0 and coord(pos[0]) = 0
+            // (bit for bit the same arithmetic, without its loads of pos / cum)
+            const double a = coord(left), b = coord(right);
+            double x = m * inv_rate[0];
+            if (discrete) {
+                x = floor(x);
+                if (x > b - 1.0) {
+                    x = b - 1.0;
+                }
+                if (x < a) {
+                    x = a;
+                }
+            } else {
+                if (!(x < b)) {
+                    x = nextafter(b, -1.7976931348623157e308);
+                }
+                if (x < a) {
+                    x = a;
+                }
+            }
+            return x;
+        }
         uint32_t i = 0;
         if (size > 1) {
             // last i with cum[i] <= m, skipping zero-mass intervals

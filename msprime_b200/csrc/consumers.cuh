@@ -369,4 +369,135 @@ __global__ void __launch_bounds__(256) sf_afs_kernel(uint64_t num_mutations, con
     }
 }
 
+// ---------------------------------------------------------------- variant decoding
+// tsk_variant_decode (git-submodules/tskit/c/tskit/genotypes.c:474): the alleles of a site are its
+// ancestral state followed by the derived states in order of first appearance; every sample carries
+// the allele of the nearest mutation of the site on its path to the root (the last such row of the
+// table when a node holds several), allele 0 when there is none.
+
+struct SfIsSample {
+    const uint32_t *is_sample;
+    MSPB_DEVFN uint32_t operator()(uint64_t u) const { return is_sample[u]; }
+};
+
+__global__ void __launch_bounds__(256) sf_sample_list_kernel(uint64_t n, const uint32_t *__restrict__ is_sample,
+    const uint32_t *__restrict__ pos, uint32_t *__restrict__ samples)
+{
+    const uint64_t u = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (u < n && is_sample[u] != 0u) {
+        samples[pos[u]] = (uint32_t) u;
+    }
+}
+
+struct SiteRows {
+    uint32_t *row_begin, *row_end; // mutation rows of site (site_begin + k)
+    double *tmax; // oldest node among its mutations
+    uint32_t *allele; // per mutation row: index of its derived state in the site's allele list
+    uint32_t *walk_id; // per mutation row: its node as the walk names it
+};
+
+// one thread per site of the range: its rows, the oldest mutated node, the allele list
+template <bool OFF32>
+__global__ void __launch_bounds__(128) sf_site_alleles_kernel(TreeSeqView ts, uint64_t site_begin, uint64_t num_sites,
+    uint64_t num_mutations, const int32_t *__restrict__ mut_site, const int32_t *__restrict__ mut_node,
+    const char *__restrict__ der, const void *__restrict__ der_off, const char *__restrict__ anc,
+    const void *__restrict__ anc_off, SiteRows out)
+{
+    const uint64_t k = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= num_sites) {
+        return;
+    }
+    const int64_t s = (int64_t) (site_begin + k);
+    uint64_t lo = 0, hi = num_mutations; // first row with mut_site >= s
+    while (lo < hi) {
+        const uint64_t mid = (lo + hi) >> 1;
+        if ((int64_t) mut_site[mid] < s) {
+            lo = mid + 1;
+        } else {
+            hi = mid;
+        }
+    }
+    const uint64_t m0 = lo;
+    uint64_t m1 = m0;
+    double tmax = -INFINITY;
+    while (m1 < num_mutations && (int64_t) mut_site[m1] == s) {
+        tmax = fmax(tmax, ts.node_time[mut_node[m1]]);
+        out.walk_id[m1] = walk_id(ts, mut_node[m1]);
+        m1++;
+    }
+    out.row_begin[k] = (uint32_t) m0;
+    out.row_end[k] = (uint32_t) m1;
+    out.tmax[k] = tmax;
+    const uint64_t a0 = sf_load_off<OFF32>(anc_off, (uint64_t) s), alen = sf_load_off<OFF32>(anc_off, (uint64_t) s + 1) - a0;
+    uint32_t distinct = 1; // the ancestral state is allele 0
+    for (uint64_t m = m0; m < m1; m++) {
+        const uint64_t d0 = sf_load_off<OFF32>(der_off, m), dlen = sf_load_off<OFF32>(der_off, m + 1) - d0;
+        bool same = alen == dlen;
+        for (uint64_t q = 0; q < dlen && same; q++) {
+            same = anc[a0 + q] == der[d0 + q];
+        }
+        uint32_t idx = 0;
+        if (!same) {
+            // an earlier row with the same state names the allele, else it is a new one
+            bool found = false;
+            for (uint64_t e = m0; e < m && !found; e++) {
+                const uint64_t e0 = sf_load_off<OFF32>(der_off, e);
+                if (sf_load_off<OFF32>(der_off, e + 1) - e0 == dlen) {
+                    bool eq = true;
+                    for (uint64_t q = 0; q < dlen && eq; q++) {
+                        eq = der[e0 + q] == der[d0 + q];
+                    }
+                    if (eq) {
+                        idx = out.allele[e];
+                        found = true;
+                    }
+                }
+            }
+            if (!found) {
+                idx = distinct++;
+            }
+        }
+        out.allele[m] = idx;
+    }
+}
+
+// one thread per (site, sample): up from the sample until a node of the site's mutations
+__global__ void __launch_bounds__(256) sf_decode_kernel(TreeSeqView ts, uint64_t site_begin, uint64_t num_sites,
+    const double *__restrict__ site_position, const uint32_t *__restrict__ samples, uint64_t num_samples, SiteRows sr,
+    int32_t *__restrict__ genotypes)
+{
+    const uint64_t j = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    const uint64_t k = blockIdx.y;
+    if (j >= num_samples || k >= num_sites) {
+        return;
+    }
+    const uint32_t m0 = sr.row_begin[k], m1 = sr.row_end[k];
+    int32_t g = 0;
+    if (m1 > m0) {
+        const double x = site_position[site_begin + k], tmax = sr.tmax[k];
+        const uint32_t u = samples[j];
+        WalkNode w = walk_node(ts, (int32_t) u);
+        double tu = ts.node_time[u];
+        for (;;) {
+            if (tu > tmax) {
+                break; // older than every mutated node of the site
+            }
+            int64_t hit = -1;
+            for (uint32_t m = m0; m < m1; m++) {
+                if (sr.walk_id[m] == w.id) {
+                    hit = m; // the last row on this node wins
+                }
+            }
+            if (hit >= 0) {
+                g = (int32_t) sr.allele[hit];
+                break;
+            }
+            if (!parent_at(ts, &w, x, &tu)) {
+                break;
+            }
+        }
+    }
+    genotypes[k * num_samples + j] = g;
+}
+
 } // namespace mspb

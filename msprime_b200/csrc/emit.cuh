@@ -348,7 +348,7 @@ __global__ void __launch_bounds__(K5_THREADS, 4) k5_emit_kernel(SortedView sv, R
         const uint64_t der = (uint64_t) aw.w[0][0] | ((uint64_t) aw.w[0][1] << 32);
         const uint64_t anc = (uint64_t) aw.w[1][0] | ((uint64_t) aw.w[1][1] << 32);
         const bool no_md = (aw.w[0][2] | aw.w[0][3] | aw.w[1][2] | aw.w[1][3]) == 0u;
-        if (MD && !out.dry_run && !(der <= K5_STAGE && anc <= K5_STAGE && no_md)) {
+        if (!out.dry_run && !(der <= K5_STAGE && anc <= K5_STAGE && no_md)) {
             __syncthreads(); // unstaged tiles: the workers wait for the prefix before writing
         }
         __syncthreads(); // rows and bytes are done
@@ -511,7 +511,9 @@ __global__ void __launch_bounds__(K5_THREADS, 4) k5_emit_kernel(SortedView sv, R
     // ---- offsets across tiles.  When the tile's state bytes fit the stage (always, unless
     // kept rows carry long strings) nothing below needs the prefix until the very end:
     // the look-back warp chains the tiles while the workers write rows and assemble bytes.
-    const bool staged = !MD || (agg.der <= K5_STAGE && agg.anc <= K5_STAGE && agg.mmd == 0 && agg.smd == 0);
+    // (a tile of long states does not fit the stage whatever the model: 1024 alleles of 13 bytes or more,
+    // i.e. allele numbers from 10^12 on or a matrix model with long alleles, go straight to global memory)
+    const bool staged = agg.der <= K5_STAGE && agg.anc <= K5_STAGE && agg.mmd == 0 && agg.smd == 0;
     Bytes4 pre = Bytes4();
     if (out.dry_run) {
         // sizing pass (models whose state lengths are not bounded up front): totals only

@@ -164,7 +164,7 @@ struct mspb_ctx {
         bool valid = false;
         uint32_t num_samples = 0, num_x = 0, levels = 0;
         uint64_t steps = 0; // entries of fx / fv in use
-        DBuf<uint32_t> is_sample, foff, fcnt;
+        DBuf<uint32_t> is_sample, foff, fcnt, samples; // samples: the sample nodes in increasing order
         DBuf<uint64_t> xs;
         uint32_t *fx = nullptr, *fv = nullptr;
         size_t fcap = 0;
@@ -172,6 +172,9 @@ struct mspb_ctx {
     } sidx;
     DBuf<uint32_t> q_below, q_own; // per mutation row of the resident result
     DBuf<unsigned long long> q_afs;
+    DBuf<uint32_t> q_row_begin, q_row_end, q_allele, q_walk_id; // variant decoding
+    DBuf<double> q_tmax;
+    DBuf<int32_t> q_geno;
 };
 
 static const char *const PHASE_NAMES[MSPB_NUM_PHASES] = { "params+kept", "K1 count+scan", "K2 place", "K3 sort",
@@ -378,7 +381,8 @@ extern "C" void mspb_ctx_destroy(mspb_ctx_t *ctx)
     REL(o_site_pos); REL(o_mut_time); REL(o_site_anc); REL(o_site_md); REL(o_mut_der); REL(o_mut_md);
     REL(o_site_anc_off); REL(o_site_md_off); REL(o_mut_der_off); REL(o_mut_md_off);
     REL(o_mut_site); REL(o_mut_node); REL(o_mut_parent);
-    REL(sidx.is_sample); REL(sidx.foff); REL(sidx.fcnt); REL(sidx.xs); REL(q_below); REL(q_own); REL(q_afs);
+    REL(sidx.is_sample); REL(sidx.foff); REL(sidx.fcnt); REL(sidx.samples); REL(sidx.xs); REL(q_below); REL(q_own); REL(q_afs);
+    REL(q_row_begin); REL(q_row_end); REL(q_allele); REL(q_walk_id); REL(q_tmax); REL(q_geno);
 #undef REL
     if (ctx->sidx.fx != nullptr) {
         cudaFree(ctx->sidx.fx);
@@ -2521,11 +2525,26 @@ constexpr size_t PINNED_CACHE_LIMIT = 16ull << 30; // free blocks kept pinned at
 
 extern "C" void *mspb_pinned_alloc(uint64_t bytes)
 {
-    const size_t want = ((size_t) (bytes > 0 ? bytes : 1) + 0xfffffull) & ~(size_t) 0xfffffull; // whole MiB
+    // size classes an eighth of an octave apart (at least 1 MiB): the columns of successive results differ by
+    // a fraction of a percent in size, and must find the blocks of the results before them
+    size_t want = (size_t) 1 << 20;
+    const size_t need = (size_t) (bytes > 0 ? bytes : 1);
+    while (want < need) {
+        size_t step = want >> 3;
+        size_t next = want;
+        for (int k = 0; k < 8 && next < need; k++) {
+            next += step;
+        }
+        if (next >= need) {
+            want = next;
+            break;
+        }
+        want <<= 1;
+    }
     {
         std::lock_guard<std::mutex> lock(g_pinned_mutex);
         auto it = g_pinned_free.lower_bound(want);
-        if (it != g_pinned_free.end() && it->first <= 2 * want) {
+        if (it != g_pinned_free.end() && it->first <= want + want / 4) {
             void *p = it->second;
             g_pinned_live[p] = it->first;
             g_pinned_cached_bytes -= it->first;
@@ -2664,6 +2683,16 @@ int build_sample_index(mspb_ctx *ctx, const uint32_t *node_flags)
     CUDA_OK(cudaStreamSynchronize(st)); // (also: the caller's flags are no longer read)
     si.num_samples = h_small[0];
     si.num_x = 0;
+    // the sample nodes in increasing order (tskit's default sample list)
+    TRY(si.samples.ensure((size_t) si.num_samples + 1));
+    if (N > 0) {
+        TRY(t.before.ensure(N + 1));
+        TRY(t.tile_sums.ensure(scan_num_tiles(N) + 2));
+        device_exclusive_scan<uint32_t, SfIsSample>(ctx->log, N, SfIsSample { si.is_sample.p }, t.before.p, t.tile_sums.p,
+            nullptr, st);
+        MSPB_LAUNCH(ctx->log, "sf_sample_list",
+            sf_sample_list_kernel<<<grid_for(N, 256), 256, 0, st>>>(N, si.is_sample.p, t.before.p, si.samples.p));
+    }
     TRY(si.xs.ensure(2 * E + 2));
     TRY(sidx_reserve(ctx, 5 * E + 1024));
     if (E > 0) {
@@ -2865,6 +2894,67 @@ extern "C" int mspb_samples_below(mspb_ctx_t *ctx, uint32_t *below)
     CUDA_OK(cudaStreamSynchronize(ctx->stream));
     CUDA_OK(cudaGetLastError());
     ctx->log.collect();
+    return 0;
+}
+
+extern "C" int mspb_decode_genotypes(mspb_ctx_t *ctx, uint64_t site_begin, uint64_t site_end, int32_t *genotypes,
+    double *device_ms)
+{
+    if (ctx == nullptr || genotypes == nullptr || site_end < site_begin) {
+        return MSPB_ERR_BAD_PARAM_VALUE;
+    }
+    if (!ctx->generated) {
+        return MSPB_ERR_NOT_GENERATED;
+    }
+    if (!ctx->sidx.valid) {
+        return MSPB_ERR_TABLES_NOT_LOADED;
+    }
+    if (site_end > ctx->counts.num_sites || ctx->pending.out.site_base != 0 || ctx->pending.out.mut_base != 0
+        || ctx->pending.out.dev_bases != nullptr) {
+        return MSPB_ERR_BAD_PARAM_VALUE;
+    }
+    CUDA_OK(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    const uint64_t ns = site_end - site_begin, n = ctx->sidx.num_samples, M = ctx->counts.num_mutations;
+    if (ns == 0 || n == 0) {
+        return 0;
+    }
+    if (ns > 65535ull || ns * n > RS_MAX_N * 16ull) {
+        return MSPB_ERR_TOO_MANY_ROWS; // decode a range of sites at a time
+    }
+    TRY(ctx->q_row_begin.ensure(ns + 1));
+    TRY(ctx->q_row_end.ensure(ns + 1));
+    TRY(ctx->q_tmax.ensure(ns + 1));
+    TRY(ctx->q_allele.ensure(M + 1));
+    TRY(ctx->q_walk_id.ensure(M + 1));
+    TRY(ctx->q_geno.ensure(ns * n + 1));
+    SiteRows sr { ctx->q_row_begin.p, ctx->q_row_end.p, ctx->q_tmax.p, ctx->q_allele.p, ctx->q_walk_id.p };
+    const TreeSeqView ts = make_ts_view(ctx);
+    cudaEvent_t e0 = ctx->ev[0], e1 = ctx->ev[1];
+    CUDA_OK(cudaEventRecord(e0, st));
+    if (ctx->counts.offset_bytes == 4) {
+        MSPB_LAUNCH(ctx->log, "sf_site_alleles",
+            sf_site_alleles_kernel<true><<<grid_for(ns, 128), 128, 0, st>>>(ts, site_begin, ns, M, ctx->o_mut_site.p,
+                ctx->o_mut_node.p, ctx->o_mut_der.p, ctx->o_mut_der_off.p, ctx->o_site_anc.p, ctx->o_site_anc_off.p, sr));
+    } else {
+        MSPB_LAUNCH(ctx->log, "sf_site_alleles",
+            sf_site_alleles_kernel<false><<<grid_for(ns, 128), 128, 0, st>>>(ts, site_begin, ns, M, ctx->o_mut_site.p,
+                ctx->o_mut_node.p, ctx->o_mut_der.p, ctx->o_mut_der_off.p, ctx->o_site_anc.p, ctx->o_site_anc_off.p, sr));
+    }
+    const dim3 grid(grid_for(n, 256), (unsigned) ns);
+    MSPB_LAUNCH(ctx->log, "sf_decode",
+        sf_decode_kernel<<<grid, 256, 0, st>>>(ts, site_begin, ns, ctx->o_site_pos.p, ctx->sidx.samples.p, n, sr,
+            ctx->q_geno.p));
+    CUDA_OK(cudaEventRecord(e1, st));
+    CUDA_OK(cudaMemcpyAsync(genotypes, ctx->q_geno.p, ns * n * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    CUDA_OK(cudaStreamSynchronize(st));
+    CUDA_OK(cudaGetLastError());
+    ctx->log.collect();
+    if (device_ms != nullptr) {
+        float ms = 0;
+        cudaEventElapsedTime(&ms, e0, e1);
+        *device_ms = ms;
+    }
     return 0;
 }
 

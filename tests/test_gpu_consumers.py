@@ -58,6 +58,12 @@ def test_afs_and_samples_below_match_the_tskit_restatement(native_built, model, 
             want_afs = consumers.site_afs(d)
             got_afs = ctx.site_afs()
             assert np.array_equal(got_afs, want_afs.astype(np.uint64)), (model, discrete, layer)
+            # variant decoding, every site: allele indexes of all samples (tsk_variant_decode)
+            want_G, _ = consumers.genotype_matrix(d)
+            G = ctx.genotypes()
+            assert G.shape == want_G.shape and np.array_equal(G, want_G), (model, discrete, layer)
+            part = ctx.genotypes(5, 17)
+            assert np.array_equal(part, want_G[5:17])
             # samples below = carriers of a mutation with nothing underneath it: the genotype matrix knows
             below = ctx.samples_below()
             samples = consumers.sample_nodes(d)
@@ -90,7 +96,17 @@ def test_step_functions_match_the_numpy_prototype(native_built, samples, L, seed
         want = fns.value_at(np.asarray(res["mutations"]["node"]), pos)
         assert np.array_equal(below, want)
         d = merged(ts, res)
-        assert np.array_equal(ctx.site_afs(), below_levels.site_afs(d, fns).astype(np.uint64))
+        afs = ctx.site_afs()
+        assert np.array_equal(afs, below_levels.site_afs(d, fns).astype(np.uint64))
+        # the two consumers agree: the spectrum recomputed from decoded genotypes of every site
+        S, n = len(res["sites"]["position"]), 2 * samples
+        from_G = np.zeros(n + 1, dtype=np.uint64)
+        for a in range(0, S, 4096):
+            G = ctx.genotypes(a, min(S, a + 4096))
+            for allele in range(1, int(G.max()) + 1):
+                c = (G == allele).sum(axis=1)
+                from_G += np.bincount(c[(c > 0) & (c < n)], minlength=n + 1).astype(np.uint64)
+        assert np.array_equal(from_G, afs)
 
 
 def test_config3_size(native_built):

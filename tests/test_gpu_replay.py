@@ -155,3 +155,21 @@ def test_large_alphabets(ctx, oracle_mod, name):
     ts2 = cases.with_kept(ts, first)
     check_case(ctx, oracle_mod, ts2, model=md, map_position=[0, L], map_rate=[1e-5], seed=2, n_stream=3_000_000,
                keep=True)
+
+
+def test_long_states_on_full_tiles(ctx, oracle_mod):
+    """A tile of K5 holds 1024 records and stages their state bytes in 12 KB of shared memory; states of 13
+    bytes or more (long alleles of a matrix model, allele numbers from 10^12 on) do not fit and must go
+    straight to the table instead, whatever the model.  Bit-exact against the oracle with tens of thousands
+    of records (every tile full), with and without kept rows."""
+    ts = cases.smc_ts(50, 1e5, 1)
+    L = ts["sequence_length"]
+    long_model = {"kind": "matrix", "alleles": ["A" * 40, "C" * 33, "G" * 50, "T" * 21],
+                  "root_distribution": [0.25] * 4, "transition_matrix": cases.JC69["transition_matrix"]}
+    for model in (long_model, dict(cases.INF_ALLELES, start_allele=10**14), dict(cases.INF_ALLELES, start_allele=2**64 - 5000)):
+        first = check_case(ctx, oracle_mod, ts, model=model, map_position=[0, L], map_rate=[4e-6], n_stream=3_000_000)
+        assert len(first["mutations"]["site"]) > 50_000
+        start2 = first["next_allele"] if model["kind"] == "infinite_alleles" else None
+        model2 = dict(model, start_allele=start2) if start2 is not None else model
+        check_case(ctx, oracle_mod, cases.with_kept(ts, first), model=model2, map_position=[0, L], map_rate=[4e-6],
+                   seed=2, n_stream=3_000_000, keep=True)
