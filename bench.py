@@ -441,12 +441,15 @@ def python_call_timing(ts, w, map_pos, map_rate, device):
     kw = dict(rate=rate, model=model, discrete_genome=w["discrete"], keep=bool(w.get("keep_layer")),
               start_time=None if lo == -FMAX else lo, end_time=None if hi == FMAX else hi, device=device)
     tsobj = mtables.TableCollection.fromdict(ts).tree_sequence()
-    walls = []
+    from msprime_b200 import _native
+
+    walls, pool = [], []
     out = None
     for i in range(5):  # the first calls create the context, size its buffers and pin the result blocks
         t0 = time.perf_counter()
         out = msp.sim_mutations(tsobj, random_seed=11 + i, **kw)
         walls.append(time.perf_counter() - t0)
+        pool.append(_native.pinned_stats())
     new = out.num_mutations - (len(ts["mutations"]["site"]) if w.get("keep_layer") else 0)
     # the same steps by hand on the call's own context
     ctx = mutations._context(device)
@@ -478,6 +481,7 @@ def python_call_timing(ts, w, map_pos, map_rate, device):
         steps["result_object"] = time.perf_counter() - t0
     return {"wall_ms_first_call": round(1e3 * walls[0], 2), "wall_ms": round(1e3 * min(walls[1:]), 2),
             "wall_ms_all": [round(1e3 * x, 2) for x in walls],
+            "pinned_pool_after_each_call": [list(p) for p in pool],
             "value": new / min(walls[1:]), "unit": UNIT,
             "steps_ms": {k: round(1e3 * v, 2) for k, v in steps.items()},
             "tree_sequence": "msprime_b200.tables stand-in (tskit is not installed here)"}

@@ -279,6 +279,8 @@ void mspb_columns_free(mspb_columns_t *cols);
  * mspb_pinned_free; NULL when the allocation fails.  Thread safe. */
 void *mspb_pinned_alloc(uint64_t bytes);
 void mspb_pinned_free(void *block);
+/* pool counters: blocks pinned, blocks reused, bytes pinned so far, blocks unpinned again */
+void mspb_pinned_stats(uint64_t out[4]);
 
 /* Consumers of the resident tables on the device: what the reference's users compute
  * next from the tables this path writes (verification.py:6008-6013).

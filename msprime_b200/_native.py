@@ -115,7 +115,7 @@ EXPORTED_SYMBOLS = [
     "mspb_exchange_buffers", "mspb_exchange_post_counts", "mspb_generate_end_device",
     "mspb_generate_finish_device", "mspb_last_fetch_bytes", "mspb_ctx_load_tables_begin",
     "mspb_ctx_load_tables_end", "mspb_site_rows_noalloc", "mspb_ctx_build_sample_index", "mspb_samples_below",
-    "mspb_site_afs", "mspb_pinned_alloc", "mspb_pinned_free", "mspb_decode_genotypes",
+    "mspb_site_afs", "mspb_pinned_alloc", "mspb_pinned_free", "mspb_decode_genotypes", "mspb_pinned_stats",
 ]
 
 EXCHANGE_WORDS = 8  # MSPB_EXCHANGE_WORDS
@@ -643,3 +643,10 @@ def site_rows_noalloc(device, stream, sorted_positions_ptr, n, site_row_ptr, num
     check(lib().mspb_site_rows_noalloc(int(device), C.c_void_p(int(stream) or None),
                                        C.c_void_p(int(sorted_positions_ptr) or None), int(n),
                                        C.c_void_p(int(site_row_ptr) or None), C.c_void_p(int(num_sites_ptr) or None)))
+
+
+def pinned_stats():
+    """(blocks pinned, blocks reused, bytes pinned so far, blocks unpinned) of the pinned-memory pool."""
+    out = (C.c_uint64 * 4)()
+    lib().mspb_pinned_stats(out)
+    return tuple(int(v) for v in out)

@@ -536,8 +536,6 @@ __global__ void __launch_bounds__(K5_THREADS, 4) k5_emit_kernel(SortedView sv, R
         pre.anc = (uint64_t) pw.w[1][0] | ((uint64_t) pw.w[1][1] << 32);
         pre.smd = (uint64_t) pw.w[1][2] | ((uint64_t) pw.w[1][3] << 32);
     }
-    char *der_base = staged ? st_der : out.mut_der + pre.der;
-    char *anc_base = staged ? st_anc : out.site_anc + pre.anc;
     // ---- rows and bytes (the remaining loads, positions and parents, all in flight first)
     double posv[K5_ITEMS];
     int32_t parv[K5_ITEMS];
@@ -548,6 +546,9 @@ __global__ void __launch_bounds__(K5_THREADS, 4) k5_emit_kernel(SortedView sv, R
         posv[k] = sv.key.mode == KEY32_POS ? (double) pos32[k] : ((m & EM_HEAD) ? sv.key.position(i) : 0.0);
         parv[k] = ((m & EM_MUT) && !(m & EM_SINGLE)) ? rv.parent[i] : -1;
     }
+    // (the loop is instantiated twice, for the stage in shared memory and for the table in global memory:
+    // with one pointer for both the state bytes went out as generic 64-bit stores, ST.E.U8)
+    auto emit_rows = [&](char *der_base, char *anc_base) {
 #pragma unroll
     for (int k = 0; k < K5_ITEMS; k++) {
         const uint32_t j = (uint32_t) k * SCAN_THREADS + threadIdx.x;
@@ -595,6 +596,12 @@ __global__ void __launch_bounds__(K5_THREADS, 4) k5_emit_kernel(SortedView sv, R
                     out.mut_md + pre.mmd + s_mmd[j] + ml);
             }
         }
+    }
+    };
+    if (staged) {
+        emit_rows(st_der, st_anc);
+    } else {
+        emit_rows(out.mut_der + pre.der, out.site_anc + pre.anc);
     }
     __syncthreads();
     if (staged) {

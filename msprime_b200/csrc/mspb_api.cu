@@ -2519,6 +2519,7 @@ std::mutex g_pinned_mutex;
 std::multimap<size_t, void *> g_pinned_free; // capacity -> block
 std::map<void *, size_t> g_pinned_live; // block -> capacity
 size_t g_pinned_cached_bytes = 0;
+uint64_t g_pinned_stats[4] = { 0, 0, 0, 0 }; // blocks pinned, blocks reused, bytes pinned so far, blocks unpinned
 constexpr size_t PINNED_CACHE_LIMIT = 16ull << 30; // free blocks kept pinned at most
 
 } // namespace
@@ -2549,6 +2550,7 @@ extern "C" void *mspb_pinned_alloc(uint64_t bytes)
             g_pinned_live[p] = it->first;
             g_pinned_cached_bytes -= it->first;
             g_pinned_free.erase(it);
+            g_pinned_stats[1]++;
             return p;
         }
     }
@@ -2559,7 +2561,18 @@ extern "C" void *mspb_pinned_alloc(uint64_t bytes)
     }
     std::lock_guard<std::mutex> lock(g_pinned_mutex);
     g_pinned_live[p] = want;
+    g_pinned_stats[0]++;
+    g_pinned_stats[2] += want;
     return p;
+}
+
+// blocks pinned, blocks reused from the pool, bytes pinned so far, blocks unpinned again
+extern "C" void mspb_pinned_stats(uint64_t out[4])
+{
+    std::lock_guard<std::mutex> lock(g_pinned_mutex);
+    for (int k = 0; k < 4; k++) {
+        out[k] = g_pinned_stats[k];
+    }
 }
 
 extern "C" void mspb_pinned_free(void *p)
@@ -2581,6 +2594,10 @@ extern "C" void mspb_pinned_free(void *p)
             g_pinned_cached_bytes += cap;
             return;
         }
+    }
+    {
+        std::lock_guard<std::mutex> lock(g_pinned_mutex);
+        g_pinned_stats[3]++;
     }
     cudaFreeHost(p);
 }
