@@ -132,6 +132,10 @@ struct mspb_ctx {
     DBuf<char> dev_totals; // HostTotals mirror
     HostTotals *host = nullptr; // pinned
     uint64_t *or_and_host = nullptr; // pinned
+    // the same pinned words as kernels address them: small read-backs are stored by a kernel, not copied by the
+    // DMA engine, where they would queue behind the column copies of other contexts (sort.cuh)
+    HostTotals *host_dev = nullptr;
+    uint64_t *or_and_host_dev = nullptr;
     // outputs
     DBuf<double> o_site_pos, o_mut_time;
     DBuf<char> o_site_anc, o_site_md, o_mut_der, o_mut_md;
@@ -350,7 +354,28 @@ extern "C" int mspb_ctx_create(int device, mspb_ctx_t **out)
         mspb_ctx_destroy(ctx);
         return MSPB_ERR_NO_MEMORY;
     }
+    if (cudaHostGetDevicePointer((void **) &ctx->host_dev, ctx->host, 0) != cudaSuccess
+        || cudaHostGetDevicePointer((void **) &ctx->or_and_host_dev, ctx->or_and_host, 0) != cudaSuccess) {
+        cudaGetLastError();
+        ctx->host_dev = nullptr; // (no unified addressing: fall back to copies)
+        ctx->or_and_host_dev = nullptr;
+    }
     *out = ctx;
+    return 0;
+}
+
+// dt (device totals) -> ctx->host, in stream order
+static int totals_to_host(mspb_ctx *ctx)
+{
+    static_assert(sizeof(HostTotals) % 4 == 0, "copied as 32-bit words");
+    if (ctx->host_dev != nullptr) {
+        rs_words_to_host_kernel<<<1, 64, 0, ctx->stream>>>(reinterpret_cast<const uint32_t *>(ctx->dev_totals.p),
+            reinterpret_cast<uint32_t *>(ctx->host_dev), (uint32_t) (sizeof(HostTotals) / 4));
+        ctx->log.count++;
+        CUDA_OK(cudaGetLastError());
+    } else {
+        CUDA_OK(cudaMemcpyAsync(ctx->host, ctx->dev_totals.p, sizeof(HostTotals), cudaMemcpyDeviceToHost, ctx->stream));
+    }
     return 0;
 }
 
@@ -610,6 +635,7 @@ RadixSortBuffers<uint64_t> sort_buffers64(mspb_ctx *ctx)
     b.tile_state = ctx->rs_scan_tiles.p;
     b.or_and = ctx->or_and.p;
     b.or_and_host = ctx->or_and_host;
+    b.or_and_host_dev = ctx->or_and_host_dev;
     return b;
 }
 
@@ -624,6 +650,7 @@ RadixSortBuffers<uint32_t> sort_buffers32(mspb_ctx *ctx)
     b.tile_state = ctx->rs_scan_tiles.p;
     b.or_and = ctx->or_and.p;
     b.or_and_host = ctx->or_and_host;
+    b.or_and_host_dev = ctx->or_and_host_dev;
     return b;
 }
 
@@ -799,9 +826,7 @@ int tables_finish(mspb_ctx_t *ctx, RadixSortBuffers<uint64_t> k0_sb, int k0_cur)
         MSPB_LAUNCH(ctx->log, "validate_mutations", validate_mutations_kernel<<<grid_for(ctx->M0, 256), 256, 0, st>>>(ctx->M0, ctx->k_mut_site.p, ctx->k_mut_node.p,
             ctx->have_mut_time ? ctx->k_mut_time.p : nullptr, ctx->S0, ctx->N, ctx->node_time.p, &dt->first_bad));
     }
-    CUDA_OK(cudaMemcpyAsync(&ctx->host->first_bad, &dt->first_bad, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
-    CUDA_OK(cudaMemcpyAsync(
-        &ctx->host->fractional_sites, &dt->fractional_sites, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    TRY(totals_to_host(ctx));
     CUDA_OK(cudaStreamSynchronize(st));
     ctx->kept_fractional = ctx->host->fractional_sites > 0;
     if (ctx->host->first_bad != ~0ull) {
@@ -1310,12 +1335,11 @@ int launch_resolve(mspb_ctx *ctx)
 int slim_size_and_emit(mspb_ctx *ctx)
 {
     cudaStream_t st = ctx->stream;
-    HostTotals *dt = (HostTotals *) ctx->dev_totals.p;
     HostTotals *ht = ctx->host;
     ctx->pending.out.dry_run = 1;
     TRY(launch_emit(ctx));
     ctx->pending.out.dry_run = 0;
-    CUDA_OK(cudaMemcpyAsync(ht, dt, sizeof(HostTotals), cudaMemcpyDeviceToHost, st));
+    TRY(totals_to_host(ctx));
     CUDA_OK(cudaStreamSynchronize(st));
     if (ht->err != 0) {
         return ht->err;
@@ -1328,7 +1352,7 @@ int slim_size_and_emit(mspb_ctx *ctx)
     ctx->pending.out.mut_der = ctx->o_mut_der.p;
     ctx->pending.out.mut_md = ctx->o_mut_md.p;
     TRY(launch_emit(ctx));
-    CUDA_OK(cudaMemcpyAsync(ht, dt, sizeof(HostTotals), cudaMemcpyDeviceToHost, st));
+    TRY(totals_to_host(ctx));
     return 0;
 }
 
@@ -1566,7 +1590,7 @@ static int generate_impl(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t 
             MSPB_LAUNCH(ctx->log, "k1_spine",
                 k1_spine_kernel<<<1, 1024, 0, st>>>(ctx->k1_tiles.p, tiles, &dt->k1_total, &dt->err));
         }
-        CUDA_OK(cudaMemcpyAsync(ht, dt, sizeof(HostTotals), cudaMemcpyDeviceToHost, st));
+        TRY(totals_to_host(ctx));
         CUDA_OK(cudaEventRecord(ctx->ev_k1, st));
         // K2 does not need the total to be launched (its grid follows the edges): when the
         // record and key buffers of earlier calls are there, it goes out now and the host's
@@ -1643,7 +1667,7 @@ static int generate_impl(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t 
         MSPB_LAUNCH(ctx->log, "replay_resolve",
             replay_resolve_kernel<<<1, 32, 0, st>>>(ts, map, call, ctx->replay.p, p->replay_len, pairs, sp,
                 &dt->replay, &dt->err));
-        CUDA_OK(cudaMemcpyAsync(ht, dt, sizeof(HostTotals), cudaMemcpyDeviceToHost, st));
+        TRY(totals_to_host(ctx));
         CUDA_OK(cudaStreamSynchronize(st));
         if (ht->err != 0) {
             return ht->err;
@@ -1820,7 +1844,7 @@ static int generate_impl(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t 
     } else {
         TRY(run_sorted_stages(ctx, p, ts, kept, model, call, R, S0, M0, out, true));
     }
-    CUDA_OK(cudaMemcpyAsync(ht, dt, sizeof(HostTotals), cudaMemcpyDeviceToHost, st));
+    TRY(totals_to_host(ctx));
     CUDA_OK(cudaStreamSynchronize(st));
     CUDA_OK(cudaGetLastError());
     if (R > 0 && ht->err == 0 && ht->dense != 0 && call.key_mode == KEY32_POS) {
@@ -1841,7 +1865,7 @@ static int generate_impl(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t 
         CUDA_OK(cudaMemsetAsync(&dt->k4_next, 0, sizeof(uint32_t), st));
         CUDA_OK(cudaMemsetAsync(&dt->collisions, 0, sizeof(uint32_t), st));
         TRY(run_sorted_stages(ctx, p, ts, kept, model, call, R, S0, M0, out, false));
-        CUDA_OK(cudaMemcpyAsync(ht, dt, sizeof(HostTotals), cudaMemcpyDeviceToHost, st));
+        TRY(totals_to_host(ctx));
     }
     // continuous genome, native stream: new mutations on occupied positions draw again
     // (lib/mutgen.c:1127-1134) until every position is unique.  (The replay harness and
@@ -1868,7 +1892,7 @@ static int generate_impl(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t 
         CUDA_OK(cudaMemsetAsync(&dt->k4_next, 0, sizeof(uint32_t), st));
         CUDA_OK(cudaMemsetAsync(&dt->collisions, 0, sizeof(uint32_t), st));
         TRY(run_sorted_stages(ctx, p, ts, kept, model, call, R, S0, M0, out, false));
-        CUDA_OK(cudaMemcpyAsync(ht, dt, sizeof(HostTotals), cudaMemcpyDeviceToHost, st));
+        TRY(totals_to_host(ctx));
         CUDA_OK(cudaStreamSynchronize(st));
     }
     CUDA_OK(cudaEventRecord(ctx->ev[8], st));
@@ -1979,7 +2003,7 @@ extern "C" int mspb_generate_end(mspb_ctx_t *ctx, uint64_t site_base, uint64_t m
     } else if (ctx->pending.R > 0) {
         TRY(launch_emit(ctx));
     }
-    CUDA_OK(cudaMemcpyAsync(ht, dt, sizeof(HostTotals), cudaMemcpyDeviceToHost, st));
+    TRY(totals_to_host(ctx));
     CUDA_OK(cudaEventRecord(e1, st));
     CUDA_OK(cudaStreamSynchronize(st));
     CUDA_OK(cudaGetLastError());
@@ -2211,7 +2235,6 @@ extern "C" int mspb_generate_finish_device(mspb_ctx_t *ctx, uint32_t rank, uint3
     ctx->pending.exchange_stage = 0;
     CUDA_OK(cudaSetDevice(ctx->device));
     cudaStream_t st = ctx->stream;
-    HostTotals *dt = (HostTotals *) ctx->dev_totals.p;
     HostTotals *ht = ctx->host;
     uint64_t *x = ctx->xchg.p;
     mspb_counts_t &c = ctx->counts;
@@ -2231,7 +2254,7 @@ extern "C" int mspb_generate_finish_device(mspb_ctx_t *ctx, uint32_t rank, uint3
     }
     uint64_t *h = ctx->xchg_host;
     CUDA_OK(cudaMemcpyAsync(h + XCHG_WORDS, x + XCHG_B1, 4 * XCHG_WORDS * sizeof(uint64_t), cudaMemcpyDeviceToHost, st));
-    CUDA_OK(cudaMemcpyAsync(ht, dt, sizeof(HostTotals), cudaMemcpyDeviceToHost, st));
+    TRY(totals_to_host(ctx));
     CUDA_OK(cudaEventRecord(ctx->ev[1], st));
     CUDA_OK(cudaStreamSynchronize(st));
     CUDA_OK(cudaGetLastError());
@@ -2463,6 +2486,7 @@ int selftest_sort_impl(mspb_ctx *ctx, uint64_t n, uint64_t key_mask, uint64_t se
         b.tile_state = state.p;
         b.or_and = ctx->or_and.p;
         b.or_and_host = ctx->or_and_host;
+        b.or_and_host_dev = ctx->or_and_host_dev;
         const int cur = device_radix_sort<KeyT>(b, n, measure_bits ? 0 : (key_mask != 0 ? key_mask : 1), true, st, ctx->log,
             passes);
         std::vector<KeyT> ok(n > 0 ? n : 1);

@@ -525,7 +525,19 @@ struct RadixSortBuffers {
     uint32_t *tile_state; // RS_MAX_PASSES * num_tiles * RS_BINS
     uint64_t *or_and; // 2 (device)
     uint64_t *or_and_host; // 2 (pinned)
+    uint64_t *or_and_host_dev; // the same two words as the device addresses them (nullptr: copy with the DMA engine)
 };
+
+// A few words from device memory into pinned host memory WITHOUT the copy engine: a cudaMemcpyAsync of 16 bytes
+// queues behind whatever that engine is already moving for other streams of the process (the 100 MB column copies
+// of another context's fetch: 13 ms measured), a store from a kernel does not.
+__global__ void rs_words_to_host_kernel(const uint32_t *__restrict__ src, uint32_t *dst_host, uint32_t words)
+{
+    for (uint32_t i = threadIdx.x; i < words; i += blockDim.x) {
+        dst_host[i] = src[i];
+    }
+    __threadfence_system();
+}
 
 template <typename KeyT>
 inline uint32_t rs_num_tiles(uint64_t n)
@@ -557,10 +569,15 @@ inline int device_radix_sort(RadixSortBuffers<KeyT> &buf, uint64_t n, uint64_t v
         return 0;
     }
     if (varying == 0) {
-        const uint64_t init[2] = { 0ull, ~0ull };
-        cudaMemcpyAsync(buf.or_and, init, sizeof(init), cudaMemcpyHostToDevice, st);
+        cudaMemsetAsync(buf.or_and, 0, sizeof(uint64_t), st); // OR of all keys
+        cudaMemsetAsync(buf.or_and + 1, 0xff, sizeof(uint64_t), st); // AND of all keys
         MSPB_LAUNCH(log, "rs_key_bits", rs_key_bits_kernel<KeyT><<<148 * 4, 256, 0, st>>>(buf.keys[0], n, buf.or_and));
-        cudaMemcpyAsync(buf.or_and_host, buf.or_and, 2 * sizeof(uint64_t), cudaMemcpyDeviceToHost, st);
+        if (buf.or_and_host_dev != nullptr) {
+            rs_words_to_host_kernel<<<1, 32, 0, st>>>(reinterpret_cast<const uint32_t *>(buf.or_and),
+                reinterpret_cast<uint32_t *>(buf.or_and_host_dev), 4u);
+        } else {
+            cudaMemcpyAsync(buf.or_and_host, buf.or_and, 2 * sizeof(uint64_t), cudaMemcpyDeviceToHost, st);
+        }
         cudaStreamSynchronize(st);
         varying = buf.or_and_host[0] & ~buf.or_and_host[1];
     }
