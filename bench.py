@@ -77,7 +77,7 @@ INPUT_TEXT = "synthetic SMC' tree sequence (msprime_b200/csrc/treegen.c)"
 
 def config_dict(w, E, N, world):
     """The ``config`` object of the JSON line: the same for the B200 arm and the reference arm."""
-    return {"workload": w["text"], "input": INPUT_TEXT, "edges": E, "nodes": N,
+    return {"workload": w["text"], "input": w.get("input_text", INPUT_TEXT), "edges": E, "nodes": N,
             "l2": "inputs larger than L2 (edge columns + records > 126 MB), no flush",
             "sharding": "whole genome on one GPU" if world == 1 else
             f"{world} genome position slices of equal expected mutation mass (edges cut to the slice, Philox stream per "
@@ -99,9 +99,22 @@ def make_input(w):
     from msprime_b200 import synth
 
     t0 = time.time()
-    ts = synth.native_treeseq(w["samples"], w["L"], w["recomb"], w["ne"], w["ts_seed"])
+    if w.get("input") == "reference":
+        # input preparation only: the reference's own ancestry simulator (lib/msprime.c compiled unmodified into
+        # oracle/_ref/libancestry_ref.so) makes the tree sequence msprime.sim_ancestry would return; practical up to
+        # config 3 (Hudson's algorithm: seconds for config 2, about an hour for config 3)
+        from oracle import ref_ancestry
+
+        if not ref_ancestry.have():
+            raise SystemExit("--input reference needs oracle/_ref/libancestry_ref.so (make -C oracle ancestry)")
+        ts = ref_ancestry.sim_ancestry(w["samples"], sequence_length=w["L"], recombination_rate=w["recomb"],
+                                       population_size=w["ne"], random_seed=w["ts_seed"])
+        w["input_text"] = ("tree sequence from the reference's own sim_ancestry (Hudson, lib/msprime.c compiled "
+                           "unmodified; random_seed=%d)" % w["ts_seed"])
+    else:
+        ts = synth.native_treeseq(w["samples"], w["L"], w["recomb"], w["ne"], w["ts_seed"])
     log(f"[bench] input: N={len(ts['nodes']['time'])} E={len(ts['edges']['left'])} trees={ts['num_trees']} "
-        f"({time.time() - t0:.1f} s, synthetic SMC' generator)")
+        f"({time.time() - t0:.1f} s, {w.get('input', 'treegen')} generator)")
     kl = w.get("keep_layer")
     if kl:
         # the existing mutations of a keep=True workload: one reference overlay (input preparation)
@@ -265,7 +278,7 @@ def run_reference_arm(args, rank, world):
     """``--impl reference``: the reference's own CPU implementation on the host cores."""
     if rank != 0:
         return
-    w = WORKLOADS[args.workload]
+    w = dict(WORKLOADS[args.workload], input=args.input)
     kind, which = cpu_kind()
     from oracle import oracle
 
@@ -508,7 +521,7 @@ def run_b200_arm(args, rank, local_rank, world):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
         dist.barrier()
     torch.cuda.set_device(local_rank)
-    w = WORKLOADS[args.workload]
+    w = dict(WORKLOADS[args.workload], input=args.input)
     ts = make_input(w)
     affinity0, binding = bind_near_gpu(local_rank)
     log(f"[bench] rank {rank}: cpu binding {binding}")
@@ -895,6 +908,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="config5", choices=sorted(WORKLOADS))
+    ap.add_argument("--input", default="treegen", choices=["treegen", "reference"],
+                    help="where the tree sequence comes from: this project's SMC' generator (any size) or the "
+                         "reference's own ancestry simulator (configs 1-3)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-validate", action="store_true", help="skip the checks of the last timed overlay")
     ap.add_argument("--no-consumers", action="store_true", help="skip the sample-count index / site AFS figures")

@@ -10,6 +10,12 @@
 extern "C" {
 #endif
 int gsl_fcmp(double x1, double x2, double epsilon);
+int gsl_isnan(const double x);
+#ifndef GSL_POSINF
+#define GSL_POSINF INFINITY
+#define GSL_NEGINF (-INFINITY)
+#define GSL_NAN NAN
+#endif
 #ifdef __cplusplus
 }
 #endif

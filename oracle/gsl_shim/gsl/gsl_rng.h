@@ -47,6 +47,7 @@ void gsl_rng_replay_set(gsl_rng *r, const double *stream, uint64_t n);
 double gsl_rng_uniform(gsl_rng *r);
 double gsl_rng_uniform_pos(gsl_rng *r);
 unsigned long int gsl_rng_get(gsl_rng *r);
+unsigned long int gsl_rng_uniform_int(gsl_rng *r, unsigned long int n); /* gsl_shim_ancestry.c */
 
 #ifdef __cplusplus
 }

@@ -116,8 +116,8 @@ _libs = {}
 
 
 def build(which=("port", "ref")):
-    """Runs ``make`` for the requested targets (``ref`` and ``tskit``, the extension of the reference's
-    tskit Python package, are no-ops without /root/reference)."""
+    """Runs ``make`` for the requested targets (``ref``, ``ancestry`` and ``tskit``, the extension of the
+    reference's tskit Python package, are no-ops without /root/reference)."""
     for target in which:
         subprocess.run(["make", "-s", "-C", HERE, target], check=True)
 

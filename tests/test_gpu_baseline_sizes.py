@@ -25,18 +25,30 @@ pytestmark = pytest.mark.gpu
 FMAX = cases.FMAX
 
 
-def workload_input(name):
+def workload_input(name, source="treegen"):
+    """``source="reference"``: the tree sequence comes from the reference's own ancestry simulator
+    (oracle/ref_ancestry.py: lib/msprime.c compiled unmodified), i.e. what msprime.sim_ancestry returns for
+    the configuration; otherwise from this project's SMC' generator."""
     w = bench.WORKLOADS[name]
+    if source == "reference":
+        from oracle import ref_ancestry
+
+        if not ref_ancestry.have():
+            pytest.skip("oracle/_ref/libancestry_ref.so not built")
+        return w, ref_ancestry.sim_ancestry(w["samples"], sequence_length=w["L"], recombination_rate=w["recomb"],
+                                            population_size=w["ne"], random_seed=w["ts_seed"])
     return w, synth.native_treeseq(w["samples"], w["L"], w["recomb"], w["ne"], w["ts_seed"])
 
 
-@pytest.mark.parametrize("name", ["config1", "config2", "config3-16"])
+@pytest.mark.parametrize("name", ["config1", "config2", "config3-16", "config1-reference", "config2-reference"])
 def test_replay_bit_exact_at_full_size(native_built, oracle_mod, name):
-    """config3-16 is config 3's tree sequence and model with a 16-interval map instead of 1000: the replay
+    """configN-reference: the same configuration on the tree sequence the REFERENCE's Hudson simulator makes for it
+    (sim_ancestry(samples, sequence_length=, recombination_rate=1e-8, population_size=1e4, random_seed=1));
+    config3-16 is config 3's tree sequence and model with a 16-interval map instead of 1000: the replay
     stream holds one uniform or more per (edge, rate interval) pair (lib/mutgen.c:1115-1120), which is 4e8
     pairs for the 1000-interval map (the ~4e5 edges alive at any position each meet every interval) against
     1.5e7 here; the sequential stream walker is what bounds the size of a replay case."""
-    w, ts = workload_input(name.split("-")[0])
+    w, ts = workload_input(name.split("-")[0], "reference" if name.endswith("-reference") else "treegen")
     if name == "config3-16":
         w = dict(w, ratemap=16)
     L = ts["sequence_length"]
@@ -62,7 +74,7 @@ def test_replay_bit_exact_at_full_size(native_built, oracle_mod, name):
             assert not diffs, diffs
             assert got["draws"] == want["draws"]
             M = len(want["mutations"]["site"])
-            assert M > (2_000 if name == "config1" else 30_000)
+            assert M > (2_000 if name.startswith("config1") else 30_000)
             base = cases.with_kept(ts, want)
 
 
