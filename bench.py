@@ -102,13 +102,15 @@ def make_input(w):
     if w.get("input") == "reference":
         # input preparation only: the reference's own ancestry simulator (lib/msprime.c compiled unmodified into
         # oracle/_ref/libancestry_ref.so) makes the tree sequence msprime.sim_ancestry would return; practical up to
-        # config 3 (Hudson's algorithm: seconds for config 2, about an hour for config 3)
+        # config 3 (Hudson's algorithm: seconds for config 2, five minutes for config 3, hours for config 5)
         from oracle import ref_ancestry
 
-        if not ref_ancestry.have():
-            raise SystemExit("--input reference needs oracle/_ref/libancestry_ref.so (make -C oracle ancestry)")
-        ts = ref_ancestry.sim_ancestry(w["samples"], sequence_length=w["L"], recombination_rate=w["recomb"],
-                                       population_size=w["ne"], random_seed=w["ts_seed"])
+        ts = ref_ancestry.load_cached(w)  # scripts/make_reference_input.py (configs 3-5 take minutes to hours)
+        if ts is None:
+            if not ref_ancestry.have():
+                raise SystemExit("--input reference needs oracle/_ref/libancestry_ref.so (make -C oracle ancestry)")
+            ts = ref_ancestry.sim_ancestry(w["samples"], sequence_length=w["L"], recombination_rate=w["recomb"],
+                                           population_size=w["ne"], random_seed=w["ts_seed"])
         w["input_text"] = ("tree sequence from the reference's own sim_ancestry (Hudson, lib/msprime.c compiled "
                            "unmodified; random_seed=%d)" % w["ts_seed"])
     else:

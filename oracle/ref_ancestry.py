@@ -38,6 +38,32 @@ def _load():
     return _lib
 
 
+def cached_input_path(w):
+    """Where scripts/make_reference_input.py keeps the simulator's output for a bench workload (same trees for every
+    workload with the same ancestry arguments)."""
+    key = "n%d_L%g_r%g_ne%g_seed%d" % (w["samples"], w["L"], w["recomb"], w["ne"], w["ts_seed"])
+    return os.path.join(HERE, "_ref", "inputs", key + ".npz")
+
+
+def load_cached(w):
+    """The cached tree sequence of a bench workload, or None."""
+    path = cached_input_path(w)
+    if not os.path.exists(path):
+        return None
+    from msprime_b200 import synth
+
+    z = np.load(path)
+    left, right = z["edge_left"], z["edge_right"]
+    return {
+        "sequence_length": float(z["sequence_length"]), "time_units": "generations",
+        "nodes": {"time": z["node_time"], "flags": z["node_flags"]},
+        "edges": {"left": left, "right": right, "parent": z["edge_parent"], "child": z["edge_child"]},
+        "sites": synth.empty_sites(), "mutations": synth.empty_mutations(),
+        "num_trees": int(len(np.unique(np.concatenate([left, right]))) - 1),
+        "generator_seconds": float(z["seconds"]),
+    }
+
+
 def sim_ancestry(samples, *, sequence_length, recombination_rate, population_size, random_seed, ploidy=2,
                  discrete_genome=True):
     lib = _load()

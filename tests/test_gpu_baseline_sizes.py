@@ -33,6 +33,11 @@ def workload_input(name, source="treegen"):
     if source == "reference":
         from oracle import ref_ancestry
 
+        cached = ref_ancestry.load_cached(w)  # scripts/make_reference_input.py (configs 3-5 take minutes to hours)
+        if cached is not None:
+            return w, cached
+        if w["samples"] > 10_000:
+            pytest.skip("no cached tree sequence from the reference's simulator for this size")
         if not ref_ancestry.have():
             pytest.skip("oracle/_ref/libancestry_ref.so not built")
         return w, ref_ancestry.sim_ancestry(w["samples"], sequence_length=w["L"], recombination_rate=w["recomb"],
@@ -40,7 +45,8 @@ def workload_input(name, source="treegen"):
     return w, synth.native_treeseq(w["samples"], w["L"], w["recomb"], w["ne"], w["ts_seed"])
 
 
-@pytest.mark.parametrize("name", ["config1", "config2", "config3-16", "config1-reference", "config2-reference"])
+@pytest.mark.parametrize("name", ["config1", "config2", "config3-16", "config1-reference", "config2-reference",
+                                  "config3-16-reference"])
 def test_replay_bit_exact_at_full_size(native_built, oracle_mod, name):
     """configN-reference: the same configuration on the tree sequence the REFERENCE's Hudson simulator makes for it
     (sim_ancestry(samples, sequence_length=, recombination_rate=1e-8, population_size=1e4, random_seed=1));
@@ -49,7 +55,7 @@ def test_replay_bit_exact_at_full_size(native_built, oracle_mod, name):
     pairs for the 1000-interval map (the ~4e5 edges alive at any position each meet every interval) against
     1.5e7 here; the sequential stream walker is what bounds the size of a replay case."""
     w, ts = workload_input(name.split("-")[0], "reference" if name.endswith("-reference") else "treegen")
-    if name == "config3-16":
+    if name.startswith("config3-16"):
         w = dict(w, ratemap=16)
     L = ts["sequence_length"]
     E = len(ts["edges"]["left"])
@@ -57,7 +63,7 @@ def test_replay_bit_exact_at_full_size(native_built, oracle_mod, name):
     pos, rate = bench.rate_map(w, L)
     which = ["port"] + (["ref"] if oracle_mod.have("ref") else [])
     # one uniform or more per (edge, rate interval) pair, two per mutation, allele draws
-    n_stream = 20_000_000 if name == "config3-16" else 3 * E + 3_000_000
+    n_stream = 20_000_000 if name.startswith("config3-16") else 3 * E + 3_000_000
     base = ts
     with _native.Context(0) as ctx:
         for layer, keep in enumerate((False, True)):
@@ -93,9 +99,13 @@ def window_args(lo, hi):
     return dict(start_time=None if lo == -FMAX else lo, end_time=None if hi == FMAX else hi)
 
 
-def test_config3_native_stream_is_valid(native_built):
+SOURCES = ["treegen", "reference"]  # this project's generator / the reference's own sim_ancestry (where cached)
+
+
+@pytest.mark.parametrize("source", SOURCES)
+def test_config3_native_stream_is_valid(native_built, source):
     """GTR, 1000-interval lognormal rate map, 1e5 samples x 1e8 bp."""
-    w, ts = workload_input("config3")
+    w, ts = workload_input("config3", source)
     with _native.Context(0) as ctx:
         counts, res, (pos, rate, lo, hi) = native_overlay(ctx, ts, w, seed=31)
     assert counts["num_new_mutations"] == counts["num_mutations"] == len(res["mutations"]["site"])
@@ -120,9 +130,10 @@ def test_config3_native_stream_is_valid(native_built):
     assert set(np.unique(res["mutations"]["derived_state"]).tolist()) <= {65, 67, 71, 84}
 
 
-def test_config4_native_stream_keeps_and_adds(native_built, oracle_mod):
+@pytest.mark.parametrize("source", SOURCES)
+def test_config4_native_stream_keeps_and_adds(native_built, oracle_mod, source):
     """HKY, keep=True over an existing HKY layer, time window [1e3, 2e4), 1e5 samples x 1e8 bp."""
-    w, ts0 = workload_input("config4")
+    w, ts0 = workload_input("config4", source)
     kl = w["keep_layer"]
     L = ts0["sequence_length"]
     which = "ref" if oracle_mod.have("ref") else "port"
@@ -153,9 +164,10 @@ def test_config4_native_stream_keeps_and_adds(native_built, oracle_mod):
     assert np.all(res["mutations"]["time"][par[has]] >= res["mutations"]["time"][has])
 
 
-def test_config5_native_stream_is_valid(native_built):
+@pytest.mark.parametrize("source", SOURCES)
+def test_config5_native_stream_is_valid(native_built, source):
     """The workload bench.py times: InfiniteAlleles, rate 1e-7, 1e6 samples x 2.5e8 bp, 1.45e7 mutations."""
-    w, ts = workload_input("config5")
+    w, ts = workload_input("config5", source)
     with _native.Context(0) as ctx:
         ctx.load_tables(ts)
         L = ts["sequence_length"]
