@@ -63,6 +63,7 @@ extern "C" {
 #define MSPB_ERR_NOT_GENERATED (-1007)
 #define MSPB_ERR_UNSORTED_SITES (-1009) /* sliced call: kept sites must be sorted by position */
 #define MSPB_ERR_OFFSET_OVERFLOW (-1008) /* offsets32 asked for, but a column may reach 4 GiB */
+#define MSPB_ERR_RETRY_WITH_HOST (-1011) /* mspb_generate_finish_device after mspb_generate_begin_device: some rank needs the host between the stages; make the call again with mspb_generate_begin */
 #define MSPB_ERR_NOALLOC_TOO_LARGE (-1010) /* mspb_site_rows_noalloc: more than MSPB_NOALLOC_MAX_RECORDS records */
 
 /* the reference's three C models (lib/mutgen.c:184-237, 257-413, 431-481) */
@@ -240,6 +241,14 @@ int mspb_exchange_post_counts(mspb_ctx_t *ctx);
 int mspb_generate_end_device(mspb_ctx_t *ctx, uint32_t rank, uint32_t world);
 int mspb_generate_finish_device(mspb_ctx_t *ctx, uint32_t rank, uint32_t world, mspb_counts_t *counts,
     uint64_t *totals, uint64_t *bases);
+/* mspb_generate_begin without its closing wait (no counterpart in the reference: lib/mutgen.c has one address space):
+ * K1 .. K4 are enqueued and the call returns; mspb_exchange_post_counts then takes this rank's counts from the
+ * device, so that the host waits once per overlay, in mspb_generate_finish_device, instead of once per stage.
+ * What the host would have looked at between the stages (an error, the second sort of a dense genome, positions
+ * to draw again) is exchanged with the counts: when any rank raises it, every rank's _finish_device returns
+ * MSPB_ERR_RETRY_WITH_HOST and the caller makes the call again through mspb_generate_begin.  Not for the replay
+ * harness or the SLiM model (MSPB_ERR_BAD_PARAM_VALUE); mspb_generate_end refuses a call begun this way. */
+int mspb_generate_begin_device(mspb_ctx_t *ctx, const mspb_params_t *params);
 /* Copies the resident result to host buffers. */
 int mspb_fetch(mspb_ctx_t *ctx, const mspb_columns_t *host_columns);
 /* Bytes the last mspb_fetch moved over the bus (columns known to be all zero, i.e. the metadata

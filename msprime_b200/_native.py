@@ -111,7 +111,7 @@ EXPORTED_SYMBOLS = [
     "mspb_device_columns", "mspb_kernel_launches", "mspb_phase_ms", "mspb_phase_name",
     "mspb_sim_mutations", "mspb_columns_free", "mspb_strerror", "mspb_version", "mspb_cuda_runtime_version",
     "mspb_ctx_stream", "mspb_kernel_timing", "mspb_kernel_time", "mspb_selftest_sort",
-    "mspb_generate_begin", "mspb_generate_end", "mspb_shift_offsets",
+    "mspb_generate_begin", "mspb_generate_begin_device", "mspb_generate_end", "mspb_shift_offsets",
     "mspb_exchange_buffers", "mspb_exchange_post_counts", "mspb_generate_end_device",
     "mspb_generate_finish_device", "mspb_last_fetch_bytes", "mspb_ctx_load_tables_begin",
     "mspb_ctx_load_tables_end", "mspb_site_rows_noalloc", "mspb_ctx_build_sample_index", "mspb_samples_below",
@@ -152,6 +152,7 @@ def lib():
         L.mspb_ctx_load_tables_end.argtypes = [C.c_void_p]
         L.mspb_generate.argtypes = [C.c_void_p, C.POINTER(_Params), C.POINTER(_Counts)]
         L.mspb_generate_begin.argtypes = [C.c_void_p, C.POINTER(_Params), C.POINTER(_Counts)]
+        L.mspb_generate_begin_device.argtypes = [C.c_void_p, C.POINTER(_Params)]
         L.mspb_generate_end.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64, C.POINTER(_Counts)]
         L.mspb_shift_offsets.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64]
         L.mspb_exchange_buffers.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]
@@ -201,10 +202,20 @@ def strerror(status: int) -> str:
     return lib().mspb_strerror(int(status)).decode()
 
 
+ERR_RETRY_WITH_HOST = -1011  # MSPB_ERR_RETRY_WITH_HOST
+
+
+class RetryWithHost(LibraryError):
+    """``generate_finish_device`` after ``generate_begin_device``: some rank needs the host between the stages
+    (every rank raises this together); make the call again with ``generate_begin``."""
+
+
 def check(status: int):
     if status == 0:
         return
     msg = strerror(status)
+    if status == ERR_RETRY_WITH_HOST:
+        raise RetryWithHost(msg, status)
     if status in _RATE_MAP_ERRORS:
         raise InputError(f"Input error in mutation rate map: {msg}", status)
     raise LibraryError(msg, status)
@@ -395,6 +406,12 @@ class Context:
         check(lib().mspb_generate_begin(self._h, C.byref(params.struct), C.byref(c)))
         self.counts = {name: getattr(c, name) for name, _ in _Counts._fields_}
         return self.counts
+
+    def generate_begin_device(self, params: Params):
+        """``generate_begin`` without its wait (``mspb_generate_begin_device``): the counts stay on the device
+        until ``generate_finish_device``, which may raise :class:`RetryWithHost`."""
+        check(lib().mspb_generate_begin_device(self._h, C.byref(params.struct)))
+        self.counts = None
 
     def generate_end(self, site_base=0, mutation_base=0, allele_base=0):
         """Second phase: writes the tables with global site / mutation / allele numbering."""

@@ -83,6 +83,7 @@ struct mspb_ctx {
     std::vector<char> cache_model_bytes;
     DBuf<ChainFree> chain_free; // K5's tile prefixes without a chain (emit.cuh)
     cudaEvent_t ev_p1 = nullptr, ev_cf = nullptr; // site rows are final / the prefix table is ready
+    cudaEvent_t ev_async0 = nullptr, ev_async1 = nullptr; // around the stages of mspb_generate_begin_device
     bool tables_pending = false; // between mspb_ctx_load_tables_begin and _end
     cudaStream_t copy_stream = nullptr; // load_tables: the columns K0's sorts do not read arrive here
     cudaEvent_t ev_keys = nullptr, ev_copied = nullptr;
@@ -149,6 +150,9 @@ struct mspb_ctx {
         bool defer_resolve = false; // SLiM in a two-phase call: K4 needs the slice's id base, so it runs in _end
         uint32_t fixed_len = 0; // matrix model: the common length of all alleles, or 0
         int exchange_stage = 0; // 2: mspb_generate_end_device ran, mspb_generate_finish_device is due
+        bool async = false; // mspb_generate_begin_device: the host has not seen P1's totals yet
+        bool key32 = false; // ... and whether a "dense" flag would mean a second sort (KEY32_POS)
+        float begin_ms = 0; // device time of the _begin stage (async: read at _finish)
         SortedView sv;
         ResolveView rv;
         KeptView kept;
@@ -264,6 +268,9 @@ extern "C" const char *mspb_strerror(int err)
             return "A ragged column may exceed 4 GiB: 32-bit offsets cannot be used";
         case MSPB_ERR_NOT_GENERATED:
             return "No result is resident: call mspb_generate first";
+        case MSPB_ERR_RETRY_WITH_HOST:
+            return "A rank of this sharded call needs the host between its stages: make the call again with "
+                   "mspb_generate_begin";
         case MSPB_ERR_NOALLOC_TOO_LARGE:
             return "Input exceeds the fixed scratch of the allocation-free entry point "
                    "(more than MSPB_NOALLOC_MAX_RECORDS records)";
@@ -341,6 +348,9 @@ extern "C" int mspb_ctx_create(int device, mspb_ctx_t **out)
     }
     for (cudaEvent_t *e : { &ctx->ev_k1, &ctx->ev_keys, &ctx->ev_p1, &ctx->ev_cf, &ctx->ev_copied }) {
         events_ok = events_ok && cudaEventCreateWithFlags(e, cudaEventDisableTiming) == cudaSuccess;
+    }
+    for (cudaEvent_t *e : { &ctx->ev_async0, &ctx->ev_async1 }) {
+        events_ok = events_ok && cudaEventCreate(e) == cudaSuccess;
     }
     if (!events_ok || cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking) != cudaSuccess) {
         cudaGetLastError();
@@ -430,7 +440,8 @@ extern "C" void mspb_ctx_destroy(mspb_ctx_t *ctx)
             cudaEventDestroy(e);
         }
     }
-    for (cudaEvent_t e : { ctx->ev_k1, ctx->ev_keys, ctx->ev_copied, ctx->ev_p1, ctx->ev_cf }) {
+    for (cudaEvent_t e : { ctx->ev_k1, ctx->ev_keys, ctx->ev_copied, ctx->ev_p1, ctx->ev_cf, ctx->ev_async0,
+             ctx->ev_async1 }) {
         if (e != nullptr) {
             cudaEventDestroy(e);
         }
@@ -1473,12 +1484,14 @@ int run_sorted_stages(mspb_ctx *ctx, const mspb_params_t *p, const TreeSeqView &
 
 } // namespace
 
-static int generate_impl(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t *counts_out, bool defer)
+static int generate_impl(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t *counts_out, bool defer,
+    bool async_begin = false)
 {
     if (ctx == nullptr || p == nullptr) {
         return MSPB_ERR_BAD_PARAM_VALUE;
     }
     ctx->pending.valid = false;
+    ctx->pending.async = false;
     ctx->pending.defer = defer;
     ctx->pending.defer_resolve = false;
     ctx->pending.R = 0;
@@ -1510,7 +1523,14 @@ static int generate_impl(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t 
     HostTotals *dt = (HostTotals *) ctx->dev_totals.p;
     HostTotals *ht = ctx->host;
 
+    if (async_begin && (replay || p->model_kind == MSPB_MODEL_SLIM)) {
+        // the replay harness and the SLiM model need the host between the stages: mspb_generate_begin
+        return MSPB_ERR_BAD_PARAM_VALUE;
+    }
     CUDA_OK(cudaEventRecord(ctx->ev[0], st));
+    if (async_begin) {
+        CUDA_OK(cudaEventRecord(ctx->ev_async0, st));
+    }
     RateMapView map;
     ModelView model;
     TRY(upload_params(ctx, p, &map, &model));
@@ -1844,6 +1864,31 @@ static int generate_impl(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t 
     } else {
         TRY(run_sorted_stages(ctx, p, ts, kept, model, call, R, S0, M0, out, true));
     }
+    if (async_begin) {
+        // mspb_generate_begin_device: K3 .. K4 are enqueued and nothing is awaited.  What the host would
+        // look at here (an error, a dense genome's second sort, collisions to draw again) travels with the
+        // exchanged counts instead (xchg_pack_counts_kernel) and mspb_generate_finish_device asks for the
+        // call to be made again through mspb_generate_begin when any rank has raised it.
+        CUDA_OK(cudaEventRecord(ctx->ev_async1, st));
+        mspb_counts_t &ca = ctx->counts;
+        memset(&ca, 0, sizeof(ca));
+        ca.num_mutations = M;
+        ca.num_new_mutations = Mnew;
+        ca.offset_bytes = ow;
+        ctx->generated = false;
+        ctx->pending.valid = true;
+        ctx->pending.async = true;
+        ctx->pending.key32 = call.key_mode == KEY32_POS;
+        ctx->pending.S0 = S0;
+        ctx->pending.Mnew = Mnew;
+        ctx->pending.M = M;
+        ctx->pending.start_allele = p->start_allele;
+        ctx->pending.model_kind = p->model_kind;
+        if (counts_out != nullptr) {
+            *counts_out = ca;
+        }
+        return 0;
+    }
     TRY(totals_to_host(ctx));
     CUDA_OK(cudaStreamSynchronize(st));
     CUDA_OK(cudaGetLastError());
@@ -1967,6 +2012,11 @@ extern "C" int mspb_generate_begin(mspb_ctx_t *ctx, const mspb_params_t *p, mspb
     return generate_impl(ctx, p, counts_out, true);
 }
 
+extern "C" int mspb_generate_begin_device(mspb_ctx_t *ctx, const mspb_params_t *p)
+{
+    return generate_impl(ctx, p, nullptr, true, true);
+}
+
 extern "C" int mspb_generate_end(mspb_ctx_t *ctx, uint64_t site_base, uint64_t mutation_base, uint64_t allele_base,
     mspb_counts_t *counts_out)
 {
@@ -1975,6 +2025,9 @@ extern "C" int mspb_generate_end(mspb_ctx_t *ctx, uint64_t site_base, uint64_t m
     }
     if (!ctx->pending.valid) {
         return MSPB_ERR_NOT_GENERATED;
+    }
+    if (ctx->pending.async) {
+        return MSPB_ERR_BAD_PARAM_VALUE; // the host does not hold this call's counts: mspb_generate_end_device
     }
     CUDA_OK(cudaSetDevice(ctx->device));
     cudaStream_t st = ctx->stream;
@@ -2125,6 +2178,19 @@ __global__ void xchg_bases_kernel(const uint64_t *recv, uint32_t rank, uint32_t 
     }
 }
 
+// mspb_generate_begin_device: this rank's counts straight from the device totals.  send[4] asks every rank to
+// make the call again with the host in the loop (an error, a dense genome's second sort, positions to draw again).
+__global__ void xchg_pack_counts_kernel(const HostTotals *dt, uint64_t num_mutations, uint64_t num_new, int numbered,
+    int key32, uint64_t *send)
+{
+    send[0] = dt->p1.s;
+    send[1] = num_mutations;
+    send[2] = numbered ? dt->p1.d : 0ull;
+    send[3] = num_new;
+    send[4] = (dt->err != 0 || (dt->dense != 0u && key32) || dt->collisions != 0u) ? 1ull : 0ull;
+    send[5] = send[6] = send[7] = 0;
+}
+
 __global__ void xchg_pack_bytes_kernel(const HostTotals *dt, uint64_t *send)
 {
     send[0] = dt->bytes.anc;
@@ -2134,10 +2200,15 @@ __global__ void xchg_pack_bytes_kernel(const HostTotals *dt, uint64_t *send)
     send[4] = send[5] = send[6] = send[7] = 0;
 }
 
-__global__ void shift_offsets_dev_kernel(void *col, uint64_t n, const uint64_t *delta, int off32)
+// (n_dev: the number of rows when only the device knows it; n then bounds the grid)
+__global__ void shift_offsets_dev_kernel(void *col, uint64_t n, const uint64_t *delta, int off32,
+    const uint32_t *n_dev = nullptr)
 {
     const uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
     const uint64_t d = *delta;
+    if (n_dev != nullptr) {
+        n = (uint64_t) *n_dev + 1;
+    }
     if (i < n && d != 0) {
         if (off32) {
             static_cast<uint32_t *>(col)[i] += (uint32_t) d;
@@ -2176,6 +2247,13 @@ extern "C" int mspb_exchange_post_counts(mspb_ctx_t *ctx)
     }
     CUDA_OK(cudaSetDevice(ctx->device));
     TRY(ensure_exchange(ctx));
+    if (ctx->pending.async) {
+        MSPB_LAUNCH(ctx->log, "xchg_pack_counts",
+            xchg_pack_counts_kernel<<<1, 1, 0, ctx->stream>>>((const HostTotals *) ctx->dev_totals.p, ctx->pending.M,
+                ctx->pending.Mnew, ctx->pending.model_kind != MSPB_MODEL_MATRIX ? 1 : 0, ctx->pending.key32 ? 1 : 0,
+                ctx->xchg.p));
+        return 0;
+    }
     const mspb_counts_t &c = ctx->counts;
     uint64_t *h = ctx->xchg_host;
     memset(h, 0, XCHG_WORDS * sizeof(uint64_t));
@@ -2239,15 +2317,22 @@ extern "C" int mspb_generate_finish_device(mspb_ctx_t *ctx, uint32_t rank, uint3
     uint64_t *x = ctx->xchg.p;
     mspb_counts_t &c = ctx->counts;
     const int off32 = c.offset_bytes == 4;
-    const uint64_t S1 = c.num_sites + 1, M1 = c.num_mutations + 1;
+    const bool async = ctx->pending.async;
+    ctx->pending.async = false;
+    // (after mspb_generate_begin_device the number of sites is still on the device: the grid covers every
+    // record and the kernel reads the count)
+    const uint64_t S1 = (async ? ctx->pending.R : c.num_sites) + 1, M1 = c.num_mutations + 1;
+    const uint32_t *s_dev = async ? &((const HostTotals *) ctx->dev_totals.p)->p1.s : nullptr;
     MSPB_LAUNCH(ctx->log, "xchg_bases", xchg_bases_kernel<<<1, 32, 0, st>>>(x + XCHG_RECV, rank, world, x + XCHG_B2));
     MSPB_LAUNCH(ctx->log, "shift_offsets",
-        shift_offsets_dev_kernel<<<grid_for(S1, 256), 256, 0, st>>>(ctx->o_site_anc_off.p, S1, x + XCHG_B2 + 0, off32));
+        shift_offsets_dev_kernel<<<grid_for(S1, 256), 256, 0, st>>>(ctx->o_site_anc_off.p, S1, x + XCHG_B2 + 0, off32,
+            s_dev));
     MSPB_LAUNCH(ctx->log, "shift_offsets",
         shift_offsets_dev_kernel<<<grid_for(M1, 256), 256, 0, st>>>(ctx->o_mut_der_off.p, M1, x + XCHG_B2 + 2, off32));
     if (ctx->pending.out.write_md_off) {
         MSPB_LAUNCH(ctx->log, "shift_offsets",
-            shift_offsets_dev_kernel<<<grid_for(S1, 256), 256, 0, st>>>(ctx->o_site_md_off.p, S1, x + XCHG_B2 + 1, off32));
+            shift_offsets_dev_kernel<<<grid_for(S1, 256), 256, 0, st>>>(ctx->o_site_md_off.p, S1, x + XCHG_B2 + 1, off32,
+                s_dev));
         MSPB_LAUNCH(ctx->log, "shift_offsets",
             shift_offsets_dev_kernel<<<grid_for(M1, 256), 256, 0, st>>>(ctx->o_mut_md_off.p, M1, x + XCHG_B2 + 3, off32));
         ctx->md_zero_site_bytes = ctx->md_zero_mut_bytes = 0;
@@ -2259,10 +2344,23 @@ extern "C" int mspb_generate_finish_device(mspb_ctx_t *ctx, uint32_t rank, uint3
     CUDA_OK(cudaStreamSynchronize(st));
     CUDA_OK(cudaGetLastError());
     ctx->log.collect();
+    const uint64_t *b1 = h + XCHG_WORDS, *t1 = b1 + XCHG_WORDS, *b2 = t1 + XCHG_WORDS, *t2 = b2 + XCHG_WORDS;
+    if (async) {
+        if (t1[4] != 0) {
+            // some rank (every rank reads the same sum) met an error, a dense genome or taken positions in
+            // its _begin stage: the call is made again through mspb_generate_begin, which deals with those
+            return MSPB_ERR_RETRY_WITH_HOST;
+        }
+        float begin_ms = 0;
+        cudaEventElapsedTime(&begin_ms, ctx->ev_async0, ctx->ev_async1);
+        c.device_ms = begin_ms;
+        c.num_sites = ht->p1.s;
+        c.num_new_sites = c.num_sites - ctx->pending.S0;
+        c.next_allele = ctx->pending.start_allele + (ctx->pending.model_kind != MSPB_MODEL_MATRIX ? ht->p1.d : 0);
+    }
     if (ht->err != 0) {
         return ht->err;
     }
-    const uint64_t *b1 = h + XCHG_WORDS, *t1 = b1 + XCHG_WORDS, *b2 = t1 + XCHG_WORDS, *t2 = b2 + XCHG_WORDS;
     if (t1[0] > 0x7fffffffull || t1[1] > 0x7fffffffull) {
         return MSPB_ERR_TOO_MANY_ROWS;
     }

@@ -189,17 +189,35 @@ def load_tables_sharded(ctx, tables_dict, *, rank, world, group=None, all_gather
     ctx.load_tables_end()
 
 
-def run_slice_device(ctx, params, *, rank, world, gather, fetch=True, out=None):
+def run_slice_device(ctx, params, *, rank, world, gather, fetch=True, out=None, host_between_stages=False):
     """:func:`run_slice` with the exchange kept on the device: ``gather()`` must all-gather the
     context's send buffer into its recv buffer on the context's stream (see
-    :func:`nccl_device_allgather`).  The host waits once, at the end, instead of after every
-    stage.  ``params.start_allele`` is the global allele counter before the call."""
-    ctx.generate_begin(params)
-    ctx.exchange_post_counts()
-    gather()
-    ctx.generate_end_device(rank, world)
-    gather()
-    _, totals, bases = ctx.generate_finish_device(rank, world)
+    :func:`nccl_device_allgather`).  The host waits once per overlay, at the end: the first stage is
+    enqueued without its closing wait (``generate_begin_device``) and its counts go from the device totals
+    into the exchange.  When some rank needs the host between the stages after all (an error, a dense
+    genome's second sort, positions to draw again) every rank learns it from the exchanged counts and the
+    call is made again the slower way, all ranks together.  ``host_between_stages=True`` (or the SLiM
+    model) takes that way at once.  ``params.start_allele`` is the global allele counter before the call."""
+    from . import _native
+
+    totals = None
+    if not host_between_stages and params.struct.model_kind != 2:
+        ctx.generate_begin_device(params)
+        ctx.exchange_post_counts()
+        gather()
+        ctx.generate_end_device(rank, world)
+        gather()
+        try:
+            _, totals, bases = ctx.generate_finish_device(rank, world)
+        except _native.RetryWithHost:
+            totals = None
+    if totals is None:
+        ctx.generate_begin(params)
+        ctx.exchange_post_counts()
+        gather()
+        ctx.generate_end_device(rank, world)
+        gather()
+        _, totals, bases = ctx.generate_finish_device(rank, world)
     local = None
     if fetch:
         local = ctx.fetch(out) if out is not None else ctx.fetch()

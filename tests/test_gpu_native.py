@@ -161,11 +161,15 @@ def test_union_of_slices_equals_whole(native_built, ts_small, world, model, keep
     assert sum(a[3] for a in all1) == cw["num_new_mutations"]
 
 
+@pytest.mark.parametrize("begin", ["host", "device"])
 @pytest.mark.parametrize("world", [2, 5])
-@pytest.mark.parametrize("model,keep", [("infinite_alleles", False), ("jc69", True), ("multichar", False)])
-def test_device_exchange_equals_whole(native_built, ts_small, world, model, keep):
+@pytest.mark.parametrize("model,keep", [("infinite_alleles", False), ("jc69", True), ("multichar", False),
+                                        ("infinite_alleles", True)])
+def test_device_exchange_equals_whole(native_built, ts_small, world, model, keep, begin):
     """The exchange kept on the device (mspb_exchange_* / _end_device / _finish_device): every
-    rank is a context on this GPU and the all-gather is a device copy between their buffers."""
+    rank is a context on this GPU and the all-gather is a device copy between their buffers.
+    begin="device": the first stage returns without waiting (mspb_generate_begin_device) and the counts go
+    from the device totals into the exchange."""
     import torch
 
     ts = ts_small
@@ -194,7 +198,8 @@ def test_device_exchange_equals_whole(native_built, ts_small, world, model, keep
 
         for r, c in enumerate(ctxs):
             c.load_tables(ts)
-            c.generate_begin(_native.Params(
+            first_stage = c.generate_begin if begin == "host" else c.generate_begin_device
+            first_stage(_native.Params(
                 map_position=[0, L], map_rate=[5e-7], model=cases.native_model(mdl), discrete_genome=True,
                 keep=keep, start_time=-cases.FMAX, end_time=cases.FMAX, seed=32, slice_left=cuts[r],
                 slice_right=cuts[r + 1]))
@@ -221,6 +226,91 @@ def test_device_exchange_equals_whole(native_built, ts_small, world, model, keep
     assert totals["derived_state_bytes"] == cw["derived_state_bytes"]
     assert counts["next_allele"] == cw["next_allele"]
     assert bases["num_sites"] == sum(i[0]["num_sites"] for i in infos[:-1])
+
+
+@pytest.mark.parametrize("why", ["dense", "collisions"])
+def test_device_begin_hands_back_to_the_host(native_built, why):
+    """What the host looks at between the stages of a call -- a dense genome's second sort, positions that are
+    taken -- is raised through the exchanged counts when the first stage did not wait: every rank's
+    generate_finish_device asks for the call to be made again (RetryWithHost), and sharding.run_slice_device then
+    makes it with the host in the loop, all ranks together, with the result of the one-GPU call."""
+    import torch
+
+    world = 2
+    if why == "dense":
+        # a few positions and thousands of mutations on each: KEY32_POS reports a dense genome
+        ts = cases.four_leaf_tree()
+        kw = dict(model=cases.JC69, rate=5.0, discrete=True)
+    else:
+        # continuous genome under a discrete-looking rate: same-position draws are impossible natively, so take
+        # positions that ARE taken: a kept layer drawn from the same seed (every new position collides)
+        ts = cases.four_leaf_tree()
+        kw = dict(model=cases.BINARY, rate=2.0, discrete=False)
+    L = ts["sequence_length"]
+    keep = why == "collisions"
+    whole_ctx = _native.Context(0)
+    if keep:
+        first, _ = run(whole_ctx, ts, model=kw["model"], rate=kw["rate"], seed=61, discrete=False)
+        ts = cases.with_kept(ts, first)
+    seed = 61 if keep else 62
+    whole, cw = run(whole_ctx, ts, model=kw["model"], rate=kw["rate"], keep=keep, seed=seed, discrete=kw["discrete"])
+    whole_ctx.close()
+    cuts = sharding.slice_cuts(L, world, kw["discrete"])
+    ctxs = [_native.Context(0) for _ in range(world)]
+    try:
+        bufs = [c.exchange_tensors(world) for c in ctxs]
+
+        def gather_all():
+            torch.cuda.synchronize()
+            sends = torch.cat([b[0] for b in bufs])
+            for b in bufs:
+                b[1].copy_(sends)
+            torch.cuda.synchronize()
+
+        def params(r):
+            return _native.Params(
+                map_position=[0, L], map_rate=[kw["rate"]], model=cases.native_model(kw["model"]),
+                discrete_genome=kw["discrete"], keep=keep, start_time=-cases.FMAX, end_time=cases.FMAX, seed=seed,
+                slice_left=cuts[r], slice_right=cuts[r + 1])
+
+        for r, c in enumerate(ctxs):
+            c.load_tables(ts)
+            c.generate_begin_device(params(r))
+            c.exchange_post_counts()
+        gather_all()
+        for r, c in enumerate(ctxs):
+            c.generate_end_device(r, world)
+        gather_all()
+        asked = 0
+        for r, c in enumerate(ctxs):
+            with pytest.raises(_native.RetryWithHost):
+                c.generate_finish_device(r, world)
+            asked += 1
+        assert asked == world
+        # the call again, with the host between the stages
+        try:
+            for r, c in enumerate(ctxs):
+                c.generate_begin(params(r))
+                c.exchange_post_counts()
+        except _native.LibraryError as e:
+            # invariant slices cannot move a colliding position: the one-call path owns that case
+            assert why == "collisions" and e.status == -1004
+            return
+        gather_all()
+        for r, c in enumerate(ctxs):
+            c.generate_end_device(r, world)
+        gather_all()
+        parts = []
+        for r, c in enumerate(ctxs):
+            c.generate_finish_device(r, world)
+            parts.append(c.fetch())
+        merged = sharding.merge_slices(parts)
+    finally:
+        for c in ctxs:
+            c.close()
+    for tbl in whole:
+        for col in whole[tbl]:
+            assert np.array_equal(np.asarray(whole[tbl][col]), np.asarray(merged[tbl][col])), (tbl, col)
 
 
 def test_device_tensors_alias_the_result(ctx, ts_small):
