@@ -249,6 +249,12 @@ int mspb_generate_finish_device(mspb_ctx_t *ctx, uint32_t rank, uint32_t world, 
  * MSPB_ERR_RETRY_WITH_HOST and the caller makes the call again through mspb_generate_begin.  Not for the replay
  * harness or the SLiM model (MSPB_ERR_BAD_PARAM_VALUE); mspb_generate_end refuses a call begun this way. */
 int mspb_generate_begin_device(mspb_ctx_t *ctx, const mspb_params_t *params);
+/* The stream (cudaStream_t) the caller's next all-gather of send -> recv goes on.  Normally the context's own
+ * (mspb_ctx_stream).  After mspb_generate_begin_device of a call without kept rows under the infinite-alleles model
+ * or a matrix model with equally long alleles it is the context's second stream: the counts are final once the
+ * sites are numbered and the byte counts follow from them in closed form, so both exchanges run BESIDE the parent
+ * search (K4), the table writer (K5) starts with every base known, and no offset is shifted afterwards. */
+void *mspb_exchange_stream(const mspb_ctx_t *ctx);
 /* Copies the resident result to host buffers. */
 int mspb_fetch(mspb_ctx_t *ctx, const mspb_columns_t *host_columns);
 /* Bytes the last mspb_fetch moved over the bus (columns known to be all zero, i.e. the metadata

@@ -112,7 +112,7 @@ EXPORTED_SYMBOLS = [
     "mspb_sim_mutations", "mspb_columns_free", "mspb_strerror", "mspb_version", "mspb_cuda_runtime_version",
     "mspb_ctx_stream", "mspb_kernel_timing", "mspb_kernel_time", "mspb_selftest_sort",
     "mspb_generate_begin", "mspb_generate_begin_device", "mspb_generate_end", "mspb_shift_offsets",
-    "mspb_exchange_buffers", "mspb_exchange_post_counts", "mspb_generate_end_device",
+    "mspb_exchange_buffers", "mspb_exchange_stream", "mspb_exchange_post_counts", "mspb_generate_end_device",
     "mspb_generate_finish_device", "mspb_last_fetch_bytes", "mspb_ctx_load_tables_begin",
     "mspb_ctx_load_tables_end", "mspb_site_rows_noalloc", "mspb_ctx_build_sample_index", "mspb_samples_below",
     "mspb_site_afs", "mspb_pinned_alloc", "mspb_pinned_free", "mspb_decode_genotypes", "mspb_pinned_stats",
@@ -153,6 +153,8 @@ def lib():
         L.mspb_generate.argtypes = [C.c_void_p, C.POINTER(_Params), C.POINTER(_Counts)]
         L.mspb_generate_begin.argtypes = [C.c_void_p, C.POINTER(_Params), C.POINTER(_Counts)]
         L.mspb_generate_begin_device.argtypes = [C.c_void_p, C.POINTER(_Params)]
+        L.mspb_exchange_stream.argtypes = [C.c_void_p]
+        L.mspb_exchange_stream.restype = C.c_void_p
         L.mspb_generate_end.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64, C.POINTER(_Counts)]
         L.mspb_shift_offsets.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64]
         L.mspb_exchange_buffers.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]
@@ -412,6 +414,10 @@ class Context:
         until ``generate_finish_device``, which may raise :class:`RetryWithHost`."""
         check(lib().mspb_generate_begin_device(self._h, C.byref(params.struct)))
         self.counts = None
+
+    def exchange_stream(self):
+        """The ``cudaStream_t`` (integer) the next all-gather of the exchange buffers must be enqueued on."""
+        return int(lib().mspb_exchange_stream(self._h) or 0)
 
     def generate_end(self, site_base=0, mutation_base=0, allele_base=0):
         """Second phase: writes the tables with global site / mutation / allele numbering."""

@@ -611,32 +611,40 @@ __global__ void __launch_bounds__(K5_THREADS, 4) k5_emit_kernel(SortedView sv, R
         pre.anc = (uint64_t) pw.w[1][0] | ((uint64_t) pw.w[1][1] << 32);
         pre.smd = (uint64_t) pw.w[1][2] | ((uint64_t) pw.w[1][3] << 32);
     }
-    // ---- the offset columns, which are what needed the prefix
+    // ---- the offset columns, which are what needed the prefix (and, in a sharded call that has exchanged its
+    // byte counts before this kernel, the bytes of the slices before this one: ob)
+    Bytes4 ob = Bytes4();
+    if (out.dev_byte_bases != nullptr) {
+        ob.anc = out.dev_byte_bases[0];
+        ob.smd = out.dev_byte_bases[1];
+        ob.der = out.dev_byte_bases[2];
+        ob.mmd = out.dev_byte_bases[3];
+    }
 #pragma unroll
     for (int k = 0; k < K5_ITEMS; k++) {
         const uint32_t j = (uint32_t) k * SCAN_THREADS + threadIdx.x;
         const uint32_t m = meta[k];
         if (m & EM_HEAD) {
-            store_offset<OFF32>(out.site_anc_off, srow[k], pre.anc + s_anc[j]);
+            store_offset<OFF32>(out.site_anc_off, srow[k], ob.anc + pre.anc + s_anc[j]);
             if (out.write_md_off) {
-                store_offset<OFF32>(out.site_md_off, srow[k], pre.smd + (MD ? s_smd[j] : 0u));
+                store_offset<OFF32>(out.site_md_off, srow[k], ob.smd + pre.smd + (MD ? s_smd[j] : 0u));
             }
         }
         if (m & EM_MUT) {
             const uint32_t row = KEPT ? sv.mut_scan[base + j] : (uint32_t) (base + j);
-            store_offset<OFF32>(out.mut_der_off, row, pre.der + s_der[j]);
+            store_offset<OFF32>(out.mut_der_off, row, ob.der + pre.der + s_der[j]);
             if (out.write_md_off) {
-                store_offset<OFF32>(out.mut_md_off, row, pre.mmd + (MD ? s_mmd[j] : 0u));
+                store_offset<OFF32>(out.mut_md_off, row, ob.mmd + pre.mmd + (MD ? s_mmd[j] : 0u));
             }
         }
     }
     if (blockIdx.x + 1 == num_tiles && threadIdx.x == 0) {
         *total = pre + agg;
-        store_offset<OFF32>(out.site_anc_off, p1_total->s, pre.anc + agg.anc);
-        store_offset<OFF32>(out.mut_der_off, p1_total->m, pre.der + agg.der);
+        store_offset<OFF32>(out.site_anc_off, p1_total->s, ob.anc + pre.anc + agg.anc);
+        store_offset<OFF32>(out.mut_der_off, p1_total->m, ob.der + pre.der + agg.der);
         if (out.write_md_off) {
-            store_offset<OFF32>(out.site_md_off, p1_total->s, pre.smd + agg.smd);
-            store_offset<OFF32>(out.mut_md_off, p1_total->m, pre.mmd + agg.mmd);
+            store_offset<OFF32>(out.site_md_off, p1_total->s, ob.smd + pre.smd + agg.smd);
+            store_offset<OFF32>(out.mut_md_off, p1_total->m, ob.mmd + pre.mmd + agg.mmd);
         }
     }
     if (staged) {

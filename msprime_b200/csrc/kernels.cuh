@@ -1585,6 +1585,9 @@ struct OutView {
     // sharded calls that exchange their counts on the device: site / mutation / allele-number
     // bases are read from here (3 words) and added to the values above
     const uint64_t *dev_bases;
+    // ... and, when the byte counts were exchanged BEFORE the tables are written, the bytes of the slices before
+    // this one (ancestral, site metadata, derived, mutation metadata), added to the offset columns only
+    const uint64_t *dev_byte_bases;
     int off32; // offset columns are uint32 (else uint64)
     int write_md_off; // 0: the metadata offset columns are known to be all zero already
     int dry_run; // K5 computes the byte totals only (sizing pass of the SLiM model)

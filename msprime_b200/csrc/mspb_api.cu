@@ -151,6 +151,10 @@ struct mspb_ctx {
         uint32_t fixed_len = 0; // matrix model: the common length of all alleles, or 0
         int exchange_stage = 0; // 2: mspb_generate_end_device ran, mspb_generate_finish_device is due
         bool async = false; // mspb_generate_begin_device: the host has not seen P1's totals yet
+        // ... and both exchanges run BESIDE K4, on the second stream, because the byte counts follow from
+        // P1's totals in closed form (ChainFree): K5 then starts with every base known and nothing is shifted
+        bool early = false;
+        bool cf_ready = false; // the ChainFree table of this call is already enqueued (early exchange)
         bool key32 = false; // ... and whether a "dense" flag would mean a second sort (KEY32_POS)
         float begin_ms = 0; // device time of the _begin stage (async: read at _finish)
         SortedView sv;
@@ -1283,10 +1287,12 @@ int launch_emit(mspb_ctx *ctx)
     // its byte prefix on its own (ChainFree): the table is filled on the second stream, beside
     // K4, from the site rows P1 left.
     ctx->pending.out.chain_free = nullptr;
-    // (Single calls only: there the table is built beside K4.  A two-phase call learns its allele
-    // base after K4 has finished, so the table's ~30 us would sit on the critical path, which is
-    // more than the chain costs for a slice's tile count.)
-    if (!kept_rows && !ctx->pending.out.dry_run && R > 0 && !ctx->pending.defer
+    // (Single calls, and sharded calls whose exchanges run beside K4 (pending.early: the table is enqueued
+    // already).  Any other two-phase call learns its allele base after K4 has finished, so the table's ~30 us
+    // would sit on the critical path, which is more than the chain costs for a slice's tile count.)
+    if (ctx->pending.cf_ready) {
+        ctx->pending.out.chain_free = ctx->chain_free.p;
+    } else if (!kept_rows && !ctx->pending.out.dry_run && R > 0 && !ctx->pending.defer
         && (model_kind == MSPB_MODEL_INFINITE_ALLELES || (model_kind == MSPB_MODEL_MATRIX && ctx->pending.fixed_len > 0))) {
         TRY(ctx->chain_free.ensure(1));
         cudaStream_t cs = ctx->copy_stream;
@@ -1492,6 +1498,8 @@ static int generate_impl(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t 
     }
     ctx->pending.valid = false;
     ctx->pending.async = false;
+    ctx->pending.early = false;
+    ctx->pending.cf_ready = false;
     ctx->pending.defer = defer;
     ctx->pending.defer_resolve = false;
     ctx->pending.R = 0;
@@ -1809,6 +1817,7 @@ static int generate_impl(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t 
     out.site_base = 0;
     out.mut_base = 0;
     out.dev_bases = nullptr;
+    out.dev_byte_bases = nullptr;
     out.dry_run = 0;
     out.chain_free = nullptr;
     // matrix models whose alleles all have one (non-zero) length: state bytes = rows x length
@@ -1878,6 +1887,9 @@ static int generate_impl(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t 
         ctx->generated = false;
         ctx->pending.valid = true;
         ctx->pending.async = true;
+        ctx->pending.early = S0 + M0 == 0 && R > 0
+                             && (p->model_kind == MSPB_MODEL_INFINITE_ALLELES
+                                 || (p->model_kind == MSPB_MODEL_MATRIX && ctx->pending.fixed_len > 0));
         ctx->pending.key32 = call.key_mode == KEY32_POS;
         ctx->pending.S0 = S0;
         ctx->pending.Mnew = Mnew;
@@ -2191,6 +2203,22 @@ __global__ void xchg_pack_counts_kernel(const HostTotals *dt, uint64_t num_mutat
     send[5] = send[6] = send[7] = 0;
 }
 
+// early exchange: this rank's byte counts from the ChainFree table (before any byte is written).  send[4]: the
+// closed form does not apply (allele numbers wrap around 2^64, or the genome is dense): back to the host-paced call
+__global__ void xchg_pack_bytes_cf_kernel(const ChainFree *cf, const Counts3 *p1, uint64_t n, uint64_t *send)
+{
+    uint64_t der = 0, anc = 0;
+    if (cf->enabled != 0u) {
+        cf->prefix(n, p1->s, &der, &anc);
+    }
+    send[0] = anc;
+    send[1] = 0;
+    send[2] = der;
+    send[3] = 0;
+    send[4] = cf->enabled != 0u ? 0ull : 1ull;
+    send[5] = send[6] = send[7] = 0;
+}
+
 __global__ void xchg_pack_bytes_kernel(const HostTotals *dt, uint64_t *send)
 {
     send[0] = dt->bytes.anc;
@@ -2231,6 +2259,16 @@ extern "C" int mspb_exchange_buffers(mspb_ctx_t *ctx, void **send, void **recv)
     return 0;
 }
 
+/* the stream the caller's next all-gather goes on: the context's own, or its second stream while the exchanges
+ * of a call begun with mspb_generate_begin_device run beside K4 */
+extern "C" void *mspb_exchange_stream(const mspb_ctx_t *ctx)
+{
+    if (ctx == nullptr) {
+        return nullptr;
+    }
+    return (void *) ((ctx->pending.async && ctx->pending.early) ? ctx->copy_stream : ctx->stream);
+}
+
 /* after mspb_generate_begin: puts this rank's (sites, mutations, allele numbers used, new
  * mutations) into the send buffer, on the stream */
 extern "C" int mspb_exchange_post_counts(mspb_ctx_t *ctx)
@@ -2248,10 +2286,17 @@ extern "C" int mspb_exchange_post_counts(mspb_ctx_t *ctx)
     CUDA_OK(cudaSetDevice(ctx->device));
     TRY(ensure_exchange(ctx));
     if (ctx->pending.async) {
-        MSPB_LAUNCH(ctx->log, "xchg_pack_counts",
-            xchg_pack_counts_kernel<<<1, 1, 0, ctx->stream>>>((const HostTotals *) ctx->dev_totals.p, ctx->pending.M,
-                ctx->pending.Mnew, ctx->pending.model_kind != MSPB_MODEL_MATRIX ? 1 : 0, ctx->pending.key32 ? 1 : 0,
-                ctx->xchg.p));
+        cudaStream_t ps = ctx->stream;
+        if (ctx->pending.early) {
+            // the counts are final once P1 is through: this exchange and the next run beside K4
+            ps = ctx->copy_stream;
+            CUDA_OK(cudaStreamWaitEvent(ps, ctx->ev_p1, 0));
+        }
+        xchg_pack_counts_kernel<<<1, 1, 0, ps>>>((const HostTotals *) ctx->dev_totals.p, ctx->pending.M,
+            ctx->pending.Mnew, ctx->pending.model_kind != MSPB_MODEL_MATRIX ? 1 : 0, ctx->pending.key32 ? 1 : 0,
+            ctx->xchg.p);
+        ctx->log.count++;
+        CUDA_OK(cudaGetLastError());
         return 0;
     }
     const mspb_counts_t &c = ctx->counts;
@@ -2282,6 +2327,22 @@ extern "C" int mspb_generate_end_device(mspb_ctx_t *ctx, uint32_t rank, uint32_t
     uint64_t *x = ctx->xchg.p;
     ctx->pending.valid = false;
     CUDA_OK(cudaEventRecord(ctx->ev[0], st));
+    if (ctx->pending.early) {
+        // beside K4, on the second stream: bases of the first exchange, the ChainFree table with this slice's
+        // allele base, this slice's byte counts from it.  K5 is launched by _finish_device.
+        cudaStream_t xs = ctx->copy_stream;
+        TRY(ctx->chain_free.ensure(1));
+        xchg_bases_kernel<<<1, 32, 0, xs>>>(x + XCHG_RECV, rank, world, x + XCHG_B1);
+        k5_prefix_table_kernel<<<1, 32, 0, xs>>>(ctx->pending.sv.site_row, &dt->p1, ctx->pending.R,
+            ctx->pending.start_allele, x + XCHG_B1,
+            ctx->pending.model_kind == MSPB_MODEL_MATRIX ? ctx->pending.fixed_len : 0u, &dt->dense, ctx->chain_free.p);
+        xchg_pack_bytes_cf_kernel<<<1, 1, 0, xs>>>(ctx->chain_free.p, &dt->p1, ctx->pending.R, x);
+        ctx->log.count += 3;
+        CUDA_OK(cudaGetLastError());
+        ctx->pending.cf_ready = true;
+        ctx->pending.exchange_stage = 2;
+        return 0;
+    }
     MSPB_LAUNCH(ctx->log, "xchg_bases", xchg_bases_kernel<<<1, 32, 0, st>>>(x + XCHG_RECV, rank, world, x + XCHG_B1));
     ctx->pending.out.site_base = 0;
     ctx->pending.out.mut_base = 0;
@@ -2323,6 +2384,26 @@ extern "C" int mspb_generate_finish_device(mspb_ctx_t *ctx, uint32_t rank, uint3
     // record and the kernel reads the count)
     const uint64_t S1 = (async ? ctx->pending.R : c.num_sites) + 1, M1 = c.num_mutations + 1;
     const uint32_t *s_dev = async ? &((const HostTotals *) ctx->dev_totals.p)->p1.s : nullptr;
+    const bool early = ctx->pending.early;
+    ctx->pending.early = false;
+    if (early) {
+        // both exchanges are through (second stream): K5 writes ids, allele numbers and byte offsets with their
+        // global bases, and nothing is shifted afterwards
+        cudaStream_t xs = ctx->copy_stream;
+        xchg_bases_kernel<<<1, 32, 0, xs>>>(x + XCHG_RECV, rank, world, x + XCHG_B2);
+        ctx->log.count++;
+        CUDA_OK(cudaEventRecord(ctx->ev_cf, xs));
+        CUDA_OK(cudaStreamWaitEvent(st, ctx->ev_cf, 0));
+        ctx->pending.out.site_base = 0;
+        ctx->pending.out.mut_base = 0;
+        ctx->pending.out.dev_bases = x + XCHG_B1;
+        ctx->pending.out.dev_byte_bases = x + XCHG_B2;
+        ctx->pending.model.start_allele = ctx->pending.start_allele;
+        TRY(launch_emit(ctx));
+        ctx->pending.out.dev_bases = nullptr;
+        ctx->pending.out.dev_byte_bases = nullptr;
+        ctx->pending.cf_ready = false;
+    } else {
     MSPB_LAUNCH(ctx->log, "xchg_bases", xchg_bases_kernel<<<1, 32, 0, st>>>(x + XCHG_RECV, rank, world, x + XCHG_B2));
     MSPB_LAUNCH(ctx->log, "shift_offsets",
         shift_offsets_dev_kernel<<<grid_for(S1, 256), 256, 0, st>>>(ctx->o_site_anc_off.p, S1, x + XCHG_B2 + 0, off32,
@@ -2337,6 +2418,7 @@ extern "C" int mspb_generate_finish_device(mspb_ctx_t *ctx, uint32_t rank, uint3
             shift_offsets_dev_kernel<<<grid_for(M1, 256), 256, 0, st>>>(ctx->o_mut_md_off.p, M1, x + XCHG_B2 + 3, off32));
         ctx->md_zero_site_bytes = ctx->md_zero_mut_bytes = 0;
     }
+    }
     uint64_t *h = ctx->xchg_host;
     CUDA_OK(cudaMemcpyAsync(h + XCHG_WORDS, x + XCHG_B1, 4 * XCHG_WORDS * sizeof(uint64_t), cudaMemcpyDeviceToHost, st));
     TRY(totals_to_host(ctx));
@@ -2346,7 +2428,7 @@ extern "C" int mspb_generate_finish_device(mspb_ctx_t *ctx, uint32_t rank, uint3
     ctx->log.collect();
     const uint64_t *b1 = h + XCHG_WORDS, *t1 = b1 + XCHG_WORDS, *b2 = t1 + XCHG_WORDS, *t2 = b2 + XCHG_WORDS;
     if (async) {
-        if (t1[4] != 0) {
+        if (t1[4] != 0 || t2[4] != 0) {
             // some rank (every rank reads the same sum) met an error, a dense genome or taken positions in
             // its _begin stage: the call is made again through mspb_generate_begin, which deals with those
             return MSPB_ERR_RETRY_WITH_HOST;

@@ -146,15 +146,19 @@ def run_slice(engine, params, *, rank, world, allgather, start_allele=0, fetch=T
 
 def nccl_device_allgather(ctx, world, group=None):
     """``gather()`` for :func:`run_slice_device`: all-gathers the context's send buffer into
-    its recv buffer with NCCL, enqueued on the context's own stream (no host wait)."""
+    its recv buffer with NCCL, enqueued on the stream the context names (no host wait)."""
     import torch
     import torch.distributed as dist
 
     send, recv = ctx.exchange_tensors(world)
-    stream = torch.cuda.ExternalStream(ctx.stream(), device=send.device)
+    streams = {}
 
     def gather():
-        with torch.cuda.stream(stream):
+        # the context's own stream, or its second one while a call's exchanges run beside K4
+        handle = ctx.exchange_stream()
+        if handle not in streams:
+            streams[handle] = torch.cuda.ExternalStream(handle, device=send.device)
+        with torch.cuda.stream(streams[handle]):
             dist.all_gather_into_tensor(recv, send, group=group)
 
     return gather

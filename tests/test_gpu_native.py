@@ -164,7 +164,7 @@ def test_union_of_slices_equals_whole(native_built, ts_small, world, model, keep
 @pytest.mark.parametrize("begin", ["host", "device"])
 @pytest.mark.parametrize("world", [2, 5])
 @pytest.mark.parametrize("model,keep", [("infinite_alleles", False), ("jc69", True), ("multichar", False),
-                                        ("infinite_alleles", True)])
+                                        ("infinite_alleles", True), ("jc69", False)])
 def test_device_exchange_equals_whole(native_built, ts_small, world, model, keep, begin):
     """The exchange kept on the device (mspb_exchange_* / _end_device / _finish_device): every
     rank is a context on this GPU and the all-gather is a device copy between their buffers.
