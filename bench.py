@@ -660,20 +660,32 @@ def run_b200_arm(args, rank, local_rank, world):
     wall0 = time.perf_counter()
     ev2.record(stream)
     e2e_muts = 0
+    e2e_phase = {"load_tables": 0.0, "overlay": 0.0, "fetch": 0.0}  # host wall seconds (every phase ends in a wait)
     for i in range(args.steps):
+        t0 = time.perf_counter()
         load()
-        e2e_muts += overlay(300 + i, out_bufs)
+        t1 = time.perf_counter()
+        e2e_muts += overlay(300 + i)
+        t2 = time.perf_counter()
+        ctx.fetch(out_bufs)
+        t3 = time.perf_counter()
+        e2e_phase["load_tables"] += t1 - t0
+        e2e_phase["overlay"] += t2 - t1
+        e2e_phase["fetch"] += t3 - t2
         sizes = ctx.result_sizes()
         d2h_bytes = ctx.last_fetch_bytes()  # what crossed the bus (all-zero metadata offsets are not copied)
     ev3.record(stream)
     sync_all()
     wall = time.perf_counter() - wall0
+    # per phase, the slowest rank's average (the phases of different ranks overlap, so they need not add up)
+    e2e_phase_ms = {k: reduce(1e3 * v / args.steps, dist.ReduceOp.MAX if world > 1 else None)
+                    for k, v in e2e_phase.items()}
     e2e_ms = reduce(max(ev2.elapsed_time(ev3), wall * 1e3), dist.ReduceOp.MAX if world > 1 else None)
     e2e_total = reduce(float(e2e_muts), dist.ReduceOp.SUM if world > 1 else None)
     e2e_value = e2e_total / (e2e_ms * 1e-3)
     h2d_total = reduce(float(h2d_bytes), dist.ReduceOp.SUM if world > 1 else None)
     d2h_total = reduce(float(d2h_bytes), dist.ReduceOp.SUM if world > 1 else None)
-    e2e_serial = {"value": e2e_value, "ms_per_step": e2e_ms / args.steps}
+    e2e_serial = {"value": e2e_value, "ms_per_step": e2e_ms / args.steps, "phases_ms_slowest_rank": e2e_phase_ms}
 
     # ---- the same calls with several overlays in flight (N = 1): PCIe is full duplex and the copy engines
     # run beside the kernels, so step i + 1 uploads while step i computes and step i - 1 downloads.  Every step
