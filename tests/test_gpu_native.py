@@ -166,6 +166,18 @@ def test_union_of_slices_equals_whole(native_built, ts_small, world, model, keep
 @pytest.mark.parametrize("model,keep", [("infinite_alleles", False), ("jc69", True), ("multichar", False),
                                         ("infinite_alleles", True), ("jc69", False)])
 def test_device_exchange_equals_whole(native_built, ts_small, world, model, keep, begin):
+    device_exchange_case(ts_small, world, model, keep, begin, 5e-7)
+
+
+@pytest.mark.parametrize("begin", ["host", "device"])
+@pytest.mark.parametrize("model", ["infinite_alleles", "jc69", "multichar"])
+def test_device_exchange_with_empty_slices(native_built, ts_small, model, begin):
+    """A handful of mutations over eight slices: some ranks have nothing to write (and take the plain order of
+    stages while their neighbours run the exchanges beside K4)."""
+    device_exchange_case(ts_small, 8, model, False, begin, 1e-10)
+
+
+def device_exchange_case(ts_small, world, model, keep, begin, rate):
     """The exchange kept on the device (mspb_exchange_* / _end_device / _finish_device): every
     rank is a context on this GPU and the all-gather is a device copy between their buffers.
     begin="device": the first stage returns without waiting (mspb_generate_begin_device) and the counts go
@@ -177,11 +189,11 @@ def test_device_exchange_equals_whole(native_built, ts_small, world, model, keep
     mdl = cases.MODELS[model]
     whole_ctx = _native.Context(0)
     if keep:
-        first, _ = run(whole_ctx, ts, model=mdl, rate=5e-7, seed=31)
+        first, _ = run(whole_ctx, ts, model=mdl, rate=rate, seed=31)
         ts = cases.with_kept(ts, first)
     start = 77 if model == "infinite_alleles" else 0
     mdl = dict(mdl, start_allele=start) if model == "infinite_alleles" else mdl
-    whole, cw = run(whole_ctx, ts, model=mdl, rate=5e-7, keep=keep, seed=32)
+    whole, cw = run(whole_ctx, ts, model=mdl, rate=rate, keep=keep, seed=32)
     whole_ctx.close()
     cuts = sharding.slice_cuts(L, world)
     ctxs = [_native.Context(0) for _ in range(world)]
@@ -200,7 +212,7 @@ def test_device_exchange_equals_whole(native_built, ts_small, world, model, keep
             c.load_tables(ts)
             first_stage = c.generate_begin if begin == "host" else c.generate_begin_device
             first_stage(_native.Params(
-                map_position=[0, L], map_rate=[5e-7], model=cases.native_model(mdl), discrete_genome=True,
+                map_position=[0, L], map_rate=[rate], model=cases.native_model(mdl), discrete_genome=True,
                 keep=keep, start_time=-cases.FMAX, end_time=cases.FMAX, seed=32, slice_left=cuts[r],
                 slice_right=cuts[r + 1]))
             c.exchange_post_counts()
