@@ -460,7 +460,7 @@ def python_call_timing(ts, w, map_pos, map_rate, device):
 
     walls, pool = [], []
     out = None
-    for i in range(8):  # the first calls create the context, size its buffers and pin the result blocks
+    for i in range(14):  # the first calls create the context, size its buffers and pin the result blocks
         t0 = time.perf_counter()
         out = msp.sim_mutations(tsobj, random_seed=11 + i, **kw)
         walls.append(time.perf_counter() - t0)

@@ -283,10 +283,15 @@ const char *mspb_phase_name(int phase);
 int mspb_selftest_sort(mspb_ctx_t *ctx, uint64_t n, int key_bytes, uint64_t key_mask, uint64_t seed,
     int measure_bits, int *passes);
 
-/* One-shot form with the semantics of _msprime.sim_mutations: host tables in,
- * malloc'd host columns out (release with mspb_columns_free). */
+/* One-shot form with the semantics of _msprime.sim_mutations: host tables in, library-owned host columns
+ * out (page-locked blocks of the library's pool where pinning succeeds, malloc otherwise: release them with
+ * mspb_columns_free, never with free).  Calls on one device are serialised and share one context, which stays
+ * alive between calls with its device buffers (a bench-size overlay holds several GB; allocating them per call
+ * took most of the call): mspb_oneshot_release(device) frees it (device < 0: every device).  Tables in pageable
+ * memory are staged through the pinned pool by a few host threads (mspb_ctx_load_tables does the same). */
 int mspb_sim_mutations(int device, const mspb_tables_t *tables, const mspb_params_t *params,
     mspb_counts_t *counts, mspb_columns_t *out);
+void mspb_oneshot_release(int device);
 void mspb_columns_free(mspb_columns_t *cols);
 
 /* Pinned host memory from a pool (no reference counterpart): result columns copied into pinned buffers arrive at

@@ -109,7 +109,7 @@ class _Columns(C.Structure):
 EXPORTED_SYMBOLS = [
     "mspb_ctx_create", "mspb_ctx_destroy", "mspb_ctx_load_tables", "mspb_generate", "mspb_fetch",
     "mspb_device_columns", "mspb_kernel_launches", "mspb_phase_ms", "mspb_phase_name",
-    "mspb_sim_mutations", "mspb_columns_free", "mspb_strerror", "mspb_version", "mspb_cuda_runtime_version",
+    "mspb_sim_mutations", "mspb_oneshot_release", "mspb_columns_free", "mspb_strerror", "mspb_version", "mspb_cuda_runtime_version",
     "mspb_ctx_stream", "mspb_kernel_timing", "mspb_kernel_time", "mspb_selftest_sort",
     "mspb_generate_begin", "mspb_generate_begin_device", "mspb_generate_end", "mspb_shift_offsets",
     "mspb_exchange_buffers", "mspb_exchange_stream", "mspb_exchange_post_counts", "mspb_generate_end_device",
@@ -186,6 +186,8 @@ def lib():
                                          C.POINTER(_Columns)]
         L.mspb_columns_free.argtypes = [C.POINTER(_Columns)]
         L.mspb_columns_free.restype = None
+        L.mspb_oneshot_release.argtypes = [C.c_int]
+        L.mspb_oneshot_release.restype = None
         L.mspb_site_rows_noalloc.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]
         L.mspb_ctx_build_sample_index.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64),
                                                   C.POINTER(C.c_uint64), C.POINTER(C.c_double)]

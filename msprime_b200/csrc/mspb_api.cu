@@ -8,7 +8,10 @@
 #include <cstring>
 #include <cmath>
 #include <cfloat>
+#include <map>
+#include <mutex>
 #include <new>
+#include <thread>
 #include <vector>
 
 #include "../../include/msprime_b200.h"
@@ -312,12 +315,90 @@ static inline unsigned grid_for(uint64_t n, unsigned threads)
     return (unsigned) ((n + threads - 1) / threads);
 }
 
+extern "C" void *mspb_pinned_alloc(uint64_t bytes);
+extern "C" void mspb_pinned_free(void *p);
+
+// ---------------------------------------------------------------- uploads from pageable memory
+// A cudaMemcpyAsync from pageable memory is staged by the driver on one thread at ~10 GB/s (25 ms for the
+// 272 MB of a bench-size tree sequence, against 5 ms of DMA).  While a StageScope lives on the calling thread,
+// large columns that are NOT page-locked are copied into blocks of the pinned pool by a few host threads first
+// and go to the device from there; the scope returns the blocks to the pool when it ends, which must be after
+// the streams have been drained (declare it BEFORE the StreamDrain of the function).
+struct StageScope {
+    std::vector<void *> blocks;
+    StageScope *outer;
+    static StageScope *&current()
+    {
+        static thread_local StageScope *cur = nullptr;
+        return cur;
+    }
+    StageScope() : outer(current())
+    {
+        current() = this;
+    }
+    ~StageScope()
+    {
+        for (void *b : blocks) {
+            mspb_pinned_free(b);
+        }
+        current() = outer;
+    }
+};
+
+constexpr size_t STAGE_MIN_BYTES = 4u << 20, STAGE_CHUNK_BYTES = 2u << 20;
+constexpr unsigned STAGE_MAX_THREADS = 8;
+
+// the source as the device will read it: `src` itself when it is page-locked (or small, or no scope is
+// open), else a pinned copy of it
+static const void *staged_source(const void *src, size_t bytes)
+{
+    StageScope *scope = StageScope::current();
+    if (scope == nullptr || bytes < STAGE_MIN_BYTES) {
+        return src;
+    }
+    cudaPointerAttributes attr;
+    if (cudaPointerGetAttributes(&attr, src) != cudaSuccess) {
+        cudaGetLastError();
+        return src;
+    }
+    if (attr.type != cudaMemoryTypeUnregistered) {
+        return src;
+    }
+    char *stage = (char *) mspb_pinned_alloc(bytes);
+    if (stage == nullptr) {
+        return src;
+    }
+    scope->blocks.push_back(stage);
+    unsigned threads = std::thread::hardware_concurrency();
+    threads = threads == 0 ? 1 : (threads > STAGE_MAX_THREADS ? STAGE_MAX_THREADS : threads);
+    const size_t chunks = (bytes + STAGE_CHUNK_BYTES - 1) / STAGE_CHUNK_BYTES;
+    if ((size_t) threads > chunks) {
+        threads = (unsigned) chunks;
+    }
+    auto work = [=](unsigned k) {
+        for (size_t c = k; c < chunks; c += threads) {
+            const size_t off = c * STAGE_CHUNK_BYTES;
+            const size_t len = off + STAGE_CHUNK_BYTES <= bytes ? STAGE_CHUNK_BYTES : bytes - off;
+            memcpy(stage + off, (const char *) src + off, len);
+        }
+    };
+    std::vector<std::thread> pool;
+    for (unsigned k = 1; k < threads; k++) {
+        pool.emplace_back(work, k);
+    }
+    work(0);
+    for (std::thread &t : pool) {
+        t.join();
+    }
+    return stage;
+}
+
 template <typename T>
 static int upload(DBuf<T> &dst, const T *src, size_t n, cudaStream_t st)
 {
     TRY(dst.ensure(n > 0 ? n : 1));
     if (n > 0) {
-        CUDA_OK(cudaMemcpyAsync(dst.p, src, n * sizeof(T), cudaMemcpyHostToDevice, st));
+        CUDA_OK(cudaMemcpyAsync(dst.p, staged_source(src, n * sizeof(T)), n * sizeof(T), cudaMemcpyHostToDevice, st));
     }
     return 0;
 }
@@ -884,6 +965,7 @@ extern "C" int mspb_ctx_load_tables(mspb_ctx_t *ctx, const mspb_tables_t *t)
     CUDA_OK(cudaSetDevice(ctx->device));
     cudaStream_t st = ctx->stream;
     TRY(tables_prepare(ctx, t));
+    StageScope staging; // (ends after the drain below)
     StreamDrain drain { st, ctx->copy_stream };
     // The two columns K0's sorts read go first, on the main stream; everything else follows on
     // the copy stream, so that with pinned sources the sorts run under the rest of the upload.
@@ -2560,59 +2642,112 @@ extern "C" uint64_t mspb_last_fetch_bytes(const mspb_ctx_t *ctx)
     return ctx != nullptr ? ctx->last_fetch_bytes : 0;
 }
 
+namespace {
+bool pinned_pool_owns(void *p);
+void host_column_free(void *p)
+{
+    if (p == nullptr) {
+        return;
+    }
+    if (pinned_pool_owns(p)) {
+        mspb_pinned_free(p);
+    } else {
+        free(p);
+    }
+}
+} // namespace
+
 extern "C" void mspb_columns_free(mspb_columns_t *c)
 {
     if (c == nullptr) {
         return;
     }
-    free(c->site_position);
-    free(c->site_ancestral_state);
-    free(c->site_ancestral_state_offset);
-    free(c->site_metadata);
-    free(c->site_metadata_offset);
-    free(c->mutation_site);
-    free(c->mutation_node);
-    free(c->mutation_parent);
-    free(c->mutation_time);
-    free(c->mutation_derived_state);
-    free(c->mutation_derived_state_offset);
-    free(c->mutation_metadata);
-    free(c->mutation_metadata_offset);
+    host_column_free(c->site_position);
+    host_column_free(c->site_ancestral_state);
+    host_column_free(c->site_ancestral_state_offset);
+    host_column_free(c->site_metadata);
+    host_column_free(c->site_metadata_offset);
+    host_column_free(c->mutation_site);
+    host_column_free(c->mutation_node);
+    host_column_free(c->mutation_parent);
+    host_column_free(c->mutation_time);
+    host_column_free(c->mutation_derived_state);
+    host_column_free(c->mutation_derived_state_offset);
+    host_column_free(c->mutation_metadata);
+    host_column_free(c->mutation_metadata_offset);
     memset(c, 0, sizeof(*c));
+}
+
+// The one-shot call keeps ONE context per device between calls (the buffers of a bench-size overlay are several
+// GB of device memory: allocating and freeing them took most of a call) and serialises the calls on it;
+// mspb_oneshot_release gives the memory back.  The output columns come from the pinned pool (a download into
+// fresh pageable memory runs at a tenth of the link's rate); mspb_columns_free returns them to it.
+namespace {
+constexpr int ONESHOT_MAX_DEVICES = 64;
+std::mutex g_oneshot_mutex[ONESHOT_MAX_DEVICES];
+mspb_ctx_t *g_oneshot_ctx[ONESHOT_MAX_DEVICES] = {};
+
+void *host_column(uint64_t bytes)
+{
+    void *p = mspb_pinned_alloc(bytes);
+    return p != nullptr ? p : malloc((size_t) bytes);
+}
+} // namespace
+
+extern "C" void mspb_oneshot_release(int device)
+{
+    for (int d = 0; d < ONESHOT_MAX_DEVICES; d++) {
+        if (device >= 0 && d != device) {
+            continue;
+        }
+        std::lock_guard<std::mutex> lock(g_oneshot_mutex[d]);
+        if (g_oneshot_ctx[d] != nullptr) {
+            mspb_ctx_destroy(g_oneshot_ctx[d]);
+            g_oneshot_ctx[d] = nullptr;
+        }
+    }
 }
 
 extern "C" int mspb_sim_mutations(int device, const mspb_tables_t *tables, const mspb_params_t *params,
     mspb_counts_t *counts, mspb_columns_t *out)
 {
-    mspb_ctx_t *ctx = nullptr;
     mspb_counts_t c;
     if (tables == nullptr || params == nullptr || out == nullptr) {
         return MSPB_ERR_BAD_PARAM_VALUE;
     }
     memset(out, 0, sizeof(*out));
-    int ret = mspb_ctx_create(device, &ctx);
-    if (ret != 0) {
-        return ret;
+    if (device < 0 || device >= ONESHOT_MAX_DEVICES) {
+        return MSPB_ERR_NO_DEVICE;
     }
+    std::lock_guard<std::mutex> lock(g_oneshot_mutex[device]);
+    int ret = 0;
+    if (g_oneshot_ctx[device] == nullptr) {
+        ret = mspb_ctx_create(device, &g_oneshot_ctx[device]);
+        if (ret != 0) {
+            g_oneshot_ctx[device] = nullptr;
+            return ret;
+        }
+    }
+    mspb_ctx_t *ctx = g_oneshot_ctx[device];
     ret = mspb_ctx_load_tables(ctx, tables);
     if (ret == 0) {
         ret = mspb_generate(ctx, params, &c);
     }
     if (ret == 0) {
         const uint64_t S = c.num_sites, M = c.num_mutations;
-        out->site_position = (double *) malloc((S + 1) * sizeof(double));
-        out->site_ancestral_state = (char *) malloc(c.ancestral_state_bytes + 1);
-        out->site_ancestral_state_offset = malloc((S + 1) * sizeof(uint64_t));
-        out->site_metadata = (char *) malloc(c.site_metadata_bytes + 1);
-        out->site_metadata_offset = malloc((S + 1) * sizeof(uint64_t));
-        out->mutation_site = (int32_t *) malloc((M + 1) * sizeof(int32_t));
-        out->mutation_node = (int32_t *) malloc((M + 1) * sizeof(int32_t));
-        out->mutation_parent = (int32_t *) malloc((M + 1) * sizeof(int32_t));
-        out->mutation_time = (double *) malloc((M + 1) * sizeof(double));
-        out->mutation_derived_state = (char *) malloc(c.derived_state_bytes + 1);
-        out->mutation_derived_state_offset = malloc((M + 1) * sizeof(uint64_t));
-        out->mutation_metadata = (char *) malloc(c.mutation_metadata_bytes + 1);
-        out->mutation_metadata_offset = malloc((M + 1) * sizeof(uint64_t));
+        out->site_position = (double *) host_column((S + 1) * sizeof(double));
+        out->site_ancestral_state = (char *) host_column(c.ancestral_state_bytes + 1);
+        out->site_ancestral_state_offset = host_column((S + 1) * sizeof(uint64_t));
+        out->site_metadata = (char *) host_column(c.site_metadata_bytes + 1);
+        out->site_metadata_offset = host_column((S + 1) * sizeof(uint64_t));
+        out->mutation_site = (int32_t *) host_column((M + 1) * sizeof(int32_t));
+        out->mutation_node = (int32_t *) host_column((M + 1) * sizeof(int32_t));
+        out->mutation_parent = (int32_t *) host_column((M + 1) * sizeof(int32_t));
+        out->mutation_time = (double *) host_column((M + 1) * sizeof(double));
+        out->mutation_derived_state = (char *) host_column(c.derived_state_bytes + 1);
+        out->mutation_derived_state_offset = host_column((M + 1) * sizeof(uint64_t));
+        out->mutation_metadata = (char *) host_column(c.mutation_metadata_bytes + 1);
+        out->mutation_metadata_offset = host_column((M + 1) * sizeof(uint64_t));
         if (!out->site_position || !out->site_ancestral_state || !out->site_ancestral_state_offset
             || !out->site_metadata || !out->site_metadata_offset || !out->mutation_site || !out->mutation_node
             || !out->mutation_parent || !out->mutation_time || !out->mutation_derived_state
@@ -2627,7 +2762,11 @@ extern "C" int mspb_sim_mutations(int device, const mspb_tables_t *tables, const
             *counts = c;
         }
     }
-    mspb_ctx_destroy(ctx);
+    if (ret != 0) {
+        // whatever went wrong, the next call starts from a fresh context
+        mspb_ctx_destroy(ctx);
+        g_oneshot_ctx[device] = nullptr;
+    }
     return ret;
 }
 
@@ -2715,8 +2854,6 @@ extern "C" int mspb_selftest_sort(mspb_ctx_t *ctx, uint64_t n, int key_bytes, ui
 // want their result columns in buffers of their own lifetime take them from this pool: blocks are pinned once
 // and handed out again after mspb_pinned_free (the Python layer frees a block when the numpy array over it is
 // collected), so a steady caller allocates nothing.
-#include <mutex>
-
 namespace {
 
 std::mutex g_pinned_mutex;
@@ -2726,6 +2863,14 @@ size_t g_pinned_cached_bytes = 0;
 uint64_t g_pinned_stats[4] = { 0, 0, 0, 0 }; // blocks pinned, blocks reused, bytes pinned so far, blocks unpinned
 constexpr size_t PINNED_CACHE_LIMIT = 16ull << 30; // free blocks kept pinned at most
 
+} // namespace
+
+namespace {
+bool pinned_pool_owns(void *p)
+{
+    std::lock_guard<std::mutex> lock(g_pinned_mutex);
+    return g_pinned_live.find(p) != g_pinned_live.end();
+}
 } // namespace
 
 extern "C" void *mspb_pinned_alloc(uint64_t bytes)
