@@ -503,6 +503,36 @@ def python_call_timing(ts, w, map_pos, map_rate, device):
             "tree_sequence": "msprime_b200.tables stand-in (tskit is not installed here)"}
 
 
+def oneshot_call_timing(ts, w, map_pos, map_rate, device):
+    """Wall time of `mspb_sim_mutations`, the ONE call INTEGRATION.md's stub binds where the reference calls
+    mutgen_alloc .. mutgen_generate (msprime/_msprimemodule.c:3047-3120): tables in PAGEABLE host memory in,
+    library-owned host columns out, released with mspb_columns_free."""
+    import ctypes as C
+
+    from msprime_b200 import _native
+
+    lib = _native.lib()
+    t, hold = _native.Context._tables_struct(ts)
+    lo, hi = time_window(w)
+    walls, new = [], 0
+    for i in range(8):
+        p = _native.Params(map_position=map_pos, map_rate=map_rate, model=native_model(w["model"]),
+                           discrete_genome=w["discrete"], keep=bool(w.get("keep_layer")), start_time=lo, end_time=hi,
+                           seed=2000 + i, offsets32=True)
+        c, cols = _native._Counts(), _native._Columns()
+        t0 = time.perf_counter()
+        _native.check(lib.mspb_sim_mutations(int(device), C.byref(t), C.byref(p.struct), C.byref(c), C.byref(cols)))
+        lib.mspb_columns_free(C.byref(cols))
+        walls.append(time.perf_counter() - t0)
+        new = int(c.num_new_mutations)
+    del hold
+    lib.mspb_oneshot_release(int(device))
+    steady = float(np.median(walls[-4:]))
+    return {"wall_ms_first_call": round(1e3 * walls[0], 2), "wall_ms_median_of_last_four": round(1e3 * steady, 2),
+            "value": new / steady, "unit": UNIT,
+            "path": "mspb_sim_mutations + mspb_columns_free, pageable host tables in, pooled pinned columns out"}
+
+
 def run_b200_arm(args, rank, local_rank, world):
     import torch
     import torch.distributed as dist
@@ -855,6 +885,12 @@ def run_b200_arm(args, rank, local_rank, world):
             e2e_python = python_call_timing(ts, w, map_pos, map_rate, local_rank)
         except Exception as e:  # noqa: BLE001
             e2e_python = {"error": f"{type(e).__name__}: {e}"[:200]}
+    e2e_oneshot = None
+    if world == 1 and not args.no_e2e_python:
+        try:
+            e2e_oneshot = oneshot_call_timing(ts, w, map_pos, map_rate, local_rank)
+        except Exception as e:  # noqa: BLE001
+            e2e_oneshot = {"error": f"{type(e).__name__}: {e}"[:200]}
 
     # ---- CPU baseline (N = 1 only): the compiled reference on all host cores
     cpu = None
@@ -901,6 +937,7 @@ def run_b200_arm(args, rank, local_rank, world):
         "validated": validated,
         "consumers": consumers_info,
         "e2e_python": e2e_python,
+        "e2e_oneshot": e2e_oneshot,
         "cpu_baseline": cpu,
         "phases_ms_last_step": {k: round(v, 4) for k, v in phases.items()},
         "kernels": kernels,

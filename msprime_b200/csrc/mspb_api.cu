@@ -346,7 +346,7 @@ struct StageScope {
 };
 
 constexpr size_t STAGE_MIN_BYTES = 4u << 20, STAGE_CHUNK_BYTES = 2u << 20;
-constexpr unsigned STAGE_MAX_THREADS = 8;
+constexpr unsigned STAGE_MAX_THREADS = 8; // (1 / 2 / 4 / 8 / 12 / 16 threads: 47 / 34 / 29 / 27 / 26 / 28 ms per bench-size one-shot call)
 
 // the source as the device will read it: `src` itself when it is page-locked (or small, or no scope is
 // open), else a pinned copy of it
