@@ -184,6 +184,69 @@ def test_one_shot_entry_point_equals_the_context_calls(native_built, oracle_mod)
     assert not replay.describe_diff(one, two) and len(one["mutations"]["site"]) > 100
 
 
+def test_one_shot_calls_share_a_context_and_survive_errors(native_built):
+    """The one-shot call keeps one context per device: tables of different sizes one after the other, a failing
+    call in between (which drops the context), mspb_oneshot_release, and the same answers as a fresh context."""
+    import test_gpu_replay as replay
+
+    small, large = cases.smc_ts(20, 2e4, 5), cases.smc_ts(60, 2e5, 6)
+
+    def params(ts, rate=2e-6, seed=9):
+        L = ts["sequence_length"]
+        return _native.Params(map_position=[0, L], map_rate=[rate], model=cases.native_model(cases.JC69),
+                              discrete_genome=True, keep=False, start_time=-FMAX, end_time=FMAX, seed=seed)
+
+    want = {}
+    for name, ts in (("small", small), ("large", large)):
+        with _native.Context(0) as ctx:
+            ctx.load_tables(ts)
+            ctx.generate(params(ts))
+            want[name] = ctx.fetch()
+    order = ["small", "large", "small", "bad", "large", "release", "small"]
+    for step in order:
+        if step == "bad":
+            with pytest.raises((_native.LibraryError, _native.InputError)):
+                _native.sim_mutations_oneshot(small, params(small, rate=-1.0))
+        elif step == "release":
+            _native.lib().mspb_oneshot_release(-1)
+            _native.lib().mspb_oneshot_release(0)  # nothing left: a no-op
+        else:
+            ts = small if step == "small" else large
+            got, _ = _native.sim_mutations_oneshot(ts, params(ts))
+            assert not replay.describe_diff(want[step], got), step
+    _native.lib().mspb_oneshot_release(-1)
+
+
+def test_pageable_and_pinned_tables_load_alike(native_built):
+    """Columns in pageable memory above 4 MB are staged through the pinned pool by host threads; the same columns
+    in page-locked memory go to the device directly.  Same index, same overlay."""
+    import test_gpu_replay as replay
+    from msprime_b200 import synth
+
+    ts = synth.native_treeseq(60_000, 3e7, 1e-8, 1e4, 4)  # 8e5 edges: 6 MB per float64 column
+    assert len(ts["edges"]["left"]) * 8 > (4 << 20)
+    L = ts["sequence_length"]
+    pinned = {k: (dict(v) if isinstance(v, dict) else v) for k, v in ts.items()}
+    hold = []
+    for tbl, cols in (("edges", ("left", "right", "parent", "child")), ("nodes", ("time", "flags"))):
+        for col in cols:
+            a = ts[tbl][col]
+            b = _native.pinned_empty(len(a), a.dtype)
+            b[:] = a
+            pinned[tbl][col] = b
+            hold.append(b)
+    prm = _native.Params(map_position=[0, L], map_rate=[1e-8], model=cases.native_model(cases.JC69),
+                         discrete_genome=True, keep=False, start_time=-FMAX, end_time=FMAX, seed=3)
+    res = []
+    for tables in (ts, pinned, ts):
+        with _native.Context(0) as ctx:
+            ctx.load_tables(tables)
+            ctx.generate(prm)
+            res.append(ctx.fetch())
+    assert len(res[0]["mutations"]["site"]) > 10_000
+    assert not replay.describe_diff(res[0], res[1]) and not replay.describe_diff(res[0], res[2])
+
+
 def test_too_many_new_mutations_is_an_error_not_a_wrap(native_built):
     """A rate that asks for more new mutations than 31-bit ids can name (a mistyped rate) must fail with
     MSPB_ERR_TOO_MANY_ROWS before anything is placed; the count must not wrap around 2^32."""
