@@ -95,28 +95,57 @@ def overall_bytes(E, M, S, DB, AB, M0=0, kept_bytes=0):
             "as_written": common + M * (4 + 4 + 4 + 8 + 4) + S * (8 + 4)}
 
 
+def load_prepared_input(w):
+    """The node and edge columns scripts/make_reference_input.py left for this workload's ancestry arguments, or
+    None."""
+    key = "n%d_L%g_r%g_ne%g_seed%d" % (w["samples"], w["L"], w["recomb"], w["ne"], w["ts_seed"])
+    path = os.path.join(ROOT, "oracle", "_ref", "inputs", key + ".npz")
+    if not os.path.exists(path):
+        return None
+    from msprime_b200 import synth
+
+    try:
+        z = np.load(path)
+        left, right = z["edge_left"], z["edge_right"]
+        return {
+            "sequence_length": float(z["sequence_length"]), "time_units": "generations",
+            "nodes": {"time": z["node_time"], "flags": z["node_flags"]},
+            "edges": {"left": left, "right": right, "parent": z["edge_parent"], "child": z["edge_child"]},
+            "sites": synth.empty_sites(), "mutations": synth.empty_mutations(),
+            "num_trees": int(len(np.unique(np.concatenate([left, right]))) - 1),
+        }
+    except Exception as e:  # noqa: BLE001  (a damaged file must not stop the bench: fall back to the generator)
+        log(f"[bench] prepared input {path} unreadable ({type(e).__name__}: {e}); using the generator")
+        return None
+
+
 def make_input(w):
     from msprime_b200 import synth
 
     t0 = time.time()
-    if w.get("input") == "reference":
-        # input preparation only: the reference's own ancestry simulator (lib/msprime.c compiled unmodified into
-        # oracle/_ref/libancestry_ref.so) makes the tree sequence msprime.sim_ancestry would return; practical up to
-        # config 3 (Hudson's algorithm: seconds for config 2, five minutes for config 3, hours for config 5)
-        from oracle import ref_ancestry
+    ts = None
+    if w.get("input", "auto") in ("auto", "reference"):
+        # The tree sequence msprime.sim_ancestry itself returns for the configuration, where it has been prepared:
+        # scripts/make_reference_input.py runs the reference's own ancestry simulator (lib/msprime.c compiled
+        # unmodified into oracle/_ref/libancestry_ref.so; seconds for config 2, five minutes for config 3, 2.6 hours
+        # for config 5) and leaves the node and edge columns in oracle/_ref/inputs/ (git-ignored, travels with the
+        # snapshot).  Plain numpy files: nothing of oracle/ is imported here.
+        ts = load_prepared_input(w)
+        if ts is None and w.get("input") == "reference":
+            from oracle import ref_ancestry  # input preparation on the spot (small configurations)
 
-        ts = ref_ancestry.load_cached(w)  # scripts/make_reference_input.py (configs 3-5 take minutes to hours)
-        if ts is None:
             if not ref_ancestry.have():
                 raise SystemExit("--input reference needs oracle/_ref/libancestry_ref.so (make -C oracle ancestry)")
             ts = ref_ancestry.sim_ancestry(w["samples"], sequence_length=w["L"], recombination_rate=w["recomb"],
                                            population_size=w["ne"], random_seed=w["ts_seed"])
-        w["input_text"] = ("tree sequence from the reference's own sim_ancestry (Hudson, lib/msprime.c compiled "
-                           "unmodified; random_seed=%d)" % w["ts_seed"])
-    else:
+        if ts is not None:
+            w["input_text"] = ("tree sequence from the reference's own sim_ancestry (Hudson, lib/msprime.c compiled "
+                               "unmodified; random_seed=%d)" % w["ts_seed"])
+    if ts is None:
         ts = synth.native_treeseq(w["samples"], w["L"], w["recomb"], w["ne"], w["ts_seed"])
+        w["input_text"] = INPUT_TEXT
     log(f"[bench] input: N={len(ts['nodes']['time'])} E={len(ts['edges']['left'])} trees={ts['num_trees']} "
-        f"({time.time() - t0:.1f} s, {w.get('input', 'treegen')} generator)")
+        f"({time.time() - t0:.1f} s; {w['input_text']})")
     kl = w.get("keep_layer")
     if kl:
         # the existing mutations of a keep=True workload: one reference overlay (input preparation)
@@ -582,6 +611,7 @@ def run_b200_arm(args, rank, local_rank, world):
         h2d_bytes += sum(int(np.asarray(v).nbytes) for v in ts[tbl].values())
 
     ctx = _native.Context(local_rank)
+    ctx.force_k2({"auto": 0, "dense": 1, "sparse": 2}[args.k2])
     stream = torch.cuda.ExternalStream(ctx.stream(), device=torch.device("cuda", local_rank))
 
     pcache = {}
@@ -959,9 +989,12 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="config5", choices=sorted(WORKLOADS))
-    ap.add_argument("--input", default="treegen", choices=["treegen", "reference"],
-                    help="where the tree sequence comes from: this project's SMC' generator (any size) or the "
-                         "reference's own ancestry simulator (configs 1-3)")
+    ap.add_argument("--input", default="auto", choices=["auto", "treegen", "reference"],
+                    help="where the tree sequence comes from: the reference's own ancestry simulator where its output "
+                         "has been prepared (auto, the default; scripts/make_reference_input.py), else this project's "
+                         "SMC' generator; 'reference' also runs the simulator on the spot, 'treegen' never uses it")
+    ap.add_argument("--k2", default="auto", choices=["auto", "dense", "sparse"],
+                    help="placement kernel: by density (default), one block per 256 edges, one thread per mutation")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-validate", action="store_true", help="skip the checks of the last timed overlay")
     ap.add_argument("--no-consumers", action="store_true", help="skip the sample-count index / site AFS figures")

@@ -262,6 +262,11 @@ int mspb_fetch(mspb_ctx_t *ctx, const mspb_columns_t *host_columns);
 uint64_t mspb_last_fetch_bytes(const mspb_ctx_t *ctx);
 /* Device pointers of the resident result (valid until the next mspb_generate). */
 int mspb_device_columns(mspb_ctx_t *ctx, mspb_columns_t *device_columns);
+/* Which placement kernel (K2) the next calls use: 0 = chosen from the mutations per edge (the default: one
+ * block per 256 edges when edges carry a mutation or more each, one thread per mutation when they are mostly
+ * empty, as in the clipped slices of a sharded call), 1 = always the former, 2 = always the latter.  Both write
+ * the same records; the switch exists for tests and measurements.  No counterpart in the reference. */
+int mspb_ctx_force_k2(mspb_ctx_t *ctx, int mode);
 /* Number of kernels this library launched since the context was created. */
 uint64_t mspb_kernel_launches(const mspb_ctx_t *ctx);
 /* The CUDA stream (cudaStream_t) every kernel and copy of this context runs on, so

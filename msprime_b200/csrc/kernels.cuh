@@ -725,6 +725,80 @@ __global__ void __launch_bounds__(K2_EDGES) k2_place_kernel(TreeSeqView ts, Rate
     }
 }
 
+// ---------------------------------------------------------------- K2, one thread per mutation (native)
+// k2_place_kernel gives a block 256 EDGES and lets each thread place one of their mutations per round: right
+// when edges carry a mutation or more each (config 5 on one GPU: 1.5), wasteful when they are sparse -- the
+// clipped slices of a sharded call keep every edge that crosses the slice but 1 / N of its mass (0.4 mutations
+// per edge at 8 GPUs: a block's one round runs with a fifth of its lanes).  Here the grid follows the MUTATIONS:
+// thread j finds the edge that owns slot j by two binary searches over the offsets K1 left (tile bases, then the
+// tile's local offsets: a warp's 32 slots fall into the same tile or two, so the probes coalesce) and places it.
+// Same slots, same Philox keys, same records as k2_place_kernel; not for invariant slices (their slots follow
+// an in-slice count).  n_grid: the slots this launch covers; a total beyond it (the launch was sized from the
+// previous call) leaves the rest to a second launch by the host.
+__global__ void __launch_bounds__(256) k2_place_sparse_kernel(TreeSeqView ts, RateMapView map, CallView call,
+    const uint32_t *__restrict__ goff, const uint64_t *__restrict__ tile_base, uint32_t base, Rec *__restrict__ rec,
+    KeyView keys, const uint64_t *__restrict__ k1_total, uint64_t capacity, const int *err, uint64_t first_slot)
+{
+    const uint64_t E = call.num_work;
+    const uint32_t num_tiles = (uint32_t) ((E + K1_TILE - 1) >> K1_TILE_SHIFT);
+    const uint64_t total = k1_total != nullptr ? (*k1_total & 0xffffffffull) : (tile_base[num_tiles] & 0xffffffffull);
+    if (k1_total != nullptr && (total + base > capacity || *err != 0)) {
+        return; // launched ahead of the K1 read-back: see k2_place_kernel
+    }
+    const uint64_t j0 = first_slot + (uint64_t) blockIdx.x * blockDim.x;
+    if (j0 >= total) {
+        return;
+    }
+    // the last tile whose base is <= the block's first slot: one search per block ...
+    __shared__ uint32_t s_lo;
+    if (threadIdx.x == 0) {
+        uint32_t lo = 0, hi = num_tiles; // invariant: base(lo) <= j0, base(hi) > j0 (hi == num_tiles: the total)
+        while (hi - lo > 1) {
+            const uint32_t mid = (lo + hi) >> 1;
+            if ((tile_base[mid] & 0xffffffffull) <= j0) {
+                lo = mid;
+            } else {
+                hi = mid;
+            }
+        }
+        s_lo = lo;
+    }
+    __syncthreads();
+    const uint64_t j = j0 + threadIdx.x;
+    if (j >= total) {
+        return;
+    }
+    // ... and a step or two from there for each slot (a tile holds hundreds of mutations unless it is nearly empty)
+    uint32_t lo = s_lo;
+    while (lo + 1 < num_tiles && (tile_base[lo + 1] & 0xffffffffull) <= j) {
+        lo++;
+    }
+    const uint32_t in_tile = (uint32_t) (j - (tile_base[lo] & 0xffffffffull));
+    // the last edge of that tile whose local offset is <= in_tile
+    const uint64_t e0 = (uint64_t) lo << K1_TILE_SHIFT;
+    uint32_t a = 0, b = (uint32_t) (E - e0 < (uint64_t) K1_TILE ? E - e0 : (uint64_t) K1_TILE);
+    while (b - a > 1) {
+        const uint32_t mid = (a + b) >> 1;
+        if (goff[e0 + mid] <= in_tile) {
+            a = mid;
+        } else {
+            b = mid;
+        }
+    }
+    const uint64_t e = e0 + a;
+    const uint32_t id = call.edge_list != nullptr ? call.edge_list[e] : (uint32_t) e;
+    const EdgeDraw d = edge_draw(ts, map, call, id);
+    double x, t;
+    place_one(Philox(call.seed), map, call, d, id, in_tile - goff[e], &x, &t);
+    Rec r;
+    r.time = t;
+    r.node = d.child;
+    r.ord = (uint32_t) j;
+    const uint64_t slot = (uint64_t) base + j;
+    rec[slot] = r;
+    keys.store(slot, x, t, false);
+}
+
 // ---------------------------------------------------------------- K1/K2 (replay)
 // Nonempty (edge, rate interval) pairs found by the sequential stream walker.
 struct ReplayPairs {

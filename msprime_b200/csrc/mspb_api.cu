@@ -174,6 +174,9 @@ struct mspb_ctx {
     const void *md_zero_site_ptr = nullptr, *md_zero_mut_ptr = nullptr;
     uint64_t md_zero_site_bytes = 0, md_zero_mut_bytes = 0;
     uint64_t last_fetch_bytes = 0; // device-to-host bytes of the last mspb_fetch
+    // K2: one block per 256 edges (dense) or one thread per mutation (sparse); chosen from the last call's density
+    int k2_force = 0; // 0: by density; 1: dense; 2: sparse (mspb_ctx_force_k2, tests)
+    uint64_t last_num_work = 0, last_new = 0;
     // sample-count step functions of the loaded tree sequence (consumers.cuh), built on request
     struct {
         bool valid = false;
@@ -1354,6 +1357,13 @@ struct StageB {
     ResolveView rv;
 };
 
+// one thread per mutation instead of one block per 256 edges: when the edges are mostly empty (sharded calls;
+// measured cross-over in DESIGN.md section 6)
+bool k2_sparse_pays(uint64_t new_mutations, uint64_t edges)
+{
+    return new_mutations * 5 < edges * 4; // fewer than 0.8 mutations per edge
+}
+
 // K5 on the state saved by run_sorted_stages
 int launch_emit(mspb_ctx *ctx)
 {
@@ -1683,6 +1693,7 @@ static int generate_impl(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t 
     uint64_t Mnew = 0, num_pairs = 0;
     uint64_t spec_rec = 0, spec_key = 0; // generations of the buffers of a K2 launched ahead of the K1 read-back
     size_t spec_cap = 0;
+    uint64_t spec_sparse_n = 0; // > 0: the early launch was the sparse kernel and covered this many slots
     ReplayPairs pairs;
     memset(&pairs, 0, sizeof(pairs));
     bool serial_placed = false; // replay harness, continuous genome: replay_resolve wrote the records itself
@@ -1716,10 +1727,25 @@ static int generate_impl(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t 
                 skeys.mode = call.key_mode;
                 skeys.k32 = ctx->k32_0.p;
                 skeys.k64 = ctx->keys0.p;
-                MSPB_LAUNCH(ctx->log, "k2_place",
-                    k2_place_kernel<<<grid_for(call.num_work, K2_EDGES), K2_EDGES, 0, st>>>(ts, map, call,
-                        ctx->goff.p, nullptr, ctx->k1_tiles.p, 0u, ctx->rec.p, skeys, &dt->k1_total, spec_cap,
-                        &dt->err));
+                // (the density of this call is not known yet: the previous call over the same edges decides)
+                const bool sparse = ctx->k2_force == 2
+                                    || (ctx->k2_force == 0 && ctx->last_num_work == call.num_work
+                                        && k2_sparse_pays(ctx->last_new, call.num_work));
+                if (sparse) {
+                    spec_sparse_n = ctx->last_new + ctx->last_new / 4 + 4096;
+                    if (ctx->k2_force == 2 && ctx->last_num_work != call.num_work) {
+                        spec_sparse_n = 4096; // (forced without a previous call: the second launch does the rest)
+                    }
+                    spec_sparse_n = spec_sparse_n < spec_cap ? spec_sparse_n : spec_cap;
+                    MSPB_LAUNCH(ctx->log, "k2_place_sparse",
+                        k2_place_sparse_kernel<<<grid_for(spec_sparse_n, 256), 256, 0, st>>>(ts, map, call, ctx->goff.p,
+                            ctx->k1_tiles.p, 0u, ctx->rec.p, skeys, &dt->k1_total, spec_cap, &dt->err, 0));
+                } else {
+                    MSPB_LAUNCH(ctx->log, "k2_place",
+                        k2_place_kernel<<<grid_for(call.num_work, K2_EDGES), K2_EDGES, 0, st>>>(ts, map, call,
+                            ctx->goff.p, nullptr, ctx->k1_tiles.p, 0u, ctx->rec.p, skeys, &dt->k1_total, spec_cap,
+                            &dt->err));
+                }
             } else {
                 spec_cap = 0;
             }
@@ -1931,16 +1957,34 @@ static int generate_impl(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t 
         if (placed || serial_placed) {
             // the early launch had room and the buffers did not move (or the replay walker placed
             // the mutations itself): the records are in place
+            if (placed && spec_sparse_n > 0 && Mnew > spec_sparse_n) {
+                // ... up to the slots the sparse launch was sized for (from the previous call's count)
+                MSPB_LAUNCH(ctx->log, "k2_place_sparse",
+                    k2_place_sparse_kernel<<<grid_for(Mnew - spec_sparse_n, 256), 256, 0, st>>>(ts, map, call,
+                        ctx->goff.p, ctx->k1_tiles.p, 0u, ctx->rec.p, keys, nullptr, 0, nullptr, spec_sparse_n));
+            }
         } else if (!replay) {
-            MSPB_LAUNCH(ctx->log, "k2_place",
-                k2_place_kernel<<<grid_for(call.num_work, K2_EDGES), K2_EDGES, 0, st>>>(ts, map, call, ctx->goff.p,
-                    sliced ? ctx->loff.p : nullptr, ctx->k1_tiles.p, (uint32_t) (S0 + M0), ctx->rec.p, keys, nullptr,
-                    0, nullptr));
+            const bool sparse = !sliced
+                                && (ctx->k2_force == 2 || (ctx->k2_force == 0 && k2_sparse_pays(Mnew, call.num_work)));
+            if (sparse) {
+                MSPB_LAUNCH(ctx->log, "k2_place_sparse",
+                    k2_place_sparse_kernel<<<grid_for(Mnew, 256), 256, 0, st>>>(ts, map, call, ctx->goff.p,
+                        ctx->k1_tiles.p, (uint32_t) (S0 + M0), ctx->rec.p, keys, nullptr, 0, nullptr, 0));
+            } else {
+                MSPB_LAUNCH(ctx->log, "k2_place",
+                    k2_place_kernel<<<grid_for(call.num_work, K2_EDGES), K2_EDGES, 0, st>>>(ts, map, call, ctx->goff.p,
+                        sliced ? ctx->loff.p : nullptr, ctx->k1_tiles.p, (uint32_t) (S0 + M0), ctx->rec.p, keys,
+                        nullptr, 0, nullptr));
+            }
         } else {
             MSPB_LAUNCH(ctx->log, "replay_place",
                 replay_place_kernel<<<grid_for(num_pairs, 128), 128, 0, st>>>(ts, map, call, ctx->replay.p, pairs,
                     num_pairs, (uint32_t) (S0 + M0), ctx->rec.p, keys, &dt->err));
         }
+    }
+    if (!replay) {
+        ctx->last_num_work = call.num_work;
+        ctx->last_new = Mnew;
     }
     if (R == 0) {
         // no sites and no mutations: only the leading zero offsets exist
@@ -2093,6 +2137,15 @@ static int generate_impl(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t 
     if (counts_out != nullptr) {
         *counts_out = c;
     }
+    return 0;
+}
+
+extern "C" int mspb_ctx_force_k2(mspb_ctx_t *ctx, int mode)
+{
+    if (ctx == nullptr || mode < 0 || mode > 2) {
+        return MSPB_ERR_BAD_PARAM_VALUE;
+    }
+    ctx->k2_force = mode;
     return 0;
 }
 

@@ -325,6 +325,41 @@ def test_device_begin_hands_back_to_the_host(native_built, why):
             assert np.array_equal(np.asarray(whole[tbl][col]), np.asarray(merged[tbl][col])), (tbl, col)
 
 
+@pytest.mark.parametrize("discrete", [True, False])
+@pytest.mark.parametrize("keep", [False, True])
+def test_both_placement_kernels_write_the_same_records(native_built, ts_small, discrete, keep):
+    """K2 as one block per 256 edges and as one thread per mutation (the form sparse slices take): whole calls and
+    clipped slices, first calls and calls on warm buffers (placed ahead of the K1 read-back, the sparse launch sized
+    from the call before: smaller, equal and larger counts), with and without kept rows."""
+    ts = ts_small
+    L = ts["sequence_length"]
+    if keep:
+        with _native.Context(0) as c0:
+            first, _ = run(c0, ts, model=cases.JC69, rate=2e-7, seed=71, discrete=discrete)
+        ts = cases.with_kept(ts, first)
+    plan = [(1e-8, 0.0, 0.0, 0), (3e-7, 0.0, 0.0, 0), (3e-7, 0.0, 0.0, 0), (2e-8, 0.0, 0.0, 0),
+            (3e-7, 2e4, 9e4, 3), (3e-7, 2e4, 9e4, 3), (1e-6, 2e4, 9e4, 3)]
+    results = {}
+    for mode in (1, 2):
+        out = []
+        with _native.Context(0) as c:
+            c.force_k2(mode)
+            c.load_tables(ts)
+            for k, (rate, lo, hi, stream) in enumerate(plan):
+                cnt = c.generate(_native.Params(
+                    map_position=[0, L], map_rate=[rate], model=cases.native_model(cases.JC69), discrete_genome=discrete,
+                    keep=keep, start_time=-cases.FMAX, end_time=cases.FMAX, seed=80 + k, slice_left=lo, slice_right=hi,
+                    slice_stream=stream))
+                out.append((cnt["num_new_mutations"], c.fetch()))
+        results[mode] = out
+    assert [n for n, _ in results[1]] == [n for n, _ in results[2]]
+    assert results[1][1][0] > 5 * results[1][0][0] > 0  # the second call outgrows what the first one sized
+    for (n, a), (_, b) in zip(results[1], results[2]):
+        for tbl in a:
+            for col in a[tbl]:
+                assert np.array_equal(np.asarray(a[tbl][col]), np.asarray(b[tbl][col])), (tbl, col, n)
+
+
 def test_device_tensors_alias_the_result(ctx, ts_small):
     """the result handed over as torch tensors on the device, no copy."""
     import torch
