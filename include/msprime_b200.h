@@ -266,7 +266,7 @@ int mspb_device_columns(mspb_ctx_t *ctx, mspb_columns_t *device_columns);
  * block per 256 edges when edges carry a mutation or more each, one thread per mutation when they are mostly
  * empty, as in the clipped slices of a sharded call), 1 = always the former, 2 = always the latter.  Both write
  * the same records; the switch exists for tests and measurements.  No counterpart in the reference. */
-int mspb_ctx_force_k2(mspb_ctx_t *ctx, int mode);
+int mspb_ctx_force_placement(mspb_ctx_t *ctx, int mode);
 /* Number of kernels this library launched since the context was created. */
 uint64_t mspb_kernel_launches(const mspb_ctx_t *ctx);
 /* The CUDA stream (cudaStream_t) every kernel and copy of this context runs on, so

@@ -111,7 +111,7 @@ EXPORTED_SYMBOLS = [
     "mspb_device_columns", "mspb_kernel_launches", "mspb_phase_ms", "mspb_phase_name",
     "mspb_sim_mutations", "mspb_oneshot_release", "mspb_columns_free", "mspb_strerror", "mspb_version", "mspb_cuda_runtime_version",
     "mspb_ctx_stream", "mspb_kernel_timing", "mspb_kernel_time", "mspb_selftest_sort",
-    "mspb_ctx_force_k2", "mspb_generate_begin", "mspb_generate_begin_device", "mspb_generate_end", "mspb_shift_offsets",
+    "mspb_ctx_force_placement", "mspb_generate_begin", "mspb_generate_begin_device", "mspb_generate_end", "mspb_shift_offsets",
     "mspb_exchange_buffers", "mspb_exchange_stream", "mspb_exchange_post_counts", "mspb_generate_end_device",
     "mspb_generate_finish_device", "mspb_last_fetch_bytes", "mspb_ctx_load_tables_begin",
     "mspb_ctx_load_tables_end", "mspb_site_rows_noalloc", "mspb_ctx_build_sample_index", "mspb_samples_below",
@@ -153,7 +153,7 @@ def lib():
         L.mspb_generate.argtypes = [C.c_void_p, C.POINTER(_Params), C.POINTER(_Counts)]
         L.mspb_generate_begin.argtypes = [C.c_void_p, C.POINTER(_Params), C.POINTER(_Counts)]
         L.mspb_generate_begin_device.argtypes = [C.c_void_p, C.POINTER(_Params)]
-        L.mspb_ctx_force_k2.argtypes = [C.c_void_p, C.c_int]
+        L.mspb_ctx_force_placement.argtypes = [C.c_void_p, C.c_int]
         L.mspb_exchange_stream.argtypes = [C.c_void_p]
         L.mspb_exchange_stream.restype = C.c_void_p
         L.mspb_generate_end.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64, C.POINTER(_Counts)]
@@ -420,7 +420,7 @@ class Context:
 
     def force_k2(self, mode):
         """0: placement kernel chosen from the density; 1: one block per 256 edges; 2: one thread per mutation."""
-        check(lib().mspb_ctx_force_k2(self._h, int(mode)))
+        check(lib().mspb_ctx_force_placement(self._h, int(mode)))
 
     def exchange_stream(self):
         """The ``cudaStream_t`` (integer) the next all-gather of the exchange buffers must be enqueued on."""

@@ -175,7 +175,7 @@ struct mspb_ctx {
     uint64_t md_zero_site_bytes = 0, md_zero_mut_bytes = 0;
     uint64_t last_fetch_bytes = 0; // device-to-host bytes of the last mspb_fetch
     // K2: one block per 256 edges (dense) or one thread per mutation (sparse); chosen from the last call's density
-    int k2_force = 0; // 0: by density; 1: dense; 2: sparse (mspb_ctx_force_k2, tests)
+    int k2_force = 0; // 0: by density; 1: dense; 2: sparse (mspb_ctx_force_placement, tests)
     uint64_t last_num_work = 0, last_new = 0;
     // sample-count step functions of the loaded tree sequence (consumers.cuh), built on request
     struct {
@@ -1004,6 +1004,7 @@ extern "C" int mspb_ctx_load_tables_begin(mspb_ctx_t *ctx, const mspb_tables_t *
     CUDA_OK(cudaSetDevice(ctx->device));
     cudaStream_t st = ctx->stream;
     TRY(tables_prepare(ctx, t));
+    StageScope staging; // (ends after the drain below)
     StreamDrain drain { st, ctx->copy_stream };
 #define SHARD(k, buf, src, n, T)                                                                                     \
     do {                                                                                                             \
@@ -1012,7 +1013,8 @@ extern "C" int mspb_ctx_load_tables_begin(mspb_ctx_t *ctx, const mspb_tables_t *
         const uint64_t lo = (uint64_t) rank * per;                                                                   \
         const uint64_t hi = lo + per < (uint64_t) (n) ? lo + per : (uint64_t) (n);                                   \
         if (hi > lo) {                                                                                               \
-            CUDA_OK(cudaMemcpyAsync(ctx->buf.p + lo, (src) + lo, (hi - lo) * sizeof(T), cudaMemcpyHostToDevice, st)); \
+            CUDA_OK(cudaMemcpyAsync(ctx->buf.p + lo, staged_source((src) + lo, (hi - lo) * sizeof(T)),              \
+                (hi - lo) * sizeof(T), cudaMemcpyHostToDevice, st));                                                 \
         }                                                                                                            \
         shards[k].ptr = ctx->buf.p;                                                                                  \
         shards[k].bytes_per_rank = per * sizeof(T);                                                                  \
@@ -2140,7 +2142,7 @@ static int generate_impl(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t 
     return 0;
 }
 
-extern "C" int mspb_ctx_force_k2(mspb_ctx_t *ctx, int mode)
+extern "C" int mspb_ctx_force_placement(mspb_ctx_t *ctx, int mode)
 {
     if (ctx == nullptr || mode < 0 || mode > 2) {
         return MSPB_ERR_BAD_PARAM_VALUE;
