@@ -64,6 +64,7 @@ extern "C" {
 #define MSPB_ERR_UNSORTED_SITES (-1009) /* sliced call: kept sites must be sorted by position */
 #define MSPB_ERR_OFFSET_OVERFLOW (-1008) /* offsets32 asked for, but a column may reach 4 GiB */
 #define MSPB_ERR_RETRY_WITH_HOST (-1011) /* mspb_generate_finish_device after mspb_generate_begin_device: some rank needs the host between the stages; make the call again with mspb_generate_begin */
+#define MSPB_ERR_KEPT_MUTATIONS_UNSORTED (-1012) /* keep: existing mutations of a site are not listed oldest first and a new mutation falls on that site; the reference's within-site comparator (lib/mutgen.c:36-49) is not a total order there (its debug build asserts at lib/mutgen.c:1200) */
 #define MSPB_ERR_NOALLOC_TOO_LARGE (-1010) /* mspb_site_rows_noalloc: more than MSPB_NOALLOC_MAX_RECORDS records */
 
 /* the reference's three C models (lib/mutgen.c:184-237, 257-413, 431-481) */

@@ -1467,6 +1467,33 @@ MSPB_DEVFN void resolve_site(const TreeSeqView &ts, const KeptView &kept, const 
     while (end < sv.n && !sv.head(end)) {
         end++;
     }
+    if (sv.has_kept) {
+        // Existing mutations of this site that are NOT listed oldest first, with a new mutation on the site: the
+        // reference's comparator (existing rows by id, anything else by time, lib/mutgen.c:36-49) is then not a
+        // total order, what its qsort returns is undefined and its debug build stops at lib/mutgen.c:1200.
+        // Refused with a code of its own.  Records arrive in slot order (= row order for existing rows) or, after
+        // a dense genome's second sort, oldest first: either way a pair out of order shows between neighbours.
+        const uint64_t KM0 = sv.S0 + sv.M0;
+        bool any_new = false, out_of_order = false;
+        uint32_t prev = 0xffffffffu;
+        double prev_t = 0.0;
+        for (uint64_t a = i; a < end; a++) {
+            const uint32_t r = sv.val[a];
+            if (r >= KM0) {
+                any_new = true;
+            } else if (r >= sv.S0) {
+                const double t = sv.rec[r].time;
+                if (prev != 0xffffffffu && ((prev < r && prev_t < t) || (prev > r && t < prev_t))) {
+                    out_of_order = true;
+                }
+                prev = r;
+                prev_t = t;
+            }
+        }
+        if (any_new && out_of_order) {
+            set_error(err, -1012); // MSPB_ERR_KEPT_MUTATIONS_UNSORTED
+        }
+    }
     // insertion sort of val[i .. end) (runs are short, or nearly sorted in KEY64_POS_TIME mode)
     for (uint64_t a = i + 1; a < end; a++) {
         const uint32_t v = sv.val[a];

@@ -278,6 +278,9 @@ extern "C" const char *mspb_strerror(int err)
             return "A ragged column may exceed 4 GiB: 32-bit offsets cannot be used";
         case MSPB_ERR_NOT_GENERATED:
             return "No result is resident: call mspb_generate first";
+        case MSPB_ERR_KEPT_MUTATIONS_UNSORTED:
+            return "Existing mutations of a site are not listed oldest first and a new mutation falls on that site "
+                   "(the reference's result is undefined for such tables)";
         case MSPB_ERR_RETRY_WITH_HOST:
             return "A rank of this sharded call needs the host between its stages: make the call again with "
                    "mspb_generate_begin";

@@ -247,6 +247,59 @@ def test_pageable_and_pinned_tables_load_alike(native_built):
     assert not replay.describe_diff(res[0], res[1]) and not replay.describe_diff(res[0], res[2])
 
 
+def hand_kept(ts, rows):
+    """``ts`` with ONE existing site at position 3 (ancestral state A) and the given existing mutations
+    ``(node, time, derived_state)`` in the order given."""
+    d = dict(ts)
+    d["sites"] = {"position": np.array([3.0]), "ancestral_state": np.frombuffer(b"A", dtype=np.uint8).copy(),
+                  "ancestral_state_offset": np.array([0, 1], dtype=np.uint64),
+                  "metadata": np.zeros(0, dtype=np.uint8), "metadata_offset": np.zeros(2, dtype=np.uint64)}
+    der = "".join(r[2] for r in rows).encode()
+    d["mutations"] = {"site": np.zeros(len(rows), dtype=np.int32), "node": np.array([r[0] for r in rows], dtype=np.int32),
+                      "parent": np.full(len(rows), -1, dtype=np.int32),
+                      "time": np.array([r[1] for r in rows], dtype=np.float64),
+                      "derived_state": np.frombuffer(der, dtype=np.uint8).copy(),
+                      "derived_state_offset": np.arange(len(rows) + 1, dtype=np.uint64),
+                      "metadata": np.zeros(0, dtype=np.uint8), "metadata_offset": np.zeros(len(rows) + 1, dtype=np.uint64)}
+    return d
+
+
+def test_existing_mutations_out_of_order_under_a_new_one_are_refused(native_built, oracle_mod):
+    """Existing mutations of a site that are not listed oldest first, with a new mutation on the site: the
+    reference's within-site comparator (existing rows by id, the rest by time, lib/mutgen.c:36-49) is then not a
+    total order, what it returns is undefined and its debug build asserts (lib/mutgen.c:1200).  The device refuses
+    such a call with MSPB_ERR_KEPT_MUTATIONS_UNSORTED; the same rows oldest first, or out of order but with no new
+    mutation on their site, go through (and match the reference's algorithm under a shared stream)."""
+    import test_gpu_replay as replay
+
+    tree = cases.four_leaf_tree()
+    young, old = (0, 0.5, "C"), (4, 1.5, "G")  # node 0 sits below node 4
+    sorted_ts, unsorted_ts = hand_kept(tree, [old, young]), hand_kept(tree, [young, old])
+
+    def status(ts, rate, seed=3):
+        with _native.Context(0) as ctx:
+            try:
+                ctx.load_tables(ts)
+                ctx.generate(_native.Params(map_position=[0, 10.0], map_rate=[rate], model=cases.native_model(cases.JC69),
+                                            discrete_genome=True, keep=True, start_time=-FMAX, end_time=FMAX, seed=seed))
+            except (_native.LibraryError, _native.InputError) as e:
+                return e.status
+        return 0
+
+    assert status(unsorted_ts, 5.0) == -1012  # every position takes new mutations at this rate
+    assert status(unsorted_ts, 0.0) == 0      # none lands on the site: the rows are kept as they are
+    assert status(sorted_ts, 5.0) == 0
+    # and the accepted forms agree with the reference's algorithm
+    stream = np.random.default_rng(8).random(200_000)
+    for ts, rate in ((sorted_ts, 5.0), (unsorted_ts, 0.0)):
+        want = oracle_mod.sim_mutations(ts, which="port", map_position=[0, 10.0], map_rate=[rate], model=cases.JC69,
+                                        discrete_genome=True, keep=True, stream=stream)
+        with _native.Context(0) as ctx:
+            got = replay.gpu_run(ctx, ts, model=cases.JC69, stream=stream, map_position=[0, 10.0], map_rate=[rate],
+                                 discrete=True, keep=True)
+        assert not replay.describe_diff(want, got)
+
+
 def test_too_many_new_mutations_is_an_error_not_a_wrap(native_built):
     """A rate that asks for more new mutations than 31-bit ids can name (a mistyped rate) must fail with
     MSPB_ERR_TOO_MANY_ROWS before anything is placed; the count must not wrap around 2^32."""
