@@ -190,3 +190,86 @@ def test_balanced_cuts_even_out_the_expected_mutations():
             assert bal.max() / bal.mean() < 1.02, (world, bal)
             assert even.max() / even.mean() > 1.2 or world == 2
     assert sharding.balanced_cuts(ts, pos, rate, 1) == [0.0, L]
+
+
+# ---------------------------------------------------------------- run_slice_device: order of calls and the retry
+
+class ScriptedContext:
+    """Stands in for ``_native.Context`` in ``sharding.run_slice_device``: records the calls and lets the first
+    ``generate_finish_device`` of a call begun without its wait ask for the host (``RetryWithHost``)."""
+
+    def __init__(self, ask_for_host):
+        import ctypes
+
+        self.ask_for_host = ask_for_host
+        self.calls = []
+        self.counts = {"next_allele": 7}
+        self.began_on_device = False
+
+        class _P(ctypes.Structure):
+            _fields_ = [("model_kind", ctypes.c_int32)]
+
+        self.Params = _P
+
+    def generate_begin_device(self, params):
+        self.calls.append("begin_device")
+        self.began_on_device = True
+
+    def generate_begin(self, params):
+        self.calls.append("begin")
+        self.began_on_device = False
+
+    def exchange_post_counts(self):
+        self.calls.append("post")
+
+    def generate_end_device(self, rank, world):
+        self.calls.append("end_device")
+
+    def generate_finish_device(self, rank, world):
+        from msprime_b200 import _native
+
+        self.calls.append("finish_device")
+        if self.began_on_device and self.ask_for_host:
+            raise _native.RetryWithHost("again, with the host", _native.ERR_RETRY_WITH_HOST)
+        z = {k: 0 for k in ("num_sites", "num_mutations", "num_new_mutations", "ancestral_state_bytes",
+                            "site_metadata_bytes", "derived_state_bytes", "mutation_metadata_bytes")}
+        return dict(z), dict(z, num_sites=5), dict(z)
+
+    def fetch(self, out=None):
+        self.calls.append("fetch")
+        return {"sites": {}, "mutations": {}}
+
+
+class _ParamsBox:
+    def __init__(self, kind):
+        import ctypes
+
+        class _P(ctypes.Structure):
+            _fields_ = [("model_kind", ctypes.c_int32)]
+
+        self.struct = _P(kind)
+
+
+@pytest.mark.parametrize("ask_for_host,model_kind,host_flag", [(False, 1, False), (True, 1, False), (False, 2, False),
+                                                               (False, 0, True)])
+def test_run_slice_device_call_order(ask_for_host, model_kind, host_flag):
+    """One wait per overlay: begin_device, counts, gather, end, gather, finish.  When finish asks for the host, the
+    SAME sequence of collectives runs again behind the host-paced begin (every rank takes that turn together, so the
+    all-gathers stay matched); the SLiM model (kind 2) and host_between_stages=True go there at once."""
+    ctx = ScriptedContext(ask_for_host)
+    gathers = []
+    local, info = sharding.run_slice_device(ctx, _ParamsBox(model_kind), rank=0, world=2,
+                                            gather=lambda: gathers.append(len(ctx.calls)), fetch=True,
+                                            host_between_stages=host_flag)
+    device = ["begin_device", "post", "end_device", "finish_device"]
+    host = ["begin", "post", "end_device", "finish_device"]
+    if model_kind == 2 or host_flag:
+        assert ctx.calls == host + ["fetch"] and len(gathers) == 2
+    elif ask_for_host:
+        assert ctx.calls == device + host + ["fetch"] and len(gathers) == 4
+    else:
+        assert ctx.calls == device + ["fetch"] and len(gathers) == 2
+    # each gather sits right after the counts / after the second stage
+    for g, after in zip(gathers, ["post", "end_device"] * 2):
+        assert ctx.calls[g - 1] == after
+    assert info["num_sites"] == 5 and info["next_allele"] == 7 and local == {"sites": {}, "mutations": {}}
