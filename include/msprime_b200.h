@@ -278,7 +278,8 @@ void *mspb_ctx_stream(const mspb_ctx_t *ctx);
  * table (kernel name, launches, summed milliseconds) and fails past the end. */
 int mspb_kernel_timing(mspb_ctx_t *ctx, int enable);
 int mspb_kernel_time(const mspb_ctx_t *ctx, int index, const char **name, uint64_t *launches, double *ms);
-/* Per-phase device milliseconds of the last mspb_generate (n <= MSPB_NUM_PHASES). */
+/* Per-phase device milliseconds of the last mspb_generate (n <= MSPB_NUM_PHASES); recorded while
+ * mspb_kernel_timing is enabled, zeros otherwise. */
 #define MSPB_NUM_PHASES 8
 int mspb_phase_ms(const mspb_ctx_t *ctx, float *ms, int n);
 const char *mspb_phase_name(int phase);

@@ -1493,7 +1493,7 @@ int run_sorted_stages(mspb_ctx *ctx, const mspb_params_t *p, const TreeSeqView &
     sv.key.k64 = nullptr;
 
     // ---- K3: stable sort by position
-    if (first_sort) {
+    if (first_sort && ctx->log.timing) {
         CUDA_OK(cudaEventRecord(ctx->ev[3], st));
     }
     if (call.key_mode == KEY32_POS) {
@@ -1517,13 +1517,15 @@ int run_sorted_stages(mspb_ctx *ctx, const mspb_params_t *p, const TreeSeqView &
     }
 
     // ---- P1: site boundaries, row and draw numbering
-    if (first_sort) {
+    if (first_sort && ctx->log.timing) {
         CUDA_OK(cudaEventRecord(ctx->ev[4], st));
     }
     const uint32_t p1_tiles = (uint32_t) ((R + P1_TILE - 1) / P1_TILE);
     LbWord *lb3 = nullptr;
     TRY(lookback_state(ctx, p1_tiles, 1, &lb3));
-    CUDA_OK(cudaMemsetAsync(&dt->dense, 0, sizeof(uint32_t), st));
+    if (!first_sort) {
+        CUDA_OK(cudaMemsetAsync(&dt->dense, 0, sizeof(uint32_t), st)); // (the call's totals start at zero)
+    }
 #define MSPB_P1(MODE, K)                                                                                             \
     MSPB_LAUNCH(ctx->log, "p1_sites",                                                                                \
         (p1_sites_kernel<MODE, K><<<p1_tiles, SCAN_THREADS, 0, st>>>(sv, call.discrete, lb3, p1_tiles, &dt->p1,      \
@@ -1546,7 +1548,7 @@ int run_sorted_stages(mspb_ctx *ctx, const mspb_params_t *p, const TreeSeqView &
 
     CUDA_OK(cudaEventRecord(ctx->ev_p1, st)); // the site rows are final from here on
     // ---- K4: sites with several records
-    if (first_sort) {
+    if (first_sort && ctx->log.timing) {
         CUDA_OK(cudaEventRecord(ctx->ev[5], st));
     }
     ResolveView rv;
@@ -1572,13 +1574,13 @@ int run_sorted_stages(mspb_ctx *ctx, const mspb_params_t *p, const TreeSeqView &
     }
 
     // ---- K5: byte offsets + rows
-    if (first_sort) {
+    if (first_sort && ctx->log.timing) {
         CUDA_OK(cudaEventRecord(ctx->ev[6], st));
     }
     if (!ctx->pending.defer) {
         TRY(launch_emit(ctx));
     }
-    if (first_sort) {
+    if (first_sort && ctx->log.timing) {
         CUDA_OK(cudaEventRecord(ctx->ev[7], st));
     }
     ctx->last_sv = sv;
@@ -1694,7 +1696,12 @@ static int generate_impl(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t 
     }
 
     // ---- K1: how many new mutations, and where they go
-    CUDA_OK(cudaEventRecord(ctx->ev[1], st));
+    // (the events between the phases are recorded while kernel timing is on only: nine records per overlay are
+    // not free on a 1.7 ms call)
+    const bool phase_events = ctx->log.timing;
+    if (phase_events) {
+        CUDA_OK(cudaEventRecord(ctx->ev[1], st));
+    }
     uint64_t Mnew = 0, num_pairs = 0;
     uint64_t spec_rec = 0, spec_key = 0; // generations of the buffers of a K2 launched ahead of the K1 read-back
     size_t spec_cap = 0;
@@ -1849,7 +1856,9 @@ static int generate_impl(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t 
     }
 
     // ---- buffers: rows are bounded before the sort (M is exact, S <= S0 + Mnew)
-    CUDA_OK(cudaEventRecord(ctx->ev[2], st));
+    if (phase_events) {
+        CUDA_OK(cudaEventRecord(ctx->ev[2], st));
+    }
     const uint64_t M = M0 + Mnew, Scap = S0 + Mnew;
     // (two-phase calls learn their allele-number base only later: size for any uint64)
     const uint64_t maxlen
@@ -1998,7 +2007,7 @@ static int generate_impl(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t 
         CUDA_OK(cudaMemsetAsync(out.mut_der_off, 0, sizeof(uint64_t), st));
         CUDA_OK(cudaMemsetAsync(out.mut_md_off, 0, sizeof(uint64_t), st));
         ctx->md_zero_site_bytes = ctx->md_zero_mut_bytes = 0;
-        for (int e = 3; e <= 7; e++) {
+        for (int e = 3; e <= 7 && phase_events; e++) {
             CUDA_OK(cudaEventRecord(ctx->ev[e], st));
         }
     } else {
@@ -2113,7 +2122,10 @@ static int generate_impl(mspb_ctx_t *ctx, const mspb_params_t *p, mspb_counts_t 
     const uint64_t S = ht->p1.s;
     float total = 0;
     for (int i = 0; i < MSPB_NUM_PHASES; i++) {
-        cudaEventElapsedTime(&ctx->phase_ms[i], ctx->ev[i], ctx->ev[i + 1]);
+        ctx->phase_ms[i] = 0.0f;
+        if (phase_events) {
+            cudaEventElapsedTime(&ctx->phase_ms[i], ctx->ev[i], ctx->ev[i + 1]);
+        }
     }
     cudaEventElapsedTime(&total, ctx->ev[0], ctx->ev[8]);
     mspb_counts_t &c = ctx->counts;
