@@ -224,3 +224,45 @@ def test_number_of_trees_grows_with_the_recombination_rate():
     expected_breaks = 4 * ne * r * (L - 1) * np.sum(1.0 / np.arange(1, n))
     mean = float(np.mean(trees))
     assert 0.6 * expected_breaks < mean - 1 <= 1.05 * expected_breaks
+
+
+def test_prepared_input_paths_agree():
+    """bench.py looks for the simulator's prepared output where scripts/make_reference_input.py (through
+    oracle/ref_ancestry.py) leaves it, without importing anything of oracle/."""
+    import os
+
+    import bench
+
+    for w in bench.WORKLOADS.values():
+        key = "n%d_L%g_r%g_ne%g_seed%d" % (w["samples"], w["L"], w["recomb"], w["ne"], w["ts_seed"])
+        want = os.path.join(bench.ROOT, "oracle", "_ref", "inputs", key + ".npz")
+        assert os.path.normpath(ref_ancestry.cached_input_path(w)) == os.path.normpath(want)
+    src = open(os.path.join(bench.ROOT, "bench.py")).read()
+    body = src[src.index("def load_prepared_input"):src.index("def make_input")]
+    assert "oracle import" not in body and "import oracle" not in body
+
+
+@needs_simulator
+def test_prepared_input_round_trip(tmp_path, monkeypatch):
+    """What the preparation script stores is what the loaders hand back (a small configuration, in a scratch copy
+    of the layout)."""
+    import bench
+
+    w = dict(samples=6, L=500.0, recomb=1e-4, ne=100.0, ts_seed=4)
+    ts = ref_ancestry.sim_ancestry(w["samples"], sequence_length=w["L"], recombination_rate=w["recomb"],
+                                   population_size=w["ne"], random_seed=w["ts_seed"])
+    monkeypatch.setattr(ref_ancestry, "HERE", str(tmp_path / "oracle"))
+    monkeypatch.setattr(bench, "ROOT", str(tmp_path))
+    path = ref_ancestry.cached_input_path(w)
+    import os
+
+    os.makedirs(os.path.dirname(path))
+    np.savez(path, sequence_length=np.float64(ts["sequence_length"]), seconds=np.float64(0.1),
+             node_time=ts["nodes"]["time"], node_flags=ts["nodes"]["flags"], edge_left=ts["edges"]["left"],
+             edge_right=ts["edges"]["right"], edge_parent=ts["edges"]["parent"], edge_child=ts["edges"]["child"])
+    for got in (ref_ancestry.load_cached(w), bench.load_prepared_input(w)):
+        assert got is not None and got["num_trees"] == ts["num_trees"]
+        for tbl, cols in (("nodes", ("time", "flags")), ("edges", ("left", "right", "parent", "child"))):
+            for col in cols:
+                assert np.array_equal(got[tbl][col], ts[tbl][col])
+    assert bench.load_prepared_input(dict(w, ts_seed=5)) is None
