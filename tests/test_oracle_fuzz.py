@@ -150,3 +150,40 @@ def test_port_equals_reference_on_trees_with_several_roots(oracle_mod, case):
         assert not golden_util.diff_tables(want, got)
         assert (got["draws"], got["next_allele"]) == (want["draws"], want["next_allele"])
         ts = cases.with_kept(ts, want)
+
+
+@pytest.mark.parametrize("case", range(60))
+def test_port_equals_reference_on_the_reference_simulators_trees(oracle_mod, case):
+    """The same comparison on tree sequences from the reference's OWN ancestry simulator (lib/msprime.c compiled
+    unmodified, oracle/ref_ancestry.py): random sample sizes, lengths, recombination rates, ploidies and genome kinds;
+    two layers, replay and free-running MT19937."""
+    from oracle import ref_ancestry
+
+    if not oracle_mod.have("ref") or not ref_ancestry.have():
+        pytest.skip("compiled reference absent")
+    rng = np.random.default_rng(9000 + case)
+    L = float(rng.choice([50, 1e3, 2e4]))
+    discrete_trees = bool(rng.random() < 0.7)
+    ts = ref_ancestry.sim_ancestry(
+        int(rng.integers(1, 25)), sequence_length=L, recombination_rate=float(rng.choice([0.0, 1e-4, 1e-3])) / 4,
+        population_size=float(rng.choice([10, 100, 1000])), random_seed=int(rng.integers(1, 2**31)),
+        ploidy=int(rng.integers(1, 3)), discrete_genome=discrete_trees)
+    branch = float(np.sum((ts["edges"]["right"] - ts["edges"]["left"])
+                          * (ts["nodes"]["time"][ts["edges"]["parent"]] - ts["nodes"]["time"][ts["edges"]["child"]])))
+    target = float(rng.choice([5, 50, 400, 2000]))
+    model = random_model(rng)
+    for layer in range(2):
+        position, rate = random_map(rng, L, 2 * target / branch)
+        kw = dict(map_position=position, map_rate=rate, model=model, discrete_genome=bool(rng.random() < 0.7),
+                  keep=bool(layer == 1))
+        if rng.random() < 0.3:
+            kw["seed"] = int(rng.integers(1, 2**32))
+        else:
+            kw["stream"] = rng.random(int(40 * target) + 10_000)
+        want, got = run(oracle_mod, "ref", ts, kw), run(oracle_mod, "port", ts, kw)
+        if isinstance(want, int) or isinstance(got, int):
+            assert want == got, (want, got)
+            return
+        assert not golden_util.diff_tables(want, got)
+        assert (got["draws"], got["next_allele"]) == (want["draws"], want["next_allele"])
+        ts = cases.with_kept(ts, want)
