@@ -173,7 +173,7 @@ def test_port_equals_reference_on_the_reference_simulators_trees(oracle_mod, cas
     target = float(rng.choice([5, 50, 400, 2000]))
     model = random_model(rng)
     for layer in range(2):
-        position, rate = random_map(rng, L, 2 * target / branch)
+        position, rate = random_map(rng, L, 2 * target / (branch or 1.0))  # (one haploid sample: no edges)
         kw = dict(map_position=position, map_rate=rate, model=model, discrete_genome=bool(rng.random() < 0.7),
                   keep=bool(layer == 1))
         if rng.random() < 0.3:
