@@ -151,6 +151,22 @@ __global__ void __launch_bounds__(256) sf_relax_levels_kernel(TreeSeqView ts, ui
     }
 }
 
+// The deepest level.  (A round of the relaxation above works in place, so a node can climb several levels in one
+// round when its descendants' updates happen to land first: the number of rounds does NOT bound the levels.)
+__global__ void __launch_bounds__(256) sf_max_level_kernel(uint64_t n, const uint32_t *__restrict__ level, uint32_t *out)
+{
+    const uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t v = i < n ? level[i] : 0u;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const uint32_t w = __shfl_xor_sync(0xffffffffu, v, o);
+        v = w > v ? w : v;
+    }
+    if ((threadIdx.x & 31) == 0 && v > 0u) {
+        atomicMax(out, v);
+    }
+}
+
 // sort key of an edge: (level of its parent, parent), and how many edges every level has
 __global__ void __launch_bounds__(256) sf_edge_level_keys_kernel(TreeSeqView ts, const uint32_t *__restrict__ level,
     uint64_t *__restrict__ keys, uint32_t *__restrict__ level_count, uint32_t max_levels)

@@ -3170,8 +3170,16 @@ int build_sample_index(mspb_ctx *ctx, const uint32_t *node_flags)
                 return MSPB_ERR_GENERIC; // cannot happen for edges whose parents are older than their children
             }
         }
-        // ---- edges by (level of the parent, parent)
-        const uint32_t max_levels = rounds + 2;
+        // ---- edges by (level of the parent, parent).  The deepest level is read from the levels themselves: the
+        // in-place rounds above can climb several levels at once, so their number is no bound (with `rounds + 2`
+        // buckets the deepest levels of a 2e6-leaf Hudson tree sequence shared the last bucket and their nodes were
+        // summed before their children were final)
+        CUDA_OK(cudaMemsetAsync(t.small.p + 5, 0, sizeof(uint32_t), st));
+        MSPB_LAUNCH(ctx->log, "sf_max_level",
+            sf_max_level_kernel<<<grid_for(N, 256), 256, 0, st>>>(N, t.level.p, t.small.p + 5));
+        CUDA_OK(cudaMemcpyAsync(h_small, t.small.p, sizeof(h_small), cudaMemcpyDeviceToHost, st));
+        CUDA_OK(cudaStreamSynchronize(st));
+        const uint32_t max_levels = h_small[5] + 2;
         DBuf<uint32_t> level_count;
         TRY(level_count.ensure(max_levels + 1));
         struct Rel {

@@ -82,9 +82,19 @@ def test_afs_and_samples_below_match_the_tskit_restatement(native_built, model, 
             ctx.build_sample_index(ts["nodes"]["flags"])  # load_tables dropped the index
 
 
+@pytest.mark.parametrize("source", ["smc", "hudson"])
 @pytest.mark.parametrize("samples, L, seed", [(30, 5e4, 3), (60, 2e5, 4), (500, 1e6, 5)])
-def test_step_functions_match_the_numpy_prototype(native_built, samples, L, seed):
-    ts = cases.smc_ts(samples, L, seed)
+def test_step_functions_match_the_numpy_prototype(native_built, samples, L, seed, source):
+    """source="hudson": the same on tree sequences from the reference's own ancestry simulator."""
+    if source == "hudson":
+        from oracle import ref_ancestry
+
+        if not ref_ancestry.have():
+            pytest.skip("oracle/_ref/libancestry_ref.so not built")
+        ts = ref_ancestry.sim_ancestry(samples, sequence_length=L, recombination_rate=1e-8, population_size=1e4,
+                                       random_seed=seed)
+    else:
+        ts = cases.smc_ts(samples, L, seed)
     fns, stats = below_levels.build_fast(ts)
     with _native.Context(0) as ctx:
         res = overlay(ctx, ts, cases.JC69, 3e-6, seed=seed)
@@ -109,11 +119,20 @@ def test_step_functions_match_the_numpy_prototype(native_built, samples, L, seed
         assert np.array_equal(from_G, afs)
 
 
-def test_config3_size(native_built):
+@pytest.mark.parametrize("source", ["treegen", "reference"])
+def test_config3_size(native_built, source):
     """1e5 samples x 1e8 bp (E = 2.3e6): build time, query time, and samples below a mutation checked by
-    walking the parent array from every sample for a handful of mutations."""
+    walking the parent array from every sample for a handful of mutations.  source="reference": on the tree
+    sequence the reference's own ancestry simulator makes for config 3 (where it has been prepared), whose
+    deepest nodes sit more levels up than the relaxation takes rounds (the index is built twice and must come
+    out the same)."""
     w = bench.WORKLOADS["config3"]
-    ts = synth.native_treeseq(w["samples"], w["L"], w["recomb"], w["ne"], w["ts_seed"])
+    if source == "reference":
+        ts = bench.load_prepared_input(w)
+        if ts is None:
+            pytest.skip("no prepared tree sequence of the reference's simulator for config 3")
+    else:
+        ts = synth.native_treeseq(w["samples"], w["L"], w["recomb"], w["ne"], w["ts_seed"])
     n = int(np.sum(ts["nodes"]["flags"] & 1))
     with _native.Context(0) as ctx:
         res = overlay(ctx, ts, cases.INF_ALLELES, 1e-8, seed=9, offsets32=True)
@@ -121,6 +140,9 @@ def test_config3_size(native_built):
         assert info["num_samples"] == n == 200_000
         afs = ctx.site_afs()
         below = ctx.samples_below()
+        again = ctx.build_sample_index(ts["nodes"]["flags"])
+        assert (again["levels"], again["steps"]) == (info["levels"], info["steps"])
+        assert np.array_equal(ctx.site_afs(), afs) and np.array_equal(ctx.samples_below(), below)
         print(f"config3 sample index: {info}; afs query {ctx.afs_ms:.3f} ms for {len(below)} mutations")
     M = len(below)
     assert M > 400_000 and below.min() >= 1 and below.max() <= n
@@ -151,3 +173,43 @@ def test_config3_size(native_built):
     lower = np.bincount(below[single & (below < n)], minlength=n + 1)
     assert np.all(afs[: n + 1] >= lower) and afs[0] == 0 and afs[n] == 0
     assert afs.sum() <= M and afs.sum() >= lower.sum()
+
+
+def test_config5_size(native_built):
+    """The size bench.py reports its consumer figures on (1e6 diploid samples x 2.5e8 bp; the reference simulator's
+    tree sequence where it has been prepared, else this project's generator's): the deepest nodes sit far more levels
+    up than the level relaxation takes rounds, so the index is built twice and must come out the same, and samples
+    below a mutation are checked against a walk up the parent array for a handful of mutations."""
+    w = bench.WORKLOADS["config5"]
+    ts = bench.load_prepared_input(w)
+    if ts is None:
+        ts = synth.native_treeseq(w["samples"], w["L"], w["recomb"], w["ne"], w["ts_seed"])
+    n = int(np.sum(ts["nodes"]["flags"] & 1))
+    with _native.Context(0) as ctx:
+        res = overlay(ctx, ts, cases.INF_ALLELES, 2e-9, seed=9, offsets32=True)  # ~3e5 mutations
+        info = ctx.build_sample_index(ts["nodes"]["flags"])
+        afs, below = ctx.site_afs(), ctx.samples_below()
+        again = ctx.build_sample_index(ts["nodes"]["flags"])
+        assert (again["levels"], again["steps"]) == (info["levels"], info["steps"])
+        assert np.array_equal(ctx.site_afs(), afs) and np.array_equal(ctx.samples_below(), below)
+    print(f"config5 sample index: {info}")
+    M = len(below)
+    assert info["num_samples"] == n == 2_000_000 and M > 100_000 and below.min() >= 1 and below.max() <= n
+    d = merged(ts, res)
+    samples = consumers.sample_nodes(d)
+    pos = np.asarray(res["sites"]["position"])[np.asarray(res["mutations"]["site"])]
+    rng = np.random.default_rng(2)
+    # (mutations high up in the tree are the ones whose counts pass through the deepest levels)
+    deep = np.argsort(below)[-2000:]
+    for k in list(rng.choice(M, size=2, replace=False)) + list(rng.choice(deep, size=2, replace=False)):
+        parent = consumers.parent_array(d, pos[k])
+        target = res["mutations"]["node"][k]
+        u = samples.copy()
+        hit = np.zeros(len(u), dtype=bool)
+        while True:
+            hit |= u == target
+            alive = (u != -1) & ~hit
+            if not alive.any():
+                break
+            u = np.where(alive, parent[np.maximum(u, 0)], u)
+        assert below[k] == hit.sum(), (k, below[k], hit.sum())
