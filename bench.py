@@ -942,10 +942,15 @@ def run_b200_arm(args, rank, local_rank, world):
     consumers_info = None
     if world == 1 and not args.no_consumers:
         try:
+            first_build = ctx.build_sample_index(ts["nodes"]["flags"])["build_ms"]  # sizes its buffers
             info = ctx.build_sample_index(ts["nodes"]["flags"])
+            info["build_ms_first"] = first_build
             cnt = ctx.generate(params(100 + args.steps - 1))
+            ctx.site_afs()
+            first_afs = ctx.afs_ms  # (allocates the per-row scratch)
             afs = ctx.site_afs()
             consumers_info = {"sample_index": info, "site_afs_ms": round(ctx.afs_ms, 4),
+                              "site_afs_ms_first": round(first_afs, 4),
                               "mutations": int(cnt["num_mutations"]), "afs_total": int(afs.sum()),
                               "afs_head": [int(v) for v in afs[:6]]}
         except Exception as e:  # noqa: BLE001
